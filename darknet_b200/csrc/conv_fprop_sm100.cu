@@ -1,0 +1,517 @@
+// Convolution forward as ONE implicit-GEMM kernel for sm_100a.
+//
+// Replaces ForwardConvolutionalLayerGpu (convolutional_kernels.cu:252-553): cuDNN / per-image
+// im2col_gpu_ext + cublasSgemm, then add_bias_gpu / scale_bias_gpu, activate_array_ongpu, and the
+// shortcut add that follows in residual blocks (shortcut_layer.c:191-204) — all in one launch, with no
+// materialised im2col workspace.
+//
+// GEMM view:  D[M = B*Ho*Wo pixels][N = out_c] = A[M][K = taps*Cin_p] * W[N][K]^T
+//   A rows are gathered by the TMA engine in im2col mode straight from the NHWC activation tensor
+//   (one (tap, 64-channel chunk) slab per pipeline stage; zero padding = TMA out-of-bounds fill), or by a
+//   plain 2-D tiled tensor map for 1x1/stride-1 layers.  W rows come from the pre-packed K-major bf16
+//   weights.  Both land in shared memory in the canonical K-major 128B/64B/32B-swizzled layout that
+//   tcgen05.mma reads through shared-memory descriptors.  Accumulators live in TMEM (two buffers, so the
+//   epilogue of tile i overlaps the main loop of tile i+1).
+//
+// CTA = 192 threads, persistent over tiles (grid = min(tiles, #SM)):
+//   warp 0 / lane 0 : TMA producer        (full/empty mbarrier ring, `stages` deep)
+//   warp 1 / lane 0 : tcgen05.mma issuer  (UMMA 128 x block_n x 16, bf16 -> fp32)
+//   warps 2..5      : epilogue            (tcgen05.ld -> *scale +bias -> act -> +residual -> act2 -> store)
+#include <cuda.h>
+#include <algorithm>
+
+#include "ptx.cuh"
+#include "yc_common.cuh"
+
+namespace yc {
+
+constexpr int kBlockM = 128;
+constexpr int kMaxStages = 16;
+constexpr int kThreads = 192;
+
+struct ConvParams {
+  int M, N, n_store;
+  int taps, ksize, cchunks, block_k, block_n, stages;
+  int m_tiles, n_tiles;
+  int a_mode;  // 0: 2-D tiled map (1x1 s1 p0), 1: im2col map
+  int Ho, Wo, stride, pad, dil;
+  const float* bias;   // padded to n_tiles*block_n
+  const float* scale;  // same padding, or nullptr
+  void* y;
+  long long ldy;
+  int y_f32;
+  const __nv_bfloat16* res;
+  long long ldres;
+  int act, act2;
+  uint32_t tmem_cols;
+};
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                  const ConvParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  // 1024-byte alignment: required by the 128B swizzle atom (8 rows x 128 B)
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t a_bytes = kBlockM * p.block_k * 2;
+  const uint32_t b_bytes = ((uint32_t)(p.block_n * p.block_k * 2) + 1023u) & ~1023u;
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t tx_bytes = a_bytes + (uint32_t)(p.block_n * p.block_k * 2);
+  const uint32_t bar_base = smem_base + p.stages * stage_bytes;  // 8-byte aligned
+  // barrier map: full[s] @ +8s, empty[s] @ +8(kMaxStages+s), tmem_full[2], tmem_empty[2], tmem ptr
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tmap(&tmap_a);
+    ptx::prefetch_tmap(&tmap_b);
+    for (int s = 0; s < p.stages; ++s) {
+      ptx::mbar_init(full_bar(s), 1);
+      ptx::mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      ptx::mbar_init(tfull_bar(a), 1);
+      ptx::mbar_init(tempty_bar(a), 4);  // one arrival per epilogue warp
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_slot, p.tmem_cols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  const int total_tiles = p.m_tiles * p.n_tiles;
+  const int k_blocks = p.taps * p.cchunks;
+
+  if (warp == 0 && lane == 0) {
+    // ===================== TMA producer =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    const int hw = p.Ho * p.Wo;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int m0 = (t / p.n_tiles) * kBlockM;
+      const int n0 = (t % p.n_tiles) * p.block_n;
+      int img = 0, base_w = 0, base_h = 0;
+      if (p.a_mode == 1) {
+        img = m0 / hw;
+        const int rem = m0 - img * hw;
+        const int ho = rem / p.Wo;
+        base_h = ho * p.stride - p.pad;
+        base_w = (rem - ho * p.Wo) * p.stride - p.pad;
+      }
+      int kb = 0;
+      for (int tap = 0; tap < p.taps; ++tap) {
+        const int r = tap / p.ksize, s = tap - r * p.ksize;
+        for (int cc = 0; cc < p.cchunks; ++cc, ++kb) {
+          ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = smem_base + stage * stage_bytes;
+          const uint32_t sb = sa + a_bytes;
+          ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
+          if (p.a_mode == 1)
+            ptx::tma_load_im2col_4d(sa, &tmap_a, full_bar(stage), cc * p.block_k, base_w, base_h, img,
+                                    (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
+          else
+            ptx::tma_load_2d(sa, &tmap_a, full_bar(stage), cc * p.block_k, m0);
+          ptx::tma_load_2d(sb, &tmap_b, full_bar(stage), kb * p.block_k, n0);
+          if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc = ptx::make_idesc_bf16(kBlockM, p.block_n);
+    const uint32_t row_bytes = p.block_k * 2;
+    const int k_steps = p.block_k / 16;
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * p.block_n;
+      for (int kb = 0; kb < k_blocks; ++kb) {
+        ptx::mbar_wait(full_bar(stage), phase);
+        ptx::tc_fence_after();
+        const uint32_t sa = smem_base + stage * stage_bytes;
+        const uint64_t adesc = ptx::make_smem_desc(sa, row_bytes);
+        const uint64_t bdesc = ptx::make_smem_desc(sa + a_bytes, row_bytes);
+        for (int k = 0; k < k_steps; ++k) {
+          // advancing K by 16 bf16 = 32 bytes inside the swizzle atom: +2 in the (addr>>4) field
+          ptx::mma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+        }
+        ptx::mma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
+        if (kb == k_blocks - 1) ptx::mma_commit(tfull_bar(acc));
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp >= 2) {
+    // ===================== epilogue =====================
+    const int quad = warp & 3;  // TMEM lane quadrant this warp may access
+    int it = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      const int m0 = (t / p.n_tiles) * kBlockM;
+      const int n0 = (t % p.n_tiles) * p.block_n;
+      const long long row = (long long)m0 + quad * 32 + lane;
+      const bool row_ok = row < p.M;
+      ptx::mbar_wait(tfull_bar(acc), acc_phase);
+      ptx::tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * p.block_n;
+      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
+        const int col0 = n0 + c0;
+        if (col0 >= p.n_store) break;  // warp-uniform
+        uint32_t r[32];
+        ptx::tmem_ld_32x32b_x32(t_row + c0, r);
+        ptx::tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+          float4 s4 = make_float4(1.f, 1.f, 1.f, 1.f);
+          if (p.scale) s4 = __ldg(reinterpret_cast<const float4*>(p.scale + col0 + j));
+          v[j + 0] = fmaf(__uint_as_float(r[j + 0]), s4.x, b4.x);
+          v[j + 1] = fmaf(__uint_as_float(r[j + 1]), s4.y, b4.y);
+          v[j + 2] = fmaf(__uint_as_float(r[j + 2]), s4.z, b4.z);
+          v[j + 3] = fmaf(__uint_as_float(r[j + 3]), s4.w, b4.w);
+        }
+        if (p.act != YC_LINEAR) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act);
+        }
+        if (p.res != nullptr && row_ok) {
+          const __nv_bfloat16* rp = p.res + row * p.ldres + col0;
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            if (col0 + j + 8 <= p.n_store) {
+              const uint4 q = __ldg(reinterpret_cast<const uint4*>(rp + j));
+              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 f = __bfloat1622float2(h[e]);
+                v[j + 2 * e] += f.x;
+                v[j + 2 * e + 1] += f.y;
+              }
+            }
+          }
+          if (p.act2 != YC_LINEAR) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act2);
+          }
+        }
+        if (row_ok) {
+          if (p.y_f32) {
+            float* yp = reinterpret_cast<float*>(p.y) + row * p.ldy + col0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              if (col0 + j + 4 <= p.n_store)
+                *reinterpret_cast<float4*>(yp + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+            __nv_bfloat16* yp = reinterpret_cast<__nv_bfloat16*>(p.y) + row * p.ldy + col0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 8)
+              if (col0 + j + 8 <= p.n_store) {
+                uint4 q;
+                q.x = pack_bf16x2(v[j + 0], v[j + 1]);
+                q.y = pack_bf16x2(v[j + 2], v[j + 3]);
+                q.z = pack_bf16x2(v[j + 4], v[j + 5]);
+                q.w = pack_bf16x2(v[j + 6], v[j + 7]);
+                *reinterpret_cast<uint4*>(yp + j) = q;
+              }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(tempty_bar(acc));
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+// ---- weight packing: OIHW fp32 -> [out_c][tap][in_c_p] bf16 ------------------------------------
+__global__ void pack_weights_kernel(const float* __restrict__ w, int out_c, int in_c, int taps, int in_c_p,
+                                    __nv_bfloat16* __restrict__ out) {
+  const long long total = (long long)out_c * taps * in_c_p;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % in_c_p);
+    const int tap = (int)((i / in_c_p) % taps);
+    const int n = (int)(i / ((long long)in_c_p * taps));
+    float v = 0.f;
+    if (c < in_c) v = w[((long long)n * in_c + c) * taps + tap];
+    out[i] = __float2bfloat16_rn(v);
+  }
+}
+
+}  // namespace yc
+
+// ================================== host side ==================================================
+using namespace yc;
+
+struct yc_conv_plan {
+  CUtensorMap tmap_a, tmap_b;
+  ConvParams p;
+  float* bias_pad = nullptr;
+  float* scale_pad = nullptr;
+  int grid = 0;
+  size_t smem = 0;
+};
+
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn g_encode_tiled = nullptr;
+EncodeIm2colFn g_encode_im2col = nullptr;
+
+int load_driver_entry_points() {
+  if (g_encode_tiled && g_encode_im2col) return YC_OK;
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qr;
+  YC_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr));
+  YC_REQUIRE(fn && qr == cudaDriverEntryPointSuccess, "cuTensorMapEncodeTiled not available");
+  g_encode_tiled = (EncodeTiledFn)fn;
+  YC_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &fn, cudaEnableDefault, &qr));
+  YC_REQUIRE(fn && qr == cudaDriverEntryPointSuccess, "cuTensorMapEncodeIm2col not available");
+  g_encode_im2col = (EncodeIm2colFn)fn;
+  return YC_OK;
+}
+
+int pick_block_k(int in_c) {
+  if (in_c % 64 == 0) return 64;
+  if (in_c % 32 == 0) return 32;
+  return 16;
+}
+
+CUtensorMapSwizzle swizzle_for(int block_k) {
+  return block_k == 64 ? CU_TENSOR_MAP_SWIZZLE_128B
+                       : (block_k == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+}
+
+}  // namespace
+
+extern "C" int yc_conv_padded_in_c(int in_c) { return round_up(in_c, pick_block_k(in_c)); }
+
+extern "C" size_t yc_conv_packed_bytes(int out_c, int in_c, int ksize) {
+  return (size_t)out_c * ksize * ksize * yc_conv_padded_in_c(in_c) * 2;
+}
+
+extern "C" int yc_conv_pack(const float* w, int out_c, int in_c, int ksize, void* out, void* stream) {
+  YC_REQUIRE(w && out && out_c > 0 && in_c > 0 && ksize > 0, "yc_conv_pack: bad arguments");
+  const int in_c_p = yc_conv_padded_in_c(in_c);
+  const long long total = (long long)out_c * ksize * ksize * in_c_p;
+  const int blocks = (int)std::min<long long>(ceil_div_ll(total, 256), 148 * 8);
+  pack_weights_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, out_c, in_c, ksize * ksize, in_c_p,
+                                                                 (__nv_bfloat16*)out);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* d, const yc_tensor* x,
+                                   const void* w_packed, const float* bias, const float* scale,
+                                   const yc_tensor* residual, const yc_tensor* y) {
+  YC_REQUIRE(out_plan && d && x && w_packed && bias && y, "yc_conv_plan_create: null argument");
+  YC_REQUIRE(x->dtype == YC_BF16, "conv input must be bf16 NHWC");
+  YC_REQUIRE(x->ldc % 8 == 0 && ((uintptr_t)x->ptr & 15) == 0, "conv input view must be 16-byte aligned (ldc%%8)");
+  YC_REQUIRE(d->ksize >= 1 && d->stride >= 1 && d->dilation >= 1 && d->pad >= 0, "bad conv geometry");
+  const int eff = d->dilation * (d->ksize - 1) + 1;
+  const int Ho = (x->h + 2 * d->pad - eff) / d->stride + 1;
+  const int Wo = (x->w + 2 * d->pad - eff) / d->stride + 1;
+  YC_REQUIRE(y->n == x->n && y->h == Ho && y->w == Wo, "conv output shape mismatch: want %dx%d got %dx%d", Ho, Wo,
+             y->h, y->w);
+  const int elt = y->dtype == YC_F32 ? 4 : 8;  // store granularity in elements (16 bytes)
+  YC_REQUIRE(y->ldc % elt == 0 && ((uintptr_t)y->ptr & 15) == 0, "conv output view must be 16-byte aligned");
+  if (residual) {
+    YC_REQUIRE(residual->dtype == YC_BF16 && residual->n == y->n && residual->h == y->h && residual->w == y->w &&
+                   residual->c == y->c && residual->ldc % 8 == 0 && ((uintptr_t)residual->ptr & 15) == 0,
+               "residual must be a bf16 view of the output's shape");
+  }
+  YC_REQUIRE((long long)x->n * Ho * Wo < (1LL << 31), "M too large");
+  int rc = load_driver_entry_points();
+  if (rc) return rc;
+
+  yc_conv_plan* pl = new yc_conv_plan();
+  ConvParams& p = pl->p;
+  const int N = y->c;
+  p.M = x->n * Ho * Wo;
+  p.N = N;
+  // columns we may write: up to the padded pitch when the tensor owns its pitch, else exactly c
+  p.n_store = std::min(round_up(N, elt), (int)y->ldc);
+  YC_REQUIRE(p.n_store % elt == 0, "output channel count must be a multiple of %d for this view", elt);
+  p.taps = d->ksize * d->ksize;
+  p.ksize = d->ksize;
+  p.block_k = pick_block_k(x->c);
+  const int in_c_p = round_up(x->c, p.block_k);
+  p.cchunks = in_c_p / p.block_k;
+  p.a_mode = (d->ksize == 1 && d->stride == 1 && d->pad == 0) ? 0 : 1;
+  p.Ho = Ho; p.Wo = Wo; p.stride = d->stride; p.pad = d->pad; p.dil = d->dilation;
+  p.m_tiles = ceil_div(p.M, kBlockM);
+
+  // ---- tile width: minimise (waves x per-tile cost); per-tile cost ~ block_n + fixed overhead -----
+  const int sms = sm_count();
+  int best_bn = 32;
+  double best_cost = 1e30;
+  for (int bn = 32; bn <= 256; bn += 32) {
+    if (bn > round_up(N, 32)) break;
+    const int nt = ceil_div(N, bn);
+    const long long tiles = (long long)p.m_tiles * nt;
+    const double waves = (double)ceil_div_ll(tiles, sms);
+    // MMA time ~ bn (cycles per K=16 step: 128*bn/256) ; A-operand smem reads put a floor near bn=128
+    const double per_tile = std::max(bn, 96) + 24.0;
+    const double cost = waves * per_tile;
+    if (cost < best_cost - 1e-9) { best_cost = cost; best_bn = bn; }
+  }
+  p.block_n = best_bn;
+  p.n_tiles = ceil_div(N, p.block_n);
+  const uint32_t a_bytes = kBlockM * p.block_k * 2;
+  const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t smem_budget = 227 * 1024 - 1024 /*align slack*/ - 512 /*barriers*/;
+  p.stages = std::min<int>(kMaxStages, smem_budget / stage_bytes);
+  p.stages = std::min(p.stages, std::max(2, p.taps * p.cchunks * 2));
+  YC_REQUIRE(p.stages >= 2, "tile does not fit shared memory");
+  pl->smem = (size_t)p.stages * stage_bytes + 1024 + 512;
+  uint32_t cols = 32;
+  while (cols < (uint32_t)(2 * p.block_n)) cols <<= 1;
+  p.tmem_cols = cols;
+  p.act = d->activation;
+  p.act2 = d->residual_activation;
+  p.y = y->ptr; p.ldy = y->ldc; p.y_f32 = (y->dtype == YC_F32);
+  p.res = residual ? (const __nv_bfloat16*)residual->ptr : nullptr;
+  p.ldres = residual ? residual->ldc : 0;
+
+  // ---- padded bias / scale ------------------------------------------------------------------------
+  const int npad = p.n_tiles * p.block_n;
+  cudaError_t e = cudaMalloc(&pl->bias_pad, sizeof(float) * npad);
+  if (e == cudaSuccess) e = cudaMemset(pl->bias_pad, 0, sizeof(float) * npad);
+  if (e == cudaSuccess) e = cudaMemcpy(pl->bias_pad, bias, sizeof(float) * N, cudaMemcpyDeviceToDevice);
+  if (e == cudaSuccess && scale) {
+    e = cudaMalloc(&pl->scale_pad, sizeof(float) * npad);
+    if (e == cudaSuccess) e = cudaMemset(pl->scale_pad, 0, sizeof(float) * npad);
+    if (e == cudaSuccess) e = cudaMemcpy(pl->scale_pad, scale, sizeof(float) * N, cudaMemcpyDeviceToDevice);
+  }
+  if (e != cudaSuccess) {
+    set_error("yc_conv_plan_create: bias staging failed: %s", cudaGetErrorString(e));
+    yc_conv_plan_destroy(pl);
+    return YC_ERR_CUDA;
+  }
+  p.bias = pl->bias_pad;
+  p.scale = pl->scale_pad;
+
+  // ---- tensor maps ---------------------------------------------------------------------------------
+  const CUtensorMapSwizzle swz = swizzle_for(p.block_k);
+  CUresult cr;
+  if (p.a_mode == 0) {
+    cuuint64_t dims[2] = {(cuuint64_t)x->c, (cuuint64_t)p.M};
+    cuuint64_t strides[1] = {(cuuint64_t)x->ldc * 2};
+    cuuint32_t box[2] = {(cuuint32_t)p.block_k, (cuuint32_t)kBlockM};
+    cuuint32_t estr[2] = {1, 1};
+    cr = g_encode_tiled(&pl->tmap_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, x->ptr, dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  } else {
+    cuuint64_t dims[4] = {(cuuint64_t)x->c, (cuuint64_t)x->w, (cuuint64_t)x->h, (cuuint64_t)x->n};
+    cuuint64_t strides[3] = {(cuuint64_t)x->ldc * 2, (cuuint64_t)x->ldc * 2 * x->w,
+                             (cuuint64_t)x->ldc * 2 * x->w * x->h};
+    // base-pixel bounding box (fprop): lower = -pad, upper = pad - (k-1)*dilation  (relative to W-1/H-1)
+    int lower[2] = {-d->pad, -d->pad};
+    int upper[2] = {d->pad - (d->ksize - 1) * d->dilation, d->pad - (d->ksize - 1) * d->dilation};
+    cuuint32_t estr[4] = {1, (cuuint32_t)d->stride, (cuuint32_t)d->stride, 1};
+    cr = g_encode_im2col(&pl->tmap_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, x->ptr, dims, strides, lower, upper,
+                         (cuuint32_t)p.block_k, (cuuint32_t)kBlockM, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  if (cr != CUDA_SUCCESS) {
+    set_error("yc_conv_plan_create: activation tensor map encode failed (CUresult %d, mode %d, c=%d ldc=%d)", (int)cr,
+              p.a_mode, x->c, x->ldc);
+    yc_conv_plan_destroy(pl);
+    return YC_ERR_CUDA;
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)p.taps * in_c_p, (cuuint64_t)N};
+    cuuint64_t strides[1] = {(cuuint64_t)p.taps * in_c_p * 2};
+    cuuint32_t box[2] = {(cuuint32_t)p.block_k, (cuuint32_t)p.block_n};
+    cuuint32_t estr[2] = {1, 1};
+    cr = g_encode_tiled(&pl->tmap_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(w_packed), dims, strides,
+                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  if (cr != CUDA_SUCCESS) {
+    set_error("yc_conv_plan_create: weight tensor map encode failed (CUresult %d)", (int)cr);
+    yc_conv_plan_destroy(pl);
+    return YC_ERR_CUDA;
+  }
+
+  pl->grid = (int)std::min<long long>((long long)p.m_tiles * p.n_tiles, sms);
+  static bool attr_set = false;
+  if (!attr_set) {
+    e = cudaFuncSetAttribute(conv_fprop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) {
+      set_error("cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(e));
+      yc_conv_plan_destroy(pl);
+      return YC_ERR_CUDA;
+    }
+    attr_set = true;
+  }
+  *out_plan = pl;
+  return YC_OK;
+}
+
+extern "C" int yc_conv_plan_destroy(yc_conv_plan* pl) {
+  if (!pl) return YC_OK;
+  if (pl->bias_pad) cudaFree(pl->bias_pad);
+  if (pl->scale_pad) cudaFree(pl->scale_pad);
+  delete pl;
+  return YC_OK;
+}
+
+extern "C" int yc_conv_fprop(const yc_conv_plan* pl, void* stream) {
+  YC_REQUIRE(pl, "yc_conv_fprop: null plan");
+  conv_fprop_kernel<<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->p);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+extern "C" int yc_conv_plan_info(const yc_conv_plan* pl, int what) {
+  if (!pl) return -1;
+  switch (what) {
+    case 0: return pl->p.block_n;
+    case 1: return pl->p.block_k;
+    case 2: return pl->p.stages;
+    case 3: return pl->p.m_tiles * pl->p.n_tiles;
+    case 4: return pl->grid;
+    case 5: return pl->p.a_mode;
+    case 6: return (int)pl->smem;
+  }
+  return -1;
+}

@@ -1,0 +1,356 @@
+// Memory-bound layers of the hot path on NHWC views: layout conversion at the seam, maxpool,
+// upsample, shortcut, route copy, scale_channels, reorg.  One pass each, 128-bit accesses along the
+// channel axis, grids sized as a multiple of the SM count with grid-stride loops.
+// Replaces maxpool_layer_kernels.cu and the corresponding pieces of blas_kernels.cu (cited per kernel).
+#include <float.h>
+#include <algorithm>
+
+#include "yc_common.cuh"
+
+namespace yc {
+
+struct View {
+  void* ptr;
+  int n, h, w, c;
+  long long ldc;
+  int f32;
+};
+static inline View mk(const yc_tensor* t) { return View{t->ptr, t->n, t->h, t->w, t->c, t->ldc, t->dtype == YC_F32}; }
+
+static inline int grid_for(long long work, int threads) {
+  long long blocks = ceil_div_ll(work, threads);
+  long long cap = (long long)sm_count() * 16;
+  return (int)std::max<long long>(1, std::min(blocks, cap));
+}
+
+// ---- 8-channel vector load/store on a view (bf16: one 16-byte access; fp32: two) ------------------
+struct V8 { float v[8]; };
+
+__device__ __forceinline__ V8 load8(const View& t, long long pix, int c0) {
+  V8 r;
+  if (t.f32) {
+    const float* p = reinterpret_cast<const float*>(t.ptr) + pix * t.ldc + c0;
+    if (c0 + 8 <= t.c && (t.ldc & 3) == 0) {
+      const float4 a = *reinterpret_cast<const float4*>(p), b = *reinterpret_cast<const float4*>(p + 4);
+      r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) r.v[j] = (c0 + j < t.c) ? p[j] : 0.f;
+    }
+  } else {
+    const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(t.ptr) + pix * t.ldc + c0;
+    if (c0 + 8 <= t.c) {
+      const uint4 q = *reinterpret_cast<const uint4*>(p);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = __bfloat1622float2(h[e]);
+        r.v[2 * e] = f.x; r.v[2 * e + 1] = f.y;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) r.v[j] = (c0 + j < t.c) ? __bfloat162float(p[j]) : 0.f;
+    }
+  }
+  return r;
+}
+__device__ __forceinline__ void store8(const View& t, long long pix, int c0, const V8& r) {
+  if (t.f32) {
+    float* p = reinterpret_cast<float*>(t.ptr) + pix * t.ldc + c0;
+    if (c0 + 8 <= t.c && (t.ldc & 3) == 0) {
+      *reinterpret_cast<float4*>(p) = make_float4(r.v[0], r.v[1], r.v[2], r.v[3]);
+      *reinterpret_cast<float4*>(p + 4) = make_float4(r.v[4], r.v[5], r.v[6], r.v[7]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) if (c0 + j < t.c) p[j] = r.v[j];
+    }
+  } else {
+    __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(t.ptr) + pix * t.ldc + c0;
+    if (c0 + 8 <= t.c) {
+      uint4 q;
+      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&q);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(r.v[2 * e], r.v[2 * e + 1]);
+      *reinterpret_cast<uint4*>(p) = q;
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) if (c0 + j < t.c) p[j] = __float2bfloat16_rn(r.v[j]);
+    }
+  }
+}
+
+// ---- NCHW fp32 <-> NHWC view ------------------------------------------------------------------------
+// thread = (pixel, 8-channel group), pixel fastest across threads so the NCHW side is coalesced.
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, View dst, int real_c) {
+  // dst.c may be rounded up to the (owned) pitch so that padded channels are written as zeros with
+  // the same 16-byte store; real_c is the number of channels present in src.
+  const long long hw = (long long)dst.h * dst.w;
+  const int groups = (dst.c + 7) / 8;
+  const long long total = (long long)dst.n * hw * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long s = i % hw;
+    const int g = (int)((i / hw) % groups);
+    const long long b = i / (hw * groups);
+    V8 r;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = g * 8 + j;
+      r.v[j] = c < real_c ? src[(b * real_c + c) * hw + s] : 0.f;
+    }
+    store8(dst, b * hw + s, g * 8, r);
+  }
+}
+__global__ void nhwc_to_nchw_kernel(View src, float* __restrict__ dst) {
+  const long long hw = (long long)src.h * src.w;
+  const int groups = (src.c + 7) / 8;
+  const long long total = (long long)src.n * hw * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long s = i % hw;
+    const int g = (int)((i / hw) % groups);
+    const long long b = i / (hw * groups);
+    const V8 r = load8(src, b * hw + s, g * 8);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = g * 8 + j;
+      if (c < src.c) dst[(b * src.c + c) * hw + s] = r.v[j];
+    }
+  }
+}
+
+// ---- maxpool: forward_maxpool_layer_kernel (maxpool_layer_kernels.cu:58-101) ----------------------
+// thread = (output pixel, 8-channel group), channel group fastest -> every window tap is one
+// contiguous 16-byte read per thread, fully coalesced across the warp.
+__global__ void maxpool_kernel(View x, View y, int size, int stride, int pad, int quirk) {
+  const int groups = (x.c + 7) / 8;
+  const long long total = (long long)y.n * y.h * y.w * groups;
+  const int off = -pad / 2;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    long long pix = i / groups;
+    const int ow = (int)(pix % y.w);
+    const int oh = (int)((pix / y.w) % y.h);
+    const long long b = pix / ((long long)y.w * y.h);
+    // reference CPU-inference artefact (gemm.c:2127-2150): in 8-wide blocks j0 < out_w-8-(size-1) a tap is
+    // dropped for the whole block when it is out of range for the block's FIRST column.
+    const int j0 = (ow / 8) * 8;
+    const bool qblock = quirk && stride == 1 && j0 < y.w - 8 - (size - 1);
+    V8 m;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) m.v[j] = -FLT_MAX;
+    for (int n = 0; n < size; ++n) {
+      const int ih = off + oh * stride + n;
+      if (ih < 0 || ih >= x.h) continue;
+      for (int k = 0; k < size; ++k) {
+        const int iw = off + ow * stride + k;
+        if (iw < 0 || iw >= x.w) continue;
+        if (qblock && (off + j0 + k < 0)) continue;
+        const V8 v = load8(x, (b * x.h + ih) * x.w + iw, g * 8);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m.v[j] = v.v[j] > m.v[j] ? v.v[j] : m.v[j];
+      }
+    }
+    store8(y, pix, g * 8, m);
+  }
+}
+
+// ---- upsample: upsample_kernel (blas_kernels.cu:1121-1155), forward, nearest ----------------------
+__global__ void upsample_kernel(View x, View y, int stride, float scale) {
+  const int groups = (x.c + 7) / 8;
+  const long long total = (long long)y.n * y.h * y.w * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long pix = i / groups;
+    const int ow = (int)(pix % y.w);
+    const int oh = (int)((pix / y.w) % y.h);
+    const long long b = pix / ((long long)y.w * y.h);
+    V8 v = load8(x, (b * x.h + oh / stride) * x.w + ow / stride, g * 8);
+    if (scale != 1.f) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v.v[j] *= scale;
+    }
+    store8(y, pix, g * 8, v);
+  }
+}
+
+// ---- shortcut: shortcut_singlelayer_simple_kernel (blas_kernels.cu:941-978) + activation ----------
+__global__ void shortcut_kernel(View a, View b, View y, int act) {
+  const int groups = (y.c + 7) / 8;
+  const long long total = (long long)y.n * y.h * y.w * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long pix = i / groups;
+    V8 va = load8(a, pix, g * 8);
+    const V8 vb = load8(b, pix, g * 8);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) va.v[j] = apply_act(va.v[j] + vb.v[j], act);
+    store8(y, pix, g * 8, va);
+  }
+}
+
+// ---- route copy: simple_copy_kernel (blas_kernels.cu:520-525) on views ------------------------------
+__global__ void copy_kernel(View s, View d) {
+  const int groups = (d.c + 7) / 8;
+  const long long total = (long long)d.n * d.h * d.w * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long pix = i / groups;
+    store8(d, pix, g * 8, load8(s, pix, g * 8));
+  }
+}
+
+// ---- scale_channels: scale_channels_kernel (blas_kernels.cu:1318-1346) -----------------------------
+__global__ void scale_channels_kernel(View x, View s, View y, int act) {
+  const int groups = (y.c + 7) / 8;
+  const long long hw = (long long)y.h * y.w;
+  const long long total = (long long)y.n * hw * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long pix = i / groups;
+    V8 v = load8(x, pix, g * 8);
+    const V8 sc = load8(s, pix / hw, g * 8);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v.v[j] = apply_act(v.v[j] * sc.v[j], act);
+    store8(y, pix, g * 8, v);
+  }
+}
+
+// ---- reorg: reorg_kernel (blas_kernels.cu:368-402), index math of reorg_cpu (blas.c:12-46) ----------
+// forward==0 (what [reorg] forward uses): y[b,k,j,i] = x[b, k%in_c, j*s + (k/in_c)/s, i*s + (k/in_c)%s]
+// forward==1: the inverse scatter.  Scalar: not used by any of the five configs.
+__device__ __forceinline__ float ld1(const View& t, long long pix, int c) {
+  return t.f32 ? reinterpret_cast<const float*>(t.ptr)[pix * t.ldc + c]
+               : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(t.ptr)[pix * t.ldc + c]);
+}
+__device__ __forceinline__ void st1(const View& t, long long pix, int c, float v) {
+  if (t.f32) reinterpret_cast<float*>(t.ptr)[pix * t.ldc + c] = v;
+  else reinterpret_cast<__nv_bfloat16*>(t.ptr)[pix * t.ldc + c] = __float2bfloat16_rn(v);
+}
+__global__ void reorg_kernel(View x, View y, int stride, int forward) {
+  // "small" = the tensor with (c*s*s, h/s, w/s); "big" = (c, h, w).  forward==0: y small <- x big.
+  const View sm = forward ? x : y;
+  const View bg = forward ? y : x;
+  const int in_c = sm.c / (stride * stride);
+  const long long total = (long long)sm.n * sm.h * sm.w * sm.c;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % sm.c);
+    const long long pix = i / sm.c;
+    const int ii = (int)(pix % sm.w);
+    const int jj = (int)((pix / sm.w) % sm.h);
+    const long long b = pix / ((long long)sm.w * sm.h);
+    const int c2 = k % in_c, offset = k / in_c;
+    const int w2 = ii * stride + offset % stride, h2 = jj * stride + offset / stride;
+    const long long bpix = (b * bg.h + h2) * bg.w + w2;
+    if (forward) st1(bg, bpix, c2, ld1(sm, pix, k));
+    else st1(sm, pix, k, ld1(bg, bpix, c2));
+  }
+}
+
+}  // namespace yc
+
+using namespace yc;
+
+#define YC_CHECK_T(t, name) YC_REQUIRE((t) && (t)->ptr && (t)->n > 0 && (t)->h > 0 && (t)->w > 0 && (t)->c > 0 && (t)->ldc >= (t)->c, "%s: bad tensor", name)
+static bool aligned16(const yc_tensor* t) {
+  const int e = t->dtype == YC_F32 ? 4 : 8;
+  return ((uintptr_t)t->ptr & 15) == 0 && t->ldc % e == 0;
+}
+
+extern "C" int yc_nchw_to_nhwc(const float* src, const yc_tensor* dst, void* stream) {
+  YC_CHECK_T(dst, "yc_nchw_to_nhwc");
+  YC_REQUIRE(src && aligned16(dst), "yc_nchw_to_nhwc: dst must be 16-byte aligned");
+  const long long work = (long long)dst->n * dst->h * dst->w * ((dst->c + 7) / 8);
+  View d = mk(dst);
+  const int e = dst->dtype == YC_F32 ? 4 : 8;
+  if (dst->ldc == round_up(dst->c, e)) d.c = (int)dst->ldc;  // tensor owns its pitch: zero-fill the pad lanes
+  nchw_to_nhwc_kernel<<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(src, d, dst->c);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+extern "C" int yc_nhwc_to_nchw(const yc_tensor* src, float* dst, void* stream) {
+  YC_CHECK_T(src, "yc_nhwc_to_nchw");
+  YC_REQUIRE(dst && aligned16(src), "yc_nhwc_to_nchw: src must be 16-byte aligned");
+  const long long work = (long long)src->n * src->h * src->w * ((src->c + 7) / 8);
+  nhwc_to_nchw_kernel<<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(mk(src), dst);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+extern "C" int yc_maxpool_fwd(const yc_tensor* x, const yc_tensor* y, int size, int stride, int pad, int quirk,
+                              void* stream) {
+  YC_CHECK_T(x, "yc_maxpool_fwd x");
+  YC_CHECK_T(y, "yc_maxpool_fwd y");
+  YC_REQUIRE(aligned16(x) && aligned16(y), "yc_maxpool_fwd: views must be 16-byte aligned");
+  YC_REQUIRE(size >= 1 && stride >= 1 && pad >= 0, "yc_maxpool_fwd: bad geometry");
+  YC_REQUIRE(y->n == x->n && y->c == x->c && y->h == (x->h + pad - size) / stride + 1 &&
+                 y->w == (x->w + pad - size) / stride + 1,
+             "yc_maxpool_fwd: output shape mismatch");
+  const long long work = (long long)y->n * y->h * y->w * ((y->c + 7) / 8);
+  maxpool_kernel<<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(mk(x), mk(y), size, stride, pad, quirk);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+extern "C" int yc_upsample_fwd(const yc_tensor* x, const yc_tensor* y, int stride, float scale, void* stream) {
+  YC_CHECK_T(x, "yc_upsample_fwd x");
+  YC_CHECK_T(y, "yc_upsample_fwd y");
+  YC_REQUIRE(aligned16(x) && aligned16(y), "yc_upsample_fwd: views must be 16-byte aligned");
+  YC_REQUIRE(stride >= 1 && y->n == x->n && y->c == x->c && y->h == x->h * stride && y->w == x->w * stride,
+             "yc_upsample_fwd: output shape mismatch");
+  const long long work = (long long)y->n * y->h * y->w * ((y->c + 7) / 8);
+  upsample_kernel<<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(mk(x), mk(y), stride, scale);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+static bool same_shape(const yc_tensor* a, const yc_tensor* b) {
+  return a->n == b->n && a->h == b->h && a->w == b->w && a->c == b->c;
+}
+
+extern "C" int yc_shortcut_fwd(const yc_tensor* a, const yc_tensor* b, const yc_tensor* y, int act, void* stream) {
+  YC_CHECK_T(a, "yc_shortcut_fwd a");
+  YC_CHECK_T(b, "yc_shortcut_fwd b");
+  YC_CHECK_T(y, "yc_shortcut_fwd y");
+  YC_REQUIRE(same_shape(a, b) && same_shape(a, y), "yc_shortcut_fwd: shapes differ (the reference asserts equal dims, shortcut_layer.c:151-164)");
+  YC_REQUIRE(aligned16(a) && aligned16(b) && aligned16(y), "yc_shortcut_fwd: views must be 16-byte aligned");
+  const long long work = (long long)y->n * y->h * y->w * ((y->c + 7) / 8);
+  shortcut_kernel<<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(mk(a), mk(b), mk(y), act);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+extern "C" int yc_route_copy(const yc_tensor* s, const yc_tensor* d, void* stream) {
+  YC_CHECK_T(s, "yc_route_copy src");
+  YC_CHECK_T(d, "yc_route_copy dst");
+  YC_REQUIRE(same_shape(s, d) && aligned16(s) && aligned16(d), "yc_route_copy: shape/alignment mismatch");
+  const long long work = (long long)d->n * d->h * d->w * ((d->c + 7) / 8);
+  copy_kernel<<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(mk(s), mk(d));
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+extern "C" int yc_scale_channels_fwd(const yc_tensor* x, const yc_tensor* s, const yc_tensor* y, int act, void* stream) {
+  YC_CHECK_T(x, "yc_scale_channels_fwd x");
+  YC_CHECK_T(s, "yc_scale_channels_fwd s");
+  YC_CHECK_T(y, "yc_scale_channels_fwd y");
+  YC_REQUIRE(same_shape(x, y) && s->n == x->n && s->c == x->c && s->h == 1 && s->w == 1,
+             "yc_scale_channels_fwd: scale must be [n,1,1,c]");
+  YC_REQUIRE(aligned16(x) && aligned16(s) && aligned16(y), "yc_scale_channels_fwd: alignment");
+  const long long work = (long long)y->n * y->h * y->w * ((y->c + 7) / 8);
+  scale_channels_kernel<<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(mk(x), mk(s), mk(y), act);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+extern "C" int yc_reorg_fwd(const yc_tensor* x, const yc_tensor* y, int stride, int forward, void* stream) {
+  YC_CHECK_T(x, "yc_reorg_fwd x");
+  YC_CHECK_T(y, "yc_reorg_fwd y");
+  const yc_tensor* sm = forward ? x : y;
+  const yc_tensor* bg = forward ? y : x;
+  YC_REQUIRE(stride >= 1 && sm->n == bg->n && sm->c == bg->c * stride * stride && sm->h * stride == bg->h &&
+                 sm->w * stride == bg->w,
+             "yc_reorg_fwd: shape mismatch");
+  const long long work = (long long)sm->n * sm->h * sm->w * sm->c;
+  reorg_kernel<<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(mk(x), mk(y), stride, forward);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}

@@ -1,0 +1,73 @@
+// Shared host-side plumbing for libyc_b200: status codes, last-error string, launch counter.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdint.h>
+
+#include "../../include/yc_b200.h"
+
+namespace yc {
+
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+
+#define YC_CUDA(call)                                                                          \
+  do {                                                                                         \
+    cudaError_t _e = (call);                                                                   \
+    if (_e != cudaSuccess) {                                                                   \
+      yc::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e));     \
+      return YC_ERR_CUDA;                                                                      \
+    }                                                                                          \
+  } while (0)
+
+#define YC_LAUNCH_CHECK()                                                                      \
+  do {                                                                                         \
+    cudaError_t _e = cudaPeekAtLastError();                                                    \
+    if (_e != cudaSuccess) {                                                                   \
+      yc::set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(_e)); \
+      return YC_ERR_CUDA;                                                                      \
+    }                                                                                          \
+    yc::count_launch();                                                                        \
+  } while (0)
+
+#define YC_REQUIRE(cond, ...)          \
+  do {                                 \
+    if (!(cond)) {                     \
+      yc::set_error(__VA_ARGS__);      \
+      return YC_ERR_ARG;               \
+    }                                  \
+  } while (0)
+
+static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+static inline long long ceil_div_ll(long long a, long long b) { return (a + b - 1) / b; }
+static inline int round_up(int a, int b) { return ceil_div(a, b) * b; }
+
+int sm_count();
+
+// ---- device-side activation math shared by the conv epilogue and the elementwise kernels ------
+// Formulas follow the reference (activations.h:80-121, activation_kernels.cu:56-79), fp32.
+__device__ __forceinline__ float act_logistic(float x) { return 1.f / (1.f + __expf(-x)); }
+__device__ __forceinline__ float act_mish(float x) {
+  // x * tanh(softplus(x)); with n = e^x: tanh(log(1+n)) = n(n+2) / (n(n+2) + 2).
+  // The reference's softplus thresholds at +-20 (activations.h:106-113): for x > 20 tanh == 1 in
+  // fp32, for x < -20 tanh(e^x) == e^x to fp32 rounding; both limits are what this form gives when
+  // x is clamped to 20, so one branch-free expression covers all three cases.
+  float n = __expf(fminf(x, 20.f));
+  float t = n * (n + 2.f);
+  return x * __fdividef(t, t + 2.f);
+}
+__device__ __forceinline__ float apply_act(float x, int act) {
+  switch (act) {
+    case YC_LINEAR: return x;
+    case YC_LEAKY: return x > 0.f ? x : 0.1f * x;
+    case YC_MISH: return act_mish(x);
+    case YC_LOGISTIC: return act_logistic(x);
+    case YC_SWISH: return x * act_logistic(x);
+    case YC_RELU: return x > 0.f ? x : 0.f;
+  }
+  return x;
+}
+
+}  // namespace yc

@@ -1,0 +1,159 @@
+// YOLO / Gaussian-YOLO head: decode and on-device detection extraction.
+//
+// yc_yolo_decode replaces ForwardYoloLayerGpu's copy + B*n*(2..3) strided activation launches
+// (yolo_layer.cpp:836-853; Gaussian: gaussian_yolo_layer.cpp:934-961) with ONE transposing kernel that reads
+// the head conv's NHWC output, applies logistic / scale_x_y per entry and writes the reference's NCHW fp32
+// `l->output` layout (EntryIndex, yolo_layer.cpp:380-386).
+//
+// yc_yolo_extract is GetYoloDetections (yolo_layer.cpp:794-832) for EVERY batch index, on the device,
+// emitting rows in the reference's scan order (anchor, then cell) so indices are comparable.
+#include "yc_common.cuh"
+
+namespace yc {
+
+struct HeadView {
+  const void* ptr;
+  long long ldc;
+  int f32;
+};
+
+__device__ __forceinline__ float head_ld(const HeadView& t, long long pix, int c) {
+  return t.f32 ? reinterpret_cast<const float*>(t.ptr)[pix * t.ldc + c]
+               : __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(t.ptr)[pix * t.ldc + c]);
+}
+
+// accurate logistic for the head (few elements; feeds thresholds): expf, not __expf
+__device__ __forceinline__ float logistic_acc(float x) { return 1.f / (1.f + expf(-x)); }
+
+// 32 pixels x 32 channels tile through shared memory: coalesced along channels on the NHWC read,
+// coalesced along pixels on the NCHW write.
+__global__ void yolo_decode_kernel(HeadView x, float* __restrict__ out, int S, int C, int E, float sxy,
+                                   int gaussian) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z;
+  const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const float bias = -0.5f * (sxy - 1.f);
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int p = p0 + i, c = c0 + threadIdx.x;
+    float v = 0.f;
+    if (p < S && c < C) {
+      v = head_ld(x, (long long)b * S + p, c);
+      const int e = c % E;
+      bool sig, aff;
+      if (gaussian) {  // gaussian_yolo_layer.cpp:497-516: x,sx,y,sy,_,sw,_,sh, obj, classes
+        sig = (e <= 3) || e == 5 || e == 7 || e >= 8;
+        aff = (e == 0) || (e == 2);
+      } else {         // yolo_layer.cpp:399-404
+        sig = (e < 2) || (e >= 4);
+        aff = (e < 2);
+      }
+      if (sig) v = logistic_acc(v);
+      if (aff) v = v * sxy + bias;
+    }
+    tile[i][threadIdx.x] = v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+    const int c = c0 + i, p = p0 + threadIdx.x;
+    if (c < C && p < S) out[((long long)b * C + c) * S + p] = tile[threadIdx.x][i];
+  }
+}
+
+// one block per image: ordered compaction by block-wide exclusive scan over (anchor, cell)
+__global__ void yolo_extract_kernel(const float* __restrict__ pred, int S, int W, int H, int A, int classes, int E,
+                                    const float* __restrict__ anchor_wh, const int* __restrict__ mask, int net_w,
+                                    int net_h, float thresh, int gaussian, float* __restrict__ rows,
+                                    int rows_per_image, int* __restrict__ counts) {
+  __shared__ int warp_sums[32];
+  __shared__ int base_s;
+  const int b = blockIdx.x;
+  const int R = 6 + classes;  // [batch x y w h obj probs...]
+  const float* p = pred + (long long)b * A * E * S;
+  const int total = A * S;
+  const int obj_e = gaussian ? 8 : 4;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  if (threadIdx.x == 0) base_s = 0;
+  __syncthreads();
+  for (int start = 0; start < total; start += blockDim.x) {
+    const int loc = start + threadIdx.x;
+    int a = 0, i = 0;
+    float obj = 0.f;
+    bool keep = false;
+    if (loc < total) {
+      a = loc / S;
+      i = loc - a * S;
+      obj = p[((long long)a * E + obj_e) * S + i];
+      keep = obj > thresh;  // yolo_layer.cpp:807-809
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, keep);
+    const int within = __popc(bal & ((1u << lane) - 1u));
+    if (lane == 0) warp_sums[wid] = __popc(bal);
+    __syncthreads();
+    int woff = 0, chunk_total = 0;
+    for (int w = 0; w < nw; ++w) {
+      const int s = warp_sums[w];
+      if (w < wid) woff += s;
+      chunk_total += s;
+    }
+    const int base = base_s;
+    const int pos = base + woff + within;
+    if (keep && pos < rows_per_image) {
+      const float* q = p + (long long)a * E * S + i;
+      float* o = rows + ((long long)b * rows_per_image + pos) * R;
+      const int col = i % W, row = i / W;
+      const int m = mask[a];
+      float bx, by, bw, bh, scale = 1.f;
+      if (gaussian) {  // GetGaussianYoloBox gaussian_yolo_layer.cpp:151-160 ; uncertainty :893-900
+        bx = (col + q[0]) / W;
+        by = (row + q[2 * (long long)S]) / H;
+        bw = (float)(exp((double)q[4 * (long long)S]) * anchor_wh[2 * m] / net_w);
+        bh = (float)(exp((double)q[6 * (long long)S]) * anchor_wh[2 * m + 1] / net_h);
+        const float uc = (q[1 * (long long)S] + q[3 * (long long)S] + q[5 * (long long)S] + q[7 * (long long)S]) / 4.f;
+        scale = 1.f - uc;
+      } else {         // GetYoloBox yolo_layer.cpp:139-148 (exp in double, as the reference)
+        bx = (col + q[0]) / W;
+        by = (row + q[(long long)S]) / H;
+        bw = (float)(exp((double)q[2 * (long long)S]) * anchor_wh[2 * m] / net_w);
+        bh = (float)(exp((double)q[3 * (long long)S]) * anchor_wh[2 * m + 1] / net_h);
+      }
+      o[0] = (float)b; o[1] = bx; o[2] = by; o[3] = bw; o[4] = bh; o[5] = obj;
+      for (int j = 0; j < classes; ++j) {
+        const float pr = obj * q[(long long)(obj_e + 1 + j) * S] * scale;
+        o[6 + j] = (pr > thresh) ? pr : 0.f;  // yolo_layer.cpp:820-826
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) base_s = base + chunk_total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) counts[b] = base_s;
+}
+
+}  // namespace yc
+
+using namespace yc;
+
+extern "C" int yc_yolo_decode(const yc_tensor* x, float* out, int anchors, int classes, float sxy, int gaussian,
+                              void* stream) {
+  YC_REQUIRE(x && x->ptr && out, "yc_yolo_decode: null argument");
+  const int E = (gaussian ? 9 : 5) + classes;
+  YC_REQUIRE(x->c == anchors * E, "yc_yolo_decode: channels %d != anchors*(%d+classes)=%d (parser.cpp:323-330)", x->c,
+             gaussian ? 9 : 5, anchors * E);
+  const int S = x->h * x->w;
+  dim3 grid(ceil_div(S, 32), ceil_div(x->c, 32), x->n), block(32, 8);
+  HeadView hv{x->ptr, x->ldc, x->dtype == YC_F32};
+  yolo_decode_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(hv, out, S, x->c, E, sxy, gaussian);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+extern "C" int yc_yolo_extract(const float* decoded, int n, int h, int w, int anchors, int classes,
+                               const float* anchor_wh, const int* mask, int net_w, int net_h, float thresh,
+                               int gaussian, float* rows, int rows_per_image, int* counts, void* stream) {
+  YC_REQUIRE(decoded && anchor_wh && mask && rows && counts && n > 0, "yc_yolo_extract: null argument");
+  const int E = (gaussian ? 9 : 5) + classes;
+  yolo_extract_kernel<<<n, 256, 0, (cudaStream_t)stream>>>(decoded, h * w, w, h, anchors, classes, E, anchor_wh, mask,
+                                                          net_w, net_h, thresh, gaussian, rows, rows_per_image, counts);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}

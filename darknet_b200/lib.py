@@ -1,0 +1,114 @@
+"""ctypes binding of libyc_b200.so (the C ABI declared in include/yc_b200.h).
+
+There is no fallback: if the shared library is missing or a call fails, this raises.
+PyTorch is used by callers only for device memory and streams (tensor.data_ptr(), current stream).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO = os.path.join(HERE, "libyc_b200.so")
+
+LOGISTIC, RELU, LINEAR, LEAKY, SWISH, MISH = 0, 1, 4, 8, 16, 17
+ACT = {"logistic": 0, "relu": 1, "linear": 4, "leaky": 8, "swish": 16, "mish": 17}
+BF16, F32 = 0, 1
+
+
+class YcError(RuntimeError):
+    pass
+
+
+class Tensor(C.Structure):
+    """struct yc_tensor: NHWC view."""
+    _fields_ = [("ptr", C.c_void_p), ("n", C.c_int), ("h", C.c_int), ("w", C.c_int), ("c", C.c_int),
+                ("ldc", C.c_int), ("dtype", C.c_int)]
+
+
+class ConvDesc(C.Structure):
+    _fields_ = [("ksize", C.c_int), ("stride", C.c_int), ("pad", C.c_int), ("dilation", C.c_int),
+                ("activation", C.c_int), ("residual_activation", C.c_int)]
+
+
+_lib = None
+
+_P = C.c_void_p
+_TP = C.POINTER(Tensor)
+_SIGS = {
+    "yc_last_error": (C.c_char_p, []),
+    "yc_set_device": (C.c_int, [C.c_int]),
+    "yc_get_device": (C.c_int, []),
+    "yc_device_count": (C.c_int, []),
+    "yc_sm_count": (C.c_int, []),
+    "yc_malloc": (_P, [C.c_size_t]),
+    "yc_free": (C.c_int, [_P]),
+    "yc_malloc_host": (_P, [C.c_size_t]),
+    "yc_free_host": (C.c_int, [_P]),
+    "yc_push": (C.c_int, [_P, _P, C.c_size_t, _P]),
+    "yc_pull": (C.c_int, [_P, _P, C.c_size_t, _P]),
+    "yc_memset": (C.c_int, [_P, C.c_int, C.c_size_t, _P]),
+    "yc_stream_sync": (C.c_int, [_P]),
+    "yc_stream_create": (C.c_int, [C.POINTER(_P)]),
+    "yc_stream_destroy": (C.c_int, [_P]),
+    "yc_launch_count": (C.c_longlong, [C.c_int]),
+    "yc_nchw_to_nhwc": (C.c_int, [_P, _TP, _P]),
+    "yc_nhwc_to_nchw": (C.c_int, [_TP, _P, _P]),
+    "yc_conv_padded_in_c": (C.c_int, [C.c_int]),
+    "yc_conv_packed_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "yc_conv_pack": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "yc_conv_plan_create": (C.c_int, [C.POINTER(_P), C.POINTER(ConvDesc), _TP, _P, _P, _P, _TP, _TP]),
+    "yc_conv_plan_destroy": (C.c_int, [_P]),
+    "yc_conv_fprop": (C.c_int, [_P, _P]),
+    "yc_conv_plan_info": (C.c_int, [_P, C.c_int]),
+    "yc_maxpool_fwd": (C.c_int, [_TP, _TP, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+    "yc_upsample_fwd": (C.c_int, [_TP, _TP, C.c_int, C.c_float, _P]),
+    "yc_shortcut_fwd": (C.c_int, [_TP, _TP, _TP, C.c_int, _P]),
+    "yc_route_copy": (C.c_int, [_TP, _TP, _P]),
+    "yc_scale_channels_fwd": (C.c_int, [_TP, _TP, _TP, C.c_int, _P]),
+    "yc_reorg_fwd": (C.c_int, [_TP, _TP, C.c_int, C.c_int, _P]),
+    "yc_yolo_decode": (C.c_int, [_TP, _P, C.c_int, C.c_int, C.c_float, C.c_int, _P]),
+    "yc_yolo_extract": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, C.c_int,
+                                  C.c_float, C.c_int, _P, C.c_int, _P, _P]),
+}
+
+
+def declared_symbols():
+    """Every function the public header declares (parsed from include/yc_b200.h)."""
+    import re
+    hdr = open(os.path.join(HERE, "..", "include", "yc_b200.h")).read()
+    return sorted(set(re.findall(r"YC_API[^;(]*?\b(yc_\w+)\s*\(", hdr)))
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO):
+            raise YcError(f"{SO} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback)")
+        L = C.CDLL(SO)
+        for name, (res, args) in _SIGS.items():
+            f = getattr(L, name)
+            f.restype = res
+            f.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        raise YcError(f"{what} failed ({rc}): {lib().yc_last_error().decode()}")
+
+
+def view(t, n, h, w, c, ldc=None, c_off=0):
+    """yc_tensor over a torch CUDA tensor's storage (NHWC). `t` is the buffer that holds the data."""
+    import torch
+    dtype = BF16 if t.dtype == torch.bfloat16 else F32
+    assert t.dtype in (torch.bfloat16, torch.float32)
+    ldc = c if ldc is None else ldc
+    return Tensor(t.data_ptr() + c_off * t.element_size(), n, h, w, c, ldc, dtype)
+
+
+def stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,91 @@
+"""Parity of the tcgen05 implicit-GEMM conv (through the C ABI) against the CPU oracle.
+
+Inputs/weights are rounded to bf16 first, so the only differences left are fp32 accumulation order
+and the bf16 rounding of the output: tolerance 1e-2 relative to the layer's max (north_star bf16
+bound) for bf16 outputs, 1e-4 for fp32 outputs (the "fp32-accumulate check").
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle.pyoracle import O
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf16_round(a):
+    return torch.from_numpy(a).to(torch.bfloat16).float().numpy()
+
+
+def _run(gpu, B, C, H, W, N, k, stride, act, out_f32=False, residual=False, seed=0, scale=False):
+    from darknet_b200 import ops
+    rng = np.random.default_rng(seed)
+    pad = k // 2
+    x = _bf16_round(rng.standard_normal((B, C, H, W)).astype(np.float32))
+    w = _bf16_round((rng.standard_normal((N, C, k, k)) * np.sqrt(2.0 / (C * k * k))).astype(np.float32))
+    b = rng.uniform(-0.5, 0.5, N).astype(np.float32)
+    sc = rng.uniform(0.5, 1.5, N).astype(np.float32) if scale else None
+    wref = w * sc[:, None, None, None] if scale else w
+    ref, pre = O.conv_forward(x, wref, b, k, stride, pad, act, want_pre=True)
+    xd = ops.to_nhwc(torch.from_numpy(x).to(gpu))
+    res_t = None
+    if residual:
+        r = _bf16_round(rng.standard_normal(ref.shape).astype(np.float32))
+        ref = ref + r
+        res_t = ops.to_nhwc(torch.from_numpy(r).to(gpu))
+    conv = ops.Conv(xd, (B, H, W, C), torch.from_numpy(w), torch.from_numpy(b), k, stride, pad, act,
+                    scale=None if sc is None else torch.from_numpy(sc),
+                    out_dtype=torch.float32 if out_f32 else torch.bfloat16, residual=res_t)
+    y = conv()
+    torch.cuda.synchronize()
+    got = ops.to_nchw(y, N).cpu().numpy()
+    assert got.shape == ref.shape
+    denom = np.abs(ref).max() + 1e-12
+    err = np.abs(got - ref).max() / denom
+    tol = 2e-4 if out_f32 else 1e-2
+    assert err < tol, f"rel-to-max err {err:.3e} (tol {tol}) info={conv.info()}"
+    return err
+
+
+@pytest.mark.parametrize("C,N,HW", [(64, 64, 16), (128, 256, 19), (256, 128, 13), (512, 255, 8), (64, 32, 24)])
+def test_conv1x1_tiled_map(gpu, C, N, HW):
+    _run(gpu, 2, C, HW, HW, N, 1, 1, "leaky", out_f32=(N == 255))
+
+
+@pytest.mark.parametrize("C,N,HW,stride", [(64, 64, 16, 1), (128, 128, 19, 1), (64, 128, 32, 2), (256, 512, 13, 1),
+                                           (128, 256, 19, 2), (64, 96, 7, 1)])
+def test_conv3x3_im2col_map(gpu, C, N, HW, stride):
+    _run(gpu, 2, C, HW, HW, N, 3, stride, "mish")
+
+
+def test_conv_first_layer_c3(gpu):
+    _run(gpu, 2, 3, 32, 32, 32, 3, 1, "mish")
+    _run(gpu, 1, 3, 33, 47, 32, 3, 2, "leaky")
+
+
+@pytest.mark.parametrize("C", [32, 48, 96, 192, 384])
+def test_conv_small_k_chunks(gpu, C):
+    _run(gpu, 1, C, 12, 12, 64, 3, 1, "leaky")
+    _run(gpu, 1, C, 12, 12, 64, 1, 1, "linear")
+
+
+def test_conv_fp32_out_and_scale(gpu):
+    _run(gpu, 2, 128, 10, 10, 24, 1, 1, "linear", out_f32=True)
+    _run(gpu, 2, 64, 10, 10, 64, 3, 1, "leaky", out_f32=True, scale=True)
+
+
+def test_conv_residual_fused(gpu):
+    _run(gpu, 2, 64, 19, 19, 128, 3, 1, "mish", residual=True)
+    _run(gpu, 2, 128, 19, 19, 64, 1, 1, "leaky", residual=True)
+
+
+def test_conv_many_tiles_persistent(gpu):
+    # > 148 tiles per CTA wave and both TMEM buffers / several ring wraps
+    _run(gpu, 8, 64, 76, 76, 64, 3, 1, "leaky")
+    _run(gpu, 4, 128, 38, 38, 512, 3, 1, "leaky")
+
+
+def test_conv_ragged_rect(gpu):
+    _run(gpu, 3, 64, 5, 11, 72, 3, 1, "logistic")
+    _run(gpu, 1, 64, 1, 1, 64, 1, 1, "swish")
+    _run(gpu, 1, 64, 3, 2, 64, 3, 2, "relu")
