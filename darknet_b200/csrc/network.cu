@@ -1,0 +1,1059 @@
+// Whole-network host runtime (C++): the B200-native counterpart of the reference's parser.cpp (cfg + .weights),
+// network.cpp (NetworkPredict / GetNetworkBoxes / FuseConvBatchNorm) and network_kernels.cu
+// (ForwardNetworkGpu / NetworkPredictGpu).  No `struct layer` crosses into the kernels: this file translates the
+// parsed network into POD descriptors and calls the launch ABI of include/yc_b200.h.
+//
+// Design (differs from the reference on purpose):
+//   * device tensors are NHWC bf16 (heads fp32); the NCHW fp32 layout exists only at the seam (network input,
+//     YOLO outputs, yc_network_layer_output).
+//   * every conv is ONE kernel (implicit GEMM + bias/BN + activation + residual add), see conv_fprop_sm100.cu.
+//   * [route] costs nothing: single-input routes (incl. groups/group_id slices, route_layer.c:125-142) are views;
+//     multi-input routes own a concat buffer and their producers write straight into their channel slice.
+//   * [shortcut] (shortcut_layer.c:191-204) is fused into the producing conv's epilogue when that conv has no other
+//     consumer.
+//   * the whole forward (input layout conversion ... YOLO decode) is captured once into a CUDA graph.
+//   * all layer outputs stay allocated (like the reference, which keeps l->output_gpu per layer): yolov4-608 at
+//     batch 64 is 22 GB of bf16, well inside 180 GB of HBM3e.
+#include <float.h>
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "cfg_parser.hpp"
+#include "yc_common.cuh"
+
+namespace yc {
+int launch_yolo_extract(const float* decoded, int n, int h, int w, int anchors, int classes, const float* anchor_wh,
+                        const int* mask, int net_w, int net_h, float thresh, int gaussian, float* rows,
+                        int rows_per_image, int* counts, int R, float tag, cudaStream_t stream);
+int launch_yolo_gather(const float* regions, const int* counts, int heads, int n, int cap, int R, float* dense,
+                       int* img_counts, int dense_cap, cudaStream_t stream);
+}  // namespace yc
+
+using namespace yc;
+
+namespace {
+
+enum LType { L_CONV = 0, L_MAXPOOL = 1, L_UPSAMPLE = 2, L_ROUTE = 3, L_SHORTCUT = 4, L_YOLO = 5, L_GYOLO = 6 };
+
+int activation_id(const std::string& s) {  // get_activation, activations.c:60-105 (subset on the path)
+  if (s == "logistic") return YC_LOGISTIC;
+  if (s == "relu") return YC_RELU;
+  if (s == "linear") return YC_LINEAR;
+  if (s == "leaky") return YC_LEAKY;
+  if (s == "swish") return YC_SWISH;
+  if (s == "mish") return YC_MISH;
+  return -1;
+}
+
+struct NLayer {
+  int type = -1;
+  int c = 0, h = 0, w = 0, out_c = 0, out_h = 0, out_w = 0;
+  // conv
+  int n = 0, size = 1, stride = 1, pad = 0, dilation = 1, bn = 0, act = YC_LINEAR;
+  std::vector<float> weights, biases, scales, rmean, rvar;  // host fp32, reference layouts
+  void* w_packed = nullptr;
+  float* bias_dev = nullptr;
+  float* scale_dev = nullptr;
+  yc_conv_plan* plan = nullptr;
+  // route / shortcut
+  std::vector<int> inputs;
+  int groups = 1, group_id = 0;
+  int from = -1;
+  // yolo
+  std::vector<int> mask;
+  std::vector<float> anchors;
+  int classes = 0, total = 0, nms_kind = 0;
+  float scale_x_y = 1.f, beta_nms = 0.6f;
+  float* dec_dev = nullptr;   // decoded fp32 NCHW (the reference's l->output_gpu)
+  float* dec_host = nullptr;  // pinned (the reference's l->output, yolo_layer.cpp:62-66)
+  float* anchors_dev = nullptr;
+  int* mask_dev = nullptr;
+  // storage of the NHWC output
+  bool alias = false;       // a view of another layer's storage (single-input route)
+  int alias_src = -1, alias_coff = 0;
+  int parent = -1, parent_coff = 0;  // placed inside `parent`'s concat buffer
+  int fused_into = -1;      // conv whose epilogue also performs shortcut `fused_into`
+  int fused_conv = -1;      // shortcut computed by conv `fused_conv`
+  void* buf = nullptr;      // owned allocation (root buffers only)
+  int own_ldc = 0;
+  int dtype = YC_BF16;
+  std::vector<std::pair<int, int>> copies;  // route fallback: (input layer, dst channel offset)
+  int consumers = 0;
+};
+
+struct Op {
+  int layer;
+  int kind;  // 0 conv, 1 maxpool, 2 upsample, 3 shortcut, 4 route copy, 5 yolo decode, 6 input convert
+  yc_tensor a, b, y;
+  int i0 = 0, i1 = 0, i2 = 0, i3 = 0;
+  float f0 = 0.f;
+};
+
+}  // namespace
+
+struct yc_network {
+  int batch = 1, w = 0, h = 0, c = 0, flags = YC_NET_DEFAULT;
+  std::vector<NLayer> layers;
+  std::vector<Op> ops;
+  bool finalized = false;
+  cudaStream_t stream = nullptr;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t graph_exec = nullptr;
+  float* input_dev = nullptr;   // fp32 NCHW staging (net->input_state_gpu)
+  float* input_pinned = nullptr;  // net->input_pinned_cpu
+  void* input_nhwc = nullptr;   // bf16 NHWC, ldc 8
+  const float* graph_input = nullptr;
+  std::vector<int> yolo_layers;
+  int n_conv = 0;
+  // detection extraction workspace
+  float* det_regions = nullptr;
+  int* det_counts = nullptr;
+  float* det_dense = nullptr;
+  int* det_img_counts = nullptr;
+  float* det_host = nullptr;
+  int* det_img_counts_host = nullptr;
+  int det_cap = 0, det_dense_cap = 0, det_R = 0;
+  std::vector<float> det_rows_out;
+};
+
+namespace {
+
+#define NET_FAIL(code, ...)   \
+  do {                        \
+    set_error(__VA_ARGS__);   \
+    return code;              \
+  } while (0)
+
+// ---- cfg -> layers (ParseNetworkCfg, parser.cpp:1076-1519; shape rules cited per layer) --------------------
+int build_layers(yc_network* net, const std::string& text, int batch) {
+  std::vector<Section> secs;
+  std::string err;
+  if (!parse_cfg_text(text, secs, err)) NET_FAIL(YC_ERR_PARSE, "%s", err.c_str());
+  const Section& n0 = secs[0];
+  net->batch = batch > 0 ? batch : n0.get_int("batch", 1);
+  net->w = n0.get_int("width", 0);
+  net->h = n0.get_int("height", 0);
+  net->c = n0.get_int("channels", 0);
+  if (!(net->w > 0 && net->h > 0 && net->c > 0)) NET_FAIL(YC_ERR_PARSE, "[net] needs width/height/channels");
+  int c = net->c, h = net->h, w = net->w;
+  for (size_t si = 1; si < secs.size(); ++si) {
+    const Section& s = secs[si];
+    const int idx = (int)si - 1;
+    NLayer L;
+    L.c = c; L.h = h; L.w = w;
+    if (s.name == "convolutional" || s.name == "conv") {  // ParseConv parser.cpp:179-242
+      L.type = L_CONV;
+      L.n = s.get_int("filters", 1);
+      L.size = s.get_int("size", 1);
+      int sx = s.get_int("stride_x", -1), sy = s.get_int("stride_y", -1);
+      L.stride = s.get_int("stride", 1);
+      if (sx >= 1 && sy >= 1 && sx != sy) NET_FAIL(YC_ERR_ARG, "layer %d: stride_x != stride_y is not supported", idx);
+      if (sx >= 1 && sy >= 1) L.stride = sx;
+      L.dilation = L.size == 1 ? 1 : s.get_int("dilation", 1);
+      const int pad = s.get_int("pad", 0);
+      L.pad = pad ? L.size / 2 : s.get_int("padding", 0);
+      if (s.get_int("groups", 1) != 1) NET_FAIL(YC_ERR_ARG, "layer %d: grouped convolution is outside the hot path", idx);
+      if (s.get_int("xnor", 0) || s.get_int("binary", 0)) NET_FAIL(YC_ERR_ARG, "layer %d: xnor/binary conv is outside the hot path", idx);
+      L.bn = s.get_int("batch_normalize", 0);
+      L.act = activation_id(s.get_str("activation", "logistic"));
+      if (L.act < 0) NET_FAIL(YC_ERR_ARG, "layer %d: activation '%s' is outside the hot path", idx, s.get_str("activation", "").c_str());
+      L.out_c = L.n;
+      const int eff = L.dilation * (L.size - 1) + 1;  // convolutional_layer.cpp:87-95
+      L.out_h = (h + 2 * L.pad - eff) / L.stride + 1;
+      L.out_w = (w + 2 * L.pad - eff) / L.stride + 1;
+      L.inputs = {idx - 1};
+      const size_t nw = (size_t)L.n * L.c * L.size * L.size;
+      L.weights.assign(nw, 0.f);
+      L.biases.assign(L.n, 0.f);
+      if (L.bn) { L.scales.assign(L.n, 1.f); L.rmean.assign(L.n, 0.f); L.rvar.assign(L.n, 1.f); }
+      net->n_conv++;
+    } else if (s.name == "maxpool" || s.name == "max") {  // ParseMaxpool parser.cpp:640-659
+      L.type = L_MAXPOOL;
+      L.stride = s.get_int("stride", 1);
+      L.size = s.get_int("size", L.stride);
+      L.pad = s.get_int("padding", L.size - 1);
+      if (s.get_int("maxpool_depth", 0)) NET_FAIL(YC_ERR_ARG, "layer %d: maxpool_depth is outside the hot path", idx);
+      L.out_c = c;
+      L.out_h = (h + L.pad - L.size) / L.stride + 1;  // maxpool_layer.cpp:62-63
+      L.out_w = (w + L.pad - L.size) / L.stride + 1;
+      L.inputs = {idx - 1};
+    } else if (s.name == "upsample") {  // parser.cpp:819-830
+      L.type = L_UPSAMPLE;
+      L.stride = s.get_int("stride", 2);
+      L.scale_x_y = s.get_float("scale", 1.f);
+      L.out_c = c; L.out_h = h * L.stride; L.out_w = w * L.stride;
+      L.inputs = {idx - 1};
+    } else if (s.name == "route") {  // ParseRoute parser.cpp:832-896
+      L.type = L_ROUTE;
+      std::vector<int> ids = parse_int_list(s.get_str("layers", ""));
+      if (ids.empty()) NET_FAIL(YC_ERR_PARSE, "layer %d: route needs layers=", idx);
+      L.groups = s.get_int("groups", 1);
+      L.group_id = s.get_int("group_id", 0);
+      int oc = 0;
+      for (int& i : ids) {
+        if (i < 0) i += idx;
+        if (i < 0 || i >= idx) NET_FAIL(YC_ERR_PARSE, "layer %d: route input %d out of range", idx, i);
+        const NLayer& src = net->layers[i];
+        if (src.out_h != net->layers[ids[0]].out_h || src.out_w != net->layers[ids[0]].out_w)
+          NET_FAIL(YC_ERR_ARG, "layer %d: route inputs differ in spatial size", idx);
+        oc += src.out_c / L.groups;
+      }
+      L.inputs = ids;
+      L.out_c = oc; L.out_h = net->layers[ids[0]].out_h; L.out_w = net->layers[ids[0]].out_w;
+    } else if (s.name == "shortcut") {  // ParseShortcut parser.cpp:720-779 (single `from`)
+      L.type = L_SHORTCUT;
+      int f = s.get_int("from", -1);
+      if (f < 0) f += idx;
+      if (f < 0 || f >= idx) NET_FAIL(YC_ERR_PARSE, "layer %d: shortcut from out of range", idx);
+      const NLayer& src = net->layers[f];
+      if (src.out_c != c || src.out_h != h || src.out_w != w)  // shortcut_layer.c:151-164 asserts equal dims
+        NET_FAIL(YC_ERR_ARG, "layer %d: shortcut source %d has a different shape", idx, f);
+      L.from = f;
+      L.act = activation_id(s.get_str("activation", "linear"));
+      if (L.act < 0) NET_FAIL(YC_ERR_ARG, "layer %d: shortcut activation outside the hot path", idx);
+      L.inputs = {idx - 1, f};
+      L.out_c = c; L.out_h = h; L.out_w = w;
+    } else if (s.name == "yolo" || s.name == "Gaussian_yolo") {  // ParseYolo :312-415, ParseGaussianYolo :443-557
+      L.type = s.name == "yolo" ? L_YOLO : L_GYOLO;
+      L.classes = s.get_int("classes", 20);
+      L.total = s.get_int("num", 1);
+      L.mask = parse_int_list(s.get_str("mask", ""));
+      if (L.mask.empty()) for (int i = 0; i < L.total; ++i) L.mask.push_back(i);
+      L.anchors = parse_float_list(s.get_str("anchors", ""));
+      L.anchors.resize((size_t)2 * L.total, 0.5f);  // FillYoloLayer default biases .5 (yolo_layer.cpp:44-47)
+      L.scale_x_y = s.get_float("scale_x_y", 1.f);
+      L.beta_nms = s.get_float("beta_nms", 0.6f);
+      const std::string nk = s.get_str("nms_kind", "default");
+      L.nms_kind = nk == "diounms" ? 1 : 0;
+      const int E = (L.type == L_YOLO ? 5 : 9) + L.classes;
+      if ((int)L.mask.size() * E != c)
+        NET_FAIL(YC_ERR_ARG, "layer %d: filters=%d does not correspond to classes/mask (want %d) (parser.cpp:323-330)", idx, c,
+                 (int)L.mask.size() * E);
+      L.n = (int)L.mask.size();
+      L.out_c = c; L.out_h = h; L.out_w = w;
+      L.inputs = {idx - 1};
+      net->yolo_layers.push_back(idx);
+    } else {
+      NET_FAIL(YC_ERR_ARG, "layer %d: [%s] is outside the conv/YOLO hot path this library replaces", idx, s.name.c_str());
+    }
+    if (idx == 0 && L.type != L_CONV) NET_FAIL(YC_ERR_ARG, "the first layer must be convolutional");
+    if (L.out_h <= 0 || L.out_w <= 0) NET_FAIL(YC_ERR_ARG, "layer %d: empty output", idx);
+    net->layers.push_back(std::move(L));
+    c = net->layers.back().out_c; h = net->layers.back().out_h; w = net->layers.back().out_w;
+  }
+  if (net->layers.empty()) NET_FAIL(YC_ERR_PARSE, "cfg has no layers");
+  return YC_OK;
+}
+
+// ---- .weights (LoadWeightsUpTo parser.cpp:1778-1844, LoadConvolutionalWeights :1695-1759) -------------------
+int load_weights_file(yc_network* net, const char* path) {
+  FILE* fp = fopen(path, "rb");
+  if (!fp) NET_FAIL(YC_ERR_IO, "cannot open weights file %s", path);
+  int hdr[3];
+  uint64_t seen = 0;
+  bool ok = fread(hdr, sizeof(int), 3, fp) == 3 && fread(&seen, sizeof(uint64_t), 1, fp) == 1;
+  for (size_t i = 0; ok && i < net->layers.size(); ++i) {
+    NLayer& L = net->layers[i];
+    if (L.type != L_CONV) continue;
+    ok = fread(L.biases.data(), 4, L.n, fp) == (size_t)L.n;
+    if (ok && L.bn) {
+      ok = fread(L.scales.data(), 4, L.n, fp) == (size_t)L.n && fread(L.rmean.data(), 4, L.n, fp) == (size_t)L.n &&
+           fread(L.rvar.data(), 4, L.n, fp) == (size_t)L.n;
+    }
+    if (ok) ok = fread(L.weights.data(), 4, L.weights.size(), fp) == L.weights.size();
+    if (!ok) {
+      fclose(fp);
+      NET_FAIL(YC_ERR_IO, "weights file %s is truncated at layer %zu", path, i);
+    }
+  }
+  fclose(fp);
+  if (!ok) NET_FAIL(YC_ERR_IO, "weights file %s: bad header", path);
+  return YC_OK;
+}
+
+// resolve a layer to its physical storage: (root layer that owns a buffer, channel offset, pitch)
+struct Loc { int root; int coff; };
+Loc locate(const yc_network* net, int i) {
+  int coff = 0;
+  for (;;) {
+    const NLayer& L = net->layers[i];
+    if (L.alias) { coff += L.alias_coff; i = L.alias_src; continue; }
+    if (L.parent >= 0) { coff += L.parent_coff; i = L.parent; continue; }
+    return Loc{i, coff};
+  }
+}
+
+yc_tensor view_of(const yc_network* net, int i) {
+  const NLayer& L = net->layers[i];
+  const Loc loc = locate(net, i);
+  const NLayer& R = net->layers[loc.root];
+  yc_tensor t;
+  const int es = R.dtype == YC_F32 ? 4 : 2;
+  t.ptr = (char*)R.buf + (size_t)loc.coff * es;
+  t.n = net->batch; t.h = L.out_h; t.w = L.out_w; t.c = L.out_c;
+  t.ldc = R.own_ldc;
+  t.dtype = R.dtype;
+  return t;
+}
+
+int free_device_state(yc_network* net) {
+  if (net->graph_exec) { cudaGraphExecDestroy(net->graph_exec); net->graph_exec = nullptr; }
+  if (net->graph) { cudaGraphDestroy(net->graph); net->graph = nullptr; }
+  for (NLayer& L : net->layers) {
+    if (L.plan) { yc_conv_plan_destroy(L.plan); L.plan = nullptr; }
+    if (L.w_packed) { cudaFree(L.w_packed); L.w_packed = nullptr; }
+    if (L.bias_dev) { cudaFree(L.bias_dev); L.bias_dev = nullptr; }
+    if (L.scale_dev) { cudaFree(L.scale_dev); L.scale_dev = nullptr; }
+    if (L.buf) { cudaFree(L.buf); L.buf = nullptr; }
+    if (L.dec_dev) { cudaFree(L.dec_dev); L.dec_dev = nullptr; }
+    if (L.dec_host) { cudaFreeHost(L.dec_host); L.dec_host = nullptr; }
+    if (L.anchors_dev) { cudaFree(L.anchors_dev); L.anchors_dev = nullptr; }
+    if (L.mask_dev) { cudaFree(L.mask_dev); L.mask_dev = nullptr; }
+    L.alias = false; L.alias_src = -1; L.alias_coff = 0; L.parent = -1; L.parent_coff = 0;
+    L.fused_into = -1; L.fused_conv = -1; L.copies.clear(); L.consumers = 0;
+  }
+  if (net->input_dev) { cudaFree(net->input_dev); net->input_dev = nullptr; }
+  if (net->input_pinned) { cudaFreeHost(net->input_pinned); net->input_pinned = nullptr; }
+  if (net->input_nhwc) { cudaFree(net->input_nhwc); net->input_nhwc = nullptr; }
+  if (net->det_regions) { cudaFree(net->det_regions); net->det_regions = nullptr; }
+  if (net->det_counts) { cudaFree(net->det_counts); net->det_counts = nullptr; }
+  if (net->det_dense) { cudaFree(net->det_dense); net->det_dense = nullptr; }
+  if (net->det_img_counts) { cudaFree(net->det_img_counts); net->det_img_counts = nullptr; }
+  if (net->det_host) { cudaFreeHost(net->det_host); net->det_host = nullptr; }
+  if (net->det_img_counts_host) { cudaFreeHost(net->det_img_counts_host); net->det_img_counts_host = nullptr; }
+  net->ops.clear();
+  net->finalized = false;
+  return YC_OK;
+}
+
+#define NET_CUDA(call)                                                                     \
+  do {                                                                                     \
+    cudaError_t _e = (call);                                                               \
+    if (_e != cudaSuccess) {                                                               \
+      set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e));     \
+      return YC_ERR_CUDA;                                                                  \
+    }                                                                                      \
+  } while (0)
+
+int run_op(yc_network* net, const Op& op, cudaStream_t st) {
+  NLayer* L = op.layer >= 0 ? &net->layers[op.layer] : nullptr;
+  switch (op.kind) {
+    case 0: return yc_conv_fprop(L->plan, st);
+    case 1: return yc_maxpool_fwd(&op.a, &op.y, op.i0, op.i1, op.i2, op.i3, st);
+    case 2: return yc_upsample_fwd(&op.a, &op.y, op.i0, op.f0, st);
+    case 3: return yc_shortcut_fwd(&op.a, &op.b, &op.y, op.i0, st);
+    case 4: return yc_route_copy(&op.a, &op.y, st);
+    case 5: return yc_yolo_decode(&op.a, L->dec_dev, op.i0, op.i1, op.f0, op.i2, st);
+    case 6: return yc_nchw_to_nhwc(net->graph_input, &op.y, st);
+  }
+  return YC_ERR_ARG;
+}
+
+int run_ops(yc_network* net, cudaStream_t st) {
+  for (const Op& op : net->ops) {
+    int rc = run_op(net, op, st);
+    if (rc) return rc;
+  }
+  return YC_OK;
+}
+
+}  // namespace
+
+// ================================================================================================
+extern "C" int yc_network_finalize(yc_network* net) {
+  YC_REQUIRE(net, "yc_network_finalize: null network");
+  if (yc_device_count() <= 0) {
+    set_error("yc_network_finalize: no CUDA device; this library has no CPU fallback");
+    return YC_ERR_NO_DEVICE;
+  }
+  free_device_state(net);
+  const int nl = (int)net->layers.size();
+  const int flags = net->flags;
+  auto& Ls = net->layers;
+  if (!net->stream) NET_CUDA(cudaStreamCreateWithFlags(&net->stream, cudaStreamNonBlocking));
+
+  // ---- consumers ------------------------------------------------------------------------------
+  for (int i = 0; i < nl; ++i)
+    for (int in : Ls[i].inputs)
+      if (in >= 0) Ls[in].consumers++;
+
+  // ---- aliases: single-input routes are views (route_layer.c:125-142 with groups/group_id) ----------
+  for (int i = 0; i < nl; ++i) {
+    NLayer& L = Ls[i];
+    if (L.type == L_ROUTE && L.inputs.size() == 1 && (flags & YC_NET_ELIDE_ROUTE)) {
+      const NLayer& S = Ls[L.inputs[0]];
+      const int part = S.out_c / L.groups;
+      if ((part * L.group_id) % 8 == 0 && S.type != L_YOLO && S.type != L_GYOLO) {
+        L.alias = true;
+        L.alias_src = L.inputs[0];
+        L.alias_coff = part * L.group_id;
+      }
+    }
+  }
+  // ---- shortcut fusion --------------------------------------------------------------------------
+  if (flags & YC_NET_FUSE_SHORTCUT) {
+    for (int i = 1; i < nl; ++i) {
+      NLayer& S = Ls[i];
+      if (S.type != L_SHORTCUT) continue;
+      NLayer& C = Ls[i - 1];
+      if (C.type == L_CONV && C.consumers == 1 && S.from != i - 1) {
+        C.fused_into = i;
+        S.fused_conv = i - 1;
+      }
+    }
+  }
+  // ---- concat placement ---------------------------------------------------------------------------
+  for (int i = 0; i < nl; ++i) {
+    NLayer& R = Ls[i];
+    if (R.type != L_ROUTE || R.alias) continue;
+    int coff = 0;
+    for (int in : R.inputs) {
+      NLayer& S = Ls[in];
+      const int part = S.out_c / R.groups;
+      // physical producer whose whole output is this slice, not yet placed elsewhere
+      int p = in;
+      bool whole = R.groups == 1;
+      while (whole && Ls[p].alias) {
+        if (Ls[p].alias_coff != 0 || Ls[p].out_c != Ls[Ls[p].alias_src].out_c) { whole = false; break; }
+        p = Ls[p].alias_src;
+      }
+      if (whole && Ls[p].fused_conv >= 0) { /* shortcut computed by a conv: the shortcut layer is the physical one */ }
+      const bool placeable = (flags & YC_NET_ELIDE_ROUTE) && whole && Ls[p].parent < 0 && Ls[p].fused_into < 0 &&
+                             Ls[p].type != L_YOLO && Ls[p].type != L_GYOLO && coff % 8 == 0 && p != i;
+      if (placeable) {
+        Ls[p].parent = i;
+        Ls[p].parent_coff = coff;
+      } else {
+        R.copies.push_back({in, coff});
+      }
+      coff += part;
+    }
+  }
+  // ---- allocate root buffers -----------------------------------------------------------------------
+  for (int i = 0; i < nl; ++i) {
+    NLayer& L = Ls[i];
+    if (L.type == L_YOLO || L.type == L_GYOLO) continue;
+    if (L.alias || L.parent >= 0 || L.fused_into >= 0) continue;
+    // head convs (feeding a YOLO layer) keep fp32 so thresholds see unrounded logits
+    const bool head = (i + 1 < nl) && (Ls[i + 1].type == L_YOLO || Ls[i + 1].type == L_GYOLO) && L.type == L_CONV;
+    L.dtype = head ? YC_F32 : YC_BF16;
+    L.own_ldc = round_up(L.out_c, head ? 4 : 8);
+    const size_t bytes = (size_t)net->batch * L.out_h * L.out_w * L.own_ldc * (head ? 4 : 2);
+    NET_CUDA(cudaMalloc(&L.buf, bytes));
+    NET_CUDA(cudaMemset(L.buf, 0, bytes));
+  }
+  // input staging
+  const size_t in_elems = (size_t)net->batch * net->c * net->h * net->w;
+  NET_CUDA(cudaMalloc(&net->input_dev, in_elems * 4));
+  NET_CUDA(cudaHostAlloc(&net->input_pinned, in_elems * 4, cudaHostAllocDefault));
+  const int in_ldc = round_up(net->c, 8);
+  NET_CUDA(cudaMalloc(&net->input_nhwc, (size_t)net->batch * net->h * net->w * in_ldc * 2));
+  NET_CUDA(cudaMemset(net->input_nhwc, 0, (size_t)net->batch * net->h * net->w * in_ldc * 2));
+
+  // ---- parameters: fuse BN (FuseConvBatchNorm network.cpp:647-682), pack, upload ----------------------
+  for (int i = 0; i < nl; ++i) {
+    NLayer& L = Ls[i];
+    if (L.type != L_CONV) continue;
+    const size_t fs = (size_t)L.size * L.size * L.c;
+    std::vector<float> w = L.weights, b = L.biases, sc;
+    if (L.bn) {
+      if (flags & YC_NET_FUSE_BN) {
+        for (int f = 0; f < L.n; ++f) {
+          const float sd = (float)sqrt((double)(L.rvar[f] + 0.00001f));
+          b[f] -= L.scales[f] * L.rmean[f] / sd;
+          const float m = L.scales[f] / sd;
+          for (size_t k = 0; k < fs; ++k) w[f * fs + k] *= m;
+        }
+      } else {
+        // inference-mode BN from rolling stats (batchnorm_layer.cpp:226-237): (x-mean)/sqrt(var+1e-6)*gamma + beta
+        sc.resize(L.n);
+        for (int f = 0; f < L.n; ++f) {
+          const float inv = 1.f / sqrtf(L.rvar[f] + .000001f);
+          sc[f] = L.scales[f] * inv;
+          b[f] = L.biases[f] - L.rmean[f] * sc[f];
+        }
+      }
+    }
+    float* w_dev = nullptr;
+    NET_CUDA(cudaMalloc(&w_dev, w.size() * 4));
+    NET_CUDA(cudaMemcpy(w_dev, w.data(), w.size() * 4, cudaMemcpyHostToDevice));
+    NET_CUDA(cudaMalloc(&L.w_packed, yc_conv_packed_bytes(L.n, L.c, L.size)));
+    int rc = yc_conv_pack(w_dev, L.n, L.c, L.size, L.w_packed, net->stream);
+    if (rc) { cudaFree(w_dev); return rc; }
+    NET_CUDA(cudaStreamSynchronize(net->stream));
+    NET_CUDA(cudaFree(w_dev));
+    NET_CUDA(cudaMalloc(&L.bias_dev, L.n * 4));
+    NET_CUDA(cudaMemcpy(L.bias_dev, b.data(), L.n * 4, cudaMemcpyHostToDevice));
+    if (!sc.empty()) {
+      NET_CUDA(cudaMalloc(&L.scale_dev, L.n * 4));
+      NET_CUDA(cudaMemcpy(L.scale_dev, sc.data(), L.n * 4, cudaMemcpyHostToDevice));
+    }
+  }
+
+  // ---- op list -------------------------------------------------------------------------------------
+  {
+    Op op;
+    op.layer = -1; op.kind = 6;
+    op.y = yc_tensor{net->input_nhwc, net->batch, net->h, net->w, net->c, in_ldc, YC_BF16};
+    net->ops.push_back(op);
+  }
+  auto input_view = [&](int i) -> yc_tensor {
+    if (i == 0) return yc_tensor{net->input_nhwc, net->batch, net->h, net->w, net->c, in_ldc, YC_BF16};
+    return view_of(net, i - 1);
+  };
+  for (int i = 0; i < nl; ++i) {
+    NLayer& L = Ls[i];
+    Op op;
+    op.layer = i;
+    switch (L.type) {
+      case L_CONV: {
+        yc_conv_desc d{L.size, L.stride, L.pad, L.dilation, L.act, YC_LINEAR};
+        yc_tensor x = input_view(i);
+        yc_tensor y, res;
+        const yc_tensor* resp = nullptr;
+        if (L.fused_into >= 0) {
+          const NLayer& S = Ls[L.fused_into];
+          y = view_of(net, L.fused_into);
+          res = view_of(net, S.from);
+          resp = &res;
+          d.residual_activation = S.act;
+        } else {
+          y = view_of(net, i);
+        }
+        int rc = yc_conv_plan_create(&L.plan, &d, &x, L.w_packed, L.bias_dev, L.scale_dev, resp, &y);
+        if (rc) return rc;
+        op.kind = 0;
+        net->ops.push_back(op);
+        break;
+      }
+      case L_MAXPOOL:
+        op.kind = 1; op.a = input_view(i); op.y = view_of(net, i);
+        op.i0 = L.size; op.i1 = L.stride; op.i2 = L.pad; op.i3 = (flags & YC_NET_REF_CPU_MAXPOOL) ? 1 : 0;
+        net->ops.push_back(op);
+        break;
+      case L_UPSAMPLE:
+        op.kind = 2; op.a = input_view(i); op.y = view_of(net, i); op.i0 = L.stride; op.f0 = L.scale_x_y;
+        net->ops.push_back(op);
+        break;
+      case L_SHORTCUT:
+        if (L.fused_conv >= 0) break;  // computed by the conv's epilogue
+        op.kind = 3; op.a = input_view(i); op.b = view_of(net, L.from); op.y = view_of(net, i); op.i0 = L.act;
+        net->ops.push_back(op);
+        break;
+      case L_ROUTE:
+        if (L.alias) break;
+        for (auto& cp : L.copies) {
+          const NLayer& S = Ls[cp.first];
+          const int part = S.out_c / L.groups;
+          Op c2; c2.layer = i; c2.kind = 4;
+          c2.a = view_of(net, cp.first);
+          c2.a.ptr = (char*)c2.a.ptr + (size_t)part * L.group_id * (c2.a.dtype == YC_F32 ? 4 : 2);
+          c2.a.c = part;
+          c2.y = view_of(net, i);
+          c2.y.ptr = (char*)c2.y.ptr + (size_t)cp.second * 2;
+          c2.y.c = part;
+          if (c2.a.dtype != YC_BF16) NET_FAIL(YC_ERR_ARG, "layer %d: route from an fp32 head output is not supported", i);
+          net->ops.push_back(c2);
+        }
+        break;
+      case L_YOLO:
+      case L_GYOLO: {
+        const size_t elems = (size_t)net->batch * L.out_c * L.out_h * L.out_w;
+        NET_CUDA(cudaMalloc(&L.dec_dev, elems * 4));
+        NET_CUDA(cudaHostAlloc(&L.dec_host, elems * 4, cudaHostAllocDefault));
+        memset(L.dec_host, 0, elems * 4);
+        NET_CUDA(cudaMalloc(&L.anchors_dev, L.anchors.size() * 4));
+        NET_CUDA(cudaMemcpy(L.anchors_dev, L.anchors.data(), L.anchors.size() * 4, cudaMemcpyHostToDevice));
+        NET_CUDA(cudaMalloc(&L.mask_dev, L.mask.size() * 4));
+        NET_CUDA(cudaMemcpy(L.mask_dev, L.mask.data(), L.mask.size() * 4, cudaMemcpyHostToDevice));
+        op.kind = 5; op.a = input_view(i); op.i0 = L.n; op.i1 = L.classes; op.f0 = L.scale_x_y;
+        op.i2 = L.type == L_GYOLO ? 1 : 0;
+        net->ops.push_back(op);
+        break;
+      }
+    }
+  }
+  net->finalized = true;
+  return YC_OK;
+}
+
+static int load_common(yc_network** out, const std::string& text, const char* weights_path, int batch, int flags) {
+  YC_REQUIRE(out, "yc_network_load: null output");
+  yc_network* net = new yc_network();
+  net->flags = flags;
+  int rc = build_layers(net, text, batch);
+  if (!rc && weights_path && weights_path[0]) {
+    rc = load_weights_file(net, weights_path);
+    if (!rc) rc = yc_network_finalize(net);
+  }
+  if (rc) {
+    yc_network_free(net);
+    return rc;
+  }
+  *out = net;
+  return YC_OK;
+}
+
+extern "C" int yc_network_load_text(yc_network** out, const char* cfg_text, const char* weights_path, int batch,
+                                    int flags) {
+  YC_REQUIRE(cfg_text, "yc_network_load_text: null cfg");
+  return load_common(out, cfg_text, weights_path, batch, flags);
+}
+
+extern "C" int yc_network_load(yc_network** out, const char* cfg_path, const char* weights_path, int batch, int flags) {
+  YC_REQUIRE(cfg_path, "yc_network_load: null cfg path");
+  std::ifstream f(cfg_path);
+  if (!f) {
+    set_error("Couldn't open file: %s", cfg_path);  // file_error utils.cpp
+    return YC_ERR_IO;
+  }
+  std::stringstream ss;
+  ss << f.rdbuf();
+  return load_common(out, ss.str(), weights_path, batch, flags);
+}
+
+extern "C" int yc_network_free(yc_network* net) {
+  if (!net) return YC_OK;
+  free_device_state(net);
+  if (net->stream) cudaStreamDestroy(net->stream);
+  delete net;
+  return YC_OK;
+}
+
+extern "C" int yc_network_set_conv_weights(yc_network* net, int layer, const float* weights, const float* biases,
+                                           const float* scales, const float* rmean, const float* rvar) {
+  YC_REQUIRE(net && layer >= 0 && layer < (int)net->layers.size(), "yc_network_set_conv_weights: bad layer");
+  NLayer& L = net->layers[layer];
+  YC_REQUIRE(L.type == L_CONV, "yc_network_set_conv_weights: layer %d is not convolutional", layer);
+  if (weights) memcpy(L.weights.data(), weights, L.weights.size() * 4);
+  if (biases) memcpy(L.biases.data(), biases, L.n * 4);
+  if (L.bn) {
+    if (scales) memcpy(L.scales.data(), scales, L.n * 4);
+    if (rmean) memcpy(L.rmean.data(), rmean, L.n * 4);
+    if (rvar) memcpy(L.rvar.data(), rvar, L.n * 4);
+  }
+  net->finalized = false;
+  return YC_OK;
+}
+
+extern "C" int yc_network_info(const yc_network* net, int what) {
+  if (!net) return -1;
+  switch (what) {
+    case 0: return (int)net->layers.size();
+    case 1: return net->batch;
+    case 2: return net->w;
+    case 3: return net->h;
+    case 4: return net->c;
+    case 5: return net->n_conv;
+    case 6: return (int)net->ops.size();
+    case 7: return (int)net->yolo_layers.size();
+  }
+  return -1;
+}
+
+extern "C" int yc_network_layer_info(const yc_network* net, int layer, int what) {
+  if (!net || layer < 0 || layer >= (int)net->layers.size()) return -1;
+  const NLayer& L = net->layers[layer];
+  switch (what) {
+    case 0: return L.type;
+    case 1: return L.out_c;
+    case 2: return L.out_h;
+    case 3: return L.out_w;
+    case 4: return (L.fused_into >= 0) ? 0 : 1;
+    case 5: return L.c;
+    case 6: return L.size;
+    case 7: return L.stride;
+    case 8: return L.act;
+    case 9: return L.bn;
+    case 10: return L.plan ? yc_conv_plan_info(L.plan, 0) : -1;
+    case 11: return L.plan ? yc_conv_plan_info(L.plan, 2) : -1;
+    case 12: return L.plan ? yc_conv_plan_info(L.plan, 3) : -1;
+  }
+  return -1;
+}
+
+extern "C" double yc_network_flops(const yc_network* net) {
+  double f = 0;
+  if (!net) return 0;
+  for (const NLayer& L : net->layers)
+    if (L.type == L_CONV) f += 2.0 * (double)L.n * L.c * L.size * L.size * L.out_h * L.out_w;
+  return f;
+}
+
+static int ensure_graph(yc_network* net, const float* input_dev) {
+  if (net->graph_exec && net->graph_input == input_dev) return YC_OK;
+  if (net->graph_exec) { cudaGraphExecDestroy(net->graph_exec); net->graph_exec = nullptr; }
+  if (net->graph) { cudaGraphDestroy(net->graph); net->graph = nullptr; }
+  net->graph_input = input_dev;
+  NET_CUDA(cudaStreamBeginCapture(net->stream, cudaStreamCaptureModeThreadLocal));
+  int rc = run_ops(net, net->stream);
+  cudaError_t e = cudaStreamEndCapture(net->stream, &net->graph);
+  if (rc) return rc;
+  if (e != cudaSuccess) {
+    set_error("cudaStreamEndCapture: %s", cudaGetErrorString(e));
+    return YC_ERR_CUDA;
+  }
+  NET_CUDA(cudaGraphInstantiate(&net->graph_exec, net->graph, 0));
+  return YC_OK;
+}
+
+extern "C" int yc_network_forward(yc_network* net, const float* input_dev, void* stream) {
+  YC_REQUIRE(net && input_dev, "yc_network_forward: null argument");
+  if (!net->finalized) {
+    int rc = yc_network_finalize(net);
+    if (rc) return rc;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (net->flags & YC_NET_CUDA_GRAPH) {
+    int rc = ensure_graph(net, input_dev);
+    if (rc) return rc;
+    NET_CUDA(cudaGraphLaunch(net->graph_exec, st));
+    count_launch((int)net->ops.size());
+    return YC_OK;
+  }
+  net->graph_input = input_dev;
+  return run_ops(net, st);
+}
+
+extern "C" float* yc_network_predict(yc_network* net, const float* input_host) {
+  if (!net || !input_host) {
+    set_error("yc_network_predict: null argument");
+    return nullptr;
+  }
+  if (!net->finalized && yc_network_finalize(net)) return nullptr;
+  const size_t in_bytes = (size_t)net->batch * net->c * net->h * net->w * 4;
+  // network_kernels.cu:513-514: memcpy into the pinned staging buffer, then H2D
+  memcpy(net->input_pinned, input_host, in_bytes);
+  if (cudaMemcpyAsync(net->input_dev, net->input_pinned, in_bytes, cudaMemcpyHostToDevice, net->stream) != cudaSuccess) {
+    set_error("yc_network_predict: H2D failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return nullptr;
+  }
+  if (yc_network_forward(net, net->input_dev, net->stream)) return nullptr;
+  float* last = nullptr;
+  if (net->flags & YC_NET_PULL_HEADS) {
+    for (int i : net->yolo_layers) {  // yolo_layer.cpp:856 cuda_pull_array_async(l->output_gpu, l->output, ...)
+      NLayer& L = net->layers[i];
+      const size_t bytes = (size_t)net->batch * L.out_c * L.out_h * L.out_w * 4;
+      if (cudaMemcpyAsync(L.dec_host, L.dec_dev, bytes, cudaMemcpyDeviceToHost, net->stream) != cudaSuccess) {
+        set_error("yc_network_predict: D2H failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return nullptr;
+      }
+    }
+  }
+  if (cudaStreamSynchronize(net->stream) != cudaSuccess) {
+    set_error("yc_network_predict: %s", cudaGetErrorString(cudaGetLastError()));
+    return nullptr;
+  }
+  // GetNetworkOutput (network.cpp:390-398): output of the last layer
+  const NLayer& Z = net->layers.back();
+  if (Z.type == L_YOLO || Z.type == L_GYOLO) last = Z.dec_host;
+  if (!last) last = net->input_pinned;  // non-YOLO tail: callers use yc_network_layer_output
+  return last;
+}
+
+extern "C" const float* yc_network_yolo_output(yc_network* net, int layer) {
+  if (!net || layer < 0 || layer >= (int)net->layers.size()) return nullptr;
+  return net->layers[layer].dec_host;
+}
+
+extern "C" int yc_network_layer_output(yc_network* net, int layer, float* dst_host) {
+  YC_REQUIRE(net && dst_host && layer >= 0 && layer < (int)net->layers.size(), "yc_network_layer_output: bad argument");
+  YC_REQUIRE(net->finalized, "yc_network_layer_output: network not finalized");
+  NLayer& L = net->layers[layer];
+  const size_t elems = (size_t)net->batch * L.out_c * L.out_h * L.out_w;
+  if (L.type == L_YOLO || L.type == L_GYOLO) {
+    NET_CUDA(cudaMemcpyAsync(dst_host, L.dec_dev, elems * 4, cudaMemcpyDeviceToHost, net->stream));
+    NET_CUDA(cudaStreamSynchronize(net->stream));
+    return YC_OK;
+  }
+  YC_REQUIRE(L.fused_into < 0, "layer %d has no output of its own: it is fused with shortcut %d (load without YC_NET_FUSE_SHORTCUT)",
+             layer, L.fused_into);
+  yc_tensor v = view_of(net, layer);
+  float* tmp = nullptr;
+  NET_CUDA(cudaMalloc(&tmp, elems * 4));
+  int rc = yc_nhwc_to_nchw(&v, tmp, net->stream);
+  if (!rc) {
+    cudaError_t e = cudaMemcpyAsync(dst_host, tmp, elems * 4, cudaMemcpyDeviceToHost, net->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(net->stream);
+    if (e != cudaSuccess) { set_error("yc_network_layer_output: %s", cudaGetErrorString(e)); rc = YC_ERR_CUDA; }
+  }
+  cudaFree(tmp);
+  return rc;
+}
+
+extern "C" int yc_network_profile(yc_network* net, const float* input_dev, int iters, float* ms_per_layer) {
+  YC_REQUIRE(net && input_dev && ms_per_layer && iters > 0, "yc_network_profile: bad argument");
+  if (!net->finalized) {
+    int rc = yc_network_finalize(net);
+    if (rc) return rc;
+  }
+  const int nl = (int)net->layers.size();
+  for (int i = 0; i <= nl; ++i) ms_per_layer[i] = 0.f;
+  net->graph_input = input_dev;
+  const size_t nops = net->ops.size();
+  std::vector<cudaEvent_t> ev(nops + 1);
+  for (auto& e : ev) NET_CUDA(cudaEventCreate(&e));
+  int rc = YC_OK;
+  for (int it = 0; it < iters && !rc; ++it) {
+    NET_CUDA(cudaEventRecord(ev[0], net->stream));
+    for (size_t k = 0; k < nops && !rc; ++k) {
+      rc = run_op(net, net->ops[k], net->stream);
+      NET_CUDA(cudaEventRecord(ev[k + 1], net->stream));
+    }
+    NET_CUDA(cudaStreamSynchronize(net->stream));
+    for (size_t k = 0; k < nops && !rc; ++k) {
+      float ms = 0.f;
+      NET_CUDA(cudaEventElapsedTime(&ms, ev[k], ev[k + 1]));
+      const int li = net->ops[k].layer < 0 ? nl : net->ops[k].layer;
+      ms_per_layer[li] += ms / iters;
+    }
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+  return rc;
+}
+
+// ---- detections on the host: GetNetworkBoxes / NmsSort --------------------------------------------------
+namespace {
+
+inline int entry_index(const NLayer& L, int batch, int location, int entry, int E) {  // EntryIndex yolo_layer.cpp:380-386
+  const int wh = L.out_w * L.out_h;
+  const int n = location / wh, loc = location % wh;
+  return batch * (L.out_c * wh) + n * wh * E + entry * wh + loc;
+}
+
+struct HBox { float x, y, w, h; };
+inline float overlap1(float x1, float w1, float x2, float w2) {  // Box::Overlap box.cpp:36-46
+  const float l1 = x1 - w1 / 2, l2 = x2 - w2 / 2;
+  const float left = l1 > l2 ? l1 : l2;
+  const float r1 = x1 + w1 / 2, r2 = x2 + w2 / 2;
+  const float right = r1 < r2 ? r1 : r2;
+  return right - left;
+}
+inline float box_intersect(const HBox& a, const HBox& b) {  // box.cpp:48-57
+  const float w = overlap1(a.x, a.w, b.x, b.w), h = overlap1(a.y, a.h, b.y, b.h);
+  if (w < 0 || h < 0) return 0;
+  return w * h;
+}
+inline float box_iou(const HBox& a, const HBox& b) {  // box.cpp:59-72
+  const float I = box_intersect(a, b);
+  const float U = a.w * a.h + b.w * b.h - I;
+  if (fabsf(I) < FLT_EPSILON || fabsf(U) < FLT_EPSILON) return 0;
+  return I / U;
+}
+inline float box_diou(const HBox& a, const HBox& b, float beta) {  // Box::Diou box.cpp:97-115
+  const float top = fminf(a.y - a.h / 2, b.y - b.h / 2), bot = fmaxf(a.y + a.h / 2, b.y + b.h / 2);
+  const float left = fminf(a.x - a.w / 2, b.x - b.w / 2), right = fmaxf(a.x + a.w / 2, b.x + b.w / 2);
+  const float w = right - left, h = bot - top;
+  const float c = w * w + h * h;
+  const float iou = box_iou(a, b);
+  if (fabsf(c) < FLT_EPSILON) return iou;
+  const float d = (a.x - b.x) * (a.x - b.x) + (a.y - b.y) * (a.y - b.y);
+  const float diou_term = powf(d / c, beta);
+  return iou - diou_term;
+}
+
+int nms_comparator(const void* pa, const void* pb) {  // NmsComparator box.cpp:372-389
+  const yc_detection* a = (const yc_detection*)pa;
+  const yc_detection* b = (const yc_detection*)pb;
+  float diff = 0;
+  if (b->sort_class >= 0) diff = a->prob[b->sort_class] - b->prob[b->sort_class];
+  else diff = a->objectness - b->objectness;
+  if (diff < 0) return 1;
+  if (diff > 0) return -1;
+  return 0;
+}
+
+}  // namespace
+
+// skip_empty: classes nobody scored change nothing but the array order in the reference (every prob[k]==0 is
+// skipped, box.cpp:405); the throughput path, whose rows do not move, skips their sort.
+static void nms_sort_impl(yc_detection* dets, int total, int classes, float thresh, int nms_kind, float beta,
+                          bool skip_empty) {
+  for (int k = 0; k < classes; ++k) {
+    if (skip_empty) {
+      bool any = false;
+      for (int i = 0; i < total && !any; ++i) any = fabsf(dets[i].prob[k]) >= FLT_EPSILON;
+      if (!any) continue;
+    }
+    for (int i = 0; i < total; ++i) dets[i].sort_class = k;
+    qsort(dets, total, sizeof(yc_detection), nms_comparator);
+    for (int i = 0; i < total; ++i) {
+      if (fabsf(dets[i].prob[k]) < FLT_EPSILON) continue;
+      const HBox a{dets[i].x, dets[i].y, dets[i].w, dets[i].h};
+      for (int j = i + 1; j < total; ++j) {
+        const HBox b{dets[j].x, dets[j].y, dets[j].w, dets[j].h};
+        if (nms_kind == 0 && box_iou(a, b) > thresh) dets[j].prob[k] = 0.f;
+        else if (nms_kind == 1 && box_diou(a, b, beta) > thresh) dets[j].prob[k] = 0.f;
+      }
+    }
+  }
+}
+
+extern "C" void yc_nms_sort(yc_detection* dets, int total, int classes, float thresh, int nms_kind, float beta) {
+  nms_sort_impl(dets, total, classes, thresh, nms_kind, beta, false);
+}
+
+extern "C" yc_detection* yc_network_get_boxes(yc_network* net, int b, float thresh, int* num) {
+  if (!net || b < 0 || b >= net->batch || !(net->flags & YC_NET_PULL_HEADS)) {
+    set_error("yc_network_get_boxes: bad argument (needs YC_NET_PULL_HEADS)");
+    return nullptr;
+  }
+  // NumDetections (network.cpp:432-448)
+  int count = 0;
+  int classes = 0;
+  for (int li : net->yolo_layers) {
+    const NLayer& L = net->layers[li];
+    const bool g = L.type == L_GYOLO;
+    const int E = (g ? 9 : 5) + L.classes, wh = L.out_w * L.out_h;
+    classes = L.classes;
+    for (int n = 0; n < L.n; ++n)
+      for (int i = 0; i < wh; ++i)
+        if (L.dec_host[entry_index(L, b, n * wh + i, g ? 8 : 4, E)] > thresh) ++count;
+  }
+  yc_detection* dets = (yc_detection*)calloc(count > 0 ? count : 1, sizeof(yc_detection));  // MakeNetworkBoxes :450-471
+  for (int i = 0; i < count; ++i) dets[i].prob = (float*)calloc(classes, sizeof(float));
+  int k = 0;
+  for (int li : net->yolo_layers) {  // FillNetworkBoxes :473-496
+    const NLayer& L = net->layers[li];
+    const bool g = L.type == L_GYOLO;
+    const int E = (g ? 9 : 5) + L.classes, wh = L.out_w * L.out_h;
+    const float* pred = L.dec_host;
+    for (int n = 0; n < L.n; ++n)
+      for (int i = 0; i < wh; ++i) {
+        const int loc = n * wh + i;
+        const float obj = pred[entry_index(L, b, loc, g ? 8 : 4, E)];
+        if (obj <= thresh) continue;
+        const int bi = entry_index(L, b, loc, 0, E);
+        const int col = i % L.out_w, row = i / L.out_w;
+        yc_detection& d = dets[k++];
+        const int m = L.mask[n];
+        float scale = 1.f;
+        if (g) {  // GetGaussianYoloBox gaussian_yolo_layer.cpp:151-160
+          d.w = (float)(exp((double)pred[bi + 4 * wh]) * L.anchors[2 * m] / net->w);
+          d.h = (float)(exp((double)pred[bi + 6 * wh]) * L.anchors[2 * m + 1] / net->h);
+          d.x = (col + pred[bi]) / L.out_w;
+          d.y = (row + pred[bi + 2 * wh]) / L.out_h;
+          d.uc[0] = pred[bi + 1 * wh]; d.uc[1] = pred[bi + 3 * wh]; d.uc[2] = pred[bi + 5 * wh]; d.uc[3] = pred[bi + 7 * wh];
+        } else {  // GetYoloBox yolo_layer.cpp:139-148
+          d.x = (col + pred[bi]) / L.out_w;
+          d.y = (row + pred[bi + wh]) / L.out_h;
+          d.w = (float)(exp((double)pred[bi + 2 * wh]) * L.anchors[2 * m] / net->w);
+          d.h = (float)(exp((double)pred[bi + 3 * wh]) * L.anchors[2 * m + 1] / net->h);
+        }
+        d.objectness = obj;
+        d.classes = L.classes;
+        for (int j = 0; j < L.classes; ++j) {
+          const float cls = pred[entry_index(L, b, loc, (g ? 9 : 5) + j, E)];
+          float prob;
+          if (g) {
+            const float uc_avg = (float)((d.uc[0] + d.uc[1] + d.uc[2] + d.uc[3]) / 4.0);
+            prob = (float)(obj * cls * (1.0 - uc_avg));
+          } else {
+            prob = obj * cls;
+          }
+          d.prob[j] = (prob > thresh) ? prob : 0;
+        }
+        (void)scale;
+      }
+  }
+  if (num) *num = count;
+  return dets;
+}
+
+extern "C" void yc_free_detections(yc_detection* dets, int n) {
+  if (!dets) return;
+  for (int i = 0; i < n; ++i) free(dets[i].prob);
+  free(dets);
+}
+
+extern "C" int yc_network_detect(yc_network* net, float thresh, float nms_thresh, const float** rows, int* counts,
+                                 int* total) {
+  YC_REQUIRE(net && rows && counts && total && net->finalized, "yc_network_detect: bad argument");
+  const int heads = (int)net->yolo_layers.size();
+  YC_REQUIRE(heads > 0, "yc_network_detect: network has no YOLO layer");
+  const int classes = net->layers[net->yolo_layers[0]].classes;
+  const int R = 7 + classes;
+  const int B = net->batch;
+  if (!net->det_regions) {
+    net->det_cap = 4096;        // rows kept per (head, image)
+    net->det_dense_cap = B * 1024;
+    net->det_R = R;
+    NET_CUDA(cudaMalloc(&net->det_regions, (size_t)heads * B * net->det_cap * R * 4));
+    NET_CUDA(cudaMalloc(&net->det_counts, (size_t)heads * B * 4));
+    NET_CUDA(cudaMalloc(&net->det_dense, (size_t)net->det_dense_cap * R * 4));
+    NET_CUDA(cudaMalloc(&net->det_img_counts, (size_t)B * 4));
+    NET_CUDA(cudaHostAlloc(&net->det_host, (size_t)net->det_dense_cap * R * 4, cudaHostAllocDefault));
+    NET_CUDA(cudaHostAlloc(&net->det_img_counts_host, (size_t)B * 4, cudaHostAllocDefault));
+  }
+  cudaStream_t st = net->stream;
+  for (int hd = 0; hd < heads; ++hd) {
+    const int li = net->yolo_layers[hd];
+    NLayer& L = net->layers[li];
+    int rc = launch_yolo_extract(L.dec_dev, B, L.out_h, L.out_w, L.n, L.classes, L.anchors_dev, L.mask_dev, net->w, net->h,
+                                 thresh, L.type == L_GYOLO, net->det_regions + (size_t)hd * B * net->det_cap * R,
+                                 net->det_cap, net->det_counts + (size_t)hd * B, R, (float)li, st);
+    if (rc) return rc;
+  }
+  int rc = launch_yolo_gather(net->det_regions, net->det_counts, heads, B, net->det_cap, R, net->det_dense,
+                              net->det_img_counts, net->det_dense_cap, st);
+  if (rc) return rc;
+  NET_CUDA(cudaMemcpyAsync(net->det_img_counts_host, net->det_img_counts, (size_t)B * 4, cudaMemcpyDeviceToHost, st));
+  NET_CUDA(cudaStreamSynchronize(st));
+  long long tot = 0;
+  for (int b = 0; b < B; ++b) tot += net->det_img_counts_host[b];
+  if (tot > net->det_dense_cap) {
+    set_error("yc_network_detect: %lld detections exceed the dense capacity %d (raise thresh)", tot, net->det_dense_cap);
+    return YC_ERR_ARG;
+  }
+  if (tot > 0) {
+    NET_CUDA(cudaMemcpyAsync(net->det_host, net->det_dense, (size_t)tot * R * 4, cudaMemcpyDeviceToHost, st));
+    NET_CUDA(cudaStreamSynchronize(st));
+  }
+  for (int b = 0; b < B; ++b) counts[b] = net->det_img_counts_host[b];
+  *total = (int)tot;
+  *rows = net->det_host;
+  if (nms_thresh > 0 && tot > 0) {
+    const NLayer& L0 = net->layers[net->yolo_layers[0]];
+    const int nms_kind = L0.nms_kind;
+    const float beta = L0.beta_nms;
+    std::vector<int> offs(B + 1, 0);
+    for (int b = 0; b < B; ++b) offs[b + 1] = offs[b] + counts[b];
+    float* base = net->det_host;
+    auto work = [&](int b0, int b1) {
+      std::vector<yc_detection> d;
+      std::vector<int> order;
+      for (int b = b0; b < b1; ++b) {
+        const int n = counts[b];
+        if (n <= 1) continue;
+        d.resize(n);
+        for (int i = 0; i < n; ++i) {
+          float* r = base + (size_t)(offs[b] + i) * R;
+          d[i].x = r[1]; d[i].y = r[2]; d[i].w = r[3]; d[i].h = r[4]; d[i].objectness = r[5];
+          d[i].classes = classes; d[i].prob = r + 7; d[i].sort_class = -1;
+        }
+        nms_sort_impl(d.data(), n, classes, nms_thresh, nms_kind, beta, true);  // probs are zeroed in place in the rows
+      }
+    };
+    const int nthreads = std::max(1, std::min<int>(B, (int)std::thread::hardware_concurrency()));
+    if (nthreads == 1 || tot < 256) {
+      work(0, B);
+    } else {
+      std::vector<std::thread> th;
+      const int per = (B + nthreads - 1) / nthreads;
+      for (int t = 0; t < nthreads; ++t) {
+        const int b0 = t * per, b1 = std::min(B, b0 + per);
+        if (b0 < b1) th.emplace_back(work, b0, b1);
+      }
+      for (auto& t : th) t.join();
+    }
+  }
+  return YC_OK;
+}

@@ -63,11 +63,12 @@ __global__ void yolo_decode_kernel(HeadView x, float* __restrict__ out, int S, i
 __global__ void yolo_extract_kernel(const float* __restrict__ pred, int S, int W, int H, int A, int classes, int E,
                                     const float* __restrict__ anchor_wh, const int* __restrict__ mask, int net_w,
                                     int net_h, float thresh, int gaussian, float* __restrict__ rows,
-                                    int rows_per_image, int* __restrict__ counts) {
+                                    int rows_per_image, int* __restrict__ counts, int R, float tag) {
   __shared__ int warp_sums[32];
   __shared__ int base_s;
   const int b = blockIdx.x;
-  const int R = 6 + classes;  // [batch x y w h obj probs...]
+  // row = [batch x y w h obj (tag) probs...]; probs occupy the last `classes` columns of the R-wide row
+  const int pc = R - classes;
   const float* p = pred + (long long)b * A * E * S;
   const int total = A * S;
   const int obj_e = gaussian ? 8 : 4;
@@ -117,9 +118,10 @@ __global__ void yolo_extract_kernel(const float* __restrict__ pred, int S, int W
         bh = (float)(exp((double)q[3 * (long long)S]) * anchor_wh[2 * m + 1] / net_h);
       }
       o[0] = (float)b; o[1] = bx; o[2] = by; o[3] = bw; o[4] = bh; o[5] = obj;
+      if (pc > 6) o[6] = tag;
       for (int j = 0; j < classes; ++j) {
         const float pr = obj * q[(long long)(obj_e + 1 + j) * S] * scale;
-        o[6 + j] = (pr > thresh) ? pr : 0.f;  // yolo_layer.cpp:820-826
+        o[pc + j] = (pr > thresh) ? pr : 0.f;  // yolo_layer.cpp:820-826
       }
     }
     __syncthreads();
@@ -127,6 +129,49 @@ __global__ void yolo_extract_kernel(const float* __restrict__ pred, int S, int W
     __syncthreads();
   }
   if (threadIdx.x == 0) counts[b] = base_s;
+}
+
+// Dense gather of the per-(head,image) row regions into one [total][R] array ordered by image, then
+// head (the reference's order within an image: FillNetworkBoxes walks layers in net order,
+// network.cpp:473-496).  counts is [heads][n]; every block recomputes the (tiny) exclusive scan.
+__global__ void yolo_gather_kernel(const float* __restrict__ regions, const int* __restrict__ counts, int heads,
+                                   int n, int cap, int R, float* __restrict__ dense, int* __restrict__ img_counts,
+                                   int dense_cap) {
+  const int b = blockIdx.x / heads, hd = blockIdx.x % heads;
+  int off = 0;
+  for (int bb = 0; bb <= b; ++bb)
+    for (int hh = 0; hh < heads; ++hh) {
+      if (bb == b && hh >= hd) break;
+      off += min(counts[hh * n + bb], cap);
+    }
+  const int cnt = min(counts[hd * n + b], cap);
+  if (hd == 0 && threadIdx.x == 0) {
+    int t = 0;
+    for (int hh = 0; hh < heads; ++hh) t += min(counts[hh * n + b], cap);
+    img_counts[b] = t;
+  }
+  const float* src = regions + ((long long)(hd * n + b) * cap) * R;
+  const long long total = (long long)cnt * R;
+  for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+    const long long row = off + i / R;
+    if (row < dense_cap) dense[(long long)off * R + i] = src[i];
+  }
+}
+
+int launch_yolo_extract(const float* decoded, int n, int h, int w, int anchors, int classes, const float* anchor_wh,
+                        const int* mask, int net_w, int net_h, float thresh, int gaussian, float* rows,
+                        int rows_per_image, int* counts, int R, float tag, cudaStream_t stream) {
+  const int E = (gaussian ? 9 : 5) + classes;
+  yolo_extract_kernel<<<n, 256, 0, stream>>>(decoded, h * w, w, h, anchors, classes, E, anchor_wh, mask, net_w, net_h,
+                                             thresh, gaussian, rows, rows_per_image, counts, R, tag);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+int launch_yolo_gather(const float* regions, const int* counts, int heads, int n, int cap, int R, float* dense,
+                       int* img_counts, int dense_cap, cudaStream_t stream) {
+  yolo_gather_kernel<<<heads * n, 256, 0, stream>>>(regions, counts, heads, n, cap, R, dense, img_counts, dense_cap);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
 }
 
 }  // namespace yc
@@ -151,9 +196,6 @@ extern "C" int yc_yolo_extract(const float* decoded, int n, int h, int w, int an
                                const float* anchor_wh, const int* mask, int net_w, int net_h, float thresh,
                                int gaussian, float* rows, int rows_per_image, int* counts, void* stream) {
   YC_REQUIRE(decoded && anchor_wh && mask && rows && counts && n > 0, "yc_yolo_extract: null argument");
-  const int E = (gaussian ? 9 : 5) + classes;
-  yolo_extract_kernel<<<n, 256, 0, (cudaStream_t)stream>>>(decoded, h * w, w, h, anchors, classes, E, anchor_wh, mask,
-                                                          net_w, net_h, thresh, gaussian, rows, rows_per_image, counts);
-  YC_LAUNCH_CHECK();
-  return YC_OK;
+  return launch_yolo_extract(decoded, n, h, w, anchors, classes, anchor_wh, mask, net_w, net_h, thresh, gaussian, rows,
+                             rows_per_image, counts, 6 + classes, 0.f, (cudaStream_t)stream);
 }

@@ -31,6 +31,16 @@ class ConvDesc(C.Structure):
                 ("activation", C.c_int), ("residual_activation", C.c_int)]
 
 
+class Detection(C.Structure):
+    """struct yc_detection == the reference's struct Detection (yolo_core.h:598-609) on the path."""
+    _fields_ = [("x", C.c_float), ("y", C.c_float), ("w", C.c_float), ("h", C.c_float), ("classes", C.c_int),
+                ("prob", C.POINTER(C.c_float)), ("objectness", C.c_float), ("sort_class", C.c_int),
+                ("uc", C.c_float * 4)]
+
+
+NET_FUSE_BN, NET_FUSE_SHORTCUT, NET_ELIDE_ROUTE, NET_CUDA_GRAPH, NET_PULL_HEADS, NET_REF_CPU_MAXPOOL = 1, 2, 4, 8, 16, 32
+NET_DEFAULT = 1 | 2 | 4 | 8 | 16
+
 _lib = None
 
 _P = C.c_void_p
@@ -70,6 +80,23 @@ _SIGS = {
     "yc_yolo_decode": (C.c_int, [_TP, _P, C.c_int, C.c_int, C.c_float, C.c_int, _P]),
     "yc_yolo_extract": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, C.c_int,
                                   C.c_float, C.c_int, _P, C.c_int, _P, _P]),
+    "yc_network_load": (C.c_int, [C.POINTER(_P), C.c_char_p, C.c_char_p, C.c_int, C.c_int]),
+    "yc_network_load_text": (C.c_int, [C.POINTER(_P), C.c_char_p, C.c_char_p, C.c_int, C.c_int]),
+    "yc_network_free": (C.c_int, [_P]),
+    "yc_network_set_conv_weights": (C.c_int, [_P, C.c_int, _P, _P, _P, _P, _P]),
+    "yc_network_finalize": (C.c_int, [_P]),
+    "yc_network_info": (C.c_int, [_P, C.c_int]),
+    "yc_network_layer_info": (C.c_int, [_P, C.c_int, C.c_int]),
+    "yc_network_flops": (C.c_double, [_P]),
+    "yc_network_predict": (_P, [_P, _P]),
+    "yc_network_forward": (C.c_int, [_P, _P, _P]),
+    "yc_network_layer_output": (C.c_int, [_P, C.c_int, _P]),
+    "yc_network_yolo_output": (_P, [_P, C.c_int]),
+    "yc_network_profile": (C.c_int, [_P, _P, C.c_int, _P]),
+    "yc_network_get_boxes": (C.POINTER(Detection), [_P, C.c_int, C.c_float, C.POINTER(C.c_int)]),
+    "yc_free_detections": (None, [C.POINTER(Detection), C.c_int]),
+    "yc_nms_sort": (None, [C.POINTER(Detection), C.c_int, C.c_int, C.c_float, C.c_int, C.c_float]),
+    "yc_network_detect": (C.c_int, [_P, C.c_float, C.c_float, C.POINTER(C.POINTER(C.c_float)), _P, C.POINTER(C.c_int)]),
 }
 
 

@@ -1,0 +1,204 @@
+"""Host-side mirror of the reference's network API for the hot path, over the C ABI.
+
+Same names and argument meaning as the reference (`src/yolo_core.h:625-663`, `src/network.h:8-37`,
+`src/box.h:93-97`): LoadNetwork / NetworkPredict / GetNetworkBoxes / NmsSort / FreeNetwork.  All the
+work happens in libyc_b200.so (csrc/network.cu + the kernels); this module only marshals numpy
+buffers.  There is no CPU fallback: every call raises YcError if the library or the GPU is missing.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import lib as L
+
+
+class Network:
+    """yc_network handle (the reference's `Network`, yolo_core.h:453-546)."""
+
+    def __init__(self, handle):
+        self.h = handle
+        lib = L.lib()
+        self.n = lib.yc_network_info(self.h, 0)
+        self.batch = lib.yc_network_info(self.h, 1)
+        self.w = lib.yc_network_info(self.h, 2)
+        self.hh = lib.yc_network_info(self.h, 3)
+        self.c = lib.yc_network_info(self.h, 4)
+
+    # ---- introspection --------------------------------------------------------------------------
+    def info(self, what):
+        return L.lib().yc_network_info(self.h, what)
+
+    def layer_info(self, i, what):
+        return L.lib().yc_network_layer_info(self.h, i, what)
+
+    def layer_shape(self, i):
+        return (self.batch, self.layer_info(i, 1), self.layer_info(i, 2), self.layer_info(i, 3))
+
+    def layer_type(self, i):
+        return ["convolutional", "maxpool", "upsample", "route", "shortcut", "yolo", "Gaussian_yolo"][self.layer_info(i, 0)]
+
+    def has_output(self, i):
+        return bool(self.layer_info(i, 4))
+
+    def flops_per_image(self):
+        return L.lib().yc_network_flops(self.h)
+
+    def kernels_per_forward(self):
+        return self.info(6)
+
+    def layer_output(self, i):
+        """fp32 NCHW copy of layer i's output (cuda_pull_array of l->output_gpu)."""
+        out = np.empty(self.layer_shape(i), np.float32)
+        L.check(L.lib().yc_network_layer_output(self.h, i, out.ctypes.data_as(C.c_void_p)), "yc_network_layer_output")
+        return out
+
+    def yolo_layers(self):
+        return [i for i in range(self.n) if self.layer_info(i, 0) in (5, 6)]
+
+    def close(self):
+        if self.h:
+            L.lib().yc_network_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def LoadNetwork(cfg, weights=None, batch=0, flags=L.NET_DEFAULT, cfg_is_text=False) -> Network:
+    """LoadNetwork (parser.cpp:1852-1875): parse cfg, load .weights, fuse BN, plan kernels.
+    `batch<=0` keeps the cfg's batch; the reference forces 1 for inference (parser.cpp:1114-1115)."""
+    h = C.c_void_p()
+    fn = L.lib().yc_network_load_text if cfg_is_text else L.lib().yc_network_load
+    L.check(fn(C.byref(h), cfg.encode(), weights.encode() if weights else None, batch, flags), "LoadNetwork")
+    net = Network(h)
+    if not weights:
+        L.check(L.lib().yc_network_finalize(h), "yc_network_finalize")
+    return net
+
+
+def FreeNetwork(net: Network):
+    net.close()
+
+
+def NetworkPredict(net: Network, x: np.ndarray):
+    """NetworkPredict (network.cpp:412-430): x = host fp32 NCHW [batch,c,h,w]; synchronous.  Returns a numpy
+    view of the last layer's host output (layer-owned, valid until the next call)."""
+    x = np.ascontiguousarray(x, np.float32)
+    assert x.size == net.batch * net.c * net.hh * net.w, "input size != batch*c*h*w"
+    p = L.lib().yc_network_predict(net.h, x.ctypes.data_as(C.c_void_p))
+    if not p:
+        raise L.YcError("NetworkPredict failed: " + L.lib().yc_last_error().decode())
+    last = net.n - 1
+    shape = net.layer_shape(last)
+    if net.layer_info(last, 0) in (5, 6):
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=shape)
+    return None
+
+
+def ForwardNetworkGpu(net: Network, input_dev_ptr: int, stream=None):
+    """ForwardNetworkGpu (network_kernels.cu:45-114) on a device-resident fp32 NCHW input; asynchronous."""
+    L.check(L.lib().yc_network_forward(net.h, C.c_void_p(input_dev_ptr), stream if stream is not None else L.stream_ptr()),
+            "ForwardNetworkGpu")
+
+
+def yolo_output(net: Network, i):
+    """l->output of YOLO layer i after NetworkPredict (pinned host memory), as [batch, c, h, w]."""
+    p = L.lib().yc_network_yolo_output(net.h, i)
+    return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=net.layer_shape(i))
+
+
+class Detections:
+    """Owning wrapper over the Detection array returned by GetNetworkBoxes (freed with FreeDetections)."""
+
+    def __init__(self, ptr, n, classes):
+        self.ptr, self.n, self.classes = ptr, n, classes
+
+    def boxes(self):
+        """[n, 5]: x y w h objectness"""
+        return np.array([[d.x, d.y, d.w, d.h, d.objectness] for d in (self.ptr[i] for i in range(self.n))],
+                        np.float32).reshape(self.n, 5)
+
+    def probs(self):
+        out = np.zeros((self.n, self.classes), np.float32)
+        for i in range(self.n):
+            out[i] = np.ctypeslib.as_array(self.ptr[i].prob, shape=(self.classes,))
+        return out
+
+    def free(self):
+        if self.ptr is not None:
+            L.lib().yc_free_detections(self.ptr, self.n)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def DetectionsFromArrays(boxes4, obj, probs):
+    """Build a Detection array from numpy (tests / callers with their own candidates).  Returns (array, keepalive)."""
+    boxes4 = np.ascontiguousarray(boxes4, np.float32)
+    probs = np.ascontiguousarray(probs, np.float32).copy()
+    n, classes = probs.shape
+    arr = (L.Detection * max(n, 1))()
+    for i in range(n):
+        arr[i].x, arr[i].y, arr[i].w, arr[i].h = (float(v) for v in boxes4[i])
+        arr[i].objectness = float(obj[i])
+        arr[i].classes = classes
+        arr[i].prob = C.cast(probs[i].ctypes.data_as(C.c_void_p), C.POINTER(C.c_float))
+        arr[i].sort_class = -1
+    return arr, probs
+
+
+def NmsSortArrays(boxes4, obj, probs, thresh, nms_kind=0, beta=0.6):
+    """NmsSort on arrays: (probs after suppression in original order, final array order)."""
+    arr, p = DetectionsFromArrays(boxes4, obj, probs)
+    n, classes = p.shape
+    L.lib().yc_nms_sort(arr, n, classes, thresh, nms_kind, beta)
+    base = p.ctypes.data
+    order = np.array([(C.cast(arr[i].prob, C.c_void_p).value - base) // (4 * classes) for i in range(n)], np.int32)
+    return p, order
+
+
+def GetNetworkBoxes(net: Network, thresh: float, b: int = 0) -> Detections:
+    """GetNetworkBoxes (network.cpp:498-503) for batch element b (the reference reads b=0 only)."""
+    n = C.c_int(0)
+    ptr = L.lib().yc_network_get_boxes(net.h, b, thresh, C.byref(n))
+    if not ptr:
+        raise L.YcError("GetNetworkBoxes failed: " + L.lib().yc_last_error().decode())
+    yl = net.yolo_layers()
+    classes = net.layer_info(yl[-1], 1) // 3 - 5 if yl else 0
+    return Detections(ptr, n.value, _classes(net))
+
+
+def _classes(net):
+    yl = net.yolo_layers()
+    i = yl[-1]
+    per = net.layer_info(i, 1)
+    gaussian = net.layer_info(i, 0) == 6
+    return per // 3 - (9 if gaussian else 5)  # heads on the path use 3 anchors per layer
+
+
+def NmsSort(dets: Detections, thresh: float, nms_kind: int = 0, beta: float = 0.6):
+    """NmsSort (box.cpp:393-419), in place."""
+    L.lib().yc_nms_sort(dets.ptr, dets.n, dets.classes, thresh, nms_kind, beta)
+
+
+def DetectBatch(net: Network, thresh: float, nms_thresh: float = 0.45):
+    """Throughput path: on-device threshold + box decode for every image, host NmsSort per image.
+    Returns (rows [total, 7+classes], counts [batch]); row = image, x, y, w, h, objectness, head_layer, probs."""
+    rows = C.POINTER(C.c_float)()
+    counts = np.zeros(net.batch, np.int32)
+    total = C.c_int(0)
+    L.check(L.lib().yc_network_detect(net.h, thresh, nms_thresh, C.byref(rows), counts.ctypes.data_as(C.c_void_p),
+                                      C.byref(total)), "yc_network_detect")
+    R = 7 + _classes(net)
+    if total.value == 0:
+        return np.zeros((0, R), np.float32), counts
+    return np.ctypeslib.as_array(rows, shape=(total.value, R)).copy(), counts

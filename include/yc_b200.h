@@ -151,6 +151,85 @@ YC_API int yc_yolo_extract(const float* decoded_nchw, int n, int h, int w, int a
                     const float* anchor_wh, const int* mask, int net_w, int net_h, float thresh,
                     int gaussian, float* rows_dev, int rows_per_image, int* count_dev, void* stream);
 
+/* ---- whole network: replaces LoadNetwork / NetworkPredict / GetNetworkBoxes / NmsSort ------------ */
+/* Host side (csrc/network.cu, C++): cfg reader with the reference's INI semantics (parser.cpp:59-100,
+ * 1076-1519), darknet .weights reader (parser.cpp:1695-1759,1778-1844), FuseConvBatchNorm
+ * (network.cpp:647-682), buffer planner (NHWC bf16, [route] elided by writing producers into concat
+ * slots, [shortcut] fused into the producing conv's epilogue), CUDA-graph capture of the forward. */
+typedef struct yc_network yc_network;
+
+enum {
+  YC_NET_FUSE_BN = 1,        /* fold BN into W,b on the host in fp32, eps 1e-5: what LoadNetwork(train=false)
+                                does (parser.cpp:1866-1867).  Off: BN applied in the conv epilogue from the
+                                rolling statistics with eps 1e-6 (batchnorm_layer.cpp:226-237, blas.c:214). */
+  YC_NET_FUSE_SHORTCUT = 2,  /* conv + following [shortcut] in one kernel (the conv's own output is not kept) */
+  YC_NET_ELIDE_ROUTE = 4,    /* producers write straight into concat buffers; off: route = copy kernels */
+  YC_NET_CUDA_GRAPH = 8,     /* replay the forward as one captured graph */
+  YC_NET_PULL_HEADS = 16,    /* D2H every YOLO layer output after forward like the reference
+                                (yolo_layer.cpp:856); off: heads stay on the device (use yc_network_detect) */
+  YC_NET_REF_CPU_MAXPOOL = 32, /* reproduce forward_maxpool_layer_avx's artefact (see yc_maxpool_fwd) */
+  YC_NET_DEFAULT = 1 | 2 | 4 | 8 | 16
+};
+
+/* [setup] LoadNetwork (parser.cpp:1852-1875).  batch <= 0 keeps the cfg's batch (the reference forces
+ * batch=1 for inference, parser.cpp:1114-1115; batch>1 is this library's extension).  weights_path may be
+ * NULL (weights then come from yc_network_set_conv_weights). */
+YC_API int yc_network_load(yc_network** net, const char* cfg_path, const char* weights_path, int batch, int flags);
+YC_API int yc_network_load_text(yc_network** net, const char* cfg_text, const char* weights_path, int batch, int flags);
+YC_API int yc_network_free(yc_network* net);                         /* FreeNetwork network.cpp:518-645 */
+/* [setup] overwrite one conv layer's parameters from host fp32 arrays in the reference's layouts
+ * (OIHW weights; scales/mean/var may be NULL when the layer has no BN).  Call yc_network_finalize after. */
+YC_API int yc_network_set_conv_weights(yc_network* net, int layer, const float* weights, const float* biases,
+                                       const float* scales, const float* rolling_mean, const float* rolling_var);
+/* [setup] fuse BN, pack weights, plan buffers and conv kernels.  Called by yc_network_load when weights_path
+ * is given; idempotent. */
+YC_API int yc_network_finalize(yc_network* net);
+/* what: 0 n_layers, 1 batch, 2 w, 3 h, 4 c, 5 n_conv, 6 kernels launched per forward, 7 n_yolo */
+YC_API int yc_network_info(const yc_network* net, int what);
+/* per-layer: what: 0 type(0 conv,1 maxpool,2 upsample,3 route,4 shortcut,5 yolo,6 gaussian_yolo) 1 out_c 2 out_h
+ * 3 out_w 4 has_output(0 if fused away) 5 in_c 6 size 7 stride 8 activation 9 batch_normalize */
+YC_API int yc_network_layer_info(const yc_network* net, int layer, int what);
+YC_API double yc_network_flops(const yc_network* net);               /* sum 2*nweights*out_h*out_w per image
+                                                                        (convolutional_layer.cpp:714) */
+/* NetworkPredict (network.cpp:412-430 -> NetworkPredictGpu network_kernels.cu:502-522): input = host fp32 NCHW
+ * [batch*c*h*w] (borrowed), returns the host buffer of the last layer's output (layer-owned, valid until the
+ * next call) or NULL on error.  Synchronous like the reference. */
+YC_API float* yc_network_predict(yc_network* net, const float* input_host);
+/* ForwardNetworkGpu (network_kernels.cu:45-114) on an input already resident on the device
+ * (fp32 NCHW, the reference's net->input_state_gpu layout).  Asynchronous on `stream`. */
+YC_API int yc_network_forward(yc_network* net, const float* input_dev_nchw, void* stream);
+/* cuda_pull_array(l->output_gpu) equivalent: layer output as fp32 NCHW [batch,out_c,out_h,out_w] on the host. */
+YC_API int yc_network_layer_output(yc_network* net, int layer, float* dst_host);
+/* host pointer of a YOLO layer's pulled output (l->output; needs YC_NET_PULL_HEADS) */
+YC_API const float* yc_network_yolo_output(yc_network* net, int layer);
+/* per-layer device time of one un-graphed forward, averaged over iters (net->benchmark_layers,
+ * network_kernels.cu:70-94).  ms_per_layer has n_layers entries (+1: the input conversion at index n). */
+YC_API int yc_network_profile(yc_network* net, const float* input_dev_nchw, int iters, float* ms_per_layer);
+
+/* Detection == the reference's struct Detection minus unused members (yolo_core.h:598-609). */
+typedef struct yc_detection {
+  float x, y, w, h;        /* Box bbox */
+  int classes;
+  float* prob;             /* [classes] */
+  float objectness;
+  int sort_class;
+  float uc[4];             /* Gaussian_yolo uncertainties */
+} yc_detection;
+/* GetNetworkBoxes (network.cpp:498-503) for batch element b (the reference is b=0 only): scans the pulled
+ * host YOLO outputs exactly like GetYoloDetections (yolo_layer.cpp:794-832).  Caller frees with
+ * yc_free_detections.  Needs YC_NET_PULL_HEADS. */
+YC_API yc_detection* yc_network_get_boxes(yc_network* net, int b, float thresh, int* num);
+YC_API void yc_free_detections(yc_detection* dets, int n);           /* FreeDetections network.cpp:505-516 */
+/* NmsSort (box.cpp:393-419). nms_kind: 0 greedy, 1 DIoU. */
+YC_API void yc_nms_sort(yc_detection* dets, int total, int classes, float thresh, int nms_kind, float beta);
+/* Throughput path: threshold + box decode on the device for every image (yc_yolo_extract per
+ * head), compact rows to the host, then NmsSort per image on host threads when nms_thresh > 0.
+ * On return *rows points to a library-owned host array of [total][7 + classes] floats
+ * (image, x, y, w, h, objectness, head_layer, prob[classes]) ordered by image, then head, anchor, cell — the
+ * reference's order within an image — and counts[b] is the number of rows of image b. */
+YC_API int yc_network_detect(yc_network* net, float thresh, float nms_thresh, const float** rows, int* counts,
+                             int* total);
+
 #ifdef __cplusplus
 }
 #endif

@@ -70,6 +70,7 @@ def ref_lib():
         L.ref_im2col.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
         L.ref_activate.argtypes = [_f32p, C.c_int, C.c_int, _f32p, _f32p]
         L.ref_activation_id.argtypes = [C.c_char_p]
+        L.ref_nms.argtypes = [_f32p, _f32p, _f32p, C.c_int, C.c_int, C.c_float, C.c_int, C.c_float, _i32p]
         _ref = L
     return _ref
 
@@ -152,6 +153,17 @@ class RefNet:
     def time_predict(self, x, iters=1):
         x = np.ascontiguousarray(x, np.float32).reshape(-1)
         return self.L.ref_time_predict(self.h, x, iters)
+
+
+def ref_nms(boxes, obj, probs, thresh, nms_kind=0, beta=0.6):
+    """The reference's NmsSort on arrays: returns (probs after suppression in ORIGINAL order, final order)."""
+    boxes = np.ascontiguousarray(boxes, np.float32)
+    obj = np.ascontiguousarray(obj, np.float32)
+    p = np.ascontiguousarray(probs, np.float32).copy()
+    n, classes = p.shape
+    order = np.zeros(n, np.int32)
+    ref_lib().ref_nms(boxes.reshape(-1), obj, p.reshape(-1), n, classes, thresh, nms_kind, beta, order)
+    return p, order
 
 
 def oracle_lib():

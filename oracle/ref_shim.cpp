@@ -193,6 +193,24 @@ int ref_get_boxes(void* h, float thresh, float nms_thresh, int nms_kind, float b
   return n;
 }
 
+// NmsSort — reference box.cpp:393-419 on caller-provided detections.  boxes: [n][4] (x y w h), obj: [n],
+// probs: [n][classes] (zeroed in place); order_out[i] = original index of the detection that ends at
+// position i of the reference's array after its qsorts.
+void ref_nms(float* boxes, float* obj, float* probs, int n, int classes, float thresh, int nms_kind, float beta,
+             int* order_out) {
+  Detection* dets = (Detection*)calloc(n > 0 ? n : 1, sizeof(Detection));
+  for (int i = 0; i < n; ++i) {
+    dets[i].bbox.x = boxes[4 * i]; dets[i].bbox.y = boxes[4 * i + 1];
+    dets[i].bbox.w = boxes[4 * i + 2]; dets[i].bbox.h = boxes[4 * i + 3];
+    dets[i].classes = classes;
+    dets[i].objectness = obj[i];
+    dets[i].prob = probs + (size_t)i * classes;
+  }
+  NmsSort(dets, n, classes, thresh, (NMS_KIND)nms_kind, beta);
+  for (int i = 0; i < n; ++i) order_out[i] = (int)((dets[i].prob - probs) / classes);
+  free(dets);
+}
+
 // wall-clock timing of K NetworkPredict calls using the reference's own timer granularity
 // (std::chrono steady_clock, same clock as GetTimePoint utils.cpp:437-444).  Returns seconds.
 double ref_time_predict(void* h, float* input, int iters) {
