@@ -1,0 +1,324 @@
+#!/usr/bin/env python
+"""bench.py — YOLOv4-608 batch-64 inference throughput on B200 (BASELINE.json metric), one JSON line.
+
+  python bench.py --gpus N --steps K --warmup W            # our arm (libyc_b200.so through the C ABI)
+  python bench.py --impl reference --gpus N --steps K ...  # the reference's own CPU path (oracle/_ref)
+
+A "step" = one forward pass of the hot path over one batch of 64 synthetic 608x608 images per GPU
+(ForwardNetworkGpu: input layout conversion, 110 fused conv kernels, SPP maxpools, upsamples, YOLO decode).
+  value : images/s, whole job, inputs already resident in HBM, timed with CUDA events on the launch stream,
+          barrier + synchronize on both sides, max over ranks.
+  e2e   : images/s through the public NetworkPredict-style call with HOST buffers: every step copies the
+          batch from pinned host memory (H2D), runs the forward, extracts detections on the device and reads
+          them back (D2H) + host NMS.
+  roofline     : the conv kernel (tensor bound): algorithmic FLOPs (2*nweights*Ho*Wo per layer, the
+                 reference's own bflops, convolutional_layer.cpp:714) / summed conv-kernel time measured with
+                 CUDA events per launch; peak = MEASURED_PEAKS.json (sustained bf16, since the kernel is
+                 timed inside a long step).
+  cpu_baseline : the UNMODIFIED reference CPU path (oracle/_ref) on this box's host cores, bounded sample.
+Multi-GPU: image-sharded, one process per GPU (torchrun), no collective on the data path -> weak scaling.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "images_per_sec"
+UNIT = "images/s"
+WORKLOADS = {
+    "yolov4": ("yolov4", 608, "yolov4.cfg 608x608 batch 64 inference"),
+    "yolov3": ("yolov3", 416, "yolov3.cfg 416x416 batch 64 inference"),
+    "yolov4-tiny": ("yolov4-tiny", 416, "yolov4-tiny.cfg 416x416 inference"),
+}
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"burst": d.get("bf16_tflops", 1590.0), "sustained": d.get("bf16_tflops_sustained", 1400.0),
+                "hbm": d.get("hbm_gbs", 6650.0), "source": "measured (MEASURED_PEAKS.json)"}
+    return {"burst": 1590.0, "sustained": 1400.0, "hbm": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path on this box's host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cfgname, hw, wl = WORKLOADS[args.workload]
+    cores = os.cpu_count() or 1
+    # each step = a bounded sample: `images_per_step` batch-1 NetworkPredict calls of the same workload
+    per_step_budget = max(2.0, 150.0 / max(1, args.steps + args.warmup))
+    env = dict(os.environ, OMP_NUM_THREADS=str(cores))
+    vals = []
+    info = {}
+    for i in range(args.warmup + args.steps):
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "oracle", "time_ref.py"), "--config", cfgname, "--width", str(hw),
+                            "--height", str(hw), "--budget", str(per_step_budget), "--max-images", "8"],
+                           capture_output=True, text=True, env=env)
+        line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+        if not line:
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref run failed: " + r.stderr[-200:]}))
+            return 0
+        info = json.loads(line[-1])
+        if "error" in info:
+            print(json.dumps({"impl": "reference", "unavailable": info["error"]}))
+            return 0
+        if i >= args.warmup:
+            vals.append(info["images_per_s"])
+    v = statistics.mean(vals)
+    sample = f"{info['images']} batch-1 NetworkPredict calls per step after 1 warm-up (reference inference is batch 1, parser.cpp:1114-1115)"
+    out = {"metric": METRIC, "value": v, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": 1e3 * 64 / v, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": wl, "net": cfgname, "width": hw, "height": hw, "batch": 64,
+                      "note": "CPU reference timed per image; ms_per_step = 64 images at that rate"},
+           "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+           "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out))
+    return 0
+
+
+def cpu_baseline(cfgname, hw, budget):
+    cores = os.cpu_count() or 1
+    env = dict(os.environ, OMP_NUM_THREADS=str(cores))
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "oracle", "time_ref.py"), "--config", cfgname, "--width", str(hw),
+                            "--height", str(hw), "--budget", str(budget), "--max-images", "16"],
+                           capture_output=True, text=True, env=env, timeout=600)
+        line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+        info = json.loads(line[-1])
+        if "error" in info:
+            return {"value": None, "unit": UNIT, "cores": cores, "kind": "reference", "sample": info["error"]}
+        return {"value": info["images_per_s"], "unit": UNIT, "cores": cores, "kind": "reference",
+                "sample": f"{info['images']} images, batch-1 NetworkPredict of the same net ({info['s_per_image']:.3f} s/image), "
+                          f"OMP_NUM_THREADS={cores}, 1 warm-up"}
+    except Exception as e:  # noqa: BLE001
+        return {"value": None, "unit": UNIT, "cores": cores, "kind": "reference", "sample": f"failed: {e}"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="yolov4", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=15.0)
+    ap.add_argument("--layers", action="store_true", help="print the per-layer time table to stderr")
+    ap.add_argument("--quick-exit-after-timed", action="store_true", help="(profiling) skip e2e / roofline / cpu legs")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+    from darknet_b200 import cfg as cfgmod, cfgs, lib as L, network as N
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU: the product has no CPU fallback"
+    torch.cuda.set_device(local)
+    L.check(L.lib().yc_set_device(local), "yc_set_device")
+    dist = None
+    if world > 1:
+        import torch.distributed as dist  # noqa: F811
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    cfgname, hw, wl = WORKLOADS[args.workload]
+    B = args.batch
+    text = cfgs.CONFIGS[cfgname](w=hw, h=hw)
+    weights = cfgmod.synth_weights(text)
+    # sparse-detection regime like a trained detector: spread head logits, objectness bias -7
+    cfgmod.shift_head_objectness(text, weights, -7.0, 40.0)
+    flags = L.NET_DEFAULT & ~L.NET_PULL_HEADS
+    net = N.LoadSynthetic(text, weights, batch=B, flags=flags)
+    del weights
+    flops_img = net.flops_per_image()
+
+    # synthetic images, different per rank (image sharding), resident on the device for the `value` leg
+    x_host = N.InputBuffer(net)
+    x_host[...] = cfgmod.synth_images(B, 3, hw, hw, seed=1234 + rank)
+    x_dev = torch.from_numpy(np.ascontiguousarray(x_host)).cuda()
+    stream = torch.cuda.current_stream()
+    sp = C.c_void_p(stream.cuda_stream)
+
+    def step():
+        L.check(L.lib().yc_network_forward(net.h, C.c_void_p(x_dev.data_ptr()), sp), "yc_network_forward")
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    barrier()
+    L.lib().yc_launch_count(1)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = int(L.lib().yc_launch_count(0))
+    clocks = sampler.stop() if rank == 0 else None
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = world * B * args.steps / (ms / 1e3)
+
+    # ---- e2e: host buffers, H2D + forward + on-device extraction + D2H + host NMS -------------------
+    e2e = None
+    roof = None
+    cpu = None
+    if not args.quick_exit_after_timed:
+        def e2e_step():
+            N.NetworkPredict(net, x_host)            # pinned host -> H2D -> forward (synchronous)
+            return N.DetectBatch(net, 0.25, 0.45)    # device threshold/decode -> D2H rows -> host NmsSort
+        for _ in range(2):
+            rows, counts = e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        d2h = 0
+        for _ in range(args.steps):
+            rows, counts = e2e_step()
+            d2h += rows.nbytes + counts.nbytes
+        torch.cuda.synchronize()
+        t_e2e = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([t_e2e], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            t_e2e = float(t.item())
+        e2e = {"value": world * B * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(x_host.nbytes),
+               "d2h_bytes_per_step": int(d2h // args.steps), "ms_per_step": 1e3 * t_e2e / args.steps,
+               "detections_per_step": int(counts.sum()),
+               "api": "yc_network_predict(pinned host fp32 NCHW) + yc_network_detect(thresh .25, nms .45)"}
+
+        # ---- roofline of the dominant kernel (conv_fprop_kernel), rank 0 ---------------------------------
+        if rank == 0:
+            nl = net.n
+            ms_layer = np.zeros(nl + 1, np.float32)
+            L.check(L.lib().yc_network_profile(net.h, C.c_void_p(x_dev.data_ptr()), 3, ms_layer.ctypes.data_as(C.c_void_p)),
+                    "yc_network_profile")
+            conv_ms = float(sum(ms_layer[i] for i in range(nl) if net.layer_info(i, 0) == 0))
+            other_ms = float(ms_layer.sum() - conv_ms)
+            peaks = _peaks()
+            ach = flops_img * B / (conv_ms / 1e3) / 1e12
+            n_conv = net.info(5)
+            roof = {"bound": "tensor", "kernel": "conv_fprop_kernel", "achieved": ach, "peak": peaks["sustained"],
+                    "unit": "TFLOP/s", "frac": ach / peaks["sustained"], "traffic": None,
+                    "frac_of_burst_peak": ach / peaks["burst"], "peak_source": peaks["source"] + ", sustained bf16",
+                    "launches_per_step": n_conv, "flops_per_step": flops_img * B, "conv_ms_per_step": conv_ms,
+                    "other_kernels_ms_per_step": other_ms,
+                    "avg_launch_us": 1e3 * conv_ms / n_conv,
+                    "whole_step_frac": (flops_img * B / (ms_per_step / 1e3) / 1e12) / peaks["sustained"],
+                    "how": "sum of algorithmic FLOPs of the conv launches of one step / sum of their durations; each launch "
+                           "bracketed by CUDA events on the launch stream (yc_network_profile, 3 passes averaged)"}
+            if args.layers:
+                for i in range(nl):
+                    if ms_layer[i] > 0:
+                        t = net.layer_type(i)
+                        extra = ""
+                        if t == "convolutional":
+                            f = 2.0 * net.layer_info(i, 1) * net.layer_info(i, 5) * net.layer_info(i, 6) ** 2 * net.layer_info(i, 2) * net.layer_info(i, 3) * B
+                            extra = (f" k{net.layer_info(i,6)} s{net.layer_info(i,7)} {net.layer_info(i,5)}->{net.layer_info(i,1)} "
+                                     f"@{net.layer_info(i,2)} bn={net.layer_info(i,10)} st={net.layer_info(i,11)} tiles={net.layer_info(i,12)} "
+                                     f"{f/ms_layer[i]/1e9:.0f} TF/s")
+                        print(f"  L{i:3d} {t:14s} {ms_layer[i]*1e3:8.1f} us{extra}", file=sys.stderr)
+                print(f"  input convert {ms_layer[nl]*1e3:8.1f} us", file=sys.stderr)
+            if not args.no_cpu_baseline and world == 1:
+                cpu = cpu_baseline(cfgname, hw, args.cpu_budget)
+
+    if rank == 0:
+        out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+               "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+               "dtype": "bf16", "data": "synthetic",
+               "config": {"workload": wl, "net": cfgname, "width": hw, "height": hw, "batch_per_gpu": B,
+                          "global_batch": B * world, "parallelism": f"image-sharded x{world}, no collective",
+                          "weights": "random-init (reference init law), BN folded", "conv_gflop_per_image": flops_img / 1e9,
+                          "l2_policy": "per-step working set (>20 GB of activations at batch 64) far exceeds the 126 MB L2; "
+                                       "no explicit flush"},
+               "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "kernels_per_step": net.kernels_per_forward(),
+               "roofline": roof, "cpu_baseline": cpu}
+        print(json.dumps(out))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

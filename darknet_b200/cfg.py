@@ -151,6 +151,24 @@ def synth_weights(text: str, seed: int = 42):
     return out
 
 
+def shift_head_objectness(text, weights, bias, gain=None):
+    """Sparse-detection regime: head weights scaled by `gain` so the logits spread like a trained
+    net's, objectness bias shifted so only a few cells pass."""
+    _, layers = walk_shapes(text)
+    for L in layers:
+        if L.kind in ("yolo", "Gaussian_yolo"):
+            conv = layers[L.index - 1]
+            gaussian = L.kind == "Gaussian_yolo"
+            classes = int(L.opts.get("classes", 20))
+            E = classes + (9 if gaussian else 5)
+            if gain is not None:
+                weights[conv.index]["weights"] *= np.float32(gain)
+            b = weights[conv.index]["biases"]
+            for a in range(conv.n // E):
+                if bias is not None:
+                    b[a * E + (8 if gaussian else 4)] = bias
+
+
 def write_weights(path: str, text: str, weights: dict, seen: int = 0):
     _, layers = walk_shapes(text)
     with open(path, "wb") as f:

@@ -37,23 +37,148 @@ struct ConvParams {
   int Ho, Wo, stride, pad, dil;
   const float* bias;   // padded to n_tiles*block_n
   const float* scale;  // same padding, or nullptr
-  void* y;
-  long long ldy;
   int y_f32;
+  int chunk;           // output columns per TMA store box: 64 or 32 (bf16), 32 (fp32)
   const __nv_bfloat16* res;
   long long ldres;
   int act, act2;
   uint32_t tmem_cols;
 };
 
+constexpr int kStageOutBytes = 4096;  // one epilogue staging buffer: 32 rows x 128 B (or 32 x 64 B)
+constexpr int kEpiWarps = 4;
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+template <int ACT>
+__device__ __forceinline__ float act_ct(float x) {
+  if (ACT == YC_LINEAR) return x;
+  if (ACT == YC_LEAKY) return x > 0.f ? x : 0.1f * x;
+  if (ACT == YC_MISH) return act_mish(x);
+  if (ACT == YC_LOGISTIC) return act_logistic(x);
+  if (ACT == YC_SWISH) return x * act_logistic(x);
+  if (ACT == YC_RELU) return x > 0.f ? x : 0.f;
+  return x;
+}
+
+// Epilogue of one warp (TMEM lane quadrant `quad`) over all tiles of this CTA:
+//   tcgen05.ld 32 columns -> *scale + bias -> act -> (+residual -> act2) -> bf16/fp32 -> swizzled smem ->
+//   one TMA store per 32-row x `chunk`-column box (coalesced 128 B rows; M / channel tails clipped by the map).
+template <int ACT>
+__device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtensorMap* tmap_y, uint32_t tmem_base,
+                                              uint32_t tfull0, uint32_t tempty0, uint32_t stage_base, int quad,
+                                              int lane, int total_tiles) {
+  const int elt = p.y_f32 ? 4 : 2;
+  const uint32_t row_bytes = (uint32_t)(p.chunk * elt);  // 128 or 64
+  const uint32_t smask = row_bytes == 128 ? 7u : 3u;
+  const int groups = p.chunk / 32;                        // 32-column TMEM loads per chunk
+  int it = 0;
+  uint32_t buf = 0;
+  for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+    const int acc = it & 1;
+    const uint32_t acc_phase = (it >> 1) & 1;
+    const int m0 = (t / p.n_tiles) * kBlockM;
+    const int n0 = (t % p.n_tiles) * p.block_n;
+    const int row0 = m0 + quad * 32;
+    const long long row = (long long)row0 + lane;
+    const bool row_ok = row < p.M;
+    ptx::mbar_wait(tfull0 + 8u * acc, acc_phase);
+    ptx::tc_fence_after();
+    const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * p.block_n;
+    int n_chunks = 0;
+    for (int c0 = 0; c0 < p.block_n && n0 + c0 < p.n_store; c0 += p.chunk) ++n_chunks;
+    for (int ci = 0; ci < n_chunks; ++ci) {
+      const int c0 = ci * p.chunk;
+      const uint32_t sbuf = stage_base + buf * kStageOutBytes;
+      // the TMA store issued two chunks ago from this buffer must have finished reading it
+      if (lane == 0) ptx::tma_store_wait_read<1>();
+      __syncwarp();
+      for (int g = 0; g < groups; ++g) {
+        const int col0 = n0 + c0 + g * 32;
+        uint32_t r[32];
+        ptx::tmem_ld_32x32b_x32(t_row + c0 + g * 32, r);
+        // residual rows are fetched while the TMEM load is in flight
+        uint4 rq[4];
+        const bool has_res = p.res != nullptr;
+        if (has_res) {
+          const __nv_bfloat16* rp = p.res + row * p.ldres + col0;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            rq[j] = make_uint4(0, 0, 0, 0);
+            if (row_ok && col0 + j * 8 + 8 <= p.n_store) rq[j] = __ldg(reinterpret_cast<const uint4*>(rp + j * 8));
+          }
+        }
+        ptx::tmem_ld_wait();
+        if (ci == n_chunks - 1 && g == groups - 1) {  // accumulator fully read: hand it back to the MMA warp
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(tempty0 + 8u * acc);
+        }
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+          float4 s4 = make_float4(1.f, 1.f, 1.f, 1.f);
+          if (p.scale) s4 = __ldg(reinterpret_cast<const float4*>(p.scale + col0 + j));
+          v[j + 0] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 0]), s4.x, b4.x));
+          v[j + 1] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 1]), s4.y, b4.y));
+          v[j + 2] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 2]), s4.z, b4.z));
+          v[j + 3] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 3]), s4.w, b4.w));
+        }
+        if (has_res) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rq[j]);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 f = __bfloat1622float2(h[e]);
+              v[j * 8 + 2 * e] += f.x;
+              v[j * 8 + 2 * e + 1] += f.y;
+            }
+          }
+          if (p.act2 != YC_LINEAR) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act2);
+          }
+        }
+        // registers -> swizzled staging tile (row = lane): conflict-free 16-byte stores
+        const uint32_t rowoff = (uint32_t)lane * row_bytes;
+        if (p.y_f32) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint32_t o = rowoff + (uint32_t)j * 16u;  // chunk == 32 columns of fp32 == one 128 B row
+            o ^= ((o >> 7) & smask) << 4;
+            ptx::st_shared_v4(sbuf + o, __float_as_uint(v[4 * j]), __float_as_uint(v[4 * j + 1]),
+                              __float_as_uint(v[4 * j + 2]), __float_as_uint(v[4 * j + 3]));
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint32_t o = rowoff + (uint32_t)(g * 4 + j) * 16u;
+            o ^= ((o >> 7) & smask) << 4;
+            ptx::st_shared_v4(sbuf + o, pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
+                              pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+          }
+        }
+      }
+      ptx::fence_proxy_async();  // make the generic-proxy smem writes visible to the TMA engine
+      __syncwarp();
+      if (lane == 0 && row0 < p.M) {
+        ptx::tma_store_2d(tmap_y, sbuf, n0 + c0, row0);
+        ptx::tma_store_commit();
+      }
+      buf ^= 1u;
+    }
+  }
+  if (lane == 0) ptx::tma_store_wait<0>();  // smem must stay valid until the last store has read it
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                  const ConvParams p) {
+                  const __grid_constant__ CUtensorMap tmap_y, const ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment: required by the 128B swizzle atom (8 rows x 128 B)
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -61,7 +186,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const uint32_t b_bytes = ((uint32_t)(p.block_n * p.block_k * 2) + 1023u) & ~1023u;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t tx_bytes = a_bytes + (uint32_t)(p.block_n * p.block_k * 2);
-  const uint32_t bar_base = smem_base + p.stages * stage_bytes;  // 8-byte aligned
+  const uint32_t out_base = smem_base + p.stages * stage_bytes;           // 1024-aligned
+  const uint32_t bar_base = out_base + kEpiWarps * 2 * kStageOutBytes;    // 8-byte aligned
   // barrier map: full[s] @ +8s, empty[s] @ +8(kMaxStages+s), tmem_full[2], tmem_empty[2], tmem ptr
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
@@ -75,13 +201,14 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   if (threadIdx.x == 0) {
     ptx::prefetch_tmap(&tmap_a);
     ptx::prefetch_tmap(&tmap_b);
+    ptx::prefetch_tmap(&tmap_y);
     for (int s = 0; s < p.stages; ++s) {
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), 1);
     }
     for (int a = 0; a < 2; ++a) {
       ptx::mbar_init(tfull_bar(a), 1);
-      ptx::mbar_init(tempty_bar(a), 4);  // one arrival per epilogue warp
+      ptx::mbar_init(tempty_bar(a), kEpiWarps);  // one arrival per epilogue warp
     }
     ptx::fence_barrier_init();
   }
@@ -164,83 +291,14 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   } else if (warp >= 2) {
     // ===================== epilogue =====================
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
-    int it = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-      const int acc = it & 1;
-      const uint32_t acc_phase = (it >> 1) & 1;
-      const int m0 = (t / p.n_tiles) * kBlockM;
-      const int n0 = (t % p.n_tiles) * p.block_n;
-      const long long row = (long long)m0 + quad * 32 + lane;
-      const bool row_ok = row < p.M;
-      ptx::mbar_wait(tfull_bar(acc), acc_phase);
-      ptx::tc_fence_after();
-      const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * p.block_n;
-      for (int c0 = 0; c0 < p.block_n; c0 += 32) {
-        const int col0 = n0 + c0;
-        if (col0 >= p.n_store) break;  // warp-uniform
-        uint32_t r[32];
-        ptx::tmem_ld_32x32b_x32(t_row + c0, r);
-        ptx::tmem_ld_wait();
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-          float4 s4 = make_float4(1.f, 1.f, 1.f, 1.f);
-          if (p.scale) s4 = __ldg(reinterpret_cast<const float4*>(p.scale + col0 + j));
-          v[j + 0] = fmaf(__uint_as_float(r[j + 0]), s4.x, b4.x);
-          v[j + 1] = fmaf(__uint_as_float(r[j + 1]), s4.y, b4.y);
-          v[j + 2] = fmaf(__uint_as_float(r[j + 2]), s4.z, b4.z);
-          v[j + 3] = fmaf(__uint_as_float(r[j + 3]), s4.w, b4.w);
-        }
-        if (p.act != YC_LINEAR) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act);
-        }
-        if (p.res != nullptr && row_ok) {
-          const __nv_bfloat16* rp = p.res + row * p.ldres + col0;
-#pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            if (col0 + j + 8 <= p.n_store) {
-              const uint4 q = __ldg(reinterpret_cast<const uint4*>(rp + j));
-              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float2 f = __bfloat1622float2(h[e]);
-                v[j + 2 * e] += f.x;
-                v[j + 2 * e + 1] += f.y;
-              }
-            }
-          }
-          if (p.act2 != YC_LINEAR) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act2);
-          }
-        }
-        if (row_ok) {
-          if (p.y_f32) {
-            float* yp = reinterpret_cast<float*>(p.y) + row * p.ldy + col0;
-#pragma unroll
-            for (int j = 0; j < 32; j += 4)
-              if (col0 + j + 4 <= p.n_store)
-                *reinterpret_cast<float4*>(yp + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-          } else {
-            __nv_bfloat16* yp = reinterpret_cast<__nv_bfloat16*>(p.y) + row * p.ldy + col0;
-#pragma unroll
-            for (int j = 0; j < 32; j += 8)
-              if (col0 + j + 8 <= p.n_store) {
-                uint4 q;
-                q.x = pack_bf16x2(v[j + 0], v[j + 1]);
-                q.y = pack_bf16x2(v[j + 2], v[j + 3]);
-                q.z = pack_bf16x2(v[j + 4], v[j + 5]);
-                q.w = pack_bf16x2(v[j + 6], v[j + 7]);
-                *reinterpret_cast<uint4*>(yp + j) = q;
-              }
-          }
-        }
-      }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(tempty_bar(acc));
+    const uint32_t stage_base = out_base + (uint32_t)(warp - 2) * 2u * kStageOutBytes;
+    switch (p.act) {
+      case YC_LEAKY: epilogue_role<YC_LEAKY>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
+      case YC_MISH: epilogue_role<YC_MISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
+      case YC_LINEAR: epilogue_role<YC_LINEAR>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
+      case YC_LOGISTIC: epilogue_role<YC_LOGISTIC>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
+      case YC_SWISH: epilogue_role<YC_SWISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
+      default: epilogue_role<YC_RELU>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
     }
   }
 
@@ -274,7 +332,7 @@ __global__ void pack_weights_kernel(const float* __restrict__ w, int out_c, int 
 using namespace yc;
 
 struct yc_conv_plan {
-  CUtensorMap tmap_a, tmap_b;
+  CUtensorMap tmap_a, tmap_b, tmap_y;
   ConvParams p;
   float* bias_pad = nullptr;
   float* scale_pad = nullptr;
@@ -396,17 +454,20 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
   const uint32_t a_bytes = kBlockM * p.block_k * 2;
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
   const uint32_t stage_bytes = a_bytes + b_bytes;
-  const uint32_t smem_budget = 227 * 1024 - 1024 /*align slack*/ - 512 /*barriers*/;
+  const uint32_t out_stage = kEpiWarps * 2 * kStageOutBytes;
+  const uint32_t smem_budget = 227 * 1024 - 1024 /*align slack*/ - 512 /*barriers*/ - out_stage;
+  // as deep as shared memory allows: the producer runs ahead across tiles, so the ring depth is the amount of
+  // HBM traffic in flight per SM (what the memory-bound 1x1 layers live on)
   p.stages = std::min<int>(kMaxStages, smem_budget / stage_bytes);
-  p.stages = std::min(p.stages, std::max(2, p.taps * p.cchunks * 2));
   YC_REQUIRE(p.stages >= 2, "tile does not fit shared memory");
-  pl->smem = (size_t)p.stages * stage_bytes + 1024 + 512;
+  pl->smem = (size_t)p.stages * stage_bytes + out_stage + 1024 + 512;
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * p.block_n)) cols <<= 1;
   p.tmem_cols = cols;
   p.act = d->activation;
   p.act2 = d->residual_activation;
-  p.y = y->ptr; p.ldy = y->ldc; p.y_f32 = (y->dtype == YC_F32);
+  p.y_f32 = (y->dtype == YC_F32);
+  p.chunk = p.y_f32 ? 32 : (p.block_n % 64 == 0 ? 64 : 32);
   p.res = residual ? (const __nv_bfloat16*)residual->ptr : nullptr;
   p.ldres = residual ? residual->ldc : 0;
 
@@ -472,6 +533,25 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
     return YC_ERR_CUDA;
   }
 
+  {
+    // output map: [M rows][n_store columns] with the view's pixel pitch; box = 32 rows x chunk columns, swizzled
+    // like the staging tile the epilogue writes.  Rows >= M and columns >= n_store are clipped by the TMA engine.
+    const int elt_b = p.y_f32 ? 4 : 2;
+    cuuint64_t dims[2] = {(cuuint64_t)p.n_store, (cuuint64_t)p.M};
+    cuuint64_t strides[1] = {(cuuint64_t)y->ldc * elt_b};
+    cuuint32_t box[2] = {(cuuint32_t)p.chunk, 32};
+    cuuint32_t estr[2] = {1, 1};
+    const CUtensorMapSwizzle oswz = (p.chunk * elt_b == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    cr = g_encode_tiled(&pl->tmap_y, p.y_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                        y->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, oswz,
+                        CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cr != CUDA_SUCCESS) {
+      set_error("yc_conv_plan_create: output tensor map encode failed (CUresult %d, c=%d ldc=%d)", (int)cr, p.n_store, y->ldc);
+      yc_conv_plan_destroy(pl);
+      return YC_ERR_CUDA;
+    }
+  }
+
   pl->grid = (int)std::min<long long>((long long)p.m_tiles * p.n_tiles, sms);
   static bool attr_set = false;
   if (!attr_set) {
@@ -497,7 +577,7 @@ extern "C" int yc_conv_plan_destroy(yc_conv_plan* pl) {
 
 extern "C" int yc_conv_fprop(const yc_conv_plan* pl, void* stream) {
   YC_REQUIRE(pl, "yc_conv_fprop: null plan");
-  conv_fprop_kernel<<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->p);
+  conv_fprop_kernel<<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->p);
   YC_LAUNCH_CHECK();
   return YC_OK;
 }

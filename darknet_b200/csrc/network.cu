@@ -731,7 +731,8 @@ extern "C" float* yc_network_predict(yc_network* net, const float* input_host) {
   if (!net->finalized && yc_network_finalize(net)) return nullptr;
   const size_t in_bytes = (size_t)net->batch * net->c * net->h * net->w * 4;
   // network_kernels.cu:513-514: memcpy into the pinned staging buffer, then H2D
-  memcpy(net->input_pinned, input_host, in_bytes);
+  // (a caller that produced its batch directly in yc_network_input_buffer() skips the staging copy)
+  if (input_host != net->input_pinned) memcpy(net->input_pinned, input_host, in_bytes);
   if (cudaMemcpyAsync(net->input_dev, net->input_pinned, in_bytes, cudaMemcpyHostToDevice, net->stream) != cudaSuccess) {
     set_error("yc_network_predict: H2D failed: %s", cudaGetErrorString(cudaGetLastError()));
     return nullptr;
@@ -757,6 +758,12 @@ extern "C" float* yc_network_predict(yc_network* net, const float* input_host) {
   if (Z.type == L_YOLO || Z.type == L_GYOLO) last = Z.dec_host;
   if (!last) last = net->input_pinned;  // non-YOLO tail: callers use yc_network_layer_output
   return last;
+}
+
+extern "C" float* yc_network_input_buffer(yc_network* net) {
+  if (!net) return nullptr;
+  if (!net->finalized && yc_network_finalize(net)) return nullptr;
+  return net->input_pinned;
 }
 
 extern "C" const float* yc_network_yolo_output(yc_network* net, int layer) {
@@ -983,15 +990,17 @@ extern "C" int yc_network_detect(yc_network* net, float thresh, float nms_thresh
   const int R = 7 + classes;
   const int B = net->batch;
   if (!net->det_regions) {
-    net->det_cap = 4096;        // rows kept per (head, image)
-    net->det_dense_cap = B * 1024;
+    int max_cells = 0;
+    for (int li : net->yolo_layers) max_cells = std::max(max_cells, net->layers[li].n * net->layers[li].out_h * net->layers[li].out_w);
+    net->det_cap = std::min(max_cells, 16384);  // rows kept per (head, image); more is reported as an error
+    net->det_dense_cap = B * 256;
     net->det_R = R;
     NET_CUDA(cudaMalloc(&net->det_regions, (size_t)heads * B * net->det_cap * R * 4));
     NET_CUDA(cudaMalloc(&net->det_counts, (size_t)heads * B * 4));
     NET_CUDA(cudaMalloc(&net->det_dense, (size_t)net->det_dense_cap * R * 4));
     NET_CUDA(cudaMalloc(&net->det_img_counts, (size_t)B * 4));
     NET_CUDA(cudaHostAlloc(&net->det_host, (size_t)net->det_dense_cap * R * 4, cudaHostAllocDefault));
-    NET_CUDA(cudaHostAlloc(&net->det_img_counts_host, (size_t)B * 4, cudaHostAllocDefault));
+    NET_CUDA(cudaHostAlloc(&net->det_img_counts_host, (size_t)(heads + 1) * B * 4, cudaHostAllocDefault));
   }
   cudaStream_t st = net->stream;
   for (int hd = 0; hd < heads; ++hd) {
@@ -1006,12 +1015,26 @@ extern "C" int yc_network_detect(yc_network* net, float thresh, float nms_thresh
                               net->det_img_counts, net->det_dense_cap, st);
   if (rc) return rc;
   NET_CUDA(cudaMemcpyAsync(net->det_img_counts_host, net->det_img_counts, (size_t)B * 4, cudaMemcpyDeviceToHost, st));
+  NET_CUDA(cudaMemcpyAsync(net->det_img_counts_host + B, net->det_counts, (size_t)heads * B * 4, cudaMemcpyDeviceToHost, st));
   NET_CUDA(cudaStreamSynchronize(st));
   long long tot = 0;
   for (int b = 0; b < B; ++b) tot += net->det_img_counts_host[b];
-  if (tot > net->det_dense_cap) {
-    set_error("yc_network_detect: %lld detections exceed the dense capacity %d (raise thresh)", tot, net->det_dense_cap);
-    return YC_ERR_ARG;
+  for (int i = 0; i < heads * B; ++i)
+    if (net->det_img_counts_host[B + i] > net->det_cap) {
+      set_error("yc_network_detect: %d candidates in one image of head %d exceed the per-head capacity %d (raise thresh)",
+                net->det_img_counts_host[B + i], i / B, net->det_cap);
+      return YC_ERR_ARG;
+    }
+  if (tot > net->det_dense_cap) {  // grow the dense buffers and gather again (the per-head regions are intact)
+    cudaFree(net->det_dense);
+    cudaFreeHost(net->det_host);
+    net->det_dense = nullptr; net->det_host = nullptr;
+    net->det_dense_cap = (int)std::min<long long>(tot + tot / 2, (long long)heads * B * net->det_cap);
+    NET_CUDA(cudaMalloc(&net->det_dense, (size_t)net->det_dense_cap * R * 4));
+    NET_CUDA(cudaHostAlloc(&net->det_host, (size_t)net->det_dense_cap * R * 4, cudaHostAllocDefault));
+    rc = launch_yolo_gather(net->det_regions, net->det_counts, heads, B, net->det_cap, R, net->det_dense,
+                            net->det_img_counts, net->det_dense_cap, st);
+    if (rc) return rc;
   }
   if (tot > 0) {
     NET_CUDA(cudaMemcpyAsync(net->det_host, net->det_dense, (size_t)tot * R * 4, cudaMemcpyDeviceToHost, st));

@@ -89,6 +89,7 @@ _SIGS = {
     "yc_network_layer_info": (C.c_int, [_P, C.c_int, C.c_int]),
     "yc_network_flops": (C.c_double, [_P]),
     "yc_network_predict": (_P, [_P, _P]),
+    "yc_network_input_buffer": (_P, [_P]),
     "yc_network_forward": (C.c_int, [_P, _P, _P]),
     "yc_network_layer_output": (C.c_int, [_P, C.c_int, _P]),
     "yc_network_yolo_output": (_P, [_P, C.c_int]),

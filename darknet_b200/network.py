@@ -69,16 +69,51 @@ class Network:
             pass
 
 
-def LoadNetwork(cfg, weights=None, batch=0, flags=L.NET_DEFAULT, cfg_is_text=False) -> Network:
+def LoadNetwork(cfg, weights=None, batch=0, flags=L.NET_DEFAULT, cfg_is_text=False, finalize=True) -> Network:
     """LoadNetwork (parser.cpp:1852-1875): parse cfg, load .weights, fuse BN, plan kernels.
     `batch<=0` keeps the cfg's batch; the reference forces 1 for inference (parser.cpp:1114-1115)."""
     h = C.c_void_p()
     fn = L.lib().yc_network_load_text if cfg_is_text else L.lib().yc_network_load
     L.check(fn(C.byref(h), cfg.encode(), weights.encode() if weights else None, batch, flags), "LoadNetwork")
     net = Network(h)
-    if not weights:
+    if not weights and finalize:
         L.check(L.lib().yc_network_finalize(h), "yc_network_finalize")
     return net
+
+
+def SetConvWeights(net: Network, layer: int, weights, biases, scales=None, rolling_mean=None, rolling_variance=None):
+    """Overwrite one conv layer's parameters from numpy (reference layouts: OIHW weights); call Finalize after."""
+    def p(a):
+        if a is None:
+            return None
+        a = np.ascontiguousarray(a, np.float32)
+        keep.append(a)
+        return a.ctypes.data_as(C.c_void_p)
+    keep = []
+    L.check(L.lib().yc_network_set_conv_weights(net.h, layer, p(weights), p(biases), p(scales), p(rolling_mean),
+                                                p(rolling_variance)), "yc_network_set_conv_weights")
+
+
+def Finalize(net: Network):
+    L.check(L.lib().yc_network_finalize(net.h), "yc_network_finalize")
+
+
+def LoadSynthetic(cfg_text, weights: dict, batch=0, flags=L.NET_DEFAULT) -> Network:
+    """LoadNetwork from a cfg string and a {layer: {weights,biases,scales,rolling_mean,rolling_variance}} dict
+    (darknet_b200.cfg.synth_weights) without going through a .weights file."""
+    net = LoadNetwork(cfg_text, None, batch, flags, cfg_is_text=True, finalize=False)
+    for i, d in weights.items():
+        SetConvWeights(net, i, d["weights"], d["biases"], d.get("scales"), d.get("rolling_mean"), d.get("rolling_variance"))
+    Finalize(net)
+    return net
+
+
+def InputBuffer(net: Network):
+    """numpy view of the library's pinned input staging buffer [batch,c,h,w] (net->input_pinned_cpu)."""
+    p = L.lib().yc_network_input_buffer(net.h)
+    if not p:
+        raise L.YcError("yc_network_input_buffer: " + L.lib().yc_last_error().decode())
+    return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=(net.batch, net.c, net.hh, net.w))
 
 
 def FreeNetwork(net: Network):
@@ -88,7 +123,8 @@ def FreeNetwork(net: Network):
 def NetworkPredict(net: Network, x: np.ndarray):
     """NetworkPredict (network.cpp:412-430): x = host fp32 NCHW [batch,c,h,w]; synchronous.  Returns a numpy
     view of the last layer's host output (layer-owned, valid until the next call)."""
-    x = np.ascontiguousarray(x, np.float32)
+    if not (x.dtype == np.float32 and x.flags["C_CONTIGUOUS"]):
+        x = np.ascontiguousarray(x, np.float32)
     assert x.size == net.batch * net.c * net.hh * net.w, "input size != batch*c*h*w"
     p = L.lib().yc_network_predict(net.h, x.ctypes.data_as(C.c_void_p))
     if not p:

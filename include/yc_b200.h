@@ -195,6 +195,9 @@ YC_API double yc_network_flops(const yc_network* net);               /* sum 2*nw
  * [batch*c*h*w] (borrowed), returns the host buffer of the last layer's output (layer-owned, valid until the
  * next call) or NULL on error.  Synchronous like the reference. */
 YC_API float* yc_network_predict(yc_network* net, const float* input_host);
+/* net->input_pinned_cpu (network_kernels.cu:505-513): the library's pinned staging buffer of batch*c*h*w floats.
+ * A producer may fill it in place and pass it to yc_network_predict, which then skips its staging memcpy. */
+YC_API float* yc_network_input_buffer(yc_network* net);
 /* ForwardNetworkGpu (network_kernels.cu:45-114) on an input already resident on the device
  * (fp32 NCHW, the reference's net->input_state_gpu layout).  Asynchronous on `stream`. */
 YC_API int yc_network_forward(yc_network* net, const float* input_dev_nchw, void* stream);

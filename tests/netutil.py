@@ -8,6 +8,7 @@ import numpy as np
 
 from darknet_b200 import cfg as cfgmod
 from darknet_b200 import cfgs
+from darknet_b200.cfg import shift_head_objectness  # noqa: F401
 
 _TMP = tempfile.mkdtemp(prefix="yc_nets_")
 
@@ -26,24 +27,6 @@ def materialise(name, seed=42, head_bias=None, head_gain=None, **kw):
             shift_head_objectness(text, weights, head_bias, head_gain)
         cfgmod.write_weights(wpath, text, weights)
     return text, cpath, wpath
-
-
-def shift_head_objectness(text, weights, bias, gain=None):
-    """Sparse-detection regime: head weights scaled by `gain` so the logits spread like a trained
-    net's, objectness bias shifted so only a few cells pass."""
-    _, layers = cfgmod.walk_shapes(text)
-    for L in layers:
-        if L.kind in ("yolo", "Gaussian_yolo"):
-            conv = layers[L.index - 1]
-            gaussian = L.kind == "Gaussian_yolo"
-            classes = int(L.opts.get("classes", 20))
-            E = classes + (9 if gaussian else 5)
-            if gain is not None:
-                weights[conv.index]["weights"] *= np.float32(gain)
-            b = weights[conv.index]["biases"]
-            for a in range(conv.n // E):
-                if bias is not None:
-                    b[a * E + (8 if gaussian else 4)] = bias
 
 
 def rel_to_max(a, b):
