@@ -193,8 +193,8 @@ def main():
     B = args.batch
     text = cfgs.CONFIGS[cfgname](w=hw, h=hw)
     weights = cfgmod.synth_weights(text)
-    # sparse-detection regime like a trained detector: spread head logits, objectness bias -7
-    cfgmod.shift_head_objectness(text, weights, -7.0, 40.0)
+    # sparse-detection regime like a trained detector: spread head logits, objectness bias -6
+    cfgmod.shift_head_objectness(text, weights, -6.0, 40.0)
     flags = L.NET_DEFAULT & ~L.NET_PULL_HEADS
     net = N.LoadSynthetic(text, weights, batch=B, flags=flags)
     del weights

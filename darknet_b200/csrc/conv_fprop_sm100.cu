@@ -13,10 +13,10 @@
 //   tcgen05.mma reads through shared-memory descriptors.  Accumulators live in TMEM (two buffers, so the
 //   epilogue of tile i overlaps the main loop of tile i+1).
 //
-// CTA = 192 threads, persistent over tiles (grid = min(tiles, #SM)):
+// CTA = 320 threads, persistent over tiles (grid = min(tiles, #SM)):
 //   warp 0 / lane 0 : TMA producer        (full/empty mbarrier ring, `stages` deep)
 //   warp 1 / lane 0 : tcgen05.mma issuer  (UMMA 128 x block_n x 16, bf16 -> fp32)
-//   warps 2..5      : epilogue            (tcgen05.ld -> *scale +bias -> act -> +residual -> act2 -> store)
+//   warps 2..9      : epilogue            (tcgen05.ld -> *scale +bias -> act -> +residual -> act2 -> store)
 #include <cuda.h>
 #include <algorithm>
 
@@ -27,7 +27,7 @@ namespace yc {
 
 constexpr int kBlockM = 128;
 constexpr int kMaxStages = 16;
-constexpr int kThreads = 192;
+constexpr int kThreads = 64 + 32 * 16;  // producer warp, MMA warp, 16 epilogue warps
 
 struct ConvParams {
   int M, N, n_store;
@@ -43,10 +43,13 @@ struct ConvParams {
   long long ldres;
   int act, act2;
   uint32_t tmem_cols;
+  int epi_sets;        // 1, 2 or 4 groups of epilogue warps working on different tiles at the same time
+  int nacc;            // TMEM accumulator buffers in use (>= epi_sets)
 };
 
-constexpr int kStageOutBytes = 4096;  // one epilogue staging buffer: 32 rows x 128 B (or 32 x 64 B)
-constexpr int kEpiWarps = 4;
+constexpr int kStageOutBytes = 2048;  // one epilogue staging buffer: 32 rows x 64 B
+constexpr int kEpiWarps = 16;         // four per TMEM lane quadrant == four per scheduler: enough to hide ALU/MUFU latency
+constexpr int kMaxAcc = 4;            // TMEM accumulator buffers
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
@@ -56,7 +59,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 template <int ACT>
 __device__ __forceinline__ float act_ct(float x) {
   if (ACT == YC_LINEAR) return x;
-  if (ACT == YC_LEAKY) return x > 0.f ? x : 0.1f * x;
+  if (ACT == YC_LEAKY) return fmaxf(x, 0.1f * x);
   if (ACT == YC_MISH) return act_mish(x);
   if (ACT == YC_LOGISTIC) return act_logistic(x);
   if (ACT == YC_SWISH) return x * act_logistic(x);
@@ -64,113 +67,125 @@ __device__ __forceinline__ float act_ct(float x) {
   return x;
 }
 
-// Epilogue of one warp (TMEM lane quadrant `quad`) over all tiles of this CTA:
+// Epilogue of one warp over all tiles of this CTA.  The warp owns TMEM lane quadrant `quad` (rows) and every
+// second 32-column group (`half`):
 //   tcgen05.ld 32 columns -> *scale + bias -> act -> (+residual -> act2) -> bf16/fp32 -> swizzled smem ->
-//   one TMA store per 32-row x `chunk`-column box (coalesced 128 B rows; M / channel tails clipped by the map).
+//   TMA store of a 32-row x 64-byte box (bf16: 32 columns, fp32: 16 columns); M / channel tails are clipped by
+//   the tensor map.  No inter-warp synchronisation: each warp has its own two staging buffers.
 template <int ACT>
 __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtensorMap* tmap_y, uint32_t tmem_base,
-                                              uint32_t tfull0, uint32_t tempty0, uint32_t stage_base, int quad,
-                                              int lane, int total_tiles) {
-  const int elt = p.y_f32 ? 4 : 2;
-  const uint32_t row_bytes = (uint32_t)(p.chunk * elt);  // 128 or 64
-  const uint32_t smask = row_bytes == 128 ? 7u : 3u;
-  const int groups = p.chunk / 32;                        // 32-column TMEM loads per chunk
+                                              uint32_t tfull0, uint32_t tempty0, uint32_t sbuf, int quad,
+                                              int slot, int lane, int total_tiles) {
+  // Narrow tiles (block_n 32 / 64) have fewer 32-column groups than the four warps of a quadrant: the warps then
+  // split into `epi_sets` sets that take alternate tiles, so all sixteen stay busy.
+  const int wps = 4 / p.epi_sets;        // warps of one quadrant working on the same tile
+  const int set = slot / wps, sub = slot - set * wps;
   int it = 0;
-  uint32_t buf = 0;
+  const uint32_t rowoff = (uint32_t)lane * 64u;
+  const uint32_t swz = ((rowoff >> 7) & 3u) << 4;  // 64B swizzle: 16-byte chunk index ^= (row / 2) % 4
+  const bool has_res = p.res != nullptr;
   for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-    const int acc = it & 1;
-    const uint32_t acc_phase = (it >> 1) & 1;
+    if (it % p.epi_sets != set) continue;
+    const int acc = it % p.nacc;
+    const uint32_t acc_phase = (it / p.nacc) & 1;
     const int m0 = (t / p.n_tiles) * kBlockM;
     const int n0 = (t % p.n_tiles) * p.block_n;
     const int row0 = m0 + quad * 32;
     const long long row = (long long)row0 + lane;
     const bool row_ok = row < p.M;
+    const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * p.block_n;
+    int n_groups = (min(p.block_n, p.n_store - n0) + 31) >> 5;  // 32-column groups with something to store
+    // this warp's groups: sub, sub+wps, ...
+    int last_g = -1;
+    for (int g = sub; g < n_groups; g += wps) last_g = g;
     ptx::mbar_wait(tfull0 + 8u * acc, acc_phase);
     ptx::tc_fence_after();
-    const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * p.block_n;
-    int n_chunks = 0;
-    for (int c0 = 0; c0 < p.block_n && n0 + c0 < p.n_store; c0 += p.chunk) ++n_chunks;
-    for (int ci = 0; ci < n_chunks; ++ci) {
-      const int c0 = ci * p.chunk;
-      const uint32_t sbuf = stage_base + buf * kStageOutBytes;
-      // the TMA store issued two chunks ago from this buffer must have finished reading it
-      if (lane == 0) ptx::tma_store_wait_read<1>();
+    if (last_g < 0) {  // nothing to do in this tile: still hand the accumulator back
+      ptx::tc_fence_before();
       __syncwarp();
-      for (int g = 0; g < groups; ++g) {
-        const int col0 = n0 + c0 + g * 32;
-        uint32_t r[32];
-        ptx::tmem_ld_32x32b_x32(t_row + c0 + g * 32, r);
-        // residual rows are fetched while the TMEM load is in flight
-        uint4 rq[4];
-        const bool has_res = p.res != nullptr;
-        if (has_res) {
-          const __nv_bfloat16* rp = p.res + row * p.ldres + col0;
+      if (lane == 0) ptx::mbar_arrive(tempty0 + 8u * acc);
+      continue;
+    }
+    for (int g = sub; g < n_groups; g += wps) {
+      const int col0 = n0 + g * 32;
+      uint32_t r[32];
+      ptx::tmem_ld_32x32b_x32(t_row + g * 32, r);
+      // residual rows are fetched while the TMEM load is in flight
+      uint4 rq[4];
+      if (has_res) {
+        const __nv_bfloat16* rp = p.res + row * p.ldres + col0;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            rq[j] = make_uint4(0, 0, 0, 0);
-            if (row_ok && col0 + j * 8 + 8 <= p.n_store) rq[j] = __ldg(reinterpret_cast<const uint4*>(rp + j * 8));
+        for (int j = 0; j < 4; ++j) {
+          rq[j] = make_uint4(0, 0, 0, 0);
+          if (row_ok && col0 + j * 8 + 8 <= p.n_store) rq[j] = __ldg(reinterpret_cast<const uint4*>(rp + j * 8));
+        }
+      }
+      ptx::tmem_ld_wait();
+      if (g == last_g) {  // accumulator fully read by this warp: hand it back to the MMA warp
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(tempty0 + 8u * acc);
+      }
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) {
+        const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+        float4 s4 = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (p.scale) s4 = __ldg(reinterpret_cast<const float4*>(p.scale + col0 + j));
+        v[j + 0] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 0]), s4.x, b4.x));
+        v[j + 1] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 1]), s4.y, b4.y));
+        v[j + 2] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 2]), s4.z, b4.z));
+        v[j + 3] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 3]), s4.w, b4.w));
+      }
+      if (has_res) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rq[j]);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = __bfloat1622float2(h[e]);
+            v[j * 8 + 2 * e] += f.x;
+            v[j * 8 + 2 * e + 1] += f.y;
           }
         }
-        ptx::tmem_ld_wait();
-        if (ci == n_chunks - 1 && g == groups - 1) {  // accumulator fully read: hand it back to the MMA warp
-          ptx::tc_fence_before();
+        if (p.act2 != YC_LINEAR) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act2);
+        }
+      }
+      if (!p.y_f32) {
+        if (lane == 0) ptx::tma_store_wait_read<0>();  // this warp's previous store has finished reading `sbuf`
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          ptx::st_shared_v4(sbuf + rowoff + (((uint32_t)j * 16u) ^ swz), pack_bf16x2(v[8 * j], v[8 * j + 1]),
+                            pack_bf16x2(v[8 * j + 2], v[8 * j + 3]), pack_bf16x2(v[8 * j + 4], v[8 * j + 5]),
+                            pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+        ptx::fence_proxy_async();  // generic-proxy smem writes -> visible to the TMA engine
+        __syncwarp();
+        if (lane == 0 && row0 < p.M) {
+          ptx::tma_store_2d(tmap_y, sbuf, col0, row0);
+          ptx::tma_store_commit();
+        }
+      } else {
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {  // fp32: two boxes of 16 columns
+          if (lane == 0) ptx::tma_store_wait_read<0>();
           __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(tempty0 + 8u * acc);
-        }
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-          float4 s4 = make_float4(1.f, 1.f, 1.f, 1.f);
-          if (p.scale) s4 = __ldg(reinterpret_cast<const float4*>(p.scale + col0 + j));
-          v[j + 0] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 0]), s4.x, b4.x));
-          v[j + 1] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 1]), s4.y, b4.y));
-          v[j + 2] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 2]), s4.z, b4.z));
-          v[j + 3] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 3]), s4.w, b4.w));
-        }
-        if (has_res) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
-            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rq[j]);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float2 f = __bfloat1622float2(h[e]);
-              v[j * 8 + 2 * e] += f.x;
-              v[j * 8 + 2 * e + 1] += f.y;
-            }
+            const int e = hh * 16 + j * 4;
+            ptx::st_shared_v4(sbuf + rowoff + (((uint32_t)j * 16u) ^ swz), __float_as_uint(v[e]), __float_as_uint(v[e + 1]),
+                              __float_as_uint(v[e + 2]), __float_as_uint(v[e + 3]));
           }
-          if (p.act2 != YC_LINEAR) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act2);
-          }
-        }
-        // registers -> swizzled staging tile (row = lane): conflict-free 16-byte stores
-        const uint32_t rowoff = (uint32_t)lane * row_bytes;
-        if (p.y_f32) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            uint32_t o = rowoff + (uint32_t)j * 16u;  // chunk == 32 columns of fp32 == one 128 B row
-            o ^= ((o >> 7) & smask) << 4;
-            ptx::st_shared_v4(sbuf + o, __float_as_uint(v[4 * j]), __float_as_uint(v[4 * j + 1]),
-                              __float_as_uint(v[4 * j + 2]), __float_as_uint(v[4 * j + 3]));
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint32_t o = rowoff + (uint32_t)(g * 4 + j) * 16u;
-            o ^= ((o >> 7) & smask) << 4;
-            ptx::st_shared_v4(sbuf + o, pack_bf16x2(v[8 * j], v[8 * j + 1]), pack_bf16x2(v[8 * j + 2], v[8 * j + 3]),
-                              pack_bf16x2(v[8 * j + 4], v[8 * j + 5]), pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
+          ptx::fence_proxy_async();
+          __syncwarp();
+          if (lane == 0 && row0 < p.M && col0 + hh * 16 < p.n_store) {
+            ptx::tma_store_2d(tmap_y, sbuf, col0 + hh * 16, row0);
+            ptx::tma_store_commit();
           }
         }
       }
-      ptx::fence_proxy_async();  // make the generic-proxy smem writes visible to the TMA engine
-      __syncwarp();
-      if (lane == 0 && row0 < p.M) {
-        ptx::tma_store_2d(tmap_y, sbuf, n0 + c0, row0);
-        ptx::tma_store_commit();
-      }
-      buf ^= 1u;
     }
   }
   if (lane == 0) ptx::tma_store_wait<0>();  // smem must stay valid until the last store has read it
@@ -187,13 +202,13 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t tx_bytes = a_bytes + (uint32_t)(p.block_n * p.block_k * 2);
   const uint32_t out_base = smem_base + p.stages * stage_bytes;           // 1024-aligned
-  const uint32_t bar_base = out_base + kEpiWarps * 2 * kStageOutBytes;    // 8-byte aligned
-  // barrier map: full[s] @ +8s, empty[s] @ +8(kMaxStages+s), tmem_full[2], tmem_empty[2], tmem ptr
+  const uint32_t bar_base = out_base + kEpiWarps * kStageOutBytes;        // 8-byte aligned
+  // barrier map: full[s] @ +8s, empty[s] @ +8(kMaxStages+s), tmem_full[4], tmem_empty[4], tmem ptr
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + a); };
-  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + 2 + a); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 4);
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + kMaxAcc + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -206,9 +221,9 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), 1);
     }
-    for (int a = 0; a < 2; ++a) {
+    for (int a = 0; a < kMaxAcc; ++a) {
       ptx::mbar_init(tfull_bar(a), 1);
-      ptx::mbar_init(tempty_bar(a), kEpiWarps);  // one arrival per epilogue warp
+      ptx::mbar_init(tempty_bar(a), kEpiWarps / p.epi_sets);  // one arrival per epilogue warp of the tile's set
     }
     ptx::fence_barrier_init();
   }
@@ -268,8 +283,8 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     uint32_t phase = 0;
     int it = 0;
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-      const int acc = it & 1;
-      const uint32_t acc_phase = (it >> 1) & 1;
+      const int acc = it % p.nacc;
+      const uint32_t acc_phase = (it / p.nacc) & 1;
       ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
       ptx::tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * p.block_n;
@@ -291,14 +306,15 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   } else if (warp >= 2) {
     // ===================== epilogue =====================
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
-    const uint32_t stage_base = out_base + (uint32_t)(warp - 2) * 2u * kStageOutBytes;
+    const uint32_t stage_base = out_base + (uint32_t)(warp - 2) * kStageOutBytes;
+    const int half = (warp - 2) >> 2;  // slot 0..3 within the quadrant
     switch (p.act) {
-      case YC_LEAKY: epilogue_role<YC_LEAKY>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
-      case YC_MISH: epilogue_role<YC_MISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
-      case YC_LINEAR: epilogue_role<YC_LINEAR>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
-      case YC_LOGISTIC: epilogue_role<YC_LOGISTIC>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
-      case YC_SWISH: epilogue_role<YC_SWISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
-      default: epilogue_role<YC_RELU>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, lane, total_tiles); break;
+      case YC_LEAKY: epilogue_role<YC_LEAKY>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
+      case YC_MISH: epilogue_role<YC_MISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
+      case YC_LINEAR: epilogue_role<YC_LINEAR>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
+      case YC_LOGISTIC: epilogue_role<YC_LOGISTIC>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
+      case YC_SWISH: epilogue_role<YC_SWISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
+      default: epilogue_role<YC_RELU>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
     }
   }
 
@@ -454,20 +470,24 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
   const uint32_t a_bytes = kBlockM * p.block_k * 2;
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
   const uint32_t stage_bytes = a_bytes + b_bytes;
-  const uint32_t out_stage = kEpiWarps * 2 * kStageOutBytes;
+  const uint32_t out_stage = kEpiWarps * kStageOutBytes;
   const uint32_t smem_budget = 227 * 1024 - 1024 /*align slack*/ - 512 /*barriers*/ - out_stage;
   // as deep as shared memory allows: the producer runs ahead across tiles, so the ring depth is the amount of
   // HBM traffic in flight per SM (what the memory-bound 1x1 layers live on)
   p.stages = std::min<int>(kMaxStages, smem_budget / stage_bytes);
   YC_REQUIRE(p.stages >= 2, "tile does not fit shared memory");
   pl->smem = (size_t)p.stages * stage_bytes + out_stage + 1024 + 512;
+  const int groups = p.block_n / 32;
+  p.epi_sets = groups >= 4 ? 1 : (groups >= 2 ? 2 : 4);
+  p.nacc = std::max(2, p.epi_sets);
+  if (p.block_n <= 128) p.nacc = 4;  // 4 x 128 columns fit: deeper MMA/epilogue decoupling for free
   uint32_t cols = 32;
-  while (cols < (uint32_t)(2 * p.block_n)) cols <<= 1;
+  while (cols < (uint32_t)(p.nacc * p.block_n)) cols <<= 1;
   p.tmem_cols = cols;
   p.act = d->activation;
   p.act2 = d->residual_activation;
   p.y_f32 = (y->dtype == YC_F32);
-  p.chunk = p.y_f32 ? 32 : (p.block_n % 64 == 0 ? 64 : 32);
+  p.chunk = p.y_f32 ? 16 : 32;  // columns per TMA store box: 64-byte rows
   p.res = residual ? (const __nv_bfloat16*)residual->ptr : nullptr;
   p.ldres = residual ? residual->ldc : 0;
 
@@ -541,7 +561,7 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
     cuuint64_t strides[1] = {(cuuint64_t)y->ldc * elt_b};
     cuuint32_t box[2] = {(cuuint32_t)p.chunk, 32};
     cuuint32_t estr[2] = {1, 1};
-    const CUtensorMapSwizzle oswz = (p.chunk * elt_b == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    const CUtensorMapSwizzle oswz = CU_TENSOR_MAP_SWIZZLE_64B;
     cr = g_encode_tiled(&pl->tmap_y, p.y_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
                         y->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, oswz,
                         CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

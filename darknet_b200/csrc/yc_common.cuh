@@ -48,20 +48,34 @@ int sm_count();
 
 // ---- device-side activation math shared by the conv epilogue and the elementwise kernels ------
 // Formulas follow the reference (activations.h:80-121, activation_kernels.cu:56-79), fp32.
-__device__ __forceinline__ float act_logistic(float x) { return 1.f / (1.f + __expf(-x)); }
+// MUFU wrappers with flush-to-zero: one SASS instruction each (the non-ftz intrinsics add range-scaling code).
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_ftz(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float act_logistic(float x) {
+  // 1/(1+e^-x); the clamp keeps e^-x finite so that rcp never sees inf (activations.h:80)
+  return rcp_ftz(1.f + ex2_ftz(fmaxf(x, -80.f) * -1.4426950408889634f));
+}
 __device__ __forceinline__ float act_mish(float x) {
   // x * tanh(softplus(x)); with n = e^x: tanh(log(1+n)) = n(n+2) / (n(n+2) + 2).
   // The reference's softplus thresholds at +-20 (activations.h:106-113): for x > 20 tanh == 1 in
   // fp32, for x < -20 tanh(e^x) == e^x to fp32 rounding; both limits are what this form gives when
   // x is clamped to 20, so one branch-free expression covers all three cases.
-  float n = __expf(fminf(x, 20.f));
-  float t = n * (n + 2.f);
-  return x * __fdividef(t, t + 2.f);
+  const float n = ex2_ftz(fminf(x, 20.f) * 1.4426950408889634f);
+  const float t = n * (n + 2.f);
+  return x * (t * rcp_ftz(t + 2.f));
 }
 __device__ __forceinline__ float apply_act(float x, int act) {
   switch (act) {
     case YC_LINEAR: return x;
-    case YC_LEAKY: return x > 0.f ? x : 0.1f * x;
+    case YC_LEAKY: return fmaxf(x, 0.1f * x);
     case YC_MISH: return act_mish(x);
     case YC_LOGISTIC: return act_logistic(x);
     case YC_SWISH: return x * act_logistic(x);

@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--shapes", default="all")
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--act", default=None)
     a = ap.parse_args()
     L.check(L.lib().yc_set_device(0), "set_device")
     dev = torch.device("cuda:0")
@@ -38,6 +39,7 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     for nm in names:
         C, N, HW, k, s, act = SHAPES[nm]
+        act = a.act or act
         B = a.batch
         ldc = (C + 7) // 8 * 8
         x = torch.randn((B, HW, HW, ldc), device=dev, dtype=torch.bfloat16)
