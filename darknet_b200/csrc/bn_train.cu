@@ -1,0 +1,395 @@
+// Training-mode batchnorm / bias / activation-gradient passes around the conv GEMMs (NHWC bf16, fp32 math).
+//
+// Replaces, for a convolutional layer in training (convolutional_kernels.cu:252-553, 555-815 and their CPU twins):
+//   forward : fast_mean_gpu / fast_variance_gpu (fused into the conv epilogue, conv_fprop_sm100.cu), the rolling
+//             update, normalize_gpu, scale_bias_gpu, add_bias_gpu, activate_array_ongpu   -> bn_finalize + bn_act_fwd
+//   backward: gradient_array_ongpu, backward_scale_gpu, scale_bias, fast_mean_delta_gpu, fast_variance_delta_gpu,
+//             normalize_delta_gpu (batchnorm_layer.cpp:240-255)                            -> bn_bwd_reduce + bn_bwd_apply
+//             gradient_array_ongpu + backward_bias_gpu for layers without batchnorm       -> bias_act_bwd
+// Numerical semantics follow the reference CPU path.
+// Each pass reads/writes every tensor element once with 16-byte accesses; reductions go registers -> shared-memory
+// atomics -> one global atomic per (block, channel).
+#include <algorithm>
+
+#include "yc_common.cuh"
+
+namespace yc {
+
+struct TView {
+  void* ptr;
+  long long rows;  // n*h*w
+  int c;
+  long long ldc;
+  int f32;
+};
+static inline TView tv(const yc_tensor* t) {
+  return TView{t->ptr, (long long)t->n * t->h * t->w, t->c, t->ldc, t->dtype == YC_F32};
+}
+
+__device__ __forceinline__ void ld8(const TView& t, long long row, int c0, float (&v)[8]) {
+  if (t.f32) {
+    const float* p = reinterpret_cast<const float*>(t.ptr) + row * t.ldc + c0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = (c0 + j < t.c) ? p[j] : 0.f;
+    return;
+  }
+  const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(t.ptr) + row * t.ldc + c0;
+  if (c0 + 8 <= t.ldc) {  // whole 16-byte group lies inside the pixel pitch (pad lanes are readable)
+    const uint4 q = *reinterpret_cast<const uint4*>(p);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(h[e]);
+      v[2 * e] = f.x;
+      v[2 * e + 1] = f.y;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (c0 + j >= t.c) v[j] = 0.f;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = (c0 + j < t.c) ? __bfloat162float(p[j]) : 0.f;
+  }
+}
+// pad_zero: the tensor owns lanes [c, ldc) and wants zeros there (delta buffers feeding the GEMMs)
+__device__ __forceinline__ void st8(const TView& t, long long row, int c0, const float (&v)[8], bool own_pad) {
+  if (t.f32) {
+    float* p = reinterpret_cast<float*>(t.ptr) + row * t.ldc + c0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (c0 + j < t.c) p[j] = v[j];
+    return;
+  }
+  __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(t.ptr) + row * t.ldc + c0;
+  if (c0 + 8 <= t.c || (own_pad && c0 + 8 <= t.ldc)) {
+    uint4 q;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&q);
+#pragma unroll
+    for (int e = 0; e < 4; ++e)
+      h[e] = __floats2bfloat162_rn(c0 + 2 * e < t.c ? v[2 * e] : 0.f, c0 + 2 * e + 1 < t.c ? v[2 * e + 1] : 0.f);
+    *reinterpret_cast<uint4*>(p) = q;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (c0 + j < t.c) p[j] = __float2bfloat16_rn(v[j]);
+  }
+}
+
+// gradient of the activation at pre-activation u (activations.h:152-178, activations.c:412-452).  The reference
+// evaluates leaky/relu/logistic on the post-activation output; those are the same functions of u.
+__device__ __forceinline__ float act_grad(float u, int act) {
+  switch (act) {
+    case YC_LINEAR: return 1.f;
+    case YC_LEAKY: return u > 0.f ? 1.f : .1f;
+    case YC_RELU: return u > 0.f ? 1.f : 0.f;
+    case YC_LOGISTIC: {
+      const float y = 1.f / (1.f + expf(-u));
+      return (1.f - y) * y;
+    }
+    case YC_SWISH: {  // gradient_array_swish: swish + sigmoid*(1-swish)
+      const float s = 1.f / (1.f + expf(-u));
+      const float y = u * s;
+      return y + s * (1.f - y);
+    }
+    case YC_MISH: {  // gradient_array_mish (activations.c:426-452)
+      const float sp = u > 20.f ? u : (u < -20.f ? expf(u) : logf(expf(u) + 1.f));
+      const float grad_sp = 1.f - expf(-sp);
+      const float tsp = tanhf(sp);
+      const float grad_tsp = (1.f - tsp * tsp) * grad_sp;
+      return u * grad_tsp + tsp;
+    }
+  }
+  return 1.f;
+}
+// gradient evaluated on the post-activation output, as gradient_array(l->output, ...) does for layers without a
+// saved pre-activation (activations.h:152-178)
+__device__ __forceinline__ float act_grad_out(float y, int act) {
+  switch (act) {
+    case YC_LEAKY: return y > 0.f ? 1.f : .1f;
+    case YC_RELU: return y > 0.f ? 1.f : 0.f;
+    case YC_LOGISTIC: return (1.f - y) * y;
+  }
+  return 1.f;
+}
+__device__ __forceinline__ float act_fwd_exact(float x, int act) {  // training forward: libm-accurate forms
+  switch (act) {
+    case YC_LINEAR: return x;
+    case YC_LEAKY: return x > 0.f ? x : .1f * x;
+    case YC_RELU: return x > 0.f ? x : 0.f;
+    case YC_LOGISTIC: return 1.f / (1.f + expf(-x));
+    case YC_SWISH: return x / (1.f + expf(-x));
+    case YC_MISH: {
+      const float sp = x > 20.f ? x : (x < -20.f ? expf(x) : logf(expf(x) + 1.f));
+      return x * (2.f / (1.f + expf(-2.f * sp)) - 1.f);
+    }
+  }
+  return x;
+}
+
+// ---- per-channel finalize of the statistics the conv epilogue accumulated --------------------------------
+// mean_cpu / variance_cpu (blas.c:164-195: unbiased 1/(N-1)) + rolling update .9/.1 (batchnorm_layer.cpp:221-224)
+__global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* __restrict__ sq, float count,
+                                   float* __restrict__ mean, float* __restrict__ var, float* __restrict__ rmean,
+                                   float* __restrict__ rvar, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float m = sum[i] / count;
+  float v = (sq[i] - count * m * m) / (count - 1.f);
+  v = fmaxf(v, 0.f);
+  mean[i] = m;
+  var[i] = v;
+  if (rmean) rmean[i] = .9f * rmean[i] + .1f * m;
+  if (rvar) rvar[i] = .9f * rvar[i] + .1f * v;
+}
+
+// y = act( gamma * (z - mean)/sqrt(var + 1e-6) + beta )   (normalize_cpu blas.c:214, scale_bias, add_bias)
+__global__ void bn_act_fwd_kernel(TView z, const float* __restrict__ mean, const float* __restrict__ var,
+                                  const float* __restrict__ gamma, const float* __restrict__ beta, int act, TView y,
+                                  int y_own_pad) {
+  const int groups = (z.c + 7) / 8;
+  const long long total = z.rows * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long row = i / groups;
+    float v[8];
+    ld8(z, row, g * 8, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = g * 8 + j;
+      if (c < z.c) {
+        const float xh = (v[j] - mean[c]) / sqrtf(var[c] + .000001f);
+        v[j] = act_fwd_exact(gamma[c] * xh + beta[c], act);
+      }
+    }
+    st8(y, row, g * 8, v, y_own_pad != 0);
+  }
+}
+
+// ---- backward reductions ------------------------------------------------------------------------------------
+// MODE 0 (batchnorm):  g = dy * act'(u), u = gamma*xhat + beta;  S1[c] += sum g ; S2[c] += sum g*(z - mean)
+// MODE 1 (bias only):  g = dy * act'(y) evaluated on the layer OUTPUT y (leaky/relu/logistic/linear): S1 only
+// thread = (row slot, 8-channel group); registers -> shared atomics -> global atomics.
+template <int MODE>
+__global__ void bwd_reduce_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
+                                  const float* __restrict__ gamma, const float* __restrict__ beta, int act,
+                                  float* __restrict__ S1, float* __restrict__ S2) {
+  extern __shared__ float sh[];  // [2][groups*8]
+  const int groups = (dy.c + 7) / 8;
+  const int C8 = groups * 8;
+  for (int i = threadIdx.x; i < 2 * C8; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  const int tg = threadIdx.x % groups;  // blockDim.x is a multiple of groups (host)
+  const int slots = blockDim.x / groups;
+  const int slot = threadIdx.x / groups;
+  float a1[8], a2[8];
+  float mu[8], ga[8], be[8], is[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    a1[j] = a2[j] = 0.f;
+    const int c = tg * 8 + j;
+    const bool ok = c < dy.c;
+    mu[j] = (MODE == 0 && ok) ? mean[c] : 0.f;
+    ga[j] = (MODE == 0 && ok) ? gamma[c] : 1.f;
+    be[j] = (ok && beta) ? beta[c] : 0.f;
+    is[j] = (MODE == 0 && ok) ? 1.f / sqrtf(var[c] + .000001f) : 1.f;
+  }
+  if (slot < slots) {
+    for (long long row = (long long)blockIdx.x * slots + slot; row < dy.rows; row += (long long)gridDim.x * slots) {
+      float d[8], x[8];
+      ld8(dy, row, tg * 8, d);
+      ld8(z, row, tg * 8, x);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        if (MODE == 0) {
+          const float xc = x[j] - mu[j];
+          const float u = ga[j] * (xc * is[j]) + be[j];
+          const float g = d[j] * act_grad(u, act);
+          a1[j] += g;
+          a2[j] += g * xc;
+        } else {
+          a1[j] += d[j] * act_grad_out(x[j], act);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&sh[tg * 8 + j], a1[j]);
+      if (MODE == 0) atomicAdd(&sh[C8 + tg * 8 + j], a2[j]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < dy.c; i += blockDim.x) {
+    atomicAdd(&S1[i], sh[i]);
+    if (MODE == 0) atomicAdd(&S2[i], sh[C8 + i]);
+  }
+}
+
+// per-channel coefficients of normalize_delta_cpu (batchnorm_layer.cpp:112-166) from the two sums:
+//   scale_updates += S2 / sqrt(var + 1e-6)                                   (backward_scale_cpu on x_norm)
+//   mean_delta     = gamma*S1 * (-1/sqrt(var + 1e-5))
+//   variance_delta = gamma*S2 * (-.5 * (var + 1e-5)^(-3/2))
+//   dz = gamma*g /(sqrt(var) + 1e-5) + variance_delta*2*(z - mean)/m + mean_delta/m
+// coef[0][c] = gamma/(sqrt(var)+1e-5), coef[1][c] = 2*variance_delta/m, coef[2][c] = mean_delta/m
+__global__ void bn_bwd_coef_kernel(const float* __restrict__ S1, const float* __restrict__ S2,
+                                   const float* __restrict__ var, const float* __restrict__ gamma, float m,
+                                   float* __restrict__ scale_updates, float* __restrict__ bias_updates,
+                                   float* __restrict__ coef, int n) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  const float v = var[c], ga = gamma[c];
+  if (scale_updates) scale_updates[c] += S2[c] / sqrtf(v + .000001f);
+  if (bias_updates) bias_updates[c] += S1[c];
+  const double md = (double)(ga * S1[c]) * (-1. / sqrt((double)(v + .00001f)));
+  const double vd = (double)(ga * S2[c]) * (-.5 * pow((double)(v + .00001f), (double)(float)(-3. / 2.)));
+  coef[c] = (float)((double)ga / (sqrt((double)v) + .00001));
+  coef[n + c] = (float)(vd * 2. / m);
+  coef[2 * n + c] = (float)(md / m);
+}
+
+__global__ void bn_bwd_apply_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
+                                    const float* __restrict__ gamma, const float* __restrict__ beta, int act,
+                                    const float* __restrict__ coef, TView dz, int groups) {
+  const long long total = dy.rows * groups;
+  const int n = dy.c;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long row = i / groups;
+    float d[8] = {0, 0, 0, 0, 0, 0, 0, 0}, x[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (g * 8 < n) {
+      ld8(dy, row, g * 8, d);
+      ld8(z, row, g * 8, x);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int c = g * 8 + j;
+        if (c < n) {
+          const float xc = x[j] - mean[c];
+          const float u = gamma[c] * (xc / sqrtf(var[c] + .000001f)) + beta[c];
+          const float gg = d[j] * act_grad(u, act);
+          d[j] = gg * coef[c] + coef[n + c] * xc + coef[2 * n + c];
+        } else {
+          d[j] = 0.f;
+        }
+      }
+    }
+    st8(dz, row, g * 8, d, true);
+  }
+}
+
+// no batchnorm: dz = dy * act'(y) on the layer output y; bias_updates += column sums of dz
+// (gradient_array + backward_bias, convolutional_layer.cpp:1327-1336)
+__global__ void act_bwd_apply_kernel(TView dy, TView u, int act, TView dz, int groups) {
+  const long long total = dy.rows * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long row = i / groups;
+    float d[8] = {0, 0, 0, 0, 0, 0, 0, 0}, x[8];
+    if (g * 8 < dy.c) {
+      ld8(dy, row, g * 8, d);
+      if (act != YC_LINEAR) {
+        ld8(u, row, g * 8, x);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) d[j] *= act_grad_out(x[j], act);
+      }
+    }
+    st8(dz, row, g * 8, d, true);
+  }
+}
+
+static int reduce_threads(int groups) {
+  int t = (256 / groups) * groups;
+  if (t < groups) t = groups;  // more than 256 groups (c > 2048): one row slot
+  return t;
+}
+
+}  // namespace yc
+
+using namespace yc;
+
+static bool ok_view(const yc_tensor* t) {
+  return t && t->ptr && t->n > 0 && t->h > 0 && t->w > 0 && t->c > 0 && t->ldc >= t->c &&
+         ((uintptr_t)t->ptr & 15) == 0 && t->ldc % (t->dtype == YC_F32 ? 4 : 8) == 0;
+}
+static int ew_grid(long long work) {
+  long long blocks = ceil_div_ll(work, 256);
+  return (int)std::max<long long>(1, std::min<long long>(blocks, (long long)sm_count() * 16));
+}
+
+extern "C" int yc_bn_finalize(const float* sum, const float* sumsq, long long count, float* mean, float* var,
+                              float* rolling_mean, float* rolling_var, int n, void* stream) {
+  YC_REQUIRE(sum && sumsq && mean && var && n > 0 && count > 1, "yc_bn_finalize: bad arguments");
+  bn_finalize_kernel<<<ceil_div(n, 128), 128, 0, (cudaStream_t)stream>>>(sum, sumsq, (float)count, mean, var,
+                                                                         rolling_mean, rolling_var, n);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+extern "C" int yc_bn_act_fwd(const yc_tensor* z, const float* mean, const float* var, const float* gamma,
+                             const float* beta, int activation, const yc_tensor* y, void* stream) {
+  YC_REQUIRE(ok_view(z) && ok_view(y) && mean && var && gamma && beta, "yc_bn_act_fwd: bad arguments");
+  YC_REQUIRE(z->n == y->n && z->h == y->h && z->w == y->w && z->c == y->c, "yc_bn_act_fwd: shape mismatch");
+  const TView zv = tv(z), yv = tv(y);
+  const int own = y->ldc == round_up(y->c, 8);
+  bn_act_fwd_kernel<<<ew_grid(zv.rows * ((z->c + 7) / 8)), 256, 0, (cudaStream_t)stream>>>(zv, mean, var, gamma, beta,
+                                                                                           activation, yv, own);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+extern "C" int yc_bn_bwd(const yc_tensor* dy, const yc_tensor* z, const float* mean, const float* var,
+                         const float* gamma, const float* beta, int activation, float* scale_updates,
+                         float* bias_updates, float* workspace, const yc_tensor* dz, void* stream) {
+  YC_REQUIRE(ok_view(dy) && ok_view(z) && ok_view(dz) && mean && var && gamma && beta && workspace,
+             "yc_bn_bwd: bad arguments");
+  YC_REQUIRE(dy->n == z->n && dy->h == z->h && dy->w == z->w && dy->c == z->c && dz->n == dy->n && dz->h == dy->h &&
+                 dz->w == dy->w && dz->c >= dy->c && dz->dtype == YC_BF16,
+             "yc_bn_bwd: shape mismatch");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int n = dy->c;
+  const TView dv = tv(dy), zv = tv(z);
+  TView ov = tv(dz);
+  float* S1 = workspace;          // [n]
+  float* S2 = workspace + n;      // [n]
+  float* coef = workspace + 2 * n;  // [3n]
+  YC_CUDA(cudaMemsetAsync(workspace, 0, sizeof(float) * 2 * n, st));
+  const int groups = (n + 7) / 8;
+  const int threads = reduce_threads(groups);
+  const int slots = threads / groups;
+  const int grid = (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(dv.rows, (long long)slots * 4), (long long)sm_count() * 4));
+  bwd_reduce_kernel<0><<<grid, threads, sizeof(float) * 2 * groups * 8, st>>>(dv, zv, mean, var, gamma, beta, activation, S1, S2);
+  YC_LAUNCH_CHECK();
+  bn_bwd_coef_kernel<<<ceil_div(n, 128), 128, 0, st>>>(S1, S2, var, gamma, (float)dv.rows, scale_updates, bias_updates, coef, n);
+  YC_LAUNCH_CHECK();
+  ov.c = dy->c;
+  const int agroups = (dz->ldc >= (long long)groups * 8) ? dz->ldc / 8 : groups;
+  bn_bwd_apply_kernel<<<ew_grid(dv.rows * agroups), 256, 0, st>>>(dv, zv, mean, var, gamma, beta, activation, coef, ov, agroups);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+extern "C" int yc_bias_act_bwd(const yc_tensor* dy, const yc_tensor* y, int activation, float* bias_updates,
+                               const yc_tensor* dz, void* stream) {
+  YC_REQUIRE(ok_view(dy) && ok_view(dz) && (activation == YC_LINEAR || ok_view(y)), "yc_bias_act_bwd: bad arguments");
+  YC_REQUIRE(activation == YC_LINEAR || activation == YC_LEAKY || activation == YC_RELU || activation == YC_LOGISTIC,
+             "yc_bias_act_bwd: mish/swish need the saved pre-activation, which only batch-normalised layers keep");
+  YC_REQUIRE(dz->n == dy->n && dz->h == dy->h && dz->w == dy->w && dz->c >= dy->c && dz->dtype == YC_BF16,
+             "yc_bias_act_bwd: shape mismatch");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int n = dy->c;
+  const TView dv = tv(dy);
+  const TView uv = activation == YC_LINEAR ? dv : tv(y);
+  TView ov = tv(dz);
+  ov.c = n;
+  const int groups = (n + 7) / 8;
+  if (bias_updates) {
+    const int threads = reduce_threads(groups);
+    const int slots = threads / groups;
+    const int grid = (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(dv.rows, (long long)slots * 4), (long long)sm_count() * 4));
+    bwd_reduce_kernel<1><<<grid, threads, sizeof(float) * 2 * groups * 8, st>>>(dv, uv, nullptr, nullptr, nullptr, nullptr,
+                                                                               activation, bias_updates, nullptr);
+    YC_LAUNCH_CHECK();
+  }
+  const int agroups = (dz->ldc >= (long long)groups * 8) ? dz->ldc / 8 : groups;
+  act_bwd_apply_kernel<<<ew_grid(dv.rows * agroups), 256, 0, st>>>(dv, uv, activation, ov, agroups);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}

@@ -45,6 +45,11 @@ struct ConvParams {
   uint32_t tmem_cols;
   int epi_sets;        // 1, 2 or 4 groups of epilogue warps working on different tiles at the same time
   int nacc;            // TMEM accumulator buffers in use (>= epi_sets)
+  // training-mode batchnorm statistics fused into the epilogue (fast_mean_gpu / fast_variance_gpu,
+  // blas_kernels.cu:534-616): per-channel sum and sum of squares of the fp32 results, nullptr = off
+  float* stat_sum;
+  float* stat_sq;
+  int stat_cols;       // n_tiles * block_n: floats per statistic in the CTA's shared-memory accumulator
 };
 
 constexpr int kStageOutBytes = 2048;  // one epilogue staging buffer: 32 rows x 64 B
@@ -72,10 +77,10 @@ __device__ __forceinline__ float act_ct(float x) {
 //   tcgen05.ld 32 columns -> *scale + bias -> act -> (+residual -> act2) -> bf16/fp32 -> swizzled smem ->
 //   TMA store of a 32-row x 64-byte box (bf16: 32 columns, fp32: 16 columns); M / channel tails are clipped by
 //   the tensor map.  No inter-warp synchronisation: each warp has its own two staging buffers.
-template <int ACT>
+template <int ACT, bool STATS = false>
 __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtensorMap* tmap_y, uint32_t tmem_base,
                                               uint32_t tfull0, uint32_t tempty0, uint32_t sbuf, int quad,
-                                              int slot, int lane, int total_tiles) {
+                                              int slot, int lane, int total_tiles, uint32_t stat_smem) {
   // Narrow tiles (block_n 32 / 64) have fewer 32-column groups than the four warps of a quadrant: the warps then
   // split into `epi_sets` sets that take alternate tiles, so all sixteen stay busy.
   const int wps = 4 / p.epi_sets;        // warps of one quadrant working on the same tile
@@ -137,6 +142,34 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
         v[j + 2] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 2]), s4.z, b4.z));
         v[j + 3] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 3]), s4.w, b4.w));
       }
+      if (STATS) {
+        // column sums over this warp's 32 rows by a transposing butterfly: 31 shuffles per statistic, after
+        // which lane j holds column col0+j.  Rows past M contribute nothing.  Accumulated per CTA in shared
+        // memory and flushed once at kernel end (grid x N atomics instead of tiles x N).
+        float red[2];
+#pragma unroll
+        for (int pass = 0; pass < 2; ++pass) {  // pass 0: sum, pass 1: sum of squares (sequential: fewer live registers)
+          float a[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float x = row_ok ? v[j] : 0.f;
+            a[j] = pass ? x * x : x;
+          }
+#pragma unroll
+          for (int off = 16; off >= 1; off >>= 1) {
+            const bool upper = (lane & off) != 0;
+#pragma unroll
+            for (int j = 0; j < off; ++j) {
+              const float send = upper ? a[j] : a[j + off], keep = upper ? a[j + off] : a[j];
+              a[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+          }
+          red[pass] = a[0];
+        }
+        const uint32_t so = stat_smem + 4u * (uint32_t)(col0 + lane);
+        asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(so), "f"(red[0]) : "memory");
+        asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(so + 4u * (uint32_t)p.stat_cols), "f"(red[1]) : "memory");
+      }
       if (has_res) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -191,8 +224,9 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
   if (lane == 0) ptx::tma_store_wait<0>();  // smem must stay valid until the last store has read it
 }
 
+template <bool STATS>
 __global__ void __launch_bounds__(kThreads, 1)
-conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_y, const ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment: required by the 128B swizzle atom (8 rows x 128 B)
@@ -209,6 +243,11 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + kMaxAcc + a); };
   const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc);
+  const uint32_t stat_smem = bar_base + 512u;  // 2 x stat_cols floats, only when statistics are requested
+  if (STATS) {
+    for (int i = threadIdx.x; i < 2 * p.stat_cols; i += blockDim.x)
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(stat_smem + 4u * i), "f"(0.f) : "memory");
+  }
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -308,18 +347,31 @@ conv_fprop_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
     const uint32_t stage_base = out_base + (uint32_t)(warp - 2) * kStageOutBytes;
     const int half = (warp - 2) >> 2;  // slot 0..3 within the quadrant
+    if (STATS) {
+      epilogue_role<YC_LINEAR, true>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem);
+    } else
     switch (p.act) {
-      case YC_LEAKY: epilogue_role<YC_LEAKY>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
-      case YC_MISH: epilogue_role<YC_MISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
-      case YC_LINEAR: epilogue_role<YC_LINEAR>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
-      case YC_LOGISTIC: epilogue_role<YC_LOGISTIC>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
-      case YC_SWISH: epilogue_role<YC_SWISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
-      default: epilogue_role<YC_RELU>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles); break;
+      case YC_LEAKY: epilogue_role<YC_LEAKY>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      case YC_MISH: epilogue_role<YC_MISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      case YC_LINEAR: epilogue_role<YC_LINEAR>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      case YC_LOGISTIC: epilogue_role<YC_LOGISTIC>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      case YC_SWISH: epilogue_role<YC_SWISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      default: epilogue_role<YC_RELU>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
     }
   }
 
   ptx::tc_fence_before();
   __syncthreads();
+  if (STATS) {
+    for (int i = threadIdx.x; i < p.stat_cols; i += blockDim.x) {
+      if (i >= p.N) break;
+      float a, q;
+      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(a) : "r"(stat_smem + 4u * i));
+      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(q) : "r"(stat_smem + 4u * (i + p.stat_cols)));
+      atomicAdd(p.stat_sum + i, a);
+      atomicAdd(p.stat_sq + i, q);
+    }
+  }
   if (warp == 1) {
     __syncwarp();
     ptx::tc_fence_after();
@@ -339,6 +391,45 @@ __global__ void pack_weights_kernel(const float* __restrict__ w, int out_c, int 
     float v = 0.f;
     if (c < in_c) v = w[((long long)n * in_c + c) * taps + tap];
     out[i] = __float2bfloat16_rn(v);
+  }
+}
+
+// ---- dgrad weight packing: OIHW fp32 -> [in_c][flipped tap][out_c_p] bf16 ------------------------
+// dX = correlation of dY with the spatially flipped, channel-transposed filter (the col2im(W^T * dY) of
+// convolutional_layer.cpp:1360-1376 / convolutional_kernels.cu:765-802 written as a forward conv), so the
+// data-gradient runs through conv_fprop_kernel itself.
+__global__ void pack_weights_dgrad_kernel(const float* __restrict__ w, int out_c, int in_c, int ksize, int out_c_p,
+                                          __nv_bfloat16* __restrict__ out) {
+  const int taps = ksize * ksize;
+  const long long total = (long long)in_c * taps * out_c_p;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int n = (int)(i % out_c_p);
+    const int tap = (int)((i / out_c_p) % taps);
+    const int c = (int)(i / ((long long)out_c_p * taps));
+    float v = 0.f;
+    if (n < out_c) v = w[((long long)n * in_c + c) * taps + (taps - 1 - tap)];
+    out[i] = __float2bfloat16_rn(v);
+  }
+}
+
+// zero-insertion for strided layers: up[b][s*i][s*j][:] = dy[b][i][j][:], zeros elsewhere
+__global__ void dgrad_dilate_kernel(const __nv_bfloat16* __restrict__ dy, int B, int Ho, int Wo, int c8, long long ld_dy,
+                                    int stride, int Hu, int Wu, long long ld_up, __nv_bfloat16* __restrict__ up) {
+  const long long total = (long long)B * Hu * Wu * c8;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % c8);
+    const long long pix = i / c8;
+    const int wu = (int)(pix % Wu);
+    const int hu = (int)((pix / Wu) % Hu);
+    const long long b = pix / ((long long)Wu * Hu);
+    uint4 q = make_uint4(0, 0, 0, 0);
+    if (hu % stride == 0 && wu % stride == 0) {
+      const int ho = hu / stride, wo = wu / stride;
+      if (ho < Ho && wo < Wo) q = *reinterpret_cast<const uint4*>(dy + ((b * Ho + ho) * Wo + wo) * ld_dy + g * 8);
+    }
+    *reinterpret_cast<uint4*>(up + pix * ld_up + g * 8) = q;
   }
 }
 
@@ -414,7 +505,7 @@ extern "C" int yc_conv_pack(const float* w, int out_c, int in_c, int ksize, void
 extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* d, const yc_tensor* x,
                                    const void* w_packed, const float* bias, const float* scale,
                                    const yc_tensor* residual, const yc_tensor* y) {
-  YC_REQUIRE(out_plan && d && x && w_packed && bias && y, "yc_conv_plan_create: null argument");
+  YC_REQUIRE(out_plan && d && x && w_packed && y, "yc_conv_plan_create: null argument");  // bias == NULL: zeros
   YC_REQUIRE(x->dtype == YC_BF16, "conv input must be bf16 NHWC");
   YC_REQUIRE(x->ldc % 8 == 0 && ((uintptr_t)x->ptr & 15) == 0, "conv input view must be 16-byte aligned (ldc%%8)");
   YC_REQUIRE(d->ksize >= 1 && d->stride >= 1 && d->dilation >= 1 && d->pad >= 0, "bad conv geometry");
@@ -495,7 +586,7 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
   const int npad = p.n_tiles * p.block_n;
   cudaError_t e = cudaMalloc(&pl->bias_pad, sizeof(float) * npad);
   if (e == cudaSuccess) e = cudaMemset(pl->bias_pad, 0, sizeof(float) * npad);
-  if (e == cudaSuccess) e = cudaMemcpy(pl->bias_pad, bias, sizeof(float) * N, cudaMemcpyDeviceToDevice);
+  if (e == cudaSuccess && bias) e = cudaMemcpy(pl->bias_pad, bias, sizeof(float) * N, cudaMemcpyDeviceToDevice);
   if (e == cudaSuccess && scale) {
     e = cudaMalloc(&pl->scale_pad, sizeof(float) * npad);
     if (e == cudaSuccess) e = cudaMemset(pl->scale_pad, 0, sizeof(float) * npad);
@@ -575,7 +666,9 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
   pl->grid = (int)std::min<long long>((long long)p.m_tiles * p.n_tiles, sms);
   static bool attr_set = false;
   if (!attr_set) {
-    e = cudaFuncSetAttribute(conv_fprop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    e = cudaFuncSetAttribute(conv_fprop_kernel_t<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(conv_fprop_kernel_t<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(e));
       yc_conv_plan_destroy(pl);
@@ -584,6 +677,81 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
     attr_set = true;
   }
   *out_plan = pl;
+  return YC_OK;
+}
+
+// ---- data gradient through the forward kernel -------------------------------------------------------------
+extern "C" int yc_conv_dgrad_channels(int out_c) {  // channel count (and minimum pitch) of the dY view the GEMM reads
+  return out_c <= 64 ? round_up(out_c, 16) : round_up(out_c, 64);
+}
+extern "C" size_t yc_conv_dgrad_packed_bytes(int out_c, int in_c, int ksize) {
+  return (size_t)in_c * ksize * ksize * yc_conv_padded_in_c(yc_conv_dgrad_channels(out_c)) * 2;
+}
+extern "C" int yc_conv_pack_dgrad(const float* w, int out_c, int in_c, int ksize, void* out, void* stream) {
+  YC_REQUIRE(w && out && out_c > 0 && in_c > 0 && ksize > 0, "yc_conv_pack_dgrad: bad arguments");
+  const int out_c_p = yc_conv_padded_in_c(yc_conv_dgrad_channels(out_c));
+  const long long total = (long long)in_c * ksize * ksize * out_c_p;
+  const int blocks = (int)std::min<long long>(ceil_div_ll(total, 256), 148 * 8);
+  pack_weights_dgrad_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w, out_c, in_c, ksize, out_c_p, (__nv_bfloat16*)out);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+// geometry of the zero-inserted dY a strided layer's data gradient reads (stride 1: dY itself)
+extern "C" int yc_conv_dgrad_dilated_size(const yc_conv_desc* d, int in_h, int in_w, int* hu, int* wu) {
+  YC_REQUIRE(d && hu && wu, "yc_conv_dgrad_dilated_size: null argument");
+  const int eff = d->dilation * (d->ksize - 1) + 1;
+  *hu = in_h + 2 * d->pad - eff + 1;
+  *wu = in_w + 2 * d->pad - eff + 1;
+  return YC_OK;
+}
+extern "C" int yc_conv_dgrad_dilate(const yc_tensor* dy, int stride, const yc_tensor* up, void* stream) {
+  YC_REQUIRE(dy && up && dy->dtype == YC_BF16 && up->dtype == YC_BF16 && stride >= 1, "yc_conv_dgrad_dilate: bad arguments");
+  YC_REQUIRE(up->n == dy->n && up->c == dy->c && up->ldc % 8 == 0 && dy->ldc % 8 == 0 && (dy->h - 1) * stride < up->h &&
+                 (dy->w - 1) * stride < up->w && ((uintptr_t)dy->ptr & 15) == 0 && ((uintptr_t)up->ptr & 15) == 0,
+             "yc_conv_dgrad_dilate: shape mismatch");
+  const int c8 = std::min(dy->ldc, up->ldc) / 8;
+  YC_REQUIRE(c8 * 8 >= dy->c, "yc_conv_dgrad_dilate: pitch too small");
+  const long long total = (long long)up->n * up->h * up->w * c8;
+  const int blocks = (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(total, 256), (long long)sm_count() * 16));
+  dgrad_dilate_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dy->ptr, dy->n, dy->h, dy->w, c8, dy->ldc,
+                                                                 stride, up->h, up->w, up->ldc, (__nv_bfloat16*)up->ptr);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+// dX = dgrad(dY): `d` is the FORWARD layer's geometry; dy_s1 is dY for stride-1 layers or its zero-inserted
+// version (yc_conv_dgrad_dilate) for strided ones; dx is the forward input's shape.  accumulate != 0 adds to dx
+// (cuDNN beta=1 semantics) instead of overwriting it (col2im semantics).
+extern "C" int yc_conv_dgrad_plan_create(yc_conv_plan** plan, const yc_conv_desc* d, const yc_tensor* dy_s1,
+                                         const void* w_packed_dgrad, const yc_tensor* dx, int accumulate) {
+  YC_REQUIRE(plan && d && dy_s1 && w_packed_dgrad && dx, "yc_conv_dgrad_plan_create: null argument");
+  yc_conv_desc g;
+  g.ksize = d->ksize;
+  g.stride = 1;
+  g.dilation = d->dilation;
+  g.pad = (d->ksize - 1) * d->dilation - d->pad;
+  g.activation = YC_LINEAR;
+  g.residual_activation = YC_LINEAR;
+  YC_REQUIRE(g.pad >= 0, "yc_conv_dgrad: pad larger than the filter reach is not supported");
+  return yc_conv_plan_create(plan, &g, dy_s1, w_packed_dgrad, nullptr, nullptr, accumulate ? dx : nullptr, dx);
+}
+
+// Training-mode forward: also accumulate per-channel sum / sum of squares of the (pre-batchnorm) results.
+extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq) {
+  YC_REQUIRE(pl && ((sum && sumsq) || (!sum && !sumsq)), "yc_conv_plan_set_stats: bad arguments");
+  ConvParams& p = pl->p;
+  const uint32_t a_bytes = kBlockM * p.block_k * 2;
+  const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
+  const uint32_t stage_bytes = a_bytes + b_bytes;
+  const uint32_t out_stage = kEpiWarps * kStageOutBytes;
+  p.stat_cols = sum ? p.n_tiles * p.block_n : 0;
+  const uint32_t stat_bytes = 2u * 4u * (uint32_t)p.stat_cols;
+  const uint32_t smem_budget = 227 * 1024 - 1024 - 512 - out_stage - stat_bytes;
+  p.stages = std::min<int>(kMaxStages, smem_budget / stage_bytes);
+  YC_REQUIRE(p.stages >= 2, "tile does not fit shared memory");
+  pl->smem = (size_t)p.stages * stage_bytes + out_stage + 1024 + 512 + stat_bytes;
+  YC_REQUIRE(!sum || p.act == YC_LINEAR, "yc_conv_plan_set_stats: statistics are taken on the linear (pre-batchnorm) output");
+  p.stat_sum = sum;
+  p.stat_sq = sumsq;
   return YC_OK;
 }
 
@@ -597,7 +765,10 @@ extern "C" int yc_conv_plan_destroy(yc_conv_plan* pl) {
 
 extern "C" int yc_conv_fprop(const yc_conv_plan* pl, void* stream) {
   YC_REQUIRE(pl, "yc_conv_fprop: null plan");
-  conv_fprop_kernel<<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->p);
+  if (pl->p.stat_sum)
+    conv_fprop_kernel_t<true><<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->p);
+  else
+    conv_fprop_kernel_t<false><<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->p);
   YC_LAUNCH_CHECK();
   return YC_OK;
 }

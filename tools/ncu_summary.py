@@ -1,0 +1,31 @@
+#!/usr/bin/env python
+"""Summarise an ncu report (full set) into a small CSV: one row per captured launch with the metrics the
+roofline discussion uses.  usage: python tools/ncu_summary.py gpurun_out/prof_conv.ncu-rep > profiles/x.csv"""
+import csv
+import subprocess
+import sys
+
+WANT = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__ops_path_tensor_op_hmma_src_bf16_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed",
+        "sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
+        "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "l1tex__m_xbar2l1tex_read_bytes.sum", "lts__t_sector_hit_rate.pct", "launch__registers_per_thread",
+        "launch__shared_mem_per_block_dynamic", "smsp__cycles_active.avg"]
+
+
+def main():
+    rep = sys.argv[1]
+    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], rows[1]
+    idx = [hdr.index(w) for w in WANT if w in hdr]
+    w = csv.writer(sys.stdout)
+    w.writerow([hdr[i] + (f" [{units[i]}]" if units[i] else "") for i in idx])
+    for r in rows[2:]:
+        w.writerow([r[i][:60] for i in idx])
+
+
+if __name__ == "__main__":
+    main()
