@@ -1,0 +1,346 @@
+// Backward passes of the memory-bound layers + the SGD update, NHWC bf16 deltas, fp32 math, 16-byte accesses.
+// Replaces BackwardMaxpoolLayerGpu (maxpool_layer_kernels.cu:103-143), BackwardUpsampleLayerGpu
+// (upsample_layer.c:121-133), BackwardRouteLayerGpu (route_layer.c:144-160), BackwardShortcutLayerGpu
+// (shortcut_layer.c:206-220, blas_kernels.cu:980-1018) and UpdateConvolutionalLayerGpu
+// (convolutional_kernels.cu:865-921); semantics follow the CPU twins cited per kernel.
+#include <float.h>
+#include <algorithm>
+
+#include "yc_common.cuh"
+
+namespace yc {
+
+struct BV {  // bf16 NHWC view
+  __nv_bfloat16* ptr;
+  int n, h, w, c;
+  long long ldc;
+};
+static inline BV bv(const yc_tensor* t) { return BV{(__nv_bfloat16*)t->ptr, t->n, t->h, t->w, t->c, t->ldc}; }
+
+__device__ __forceinline__ void bld8(const BV& t, long long pix, int c0, float (&v)[8]) {
+  const __nv_bfloat16* p = t.ptr + pix * t.ldc + c0;
+  if (c0 + 8 <= t.c) {
+    const uint4 q = *reinterpret_cast<const uint4*>(p);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(h[e]);
+      v[2 * e] = f.x;
+      v[2 * e + 1] = f.y;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = (c0 + j < t.c) ? __bfloat162float(p[j]) : 0.f;
+  }
+}
+__device__ __forceinline__ void bst8(const BV& t, long long pix, int c0, const float (&v)[8]) {
+  __nv_bfloat16* p = t.ptr + pix * t.ldc + c0;
+  if (c0 + 8 <= t.c) {
+    uint4 q;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&q);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(v[2 * e], v[2 * e + 1]);
+    *reinterpret_cast<uint4*>(p) = q;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (c0 + j < t.c) p[j] = __float2bfloat16_rn(v[j]);
+  }
+}
+
+// ---- maxpool, training forward: also records which tap of the window won (ForwardMaxpoolLayer,
+// maxpool_layer.cpp:258-288: strict '>' keeps the first maximum in row-major scan order; the reference stores the
+// flat input index in l->indexes, we store the tap number n*size+m, one byte per output element) ----------------
+__global__ void maxpool_train_kernel(BV x, BV y, uint8_t* __restrict__ idx, int size, int stride, int pad) {
+  const int groups = (x.c + 7) / 8;
+  const long long total = (long long)y.n * y.h * y.w * groups;
+  const int off = -pad / 2;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long pix = i / groups;
+    const int ow = (int)(pix % y.w);
+    const int oh = (int)((pix / y.w) % y.h);
+    const long long b = pix / ((long long)y.w * y.h);
+    float m[8];
+    int mi[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { m[j] = -FLT_MAX; mi[j] = 255; }
+    for (int n = 0; n < size; ++n) {
+      const int ih = off + oh * stride + n;
+      if (ih < 0 || ih >= x.h) continue;
+      for (int k = 0; k < size; ++k) {
+        const int iw = off + ow * stride + k;
+        if (iw < 0 || iw >= x.w) continue;
+        float v[8];
+        bld8(x, (b * x.h + ih) * x.w + iw, g * 8, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (v[j] > m[j]) { m[j] = v[j]; mi[j] = n * size + k; }
+      }
+    }
+    bst8(y, pix, g * 8, m);
+    uint8_t* ip = idx + pix * (long long)(groups * 8) + g * 8;
+    uint2 q;
+    q.x = (uint32_t)mi[0] | ((uint32_t)mi[1] << 8) | ((uint32_t)mi[2] << 16) | ((uint32_t)mi[3] << 24);
+    q.y = (uint32_t)mi[4] | ((uint32_t)mi[5] << 8) | ((uint32_t)mi[6] << 16) | ((uint32_t)mi[7] << 24);
+    *reinterpret_cast<uint2*>(ip) = q;
+  }
+}
+
+// BackwardMaxpoolLayer (maxpool_layer.cpp:311-323): state.delta[indexes[i]] += l->delta[i], as a gather over the
+// windows that contain each input pixel (no atomics, deterministic)
+__global__ void maxpool_bwd_kernel(BV dy, const uint8_t* __restrict__ idx, BV dx, int size, int stride, int pad) {
+  const int groups = (dx.c + 7) / 8;
+  const long long total = (long long)dx.n * dx.h * dx.w * groups;
+  const int off = -pad / 2;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long pix = i / groups;
+    const int iw = (int)(pix % dx.w);
+    const int ih = (int)((pix / dx.w) % dx.h);
+    const long long b = pix / ((long long)dx.w * dx.h);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    bool any = false;
+    // windows (oh, ow) with ih = off + oh*stride + n, 0 <= n < size
+    for (int n = 0; n < size; ++n) {
+      const int th = ih - off - n;
+      if (th < 0 || th % stride) continue;
+      const int oh = th / stride;
+      if (oh >= dy.h) continue;
+      for (int k = 0; k < size; ++k) {
+        const int tw = iw - off - k;
+        if (tw < 0 || tw % stride) continue;
+        const int ow = tw / stride;
+        if (ow >= dy.w) continue;
+        const long long opix = (b * dy.h + oh) * dy.w + ow;
+        const uint2 q = *reinterpret_cast<const uint2*>(idx + opix * (long long)(groups * 8) + g * 8);
+        const int tap = n * size + k;
+        float d[8];
+        bld8(dy, opix, g * 8, d);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t w32 = j < 4 ? q.x : q.y;
+          const int t = (w32 >> (8 * (j & 3))) & 255;
+          if (t == tap) { acc[j] += d[j]; any = true; }
+        }
+      }
+    }
+    if (any) {
+      float v[8];
+      bld8(dx, pix, g * 8, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += acc[j];
+      bst8(dx, pix, g * 8, v);
+    }
+  }
+}
+
+// BackwardUpsampleLayer (upsample_layer.c:92-103 -> upsample_cpu forward=0, blas.c:382-406):
+// state.delta[in] += scale * sum of the stride^2 children of l->delta
+__global__ void upsample_bwd_kernel(BV dy, BV dx, int stride, float scale) {
+  const int groups = (dx.c + 7) / 8;
+  const long long total = (long long)dx.n * dx.h * dx.w * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long pix = i / groups;
+    const int iw = (int)(pix % dx.w);
+    const int ih = (int)((pix / dx.w) % dx.h);
+    const long long b = pix / ((long long)dx.w * dx.h);
+    float v[8];
+    bld8(dx, pix, g * 8, v);
+    for (int r = 0; r < stride; ++r)
+      for (int s = 0; s < stride; ++s) {
+        float d[8];
+        bld8(dy, (b * dy.h + ih * stride + r) * dy.w + iw * stride + s, g * 8, d);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] += scale * d[j];
+      }
+    bst8(dx, pix, g * 8, v);
+  }
+}
+
+// dst += src on views: BackwardRouteLayer's axpy_cpu per input (route_layer.c:106-122) and BackwardShortcutCpu's two
+// accumulations (blas.c:101-129)
+__global__ void axpy_view_kernel(BV src, BV dst) {
+  const int groups = (dst.c + 7) / 8;
+  const long long total = (long long)dst.n * dst.h * dst.w * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long pix = i / groups;
+    float a[8], d[8];
+    bld8(src, pix, g * 8, a);
+    bld8(dst, pix, g * 8, d);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) d[j] += a[j];
+    bst8(dst, pix, g * 8, d);
+  }
+}
+
+// BackwardShortcutLayer (shortcut_layer.c:176-188): dy *= act'(y) in place, then prev.delta += dy, from.delta += dy
+__global__ void shortcut_bwd_kernel(BV dy, BV y, int act, BV dprev, BV dfrom) {
+  const int groups = (dy.c + 7) / 8;
+  const long long total = (long long)dy.n * dy.h * dy.w * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long pix = i / groups;
+    float d[8];
+    bld8(dy, pix, g * 8, d);
+    if (act != YC_LINEAR) {
+      float o[8];
+      bld8(y, pix, g * 8, o);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float gr = 1.f;
+        if (act == YC_LEAKY) gr = o[j] > 0.f ? 1.f : .1f;
+        else if (act == YC_RELU) gr = o[j] > 0.f ? 1.f : 0.f;
+        else if (act == YC_LOGISTIC) gr = (1.f - o[j]) * o[j];
+        d[j] *= gr;
+      }
+      bst8(dy, pix, g * 8, d);
+    }
+    float v[8];
+    if (dprev.ptr) {
+      bld8(dprev, pix, g * 8, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += d[j];
+      bst8(dprev, pix, g * 8, v);
+    }
+    if (dfrom.ptr) {
+      bld8(dfrom, pix, g * 8, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[j] += d[j];
+      bst8(dfrom, pix, g * 8, v);
+    }
+  }
+}
+
+}  // namespace yc
+
+namespace yc {
+
+// UpdateConvolutionalLayer (convolutional_layer.cpp:1382-1400), SGD with momentum and weight decay:
+//   dW -= decay*batch*W ; W += (lr/batch)*dW ; dW *= momentum
+// in one pass over the packed gradient; also refreshes the two bf16 operand packings the GEMMs read
+// (forward [n][tap][c_p], data-gradient [c][flipped tap][n_p]) so no separate repack launch is needed.
+__global__ void sgd_weights_kernel(float* __restrict__ w_oihw, float* __restrict__ dwp, int out_c, int in_c, int taps,
+                                   int ldw, float lr_over_batch, float decay_batch, float momentum,
+                                   __nv_bfloat16* __restrict__ wp_f, int in_c_p, __nv_bfloat16* __restrict__ wp_d,
+                                   int out_c_p) {
+  const long long total = (long long)out_c * taps * in_c;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % in_c);
+    const int tap = (int)((i / in_c) % taps);
+    const int n = (int)(i / ((long long)in_c * taps));
+    const long long gi = ((long long)n * taps + tap) * ldw + c;
+    const long long wi = ((long long)n * in_c + c) * taps + tap;
+    float w = w_oihw[wi];
+    float g = dwp[gi];
+    g += -decay_batch * w;
+    w += lr_over_batch * g;
+    g *= momentum;
+    w_oihw[wi] = w;
+    dwp[gi] = g;
+    const __nv_bfloat16 wb = __float2bfloat16_rn(w);
+    if (wp_f) wp_f[((long long)n * taps + tap) * in_c_p + c] = wb;
+    if (wp_d) wp_d[((long long)c * taps + (taps - 1 - tap)) * out_c_p + n] = wb;
+  }
+}
+// biases / scales: p += (lr/batch)*dp ; dp *= momentum   (no decay)
+__global__ void sgd_vector_kernel(float* __restrict__ p, float* __restrict__ dp, int n, float lr_over_batch,
+                                  float momentum) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float g = dp[i];
+  p[i] += lr_over_batch * g;
+  dp[i] = g * momentum;
+}
+// all-reduce staging helpers are not needed: gradients are fp32 and contiguous per layer.
+
+}  // namespace yc
+
+using namespace yc;
+
+static bool okv(const yc_tensor* t) {
+  return t && t->ptr && t->dtype == YC_BF16 && t->n > 0 && t->h > 0 && t->w > 0 && t->c > 0 && t->ldc >= t->c &&
+         t->ldc % 8 == 0 && ((uintptr_t)t->ptr & 15) == 0;
+}
+static int tl_grid(long long work) {
+  return (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(work, 256), (long long)sm_count() * 16));
+}
+
+extern "C" int yc_maxpool_fwd_train(const yc_tensor* x, const yc_tensor* y, unsigned char* idx, int size, int stride,
+                                    int pad, void* stream) {
+  YC_REQUIRE(okv(x) && okv(y) && idx && size >= 1 && size <= 15 && stride >= 1 && pad >= 0, "yc_maxpool_fwd_train: bad arguments");
+  YC_REQUIRE(y->n == x->n && y->c == x->c && y->h == (x->h + pad - size) / stride + 1 &&
+                 y->w == (x->w + pad - size) / stride + 1 && ((uintptr_t)idx & 7) == 0,
+             "yc_maxpool_fwd_train: output shape mismatch");
+  const long long work = (long long)y->n * y->h * y->w * ((y->c + 7) / 8);
+  maxpool_train_kernel<<<tl_grid(work), 256, 0, (cudaStream_t)stream>>>(bv(x), bv(y), idx, size, stride, pad);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+extern "C" int yc_maxpool_bwd(const yc_tensor* dy, const unsigned char* idx, const yc_tensor* dx, int size, int stride,
+                              int pad, void* stream) {
+  YC_REQUIRE(okv(dy) && okv(dx) && idx && size >= 1 && size <= 15 && stride >= 1, "yc_maxpool_bwd: bad arguments");
+  YC_REQUIRE(dy->n == dx->n && dy->c == dx->c && dy->h == (dx->h + pad - size) / stride + 1 &&
+                 dy->w == (dx->w + pad - size) / stride + 1,
+             "yc_maxpool_bwd: shape mismatch");
+  const long long work = (long long)dx->n * dx->h * dx->w * ((dx->c + 7) / 8);
+  maxpool_bwd_kernel<<<tl_grid(work), 256, 0, (cudaStream_t)stream>>>(bv(dy), idx, bv(dx), size, stride, pad);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+extern "C" int yc_upsample_bwd(const yc_tensor* dy, const yc_tensor* dx, int stride, float scale, void* stream) {
+  YC_REQUIRE(okv(dy) && okv(dx) && stride >= 1 && dy->n == dx->n && dy->c == dx->c && dy->h == dx->h * stride &&
+                 dy->w == dx->w * stride,
+             "yc_upsample_bwd: bad arguments");
+  const long long work = (long long)dx->n * dx->h * dx->w * ((dx->c + 7) / 8);
+  upsample_bwd_kernel<<<tl_grid(work), 256, 0, (cudaStream_t)stream>>>(bv(dy), bv(dx), stride, scale);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+extern "C" int yc_axpy_view(const yc_tensor* src, const yc_tensor* dst, void* stream) {
+  YC_REQUIRE(okv(src) && okv(dst) && src->n == dst->n && src->h == dst->h && src->w == dst->w && src->c == dst->c,
+             "yc_axpy_view: bad arguments");
+  const long long work = (long long)dst->n * dst->h * dst->w * ((dst->c + 7) / 8);
+  axpy_view_kernel<<<tl_grid(work), 256, 0, (cudaStream_t)stream>>>(bv(src), bv(dst));
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+extern "C" int yc_shortcut_bwd(const yc_tensor* dy, const yc_tensor* y, int activation, const yc_tensor* dprev,
+                               const yc_tensor* dfrom, void* stream) {
+  YC_REQUIRE(okv(dy) && (activation == YC_LINEAR || okv(y)) && (!dprev || okv(dprev)) && (!dfrom || okv(dfrom)),
+             "yc_shortcut_bwd: bad arguments");
+  YC_REQUIRE(activation == YC_LINEAR || activation == YC_LEAKY || activation == YC_RELU || activation == YC_LOGISTIC,
+             "yc_shortcut_bwd: activation outside the hot path");
+  BV none{nullptr, 0, 0, 0, 0, 0};
+  const long long work = (long long)dy->n * dy->h * dy->w * ((dy->c + 7) / 8);
+  shortcut_bwd_kernel<<<tl_grid(work), 256, 0, (cudaStream_t)stream>>>(bv(dy), activation == YC_LINEAR ? bv(dy) : bv(y),
+                                                                       activation, dprev ? bv(dprev) : none,
+                                                                       dfrom ? bv(dfrom) : none);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+extern "C" int yc_sgd_update_conv(float* w_oihw, float* dw_packed, int out_c, int in_c, int ksize, float lr, int batch,
+                                  float momentum, float decay, void* w_packed_fwd, void* w_packed_dgrad, float* biases,
+                                  float* bias_updates, float* scales, float* scale_updates, void* stream) {
+  YC_REQUIRE(w_oihw && dw_packed && out_c > 0 && in_c > 0 && ksize > 0 && batch > 0, "yc_sgd_update_conv: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int taps = ksize * ksize;
+  const long long total = (long long)out_c * taps * in_c;
+  const int in_c_p = yc_conv_padded_in_c(in_c);
+  const int out_c_p = yc_conv_padded_in_c(yc_conv_dgrad_channels(out_c));
+  sgd_weights_kernel<<<tl_grid(total), 256, 0, st>>>(w_oihw, dw_packed, out_c, in_c, taps, yc_conv_wgrad_ld(in_c),
+                                                     lr / batch, decay * batch, momentum, (__nv_bfloat16*)w_packed_fwd,
+                                                     in_c_p, (__nv_bfloat16*)w_packed_dgrad, out_c_p);
+  YC_LAUNCH_CHECK();
+  if (biases && bias_updates) {
+    sgd_vector_kernel<<<ceil_div(out_c, 128), 128, 0, st>>>(biases, bias_updates, out_c, lr / batch, momentum);
+    YC_LAUNCH_CHECK();
+  }
+  if (scales && scale_updates) {
+    sgd_vector_kernel<<<ceil_div(out_c, 128), 128, 0, st>>>(scales, scale_updates, out_c, lr / batch, momentum);
+    YC_LAUNCH_CHECK();
+  }
+  return YC_OK;
+}

@@ -71,6 +71,31 @@ _SIGS = {
     "yc_conv_plan_destroy": (C.c_int, [_P]),
     "yc_conv_fprop": (C.c_int, [_P, _P]),
     "yc_conv_plan_info": (C.c_int, [_P, C.c_int]),
+    "yc_conv_plan_set_stats": (C.c_int, [_P, _P, _P]),
+    "yc_bn_finalize": (C.c_int, [_P, _P, C.c_longlong, _P, _P, _P, _P, C.c_int, _P]),
+    "yc_bn_act_fwd": (C.c_int, [_TP, _P, _P, _P, _P, C.c_int, _TP, _P]),
+    "yc_bn_bwd": (C.c_int, [_TP, _TP, _P, _P, _P, _P, C.c_int, _P, _P, _P, _TP, _P]),
+    "yc_bias_act_bwd": (C.c_int, [_TP, _TP, C.c_int, _P, _TP, _P]),
+    "yc_conv_dgrad_channels": (C.c_int, [C.c_int]),
+    "yc_conv_dgrad_packed_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "yc_conv_pack_dgrad": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "yc_conv_dgrad_dilated_size": (C.c_int, [C.POINTER(ConvDesc), C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "yc_conv_dgrad_dilate": (C.c_int, [_TP, C.c_int, _TP, _P]),
+    "yc_conv_dgrad_plan_create": (C.c_int, [C.POINTER(_P), C.POINTER(ConvDesc), _TP, _P, _TP, C.c_int]),
+    "yc_conv_wgrad_ld": (C.c_int, [C.c_int]),
+    "yc_conv_wgrad_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "yc_conv_wgrad_plan_create": (C.c_int, [C.POINTER(_P), C.POINTER(ConvDesc), _TP, _TP, C.c_int, _P]),
+    "yc_conv_wgrad_plan_destroy": (C.c_int, [_P]),
+    "yc_conv_wgrad": (C.c_int, [_P, _P]),
+    "yc_conv_wgrad_plan_info": (C.c_int, [_P, C.c_int]),
+    "yc_conv_wgrad_unpack": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "yc_conv_wgrad_pack": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "yc_maxpool_fwd_train": (C.c_int, [_TP, _TP, _P, C.c_int, C.c_int, C.c_int, _P]),
+    "yc_maxpool_bwd": (C.c_int, [_TP, _P, _TP, C.c_int, C.c_int, C.c_int, _P]),
+    "yc_upsample_bwd": (C.c_int, [_TP, _TP, C.c_int, C.c_float, _P]),
+    "yc_axpy_view": (C.c_int, [_TP, _TP, _P]),
+    "yc_shortcut_bwd": (C.c_int, [_TP, _TP, C.c_int, _TP, _TP, _P]),
+    "yc_sgd_update_conv": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_float, C.c_float, _P, _P, _P, _P, _P, _P, _P]),
     "yc_maxpool_fwd": (C.c_int, [_TP, _TP, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "yc_upsample_fwd": (C.c_int, [_TP, _TP, C.c_int, C.c_float, _P]),
     "yc_shortcut_fwd": (C.c_int, [_TP, _TP, _TP, C.c_int, _P]),

@@ -90,6 +90,132 @@ class Conv:
             pass
 
 
+class ConvTrain:
+    """One convolutional layer in training mode through the operator-level ABI: forward with batch statistics
+    (ForwardConvolutionalLayerGpu with state.train) and backward (BackwardConvolutionalLayerGpu)."""
+
+    def __init__(self, x_buf, x_shape, w_oihw, biases, k, stride, pad, act, scales=None, dil=1):
+        lib = L.lib()
+        n, h, w, c = x_shape
+        dev = x_buf.device
+        self.dev, self.x_buf, self.x_shape = dev, x_buf, x_shape
+        self.k, self.stride, self.pad, self.dil = k, stride, pad, dil
+        self.act = L.ACT[act] if isinstance(act, str) else act
+        self.N = N = w_oihw.shape[0]
+        self.bn = scales is not None
+        eff = dil * (k - 1) + 1
+        self.ho, self.wo = ho, wo = (h + 2 * pad - eff) // stride + 1, (w + 2 * pad - eff) // stride + 1
+        self.w32 = w_oihw.contiguous().float().to(dev)
+        self.packed = torch.zeros(lib.yc_conv_packed_bytes(N, c, k) // 2, dtype=torch.bfloat16, device=dev)
+        L.check(lib.yc_conv_pack(self.w32.data_ptr(), N, c, k, self.packed.data_ptr(), L.stream_ptr()), "yc_conv_pack")
+        self.packed_d = torch.zeros(lib.yc_conv_dgrad_packed_bytes(N, c, k) // 2, dtype=torch.bfloat16, device=dev)
+        L.check(lib.yc_conv_pack_dgrad(self.w32.data_ptr(), N, c, k, self.packed_d.data_ptr(), L.stream_ptr()), "yc_conv_pack_dgrad")
+        self.biases = biases.contiguous().float().to(dev)
+        self.scales = scales.contiguous().float().to(dev) if self.bn else None
+        ldy = _chan_pad(N, torch.bfloat16)
+        self.z = torch.zeros((n, ho, wo, ldy), dtype=torch.bfloat16, device=dev)   # pre-BN conv output (l->x)
+        self.y = torch.zeros((n, ho, wo, ldy), dtype=torch.bfloat16, device=dev)
+        self.stats = torch.zeros((2, N), dtype=torch.float32, device=dev)
+        self.mean = torch.zeros(N, dtype=torch.float32, device=dev)
+        self.var = torch.zeros(N, dtype=torch.float32, device=dev)
+        self.rmean = torch.zeros(N, dtype=torch.float32, device=dev)
+        self.rvar = torch.zeros(N, dtype=torch.float32, device=dev)
+        self.desc = L.ConvDesc(k, stride, pad, dil, L.LINEAR if self.bn else self.act, L.LINEAR)
+        xv = L.view(x_buf, n, h, w, c, x_buf.shape[-1])
+        self.plan = C.c_void_p()
+        out = self.z if self.bn else self.y
+        L.check(lib.yc_conv_plan_create(C.byref(self.plan), C.byref(self.desc), C.byref(xv), self.packed.data_ptr(),
+                                        None if self.bn else self.biases.data_ptr(), None, None,
+                                        C.byref(L.view(out, n, ho, wo, N, ldy))), "yc_conv_plan_create")
+        if self.bn:
+            L.check(lib.yc_conv_plan_set_stats(self.plan, self.stats[0].data_ptr(), self.stats[1].data_ptr()), "set_stats")
+        # backward buffers
+        self.cd = lib.yc_conv_dgrad_channels(N)
+        self.dz = torch.zeros((n, ho, wo, self.cd), dtype=torch.bfloat16, device=dev)
+        self.ws = torch.zeros(5 * N, dtype=torch.float32, device=dev)
+        self.scale_updates = torch.zeros(N, dtype=torch.float32, device=dev)
+        self.bias_updates = torch.zeros(N, dtype=torch.float32, device=dev)
+        self.dw_packed = torch.zeros(lib.yc_conv_wgrad_bytes(N, c, k) // 4, dtype=torch.float32, device=dev)
+        self.dx = torch.zeros((n, h, w, x_buf.shape[-1]), dtype=torch.bfloat16, device=dev)
+        self.wplan = C.c_void_p()
+        fdesc = L.ConvDesc(k, stride, pad, dil, L.LINEAR, L.LINEAR)
+        L.check(lib.yc_conv_wgrad_plan_create(C.byref(self.wplan), C.byref(fdesc), C.byref(xv),
+                                              C.byref(L.view(self.dz, n, ho, wo, self.cd, self.cd)), N,
+                                              self.dw_packed.data_ptr()), "yc_conv_wgrad_plan_create")
+        self.dz_s1 = self.dz
+        hu, wu = ho, wo
+        if stride > 1:
+            a, b = C.c_int(), C.c_int()
+            L.check(lib.yc_conv_dgrad_dilated_size(C.byref(fdesc), h, w, C.byref(a), C.byref(b)), "dilated_size")
+            hu, wu = a.value, b.value
+            self.dz_s1 = torch.zeros((n, hu, wu, self.cd), dtype=torch.bfloat16, device=dev)
+        self.hu, self.wu = hu, wu
+        self.dplan = {}
+        self.fdesc = fdesc
+
+    def forward(self):
+        lib = L.lib()
+        n, h, w, c = self.x_shape
+        st = L.stream_ptr()
+        if self.bn:
+            self.stats.zero_()
+        L.check(lib.yc_conv_fprop(self.plan, st), "yc_conv_fprop")
+        if self.bn:
+            ldy = self.z.shape[-1]
+            L.check(lib.yc_bn_finalize(self.stats[0].data_ptr(), self.stats[1].data_ptr(), n * self.ho * self.wo,
+                                       self.mean.data_ptr(), self.var.data_ptr(), self.rmean.data_ptr(), self.rvar.data_ptr(),
+                                       self.N, st), "yc_bn_finalize")
+            L.check(lib.yc_bn_act_fwd(L.view(self.z, n, self.ho, self.wo, self.N, ldy), self.mean.data_ptr(), self.var.data_ptr(),
+                                      self.scales.data_ptr(), self.biases.data_ptr(), self.act,
+                                      L.view(self.y, n, self.ho, self.wo, self.N, ldy), st), "yc_bn_act_fwd")
+        return self.y
+
+    def backward(self, dy, accumulate=False, want_dx=True):
+        """dy: NHWC bf16 [n,ho,wo,ld] (l->delta).  Returns dx (NHWC bf16) or None."""
+        lib = L.lib()
+        n, h, w, c = self.x_shape
+        st = L.stream_ptr()
+        ho, wo, N = self.ho, self.wo, self.N
+        dyv = L.view(dy, n, ho, wo, N, dy.shape[-1])
+        dzv = L.view(self.dz, n, ho, wo, self.cd, self.cd)
+        ldy = self.z.shape[-1]
+        if self.bn:
+            L.check(lib.yc_bn_bwd(dyv, L.view(self.z, n, ho, wo, N, ldy), self.mean.data_ptr(), self.var.data_ptr(),
+                                  self.scales.data_ptr(), self.biases.data_ptr(), self.act, self.scale_updates.data_ptr(),
+                                  None, self.ws.data_ptr(), dzv, st), "yc_bn_bwd")
+        else:
+            L.check(lib.yc_bias_act_bwd(dyv, L.view(self.y, n, ho, wo, N, ldy), self.act, self.bias_updates.data_ptr(),
+                                        dzv, st), "yc_bias_act_bwd")
+        L.check(lib.yc_conv_wgrad(self.wplan, st), "yc_conv_wgrad")
+        if not want_dx:
+            return None
+        if self.stride > 1:
+            L.check(lib.yc_conv_dgrad_dilate(dzv, self.stride, L.view(self.dz_s1, n, self.hu, self.wu, self.cd, self.cd), st),
+                    "yc_conv_dgrad_dilate")
+        key = bool(accumulate)
+        if key not in self.dplan:
+            p = C.c_void_p()
+            L.check(lib.yc_conv_dgrad_plan_create(C.byref(p), C.byref(self.fdesc),
+                                                  C.byref(L.view(self.dz_s1, n, self.hu, self.wu, self.cd, self.cd)),
+                                                  self.packed_d.data_ptr(),
+                                                  C.byref(L.view(self.dx, n, h, w, c, self.dx.shape[-1])), int(key)),
+                    "yc_conv_dgrad_plan_create")
+            self.dplan[key] = p
+        L.check(lib.yc_conv_fprop(self.dplan[key], st), "yc_conv_dgrad")
+        return self.dx
+
+    def weight_updates(self):
+        n, h, w, c = self.x_shape
+        out = torch.zeros((self.N, c, self.k, self.k), dtype=torch.float32, device=self.dev)
+        L.check(L.lib().yc_conv_wgrad_unpack(self.dw_packed.data_ptr(), self.N, c, self.k, out.data_ptr(), L.stream_ptr()),
+                "yc_conv_wgrad_unpack")
+        return out
+
+    def winfo(self):
+        keys = ["block_n", "splits", "stages", "tiles", "grid", "kb_per_split"]
+        return {k: L.lib().yc_conv_wgrad_plan_info(self.wplan, i) for i, k in enumerate(keys)}
+
+
 def maxpool(x, c, size, stride, pad=None, quirk=False):
     n, h, w, ldc = x.shape
     pad = size - 1 if pad is None else pad

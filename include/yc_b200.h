@@ -113,6 +113,66 @@ YC_API int yc_conv_fprop(const yc_conv_plan* plan, void* stream);
 /* plan introspection for tests/bench: what=0 block_n, 1 block_k, 2 stages, 3 tiles, 4 grid */
 YC_API int yc_conv_plan_info(const yc_conv_plan* plan, int what);
 
+/* ---- convolution training path: replaces ForwardConvolutionalLayerGpu(train) / BackwardConvolutionalLayerGpu --- */
+/* (convolutional_kernels.cu:252-553 with state.train, 555-815; CPU twins convolutional_layer.cpp:1128-1380,
+ *  batchnorm_layer.cpp:92-166,206-255.)  Semantics follow the reference CPU path.
+ *
+ * Forward of a batch-normalised layer in training:
+ *   z = conv(x, w)                       yc_conv_fprop on a plan with activation LINEAR, bias NULL, and
+ *   sum_c z, sum_c z^2                   yc_conv_plan_set_stats(): the statistics of fast_mean_gpu /
+ *                                        fast_variance_gpu are reduced inside the conv epilogue (from the fp32
+ *                                        accumulators; caller zeroes sum/sumsq before the launch)
+ *   mean, var, rolling update            yc_bn_finalize (unbiased variance, rolling = .9 roll + .1 batch)
+ *   y = act(gamma*(z-mean)/sqrt(var+1e-6)+beta)   yc_bn_act_fwd */
+YC_API int yc_conv_plan_set_stats(yc_conv_plan* plan, float* sum, float* sumsq);
+YC_API int yc_bn_finalize(const float* sum, const float* sumsq, long long count, float* mean, float* var,
+                          float* rolling_mean, float* rolling_var, int n, void* stream);
+YC_API int yc_bn_act_fwd(const yc_tensor* z, const float* mean, const float* var, const float* gamma,
+                         const float* beta, int activation, const yc_tensor* y, void* stream);
+/* Backward of a batch-normalised layer up to the GEMMs: gradient_array_ongpu + BackwardBatchnormLayerGpu
+ * (batchnorm_layer.cpp:240-255: backward_scale, scale_bias, mean_delta, variance_delta, normalize_delta).
+ * dy = l->delta (NHWC bf16), z = saved pre-batchnorm conv output; dz (bf16, channels >= dy.c, pad lanes zeroed)
+ * receives the gradient the dgrad / wgrad GEMMs read.  scale_updates is accumulated into; bias_updates may be NULL
+ * (the reference CPU path leaves the batchnorm shift without gradient) or receives sum(dy*act').
+ * workspace: 5*c floats. */
+YC_API int yc_bn_bwd(const yc_tensor* dy, const yc_tensor* z, const float* mean, const float* var,
+                     const float* gamma, const float* beta, int activation, float* scale_updates,
+                     float* bias_updates, float* workspace, const yc_tensor* dz, void* stream);
+/* Layers without batchnorm: dz = dy * act'(y) on the layer output y (leaky/relu/logistic/linear), bias_updates +=
+ * per-channel sums (gradient_array + backward_bias, convolutional_layer.cpp:1327-1336).  y may be NULL for LINEAR. */
+YC_API int yc_bias_act_bwd(const yc_tensor* dy, const yc_tensor* y, int activation, float* bias_updates,
+                           const yc_tensor* dz, void* stream);
+
+/* Data gradient (gemm(1,0,...) + col2im_gpu_ext, convolutional_kernels.cu:765-802): runs through the forward
+ * implicit-GEMM kernel on the flipped, channel-transposed filter.  yc_conv_dgrad_channels(out_c) is the channel
+ * count (and minimum pixel pitch) the dz view must have; strided layers first zero-insert dz
+ * (yc_conv_dgrad_dilate into a buffer of yc_conv_dgrad_dilated_size).  accumulate=0 overwrites dx like col2im
+ * (SURVEY B6), accumulate=1 adds to it (cuDNN beta=1). Launch with yc_conv_fprop(plan). */
+YC_API int yc_conv_dgrad_channels(int out_c);
+YC_API size_t yc_conv_dgrad_packed_bytes(int out_c, int in_c, int ksize);
+YC_API int yc_conv_pack_dgrad(const float* w_oihw_dev, int out_c, int in_c, int ksize, void* w_packed_dev, void* stream);
+YC_API int yc_conv_dgrad_dilated_size(const yc_conv_desc* desc, int in_h, int in_w, int* hu, int* wu);
+YC_API int yc_conv_dgrad_dilate(const yc_tensor* dz, int stride, const yc_tensor* dz_dilated, void* stream);
+YC_API int yc_conv_dgrad_plan_create(yc_conv_plan** plan, const yc_conv_desc* desc, const yc_tensor* dz_s1,
+                                     const void* w_packed_dgrad, const yc_tensor* dx, int accumulate);
+
+/* Weight gradient (im2col_gpu_ext + gemm(0,1,...) per image accumulating into weight_updates_gpu,
+ * convolutional_kernels.cu:741-763): one tcgen05 implicit-GEMM kernel, K = output pixels split across CTAs,
+ * fp32 partial sums ADDED to dw_packed ([out_c][kh][kw][yc_conv_wgrad_ld(in_c)] fp32) — the reference's
+ * accumulate-across-images/subdivisions semantics. */
+typedef struct yc_wgrad_plan yc_wgrad_plan;
+YC_API int yc_conv_wgrad_ld(int in_c);
+YC_API size_t yc_conv_wgrad_bytes(int out_c, int in_c, int ksize);
+YC_API int yc_conv_wgrad_plan_create(yc_wgrad_plan** plan, const yc_conv_desc* desc, const yc_tensor* x,
+                                     const yc_tensor* dz, int out_c, float* dw_packed);
+YC_API int yc_conv_wgrad_plan_destroy(yc_wgrad_plan* plan);
+YC_API int yc_conv_wgrad(const yc_wgrad_plan* plan, void* stream);
+/* what=0 block_n, 1 K splits, 2 stages, 3 tiles, 4 grid, 5 K blocks per split */
+YC_API int yc_conv_wgrad_plan_info(const yc_wgrad_plan* plan, int what);
+/* packed fp32 gradient <-> the reference's OIHW weight_updates layout */
+YC_API int yc_conv_wgrad_unpack(const float* dw_packed, int out_c, int in_c, int ksize, float* dw_oihw, void* stream);
+YC_API int yc_conv_wgrad_pack(const float* dw_oihw, int out_c, int in_c, int ksize, float* dw_packed, void* stream);
+
 /* ---- memory-bound layers (128-bit vectorised NHWC) ------------------------------------------- */
 /* ForwardMaxpoolLayerGpu (maxpool_layer_kernels.cu:58-101,145-201). pad = total padding
  * (parser.cpp:646 default size-1), window offset -pad/2. ref_cpu_quirk=1 reproduces the reference
@@ -132,6 +192,29 @@ YC_API int yc_scale_channels_fwd(const yc_tensor* x, const yc_tensor* s, const y
 /* ForwardReorgLayerGpu (reorg_layer.c:113-127, blas_kernels.cu:368-402) on the reference's NCHW
  * index math, expressed over NHWC views. forward as in reorg_cpu (blas.c:12-46). */
 YC_API int yc_reorg_fwd(const yc_tensor* x, const yc_tensor* y, int stride, int forward, void* stream);
+
+/* ---- backward of the memory-bound layers + update ---------------------------------------------- */
+/* ForwardMaxpoolLayerGpu in training: also records the winning tap (one byte per output element, [n,h,w,ceil8(c)]),
+ * the equivalent of l->indexes (maxpool_layer.cpp:258-288). */
+YC_API int yc_maxpool_fwd_train(const yc_tensor* x, const yc_tensor* y, unsigned char* idx, int size, int stride,
+                                int pad, void* stream);
+/* BackwardMaxpoolLayerGpu (maxpool_layer_kernels.cu:103-143; maxpool_layer.cpp:311-323): dx += scatter(dy) */
+YC_API int yc_maxpool_bwd(const yc_tensor* dy, const unsigned char* idx, const yc_tensor* dx, int size, int stride,
+                          int pad, void* stream);
+/* BackwardUpsampleLayerGpu (upsample_layer.c:121-133): dx += scale * sum of children */
+YC_API int yc_upsample_bwd(const yc_tensor* dy, const yc_tensor* dx, int stride, float scale, void* stream);
+/* dst += src on views: BackwardRouteLayerGpu's axpy per input (route_layer.c:144-160) */
+YC_API int yc_axpy_view(const yc_tensor* src, const yc_tensor* dst, void* stream);
+/* BackwardShortcutLayerGpu (shortcut_layer.c:206-220): dy *= act'(y) in place; dprev += dy; dfrom += dy */
+YC_API int yc_shortcut_bwd(const yc_tensor* dy, const yc_tensor* y, int activation, const yc_tensor* dprev,
+                           const yc_tensor* dfrom, void* stream);
+/* UpdateConvolutionalLayerGpu (convolutional_kernels.cu:865-921; convolutional_layer.cpp:1382-1400), SGD:
+ * dW -= decay*batch*W; W += lr/batch*dW; dW *= momentum (same for biases/scales without decay).  w_oihw is the fp32
+ * master copy in the reference layout; the bf16 operand packings (forward and data-gradient) are refreshed in the
+ * same pass.  biases/scales pairs may be NULL. */
+YC_API int yc_sgd_update_conv(float* w_oihw, float* dw_packed, int out_c, int in_c, int ksize, float lr, int batch,
+                              float momentum, float decay, void* w_packed_fwd, void* w_packed_dgrad, float* biases,
+                              float* bias_updates, float* scales, float* scale_updates, void* stream);
 
 /* ---- YOLO head: replaces ForwardYoloLayerGpu ------------------------------------------------- */
 /* (yolo_layer.cpp:836-859: copy + per-(b,anchor) logistic / scal_add launches.)

@@ -179,6 +179,8 @@ def oracle_lib():
         L.yo_gemm.argtypes = [C.c_int] * 5 + [C.c_float, _f32p, C.c_int, _f32p, C.c_int, C.c_float, _f32p, C.c_int]
         L.yo_fuse_bn.argtypes = [_f32p, _f32p, _f32p, _f32p, _f32p, C.c_int, C.c_int]
         L.yo_conv_forward.argtypes = [_f32p, _f32p, _f32p, C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 10 + [_f32p, C.c_void_p]
+        L.yo_conv_forward_train.argtypes = [_f32p, _f32p, _f32p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p] + [C.c_int] * 11 + [_f32p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.yo_conv_backward.argtypes = [_f32p, _f32p] + [C.c_void_p] * 7 + [_f32p] + [C.c_int] * 11 + [_f32p, _f32p, C.c_void_p, C.c_void_p]
         L.yo_maxpool.argtypes = [_f32p] + [C.c_int] * 7 + [_f32p, C.c_void_p, C.c_int]
         L.yo_upsample.argtypes = [_f32p] + [C.c_int] * 5 + [C.c_float, _f32p]
         L.yo_shortcut.argtypes = [_f32p, _f32p, C.c_longlong, C.c_int, _f32p]
@@ -221,6 +223,49 @@ class O:
                           ACT[act] if isinstance(act, str) else act, out.reshape(-1),
                           pre.ctypes.data_as(C.c_void_p) if want_pre else None)
         return (out, pre) if want_pre else out
+
+    @staticmethod
+    def conv_forward_train(x, w, biases, k, stride, pad, act, scales=None, rolling=None, dil=1):
+        """Training forward. Returns dict(out, z, xnorm, pre, mean, var, rolling_mean, rolling_var)."""
+        L = oracle_lib()
+        B, Cc, H, W = x.shape
+        N = w.shape[0]
+        bn = scales is not None
+        oh = (H + 2 * pad - (dil * (k - 1) + 1)) // stride + 1
+        ow = (W + 2 * pad - (dil * (k - 1) + 1)) // stride + 1
+        out = np.zeros((B, N, oh, ow), np.float32)
+        z, xn, pre = np.zeros_like(out), np.zeros_like(out), np.zeros_like(out)
+        mean, var = np.zeros(N, np.float32), np.zeros(N, np.float32)
+        rm = np.zeros(N, np.float32) if rolling is None else np.ascontiguousarray(rolling[0], np.float32).copy()
+        rv = np.zeros(N, np.float32) if rolling is None else np.ascontiguousarray(rolling[1], np.float32).copy()
+        sc = np.ascontiguousarray(scales, np.float32) if bn else np.zeros(N, np.float32)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        L.yo_conv_forward_train(np.ascontiguousarray(x, np.float32).reshape(-1), np.ascontiguousarray(w, np.float32).reshape(-1),
+                                np.ascontiguousarray(biases, np.float32), vp(sc), vp(rm), vp(rv), vp(mean), vp(var),
+                                B, Cc, H, W, N, k, stride, pad, dil, ACT[act] if isinstance(act, str) else act, int(bn),
+                                out.reshape(-1), vp(z), vp(xn), vp(pre))
+        return dict(out=out, z=z, xnorm=xn, pre=pre, mean=mean, var=var, rolling_mean=rm, rolling_var=rv)
+
+    @staticmethod
+    def conv_backward(x, w, fwd, delta, k, stride, pad, act, scales=None, dil=1, want_dx=True,
+                      weight_updates=None, bias_updates=None, scale_updates=None):
+        """BackwardConvolutionalLayer on the buffers of conv_forward_train (`fwd`). Returns dict."""
+        L = oracle_lib()
+        B, Cc, H, W = x.shape
+        N = w.shape[0]
+        bn = scales is not None
+        d = np.ascontiguousarray(delta, np.float32).copy()
+        wu = np.zeros(w.shape, np.float32) if weight_updates is None else np.ascontiguousarray(weight_updates, np.float32).copy()
+        bu = np.zeros(N, np.float32) if bias_updates is None else np.ascontiguousarray(bias_updates, np.float32).copy()
+        su = np.zeros(N, np.float32) if scale_updates is None else np.ascontiguousarray(scale_updates, np.float32).copy()
+        dx = np.zeros(x.shape, np.float32) if want_dx else None
+        sc = np.ascontiguousarray(scales, np.float32) if bn else np.zeros(N, np.float32)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        L.yo_conv_backward(np.ascontiguousarray(x, np.float32).reshape(-1), np.ascontiguousarray(w, np.float32).reshape(-1),
+                           vp(sc), vp(fwd["mean"]), vp(fwd["var"]), vp(fwd["out"]), vp(fwd["pre"]), vp(fwd["z"]), vp(fwd["xnorm"]),
+                           d.reshape(-1), B, Cc, H, W, N, k, stride, pad, dil, ACT[act] if isinstance(act, str) else act, int(bn),
+                           wu.reshape(-1), bu, vp(su), vp(dx) if want_dx else None)
+        return dict(delta=d, weight_updates=wu, bias_updates=bu, scale_updates=su, dx=dx)
 
     @staticmethod
     def fuse_bn(w, b, scales, mean, var):

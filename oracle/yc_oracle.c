@@ -359,3 +359,125 @@ void yo_nms_sort(float* dets, int total, int classes, float thresh, int nms_kind
   }
   free(tmp);
 }
+
+/* ---- training: conv forward with batch statistics, conv backward -------------------------------- */
+/* ForwardConvolutionalLayer with state.train (convolutional_layer.cpp:1128-1305) + ForwardBatchnormLayer
+ * (batchnorm_layer.cpp:206-238): z = conv(x,w); if bn: mean/var (blas.c:164-195, unbiased), rolling .9/.1,
+ * xhat=(z-mean)/sqrt(var+1e-6) (blas.c:214), y = act(gamma*xhat+beta); else y = act(z + bias).
+ * z_out receives the pre-batchnorm conv output (l->x), xnorm_out the normalised values (l->x_norm), pre_out
+ * the pre-activation (l->activation_input); any may be NULL. */
+void yo_conv_forward_train(const float* x, const float* w, const float* biases, const float* scales,
+                           float* rolling_mean, float* rolling_var, float* mean, float* var, int B, int C, int H,
+                           int W, int N, int k, int stride, int pad, int dil, int act, int bn, float* out,
+                           float* z_out, float* xnorm_out, float* pre_out) {
+  int oh = (H + 2 * pad - (dil * (k - 1) + 1)) / stride + 1;
+  int ow = (W + 2 * pad - (dil * (k - 1) + 1)) / stride + 1;
+  int S = oh * ow, K = k * k * C;
+  float* col = (float*)malloc(sizeof(float) * (size_t)K * S);
+  memset(out, 0, sizeof(float) * (size_t)B * N * S);
+  for (int b = 0; b < B; ++b) {
+    yo_im2col(x + (size_t)b * C * H * W, C, H, W, k, pad * dil, stride, dil, col);
+    yo_gemm(0, 0, N, S, K, 1.f, w, K, col, S, 1.f, out + (size_t)b * N * S, S);
+  }
+  free(col);
+  if (bn) {
+    for (int f = 0; f < N; ++f) {                                  /* mean_cpu blas.c:164-177 */
+      float m = 0;
+      for (int b = 0; b < B; ++b) for (int i = 0; i < S; ++i) m += out[((size_t)b * N + f) * S + i];
+      mean[f] = m * (1.f / (B * S));
+    }
+    for (int f = 0; f < N; ++f) {                                  /* variance_cpu blas.c:179-195 */
+      float v = 0;
+      for (int b = 0; b < B; ++b) for (int i = 0; i < S; ++i) {
+        float d = out[((size_t)b * N + f) * S + i] - mean[f];
+        v += d * d;
+      }
+      var[f] = v * (1.f / (B * S - 1));
+    }
+    for (int f = 0; f < N; ++f) {                                  /* batchnorm_layer.cpp:221-224 */
+      if (rolling_mean) rolling_mean[f] = .9f * rolling_mean[f] + .1f * mean[f];
+      if (rolling_var) rolling_var[f] = .9f * rolling_var[f] + .1f * var[f];
+    }
+    if (z_out) memcpy(z_out, out, sizeof(float) * (size_t)B * N * S);
+    for (int b = 0; b < B; ++b) for (int f = 0; f < N; ++f) for (int i = 0; i < S; ++i) {
+      size_t idx = ((size_t)b * N + f) * S + i;
+      out[idx] = (out[idx] - mean[f]) / (sqrt(var[f] + .000001f));  /* normalize_cpu blas.c:214 */
+    }
+    if (xnorm_out) memcpy(xnorm_out, out, sizeof(float) * (size_t)B * N * S);
+    for (int b = 0; b < B; ++b) for (int f = 0; f < N; ++f) for (int i = 0; i < S; ++i) {
+      size_t idx = ((size_t)b * N + f) * S + i;
+      out[idx] = out[idx] * scales[f] + biases[f];
+    }
+  } else {
+    for (int b = 0; b < B; ++b) for (int f = 0; f < N; ++f) for (int i = 0; i < S; ++i)
+      out[((size_t)b * N + f) * S + i] += biases[f];
+    if (z_out) memcpy(z_out, out, sizeof(float) * (size_t)B * N * S);
+  }
+  if (pre_out) memcpy(pre_out, out, sizeof(float) * (size_t)B * N * S);
+  yo_activate(out, (long long)B * N * S, act);
+}
+
+/* BackwardConvolutionalLayer (convolutional_layer.cpp:1307-1380) + BackwardBatchnormLayer
+ * (batchnorm_layer.cpp:92-166, 240-255).  delta [B,N,oh,ow] is modified in place exactly like l->delta
+ * (activation gradient, then the batchnorm backward), weight_updates / bias_updates / scale_updates are
+ * ACCUMULATED into, dx (may be NULL) is OVERWRITTEN (col2im.c:70).  out = l->output, pre = saved
+ * pre-activation (mish/swish), z = l->x, xnorm = l->x_norm. */
+void yo_conv_backward(const float* x, const float* w, const float* scales, const float* mean, const float* var,
+                      const float* out, const float* pre, const float* z, const float* xnorm, float* delta, int B,
+                      int C, int H, int W, int N, int k, int stride, int pad, int dil, int act, int bn,
+                      float* weight_updates, float* bias_updates, float* scale_updates, float* dx) {
+  int oh = (H + 2 * pad - (dil * (k - 1) + 1)) / stride + 1;
+  int ow = (W + 2 * pad - (dil * (k - 1) + 1)) / stride + 1;
+  int S = oh * ow, K = k * k * C;
+  long long tot = (long long)B * N * S;
+  if (act == YO_MISH || act == YO_SWISH) yo_gradient(pre, tot, act, delta);
+  else yo_gradient(out, tot, act, delta);
+  if (bn) {
+    for (int f = 0; f < N; ++f) {                                  /* backward_scale_cpu :92-110 */
+      float sum = 0;
+      for (int b = 0; b < B; ++b) for (int i = 0; i < S; ++i) {
+        size_t idx = ((size_t)b * N + f) * S + i;
+        sum += delta[idx] * xnorm[idx];
+      }
+      scale_updates[f] += sum;
+    }
+    for (int b = 0; b < B; ++b) for (int f = 0; f < N; ++f) for (int i = 0; i < S; ++i)   /* scale_bias */
+      delta[((size_t)b * N + f) * S + i] *= scales[f];
+    float* md = (float*)calloc(N, sizeof(float));
+    float* vd = (float*)calloc(N, sizeof(float));
+    for (int f = 0; f < N; ++f) {                                  /* mean_delta_cpu :112-129 */
+      for (int b = 0; b < B; ++b) for (int i = 0; i < S; ++i) md[f] += delta[((size_t)b * N + f) * S + i];
+      md[f] *= (-1. / sqrt(var[f] + .00001f));
+    }
+    for (int f = 0; f < N; ++f) {                                  /* variance_delta_cpu :130-147 */
+      for (int b = 0; b < B; ++b) for (int i = 0; i < S; ++i) {
+        size_t idx = ((size_t)b * N + f) * S + i;
+        vd[f] += delta[idx] * (z[idx] - mean[f]);
+      }
+      vd[f] *= -.5 * pow(var[f] + .00001f, (float)(-3. / 2.));
+    }
+    for (int b = 0; b < B; ++b) for (int f = 0; f < N; ++f) for (int i = 0; i < S; ++i) {  /* normalize_delta_cpu */
+      size_t idx = ((size_t)b * N + f) * S + i;
+      delta[idx] = delta[idx] * 1. / (sqrt(var[f]) + .00001f) + vd[f] * 2. * (z[idx] - mean[f]) / (S * B) +
+                   md[f] / (S * B);
+    }
+    free(md); free(vd);
+  } else {
+    for (int b = 0; b < B; ++b) for (int f = 0; f < N; ++f) {      /* backward_bias */
+      float s = 0;
+      for (int i = 0; i < S; ++i) s += delta[((size_t)b * N + f) * S + i];
+      bias_updates[f] += s;
+    }
+  }
+  float* col = (float*)malloc(sizeof(float) * (size_t)K * S);
+  for (int b = 0; b < B; ++b) {
+    const float* a = delta + (size_t)b * N * S;
+    yo_im2col(x + (size_t)b * C * H * W, C, H, W, k, pad * dil, stride, dil, col);
+    yo_gemm(0, 1, N, K, S, 1.f, a, S, col, S, 1.f, weight_updates, K);           /* :1358 */
+    if (dx) {
+      yo_gemm(1, 0, K, S, N, 1.f, w, K, a, S, 0.f, col, S);                       /* :1366 */
+      yo_col2im(col, C, H, W, k, pad * dil, stride, dil, dx + (size_t)b * C * H * W);
+    }
+  }
+  free(col);
+}
