@@ -31,6 +31,14 @@ class ConvDesc(C.Structure):
                 ("activation", C.c_int), ("residual_activation", C.c_int)]
 
 
+class YoloLossDesc(C.Structure):
+    _fields_ = [("anchors", C.c_int), ("total", C.c_int), ("classes", C.c_int), ("max_boxes", C.c_int),
+                ("net_w", C.c_int), ("net_h", C.c_int), ("iou_loss", C.c_int), ("iou_thresh_kind", C.c_int),
+                ("focal_loss", C.c_int), ("ignore_thresh", C.c_float), ("truth_thresh", C.c_float),
+                ("iou_thresh", C.c_float), ("iou_normalizer", C.c_float), ("cls_normalizer", C.c_float),
+                ("label_smooth_eps", C.c_float), ("max_delta", C.c_float)]
+
+
 class Detection(C.Structure):
     """struct yc_detection == the reference's struct Detection (yolo_core.h:598-609) on the path."""
     _fields_ = [("x", C.c_float), ("y", C.c_float), ("w", C.c_float), ("h", C.c_float), ("classes", C.c_int),
@@ -103,6 +111,7 @@ _SIGS = {
     "yc_scale_channels_fwd": (C.c_int, [_TP, _TP, _TP, C.c_int, _P]),
     "yc_reorg_fwd": (C.c_int, [_TP, _TP, C.c_int, C.c_int, _P]),
     "yc_yolo_decode": (C.c_int, [_TP, _P, C.c_int, C.c_int, C.c_float, C.c_int, _P]),
+    "yc_yolo_loss": (C.c_int, [C.POINTER(YoloLossDesc), _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _TP, _P, _P]),
     "yc_yolo_extract": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, C.c_int,
                                   C.c_float, C.c_int, _P, C.c_int, _P, _P]),
     "yc_network_load": (C.c_int, [C.POINTER(_P), C.c_char_p, C.c_char_p, C.c_int, C.c_int]),

@@ -289,3 +289,27 @@ def yolo_extract(decoded, anchors_wh, mask, classes, net_w, net_h, thresh, rows_
                                     net_h, thresh, int(gaussian), rows.data_ptr(), rows_per_image, counts.data_ptr(),
                                     L.stream_ptr()), "yc_yolo_extract")
     return rows, counts
+
+
+def yolo_loss(out_nchw, truth, anchors_wh, mask, classes, net_w, net_h, max_boxes=90, total=None, iou_loss="mse",
+              iou_thresh_kind="iou", focal_loss=0, ignore_thresh=.5, truth_thresh=1.0, iou_thresh=1.0,
+              iou_normalizer=.75, cls_normalizer=1.0, label_smooth_eps=0.0, max_delta=3.402823466e+38, prev_delta=None):
+    """ForwardYoloLayer's training half + BackwardYoloLayer on the device. Returns (delta_nchw, stats[8])."""
+    kinds = {"iou": 0, "giou": 1, "mse": 2, "diou": 3, "ciou": 4}
+    n, c, h, w = out_nchw.shape
+    dev = out_nchw.device
+    a = torch.as_tensor(anchors_wh, dtype=torch.float32, device=dev).contiguous()
+    m = torch.as_tensor(mask, dtype=torch.int32, device=dev).contiguous()
+    t = torch.as_tensor(truth, dtype=torch.float32, device=dev).contiguous()
+    total = a.numel() // 2 if total is None else total
+    d = L.YoloLossDesc(len(mask), total, classes, max_boxes, net_w, net_h, kinds[iou_loss], kinds[iou_thresh_kind],
+                       focal_loss, ignore_thresh, truth_thresh, iou_thresh, iou_normalizer, cls_normalizer,
+                       label_smooth_eps, max_delta)
+    delta = torch.empty_like(out_nchw)
+    stats = torch.zeros(8, dtype=torch.float32, device=dev)
+    pv = None
+    if prev_delta is not None:
+        pv = C.byref(L.view(prev_delta, n, h, w, c, prev_delta.shape[-1]))
+    L.check(L.lib().yc_yolo_loss(C.byref(d), out_nchw.data_ptr(), t.data_ptr(), a.data_ptr(), m.data_ptr(), n, h, w,
+                                 delta.data_ptr(), pv, stats.data_ptr(), L.stream_ptr()), "yc_yolo_loss")
+    return delta, stats

@@ -225,6 +225,26 @@ YC_API int yc_sgd_update_conv(float* w_oihw, float* dw_packed, int out_c, int in
 YC_API int yc_yolo_decode(const yc_tensor* x, float* out_nchw, int anchors, int classes, float scale_x_y,
                    int gaussian, void* stream);
 
+/* YOLO loss + deltas on the device: the training half of ForwardYoloLayer (yolo_layer.cpp:409-772, entirely on one
+ * host thread in the reference) and BackwardYoloLayerGpu (:884-888).  out_nchw = decoded head (yc_yolo_decode),
+ * truth = [n][max_boxes][5] (x, y, w, h, class id; the list ends at the first x == 0), anchor_wh = l->biases
+ * (2*total floats), delta_nchw = l->delta (fp32, same shape as the head, overwritten).  prev_delta (optional) is the
+ * head conv's NHWC bf16 delta, which receives += delta.  stats (device, 8 floats): [0] *(l->cost), [1] count,
+ * [2] sum(1-iou), [3] sum(1-giou), [4] |delta|^2, [5] |delta without box entries|^2, [6] sum iou, [7] class_count. */
+typedef struct yc_yolo_loss_desc {
+  int anchors;  /* l->n: anchors of this head (mask length) */
+  int total;    /* l->total */
+  int classes;
+  int max_boxes;
+  int net_w, net_h;
+  int iou_loss, iou_thresh_kind; /* IOU_LOSS (box.h:6-13): 0 iou, 1 giou, 2 mse, 3 diou, 4 ciou */
+  int focal_loss;
+  float ignore_thresh, truth_thresh, iou_thresh, iou_normalizer, cls_normalizer, label_smooth_eps, max_delta;
+} yc_yolo_loss_desc;
+YC_API int yc_yolo_loss(const yc_yolo_loss_desc* desc, const float* out_nchw, const float* truth, const float* anchor_wh,
+                        const int* mask, int n, int h, int w, float* delta_nchw, const yc_tensor* prev_delta,
+                        float* stats, void* stream);
+
 /* On-device detection extraction (GetYoloDetections for every batch index, yolo_layer.cpp:794-832):
  * scans the decoded NCHW head in the reference's order (anchor n, then cell i), keeps cells with
  * objectness > thresh and writes rows [batch, x, y, w, h, obj, prob[classes]] compactly, ordered
