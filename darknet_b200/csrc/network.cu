@@ -53,6 +53,10 @@ int build_layers(yc_network* net, const std::string& text, int batch) {
   net->h = n0.get_int("height", 0);
   net->c = n0.get_int("channels", 0);
   if (!(net->w > 0 && net->h > 0 && net->c > 0)) NET_FAIL(YC_ERR_PARSE, "[net] needs width/height/channels");
+  net->lr = n0.get_float("learning_rate", .001f);   // ParseNetOptions parser.cpp:1116-1140
+  net->momentum = n0.get_float("momentum", .9f);
+  net->decay = n0.get_float("decay", .0001f);
+  net->subdivisions = n0.get_int("subdivisions", 1);
   int c = net->c, h = net->h, w = net->w;
   for (size_t si = 1; si < secs.size(); ++si) {
     const Section& s = secs[si];
@@ -143,6 +147,23 @@ int build_layers(yc_network* net, const std::string& text, int batch) {
       L.beta_nms = s.get_float("beta_nms", 0.6f);
       const std::string nk = s.get_str("nms_kind", "default");
       L.nms_kind = nk == "diounms" ? 1 : 0;
+      {  // loss hyper-parameters (ParseYolo parser.cpp:337-392)
+        auto kind = [](const std::string& k, int dflt) {
+          if (k == "iou") return 0; if (k == "giou") return 1; if (k == "mse") return 2; if (k == "diou") return 3;
+          if (k == "ciou") return 4; return dflt;
+        };
+        L.max_boxes = s.get_int("max", 90);
+        L.iou_loss = kind(s.get_str("iou_loss", "mse"), 0);
+        L.iou_thresh_kind = kind(s.get_str("iou_thresh_kind", "iou"), 0);
+        L.focal_loss = s.get_int("focal_loss", 0);
+        L.ignore_thresh = s.get_float("ignore_thresh", .5f);
+        L.truth_thresh = s.get_float("truth_thresh", 1.f);
+        L.iou_thresh = s.get_float("iou_thresh", 1.f);
+        L.iou_normalizer = s.get_float("iou_normalizer", .75f);
+        L.cls_normalizer = s.get_float("cls_normalizer", 1.f);
+        L.label_smooth_eps = s.get_float("label_smooth_eps", 0.f);
+        L.max_delta = s.get_float("max_delta", 3.402823466e+38F);
+      }
       const int E = (L.type == L_YOLO ? 5 : 9) + L.classes;
       if ((int)L.mask.size() * E != c)
         NET_FAIL(YC_ERR_ARG, "layer %d: filters=%d does not correspond to classes/mask (want %d) (parser.cpp:323-330)", idx, c,
@@ -190,6 +211,7 @@ int load_weights_file(yc_network* net, const char* path) {
 }
 
 int free_device_state(yc_network* net) {
+  yc_train_free(net);
   if (net->graph_exec) { cudaGraphExecDestroy(net->graph_exec); net->graph_exec = nullptr; }
   if (net->graph) { cudaGraphDestroy(net->graph); net->graph = nullptr; }
   for (NLayer& L : net->layers) {
@@ -252,6 +274,8 @@ extern "C" int yc_network_finalize(yc_network* net) {
   }
   free_device_state(net);
   const int nl = (int)net->layers.size();
+  if (net->flags & YC_NET_TRAIN)  // training keeps batchnorm live and every layer's own output; ops run un-graphed
+    net->flags &= ~(YC_NET_FUSE_BN | YC_NET_FUSE_SHORTCUT | YC_NET_CUDA_GRAPH | YC_NET_PULL_HEADS);
   const int flags = net->flags;
   auto& Ls = net->layers;
   if (!net->stream) NET_CUDA(cudaStreamCreateWithFlags(&net->stream, cudaStreamNonBlocking));
@@ -334,6 +358,12 @@ extern "C" int yc_network_finalize(yc_network* net) {
   NET_CUDA(cudaMalloc(&net->input_nhwc, (size_t)net->batch * net->h * net->w * in_ldc * 2));
   NET_CUDA(cudaMemset(net->input_nhwc, 0, (size_t)net->batch * net->h * net->w * in_ldc * 2));
 
+  if (flags & YC_NET_TRAIN) {
+    int rc = yc_train_finalize(net);
+    if (rc) return rc;
+    net->finalized = true;
+    return YC_OK;
+  }
   // ---- parameters: fuse BN (FuseConvBatchNorm network.cpp:647-682), pack, upload ----------------------
   for (int i = 0; i < nl; ++i) {
     NLayer& L = Ls[i];
@@ -583,6 +613,7 @@ static int ensure_graph(yc_network* net, const float* input_dev) {
 
 extern "C" int yc_network_forward(yc_network* net, const float* input_dev, void* stream) {
   YC_REQUIRE(net && input_dev, "yc_network_forward: null argument");
+  YC_REQUIRE(!(net->flags & YC_NET_TRAIN), "yc_network_forward: network was loaded for training (use yc_network_forward_backward)");
   if (!net->finalized) {
     int rc = yc_network_finalize(net);
     if (rc) return rc;

@@ -53,6 +53,34 @@ struct NLayer {
   int dtype = YC_BF16;
   std::vector<std::pair<int, int>> copies;  // route fallback: (input layer, dst channel offset)
   int consumers = 0;
+  // ---- training state (network_train.cu; allocated only with YC_NET_TRAIN) ----
+  // yolo hyper-parameters (ParseYolo parser.cpp:312-415)
+  int max_boxes = 90, iou_loss = 2 /*MSE*/, iou_thresh_kind = 0, focal_loss = 0;
+  float ignore_thresh = .5f, truth_thresh = 1.f, iou_thresh = 1.f, iou_normalizer = .75f, cls_normalizer = 1.f,
+        label_smooth_eps = 0.f, max_delta = 3.402823466e+38F;
+  float* w_master = nullptr;     // fp32 OIHW (l->weights_gpu)
+  float* rmean_dev = nullptr;    // l->rolling_mean_gpu
+  float* rvar_dev = nullptr;
+  float* mean_dev = nullptr;     // l->mean_gpu
+  float* var_dev = nullptr;
+  float* stats_dev = nullptr;    // [2][n]: sum, sum of squares accumulated by the conv epilogue
+  float* ws_dev = nullptr;       // 5n floats of batchnorm-backward workspace
+  float* dw_packed = nullptr;    // l->weight_updates_gpu, [n][tap][ldw] fp32
+  size_t bucket_floats = 0;      // dw_packed + bias_upd + scale_upd, contiguous (one all-reduce per layer)
+  float* bias_upd = nullptr;     // l->bias_updates_gpu
+  float* scale_upd = nullptr;    // l->scale_updates_gpu
+  void* w_packed_d = nullptr;    // data-gradient operand packing
+  void* z_buf = nullptr;         // bf16 NHWC pre-batchnorm conv output (l->x_gpu)
+  int z_ldc = 0;
+  void* delta_buf = nullptr;     // bf16 NHWC l->delta_gpu (inside the network's delta slab)
+  int delta_ldc = 0;
+  void* dil_buf = nullptr;       // zero-inserted dz of strided layers
+  int dil_h = 0, dil_w = 0;
+  unsigned char* idx_buf = nullptr;  // maxpool winners (l->indexes_gpu)
+  yc_wgrad_plan* wplan = nullptr;
+  yc_conv_plan* dplan = nullptr;
+  float* ydelta = nullptr;       // yolo: fp32 NCHW l->delta_gpu
+  float* ystats = nullptr;       // yolo: 8 floats (cost, count, ...)
 };
 
 struct Op {
@@ -86,7 +114,28 @@ struct yc_network {
   int* det_img_counts_host = nullptr;
   int det_cap = 0, det_dense_cap = 0, det_R = 0;
   std::vector<float> det_rows_out;
+  // ---- training (network_train.cu) ----
+  float lr = .001f, momentum = .9f, decay = .0001f;  // [net] learning_rate / momentum / decay (parser.cpp:1116-1140)
+  int subdivisions = 1;
+  int train_flags = 0;
+  void* delta_slab = nullptr;
+  size_t delta_slab_bytes = 0;
+  float* truth_dev = nullptr;     // [batch][max_boxes*5] (*net->truth_gpu)
+  float* truth_pinned = nullptr;
+  int truth_floats = 0;
+  float* cost_host = nullptr;     // pinned: 8 floats per yolo layer
+  std::vector<Op> bwd_ops;
+  long long seen = 0;
+  void* dp = nullptr;             // data-parallel context (NCCL), network_dp.cu
 };
+
+// network_train.cu
+int yc_train_finalize(yc_network* net);
+void yc_train_free(yc_network* net);
+// network_dp.cu: called by the backward pass right after layer i's weight gradient has been enqueued on `compute`
+int yc_dp_layer_ready(yc_network* net, int layer, cudaStream_t compute);
+int yc_dp_backward_done(yc_network* net, cudaStream_t compute);
+void yc_dp_free(yc_network* net);
 
 
 #define NET_FAIL(code, ...)   \

@@ -48,6 +48,7 @@ class Detection(C.Structure):
 
 NET_FUSE_BN, NET_FUSE_SHORTCUT, NET_ELIDE_ROUTE, NET_CUDA_GRAPH, NET_PULL_HEADS, NET_REF_CPU_MAXPOOL = 1, 2, 4, 8, 16, 32
 NET_DEFAULT = 1 | 2 | 4 | 8 | 16
+NET_TRAIN, NET_DGRAD_ACCUMULATE, NET_BN_BIAS_GRAD = 64, 128, 256
 
 _lib = None
 
@@ -128,6 +129,16 @@ _SIGS = {
     "yc_network_layer_output": (C.c_int, [_P, C.c_int, _P]),
     "yc_network_yolo_output": (_P, [_P, C.c_int]),
     "yc_network_profile": (C.c_int, [_P, _P, C.c_int, _P]),
+    "yc_network_train_datum": (C.c_int, [_P, _P, _P, C.POINTER(C.c_float)]),
+    "yc_network_forward_backward": (C.c_int, [_P, _P, _P, _P]),
+    "yc_network_update": (C.c_int, [_P, C.c_float, C.c_float, C.c_float, _P]),
+    "yc_network_train_info": (C.c_int, [_P, C.c_int]),
+    "yc_network_layer_delta": (C.c_int, [_P, C.c_int, _P]),
+    "yc_network_get_param": (C.c_int, [_P, C.c_int, C.c_char_p, _P, C.c_int]),
+    "yc_dp_unique_id": (C.c_int, [_P]),
+    "yc_dp_nccl_version": (C.c_int, []),
+    "yc_network_dp_init": (C.c_int, [_P, _P, C.c_int, C.c_int]),
+    "yc_network_dp_info": (C.c_int, [_P, C.c_int]),
     "yc_network_get_boxes": (C.POINTER(Detection), [_P, C.c_int, C.c_float, C.POINTER(C.c_int)]),
     "yc_free_detections": (None, [C.POINTER(Detection), C.c_int]),
     "yc_nms_sort": (None, [C.POINTER(Detection), C.c_int, C.c_int, C.c_float, C.c_int, C.c_float]),

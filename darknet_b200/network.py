@@ -238,3 +238,49 @@ def DetectBatch(net: Network, thresh: float, nms_thresh: float = 0.45):
     if total.value == 0:
         return np.zeros((0, R), np.float32), counts
     return np.ctypeslib.as_array(rows, shape=(total.value, R)).copy(), counts
+
+
+# ---- training: TrainNetworkDatum / UpdateNetwork mirrors (network.cpp:116-208) -------------------------------------
+def TrainNetworkDatum(net: Network, x: np.ndarray, truth: np.ndarray) -> float:
+    """TrainNetworkDatum (network.cpp:188-208): forward + backward on host x [batch,c,h,w] and truth
+    [batch, max_boxes*5]; returns GetNetworkCost.  The network must be loaded with NET_TRAIN."""
+    x = np.ascontiguousarray(x, np.float32)
+    truth = np.ascontiguousarray(truth, np.float32)
+    tf = L.lib().yc_network_train_info(net.h, 0)
+    assert x.size == net.batch * net.c * net.hh * net.w, "input size != batch*c*h*w"
+    assert truth.size == net.batch * tf, f"truth size != batch*{tf}"
+    cost = C.c_float(0)
+    L.check(L.lib().yc_network_train_datum(net.h, x.ctypes.data_as(C.c_void_p), truth.ctypes.data_as(C.c_void_p),
+                                           C.byref(cost)), "TrainNetworkDatum")
+    return float(cost.value)
+
+
+def ForwardBackwardNetworkGpu(net: Network, input_dev_ptr: int, truth_dev_ptr: int, stream=None):
+    """ForwardBackwardNetworkGpu (network_kernels.cu:245-267) on device-resident input/truth; asynchronous."""
+    L.check(L.lib().yc_network_forward_backward(net.h, C.c_void_p(input_dev_ptr), C.c_void_p(truth_dev_ptr),
+                                                stream if stream is not None else L.stream_ptr()),
+            "ForwardBackwardNetworkGpu")
+
+
+def UpdateNetwork(net: Network, lr=-1.0, momentum=-1.0, decay=-1.0, stream=None):
+    """UpdateNetwork (network.cpp:116-128): SGD on every conv layer; negative values take the cfg's [net] entries."""
+    L.check(L.lib().yc_network_update(net.h, lr, momentum, decay, stream), "UpdateNetwork")
+
+
+def layer_delta(net: Network, i):
+    """fp32 NCHW copy of l->delta of layer i."""
+    out = np.empty(net.layer_shape(i), np.float32)
+    L.check(L.lib().yc_network_layer_delta(net.h, i, out.ctypes.data_as(C.c_void_p)), "yc_network_layer_delta")
+    return out
+
+
+def layer_param(net: Network, i, key, capacity=None):
+    """l-><key> of layer i (weights, biases, scales, rolling_mean, ..., weight_updates, cost) in reference layout."""
+    if capacity is None:
+        n, cin, k = net.layer_info(i, 1), net.layer_info(i, 5), net.layer_info(i, 6)
+        capacity = max(n * cin * k * k, 8)
+    out = np.empty(capacity, np.float32)
+    r = L.lib().yc_network_get_param(net.h, i, key.encode(), out.ctypes.data_as(C.c_void_p), capacity)
+    if r < 0:
+        raise L.YcError(f"yc_network_get_param({i}, {key}): " + L.lib().yc_last_error().decode())
+    return out[:r].copy()

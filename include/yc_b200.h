@@ -271,6 +271,13 @@ enum {
   YC_NET_PULL_HEADS = 16,    /* D2H every YOLO layer output after forward like the reference
                                 (yolo_layer.cpp:856); off: heads stay on the device (use yc_network_detect) */
   YC_NET_REF_CPU_MAXPOOL = 32, /* reproduce forward_maxpool_layer_avx's artefact (see yc_maxpool_fwd) */
+  YC_NET_TRAIN = 64,         /* LoadNetwork(train=true): batchnorm uses batch statistics, every layer keeps delta
+                                buffers, conv layers keep fp32 master weights + gradient accumulators */
+  YC_NET_DGRAD_ACCUMULATE = 128, /* data gradient ADDS to the previous layer's delta (cuDNN beta=1,
+                                convolutional_kernels.cu:735-738) instead of overwriting it like col2im (col2im.c:70, the
+                                reference CPU path's behaviour and this library's parity default) */
+  YC_NET_BN_BIAS_GRAD = 256, /* also accumulate the batchnorm shift's gradient into bias_updates (the reference GPU path;
+                                its CPU path leaves it at zero) */
   YC_NET_DEFAULT = 1 | 2 | 4 | 8 | 16
 };
 
@@ -311,6 +318,36 @@ YC_API const float* yc_network_yolo_output(yc_network* net, int layer);
 /* per-layer device time of one un-graphed forward, averaged over iters (net->benchmark_layers,
  * network_kernels.cu:70-94).  ms_per_layer has n_layers entries (+1: the input conversion at index n). */
 YC_API int yc_network_profile(yc_network* net, const float* input_dev_nchw, int iters, float* ms_per_layer);
+
+/* ---- training step: replaces TrainNetworkDatumGpu / ForwardBackwardNetworkGpu / UpdateNetworkGpu -------------- */
+/* (network_kernels.cu:116-293; CPU twins network.cpp:101-208.)  The network must be loaded with YC_NET_TRAIN.
+ * truth = [batch][max_boxes*5] floats (x, y, w, h, class id), the reference's net->truth layout. */
+/* TrainNetworkDatum: host input + truth -> forward + backward (no update); *cost = GetNetworkCost. Synchronous. */
+YC_API int yc_network_train_datum(yc_network* net, const float* x_host, const float* truth_host, float* cost);
+/* ForwardBackwardNetworkGpu on device-resident fp32 NCHW input and truth; asynchronous on `stream`. */
+YC_API int yc_network_forward_backward(yc_network* net, const float* input_dev_nchw, const float* truth_dev, void* stream);
+/* UpdateNetworkGpu: SGD step on every conv layer; negative lr/momentum/decay take the cfg's [net] values;
+ * batch = net batch * subdivisions (x data-parallel world size).  stream NULL = the network's own stream. */
+YC_API int yc_network_update(yc_network* net, float lr, float momentum, float decay, void* stream);
+/* what: 0 truth floats per image, 1 subdivisions, 2 delta slab MiB */
+YC_API int yc_network_train_info(const yc_network* net, int what);
+/* cuda_pull_array(l->delta_gpu): fp32 NCHW [batch,out_c,out_h,out_w] */
+YC_API int yc_network_layer_delta(yc_network* net, int layer, float* dst_host);
+/* PullConvolutionalLayer by name ("weights", "biases", "scales", "rolling_mean", "rolling_variance", "mean", "variance",
+ * "weight_updates", "bias_updates", "scale_updates"; yolo: "cost", "stats"), reference layouts. Returns floats written. */
+YC_API int yc_network_get_param(yc_network* net, int layer, const char* key, float* dst_host, int capacity);
+
+/* ---- data-parallel training: replaces TrainNetworks / SyncNetworks (network_kernels.cu:295-484) ------------------- */
+/* One process per GPU.  Rank 0 calls yc_dp_unique_id (ncclGetUniqueId, 128 bytes) and the host plumbing hands the id
+ * to every rank; every rank then calls yc_network_dp_init (collective).  From then on yc_network_forward_backward
+ * all-reduces (sum, fp32) each conv layer's gradient bucket [weight_updates | bias_updates | scale_updates] over
+ * NCCL / NVLink on a separate stream as soon as that layer's weight gradient is enqueued, overlapping the rest of
+ * the backward pass, and yc_network_update divides by the global batch.  Needs subdivisions=1. */
+YC_API int yc_dp_unique_id(void* out128);
+YC_API int yc_dp_nccl_version(void);
+YC_API int yc_network_dp_init(yc_network* net, const void* unique_id128, int rank, int world);
+/* what: 0 world, 1 rank, 2 buckets per step, 3 MiB all-reduced per step */
+YC_API int yc_network_dp_info(const yc_network* net, int what);
 
 /* Detection == the reference's struct Detection minus unused members (yolo_core.h:598-609). */
 typedef struct yc_detection {

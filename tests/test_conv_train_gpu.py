@@ -23,6 +23,10 @@ def _relmax(got, ref):
     return float(np.abs(got - ref).max() / (np.abs(ref).max() + 1e-12))
 
 
+def _rell2(got, ref):
+    return float(np.linalg.norm((got - ref).ravel()) / (np.linalg.norm(ref.ravel()) + 1e-30))
+
+
 def _case(gpu, B, C, H, W, N, k, stride, act, bn=True, seed=0, accumulate=False, pre_dw=False):
     from darknet_b200 import ops
     rng = np.random.default_rng(seed)
@@ -79,11 +83,13 @@ def _case(gpu, B, C, H, W, N, k, stride, act, bn=True, seed=0, accumulate=False,
     tol = 2e-2 if bn else 1e-2
     got_dz = ops.to_nchw(conv.dz, N).cpu().numpy()
     assert _relmax(got_dz, ref["delta"]) < tol, f"dz {_relmax(got_dz, ref['delta']):.3e}"
+    assert _rell2(got_dz, ref["delta"]) < 1e-2, f"dz rel-L2 {_rell2(got_dz, ref['delta']):.3e}"
     if conv.cd > N:
         assert float(conv.dz[..., N:].abs().max()) == 0.0, "pad lanes of dz must be zero"
     got_dw = conv.weight_updates().cpu().numpy()
     e_dw = _relmax(got_dw, ref["weight_updates"])
     assert e_dw < tol, f"weight_updates {e_dw:.3e} {conv.winfo()}"
+    assert _rell2(got_dw, ref["weight_updates"]) < 1e-2, f"weight_updates rel-L2 {_rell2(got_dw, ref['weight_updates']):.3e}"
     if bn:
         e_su = _relmax(conv.scale_updates.cpu().numpy(), ref["scale_updates"])
         assert e_su < tol, f"scale_updates {e_su:.3e}"
@@ -94,6 +100,7 @@ def _case(gpu, B, C, H, W, N, k, stride, act, bn=True, seed=0, accumulate=False,
     want_dx = ref["dx"] + (dx0 if accumulate else 0)
     e_dx = _relmax(got_dx, want_dx)
     assert e_dx < tol, f"dx {e_dx:.3e}"
+    assert _rell2(got_dx, want_dx) < 1e-2, f"dx rel-L2 {_rell2(got_dx, want_dx):.3e}"
     return e_fwd, e_dw, e_dx
 
 

@@ -1,0 +1,145 @@
+"""Whole-network training step through the C ABI (yc_network_train_datum / yc_network_update) against the UNMODIFIED
+reference CPU path (ForwardNetwork(train) + BackwardNetwork + UpdateNetwork, network.cpp:101-208) on the same cfg,
+the same weights file, the same synthetic images and truth.
+
+This is the FREE-RUNNING comparison: both sides start from the same fp32 inputs and never exchange state.  In training
+mode that comparison is intrinsically loose at bf16, for two measured reasons (tools/train_diag.py):
+  * batchnorm with batch statistics removes the DC part of every layer's input signal but not of the rounding noise,
+    so the relative forward error grows ~1.2x per layer (4.6e-3 at layer 0 -> 6e-2 at layer 28 of yolov4-tiny);
+  * leaky' is discontinuous: every element whose pre-activation lies within the forward error of 0 takes the other
+    branch (factor 10) than in the fp32 reference; 1-2 % of flipped elements are 15-40 % of the gradient's L2 norm.
+The tight statements are made elsewhere: every operator against the oracle on identical saved state
+(tests/test_conv_train_gpu.py, <= 1e-2 rel-L2), the loss against the reference on identical heads
+(tests/test_yolo_loss_gpu.py, 2e-5), and the whole step against the bf16-emulating CPU walker (tests/test_train_emul_gpu.py).
+Here: loss within 2e-2, outputs within 1e-1 rel-L2, head-layer gradients within 3e-2, every other gradient must point
+the same way (cosine >= 0.8) and have the same magnitude within 25 %.
+"""
+import numpy as np
+import pytest
+
+from darknet_b200 import cfg as cfgmod
+from oracle import pyoracle
+from tests import netutil
+from tests.netutil import rel_l2, rel_to_max
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(name, B, **kw):
+    from darknet_b200 import lib as L, network as N
+    if not pyoracle.have_ref():
+        pytest.skip("oracle/_ref not built")
+    text, cpath, wpath = netutil.materialise(name, batch=B, subdivisions=1, **kw)
+    ref = pyoracle.RefNet(cpath, wpath, train=True)
+    net = N.LoadNetwork(cpath, wpath, batch=B, flags=L.NET_DEFAULT | L.NET_TRAIN)
+    sh = cfgmod.walk_shapes(text)
+    return text, ref, net, sh
+
+
+def _cos(a, b):
+    return float(np.dot(a.ravel(), b.ravel()) / (np.linalg.norm(a.ravel()) * np.linalg.norm(b.ravel()) + 1e-30))
+
+
+def _same_direction(a, b, what, cos_min=0.8, mag=0.25):
+    c = _cos(a, b)
+    r = np.linalg.norm(a.ravel()) / (np.linalg.norm(b.ravel()) + 1e-30)
+    assert c >= cos_min and abs(r - 1) <= mag, f"{what}: cosine {c:.3f}, norm ratio {r:.3f}"
+    return 1 - c
+
+
+def _check_step(ref, net, x, truth, tol_fwd=1e-1, tol_grad=3e-2, tol_loss=2e-2):
+    from darknet_b200 import network as N
+    cost_ref = ref.forward_backward(x, truth)
+    cost = N.TrainNetworkDatum(net, x, truth)
+    assert abs(cost - cost_ref) <= tol_loss * abs(cost_ref), f"cost {cost} vs reference {cost_ref}"
+    worst = {"out": 0.0, "wu": 0.0, "su": 0.0, "bu": 0.0, "delta": 0.0, "mean": 0.0, "var": 0.0}
+    for i in range(net.n):
+        t = net.layer_type(i)
+        o_ref = ref.layer_output(i)
+        e = rel_l2(net.layer_output(i), o_ref)
+        worst["out"] = max(worst["out"], e)
+        assert e < tol_fwd, f"layer {i} ({t}) output rel-L2 {e:.3e}"
+        if t == "yolo":
+            d = N.layer_delta(net, i)
+            dr = ref.layer_buf(i, "delta").reshape(d.shape)
+            # obj/class deltas follow the bf16 head: compare with the tolerance of the forward
+            e = rel_l2(d, dr)
+            worst["delta"] = max(worst["delta"], e)
+            assert e < 1e-1, f"yolo layer {i} delta rel-L2 {e:.3e}"
+        if t != "convolutional":
+            continue
+        bn = net.layer_info(i, 9)
+        wu, wur = N.layer_param(net, i, "weight_updates"), ref.layer_buf(i, "weight_updates")
+        if bn:
+            worst["wu"] = max(worst["wu"], _same_direction(wu, wur, f"layer {i} weight_updates"))
+        else:  # head convs: their delta is the YOLO delta itself
+            e = rel_l2(wu, wur)
+            assert e < tol_grad, f"layer {i} (head) weight_updates rel-L2 {e:.3e}"
+        if bn:
+            for key in ("mean", "variance"):
+                a, b = N.layer_param(net, i, key), ref.layer_buf(i, key)
+                e = rel_to_max(a, b)
+                worst["mean" if key == "mean" else "var"] = max(worst["mean" if key == "mean" else "var"], e)
+                assert e < 3e-2 or np.abs(a - b).max() < 2e-3, f"layer {i} {key} {e:.3e}"
+            worst["su"] = max(worst["su"], _same_direction(N.layer_param(net, i, "scale_updates"),
+                                                           ref.layer_buf(i, "scale_updates"), f"layer {i} scale_updates",
+                                                           cos_min=0.7, mag=0.35))
+            bu = N.layer_param(net, i, "bias_updates")
+            assert np.abs(bu).max() == 0.0 and np.abs(ref.layer_buf(i, "bias_updates")).max() == 0.0
+        else:
+            e = rel_l2(N.layer_param(net, i, "bias_updates"), ref.layer_buf(i, "bias_updates"))
+            worst["bu"] = max(worst["bu"], e)
+            assert e < tol_grad, f"layer {i} bias_updates rel-L2 {e:.3e}"
+    return cost, cost_ref, worst
+
+
+@pytest.mark.parametrize("act", ["leaky", "mish"])
+def test_micro_train_step(gpu, act):
+    """micro net: conv s1/s2 + BN + leaky/mish, shortcut, grouped route, multi-route, SPP + 2/2 maxpool, upsample, 2 heads."""
+    from darknet_b200 import network as N
+    B = 4
+    text, ref, net, sh = _setup("micro", B, act=act)
+    x = cfgmod.synth_images(B, 3, 64, 64, seed=5)
+    truth = cfgmod.synth_truth(B, 90, classes=3, seed=6)
+    cost, cost_ref, worst = _check_step(ref, net, x, truth)
+    print("micro", act, cost, cost_ref, worst)
+    # UpdateNetwork: SGD with momentum/decay, then a second step from the updated weights
+    convs = [i for i in range(net.n) if net.layer_type(i) == "convolutional"]
+    before = {i: (N.layer_param(net, i, "weights"), N.layer_param(net, i, "weight_updates"), N.layer_param(net, i, "biases"),
+                  N.layer_param(net, i, "bias_updates")) for i in convs}
+    ref.L.ref_update(ref.h)
+    N.UpdateNetwork(net)
+    lr, mom, decay = 0.001, 0.9, 0.0005   # the cfg's [net] values (cfgs._Cfg)
+    for i in convs:
+        # the SGD arithmetic itself, exactly (UpdateConvolutionalLayer, convolutional_layer.cpp:1382-1400), on the
+        # GPU's own gradient ...
+        w0, g0, b0, gb0 = before[i]
+        g1 = g0 - decay * B * w0
+        w, g = N.layer_param(net, i, "weights"), N.layer_param(net, i, "weight_updates")
+        np.testing.assert_allclose(w, w0 + (lr / B) * g1, rtol=1e-6, atol=1e-7)
+        np.testing.assert_allclose(g, mom * g1, rtol=1e-6, atol=1e-7)
+        np.testing.assert_allclose(N.layer_param(net, i, "biases"), b0 + (lr / B) * gb0, rtol=1e-6, atol=1e-7)
+        # ... and against the reference's updated weights (limited by the free-running gradient error)
+        wr = ref.layer_buf(i, "weights")
+        assert rel_l2(w, wr) < 5e-3, f"layer {i} weights after update {rel_l2(w, wr):.3e}"
+        assert _cos(g, ref.layer_buf(i, "weight_updates")) > 0.8
+    x2 = cfgmod.synth_images(B, 3, 64, 64, seed=15)
+    truth2 = cfgmod.synth_truth(B, 90, classes=3, seed=16)
+    # second step from the updated weights: gradients accumulate on top of momentum * previous (B7).  The two sides'
+    # weights now differ by the first step's gradient error times lr/batch (a few 1e-3 relative), which the untrained
+    # net's forward amplifies: the loss is only required to stay within 20 %.
+    _check_step(ref, net, x2, truth2, tol_loss=0.2, tol_fwd=0.25)
+    ref.close()
+    net.close()
+
+
+def test_yolov4_tiny_train_step(gpu):
+    """BASELINE config 4 at reduced batch (CPU reference backward uses scalar gemm_nt/gemm_tn): yolov4-tiny 416, B=2."""
+    B = 2
+    text, ref, net, sh = _setup("yolov4-tiny", B, w=416, h=416)
+    x = cfgmod.synth_images(B, 3, 416, 416, seed=5)
+    truth = cfgmod.synth_truth(B, 90, classes=80, seed=6)
+    cost, cost_ref, worst = _check_step(ref, net, x, truth)
+    print("yolov4-tiny", cost, cost_ref, worst)
+    ref.close()
+    net.close()

@@ -1,0 +1,104 @@
+"""Data-parallel gradient all-reduce check (run under torchrun, one rank per GPU):
+   torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/dp_check.py
+Every rank trains the same net on ITS shard of the batch.  Checks that after yc_network_forward_backward with the NCCL
+all-reduce enabled every rank holds the SUM of the per-rank gradients (gathered with torch.distributed for the check),
+that two steps with updates keep the replicas' weights bit-identical, and prints the overlap timing."""
+import ctypes as C
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from darknet_b200 import cfg as cfgmod, cfgs, lib as L, network as N
+from darknet_b200 import dp
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    L.check(L.lib().yc_set_device(local), "yc_set_device")
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    name = sys.argv[1] if len(sys.argv) > 1 else "micro"
+    B = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+    hw = 64 if name == "micro" else 416
+    classes = 3 if name == "micro" else 80
+    kw = {} if name == "micro" else dict(w=hw, h=hw)
+    text = cfgs.CONFIGS[name](batch=B, subdivisions=1, **kw)
+    weights = cfgmod.synth_weights(text)
+    flags = L.NET_DEFAULT | L.NET_TRAIN
+
+    def fresh():
+        return N.LoadSynthetic(text, weights, batch=B, flags=flags)
+
+    # the global batch, sharded by rank (GetPartialData, data.cpp:890-901)
+    xg = cfgmod.synth_images(B * world, 3, hw, hw, seed=5)
+    tg = cfgmod.synth_truth(B * world, 90, classes=classes, seed=6)
+    x, t = dp.shard(xg, rank, world), dp.shard(tg, rank, world)
+
+    # 1. local gradients without communication
+    net0 = fresh()
+    N.TrainNetworkDatum(net0, x, t)
+    convs = [i for i in range(net0.n) if net0.layer_type(i) == "convolutional"]
+    local_g = {i: torch.from_numpy(N.layer_param(net0, i, "weight_updates")).cuda() for i in convs}
+    net0.close()
+    # 2. with the all-reduce
+    net = fresh()
+    dp.init(net, dist)
+    cost = N.TrainNetworkDatum(net, x, t)
+    worst = 0.0
+    for i in convs:
+        want = local_g[i].clone()
+        dist.all_reduce(want)
+        got = torch.from_numpy(N.layer_param(net, i, "weight_updates")).cuda()
+        err = float((got - want).abs().max() / (want.abs().max() + 1e-30))
+        worst = max(worst, err)
+    # 3. replicas stay identical through updates
+    N.UpdateNetwork(net)
+    N.TrainNetworkDatum(net, x, t)
+    N.UpdateNetwork(net)
+    same = True
+    for i in convs:
+        w = torch.from_numpy(N.layer_param(net, i, "weights")).cuda()
+        w0 = w.clone()
+        dist.broadcast(w0, 0)
+        same = same and bool(torch.equal(w, w0))
+    # 4. timing: step with and without the all-reduce (device events, max over ranks)
+    xd = torch.from_numpy(x).cuda()
+    td = torch.from_numpy(t).cuda()
+    st = torch.cuda.current_stream()
+
+    def timed(n, iters=10):
+        for _ in range(3):
+            N.ForwardBackwardNetworkGpu(n, xd.data_ptr(), td.data_ptr())
+        torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st)
+        for _ in range(iters):
+            N.ForwardBackwardNetworkGpu(n, xd.data_ptr(), td.data_ptr())
+        e1.record(st)
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda")
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    ms_dp = timed(net)
+    net1 = fresh()
+    ms_local = timed(net1)
+    if rank == 0:
+        print(json.dumps({"dp_check": name, "world": world, "batch_per_gpu": B, "cost_rank0": cost,
+                          "allreduce_max_rel_err": worst, "replicas_identical_after_2_updates": same,
+                          "ms_step_with_allreduce": ms_dp, "ms_step_local_only": ms_local,
+                          "buckets": L.lib().yc_network_dp_info(net.h, 2), "mib_per_step": L.lib().yc_network_dp_info(net.h, 3),
+                          "nccl": L.lib().yc_dp_nccl_version()}))
+        assert worst < 1e-5 and same
+    dist.barrier()
+    net.close(); net1.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
