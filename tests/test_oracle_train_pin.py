@@ -93,3 +93,75 @@ def test_conv_train_restatement_vs_reference(act, s):
     assert np.abs(r0["scale_updates"] - su).max() <= 2e-4 * np.abs(su).max() + 1e-6
     assert np.abs(ref.layer_buf(0, "bias_updates")).max() == 0.0   # the BN shift gets no gradient on the CPU path
     ref.close()
+
+
+@pytest.mark.parametrize("act", ["mish", "leaky"])
+def test_training_walker_fp32_vs_reference(act):
+    """oracle/pytrain.py in fp32 mode (whole micro net, two steps with an SGD update in between) == the unmodified
+    reference.  mish is smooth: everything to 1e-4.  leaky' jumps at 0, so a handful of elements whose pre-activation
+    is ~1e-6 flip under a different summation order even in fp32: gradients to 8e-2, everything else tight."""
+    from oracle import pytrain
+    from tests import netutil
+    from tests.netutil import rel_l2
+    B = 4
+    text, cpath, wpath = netutil.materialise("micro", batch=B, subdivisions=1, act=act)
+    ref = pyoracle.RefNet(cpath, wpath, train=True)
+    W, _ = cfgmod.read_weights(wpath, text)
+    st = pytrain.Step(text, W)
+    tol_g = 1e-4 if act == "mish" else 8e-2
+    for step in range(2):
+        x = cfgmod.synth_images(B, 3, 64, 64, seed=5 + step)
+        truth = cfgmod.synth_truth(B, 90, classes=3, seed=6 + step)
+        cr = ref.forward_backward(x, truth)
+        c = st.forward_backward(x, truth)
+        assert abs(c - cr) <= 1e-4 * abs(cr)
+        for L in st.layers:
+            i = L.index
+            assert rel_l2(st.out[i], ref.layer_output(i)) < (1e-4 if act == "mish" else 2e-3)
+            d = ref.layer_buf(i, "delta")
+            if d is not None:
+                assert rel_l2(st.delta[i], d.reshape(st.delta[i].shape)) < tol_g, (i, L.kind)
+            if i in st.P:
+                assert rel_l2(st.P[i]["weight_updates"].ravel(), ref.layer_buf(i, "weight_updates")) < tol_g
+                if L.bn:
+                    assert rel_l2(st.P[i]["scale_updates"], ref.layer_buf(i, "scale_updates")) < tol_g
+                    assert rel_l2(st.saved[i]["var"], ref.layer_buf(i, "variance")) < (1e-4 if act == "mish" else 2e-3)
+                    assert rel_l2(st.P[i]["rolling_variance"], ref.layer_buf(i, "rolling_variance")) < (1e-4 if act == "mish" else 2e-3)
+                else:
+                    assert rel_l2(st.P[i]["bias_updates"], ref.layer_buf(i, "bias_updates")) < 1e-4
+        ref.L.ref_update(ref.h)
+        st.update()
+        for i in st.P:
+            assert rel_l2(st.P[i]["weights"].ravel(), ref.layer_buf(i, "weights")) < (1e-5 if act == "mish" else 2e-3)
+    ref.close()
+
+
+@pytest.mark.parametrize("iou_loss", ["ciou", "mse", "giou", "diou"])
+def test_yolo_loss_restatement_vs_reference(iou_loss):
+    """oracle/yc_oracle_loss.c == the reference's ForwardYoloLayer(train) on the reference's own decoded heads."""
+    from darknet_b200 import cfgs
+    from oracle import pytrain
+    from tests import netutil
+    B, classes = 4, 3
+    text = cfgs.micro(batch=B, subdivisions=1, classes=classes).replace("iou_loss=ciou", "iou_loss=" + iou_loss)
+    d = tempfile.mkdtemp(prefix="yc_pin_")
+    cpath, wpath = os.path.join(d, "n.cfg"), os.path.join(d, "n.weights")
+    open(cpath, "w").write(text)
+    cfgmod.write_weights(wpath, text, cfgmod.synth_weights(text, seed=42))
+    ref = pyoracle.RefNet(cpath, wpath, train=True)
+    x = cfgmod.synth_images(B, 3, 64, 64, seed=11)
+    truth = cfgmod.synth_truth(B, 90, classes=classes, seed=12)
+    ref.forward(x, truth, train=1)
+    _, layers = cfgmod.walk_shapes(text)
+    for L in layers:
+        if L.kind != "yolo":
+            continue
+        out = ref.layer_output(L.index)
+        mask = [int(v) for v in L.opts["mask"].split(",")]
+        anchors = [float(v) for v in L.opts["anchors"].split(",")]
+        delta, cost = pytrain.yolo_loss(out, truth, anchors, mask, L.opts, 64, 64)
+        dref = ref.layer_buf(L.index, "delta").reshape(out.shape)
+        assert np.abs(delta - dref).max() < 2e-5
+        cref = float(ref.layer_buf(L.index, "cost")[0])
+        assert abs(cost - cref) <= 1e-4 * abs(cref) + 1e-5
+    ref.close()
