@@ -198,6 +198,23 @@ int yc_train_finalize(yc_network* net) {
 
 namespace {
 
+// Optional per-category device timing of one step (yc_network_train_profile): an event after every operator; the
+// time since the previous event belongs to that operator's category.
+enum { CAT_FPROP = 0, CAT_WGRAD = 1, CAT_DGRAD = 2, CAT_BN = 3, CAT_OTHER = 4, CAT_COUNT = 5 };
+struct Prof {
+  std::vector<cudaEvent_t> ev;
+  std::vector<int> cat;
+};
+Prof* g_prof = nullptr;
+inline void tick(int cat, cudaStream_t st) {
+  if (!g_prof) return;
+  cudaEvent_t e;
+  cudaEventCreate(&e);
+  cudaEventRecord(e, st);
+  g_prof->ev.push_back(e);
+  g_prof->cat.push_back(cat);
+}
+
 // ForwardNetworkGpu with state.train (network_kernels.cu:45-114)
 int train_forward(yc_network* net, const float* input_dev, const float* truth_dev, cudaStream_t st) {
   const int nl = (int)net->layers.size();
@@ -208,6 +225,7 @@ int train_forward(yc_network* net, const float* input_dev, const float* truth_de
     yc_tensor in{net->input_nhwc, B, net->h, net->w, net->c, round_up(net->c, 8), YC_BF16};
     int rc = yc_nchw_to_nhwc(input_dev, &in, st);
     if (rc) return rc;
+    tick(CAT_OTHER, st);
   }
   for (int i = 0; i < nl; ++i) {
     NLayer& L = Ls[i];
@@ -215,12 +233,15 @@ int train_forward(yc_network* net, const float* input_dev, const float* truth_de
     switch (L.type) {
       case L_CONV: {
         if (L.bn) NET_CUDA(cudaMemsetAsync(L.stats_dev, 0, sizeof(float) * 2 * L.n, st));
+        tick(CAT_OTHER, st);
         rc = yc_conv_fprop(L.plan, st);
+        tick(CAT_FPROP, st);
         if (!rc && L.bn) {
           rc = yc_bn_finalize(L.stats_dev, L.stats_dev + L.n, (long long)B * L.out_h * L.out_w, L.mean_dev, L.var_dev,
                               L.rmean_dev, L.rvar_dev, L.n, st);
           const yc_tensor z = z_view(net, i), y = view_of(net, i);
           if (!rc) rc = yc_bn_act_fwd(&z, L.mean_dev, L.var_dev, L.scale_dev, L.bias_dev, L.act, &y, st);
+          tick(CAT_BN, st);
         }
         break;
       }
@@ -275,6 +296,7 @@ int train_forward(yc_network* net, const float* input_dev, const float* truth_de
       default: rc = YC_ERR_ARG;
     }
     if (rc) return rc;
+    if (L.type != L_CONV) tick(CAT_OTHER, st);
   }
   return YC_OK;
 }
@@ -299,7 +321,9 @@ int train_backward(yc_network* net, cudaStream_t st) {
           const yc_tensor y = view_of(net, i);
           rc = yc_bias_act_bwd(&dy, L.act == YC_LINEAR ? nullptr : &y, L.act, L.bias_upd, &dz, st);
         }
+        tick(CAT_BN, st);
         if (!rc) rc = yc_conv_wgrad(L.wplan, st);
+        tick(CAT_WGRAD, st);
         if (!rc && net->dp) rc = yc_dp_layer_ready(net, i, st);  // all-reduce of this layer's bucket overlaps the rest
         if (!rc && i > 0) {
           if (L.stride > 1) {
@@ -307,6 +331,7 @@ int train_backward(yc_network* net, cudaStream_t st) {
             rc = yc_conv_dgrad_dilate(&dz, L.stride, &up, st);
           }
           if (!rc) rc = yc_conv_fprop(L.dplan, st);
+          tick(CAT_DGRAD, st);
         }
         break;
       }
@@ -348,6 +373,7 @@ int train_backward(yc_network* net, cudaStream_t st) {
       default: break;  // yolo: folded into the forward's loss kernel
     }
     if (rc) return rc;
+    if (L.type != L_CONV) tick(CAT_OTHER, st);
   }
   if (net->dp) return yc_dp_backward_done(net, st);
   return YC_OK;
@@ -426,6 +452,40 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
   return YC_OK;
 }
 
+// Device time of one forward+backward(+update) by operator category, averaged over iters:
+// ms[0] conv fprop, [1] wgrad, [2] dgrad (+ zero insertion), [3] batchnorm / activation passes, [4] everything else
+// (input conversion, pooling, routes, YOLO decode + loss, memsets), [5] SGD update, [6] total.
+extern "C" int yc_network_train_profile(yc_network* net, const float* input_dev_nchw, const float* truth_dev, int iters,
+                                        float* ms) {
+  YC_REQUIRE(net && input_dev_nchw && truth_dev && ms && iters > 0 && (net->flags & YC_NET_TRAIN) && net->finalized,
+             "yc_network_train_profile: bad argument");
+  for (int i = 0; i < 7; ++i) ms[i] = 0.f;
+  cudaStream_t st = net->stream;
+  int rc = YC_OK;
+  for (int it = 0; it < iters && !rc; ++it) {
+    Prof prof;
+    g_prof = &prof;
+    tick(CAT_OTHER, st);
+    rc = train_forward(net, input_dev_nchw, truth_dev, st);
+    if (!rc) rc = train_backward(net, st);
+    const size_t n_fb = prof.ev.size();
+    if (!rc) rc = yc_network_update(net, 0.f, -1.f, 0.f, st);  // lr = 0, decay = 0: timing only, weights unchanged
+    tick(5, st);
+    g_prof = nullptr;
+    cudaStreamSynchronize(st);
+    for (size_t k = 1; k < prof.ev.size(); ++k) {
+      float t = 0.f;
+      cudaEventElapsedTime(&t, prof.ev[k - 1], prof.ev[k]);
+      const int c = k >= n_fb ? 5 : prof.cat[k];
+      ms[c] += t / iters;
+      ms[6] += t / iters;
+    }
+    for (cudaEvent_t e : prof.ev) cudaEventDestroy(e);
+  }
+  g_prof = nullptr;
+  return rc;
+}
+
 extern "C" int yc_network_train_info(const yc_network* net, int what) {
   if (!net) return -1;
   switch (what) {
@@ -434,6 +494,19 @@ extern "C" int yc_network_train_info(const yc_network* net, int what) {
     case 2: return (int)(net->delta_slab_bytes >> 20);
   }
   return -1;
+}
+
+static int pull_nchw(yc_network* net, const yc_tensor v, size_t elems, float* dst_host, const char* who) {
+  float* tmp = nullptr;
+  NET_CUDA(cudaMalloc(&tmp, elems * 4));
+  int rc = yc_nhwc_to_nchw(&v, tmp, net->stream);
+  if (!rc) {
+    cudaError_t e = cudaMemcpyAsync(dst_host, tmp, elems * 4, cudaMemcpyDeviceToHost, net->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(net->stream);
+    if (e != cudaSuccess) { set_error("%s: %s", who, cudaGetErrorString(e)); rc = YC_ERR_CUDA; }
+  }
+  cudaFree(tmp);
+  return rc;
 }
 
 // cuda_pull_array(l->delta_gpu): layer delta as fp32 NCHW on the host
@@ -447,17 +520,16 @@ extern "C" int yc_network_layer_delta(yc_network* net, int layer, float* dst_hos
     NET_CUDA(cudaStreamSynchronize(net->stream));
     return YC_OK;
   }
-  const yc_tensor v = delta_view(net, layer);
-  float* tmp = nullptr;
-  NET_CUDA(cudaMalloc(&tmp, elems * 4));
-  int rc = yc_nhwc_to_nchw(&v, tmp, net->stream);
-  if (!rc) {
-    cudaError_t e = cudaMemcpyAsync(dst_host, tmp, elems * 4, cudaMemcpyDeviceToHost, net->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(net->stream);
-    if (e != cudaSuccess) { set_error("yc_network_layer_delta: %s", cudaGetErrorString(e)); rc = YC_ERR_CUDA; }
-  }
-  cudaFree(tmp);
-  return rc;
+  return pull_nchw(net, delta_view(net, layer), elems, dst_host, "yc_network_layer_delta");
+}
+
+// cuda_pull_array(l->x_gpu): the convolution output before batchnorm (batchnorm_layer.cpp:104 keeps it for backward)
+extern "C" int yc_network_layer_x(yc_network* net, int layer, float* dst_host) {
+  YC_REQUIRE(net && dst_host && layer >= 0 && layer < (int)net->layers.size() && (net->flags & YC_NET_TRAIN) && net->finalized,
+             "yc_network_layer_x: bad argument");
+  NLayer& L = net->layers[layer];
+  YC_REQUIRE(L.type == L_CONV && L.bn && L.z_buf, "yc_network_layer_x: not a batch-normalised convolution");
+  return pull_nchw(net, z_view(net, layer), (size_t)net->batch * L.out_c * L.out_h * L.out_w, dst_host, "yc_network_layer_x");
 }
 
 // PullConvolutionalLayer (convolutional_kernels.cu:817-836) by name: weights, biases, scales, rolling_mean,

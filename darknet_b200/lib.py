@@ -132,8 +132,10 @@ _SIGS = {
     "yc_network_train_datum": (C.c_int, [_P, _P, _P, C.POINTER(C.c_float)]),
     "yc_network_forward_backward": (C.c_int, [_P, _P, _P, _P]),
     "yc_network_update": (C.c_int, [_P, C.c_float, C.c_float, C.c_float, _P]),
+    "yc_network_train_profile": (C.c_int, [_P, _P, _P, C.c_int, _P]),
     "yc_network_train_info": (C.c_int, [_P, C.c_int]),
     "yc_network_layer_delta": (C.c_int, [_P, C.c_int, _P]),
+    "yc_network_layer_x": (C.c_int, [_P, C.c_int, _P]),
     "yc_network_get_param": (C.c_int, [_P, C.c_int, C.c_char_p, _P, C.c_int]),
     "yc_dp_unique_id": (C.c_int, [_P]),
     "yc_dp_nccl_version": (C.c_int, []),

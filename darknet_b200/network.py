@@ -274,6 +274,13 @@ def layer_delta(net: Network, i):
     return out
 
 
+def layer_x(net: Network, i):
+    """fp32 NCHW copy of l->x (the convolution output before batchnorm) of a batch-normalised conv layer i."""
+    out = np.empty(net.layer_shape(i), np.float32)
+    L.check(L.lib().yc_network_layer_x(net.h, i, out.ctypes.data_as(C.c_void_p)), "yc_network_layer_x")
+    return out
+
+
 def layer_param(net: Network, i, key, capacity=None):
     """l-><key> of layer i (weights, biases, scales, rolling_mean, ..., weight_updates, cost) in reference layout."""
     if capacity is None:

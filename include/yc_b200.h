@@ -329,10 +329,17 @@ YC_API int yc_network_forward_backward(yc_network* net, const float* input_dev_n
 /* UpdateNetworkGpu: SGD step on every conv layer; negative lr/momentum/decay take the cfg's [net] values;
  * batch = net batch * subdivisions (x data-parallel world size).  stream NULL = the network's own stream. */
 YC_API int yc_network_update(yc_network* net, float lr, float momentum, float decay, void* stream);
+/* net->benchmark_layers for the training step: device time by operator category (CUDA events after every operator),
+ * averaged over iters.  ms[7]: conv fprop, wgrad, dgrad, batchnorm/activation passes, other layers + loss, SGD update,
+ * total.  The update inside runs with lr = 0 (weights unchanged; the momentum scaling of the accumulators applies). */
+YC_API int yc_network_train_profile(yc_network* net, const float* input_dev_nchw, const float* truth_dev, int iters,
+                                    float* ms);
 /* what: 0 truth floats per image, 1 subdivisions, 2 delta slab MiB */
 YC_API int yc_network_train_info(const yc_network* net, int what);
 /* cuda_pull_array(l->delta_gpu): fp32 NCHW [batch,out_c,out_h,out_w] */
 YC_API int yc_network_layer_delta(yc_network* net, int layer, float* dst_host);
+/* cuda_pull_array(l->x_gpu): pre-batchnorm convolution output of a batch-normalised conv layer, fp32 NCHW */
+YC_API int yc_network_layer_x(yc_network* net, int layer, float* dst_host);
 /* PullConvolutionalLayer by name ("weights", "biases", "scales", "rolling_mean", "rolling_variance", "mean", "variance",
  * "weight_updates", "bias_updates", "scale_updates"; yolo: "cost", "stats"), reference layouts. Returns floats written. */
 YC_API int yc_network_get_param(yc_network* net, int layer, const char* key, float* dst_host, int capacity);

@@ -89,7 +89,37 @@ class Step:
 
     # ------------------------------------------------------------------------------------------------------------
     def forward_backward(self, x, truth):
+        self.forward(x, truth)
+        return self.backward()
+
+    def adopt_forward(self, outs, zs, means, variances):
+        """Teacher forcing: replace the saved forward state by another implementation's (the GPU's) layer outputs,
+        pre-batchnorm tensors z and batch statistics, so that backward() differentiates exactly the function values
+        that implementation holds (no leaky-branch flips from forward noise)."""
         Ls = self.layers
+        for L in Ls:
+            i = L.index
+            self.out[i] = np.ascontiguousarray(outs[i], np.float32)
+        for L in Ls:
+            i = L.index
+            if L.kind in ("convolutional", "conv"):
+                p, s_ = self.P[i], self.saved[i]
+                s_["x"] = self.out[i - 1] if i > 0 else s_["x"]
+                if L.bn:
+                    mean, var = np.asarray(means[i], np.float32), np.asarray(variances[i], np.float32)
+                    xc = np.asarray(zs[i], np.float32) - mean[None, :, None, None]
+                    xn = xc / np.sqrt(var + np.float32(.000001))[None, :, None, None]
+                    pre = (xn * p["scales"][None, :, None, None] + p["biases"][None, :, None, None]).astype(np.float32)
+                    s_.update(xc=xc, xn=xn, pre=pre, mean=mean, var=var)
+                else:
+                    s_["pre"] = self.out[i]   # only leaky/relu/logistic/linear reach here: gradient on the output
+            elif L.kind in ("maxpool", "max"):
+                _, idx = O.maxpool(self.out[i - 1], L.size, L.stride, L.pad, want_idx=True)
+                self.saved[i] = idx
+
+    def forward(self, x, truth):
+        Ls = self.layers
+        self._truth = truth
         n = len(Ls)
         out, delta, saved = [None] * n, [None] * n, [None] * n
         costs = []
@@ -137,13 +167,24 @@ class Step:
                 mask = [int(v) for v in L.opts["mask"].split(",")]
                 anchors = [float(v) for v in L.opts["anchors"].split(",")]
                 dec = O.yolo_decode(out[i - 1], len(mask), int(L.opts["classes"]), float(L.opts.get("scale_x_y", 1)))
-                d, cost = yolo_loss(dec, truth, anchors, mask, L.opts, self.net_w, self.net_h)
-                delta[i] = d
-                costs.append(cost)
                 cur = dec
             else:
                 raise ValueError(L.kind)
             out[i] = cur
+        self.out, self.saved = out, saved
+
+    def backward(self):
+        Ls = self.layers
+        n = len(Ls)
+        out, saved, truth = self.out, self.saved, self._truth
+        delta = [None] * n
+        costs = []
+        for L in Ls:  # the loss half of ForwardYoloLayer, on the decoded heads
+            if L.kind == "yolo":
+                mask = [int(v) for v in L.opts["mask"].split(",")]
+                anchors = [float(v) for v in L.opts["anchors"].split(",")]
+                delta[L.index], cost = yolo_loss(out[L.index], truth, anchors, mask, L.opts, self.net_w, self.net_h)
+                costs.append(cost)
         for L in Ls:  # network.cpp:108-109: every layer's delta starts at zero
             if delta[L.index] is None:
                 delta[L.index] = np.zeros_like(out[L.index], dtype=np.float32)
@@ -209,7 +250,7 @@ class Step:
                 delta[i - 1] = self.r(delta[i - 1] + d)
                 f = L.inputs[1]
                 delta[f] = self.r(delta[f] + d)
-        self.out, self.delta, self.saved = out, delta, saved
+        self.delta = delta
         self.cost = float(np.mean(costs)) if costs else 0.0
         return self.cost
 

@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--budget", type=float, default=20.0)
     ap.add_argument("--min-images", type=int, default=1)
     ap.add_argument("--max-images", type=int, default=64)
+    ap.add_argument("--train", type=int, default=0, help="time TrainNetworkDatum+UpdateNetwork at this batch instead")
     a = ap.parse_args()
     import numpy as np
     from darknet_b200 import cfg as cfgmod, cfgs
@@ -35,6 +36,8 @@ def main():
     if not pyoracle.have_ref():
         print(json.dumps({"error": "oracle/_ref/libyolo_ref.so missing"}))
         return 0
+    if a.train > 0:
+        return train(a)
     text = cfgs.CONFIGS[a.config](w=a.width, h=a.height)
     d = tempfile.mkdtemp(prefix="yc_ref_")
     cpath, wpath = os.path.join(d, "n.cfg"), os.path.join(d, "n.weights")
@@ -52,6 +55,37 @@ def main():
     print(json.dumps({"images_per_s": 1.0 / per, "s_per_image": per, "images": n, "warmup_s": warm,
                       "threads": int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1)), "config": a.config,
                       "w": a.width, "h": a.height}))
+    return 0
+
+
+def train(a):
+    """Training step of the reference CPU path (ForwardNetwork(train) + BackwardNetwork + UpdateNetwork) at batch
+    a.train; its backward uses the scalar gemm_nt / gemm_tn (gemm.c:2914-2947)."""
+    from darknet_b200 import cfg as cfgmod, cfgs
+    from oracle import pyoracle
+    B = a.train
+    text = cfgs.CONFIGS[a.config](w=a.width, h=a.height, batch=B, subdivisions=1)
+    d = tempfile.mkdtemp(prefix="yc_ref_")
+    cpath, wpath = os.path.join(d, "n.cfg"), os.path.join(d, "n.weights")
+    open(cpath, "w").write(text)
+    cfgmod.write_weights(wpath, text, cfgmod.synth_weights(text))
+    net = pyoracle.RefNet(cpath, wpath, train=True)
+    x = cfgmod.synth_images(B, 3, a.height, a.width)
+    classes = 3 if a.config == "micro" else 80
+    truth = cfgmod.synth_truth(B, 90, classes=classes)
+    t0 = time.perf_counter()
+    net.forward_backward(x, truth)
+    net.L.ref_update(net.h)
+    t1 = time.perf_counter() - t0
+    n = int(max(1, min(a.max_images, a.budget / max(t1, 1e-6))))
+    t0 = time.perf_counter()
+    for _ in range(n):
+        net.forward_backward(x, truth)
+        net.L.ref_update(net.h)
+    per = (time.perf_counter() - t0) / n
+    print(json.dumps({"images_per_s": B / per, "s_per_image": per / B, "images": n * B, "steps": n, "batch": B, "warmup_s": t1,
+                      "threads": int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1)), "config": a.config,
+                      "w": a.width, "h": a.height, "mode": "train"}))
     return 0
 
 

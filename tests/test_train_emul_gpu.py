@@ -6,9 +6,19 @@ Agreement here therefore says: the GPU step differs from the reference ONLY by t
 placement, overwrite-vs-accumulate semantics (B6), accumulation into weight_updates (B7), no gradient for the BN shift
 (B8), the epsilon placements (B1, B5), the unbiased variance (B3), the loss, the SGD update are all the reference's.
 
-Tolerances: smooth activation (mish): every tensor <= 1.5e-2 rel-L2.  leaky: gradients <= 6e-2, because leaky' jumps
-by 10x at 0 and the two sides sum in different orders (the walker's own fp32 mode differs from the reference by up to
-4e-2 in the same quantity for the same reason — see the pin test)."""
+Two comparisons per step:
+  forward  (free running): every layer output <= 5e-2 rel-L2 on the first step, 1e-1 on the second (two bf16 pipelines
+            that sum in different orders drift apart by one bf16 ulp on a growing share of the elements: measured
+            ~1.5e-3 per conv layer, 3e-2 after yolov4-tiny's 21 convs, 8e-2 on a linear head after one update; the
+            tight per-operator forward statements are tests/test_conv_train_gpu.py and the inference parity tests);
+            batch and rolling statistics <= 5e-3;
+  backward (teacher forced): the walker adopts the GPU's forward state (layer outputs, l->x, mean, variance) and
+            differentiates THAT; every delta / weight_updates / scale_updates / bias_updates <= 1.5e-2 rel-L2.
+Why teacher forcing: leaky' jumps by 10x at 0.  With a forward difference of 5e-3 (one bf16 ulp on a growing fraction
+of elements) about 0.4 % of the elements of a deep layer sit on different branches, which alone is an 8 % rel-L2
+gradient difference — measured, round 1: free-running leaky nets differ by 7-10 % in every batch-normalised layer
+while scale_updates (which does not see the branch of the OWN layer's neighbours) agree to 3e-4.  With the forward
+state shared, no element can flip and the tolerance is the same as for smooth activations."""
 import numpy as np
 import pytest
 
@@ -20,41 +30,62 @@ from tests.netutil import rel_l2
 pytestmark = pytest.mark.gpu
 
 
-def _compare(net, st, tol_out, tol_grad, tag):
+def _compare(net, st, tol, tag, what):
+    """what = 'forward': outputs + statistics; 'backward': deltas + parameter gradients."""
     from darknet_b200 import network as N
     worst = dict(out=0.0, delta=0.0, wu=0.0, su=0.0, bu=0.0, stat=0.0)
+    bad, table = [], []
+
+    def chk(key, i, kind, name, e, t):
+        worst[key] = max(worst[key], e)
+        if not e < t:
+            bad.append(f"layer {i} ({kind}) {name} rel-L2 {e:.3e} >= {t}")
+
     for L in st.layers:
         i = L.index
-        e = rel_l2(net.layer_output(i), st.out[i])
-        worst["out"] = max(worst["out"], e)
-        assert e < tol_out, f"{tag}: layer {i} ({L.kind}) output rel-L2 {e:.3e}"
-        e = rel_l2(N.layer_delta(net, i), st.delta[i])
-        worst["delta"] = max(worst["delta"], e)
-        assert e < tol_grad, f"{tag}: layer {i} ({L.kind}) delta rel-L2 {e:.3e}"
-        if i not in st.P:
-            continue
-        p = st.P[i]
-        e = rel_l2(N.layer_param(net, i, "weight_updates"), p["weight_updates"].ravel())
-        worst["wu"] = max(worst["wu"], e)
-        assert e < tol_grad, f"{tag}: layer {i} weight_updates rel-L2 {e:.3e}"
-        if L.bn:
-            e = rel_l2(N.layer_param(net, i, "scale_updates"), p["scale_updates"])
-            worst["su"] = max(worst["su"], e)
-            assert e < tol_grad, f"{tag}: layer {i} scale_updates rel-L2 {e:.3e}"
-            for key, v in (("mean", st.saved[i]["mean"]), ("variance", st.saved[i]["var"]),
-                           ("rolling_mean", p["rolling_mean"]), ("rolling_variance", p["rolling_variance"])):
-                e = rel_l2(N.layer_param(net, i, key), v)
-                worst["stat"] = max(worst["stat"], e)
-                assert e < 5e-3, f"{tag}: layer {i} {key} rel-L2 {e:.3e}"
-            assert np.abs(N.layer_param(net, i, "bias_updates")).max() == 0.0
+        row = [f"L{i:3d} {L.kind:14s}"]
+        if what == "forward":
+            e = rel_l2(net.layer_output(i), st.out[i]); chk("out", i, L.kind, "output", e, tol); row.append(f"out {e:.2e}")
+            if i in st.P and L.bn:
+                p = st.P[i]
+                for key, v in (("mean", st.saved[i]["mean"]), ("variance", st.saved[i]["var"]),
+                               ("rolling_mean", p["rolling_mean"]), ("rolling_variance", p["rolling_variance"])):
+                    e = rel_l2(N.layer_param(net, i, key), v); chk("stat", i, L.kind, key, e, 5e-3)
         else:
-            e = rel_l2(N.layer_param(net, i, "bias_updates"), p["bias_updates"])
-            worst["bu"] = max(worst["bu"], e)
-            assert e < tol_grad, f"{tag}: layer {i} bias_updates rel-L2 {e:.3e}"
-    return worst
+            e = rel_l2(N.layer_delta(net, i), st.delta[i]); chk("delta", i, L.kind, "delta", e, tol); row.append(f"delta {e:.2e}")
+            if i in st.P:
+                p = st.P[i]
+                e = rel_l2(N.layer_param(net, i, "weight_updates"), p["weight_updates"].ravel())
+                chk("wu", i, L.kind, "weight_updates", e, tol); row.append(f"wu {e:.2e}")
+                if L.bn:
+                    e = rel_l2(N.layer_param(net, i, "scale_updates"), p["scale_updates"])
+                    chk("su", i, L.kind, "scale_updates", e, tol); row.append(f"su {e:.2e}")
+                    if np.abs(N.layer_param(net, i, "bias_updates")).max() != 0.0:
+                        bad.append(f"layer {i}: bias_updates of a batch-normalised layer must stay 0 (B8)")
+                else:
+                    e = rel_l2(N.layer_param(net, i, "bias_updates"), p["bias_updates"])
+                    chk("bu", i, L.kind, "bias_updates", e, tol); row.append(f"bu {e:.2e}")
+        table.append("  ".join(row))
+    if bad:
+        print("\n".join(table))
+    assert not bad, f"{tag} {what}: " + "; ".join(bad[:6])
+    return {k: v for k, v in worst.items() if v}
 
 
-def _run(name, B, hw, classes, tol_out, tol_grad, steps=2, **kw):
+def _adopt(net, st):
+    """hand the GPU's forward state to the walker"""
+    from darknet_b200 import network as N
+    outs = {L.index: net.layer_output(L.index) for L in st.layers}
+    zs, means, variances = {}, {}, {}
+    for L in st.layers:
+        if L.index in st.P and L.bn:
+            zs[L.index] = N.layer_x(net, L.index)
+            means[L.index] = N.layer_param(net, L.index, "mean")
+            variances[L.index] = N.layer_param(net, L.index, "variance")
+    st.adopt_forward(outs, zs, means, variances)
+
+
+def _run(name, B, hw, classes, tol=1.5e-2, tol_fwd=(5e-2, 1e-1), steps=2, **kw):
     from darknet_b200 import lib as L, network as N
     text, cpath, wpath = netutil.materialise(name, batch=B, subdivisions=1, **kw)
     W, _ = cfgmod.read_weights(wpath, text)
@@ -63,11 +94,14 @@ def _run(name, B, hw, classes, tol_out, tol_grad, steps=2, **kw):
     for step in range(steps):
         x = cfgmod.synth_images(B, 3, hw, hw, seed=5 + 10 * step)
         truth = cfgmod.synth_truth(B, 90, classes=classes, seed=6 + 10 * step)
-        cw = st.forward_backward(x, truth)
         cg = N.TrainNetworkDatum(net, x, truth)
-        assert abs(cg - cw) <= 5e-3 * abs(cw), f"step {step}: cost {cg} vs walker {cw}"
-        worst = _compare(net, st, tol_out, tol_grad, f"{name} step {step}")
-        print(name, kw, "step", step, "cost", cg, cw, {k: f"{v:.2e}" for k, v in worst.items()})
+        st.forward(x, truth)
+        wf = _compare(net, st, tol_fwd[min(step, 1)], f"{name} step {step}", "forward")
+        _adopt(net, st)
+        cw = st.backward()
+        assert abs(cg - cw) <= 2e-3 * abs(cw), f"step {step}: cost {cg} vs walker on the same heads {cw}"
+        wb = _compare(net, st, tol, f"{name} step {step}", "backward")
+        print(name, kw, "step", step, "cost", cg, cw, {k: f"{v:.2e}" for k, v in {**wf, **wb}.items()})
         st.update()
         N.UpdateNetwork(net)
         for i, p in st.P.items():
@@ -77,13 +111,13 @@ def _run(name, B, hw, classes, tol_out, tol_grad, steps=2, **kw):
 
 
 def test_micro_mish_vs_bf16_walker(gpu):
-    _run("micro", 4, 64, 3, 1.5e-2, 1.5e-2, act="mish")
+    _run("micro", 4, 64, 3, act="mish")
 
 
 def test_micro_leaky_vs_bf16_walker(gpu):
-    _run("micro", 4, 64, 3, 1.5e-2, 6e-2, act="leaky")
+    _run("micro", 4, 64, 3, act="leaky")
 
 
 def test_yolov4_tiny_vs_bf16_walker(gpu):
     """BASELINE config 4 at batch 2."""
-    _run("yolov4-tiny", 2, 416, 80, 1.5e-2, 6e-2, steps=1, w=416, h=416)
+    _run("yolov4-tiny", 2, 416, 80, steps=1, w=416, h=416)
