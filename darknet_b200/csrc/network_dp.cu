@@ -77,6 +77,8 @@ struct DpCtx {
   cudaEvent_t done = nullptr;      // all all-reduces complete on the communication stream
   long long bytes_per_step = 0;
   int buckets = 0;
+  bool overlap = true;   // all-reduce each bucket during backward; false: all buckets at once before the update
+  bool pending = false;  // backward passes have run since the last reduction (overlap == false)
 };
 
 #define NCCL_CALL(call)                                                                        \
@@ -113,8 +115,6 @@ extern "C" int yc_dp_nccl_version(void) {
 extern "C" int yc_network_dp_init(yc_network* net, const void* unique_id128, int rank, int world) {
   YC_REQUIRE(net && unique_id128 && world >= 1 && rank >= 0 && rank < world, "yc_network_dp_init: bad arguments");
   YC_REQUIRE(net->flags & YC_NET_TRAIN, "yc_network_dp_init: network was not loaded with YC_NET_TRAIN");
-  YC_REQUIRE(net->subdivisions == 1, "yc_network_dp_init: data parallelism needs subdivisions=1 (the gradient buckets are "
-                                     "all-reduced after every backward pass)");
   if (!net->finalized) {
     int rc = yc_network_finalize(net);
     if (rc) return rc;
@@ -137,6 +137,8 @@ extern "C" int yc_network_dp_init(yc_network* net, const void* unique_id128, int
       ctx->buckets++;
     }
   NET_CUDA(cudaEventCreateWithFlags(&ctx->done, cudaEventDisableTiming));
+  // with subdivisions > 1 the buckets accumulate over several backward passes: reduce once, before the update
+  ctx->overlap = net->subdivisions == 1;
   net->dp = ctx;
   net->train_flags = world;  // yc_network_update divides by the GLOBAL batch
   return YC_OK;
@@ -145,6 +147,10 @@ extern "C" int yc_network_dp_init(yc_network* net, const void* unique_id128, int
 int yc_dp_layer_ready(yc_network* net, int layer, cudaStream_t compute) {
   DpCtx* ctx = (DpCtx*)net->dp;
   if (!ctx || ctx->world <= 1) return YC_OK;
+  if (!ctx->overlap) {
+    ctx->pending = true;
+    return YC_OK;
+  }
   NLayer& L = net->layers[layer];
   NET_CUDA(cudaEventRecord(ctx->ready[layer], compute));
   NET_CUDA(cudaStreamWaitEvent(ctx->comm_stream, ctx->ready[layer], 0));
@@ -154,10 +160,45 @@ int yc_dp_layer_ready(yc_network* net, int layer, cudaStream_t compute) {
 
 int yc_dp_backward_done(yc_network* net, cudaStream_t compute) {
   DpCtx* ctx = (DpCtx*)net->dp;
-  if (!ctx || ctx->world <= 1) return YC_OK;
+  if (!ctx || ctx->world <= 1 || !ctx->overlap) return YC_OK;
   NET_CUDA(cudaEventRecord(ctx->done, ctx->comm_stream));
   NET_CUDA(cudaStreamWaitEvent(compute, ctx->done, 0));
   return YC_OK;
+}
+
+// All buckets in one NCCL group, after everything enqueued on `compute`; `compute` then waits for the result.  Called by
+// yc_network_update when the per-layer overlap is off (subdivisions > 1, or yc_network_dp_set_overlap(net, 0)).
+int yc_dp_reduce_pending(yc_network* net, cudaStream_t compute) {
+  DpCtx* ctx = (DpCtx*)net->dp;
+  if (!ctx || ctx->world <= 1 || !ctx->pending) return YC_OK;
+  NET_CUDA(cudaEventRecord(ctx->done, compute));
+  NET_CUDA(cudaStreamWaitEvent(ctx->comm_stream, ctx->done, 0));
+  NCCL_CALL(g_nccl.GroupStart());
+  for (NLayer& L : net->layers)
+    if (L.type == L_CONV)
+      NCCL_CALL(g_nccl.AllReduce(L.dw_packed, L.dw_packed, L.bucket_floats, ncclFloat, ncclSum, ctx->comm, ctx->comm_stream));
+  NCCL_CALL(g_nccl.GroupEnd());
+  NET_CUDA(cudaEventRecord(ctx->done, ctx->comm_stream));
+  NET_CUDA(cudaStreamWaitEvent(compute, ctx->done, 0));
+  ctx->pending = false;
+  return YC_OK;
+}
+
+// on = 1 (default when subdivisions == 1): one all-reduce per layer bucket, overlapped with the backward pass;
+// on = 0: gradients stay local until yc_network_dp_reduce / yc_network_update.
+extern "C" int yc_network_dp_set_overlap(yc_network* net, int on) {
+  YC_REQUIRE(net && net->dp, "yc_network_dp_set_overlap: network has no data-parallel context");
+  DpCtx* ctx = (DpCtx*)net->dp;
+  YC_REQUIRE(!on || net->subdivisions == 1, "yc_network_dp_set_overlap: per-layer overlap needs subdivisions=1");
+  YC_REQUIRE(!ctx->pending, "yc_network_dp_set_overlap: un-reduced gradients pending");
+  ctx->overlap = on != 0;
+  return YC_OK;
+}
+
+// Reduce the accumulated local gradients now (no-op if nothing is pending).  Collective.
+extern "C" int yc_network_dp_reduce(yc_network* net, void* stream) {
+  YC_REQUIRE(net && net->dp, "yc_network_dp_reduce: network has no data-parallel context");
+  return yc_dp_reduce_pending(net, stream ? (cudaStream_t)stream : net->stream);
 }
 
 void yc_dp_free(yc_network* net) {
@@ -174,7 +215,7 @@ void yc_dp_free(yc_network* net) {
   net->train_flags = 0;
 }
 
-// what: 0 world, 1 rank, 2 buckets per step, 3 MiB all-reduced per step
+// what: 0 world, 1 rank, 2 buckets per step, 3 MiB all-reduced per step, 4 per-layer overlap on
 extern "C" int yc_network_dp_info(const yc_network* net, int what) {
   if (!net || !net->dp) return what == 0 ? 1 : 0;
   const DpCtx* ctx = (const DpCtx*)net->dp;
@@ -183,6 +224,7 @@ extern "C" int yc_network_dp_info(const yc_network* net, int what) {
     case 1: return ctx->rank;
     case 2: return ctx->buckets;
     case 3: return (int)(ctx->bytes_per_step >> 20);
+    case 4: return ctx->overlap ? 1 : 0;
   }
   return -1;
 }

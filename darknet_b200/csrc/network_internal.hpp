@@ -135,6 +135,7 @@ void yc_train_free(yc_network* net);
 // network_dp.cu: called by the backward pass right after layer i's weight gradient has been enqueued on `compute`
 int yc_dp_layer_ready(yc_network* net, int layer, cudaStream_t compute);
 int yc_dp_backward_done(yc_network* net, cudaStream_t compute);
+int yc_dp_reduce_pending(yc_network* net, cudaStream_t compute);
 void yc_dp_free(yc_network* net);
 
 

@@ -442,6 +442,10 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
   // sum_r (momentum/world * G + g_r) = momentum * G + sum_r g_r, the single-GPU recurrence on the global batch.
   const float carry = momentum / (float)world;
   cudaStream_t st = stream ? (cudaStream_t)stream : net->stream;
+  if (net->dp) {  // gradients not yet exchanged (subdivisions > 1 or overlap switched off): one grouped all-reduce now
+    int rc = yc_dp_reduce_pending(net, st);
+    if (rc) return rc;
+  }
   for (NLayer& L : net->layers) {
     if (L.type != L_CONV) continue;
     int rc = yc_sgd_update_conv(L.w_master, L.dw_packed, L.n, L.c, L.size, lr, batch, carry, decay, L.w_packed,

@@ -57,3 +57,13 @@ def init(net, dist):
     uid = exchange_unique_id(dist, _make_id)
     raw = (C.c_ubyte * 128).from_buffer_copy(uid)
     L.check(L.lib().yc_network_dp_init(net.h, raw, dist.get_rank(), dist.get_world_size()), "yc_network_dp_init")
+
+
+def set_overlap(net, on: bool):
+    """Per-layer all-reduce overlapped with backward (default, subdivisions=1) or one grouped reduction before the update."""
+    L.check(L.lib().yc_network_dp_set_overlap(net.h, 1 if on else 0), "yc_network_dp_set_overlap")
+
+
+def reduce(net, stream=None):
+    """All-reduce the gradients accumulated since the last reduction (collective; no-op if none are pending)."""
+    L.check(L.lib().yc_network_dp_reduce(net.h, stream), "yc_network_dp_reduce")

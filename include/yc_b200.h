@@ -349,11 +349,15 @@ YC_API int yc_network_get_param(yc_network* net, int layer, const char* key, flo
  * to every rank; every rank then calls yc_network_dp_init (collective).  From then on yc_network_forward_backward
  * all-reduces (sum, fp32) each conv layer's gradient bucket [weight_updates | bias_updates | scale_updates] over
  * NCCL / NVLink on a separate stream as soon as that layer's weight gradient is enqueued, overlapping the rest of
- * the backward pass, and yc_network_update divides by the global batch.  Needs subdivisions=1. */
+ * the backward pass, and yc_network_update divides by the global batch.  With subdivisions > 1 (gradients accumulate
+ * over several backward passes) or after yc_network_dp_set_overlap(net, 0) the buckets stay local and are reduced in
+ * one NCCL group by yc_network_dp_reduce, which yc_network_update calls itself when a reduction is pending. */
 YC_API int yc_dp_unique_id(void* out128);
 YC_API int yc_dp_nccl_version(void);
 YC_API int yc_network_dp_init(yc_network* net, const void* unique_id128, int rank, int world);
-/* what: 0 world, 1 rank, 2 buckets per step, 3 MiB all-reduced per step */
+YC_API int yc_network_dp_set_overlap(yc_network* net, int on);
+YC_API int yc_network_dp_reduce(yc_network* net, void* stream);
+/* what: 0 world, 1 rank, 2 buckets per step, 3 MiB all-reduced per step, 4 per-layer overlap on */
 YC_API int yc_network_dp_info(const yc_network* net, int what);
 
 /* Detection == the reference's struct Detection minus unused members (yolo_core.h:598-609). */
