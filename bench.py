@@ -36,6 +36,7 @@ if ROOT not in sys.path:
 
 METRIC = "images_per_sec"
 UNIT = "images/s"
+TRAIN_WL = "yolov4-tiny.cfg 416x416 training fwd+bwd+update batch 64, data-parallel NCCL grad allreduce"
 WORKLOADS = {
     "yolov4": ("yolov4", 608, "yolov4.cfg 608x608 batch 64 inference"),
     "yolov3": ("yolov3", 416, "yolov3.cfg 416x416 batch 64 inference"),
@@ -140,6 +141,186 @@ def run_reference(args):
     return 0
 
 
+def _time_ref_train(cfgname, hw, budget, batch):
+    cores = os.cpu_count() or 1
+    env = dict(os.environ, OMP_NUM_THREADS=str(cores))
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "oracle", "time_ref.py"), "--config", cfgname, "--width", str(hw),
+                        "--height", str(hw), "--budget", str(budget), "--max-images", "4", "--train", str(batch)],
+                       capture_output=True, text=True, env=env, timeout=900)
+    line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+    if not line:
+        return None, cores, "oracle/_ref training run failed: " + r.stderr[-200:]
+    info = json.loads(line[-1])
+    if "error" in info:
+        return None, cores, info["error"]
+    return info, cores, (f"{info['steps']} step(s) of TrainNetworkDatum+UpdateNetwork at batch {info['batch']} "
+                         f"({info['s_per_image']:.3f} s/image) after 1 warm-up step, OMP_NUM_THREADS={cores}; the reference's "
+                         f"CPU backward uses its scalar gemm_nt/gemm_tn (gemm.c:2914-2947)")
+
+
+def run_reference_train(args):
+    """--impl reference --mode train: the reference's own CPU training step (forward(train) + backward + update)."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return 0
+    hw, cfgname = 416, "yolov4-tiny"
+    vals, sample, cores = [], "", os.cpu_count() or 1
+    per_step_budget = max(2.0, 150.0 / max(1, args.steps + args.warmup))
+    for i in range(args.warmup + args.steps):
+        info, cores, sample = _time_ref_train(cfgname, hw, per_step_budget, 8)
+        if info is None:
+            print(json.dumps({"impl": "reference", "unavailable": sample}))
+            return 0
+        if i >= args.warmup:
+            vals.append(info["images_per_s"])
+    v = statistics.mean(vals)
+    out = {"metric": "train_images_per_sec", "value": v, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * args.batch / v, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": TRAIN_WL, "net": cfgname, "width": hw, "height": hw, "batch": args.batch,
+                      "note": "CPU reference timed at batch 8 per step (bounded sample); ms_per_step = the named batch at that rate"},
+           "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+           "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(out))
+    return 0
+
+
+def run_train(args):
+    """--mode train: BASELINE configs[3].  A step = yc_network_forward_backward (forward with batch statistics, YOLO loss,
+    backward with per-layer NCCL all-reduce overlapped when N > 1) + yc_network_update (SGD with momentum/decay) on one
+    batch of 64 synthetic 416x416 images and 90 truth boxes per image per GPU."""
+    import numpy as np
+    import torch
+    from darknet_b200 import cfg as cfgmod, cfgs, dp, lib as L, network as N
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU: the product has no CPU fallback"
+    torch.cuda.set_device(local)
+    L.check(L.lib().yc_set_device(local), "yc_set_device")
+    dist = None
+    if world > 1:
+        import torch.distributed as dist  # noqa: F811
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    cfgname, hw, B = "yolov4-tiny", 416, args.batch
+    text = cfgs.CONFIGS[cfgname](w=hw, h=hw, batch=B, subdivisions=1)
+    weights = cfgmod.synth_weights(text)
+    net = N.LoadSynthetic(text, weights, batch=B, flags=L.NET_DEFAULT | L.NET_TRAIN)
+    if dist is not None:
+        dp.init(net, dist)
+    flops_fwd = net.flops_per_image()
+    conv0 = [i for i in range(net.n) if net.layer_info(i, 0) == 0][0]
+    f0 = 2.0 * net.layer_info(conv0, 1) * net.layer_info(conv0, 5) * net.layer_info(conv0, 6) ** 2 * net.layer_info(conv0, 2) * net.layer_info(conv0, 3)
+    flops_step = (3.0 * flops_fwd - f0) * B      # fprop + wgrad for every conv, dgrad for all but the first
+    x = cfgmod.synth_images(B, 3, hw, hw, seed=1234 + rank)
+    truth = cfgmod.synth_truth(B, 90, classes=80, seed=4321 + rank)
+    xd, td = torch.from_numpy(x).cuda(), torch.from_numpy(truth).cuda()
+    stream = torch.cuda.current_stream()
+    sp = L.stream_ptr()
+
+    def step():
+        N.ForwardBackwardNetworkGpu(net, xd.data_ptr(), td.data_ptr(), sp)
+        N.UpdateNetwork(net, stream=sp)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    barrier()
+    L.lib().yc_launch_count(1)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = int(L.lib().yc_launch_count(0))
+    clocks = sampler.stop() if rank == 0 else None
+    if dist is not None:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = world * B * args.steps / (ms / 1e3)
+    return _run_train_tail(args, locals())
+
+
+def _run_train_tail(args, v):
+    """e2e / roofline / cpu_baseline legs and the JSON line of --mode train (v = run_train's locals)."""
+    import numpy as np
+    import torch
+    from darknet_b200 import lib as L, network as N
+    net, dist, rank, world, B, hw = v["net"], v["dist"], v["rank"], v["world"], v["B"], v["hw"]
+    x, truth, xd, td = v["x"], v["truth"], v["xd"], v["td"]
+    e2e = roof = cpu = None
+    if not args.quick_exit_after_timed:
+        def e2e_step():
+            c = N.TrainNetworkDatum(net, x, truth)   # host fp32 NCHW + truth -> H2D -> forward/backward -> cost D2H
+            N.UpdateNetwork(net)
+            return c
+        for _ in range(2):
+            e2e_step()
+        v["barrier"]()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            cost = e2e_step()
+        torch.cuda.synchronize()
+        t_e2e = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([t_e2e], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            t_e2e = float(t.item())
+        e2e = {"value": world * B * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(x.nbytes + truth.nbytes),
+               "d2h_bytes_per_step": 4 * net.info(7), "ms_per_step": 1e3 * t_e2e / args.steps, "last_cost": cost,
+               "api": "yc_network_train_datum(host fp32 NCHW images, host truth) + yc_network_update"}
+        if rank == 0:
+            ms7 = np.zeros(7, np.float32)
+            L.check(L.lib().yc_network_train_profile(net.h, C.c_void_p(xd.data_ptr()), C.c_void_p(td.data_ptr()), 3,
+                                                     ms7.ctypes.data_as(C.c_void_p)), "yc_network_train_profile")
+            peaks = _peaks()
+            conv_ms = float(ms7[0] + ms7[1] + ms7[2])
+            ach = v["flops_step"] / (conv_ms / 1e3) / 1e12
+            roof = {"bound": "tensor", "kernel": "conv_fprop_kernel (fprop + dgrad) + conv_wgrad_kernel", "achieved": ach,
+                    "peak": peaks["sustained"], "unit": "TFLOP/s", "frac": ach / peaks["sustained"], "traffic": None,
+                    "peak_source": peaks["source"] + ", sustained bf16", "flops_per_step": v["flops_step"],
+                    "ms_by_category": {"conv_fprop": float(ms7[0]), "conv_wgrad": float(ms7[1]), "conv_dgrad": float(ms7[2]),
+                                       "bn_activation_passes": float(ms7[3]), "other_layers_and_loss": float(ms7[4]),
+                                       "sgd_update": float(ms7[5]), "total_with_event_gaps": float(ms7[6])},
+                    "how": "algorithmic FLOPs (fprop + wgrad of every conv, dgrad of all but the first) / summed duration of "
+                           "those kernels, each operator bracketed by CUDA events (yc_network_train_profile, 3 passes)"}
+            if not args.no_cpu_baseline and world == 1:
+                info, cores, sample = _time_ref_train("yolov4-tiny", hw, args.cpu_budget, 8)
+                cpu = {"value": info["images_per_s"] if info else None, "unit": UNIT, "cores": cores, "kind": "reference",
+                       "sample": sample}
+    if rank == 0:
+        out = {"metric": "train_images_per_sec", "value": v["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+               "warmup": max(3, args.warmup), "ms_per_step": v["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+               "config": {"workload": TRAIN_WL, "net": "yolov4-tiny", "width": hw, "height": hw, "batch_per_gpu": B,
+                          "global_batch": B * world, "truth_boxes_per_image": 90,
+                          "parallelism": (f"data-parallel x{world}: one NCCL all-reduce per conv-layer gradient bucket, overlapped "
+                                          f"with backward ({L.lib().yc_network_dp_info(net.h, 2)} buckets, "
+                                          f"{L.lib().yc_network_dp_info(net.h, 3)} MiB per step)") if world > 1 else "single GPU",
+                          "optimizer": "SGD momentum .9 decay 5e-4 (cfg), fp32 master weights, bf16 operands",
+                          "conv_gflop_per_image_fwd": v["flops_fwd"] / 1e9,
+                          "l2_policy": "per-step working set (activations + deltas of 64 images, >2 GB) exceeds the 126 MB L2; no explicit flush"},
+               "clocks": v["clocks"], "e2e": e2e, "gpu_launches": v["launches"], "roofline": roof, "cpu_baseline": cpu}
+        print(json.dumps(out))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
 def cpu_baseline(cfgname, hw, budget):
     cores = os.cpu_count() or 1
     env = dict(os.environ, OMP_NUM_THREADS=str(cores))
@@ -164,6 +345,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="infer", choices=["infer", "train"],
+                    help="infer: the headline (BASELINE configs[2]); train: configs[3], yolov4-tiny 416 fwd+bwd+update")
     ap.add_argument("--workload", default="yolov4", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -172,7 +355,9 @@ def main():
     ap.add_argument("--quick-exit-after-timed", action="store_true", help="(profiling) skip e2e / roofline / cpu legs")
     args = ap.parse_args()
     if args.impl == "reference":
-        return run_reference(args)
+        return run_reference_train(args) if args.mode == "train" else run_reference(args)
+    if args.mode == "train":
+        return run_train(args)
 
     import numpy as np
     import torch
