@@ -75,6 +75,68 @@ __device__ __forceinline__ void st8(const TView& t, long long row, int c0, const
   }
 }
 
+// Two tensors x two rows: all four 16-byte loads are issued BEFORE any conversion.  (ld8 converts inside its own
+// branch, so back-to-back ld8 calls leave one load in flight per thread: measured 1.1 TB/s on the BN passes.)
+__device__ __forceinline__ void cvt8(const uint4& q, int c0, int c, float (&v)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float2 f = __bfloat1622float2(h[e]);
+    v[2 * e] = f.x;
+    v[2 * e + 1] = f.y;
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    if (c0 + j >= c) v[j] = 0.f;
+}
+__device__ __forceinline__ uint4 ldq(const TView& t, long long row, int c0, bool pred) {
+  uint4 q = make_uint4(0u, 0u, 0u, 0u);
+  if (pred) q = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(t.ptr) + row * t.ldc + c0));
+  return q;
+}
+__device__ __forceinline__ bool fast_view(const TView& t, int c0) { return !t.f32 && c0 + 8 <= t.ldc; }
+// rows r0 (always) and r1 (if two) of a and b; absent rows read as zeros
+__device__ __forceinline__ void ld8_2x2(const TView& a, const TView& b, long long r0, long long r1, bool two, int c0,
+                                        float (&a0)[8], float (&b0)[8], float (&a1)[8], float (&b1)[8]) {
+  if (fast_view(a, c0) && fast_view(b, c0)) {
+    const uint4 qa0 = ldq(a, r0, c0, true), qb0 = ldq(b, r0, c0, true);
+    const uint4 qa1 = ldq(a, r1, c0, two), qb1 = ldq(b, r1, c0, two);
+    cvt8(qa0, c0, a.c, a0);
+    cvt8(qb0, c0, b.c, b0);
+    cvt8(qa1, c0, a.c, a1);
+    cvt8(qb1, c0, b.c, b1);
+  } else {
+    ld8(a, r0, c0, a0);
+    ld8(b, r0, c0, b0);
+    if (two) {
+      ld8(a, r1, c0, a1);
+      ld8(b, r1, c0, b1);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a1[j] = b1[j] = 0.f;
+    }
+  }
+}
+// one tensor x four rows
+__device__ __forceinline__ void ld8_1x4(const TView& a, const long long (&r)[4], const bool (&ok)[4], int c0, float (&v)[4][8]) {
+  if (fast_view(a, c0)) {
+    uint4 q[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) q[k] = ldq(a, r[k], c0, ok[k]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) cvt8(q[k], c0, a.c, v[k]);
+  } else {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (ok[k]) ld8(a, r[k], c0, v[k]);
+      else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[k][j] = 0.f;
+      }
+    }
+  }
+}
+
 // gradient of the activation at pre-activation u (activations.h:152-178, activations.c:412-452).  The reference
 // evaluates leaky/relu/logistic on the post-activation output; those are the same functions of u.
 __device__ __forceinline__ float act_grad(float u, int act) {
@@ -143,25 +205,40 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
 }
 
 // y = act( gamma * (z - mean)/sqrt(var + 1e-6) + beta )   (normalize_cpu blas.c:214, scale_bias, add_bias)
+// thread = (row slot, 8-channel group): the per-channel constants live in registers, the thread walks rows with a
+// stride of gridDim*slots, two rows per iteration so that both 16-byte loads are in flight before the math.
+template <int ACT>
 __global__ void bn_act_fwd_kernel(TView z, const float* __restrict__ mean, const float* __restrict__ var,
-                                  const float* __restrict__ gamma, const float* __restrict__ beta, int act, TView y,
+                                  const float* __restrict__ gamma, const float* __restrict__ beta, TView y,
                                   int y_own_pad) {
+  constexpr int act = ACT;  // compile-time: with a runtime switch unrolled 32x the kernel was 64 KB of code
   const int groups = (z.c + 7) / 8;
-  const long long total = z.rows * groups;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int g = (int)(i % groups);
-    const long long row = i / groups;
-    float v[8];
-    ld8(z, row, g * 8, v);
+  const int tg = threadIdx.x % groups;  // blockDim.x is a multiple of groups (host)
+  const int slots = blockDim.x / groups;
+  const int slot = threadIdx.x / groups;
+  float mu[8], is[8], ga[8], be[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int c = g * 8 + j;
-      if (c < z.c) {
-        const float xh = (v[j] - mean[c]) / sqrtf(var[c] + .000001f);
-        v[j] = act_fwd_exact(gamma[c] * xh + beta[c], act);
-      }
+  for (int j = 0; j < 8; ++j) {
+    const int c = tg * 8 + j;
+    const bool ok = c < z.c;
+    mu[j] = ok ? mean[c] : 0.f;
+    is[j] = ok ? 1.f / sqrtf(var[c] + .000001f) : 0.f;
+    ga[j] = ok ? gamma[c] : 0.f;
+    be[j] = ok ? beta[c] : 0.f;
+  }
+  const long long step = (long long)gridDim.x * slots;
+  for (long long row = (long long)blockIdx.x * slots + slot; row < z.rows; row += 4 * step) {
+    const long long r[4] = {row, row + step, row + 2 * step, row + 3 * step};
+    const bool ok[4] = {true, r[1] < z.rows, r[2] < z.rows, r[3] < z.rows};
+    float v[4][8];
+    ld8_1x4(z, r, ok, tg * 8, v);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (!ok[k]) continue;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[k][j] = act_fwd_exact(ga[j] * ((v[k][j] - mu[j]) * is[j]) + be[j], act);
+      st8(y, r[k], tg * 8, v[k], y_own_pad != 0);
     }
-    st8(y, row, g * 8, v, y_own_pad != 0);
   }
 }
 
@@ -169,10 +246,11 @@ __global__ void bn_act_fwd_kernel(TView z, const float* __restrict__ mean, const
 // MODE 0 (batchnorm):  g = dy * act'(u), u = gamma*xhat + beta;  S1[c] += sum g ; S2[c] += sum g*(z - mean)
 // MODE 1 (bias only):  g = dy * act'(y) evaluated on the layer OUTPUT y (leaky/relu/logistic/linear): S1 only
 // thread = (row slot, 8-channel group); registers -> shared atomics -> global atomics.
-template <int MODE>
+template <int MODE, int ACT>
 __global__ void bwd_reduce_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
-                                  const float* __restrict__ gamma, const float* __restrict__ beta, int act,
+                                  const float* __restrict__ gamma, const float* __restrict__ beta,
                                   float* __restrict__ S1, float* __restrict__ S2) {
+  constexpr int act = ACT;
   extern __shared__ float sh[];  // [2][groups*8]
   const int groups = (dy.c + 7) / 8;
   const int C8 = groups * 8;
@@ -194,20 +272,22 @@ __global__ void bwd_reduce_kernel(TView dy, TView z, const float* __restrict__ m
     is[j] = (MODE == 0 && ok) ? 1.f / sqrtf(var[c] + .000001f) : 1.f;
   }
   if (slot < slots) {
-    for (long long row = (long long)blockIdx.x * slots + slot; row < dy.rows; row += (long long)gridDim.x * slots) {
-      float d[8], x[8];
-      ld8(dy, row, tg * 8, d);
-      ld8(z, row, tg * 8, x);
+    const long long step = (long long)gridDim.x * slots;
+    for (long long row = (long long)blockIdx.x * slots + slot; row < dy.rows; row += 2 * step) {
+      const long long row2 = row + step;
+      const bool two = row2 < dy.rows;
+      float d[8], x[8], d2[8], x2[8];
+      ld8_2x2(dy, z, row, row2, two, tg * 8, d, x, d2, x2);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         if (MODE == 0) {
-          const float xc = x[j] - mu[j];
-          const float u = ga[j] * (xc * is[j]) + be[j];
-          const float g = d[j] * act_grad(u, act);
-          a1[j] += g;
-          a2[j] += g * xc;
+          const float xc = x[j] - mu[j], xc2 = x2[j] - mu[j];
+          const float g = d[j] * act_grad(ga[j] * (xc * is[j]) + be[j], act);
+          const float g2 = d2[j] * act_grad(ga[j] * (xc2 * is[j]) + be[j], act);   // d2 = 0 when the row is absent
+          a1[j] += g + g2;
+          a2[j] += g * xc + g2 * xc2;
         } else {
-          a1[j] += d[j] * act_grad_out(x[j], act);
+          a1[j] += d[j] * act_grad_out(x[j], act) + d2[j] * act_grad_out(x2[j], act);
         }
       }
     }
@@ -246,38 +326,57 @@ __global__ void bn_bwd_coef_kernel(const float* __restrict__ S1, const float* __
   coef[2 * n + c] = (float)(md / m);
 }
 
+template <int ACT>
 __global__ void bn_bwd_apply_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
-                                    const float* __restrict__ gamma, const float* __restrict__ beta, int act,
+                                    const float* __restrict__ gamma, const float* __restrict__ beta,
                                     const float* __restrict__ coef, TView dz, int groups) {
-  const long long total = dy.rows * groups;
+  constexpr int act = ACT;
+  // thread = (row slot, 8-channel group of dz's pitch); groups beyond the data channels only write zeros
   const int n = dy.c;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int g = (int)(i % groups);
-    const long long row = i / groups;
+  const int tg = threadIdx.x % groups;  // blockDim.x is a multiple of groups (host)
+  const int slots = blockDim.x / groups;
+  const int slot = threadIdx.x / groups;
+  const bool live = tg * 8 < n;
+  float mu[8], is[8], ga[8], be[8], c0[8], c1[8], c2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = tg * 8 + j;
+    const bool ok = c < n;
+    mu[j] = ok ? mean[c] : 0.f;
+    is[j] = ok ? 1.f / sqrtf(var[c] + .000001f) : 0.f;
+    ga[j] = ok ? gamma[c] : 0.f;
+    be[j] = ok ? beta[c] : 0.f;
+    c0[j] = ok ? coef[c] : 0.f;
+    c1[j] = ok ? coef[n + c] : 0.f;
+    c2[j] = ok ? coef[2 * n + c] : 0.f;
+  }
+  const long long step = (long long)gridDim.x * slots;
+  for (long long row = (long long)blockIdx.x * slots + slot; row < dy.rows; row += 2 * step) {
+    const long long row2 = row + step;
+    const bool two = row2 < dy.rows;
     float d[8] = {0, 0, 0, 0, 0, 0, 0, 0}, x[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    if (g * 8 < n) {
-      ld8(dy, row, g * 8, d);
-      ld8(z, row, g * 8, x);
+    float d2[8] = {0, 0, 0, 0, 0, 0, 0, 0}, x2[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (live) {
+      ld8_2x2(dy, z, row, row2, two, tg * 8, d, x, d2, x2);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const int c = g * 8 + j;
-        if (c < n) {
-          const float xc = x[j] - mean[c];
-          const float u = gamma[c] * (xc / sqrtf(var[c] + .000001f)) + beta[c];
-          const float gg = d[j] * act_grad(u, act);
-          d[j] = gg * coef[c] + coef[n + c] * xc + coef[2 * n + c];
-        } else {
-          d[j] = 0.f;
-        }
+        const float xc = x[j] - mu[j], xc2 = x2[j] - mu[j];
+        const float gg = d[j] * act_grad(ga[j] * (xc * is[j]) + be[j], act);
+        const float gg2 = d2[j] * act_grad(ga[j] * (xc2 * is[j]) + be[j], act);
+        d[j] = gg * c0[j] + c1[j] * xc + c2[j];      // channels >= n: all coefficients are 0
+        d2[j] = gg2 * c0[j] + c1[j] * xc2 + c2[j];
       }
     }
-    st8(dz, row, g * 8, d, true);
+    st8(dz, row, tg * 8, d, true);
+    if (two) st8(dz, row2, tg * 8, d2, true);
   }
 }
 
 // no batchnorm: dz = dy * act'(y) on the layer output y; bias_updates += column sums of dz
 // (gradient_array + backward_bias, convolutional_layer.cpp:1327-1336)
-__global__ void act_bwd_apply_kernel(TView dy, TView u, int act, TView dz, int groups) {
+template <int ACT>
+__global__ void act_bwd_apply_kernel(TView dy, TView u, TView dz, int groups) {
+  constexpr int act = ACT;
   const long long total = dy.rows * groups;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int g = (int)(i % groups);
@@ -295,6 +394,22 @@ __global__ void act_bwd_apply_kernel(TView dy, TView u, int act, TView dz, int g
   }
 }
 
+// grid for the row-walking kernels: every thread handles >= 2 rows per iteration; 8 blocks per SM keep ~2k threads x
+// two 16-byte loads per tensor in flight per SM
+static int row_grid(long long rows, int slots, int per_iter = 2) {
+  return (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(rows, (long long)slots * per_iter), (long long)sm_count() * 8));
+}
+// instantiate a launch for the activation id (compile-time in the kernels)
+#define YC_ACT_DISPATCH(act_id, ...)                                                  \
+  switch (act_id) {                                                                   \
+    case YC_LINEAR: { constexpr int A = YC_LINEAR; __VA_ARGS__; } break;              \
+    case YC_LEAKY: { constexpr int A = YC_LEAKY; __VA_ARGS__; } break;                \
+    case YC_RELU: { constexpr int A = YC_RELU; __VA_ARGS__; } break;                  \
+    case YC_LOGISTIC: { constexpr int A = YC_LOGISTIC; __VA_ARGS__; } break;          \
+    case YC_SWISH: { constexpr int A = YC_SWISH; __VA_ARGS__; } break;                \
+    case YC_MISH: { constexpr int A = YC_MISH; __VA_ARGS__; } break;                  \
+    default: set_error("unsupported activation %d", (int)(act_id)); return YC_ERR_ARG; \
+  }
 static int reduce_threads(int groups) {
   int t = (256 / groups) * groups;
   if (t < groups) t = groups;  // more than 256 groups (c > 2048): one row slot
@@ -329,8 +444,10 @@ extern "C" int yc_bn_act_fwd(const yc_tensor* z, const float* mean, const float*
   YC_REQUIRE(z->n == y->n && z->h == y->h && z->w == y->w && z->c == y->c, "yc_bn_act_fwd: shape mismatch");
   const TView zv = tv(z), yv = tv(y);
   const int own = y->ldc == round_up(y->c, 8);
-  bn_act_fwd_kernel<<<ew_grid(zv.rows * ((z->c + 7) / 8)), 256, 0, (cudaStream_t)stream>>>(zv, mean, var, gamma, beta,
-                                                                                           activation, yv, own);
+  const int groups = (z->c + 7) / 8;
+  const int threads = reduce_threads(groups);
+  YC_ACT_DISPATCH(activation, (bn_act_fwd_kernel<A><<<row_grid(zv.rows, threads / groups, 4), threads, 0, (cudaStream_t)stream>>>(
+                                  zv, mean, var, gamma, beta, yv, own)));
   YC_LAUNCH_CHECK();
   return YC_OK;
 }
@@ -354,14 +471,17 @@ extern "C" int yc_bn_bwd(const yc_tensor* dy, const yc_tensor* z, const float* m
   const int groups = (n + 7) / 8;
   const int threads = reduce_threads(groups);
   const int slots = threads / groups;
-  const int grid = (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(dv.rows, (long long)slots * 4), (long long)sm_count() * 4));
-  bwd_reduce_kernel<0><<<grid, threads, sizeof(float) * 2 * groups * 8, st>>>(dv, zv, mean, var, gamma, beta, activation, S1, S2);
+  const int grid = (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(dv.rows, (long long)slots * 4), (long long)sm_count() * 8));
+  YC_ACT_DISPATCH(activation, (bwd_reduce_kernel<0, A><<<grid, threads, sizeof(float) * 2 * groups * 8, st>>>(dv, zv, mean, var, gamma,
+                                                                                                             beta, S1, S2)));
   YC_LAUNCH_CHECK();
   bn_bwd_coef_kernel<<<ceil_div(n, 128), 128, 0, st>>>(S1, S2, var, gamma, (float)dv.rows, scale_updates, bias_updates, coef, n);
   YC_LAUNCH_CHECK();
   ov.c = dy->c;
   const int agroups = (dz->ldc >= (long long)groups * 8) ? dz->ldc / 8 : groups;
-  bn_bwd_apply_kernel<<<ew_grid(dv.rows * agroups), 256, 0, st>>>(dv, zv, mean, var, gamma, beta, activation, coef, ov, agroups);
+  const int athreads = reduce_threads(agroups);
+  YC_ACT_DISPATCH(activation, (bn_bwd_apply_kernel<A><<<row_grid(dv.rows, athreads / agroups), athreads, 0, st>>>(
+                                  dv, zv, mean, var, gamma, beta, coef, ov, agroups)));
   YC_LAUNCH_CHECK();
   return YC_OK;
 }
@@ -383,13 +503,13 @@ extern "C" int yc_bias_act_bwd(const yc_tensor* dy, const yc_tensor* y, int acti
   if (bias_updates) {
     const int threads = reduce_threads(groups);
     const int slots = threads / groups;
-    const int grid = (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(dv.rows, (long long)slots * 4), (long long)sm_count() * 4));
-    bwd_reduce_kernel<1><<<grid, threads, sizeof(float) * 2 * groups * 8, st>>>(dv, uv, nullptr, nullptr, nullptr, nullptr,
-                                                                               activation, bias_updates, nullptr);
+    const int grid = (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(dv.rows, (long long)slots * 4), (long long)sm_count() * 8));
+    YC_ACT_DISPATCH(activation, (bwd_reduce_kernel<1, A><<<grid, threads, sizeof(float) * 2 * groups * 8, st>>>(
+                                    dv, uv, nullptr, nullptr, nullptr, nullptr, bias_updates, nullptr)));
     YC_LAUNCH_CHECK();
   }
   const int agroups = (dz->ldc >= (long long)groups * 8) ? dz->ldc / 8 : groups;
-  act_bwd_apply_kernel<<<ew_grid(dv.rows * agroups), 256, 0, st>>>(dv, uv, activation, ov, agroups);
+  YC_ACT_DISPATCH(activation, (act_bwd_apply_kernel<A><<<ew_grid(dv.rows * agroups), 256, 0, st>>>(dv, uv, ov, agroups)));
   YC_LAUNCH_CHECK();
   return YC_OK;
 }

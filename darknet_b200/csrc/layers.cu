@@ -100,6 +100,46 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, View dst, int
     store8(dst, b * hw + s, g * 8, r);
   }
 }
+// ---- stem: NCHW fp32 image -> im2col rows [b][oh][ow][32] bf16 -------------------------------------------------
+// The first convolution of a detector has 3 input channels: c*k*k = 27 <= 32.  Its A operand is built HERE, while the
+// fp32 image is converted anyway: row = output pixel, column k = (kh*size + kw)*c + ci, zero padding written as zeros,
+// columns 27..31 zero.  The convolution then runs as a 1x1 layer with 32 input channels on the tiled TMA map (64-byte
+// rows, HBM-bound) instead of nine im2col-mode tap loads of 16-byte rows per pixel.  thread = output pixel (adjacent
+// lanes = adjacent pixels: the NCHW reads are coalesced and every input element is reused size^2 times out of L1).
+// CT/ST > 0: channel count and kernel size known at compile time (3, 3 for every detector cfg), so the column -> (tap,
+// channel) split costs nothing; CT = 0: generic.
+template <int CT, int ST>
+__global__ void stem_im2col_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int B, int C_, int H, int W,
+                                   int OH, int OW, int size_, int stride, int pad) {
+  const int C = CT > 0 ? CT : C_, size = ST > 0 ? ST : size_;
+  const long long total = (long long)B * OH * OW;
+  const int kk = C * size * size;
+  const long long plane = (long long)H * W;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int ow = (int)(i % OW);
+    const int oh = (int)((i / OW) % OH);
+    const long long b = i / ((long long)OW * OH);
+    const float* img = src + b * C * plane;
+    const int ih0 = oh * stride - pad, iw0 = ow * stride - pad;
+    uint4 out[4];
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+#pragma unroll
+    for (int k = 0; k < 32; ++k) {
+      float v = 0.f;
+      if (k < kk) {
+        const int tap = k / C, ci = k - tap * C;
+        const int kh = tap / size, kw = tap - kh * size;
+        const int ih = ih0 + kh, iw = iw0 + kw;
+        if ((unsigned)ih < (unsigned)H && (unsigned)iw < (unsigned)W) v = __ldg(img + ci * plane + (long long)ih * W + iw);
+      }
+      o[k] = __float2bfloat16(v);
+    }
+    uint4* d = reinterpret_cast<uint4*>(dst + i * 32);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) d[q] = out[q];
+  }
+}
+
 __global__ void nhwc_to_nchw_kernel(View src, float* __restrict__ dst) {
   const long long hw = (long long)src.h * src.w;
   const int groups = (src.c + 7) / 8;
@@ -263,6 +303,26 @@ extern "C" int yc_nchw_to_nhwc(const float* src, const yc_tensor* dst, void* str
   const int e = dst->dtype == YC_F32 ? 4 : 8;
   if (dst->ldc == round_up(dst->c, e)) d.c = (int)dst->ldc;  // tensor owns its pitch: zero-fill the pad lanes
   nchw_to_nhwc_kernel<<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(src, d, dst->c);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+// Builds the first layer's GEMM operand straight from the fp32 NCHW image (see stem_im2col_kernel).  dst: bf16
+// [n][oh][ow][32] with ldc 32, oh = (h + 2*pad - size)/stride + 1.  Requires c*size*size <= 32.
+extern "C" int yc_stem_im2col(const float* src, int c, int h, int w, int size, int stride, int pad, const yc_tensor* dst,
+                              void* stream) {
+  YC_CHECK_T(dst, "yc_stem_im2col");
+  YC_REQUIRE(src && c >= 1 && size >= 1 && stride >= 1 && pad >= 0 && c * size * size <= 32,
+             "yc_stem_im2col: needs c*size*size <= 32");
+  YC_REQUIRE(dst->dtype == YC_BF16 && dst->c == 32 && dst->ldc == 32 && aligned16(dst), "yc_stem_im2col: dst must be bf16 [.,.,.,32], pitch 32");
+  YC_REQUIRE(dst->h == (h + 2 * pad - size) / stride + 1 && dst->w == (w + 2 * pad - size) / stride + 1,
+             "yc_stem_im2col: output shape mismatch");
+  const long long work = (long long)dst->n * dst->h * dst->w;
+  if (c == 3 && size == 3)
+    stem_im2col_kernel<3, 3><<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst->ptr, dst->n, c, h, w,
+                                                                                    dst->h, dst->w, size, stride, pad);
+  else
+    stem_im2col_kernel<0, 0><<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst->ptr, dst->n, c, h, w,
+                                                                                    dst->h, dst->w, size, stride, pad);
   YC_LAUNCH_CHECK();
   return YC_OK;
 }

@@ -251,6 +251,7 @@ int run_op(yc_network* net, const Op& op, cudaStream_t st) {
     case 4: return yc_route_copy(&op.a, &op.y, st);
     case 5: return yc_yolo_decode(&op.a, L->dec_dev, op.i0, op.i1, op.f0, op.i2, st);
     case 6: return yc_nchw_to_nhwc(net->graph_input, &op.y, st);
+    case 7: return yc_stem_im2col(net->graph_input, net->c, net->h, net->w, op.i0, op.i1, op.i2, &op.y, st);
   }
   return YC_ERR_ARG;
 }
@@ -354,9 +355,13 @@ extern "C" int yc_network_finalize(yc_network* net) {
   const size_t in_elems = (size_t)net->batch * net->c * net->h * net->w;
   NET_CUDA(cudaMalloc(&net->input_dev, in_elems * 4));
   NET_CUDA(cudaHostAlloc(&net->input_pinned, in_elems * 4, cudaHostAllocDefault));
-  const int in_ldc = round_up(net->c, 8);
-  NET_CUDA(cudaMalloc(&net->input_nhwc, (size_t)net->batch * net->h * net->w * in_ldc * 2));
-  NET_CUDA(cudaMemset(net->input_nhwc, 0, (size_t)net->batch * net->h * net->w * in_ldc * 2));
+  // Stem as im2col + 1x1 (see yc_stem_im2col): the input conversion writes the first conv's GEMM operand directly.
+  const bool stem = !(flags & YC_NET_TRAIN) && (flags & YC_NET_STEM_IM2COL) && nl > 0 && Ls[0].type == L_CONV &&
+                    Ls[0].size > 1 && Ls[0].dilation == 1 && Ls[0].c * Ls[0].size * Ls[0].size <= 32;
+  const int in_ldc = stem ? 32 : round_up(net->c, 8);
+  const int in_h = stem ? Ls[0].out_h : net->h, in_w = stem ? Ls[0].out_w : net->w, in_c = stem ? 32 : net->c;
+  NET_CUDA(cudaMalloc(&net->input_nhwc, (size_t)net->batch * in_h * in_w * in_ldc * 2));
+  NET_CUDA(cudaMemset(net->input_nhwc, 0, (size_t)net->batch * in_h * in_w * in_ldc * 2));
 
   if (flags & YC_NET_TRAIN) {
     int rc = yc_train_finalize(net);
@@ -388,11 +393,20 @@ extern "C" int yc_network_finalize(yc_network* net) {
         }
       }
     }
+    int pc = L.c, ps = L.size;  // geometry the packed weights are laid out for
+    if (stem && i == 0) {       // OIHW [n][c][kh][kw] -> [n][32] with column (kh*size+kw)*c + ci, as yc_stem_im2col writes
+      std::vector<float> w2((size_t)L.n * 32, 0.f);
+      for (int f = 0; f < L.n; ++f)
+        for (int ci = 0; ci < L.c; ++ci)
+          for (int t = 0; t < L.size * L.size; ++t) w2[(size_t)f * 32 + t * L.c + ci] = w[((size_t)f * L.c + ci) * L.size * L.size + t];
+      w.swap(w2);
+      pc = 32; ps = 1;
+    }
     float* w_dev = nullptr;
     NET_CUDA(cudaMalloc(&w_dev, w.size() * 4));
     NET_CUDA(cudaMemcpy(w_dev, w.data(), w.size() * 4, cudaMemcpyHostToDevice));
-    NET_CUDA(cudaMalloc(&L.w_packed, yc_conv_packed_bytes(L.n, L.c, L.size)));
-    int rc = yc_conv_pack(w_dev, L.n, L.c, L.size, L.w_packed, net->stream);
+    NET_CUDA(cudaMalloc(&L.w_packed, yc_conv_packed_bytes(L.n, pc, ps)));
+    int rc = yc_conv_pack(w_dev, L.n, pc, ps, L.w_packed, net->stream);
     if (rc) { cudaFree(w_dev); return rc; }
     NET_CUDA(cudaStreamSynchronize(net->stream));
     NET_CUDA(cudaFree(w_dev));
@@ -407,12 +421,13 @@ extern "C" int yc_network_finalize(yc_network* net) {
   // ---- op list -------------------------------------------------------------------------------------
   {
     Op op;
-    op.layer = -1; op.kind = 6;
-    op.y = yc_tensor{net->input_nhwc, net->batch, net->h, net->w, net->c, in_ldc, YC_BF16};
+    op.layer = -1; op.kind = stem ? 7 : 6;
+    op.y = yc_tensor{net->input_nhwc, net->batch, in_h, in_w, in_c, in_ldc, YC_BF16};
+    if (stem) { op.i0 = Ls[0].size; op.i1 = Ls[0].stride; op.i2 = Ls[0].pad; }
     net->ops.push_back(op);
   }
   auto input_view = [&](int i) -> yc_tensor {
-    if (i == 0) return yc_tensor{net->input_nhwc, net->batch, net->h, net->w, net->c, in_ldc, YC_BF16};
+    if (i == 0) return yc_tensor{net->input_nhwc, net->batch, in_h, in_w, in_c, in_ldc, YC_BF16};
     return view_of(net, i - 1);
   };
   for (int i = 0; i < nl; ++i) {
@@ -422,6 +437,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
     switch (L.type) {
       case L_CONV: {
         yc_conv_desc d{L.size, L.stride, L.pad, L.dilation, L.act, YC_LINEAR};
+        if (stem && i == 0) { d.ksize = 1; d.stride = 1; d.pad = 0; }
         yc_tensor x = input_view(i);
         yc_tensor y, res;
         const yc_tensor* resp = nullptr;

@@ -47,7 +47,8 @@ class Detection(C.Structure):
 
 
 NET_FUSE_BN, NET_FUSE_SHORTCUT, NET_ELIDE_ROUTE, NET_CUDA_GRAPH, NET_PULL_HEADS, NET_REF_CPU_MAXPOOL = 1, 2, 4, 8, 16, 32
-NET_DEFAULT = 1 | 2 | 4 | 8 | 16
+NET_STEM_IM2COL = 512
+NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
 NET_TRAIN, NET_DGRAD_ACCUMULATE, NET_BN_BIAS_GRAD = 64, 128, 256
 
 _lib = None
@@ -73,6 +74,7 @@ _SIGS = {
     "yc_launch_count": (C.c_longlong, [C.c_int]),
     "yc_nchw_to_nhwc": (C.c_int, [_P, _TP, _P]),
     "yc_nhwc_to_nchw": (C.c_int, [_TP, _P, _P]),
+    "yc_stem_im2col": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _TP, _P]),
     "yc_conv_padded_in_c": (C.c_int, [C.c_int]),
     "yc_conv_packed_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "yc_conv_pack": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),

@@ -79,6 +79,11 @@ YC_API long long yc_launch_count(int reset);
 /* ---- layout conversion at the seam ----------------------------------------------------------- */
 /* fp32 NCHW (reference layout, network_kernels.cu:513-514 input) -> NHWC view (bf16 or fp32). */
 YC_API int yc_nchw_to_nhwc(const float* src, const yc_tensor* dst, void* stream);
+/* fp32 NCHW image -> the first convolution's GEMM operand: bf16 [n][oh][ow][32], column (kh*size+kw)*c + ci, zero
+ * padding and columns >= c*size*size written as zeros (needs c*size*size <= 32).  The stem then runs as a 1x1
+ * convolution over 32 channels; replaces im2col_ongpu (im2col_kernels.cu) for that layer. */
+YC_API int yc_stem_im2col(const float* src, int c, int h, int w, int size, int stride, int pad, const yc_tensor* dst,
+                          void* stream);
 /* NHWC view -> fp32 NCHW (what the reference's host code and other layers read). */
 YC_API int yc_nhwc_to_nchw(const yc_tensor* src, float* dst, void* stream);
 
@@ -278,7 +283,9 @@ enum {
                                 reference CPU path's behaviour and this library's parity default) */
   YC_NET_BN_BIAS_GRAD = 256, /* also accumulate the batchnorm shift's gradient into bias_updates (the reference GPU path;
                                 its CPU path leaves it at zero) */
-  YC_NET_DEFAULT = 1 | 2 | 4 | 8 | 16
+  YC_NET_STEM_IM2COL = 512,  /* inference: a first conv with c*size*size <= 32 reads an im2col operand built by the input
+                                conversion (yc_stem_im2col) and runs as a 1x1 layer */
+  YC_NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
 };
 
 /* [setup] LoadNetwork (parser.cpp:1852-1875).  batch <= 0 keeps the cfg's batch (the reference forces
