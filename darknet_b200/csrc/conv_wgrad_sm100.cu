@@ -331,7 +331,10 @@ extern "C" int yc_conv_wgrad_plan_create(yc_wgrad_plan** out_plan, const yc_conv
   splits = std::min(splits, std::max(1, p.kb_total / 8));
   p.kb_per_split = ceil_div(p.kb_total, splits);
   p.splits = ceil_div(p.kb_total, p.kb_per_split);
-  p.a_boxes = out_c > 64 ? 2 : 2;  // M = 128 always: the second box is TMA zero-fill when out_c <= 64
+  // M = 128 always.  out_c <= 64: only the first 64-channel box of dz is loaded; the MMA's second 64-row group (LBO =
+  // one box further) then reads the B region of the stage -> accumulator rows 64..127 hold garbage that the epilogue
+  // never stores (row_ok).  Saves one third of the TMA rows of the small layers, which are TMA-row-rate bound.
+  p.a_boxes = out_c > 64 ? 2 : 1;
   p.b_boxes = p.block_n / 64;
   const uint32_t stage_bytes = (p.a_boxes + p.b_boxes) * kBoxBytes;
   p.stages = std::min<int>(kWgMaxStages, (227 * 1024 - 1024 - 256) / stage_bytes);

@@ -356,8 +356,9 @@ extern "C" int yc_network_finalize(yc_network* net) {
   NET_CUDA(cudaMalloc(&net->input_dev, in_elems * 4));
   NET_CUDA(cudaHostAlloc(&net->input_pinned, in_elems * 4, cudaHostAllocDefault));
   // Stem as im2col + 1x1 (see yc_stem_im2col): the input conversion writes the first conv's GEMM operand directly.
-  const bool stem = !(flags & YC_NET_TRAIN) && (flags & YC_NET_STEM_IM2COL) && nl > 0 && Ls[0].type == L_CONV &&
-                    Ls[0].size > 1 && Ls[0].dilation == 1 && Ls[0].c * Ls[0].size * Ls[0].size <= 32;
+  const bool stem = (flags & YC_NET_STEM_IM2COL) && nl > 0 && Ls[0].type == L_CONV && Ls[0].size > 1 &&
+                    Ls[0].dilation == 1 && Ls[0].c * Ls[0].size * Ls[0].size <= 32;
+  net->stem = stem;
   const int in_ldc = stem ? 32 : round_up(net->c, 8);
   const int in_h = stem ? Ls[0].out_h : net->h, in_w = stem ? Ls[0].out_w : net->w, in_c = stem ? 32 : net->c;
   NET_CUDA(cudaMalloc(&net->input_nhwc, (size_t)net->batch * in_h * in_w * in_ldc * 2));

@@ -25,6 +25,8 @@ using namespace yc;
 namespace {
 
 yc_tensor in_view(const yc_network* net, int i) {
+  if (i == 0 && net->stem)
+    return yc_tensor{net->input_nhwc, net->batch, net->layers[0].out_h, net->layers[0].out_w, 32, 32, YC_BF16};
   if (i == 0) return yc_tensor{net->input_nhwc, net->batch, net->h, net->w, net->c, round_up(net->c, 8), YC_BF16};
   return view_of(net, i - 1);
 }
@@ -35,6 +37,27 @@ yc_tensor delta_view(const yc_network* net, int i) {
 yc_tensor z_view(const yc_network* net, int i) {
   const NLayer& L = net->layers[i];
   return yc_tensor{L.z_buf, net->batch, L.out_h, L.out_w, L.out_c, L.z_ldc, YC_BF16};
+}
+
+// Geometry the GEMM kernels see for conv layer i: the layer's own, or — for the stem (net->stem, layer 0) — a 1x1
+// convolution over the 32 im2col columns, with weights / gradients kept in that [n][32] order (column = tap*c + ci).
+struct Geo { int c, size, stride, pad; };
+Geo geo(const yc_network* net, int i) {
+  const NLayer& L = net->layers[i];
+  if (i == 0 && net->stem) return Geo{32, 1, 1, 0};
+  return Geo{L.c, L.size, L.stride, L.pad};
+}
+// OIHW [n][c][k][k] <-> stem order [n][32]
+void stem_permute(const NLayer& L, const float* src, float* dst, bool to_stem) {
+  const int kk = L.size * L.size;
+  if (to_stem) std::fill(dst, dst + (size_t)L.n * 32, 0.f);
+  for (int f = 0; f < L.n; ++f)
+    for (int ci = 0; ci < L.c; ++ci)
+      for (int t = 0; t < kk; ++t) {
+        const size_t o = ((size_t)f * L.c + ci) * kk + t, q = (size_t)f * 32 + t * L.c + ci;
+        if (to_stem) dst[q] = src[o];
+        else dst[o] = src[q];
+      }
 }
 
 template <typename T>
@@ -99,7 +122,15 @@ int yc_train_finalize(yc_network* net) {
     NLayer& L = Ls[i];
     switch (L.type) {
       case L_CONV: {
-        int rc = upload(&L.w_master, L.weights);
+        const Geo G = geo(net, i);
+        int rc;
+        if (i == 0 && net->stem) {
+          std::vector<float> w2((size_t)L.n * 32);
+          stem_permute(L, L.weights.data(), w2.data(), true);
+          rc = upload(&L.w_master, w2);
+        } else {
+          rc = upload(&L.w_master, L.weights);
+        }
         if (!rc) rc = upload(&L.bias_dev, L.biases);
         if (!rc && L.bn) rc = upload(&L.scale_dev, L.scales);
         if (!rc && L.bn) rc = upload(&L.rmean_dev, L.rmean);
@@ -111,21 +142,21 @@ int yc_train_finalize(yc_network* net) {
         if (!rc) {
           // one contiguous gradient bucket per layer: [weight_updates | bias_updates | scale_updates] — what the
           // data-parallel all-reduce sends in a single call (network_dp.cu)
-          const size_t nw = yc_conv_wgrad_bytes(L.n, L.c, L.size) / 4;
+          const size_t nw = yc_conv_wgrad_bytes(L.n, G.c, G.size) / 4;
           L.bucket_floats = nw + (size_t)round_up(L.n, 4) * 2;
           rc = dev_alloc(&L.dw_packed, L.bucket_floats);
           L.bias_upd = L.dw_packed + nw;
           L.scale_upd = L.bias_upd + round_up(L.n, 4);
         }
         if (rc) return rc;
-        NET_CUDA(cudaMalloc(&L.w_packed, yc_conv_packed_bytes(L.n, L.c, L.size)));
-        NET_CUDA(cudaMalloc(&L.w_packed_d, yc_conv_dgrad_packed_bytes(L.n, L.c, L.size)));
-        rc = yc_conv_pack(L.w_master, L.n, L.c, L.size, L.w_packed, net->stream);
-        if (!rc) rc = yc_conv_pack_dgrad(L.w_master, L.n, L.c, L.size, L.w_packed_d, net->stream);
+        NET_CUDA(cudaMalloc(&L.w_packed, yc_conv_packed_bytes(L.n, G.c, G.size)));
+        NET_CUDA(cudaMalloc(&L.w_packed_d, yc_conv_dgrad_packed_bytes(L.n, G.c, G.size)));
+        rc = yc_conv_pack(L.w_master, L.n, G.c, G.size, L.w_packed, net->stream);
+        if (!rc) rc = yc_conv_pack_dgrad(L.w_master, L.n, G.c, G.size, L.w_packed_d, net->stream);
         if (rc) return rc;
         const yc_tensor x = in_view(net, i);
         const yc_tensor y = view_of(net, i);
-        yc_conv_desc d{L.size, L.stride, L.pad, L.dilation, L.bn ? YC_LINEAR : L.act, YC_LINEAR};
+        yc_conv_desc d{G.size, G.stride, G.pad, L.dilation, L.bn ? YC_LINEAR : L.act, YC_LINEAR};
         if (L.bn) {
           L.z_ldc = round_up(L.out_c, 8);
           const size_t zb = (size_t)B * L.out_h * L.out_w * L.z_ldc * 2;
@@ -141,7 +172,7 @@ int yc_train_finalize(yc_network* net) {
         // backward plans: the GEMMs read dz = this layer's delta after the in-place BN/activation backward
         yc_tensor dz = delta_view(net, i);
         dz.c = L.delta_ldc;
-        yc_conv_desc fd{L.size, L.stride, L.pad, L.dilation, YC_LINEAR, YC_LINEAR};
+        yc_conv_desc fd{G.size, G.stride, G.pad, L.dilation, YC_LINEAR, YC_LINEAR};
         rc = yc_conv_wgrad_plan_create(&L.wplan, &fd, &x, &dz, L.n, L.dw_packed);
         if (rc) return rc;
         if (i > 0) {
@@ -222,8 +253,9 @@ int train_forward(yc_network* net, const float* input_dev, const float* truth_de
   const int B = net->batch;
   NET_CUDA(cudaMemsetAsync(net->delta_slab, 0, net->delta_slab_bytes, st));
   {
-    yc_tensor in{net->input_nhwc, B, net->h, net->w, net->c, round_up(net->c, 8), YC_BF16};
-    int rc = yc_nchw_to_nhwc(input_dev, &in, st);
+    const yc_tensor in = in_view(net, 0);
+    int rc = net->stem ? yc_stem_im2col(input_dev, net->c, net->h, net->w, Ls[0].size, Ls[0].stride, Ls[0].pad, &in, st)
+                       : yc_nchw_to_nhwc(input_dev, &in, st);
     if (rc) return rc;
     tick(CAT_OTHER, st);
   }
@@ -448,7 +480,8 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
   }
   for (NLayer& L : net->layers) {
     if (L.type != L_CONV) continue;
-    int rc = yc_sgd_update_conv(L.w_master, L.dw_packed, L.n, L.c, L.size, lr, batch, carry, decay, L.w_packed,
+    const Geo G = geo(net, (int)(&L - net->layers.data()));
+    int rc = yc_sgd_update_conv(L.w_master, L.dw_packed, L.n, G.c, G.size, lr, batch, carry, decay, L.w_packed,
                                 L.w_packed_d, L.bias_dev, L.bias_upd, L.bn ? L.scale_dev : nullptr,
                                 L.bn ? L.scale_upd : nullptr, st);
     if (rc) return rc;
@@ -547,6 +580,31 @@ extern "C" int yc_network_get_param(yc_network* net, int layer, const char* key,
   const float* src = nullptr;
   size_t count = 0;
   float* tmp = nullptr;
+  if (L.type == L_CONV && layer == 0 && net->stem && (k == "weights" || k == "weight_updates")) {
+    // the stem keeps its weights / gradients in im2col column order [n][32]: hand them out as OIHW
+    const size_t nw = (size_t)L.n * L.c * L.size * L.size, ns = (size_t)L.n * 32;
+    if ((size_t)capacity < nw) {
+      set_error("yc_network_get_param: capacity %d < %zu", capacity, nw);
+      return YC_ERR_ARG;
+    }
+    std::vector<float> h(ns);
+    const float* from = L.w_master;
+    if (k == "weight_updates") {
+      NET_CUDA(cudaMalloc(&tmp, ns * 4));
+      int rc = yc_conv_wgrad_unpack(L.dw_packed, L.n, 32, 1, tmp, net->stream);
+      if (rc) { cudaFree(tmp); return rc; }
+      from = tmp;
+    }
+    cudaError_t e = cudaMemcpyAsync(h.data(), from, ns * 4, cudaMemcpyDeviceToHost, net->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(net->stream);
+    if (tmp) cudaFree(tmp);
+    if (e != cudaSuccess) {
+      set_error("yc_network_get_param: %s", cudaGetErrorString(e));
+      return YC_ERR_CUDA;
+    }
+    stem_permute(L, h.data(), dst_host, false);
+    return (int)nw;
+  }
   if (L.type == L_CONV) {
     const size_t nw = (size_t)L.n * L.c * L.size * L.size;
     if (k == "weights") { src = L.w_master; count = nw; }
