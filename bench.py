@@ -37,6 +37,7 @@ if ROOT not in sys.path:
 METRIC = "images_per_sec"
 UNIT = "images/s"
 TRAIN_WL = "yolov4-tiny.cfg 416x416 training fwd+bwd+update batch 64, data-parallel NCCL grad allreduce"
+TRAIN_WL_G = "yolov3 Gaussian-YOLO (gaussian_yolo_layer) 608x608 training fwd+bwd+update batch 64"
 WORKLOADS = {
     "yolov4": ("yolov4", 608, "yolov4.cfg 608x608 batch 64 inference"),
     "yolov3": ("yolov3", 416, "yolov3.cfg 416x416 batch 64 inference"),
@@ -162,11 +163,12 @@ def run_reference_train(args):
     """--impl reference --mode train: the reference's own CPU training step (forward(train) + backward + update)."""
     if int(os.environ.get("RANK", "0")) != 0:
         return 0
-    hw, cfgname = 416, "yolov4-tiny"
+    cfgname = args.train_net
+    hw = 416 if cfgname == "yolov4-tiny" else 608
     vals, sample, cores = [], "", os.cpu_count() or 1
     per_step_budget = max(2.0, 150.0 / max(1, args.steps + args.warmup))
     for i in range(args.warmup + args.steps):
-        info, cores, sample = _time_ref_train(cfgname, hw, per_step_budget, 8)
+        info, cores, sample = _time_ref_train(cfgname, hw, per_step_budget, 8 if hw == 416 else 2)
         if info is None:
             print(json.dumps({"impl": "reference", "unavailable": sample}))
             return 0
@@ -176,8 +178,8 @@ def run_reference_train(args):
     out = {"metric": "train_images_per_sec", "value": v, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * args.batch / v, "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": TRAIN_WL, "net": cfgname, "width": hw, "height": hw, "batch": args.batch,
-                      "note": "CPU reference timed at batch 8 per step (bounded sample); ms_per_step = the named batch at that rate"},
+           "config": {"workload": TRAIN_WL if hw == 416 else TRAIN_WL_G, "net": cfgname, "width": hw, "height": hw, "batch": args.batch,
+                      "note": "CPU reference timed at a reduced batch per step (bounded sample); ms_per_step = the named batch at that rate"},
            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(out))
@@ -202,7 +204,8 @@ def run_train(args):
     if world > 1:
         import torch.distributed as dist  # noqa: F811
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    cfgname, hw, B = "yolov4-tiny", 416, args.batch
+    cfgname, B = args.train_net, args.batch
+    hw = 416 if cfgname == "yolov4-tiny" else 608
     text = cfgs.CONFIGS[cfgname](w=hw, h=hw, batch=B, subdivisions=1)
     weights = cfgmod.synth_weights(text)
     net = N.LoadSynthetic(text, weights, batch=B, flags=L.NET_DEFAULT | L.NET_TRAIN)
@@ -214,6 +217,7 @@ def run_train(args):
     flops_step = (3.0 * flops_fwd - f0) * B      # fprop + wgrad for every conv, dgrad for all but the first
     x = cfgmod.synth_images(B, 3, hw, hw, seed=1234 + rank)
     truth = cfgmod.synth_truth(B, 90, classes=80, seed=4321 + rank)
+    info_mib = L.lib().yc_network_train_info(net.h, 2)
     xd, td = torch.from_numpy(x).cuda(), torch.from_numpy(truth).cuda()
     stream = torch.cuda.current_stream()
     sp = L.stream_ptr()
@@ -298,14 +302,15 @@ def _run_train_tail(args, v):
                     "how": "algorithmic FLOPs (fprop + wgrad of every conv, dgrad of all but the first) / summed duration of "
                            "those kernels, each operator bracketed by CUDA events (yc_network_train_profile, 3 passes)"}
             if not args.no_cpu_baseline and world == 1:
-                info, cores, sample = _time_ref_train("yolov4-tiny", hw, args.cpu_budget, 8)
+                info, cores, sample = _time_ref_train(v["cfgname"], hw, args.cpu_budget, 8 if hw == 416 else 2)
                 cpu = {"value": info["images_per_s"] if info else None, "unit": UNIT, "cores": cores, "kind": "reference",
                        "sample": sample}
     if rank == 0:
         out = {"metric": "train_images_per_sec", "value": v["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
                "warmup": max(3, args.warmup), "ms_per_step": v["ms_per_step"], "higher_is_better": True, "scaling": "weak",
                "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-               "config": {"workload": TRAIN_WL, "net": "yolov4-tiny", "width": hw, "height": hw, "batch_per_gpu": B,
+               "config": {"workload": TRAIN_WL if v["cfgname"] == "yolov4-tiny" else TRAIN_WL_G, "net": v["cfgname"], "width": hw,
+                          "height": hw, "batch_per_gpu": B,
                           "global_batch": B * world, "truth_boxes_per_image": 90,
                           "parallelism": (f"data-parallel x{world}: one NCCL all-reduce per conv-layer gradient bucket, overlapped "
                                           f"with backward ({L.lib().yc_network_dp_info(net.h, 2)} buckets, "
@@ -348,6 +353,8 @@ def main():
     ap.add_argument("--mode", default="infer", choices=["infer", "train"],
                     help="infer: the headline (BASELINE configs[2]); train: configs[3], yolov4-tiny 416 fwd+bwd+update")
     ap.add_argument("--workload", default="yolov4", choices=sorted(WORKLOADS))
+    ap.add_argument("--train-net", default="yolov4-tiny", choices=["yolov4-tiny", "gaussian-yolov3"],
+                    help="--mode train: yolov4-tiny 416 (configs[3]) or Gaussian-YOLOv3 608 (configs[4])")
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)

@@ -163,6 +163,10 @@ int build_layers(yc_network* net, const std::string& text, int batch) {
         L.cls_normalizer = s.get_float("cls_normalizer", 1.f);
         L.label_smooth_eps = s.get_float("label_smooth_eps", 0.f);
         L.max_delta = s.get_float("max_delta", 3.402823466e+38F);
+        L.uc_normalizer = s.get_float("uc_normalizer", 1.f);  // ParseGaussianYolo parser.cpp:471
+        const std::string yp = s.get_str("yolo_point", "center");
+        if (L.type == L_GYOLO && yp != "center")
+          NET_FAIL(YC_ERR_ARG, "layer %d: yolo_point=%s is not supported (center only)", idx, yp.c_str());
       }
       const int E = (L.type == L_YOLO ? 5 : 9) + L.classes;
       if ((int)L.mask.size() * E != c)

@@ -57,7 +57,7 @@ struct NLayer {
   // yolo hyper-parameters (ParseYolo parser.cpp:312-415)
   int max_boxes = 90, iou_loss = 2 /*MSE*/, iou_thresh_kind = 0, focal_loss = 0;
   float ignore_thresh = .5f, truth_thresh = 1.f, iou_thresh = 1.f, iou_normalizer = .75f, cls_normalizer = 1.f,
-        label_smooth_eps = 0.f, max_delta = 3.402823466e+38F;
+        label_smooth_eps = 0.f, max_delta = 3.402823466e+38F, uc_normalizer = 1.f;
   float* w_master = nullptr;     // fp32 OIHW (l->weights_gpu)
   float* rmean_dev = nullptr;    // l->rolling_mean_gpu
   float* rvar_dev = nullptr;

@@ -198,7 +198,8 @@ int yc_train_finalize(yc_network* net) {
         NET_CUDA(cudaMemset(L.idx_buf, 255, ib));
         break;
       }
-      case L_YOLO: {
+      case L_YOLO:
+      case L_GYOLO: {
         const size_t elems = (size_t)B * L.out_c * L.out_h * L.out_w;
         NET_CUDA(cudaMalloc(&L.dec_dev, elems * 4));
         NET_CUDA(cudaHostAlloc(&L.dec_host, elems * 4, cudaHostAllocDefault));
@@ -214,8 +215,6 @@ int yc_train_finalize(yc_network* net) {
         if (i == 0 || Ls[i - 1].type != L_CONV) NET_FAIL(YC_ERR_ARG, "layer %d: a [yolo] layer must follow its head conv", i);
         break;
       }
-      case L_GYOLO:
-        NET_FAIL(YC_ERR_ARG, "layer %d: Gaussian_yolo training (gaussian_yolo_layer.cpp:486-857) is not built yet", i);
       default: break;
     }
   }
@@ -308,9 +307,10 @@ int train_forward(yc_network* net, const float* input_dev, const float* truth_de
         }
         break;
       }
-      case L_YOLO: {
+      case L_YOLO:
+      case L_GYOLO: {
         const yc_tensor x = in_view(net, i);
-        rc = yc_yolo_decode(&x, L.dec_dev, L.n, L.classes, L.scale_x_y, 0, st);
+        rc = yc_yolo_decode(&x, L.dec_dev, L.n, L.classes, L.scale_x_y, L.type == L_GYOLO ? 1 : 0, st);
         if (rc) return rc;
         yc_yolo_loss_desc d;
         d.anchors = L.n; d.total = L.total; d.classes = L.classes; d.max_boxes = L.max_boxes;
@@ -318,6 +318,7 @@ int train_forward(yc_network* net, const float* input_dev, const float* truth_de
         d.focal_loss = L.focal_loss; d.ignore_thresh = L.ignore_thresh; d.truth_thresh = L.truth_thresh;
         d.iou_thresh = L.iou_thresh; d.iou_normalizer = L.iou_normalizer; d.cls_normalizer = L.cls_normalizer;
         d.label_smooth_eps = L.label_smooth_eps; d.max_delta = L.max_delta;
+        d.gaussian = L.type == L_GYOLO ? 1 : 0; d.uc_normalizer = L.uc_normalizer;
         const yc_tensor pd = delta_view(net, i - 1);
         // BackwardYoloLayerGpu (yolo_layer.cpp:884-888) is folded into the loss kernel: the head conv's delta was
         // zeroed at the start of the step and has no other contributor
@@ -623,7 +624,7 @@ extern "C" int yc_network_get_param(yc_network* net, int layer, const char* key,
       else if (k == "variance") { src = L.var_dev; count = L.n; }
       else if (k == "scale_updates") { src = L.scale_upd; count = L.n; }
     }
-  } else if (L.type == L_YOLO) {
+  } else if (L.type == L_YOLO || L.type == L_GYOLO) {
     if (k == "cost") { src = L.ystats; count = 1; }
     else if (k == "stats") { src = L.ystats; count = 8; }
   }

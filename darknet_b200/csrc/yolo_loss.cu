@@ -203,6 +203,8 @@ struct LossParams {
   int B, H, W, n, total, classes, max_boxes, net_w, net_h;
   int iou_loss, iou_thresh_kind, focal_loss;
   float ignore_thresh, truth_thresh, iou_thresh, iou_normalizer, cls_normalizer, label_smooth_eps, max_delta;
+  int gaussian;         // 1: [Gaussian_yolo] entry layout mu_x,s_x,mu_y,s_y,mu_w,s_w,mu_h,s_h,obj,classes (gaussian_yolo_layer.cpp)
+  float uc_normalizer;
   const float* out;     // decoded head, fp32 NCHW
   const float* truth;   // [B][max_boxes*5]
   const float* biases;  // anchors, 2*total
@@ -212,10 +214,13 @@ struct LossParams {
                         // [6] tot_iou [7] class_count
 };
 
-__device__ __forceinline__ int entry_index(const LossParams& p, int b, int location, int entry) {  // yolo_layer.cpp:380-386
+__device__ __forceinline__ int box_entries(const LossParams& p) { return p.gaussian ? 8 : 4; }  // obj follows, then classes
+// yolo_layer.cpp:380-386 / EntryGaussianIndex gaussian_yolo_layer.cpp:476-484
+__device__ __forceinline__ int entry_index(const LossParams& p, int b, int location, int entry) {
   const int wh = p.W * p.H;
+  const int E = box_entries(p) + 1 + p.classes;
   const int n = location / wh, loc = location % wh;
-  return b * (p.n * (5 + p.classes) * wh) + n * wh * (5 + p.classes) + entry * wh + loc;
+  return b * (p.n * E * wh) + n * wh * E + entry * wh + loc;
 }
 __device__ __forceinline__ BoxF get_yolo_box(const float* x, const float* biases, int n, int index, int i, int j, int lw,
                                              int lh, int w, int h, int stride) {  // yolo_layer.cpp:139-148
@@ -271,6 +276,95 @@ __device__ IousF delta_yolo_box(const LossParams& p, const BoxF& truth, int n, i
   return all;
 }
 
+// GetGaussianYoloBox (gaussian_yolo_layer.cpp:151-178), yolo_point = center
+__device__ __forceinline__ BoxF get_gaussian_box(const float* x, const float* biases, int n, int index, int i, int j, int lw,
+                                                 int lh, int w, int h, int stride) {
+  BoxF b;
+  b.w = expf(x[index + 4 * stride]) * biases[2 * n] / w;
+  b.h = expf(x[index + 6 * stride]) * biases[2 * n + 1] / h;
+  b.x = (i + x[index + 0 * stride]) / lw;
+  b.y = (j + x[index + 2 * stride]) / lh;
+  return b;
+}
+__device__ __forceinline__ BoxF get_box(const LossParams& p, int n, int index, int i, int j) {
+  const int wh = p.W * p.H;
+  return p.gaussian ? get_gaussian_box(p.out, p.biases, n, index, i, j, p.W, p.H, p.net_w, p.net_h, wh)
+                    : get_yolo_box(p.out, p.biases, n, index, i, j, p.W, p.H, p.net_w, p.net_h, wh);
+}
+
+// delta_gaussian_yolo_box (gaussian_yolo_layer.cpp:198-402), accumulate = 1, yolo_point = center; ONE thread.
+// The reference mixes float and double (the literals 1./2., M_PI, pow): the same promotions are kept.
+__device__ float delta_gaussian_box(const LossParams& p, const BoxF& truth, int n, int index, int i, int j, float scale,
+                                    float iou_normalizer) {
+  const int stride = p.W * p.H;
+  const float* x = p.out;
+  float* delta = p.delta;
+  BoxF pred = get_gaussian_box(x, p.biases, n, index, i, j, p.W, p.H, p.net_w, p.net_h, stride);
+  float iou = b_iou(pred, truth);
+  const float giou = b_giou(pred, truth);
+  if (pred.w == 0) pred.w = 1.0f;
+  if (pred.h == 0) pred.h = 1.0f;
+  const float sigma_const = 0.3f;
+  const float epsi = (float)pow(10.0, -9.0);
+  const float t4[4] = {truth.x * p.W - i, truth.y * p.H - j, logf(truth.w * p.net_w / p.biases[2 * n]),
+                       logf(truth.h * p.net_h / p.biases[2 * n + 1])};
+  float dl[4], du[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float mu = x[index + (2 * k) * stride], sg = x[index + (2 * k + 1) * stride];
+    const float d = t4[k] - mu;
+    const float in_exp = d / sg;
+    const float in_exp_2 = (float)pow((double)in_exp, 2.0);
+    const float normal = (float)(exp((double)in_exp_2 * (-1. / 2.)) / (sqrt(M_PI * 2.0) * (double)(sg + sigma_const)));
+    const float temp = (float)((1. / 2.) * 1. / (double)(normal + epsi) * (double)normal * (double)scale);
+    dl[k] = (float)((double)(temp * in_exp) * (1. / (double)sg));
+    du[k] = (float)((double)temp * ((double)(in_exp_2 / sg) - 1. / (double)(sg + sigma_const)));
+  }
+  if (p.iou_loss != IOU_MSE) {
+    iou = giou;
+    const DxRep g = b_dx_iou(pred, truth, p.iou_loss);
+    dl[0] = g.dt; dl[1] = g.db;
+    dl[2] = g.dl * expf(x[index + 4 * stride]);
+    dl[3] = g.dr * expf(x[index + 6 * stride]);
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    dl[k] = fix_nan_inf(dl[k] * iou_normalizer);
+    du[k] = fix_nan_inf(du[k] * p.uc_normalizer);
+    if (p.max_delta != FLT_MAX) {
+      dl[k] = clip_value(dl[k], p.max_delta);
+      du[k] = clip_value(du[k], p.max_delta);
+    }
+    delta[index + (2 * k) * stride] += dl[k];
+    delta[index + (2 * k + 1) * stride] += du[k];
+  }
+  return iou;
+}
+
+// DeltaGaussianYoloClass (gaussian_yolo_layer.cpp:429-461): the "already marked" test looks at the FIRST class entry
+// (delta[index]), no focal loss, no NaN filter.  Lanes split the class loop like delta_yolo_class.
+__device__ float delta_gaussian_class(const LossParams& p, int index, int class_id, int lane, int nl) {
+  const int stride = p.W * p.H;
+  const float* output = p.out;
+  float* delta = p.delta;
+  const bool marked = delta[index] != 0.f;
+  if (nl > 1) __syncwarp();
+  if (marked) {
+    float y_true = 1;
+    if (p.label_smooth_eps) y_true = y_true * (1 - p.label_smooth_eps) + 0.5f * p.label_smooth_eps;
+    if (lane == 0) delta[index + stride * class_id] = y_true - output[index + stride * class_id];
+    if (nl > 1) __syncwarp();
+    return output[index + stride * class_id];
+  }
+  for (int n = lane; n < p.classes; n += nl) {
+    float y_true = ((n == class_id) ? 1 : 0);
+    if (p.label_smooth_eps) y_true = y_true * (1 - p.label_smooth_eps) + 0.5f * p.label_smooth_eps;
+    delta[index + stride * n] = y_true - output[index + stride * n];
+  }
+  if (nl > 1) __syncwarp();
+  return output[index + stride * class_id];
+}
+
 // delta_yolo_class (yolo_layer.cpp:285-357); the class loop is strided over `nl` cooperating lanes (lane, nl) =
 // (0, 1) for a single thread.  Returns the avg_cat contribution.
 __device__ float delta_yolo_class(const LossParams& p, int index, int class_id, int lane, int nl) {
@@ -319,9 +413,9 @@ __global__ void yolo_loss_cells_kernel(LossParams p) {
     const int b = (int)(t0 / ((long long)wh * p.n));
     const int i = loc % p.W, j = loc / p.W;
     const int box_index = entry_index(p, b, n * wh + loc, 0);
-    const int obj_index = entry_index(p, b, n * wh + loc, 4);
-    const int class_index = entry_index(p, b, n * wh + loc, 5);
-    const BoxF pred = get_yolo_box(p.out, p.biases, p.mask[n], box_index, i, j, p.W, p.H, p.net_w, p.net_h, wh);
+    const int obj_index = entry_index(p, b, n * wh + loc, box_entries(p));
+    const int class_index = entry_index(p, b, n * wh + loc, box_entries(p) + 1);
+    const BoxF pred = get_box(p, p.mask[n], box_index, i, j);
     float best_match_iou = 0, best_iou = 0;
     int best_t = 0;
     int class_match = -1;  // compare_yolo_class(..., 0.25f) does not depend on the truth: evaluated once, on demand
@@ -347,9 +441,14 @@ __global__ void yolo_loss_cells_kernel(LossParams p) {
     if (best_iou > p.truth_thresh) {
       p.delta[obj_index] = p.cls_normalizer * (1 - o);
       const int class_id = (int)tr[best_t * 5 + 4];
-      delta_yolo_class(p, class_index, class_id, 0, 1);
       const BoxF truth{tr[best_t * 5 + 0], tr[best_t * 5 + 1], tr[best_t * 5 + 2], tr[best_t * 5 + 3]};
-      delta_yolo_box(p, truth, p.mask[n], box_index, i, j, (2 - truth.w * truth.h), p.iou_normalizer);
+      if (p.gaussian) {
+        delta_gaussian_class(p, class_index, class_id, 0, 1);
+        delta_gaussian_box(p, truth, p.mask[n], box_index, i, j, (2 - truth.w * truth.h), p.iou_normalizer);
+      } else {
+        delta_yolo_class(p, class_index, class_id, 0, 1);
+        delta_yolo_box(p, truth, p.mask[n], box_index, i, j, (2 - truth.w * truth.h), p.iou_normalizer);
+      }
     }
   }
 }
@@ -397,12 +496,13 @@ __global__ void yolo_loss_truths_kernel(LossParams p) {
       }
       const int loc = mask_n * wh + j * p.W + i;
       const int box_index = entry_index(p, b, loc, 0);
-      const int obj_index = entry_index(p, b, loc, 4);
-      const int class_index = entry_index(p, b, loc, 5);
+      const int obj_index = entry_index(p, b, loc, box_entries(p));
+      const int class_index = entry_index(p, b, loc, box_entries(p) + 1);
       __syncwarp();
       IousF all{0, 0, 0, 0};
       if (lane == 0) {
-        all = delta_yolo_box(p, truth, n_abs, box_index, i, j, (2 - truth.w * truth.h), p.iou_normalizer);
+        if (p.gaussian) all.iou = all.giou = delta_gaussian_box(p, truth, n_abs, box_index, i, j, (2 - truth.w * truth.h), p.iou_normalizer);
+        else all = delta_yolo_box(p, truth, n_abs, box_index, i, j, (2 - truth.w * truth.h), p.iou_normalizer);
         p.delta[obj_index] = p.cls_normalizer * (1 - p.out[obj_index]);
         tot_iou += all.iou;
         tot_iou_loss += 1 - all.iou;
@@ -410,7 +510,8 @@ __global__ void yolo_loss_truths_kernel(LossParams p) {
         ++count;
       }
       __syncwarp();
-      delta_yolo_class(p, class_index, class_id, lane, 32);
+      if (p.gaussian) delta_gaussian_class(p, class_index, class_id, lane, 32);
+      else delta_yolo_class(p, class_index, class_id, lane, 32);
     }
   }
   if (lane == 0 && count > 0) {
@@ -426,7 +527,8 @@ __global__ void yolo_loss_truths_kernel(LossParams p) {
 // (:708-733), and BackwardYoloLayer's prev.delta += delta (:774-777) into the head conv's NHWC bf16 delta -----------
 __global__ void yolo_loss_finish_kernel(LossParams p, __nv_bfloat16* __restrict__ prev, long long prev_ld) {
   const int wh = p.W * p.H;
-  const int E = 5 + p.classes;
+  const int BE = box_entries(p);
+  const int E = BE + 1 + p.classes;
   const long long total = (long long)p.B * p.n * wh;
   float s_all = 0, s_nobox = 0;
   for (long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; t0 < total; t0 += (long long)gridDim.x * blockDim.x) {
@@ -436,16 +538,16 @@ __global__ void yolo_loss_finish_kernel(LossParams p, __nv_bfloat16* __restrict_
     const int base = entry_index(p, b, n * wh + loc, 0);
     int in_box = 0;
     for (int c = 0; c < p.classes; ++c)
-      if (p.delta[base + (5 + c) * wh] > 0) ++in_box;
+      if (p.delta[base + (BE + 1 + c) * wh] > 0) ++in_box;
     __nv_bfloat16* pv = prev ? prev + ((long long)b * wh + loc) * prev_ld + n * E : nullptr;
     for (int e = 0; e < E; ++e) {
       float d = p.delta[base + e * wh];
-      if (e < 4 && in_box > 0) {
+      if (e < BE && in_box > 0) {
         d /= in_box;
         p.delta[base + e * wh] = d;
       }
       s_all += d * d;
-      if (e >= 4) s_nobox += d * d;
+      if (e >= BE) s_nobox += d * d;
       if (pv) pv[e] = __float2bfloat16_rn(__bfloat162float(pv[e]) + d);
     }
   }
@@ -476,7 +578,7 @@ __global__ void yolo_loss_cost_kernel(LossParams p) {
   float count = p.stats[1];
   if (count == 0) count = 1;
   const float classification_loss = p.cls_normalizer * p.stats[5];
-  if (p.iou_loss == IOU_MSE) {
+  if (p.iou_loss == IOU_MSE || p.gaussian) {  // Gaussian: *(l->cost) = |delta|^2 always (gaussian_yolo_layer.cpp:835)
     p.stats[0] = p.stats[4];
   } else {
     const float tot = p.iou_loss == IOU_GIOU ? p.stats[3] : p.stats[2];
@@ -494,7 +596,7 @@ extern "C" int yc_yolo_loss(const yc_yolo_loss_desc* d, const float* out_nchw, c
   YC_REQUIRE(d && out_nchw && truth && anchor_wh && mask && delta_nchw && stats && n > 0 && h > 0 && w > 0,
              "yc_yolo_loss: bad arguments");
   YC_REQUIRE(d->anchors > 0 && d->total >= d->anchors && d->classes > 0 && d->max_boxes > 0, "yc_yolo_loss: bad descriptor");
-  const int E = 5 + d->classes;
+  const int E = (d->gaussian ? 9 : 5) + d->classes;
   if (prev_delta)
     YC_REQUIRE(prev_delta->dtype == YC_BF16 && prev_delta->n == n && prev_delta->h == h && prev_delta->w == w &&
                    prev_delta->ldc >= d->anchors * E,
@@ -506,6 +608,8 @@ extern "C" int yc_yolo_loss(const yc_yolo_loss_desc* d, const float* out_nchw, c
   p.focal_loss = d->focal_loss; p.ignore_thresh = d->ignore_thresh; p.truth_thresh = d->truth_thresh;
   p.iou_thresh = d->iou_thresh; p.iou_normalizer = d->iou_normalizer; p.cls_normalizer = d->cls_normalizer;
   p.label_smooth_eps = d->label_smooth_eps; p.max_delta = d->max_delta;
+  p.gaussian = d->gaussian ? 1 : 0; p.uc_normalizer = d->uc_normalizer;
+  YC_REQUIRE(!(p.gaussian && p.focal_loss), "yc_yolo_loss: [Gaussian_yolo] has no focal loss");
   p.out = out_nchw; p.truth = truth; p.biases = anchor_wh; p.mask = mask; p.delta = delta_nchw; p.stats = stats;
   const size_t elems = (size_t)n * d->anchors * E * h * w;
   YC_CUDA(cudaMemsetAsync(delta_nchw, 0, elems * 4, st));

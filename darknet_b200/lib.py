@@ -36,7 +36,8 @@ class YoloLossDesc(C.Structure):
                 ("net_w", C.c_int), ("net_h", C.c_int), ("iou_loss", C.c_int), ("iou_thresh_kind", C.c_int),
                 ("focal_loss", C.c_int), ("ignore_thresh", C.c_float), ("truth_thresh", C.c_float),
                 ("iou_thresh", C.c_float), ("iou_normalizer", C.c_float), ("cls_normalizer", C.c_float),
-                ("label_smooth_eps", C.c_float), ("max_delta", C.c_float)]
+                ("label_smooth_eps", C.c_float), ("max_delta", C.c_float), ("gaussian", C.c_int),
+                ("uc_normalizer", C.c_float)]
 
 
 class Detection(C.Structure):

@@ -293,8 +293,10 @@ def yolo_extract(decoded, anchors_wh, mask, classes, net_w, net_h, thresh, rows_
 
 def yolo_loss(out_nchw, truth, anchors_wh, mask, classes, net_w, net_h, max_boxes=90, total=None, iou_loss="mse",
               iou_thresh_kind="iou", focal_loss=0, ignore_thresh=.5, truth_thresh=1.0, iou_thresh=1.0,
-              iou_normalizer=.75, cls_normalizer=1.0, label_smooth_eps=0.0, max_delta=3.402823466e+38, prev_delta=None):
-    """ForwardYoloLayer's training half + BackwardYoloLayer on the device. Returns (delta_nchw, stats[8])."""
+              iou_normalizer=.75, cls_normalizer=1.0, label_smooth_eps=0.0, max_delta=3.402823466e+38, prev_delta=None,
+              gaussian=False, uc_normalizer=1.0):
+    """ForwardYoloLayer's (or ForwardGaussianYoloLayer's) training half + Backward*YoloLayer on the device.
+    Returns (delta_nchw, stats[8])."""
     kinds = {"iou": 0, "giou": 1, "mse": 2, "diou": 3, "ciou": 4}
     n, c, h, w = out_nchw.shape
     dev = out_nchw.device
@@ -304,7 +306,7 @@ def yolo_loss(out_nchw, truth, anchors_wh, mask, classes, net_w, net_h, max_boxe
     total = a.numel() // 2 if total is None else total
     d = L.YoloLossDesc(len(mask), total, classes, max_boxes, net_w, net_h, kinds[iou_loss], kinds[iou_thresh_kind],
                        focal_loss, ignore_thresh, truth_thresh, iou_thresh, iou_normalizer, cls_normalizer,
-                       label_smooth_eps, max_delta)
+                       label_smooth_eps, max_delta, 1 if gaussian else 0, uc_normalizer)
     delta = torch.empty_like(out_nchw)
     stats = torch.zeros(8, dtype=torch.float32, device=dev)
     pv = None

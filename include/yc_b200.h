@@ -245,6 +245,10 @@ typedef struct yc_yolo_loss_desc {
   int iou_loss, iou_thresh_kind; /* IOU_LOSS (box.h:6-13): 0 iou, 1 giou, 2 mse, 3 diou, 4 ciou */
   int focal_loss;
   float ignore_thresh, truth_thresh, iou_thresh, iou_normalizer, cls_normalizer, label_smooth_eps, max_delta;
+  int gaussian;        /* 1: [Gaussian_yolo] — entries mu_x,s_x,mu_y,s_y,mu_w,s_w,mu_h,s_h,obj,classes; Gaussian NLL box
+                          gradients + uncertainty gradients (ForwardGaussianYoloLayer, gaussian_yolo_layer.cpp:486-857,
+                          yolo_point = center); cost = sum delta^2 */
+  float uc_normalizer; /* l->uc_normalizer (parser.cpp:471) */
 } yc_yolo_loss_desc;
 YC_API int yc_yolo_loss(const yc_yolo_loss_desc* desc, const float* out_nchw, const float* truth, const float* anchor_wh,
                         const int* mask, int n, int h, int w, float* delta_nchw, const yc_tensor* prev_delta,

@@ -72,3 +72,45 @@ def test_yolo_loss_vs_reference(gpu, iou_loss, extra):
         # BackwardYoloLayer: prev.delta (zero here) += delta, written as NHWC bf16
         pv = prev.float().cpu().numpy()[..., :out.shape[1]].transpose(0, 3, 1, 2)
         assert np.abs(pv - dref).max() <= 8e-3 * max(1.0, np.abs(dref).max())
+
+
+@pytest.mark.parametrize("iou_loss,extra", [("giou", {}), ("mse", {}), ("ciou", {}), ("diou", {}), ("giou", {"label_smooth_eps": 0.1}),
+                                            ("mse", {"max_delta": 2}), ("mse", {"uc_normalizer": 0.5}),
+                                            ("giou", {"iou_thresh": 1})])
+def test_gaussian_yolo_loss_vs_reference(gpu, iou_loss, extra):
+    """[Gaussian_yolo] (BASELINE configs[4]): ForwardGaussianYoloLayer's training half (gaussian_yolo_layer.cpp:525-857)
+    on the reference's own decoded head.  The reference evaluates the Gaussian terms in mixed float/double and is built
+    with -Ofast, so deltas agree to 5e-5 absolute rather than 2e-5."""
+    from darknet_b200 import ops
+    if not pyoracle.have_ref():
+        pytest.skip("oracle/_ref not built")
+    B, classes = 4, 3
+    text = cfgs.micro(batch=B, subdivisions=1, classes=classes, gaussian=True).replace("iou_loss=giou", "iou_loss=" + iou_loss)
+    kw = dict(iou_thresh=0.213, iou_normalizer=0.5, cls_normalizer=1.0, ignore_thresh=.7, truth_thresh=1.0, uc_normalizer=1.0)
+    for k, v in extra.items():
+        if k == "iou_thresh":
+            text = text.replace("iou_thresh=0.213", f"iou_thresh={v}")
+        elif k == "uc_normalizer":
+            text = text.replace("uc_normalizer=1.0", f"uc_normalizer={v}")
+        else:
+            text = text.replace("random=0", f"random=0\n{k}={v}")
+        kw[k] = v
+    tag = "gloss_" + iou_loss + "_" + "_".join(f"{k}{v}" for k, v in extra.items())
+    truth, heads = _ref_heads(text, tag, B, classes, seed=21)
+    assert len(heads) == 2
+    masks = {17: [3, 4, 5], 24: [0, 1, 2]}
+    for (i, out, dref, cost) in heads:
+        assert out.shape[1] == 3 * (9 + classes)
+        o = torch.from_numpy(np.ascontiguousarray(out)).to(gpu)
+        prev = torch.zeros((B, out.shape[2], out.shape[3], 40), dtype=torch.bfloat16, device=gpu)
+        delta, stats = ops.yolo_loss(o, truth, ANCH, masks[i], classes, 64, 64, iou_loss=iou_loss, prev_delta=prev,
+                                     gaussian=True, **kw)
+        torch.cuda.synchronize()
+        d = delta.cpu().numpy()
+        assert np.abs(dref).max() > 0.1, "reference produced no deltas: the case tests nothing"
+        err = np.abs(d - dref).max()
+        assert err < 5e-5 * max(1.0, np.abs(dref).max()), f"head {i}: delta max abs err {err:.3e} (max |delta| {np.abs(dref).max():.3f})"
+        st = stats.cpu().numpy()
+        assert abs(st[0] - cost) <= 1e-4 * abs(cost) + 1e-5, f"head {i}: cost {st[0]} vs {cost}"
+        pv = prev.float().cpu().numpy()[..., :out.shape[1]].transpose(0, 3, 1, 2)
+        assert np.abs(pv - dref).max() <= 8e-3 * max(1.0, np.abs(dref).max())
