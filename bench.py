@@ -459,6 +459,29 @@ def main():
                "detections_per_step": int(counts.sum()),
                "api": "yc_network_predict(pinned host fp32 NCHW) + yc_network_detect(thresh .25, nms .45)"}
 
+        # same end-to-end step fed with u8 HWC images (ProcImage's Mat2Image + NetworkPredict): the H2D
+        # copy carries bytes instead of floats
+        u8 = N.InputBufferU8(net)
+        u8[...] = np.clip(np.rint(np.asarray(x_host).transpose(0, 2, 3, 1) * 255.0), 0, 255).astype(np.uint8)
+        def e2e_u8_step():
+            N.NetworkPredictU8(net, u8)
+            return N.DetectBatch(net, 0.25, 0.45)
+        for _ in range(2):
+            e2e_u8_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            rows8, counts8 = e2e_u8_step()
+        torch.cuda.synchronize()
+        t_u8 = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([t_u8], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            t_u8 = float(t.item())
+        e2e["u8_input"] = {"value": world * B * args.steps / t_u8, "unit": UNIT, "h2d_bytes_per_step": int(u8.nbytes),
+                           "ms_per_step": 1e3 * t_u8 / args.steps,
+                           "api": "yc_network_predict_u8(pinned host u8 HWC) + yc_network_detect"}
+
         # ---- roofline of the dominant kernel (conv_fprop_kernel), rank 0 ---------------------------------
         if rank == 0:
             nl = net.n

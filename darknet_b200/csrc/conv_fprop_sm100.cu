@@ -592,6 +592,9 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
     if (e == cudaSuccess) e = cudaMemset(pl->scale_pad, 0, sizeof(float) * npad);
     if (e == cudaSuccess) e = cudaMemcpy(pl->scale_pad, scale, sizeof(float) * N, cudaMemcpyDeviceToDevice);
   }
+  // the memsets / copies above run on the legacy default stream, asynchronously to the host; launches go to the
+  // caller's (possibly non-blocking) stream, so finish them here (setup time)
+  if (e == cudaSuccess) e = cudaStreamSynchronize(cudaStreamLegacy);
   if (e != cudaSuccess) {
     set_error("yc_conv_plan_create: bias staging failed: %s", cudaGetErrorString(e));
     yc_conv_plan_destroy(pl);

@@ -140,6 +140,19 @@ __global__ void stem_im2col_kernel(const float* __restrict__ src, __nv_bfloat16*
   }
 }
 
+// ---- Mat2Image on the device (visualize.cpp:26-54): u8 HWC -> fp32 NCHW in [0,1] ----------------------------------
+// image->data[k*w*h + y*w + x] = data[y*step + x*c + k] / 255.0f; swap_rb folds the preceding cvtColor(RGB2BGR)
+// (yolo_core.cpp:110) by reading channel c-1-k.  thread = pixel: 3 contiguous bytes in, one coalesced store per plane.
+__global__ void u8hwc_to_nchw_kernel(const unsigned char* __restrict__ src, float* __restrict__ dst, int B, int C, int H, int W,
+                                     int swap) {
+  const long long hw = (long long)H * W, total = (long long)B * hw;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long b = i / hw, s = i - b * hw;
+    const unsigned char* px = src + i * C;
+    for (int k = 0; k < C; ++k) dst[(b * C + k) * hw + s] = (float)px[swap ? C - 1 - k : k] / 255.0f;
+  }
+}
+
 __global__ void nhwc_to_nchw_kernel(View src, float* __restrict__ dst) {
   const long long hw = (long long)src.h * src.w;
   const int groups = (src.c + 7) / 8;
@@ -323,6 +336,12 @@ extern "C" int yc_stem_im2col(const float* src, int c, int h, int w, int size, i
   else
     stem_im2col_kernel<0, 0><<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst->ptr, dst->n, c, h, w,
                                                                                     dst->h, dst->w, size, stride, pad);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+extern "C" int yc_u8hwc_to_nchw(const unsigned char* src, int n, int c, int h, int w, int swap_rb, float* dst, void* stream) {
+  YC_REQUIRE(src && dst && n > 0 && c > 0 && h > 0 && w > 0, "yc_u8hwc_to_nchw: bad arguments");
+  u8hwc_to_nchw_kernel<<<grid_for((long long)n * h * w, 256), 256, 0, (cudaStream_t)stream>>>(src, dst, n, c, h, w, swap_rb ? 1 : 0);
   YC_LAUNCH_CHECK();
   return YC_OK;
 }

@@ -233,6 +233,8 @@ int free_device_state(yc_network* net) {
   }
   if (net->input_dev) { cudaFree(net->input_dev); net->input_dev = nullptr; }
   if (net->input_pinned) { cudaFreeHost(net->input_pinned); net->input_pinned = nullptr; }
+  if (net->u8_pinned) { cudaFreeHost(net->u8_pinned); net->u8_pinned = nullptr; }
+  if (net->u8_dev) { cudaFree(net->u8_dev); net->u8_dev = nullptr; }
   if (net->input_nhwc) { cudaFree(net->input_nhwc); net->input_nhwc = nullptr; }
   if (net->det_regions) { cudaFree(net->det_regions); net->det_regions = nullptr; }
   if (net->det_counts) { cudaFree(net->det_counts); net->det_counts = nullptr; }
@@ -410,6 +412,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
     float* w_dev = nullptr;
     NET_CUDA(cudaMalloc(&w_dev, w.size() * 4));
     NET_CUDA(cudaMemcpy(w_dev, w.data(), w.size() * 4, cudaMemcpyHostToDevice));
+    NET_CUDA(h2d_done());
     NET_CUDA(cudaMalloc(&L.w_packed, yc_conv_packed_bytes(L.n, pc, ps)));
     int rc = yc_conv_pack(w_dev, L.n, pc, ps, L.w_packed, net->stream);
     if (rc) { cudaFree(w_dev); return rc; }
@@ -417,9 +420,11 @@ extern "C" int yc_network_finalize(yc_network* net) {
     NET_CUDA(cudaFree(w_dev));
     NET_CUDA(cudaMalloc(&L.bias_dev, L.n * 4));
     NET_CUDA(cudaMemcpy(L.bias_dev, b.data(), L.n * 4, cudaMemcpyHostToDevice));
+    NET_CUDA(h2d_done());
     if (!sc.empty()) {
       NET_CUDA(cudaMalloc(&L.scale_dev, L.n * 4));
       NET_CUDA(cudaMemcpy(L.scale_dev, sc.data(), L.n * 4, cudaMemcpyHostToDevice));
+    NET_CUDA(h2d_done());
     }
   }
 
@@ -499,8 +504,10 @@ extern "C" int yc_network_finalize(yc_network* net) {
         memset(L.dec_host, 0, elems * 4);
         NET_CUDA(cudaMalloc(&L.anchors_dev, L.anchors.size() * 4));
         NET_CUDA(cudaMemcpy(L.anchors_dev, L.anchors.data(), L.anchors.size() * 4, cudaMemcpyHostToDevice));
+    NET_CUDA(h2d_done());
         NET_CUDA(cudaMalloc(&L.mask_dev, L.mask.size() * 4));
         NET_CUDA(cudaMemcpy(L.mask_dev, L.mask.data(), L.mask.size() * 4, cudaMemcpyHostToDevice));
+    NET_CUDA(h2d_done());
         op.kind = 5; op.a = input_view(i); op.i0 = L.n; op.i1 = L.classes; op.f0 = L.scale_x_y;
         op.i2 = L.type == L_GYOLO ? 1 : 0;
         net->ops.push_back(op);
@@ -508,6 +515,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
       }
     }
   }
+  NET_CUDA(cudaDeviceSynchronize());  // memsets / uploads of the set-up ran on the legacy stream: finish them
   net->finalized = true;
   return YC_OK;
 }
@@ -651,6 +659,8 @@ extern "C" int yc_network_forward(yc_network* net, const float* input_dev, void*
   return run_ops(net, st);
 }
 
+static float* predict_tail(yc_network* net);  // forward on net->input_dev + D2H of the heads
+
 extern "C" float* yc_network_predict(yc_network* net, const float* input_host) {
   if (!net || !input_host) {
     set_error("yc_network_predict: null argument");
@@ -665,6 +675,39 @@ extern "C" float* yc_network_predict(yc_network* net, const float* input_host) {
     set_error("yc_network_predict: H2D failed: %s", cudaGetErrorString(cudaGetLastError()));
     return nullptr;
   }
+  return predict_tail(net);
+}
+
+// Mat2Image + NetworkPredict (yolo_core.cpp:110-112, visualize.cpp:26-54) for a batch of u8 HWC images already at the
+// network's resolution: H2D of the BYTES (4x less than fp32), /255 and HWC->NCHW on the device, then the same forward.
+static int ensure_u8(yc_network* net) {
+  const size_t bytes = (size_t)net->batch * net->c * net->h * net->w;
+  if (!net->u8_pinned) NET_CUDA(cudaHostAlloc(&net->u8_pinned, bytes, cudaHostAllocDefault));
+  if (!net->u8_dev) NET_CUDA(cudaMalloc(&net->u8_dev, bytes));
+  return YC_OK;
+}
+extern "C" unsigned char* yc_network_input_buffer_u8(yc_network* net) {
+  if (!net || (!net->finalized && yc_network_finalize(net)) || ensure_u8(net)) return nullptr;
+  return net->u8_pinned;
+}
+extern "C" float* yc_network_predict_u8(yc_network* net, const unsigned char* input_host_hwc, int swap_rb) {
+  if (!net || !input_host_hwc) {
+    set_error("yc_network_predict_u8: null argument");
+    return nullptr;
+  }
+  if (!net->finalized && yc_network_finalize(net)) return nullptr;
+  if (ensure_u8(net)) return nullptr;
+  const size_t bytes = (size_t)net->batch * net->c * net->h * net->w;
+  if (input_host_hwc != net->u8_pinned) memcpy(net->u8_pinned, input_host_hwc, bytes);
+  if (cudaMemcpyAsync(net->u8_dev, net->u8_pinned, bytes, cudaMemcpyHostToDevice, net->stream) != cudaSuccess) {
+    set_error("yc_network_predict_u8: H2D failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return nullptr;
+  }
+  if (yc_u8hwc_to_nchw(net->u8_dev, net->batch, net->c, net->h, net->w, swap_rb, net->input_dev, net->stream)) return nullptr;
+  return predict_tail(net);
+}
+
+static float* predict_tail(yc_network* net) {
   if (yc_network_forward(net, net->input_dev, net->stream)) return nullptr;
   float* last = nullptr;
   if (net->flags & YC_NET_PULL_HEADS) {

@@ -101,6 +101,8 @@ struct yc_network {
   cudaGraphExec_t graph_exec = nullptr;
   float* input_dev = nullptr;   // fp32 NCHW staging (net->input_state_gpu)
   float* input_pinned = nullptr;  // net->input_pinned_cpu
+  unsigned char* u8_pinned = nullptr;  // u8 HWC staging of yc_network_predict_u8 (allocated on first use)
+  unsigned char* u8_dev = nullptr;
   void* input_nhwc = nullptr;   // bf16 NHWC, ldc 8
   const float* graph_input = nullptr;
   std::vector<int> yolo_layers;
@@ -134,6 +136,12 @@ struct yc_network {
 int yc_train_finalize(yc_network* net);
 void yc_train_free(yc_network* net);
 // network_dp.cu: called by the backward pass right after layer i's weight gradient has been enqueued on `compute`
+// cudaMemcpy from PAGEABLE host memory returns once the data sits in the driver's staging buffer; the DMA into device
+// memory may still be in flight on the legacy default stream.  The network's own stream is non-blocking, so a kernel
+// launched there next (weight packing) is NOT ordered after that DMA: it read stale device memory for a random large
+// layer of a freshly loaded network (found in round 1: outputs differed between two instances of the same net).
+inline cudaError_t h2d_done() { return cudaStreamSynchronize(cudaStreamLegacy); }
+
 int yc_dp_layer_ready(yc_network* net, int layer, cudaStream_t compute);
 int yc_dp_backward_done(yc_network* net, cudaStream_t compute);
 int yc_dp_reduce_pending(yc_network* net, cudaStream_t compute);

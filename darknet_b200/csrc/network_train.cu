@@ -70,6 +70,7 @@ int upload(float** p, const std::vector<float>& v) {
   int rc = dev_alloc(p, v.size(), false);
   if (rc) return rc;
   NET_CUDA(cudaMemcpy(*p, v.data(), v.size() * 4, cudaMemcpyHostToDevice));
+    NET_CUDA(h2d_done());
   return YC_OK;
 }
 
@@ -206,8 +207,10 @@ int yc_train_finalize(yc_network* net) {
         memset(L.dec_host, 0, elems * 4);
         NET_CUDA(cudaMalloc(&L.anchors_dev, L.anchors.size() * 4));
         NET_CUDA(cudaMemcpy(L.anchors_dev, L.anchors.data(), L.anchors.size() * 4, cudaMemcpyHostToDevice));
+    NET_CUDA(h2d_done());
         NET_CUDA(cudaMalloc(&L.mask_dev, L.mask.size() * 4));
         NET_CUDA(cudaMemcpy(L.mask_dev, L.mask.data(), L.mask.size() * 4, cudaMemcpyHostToDevice));
+    NET_CUDA(h2d_done());
         int rc = dev_alloc(&L.ydelta, elems);
         if (!rc) rc = dev_alloc(&L.ystats, 8);
         if (rc) return rc;

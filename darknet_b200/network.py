@@ -120,6 +120,29 @@ def FreeNetwork(net: Network):
     net.close()
 
 
+def InputBufferU8(net: Network) -> np.ndarray:
+    """The pinned u8 HWC staging buffer [batch,h,w,c] of NetworkPredictU8 (zero-copy producers write here)."""
+    p = L.lib().yc_network_input_buffer_u8(net.h)
+    if not p:
+        raise L.YcError("yc_network_input_buffer_u8: " + L.lib().yc_last_error().decode())
+    return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_ubyte)), shape=(net.batch, net.hh, net.w, net.c))
+
+
+def NetworkPredictU8(net: Network, img_u8: np.ndarray, swap_rb=False):
+    """ProcImage's Mat2Image + NetworkPredict (yolo_core.cpp:104-112): img_u8 = host u8 HWC [batch,h,w,c] at the network's
+    resolution; swap_rb folds cvtColor(RGB2BGR).  Bit-identical to NetworkPredict(Mat2Image(img))."""
+    if not (img_u8.dtype == np.uint8 and img_u8.flags["C_CONTIGUOUS"]):
+        img_u8 = np.ascontiguousarray(img_u8, np.uint8)
+    assert img_u8.size == net.batch * net.c * net.hh * net.w, "input size != batch*h*w*c"
+    p = L.lib().yc_network_predict_u8(net.h, img_u8.ctypes.data_as(C.c_void_p), 1 if swap_rb else 0)
+    if not p:
+        raise L.YcError("NetworkPredictU8 failed: " + L.lib().yc_last_error().decode())
+    last = net.n - 1
+    if net.layer_info(last, 0) in (5, 6):
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=net.layer_shape(last))
+    return None
+
+
 def NetworkPredict(net: Network, x: np.ndarray):
     """NetworkPredict (network.cpp:412-430): x = host fp32 NCHW [batch,c,h,w]; synchronous.  Returns a numpy
     view of the last layer's host output (layer-owned, valid until the next call)."""

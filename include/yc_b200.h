@@ -84,6 +84,9 @@ YC_API int yc_nchw_to_nhwc(const float* src, const yc_tensor* dst, void* stream)
  * convolution over 32 channels; replaces im2col_ongpu (im2col_kernels.cu) for that layer. */
 YC_API int yc_stem_im2col(const float* src, int c, int h, int w, int size, int stride, int pad, const yc_tensor* dst,
                           void* stream);
+/* Mat2Image on the device (visualize.cpp:26-54): u8 HWC [n][h][w][c] -> fp32 NCHW, value/255.0f; swap_rb reads
+ * channel c-1-k (the cvtColor(RGB2BGR) of yolo_core.cpp:110). */
+YC_API int yc_u8hwc_to_nchw(const unsigned char* src, int n, int c, int h, int w, int swap_rb, float* dst, void* stream);
 /* NHWC view -> fp32 NCHW (what the reference's host code and other layers read). */
 YC_API int yc_nhwc_to_nchw(const yc_tensor* src, float* dst, void* stream);
 
@@ -316,6 +319,11 @@ YC_API double yc_network_flops(const yc_network* net);               /* sum 2*nw
  * [batch*c*h*w] (borrowed), returns the host buffer of the last layer's output (layer-owned, valid until the
  * next call) or NULL on error.  Synchronous like the reference. */
 YC_API float* yc_network_predict(yc_network* net, const float* input_host);
+/* Mat2Image + NetworkPredict for u8 HWC images at the network's resolution (ProcImage, yolo_core.cpp:104-112, minus
+ * cv::resize): the H2D copy carries bytes (4x less than fp32), the /255 and layout change run on the device; results
+ * are bit-identical to yc_network_predict on the Mat2Image output.  yc_network_input_buffer_u8: pinned staging. */
+YC_API float* yc_network_predict_u8(yc_network* net, const unsigned char* input_host_hwc, int swap_rb);
+YC_API unsigned char* yc_network_input_buffer_u8(yc_network* net);
 /* net->input_pinned_cpu (network_kernels.cu:505-513): the library's pinned staging buffer of batch*c*h*w floats.
  * A producer may fill it in place and pass it to yc_network_predict, which then skips its staging memcpy. */
 YC_API float* yc_network_input_buffer(yc_network* net);

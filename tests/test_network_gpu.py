@@ -169,3 +169,25 @@ def test_batch_images_independent(gpu):
             assert np.array_equal(a, b), f"image {j} layer {i} differs between batch 4 and batch 1"
     net4.close()
     net1.close()
+
+
+def test_fresh_instances_are_bit_identical(gpu):
+    """Two freshly loaded instances of the same network must produce bit-identical outputs for every layer, at two batch
+    sizes.  Regression: weight packing used to be launched on the network's non-blocking stream while the pageable
+    host->device copy of the fp32 weights could still be in flight on the legacy stream (a random large layer of a
+    random instance then ran with stale weights)."""
+    from darknet_b200 import cfg as cfgmod, cfgs, lib as L, network as N
+    text = cfgs.CONFIGS["yolov4"](w=320, h=320)
+    weights = cfgmod.synth_weights(text)
+    x = cfgmod.synth_images(4, 3, 320, 320, seed=77)
+    base = None
+    for B in (1, 4, 1):
+        net = N.LoadSynthetic(text, weights, batch=B, flags=L.NET_DEFAULT)
+        N.NetworkPredict(net, x[:B])
+        o = {i: np.array(net.layer_output(i)[0], copy=True) for i in range(net.n) if net.has_output(i)}
+        net.close()
+        if base is None:
+            base = o
+            continue
+        bad = [i for i in sorted(o) if not np.array_equal(o[i], base[i])]
+        assert not bad, f"batch {B}: layers {bad[:5]} differ from the first instance"
