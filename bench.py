@@ -45,6 +45,29 @@ WORKLOADS = {
 }
 
 
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    """Route fd 1 to stderr for the duration of the run (NCCL prints 'NCCL version ...' on stdout when the first
+    communicator comes up); emit() writes the one JSON line to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_REAL_STDOUT, line)
+
+
 def _peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -286,10 +309,11 @@ def _run_train_tail(args, v):
         e2e = {"value": world * B * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(x.nbytes + truth.nbytes),
                "d2h_bytes_per_step": 4 * net.info(7), "ms_per_step": 1e3 * t_e2e / args.steps, "last_cost": cost,
                "api": "yc_network_train_datum(host fp32 NCHW images, host truth) + yc_network_update"}
+        # every rank runs the profile pass (it contains the data-parallel all-reduces); rank 0 reports
+        ms7 = np.zeros(7, np.float32)
+        L.check(L.lib().yc_network_train_profile(net.h, C.c_void_p(xd.data_ptr()), C.c_void_p(td.data_ptr()), 3,
+                                                 ms7.ctypes.data_as(C.c_void_p)), "yc_network_train_profile")
         if rank == 0:
-            ms7 = np.zeros(7, np.float32)
-            L.check(L.lib().yc_network_train_profile(net.h, C.c_void_p(xd.data_ptr()), C.c_void_p(td.data_ptr()), 3,
-                                                     ms7.ctypes.data_as(C.c_void_p)), "yc_network_train_profile")
             peaks = _peaks()
             conv_ms = float(ms7[0] + ms7[1] + ms7[2])
             ach = v["flops_step"] / (conv_ms / 1e3) / 1e12
@@ -319,7 +343,7 @@ def _run_train_tail(args, v):
                           "conv_gflop_per_image_fwd": v["flops_fwd"] / 1e9,
                           "l2_policy": "per-step working set (activations + deltas of 64 images, >2 GB) exceeds the 126 MB L2; no explicit flush"},
                "clocks": v["clocks"], "e2e": e2e, "gpu_launches": v["launches"], "roofline": roof, "cpu_baseline": cpu}
-        print(json.dumps(out))
+        emit(out)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
@@ -363,6 +387,7 @@ def main():
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_train(args) if args.mode == "train" else run_reference(args)
+    _quiet_stdout()
     if args.mode == "train":
         return run_train(args)
 
@@ -528,7 +553,7 @@ def main():
                                        "no explicit flush"},
                "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "kernels_per_step": net.kernels_per_forward(),
                "roofline": roof, "cpu_baseline": cpu}
-        print(json.dumps(out))
+        emit(out)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

@@ -208,7 +208,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
 // thread = (row slot, 8-channel group): the per-channel constants live in registers, the thread walks rows with a
 // stride of gridDim*slots, two rows per iteration so that both 16-byte loads are in flight before the math.
 template <int ACT>
-__global__ void bn_act_fwd_kernel(TView z, const float* __restrict__ mean, const float* __restrict__ var,
+__global__ void __launch_bounds__(256, 3) bn_act_fwd_kernel(TView z, const float* __restrict__ mean, const float* __restrict__ var,
                                   const float* __restrict__ gamma, const float* __restrict__ beta, TView y,
                                   int y_own_pad) {
   constexpr int act = ACT;  // compile-time: with a runtime switch unrolled 32x the kernel was 64 KB of code
@@ -216,15 +216,13 @@ __global__ void bn_act_fwd_kernel(TView z, const float* __restrict__ mean, const
   const int tg = threadIdx.x % groups;  // blockDim.x is a multiple of groups (host)
   const int slots = blockDim.x / groups;
   const int slot = threadIdx.x / groups;
-  float mu[8], is[8], ga[8], be[8];
+  float A[8], Bc[8];  // y = act(A*z + Bc): the SAME expression the backward kernels evaluate, so leaky' sees the same sign
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int c = tg * 8 + j;
     const bool ok = c < z.c;
-    mu[j] = ok ? mean[c] : 0.f;
-    is[j] = ok ? 1.f / sqrtf(var[c] + .000001f) : 0.f;
-    ga[j] = ok ? gamma[c] : 0.f;
-    be[j] = ok ? beta[c] : 0.f;
+    A[j] = ok ? gamma[c] * (1.f / sqrtf(var[c] + .000001f)) : 0.f;
+    Bc[j] = ok ? beta[c] - mean[c] * A[j] : 0.f;
   }
   const long long step = (long long)gridDim.x * slots;
   for (long long row = (long long)blockIdx.x * slots + slot; row < z.rows; row += 4 * step) {
@@ -236,7 +234,7 @@ __global__ void bn_act_fwd_kernel(TView z, const float* __restrict__ mean, const
     for (int k = 0; k < 4; ++k) {
       if (!ok[k]) continue;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) v[k][j] = act_fwd_exact(ga[j] * ((v[k][j] - mu[j]) * is[j]) + be[j], act);
+      for (int j = 0; j < 8; ++j) v[k][j] = act_fwd_exact(fmaf(A[j], v[k][j], Bc[j]), act);
       st8(y, r[k], tg * 8, v[k], y_own_pad != 0);
     }
   }
@@ -247,7 +245,7 @@ __global__ void bn_act_fwd_kernel(TView z, const float* __restrict__ mean, const
 // MODE 1 (bias only):  g = dy * act'(y) evaluated on the layer OUTPUT y (leaky/relu/logistic/linear): S1 only
 // thread = (row slot, 8-channel group); registers -> shared atomics -> global atomics.
 template <int MODE, int ACT>
-__global__ void bwd_reduce_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
+__global__ void __launch_bounds__(256, 3) bwd_reduce_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
                                   const float* __restrict__ gamma, const float* __restrict__ beta,
                                   float* __restrict__ S1, float* __restrict__ S2) {
   constexpr int act = ACT;
@@ -260,16 +258,15 @@ __global__ void bwd_reduce_kernel(TView dy, TView z, const float* __restrict__ m
   const int slots = blockDim.x / groups;
   const int slot = threadIdx.x / groups;
   float a1[8], a2[8];
-  float mu[8], ga[8], be[8], is[8];
+  float mu[8], A[8], Bc[8];  // u = A*x + Bc
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     a1[j] = a2[j] = 0.f;
     const int c = tg * 8 + j;
     const bool ok = c < dy.c;
     mu[j] = (MODE == 0 && ok) ? mean[c] : 0.f;
-    ga[j] = (MODE == 0 && ok) ? gamma[c] : 1.f;
-    be[j] = (ok && beta) ? beta[c] : 0.f;
-    is[j] = (MODE == 0 && ok) ? 1.f / sqrtf(var[c] + .000001f) : 1.f;
+    A[j] = (MODE == 0 && ok) ? gamma[c] * (1.f / sqrtf(var[c] + .000001f)) : 1.f;
+    Bc[j] = ((ok && beta) ? beta[c] : 0.f) - mu[j] * A[j];
   }
   if (slot < slots) {
     const long long step = (long long)gridDim.x * slots;
@@ -282,8 +279,8 @@ __global__ void bwd_reduce_kernel(TView dy, TView z, const float* __restrict__ m
       for (int j = 0; j < 8; ++j) {
         if (MODE == 0) {
           const float xc = x[j] - mu[j], xc2 = x2[j] - mu[j];
-          const float g = d[j] * act_grad(ga[j] * (xc * is[j]) + be[j], act);
-          const float g2 = d2[j] * act_grad(ga[j] * (xc2 * is[j]) + be[j], act);   // d2 = 0 when the row is absent
+          const float g = d[j] * act_grad(fmaf(A[j], x[j], Bc[j]), act);
+          const float g2 = d2[j] * act_grad(fmaf(A[j], x2[j], Bc[j]), act);   // d2 = 0 when the row is absent
           a1[j] += g + g2;
           a2[j] += g * xc + g2 * xc2;
         } else {
@@ -327,7 +324,7 @@ __global__ void bn_bwd_coef_kernel(const float* __restrict__ S1, const float* __
 }
 
 template <int ACT>
-__global__ void bn_bwd_apply_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
+__global__ void __launch_bounds__(256, 3) bn_bwd_apply_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
                                     const float* __restrict__ gamma, const float* __restrict__ beta,
                                     const float* __restrict__ coef, TView dz, int groups) {
   constexpr int act = ACT;
@@ -337,18 +334,18 @@ __global__ void bn_bwd_apply_kernel(TView dy, TView z, const float* __restrict__
   const int slots = blockDim.x / groups;
   const int slot = threadIdx.x / groups;
   const bool live = tg * 8 < n;
-  float mu[8], is[8], ga[8], be[8], c0[8], c1[8], c2[8];
+  // per-channel constants folded to five registers each: u = A*x + Bc (the pre-activation), dz = g*c0 + c1*x + c2'
+  float A[8], Bc[8], c0[8], c1[8], c2[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int c = tg * 8 + j;
     const bool ok = c < n;
-    mu[j] = ok ? mean[c] : 0.f;
-    is[j] = ok ? 1.f / sqrtf(var[c] + .000001f) : 0.f;
-    ga[j] = ok ? gamma[c] : 0.f;
-    be[j] = ok ? beta[c] : 0.f;
+    const float mu = ok ? mean[c] : 0.f;
+    A[j] = ok ? gamma[c] * (1.f / sqrtf(var[c] + .000001f)) : 0.f;
+    Bc[j] = ok ? beta[c] - mu * A[j] : 0.f;
     c0[j] = ok ? coef[c] : 0.f;
     c1[j] = ok ? coef[n + c] : 0.f;
-    c2[j] = ok ? coef[2 * n + c] : 0.f;
+    c2[j] = ok ? coef[2 * n + c] - c1[j] * mu : 0.f;
   }
   const long long step = (long long)gridDim.x * slots;
   for (long long row = (long long)blockIdx.x * slots + slot; row < dy.rows; row += 2 * step) {
@@ -360,11 +357,10 @@ __global__ void bn_bwd_apply_kernel(TView dy, TView z, const float* __restrict__
       ld8_2x2(dy, z, row, row2, two, tg * 8, d, x, d2, x2);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float xc = x[j] - mu[j], xc2 = x2[j] - mu[j];
-        const float gg = d[j] * act_grad(ga[j] * (xc * is[j]) + be[j], act);
-        const float gg2 = d2[j] * act_grad(ga[j] * (xc2 * is[j]) + be[j], act);
-        d[j] = gg * c0[j] + c1[j] * xc + c2[j];      // channels >= n: all coefficients are 0
-        d2[j] = gg2 * c0[j] + c1[j] * xc2 + c2[j];
+        const float gg = d[j] * act_grad(fmaf(A[j], x[j], Bc[j]), act);
+        const float gg2 = d2[j] * act_grad(fmaf(A[j], x2[j], Bc[j]), act);
+        d[j] = fmaf(gg, c0[j], fmaf(c1[j], x[j], c2[j]));      // channels >= n: all coefficients are 0
+        d2[j] = fmaf(gg2, c0[j], fmaf(c1[j], x2[j], c2[j]));
       }
     }
     st8(dz, row, tg * 8, d, true);
@@ -412,7 +408,7 @@ static int row_grid(long long rows, int slots, int per_iter = 2) {
   }
 static int reduce_threads(int groups) {
   int t = (256 / groups) * groups;
-  if (t < groups) t = groups;  // more than 256 groups (c > 2048): one row slot
+  if (t < groups) t = groups;  // more than 256 groups (c > 2048): refused by the callers (launch bounds are 256)
   return t;
 }
 
@@ -442,6 +438,7 @@ extern "C" int yc_bn_act_fwd(const yc_tensor* z, const float* mean, const float*
                              const float* beta, int activation, const yc_tensor* y, void* stream) {
   YC_REQUIRE(ok_view(z) && ok_view(y) && mean && var && gamma && beta, "yc_bn_act_fwd: bad arguments");
   YC_REQUIRE(z->n == y->n && z->h == y->h && z->w == y->w && z->c == y->c, "yc_bn_act_fwd: shape mismatch");
+  YC_REQUIRE(z->c <= 2048, "yc_bn_act_fwd: more than 2048 channels");
   const TView zv = tv(z), yv = tv(y);
   const int own = y->ldc == round_up(y->c, 8);
   const int groups = (z->c + 7) / 8;
@@ -460,6 +457,7 @@ extern "C" int yc_bn_bwd(const yc_tensor* dy, const yc_tensor* z, const float* m
   YC_REQUIRE(dy->n == z->n && dy->h == z->h && dy->w == z->w && dy->c == z->c && dz->n == dy->n && dz->h == dy->h &&
                  dz->w == dy->w && dz->c >= dy->c && dz->dtype == YC_BF16,
              "yc_bn_bwd: shape mismatch");
+  YC_REQUIRE(dz->ldc <= 2048, "yc_bn_bwd: more than 2048 channels");
   cudaStream_t st = (cudaStream_t)stream;
   const int n = dy->c;
   const TView dv = tv(dy), zv = tv(z);
