@@ -8,9 +8,10 @@ A "step" = one forward pass of the hot path over one batch of 64 synthetic 608x6
 (ForwardNetworkGpu: input layout conversion, 110 fused conv kernels, SPP maxpools, upsamples, YOLO decode).
   value : images/s, whole job, inputs already resident in HBM, timed with CUDA events on the launch stream,
           barrier + synchronize on both sides, max over ranks.
-  e2e   : images/s through the public NetworkPredict-style call with HOST buffers: every step copies the
-          batch from pinned host memory (H2D), runs the forward, extracts detections on the device and reads
-          them back (D2H) + host NMS.
+  e2e   : images/s through the public NetworkPredict-style calls with HOST buffers: every step copies one batch
+          from pinned host memory (H2D; yc_network_prefetch starts the copy of the next batch while the current
+          forward runs), runs the forward, extracts detections on the device and reads them back (D2H) + host NMS.
+          e2e.serial = the same without prefetch (copy, then compute); e2e.u8_input = u8 HWC images (4x fewer bytes).
   roofline     : the conv kernel (tensor bound): algorithmic FLOPs (2*nweights*Ho*Wo per layer, the
                  reference's own bflops, convolutional_layer.cpp:714) / summed conv-kernel time measured with
                  CUDA events per launch; peak = MEASURED_PEAKS.json (sustained bf16, since the kernel is
@@ -484,6 +485,31 @@ def main():
                "detections_per_step": int(counts.sum()),
                "api": "yc_network_predict(pinned host fp32 NCHW) + yc_network_detect(thresh .25, nms .45)"}
 
+        # the same step with the input double-buffered: yc_network_prefetch(next batch) right before
+        # yc_network_predict(current batch), so the H2D of the next batch overlaps the forward of this one.  Every step
+        # still moves one full batch host -> device inside the timed region.
+        slots = [N.InputBufferSlot(net, 0), N.InputBufferSlot(net, 1)]
+        slots[1][...] = slots[0]
+        def e2e_pipe_step(k):
+            N.Prefetch(net, slots[(k + 1) % 2])
+            N.NetworkPredict(net, slots[k % 2])
+            return N.DetectBatch(net, 0.25, 0.45)
+        for k in range(2):
+            e2e_pipe_step(k)
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(args.steps):
+            e2e_pipe_step(k)
+        torch.cuda.synchronize()
+        t_pipe = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([t_pipe], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            t_pipe = float(t.item())
+        e2e["prefetch"] = {"value": world * B * args.steps / t_pipe, "unit": UNIT, "h2d_bytes_per_step": int(x_host.nbytes),
+                           "ms_per_step": 1e3 * t_pipe / args.steps,
+                           "api": "yc_network_prefetch(next pinned batch) + yc_network_predict(current) + yc_network_detect"}
+
         # same end-to-end step fed with u8 HWC images (ProcImage's Mat2Image + NetworkPredict): the H2D
         # copy carries bytes instead of floats
         u8 = N.InputBufferU8(net)
@@ -506,6 +532,16 @@ def main():
         e2e["u8_input"] = {"value": world * B * args.steps / t_u8, "unit": UNIT, "h2d_bytes_per_step": int(u8.nbytes),
                            "ms_per_step": 1e3 * t_u8 / args.steps,
                            "api": "yc_network_predict_u8(pinned host u8 HWC) + yc_network_detect"}
+
+        # headline e2e = the double-buffered stream (what a serving loop calls); the strictly serial call sequence and
+        # the u8-input variant are reported beside it
+        serial = {k: e2e[k] for k in ("value", "unit", "ms_per_step", "api")}
+        e2e = {"value": e2e["prefetch"]["value"], "unit": UNIT, "h2d_bytes_per_step": e2e["h2d_bytes_per_step"],
+               "d2h_bytes_per_step": e2e["d2h_bytes_per_step"], "ms_per_step": e2e["prefetch"]["ms_per_step"],
+               "detections_per_step": e2e["detections_per_step"], "api": e2e["prefetch"]["api"],
+               "note": "every step copies one full batch from pinned host memory (H2D, overlapped with the previous step's "
+                       "forward by the copy engine) and reads the detections back (D2H) + host NMS",
+               "serial": serial, "u8_input": e2e["u8_input"]}
 
         # ---- roofline of the dominant kernel (conv_fprop_kernel), rank 0 ---------------------------------
         if rank == 0:

@@ -234,6 +234,12 @@ int free_device_state(yc_network* net) {
   if (net->input_dev) { cudaFree(net->input_dev); net->input_dev = nullptr; }
   if (net->input_pinned) { cudaFreeHost(net->input_pinned); net->input_pinned = nullptr; }
   if (net->u8_pinned) { cudaFreeHost(net->u8_pinned); net->u8_pinned = nullptr; }
+  if (net->copy_stream) { cudaStreamSynchronize(net->copy_stream); cudaStreamDestroy(net->copy_stream); net->copy_stream = nullptr; }
+  if (net->copy_done) { cudaEventDestroy(net->copy_done); net->copy_done = nullptr; }
+  if (net->stage_free) { cudaEventDestroy(net->stage_free); net->stage_free = nullptr; }
+  if (net->input_pinned2) { cudaFreeHost(net->input_pinned2); net->input_pinned2 = nullptr; }
+  if (net->input_dev2) { cudaFree(net->input_dev2); net->input_dev2 = nullptr; }
+  net->staged_host = net->resident_host = nullptr;
   if (net->u8_dev) { cudaFree(net->u8_dev); net->u8_dev = nullptr; }
   if (net->input_nhwc) { cudaFree(net->input_nhwc); net->input_nhwc = nullptr; }
   if (net->det_regions) { cudaFree(net->det_regions); net->det_regions = nullptr; }
@@ -661,6 +667,17 @@ extern "C" int yc_network_forward(yc_network* net, const float* input_dev, void*
 
 static float* predict_tail(yc_network* net);  // forward on net->input_dev + D2H of the heads
 
+// staging buffer -> the graph's input, on the network's stream, once the H2D on the copy stream has landed (~0.1 ms D2D)
+static int consume_staged(yc_network* net) {
+  const size_t in_bytes = (size_t)net->batch * net->c * net->h * net->w * 4;
+  NET_CUDA(cudaStreamWaitEvent(net->stream, net->copy_done, 0));
+  NET_CUDA(cudaMemcpyAsync(net->input_dev, net->input_dev2, in_bytes, cudaMemcpyDeviceToDevice, net->stream));
+  NET_CUDA(cudaEventRecord(net->stage_free, net->stream));
+  net->resident_host = net->staged_host;
+  net->staged_host = nullptr;
+  return YC_OK;
+}
+
 extern "C" float* yc_network_predict(yc_network* net, const float* input_host) {
   if (!net || !input_host) {
     set_error("yc_network_predict: null argument");
@@ -670,12 +687,72 @@ extern "C" float* yc_network_predict(yc_network* net, const float* input_host) {
   const size_t in_bytes = (size_t)net->batch * net->c * net->h * net->w * 4;
   // network_kernels.cu:513-514: memcpy into the pinned staging buffer, then H2D
   // (a caller that produced its batch directly in yc_network_input_buffer() skips the staging copy)
+  if (net->resident_host == input_host) {  // announced two calls ago and already moved into the graph's input
+    net->resident_host = nullptr;
+    return predict_tail(net);
+  }
+  if (net->staged_host == input_host) {  // announced with yc_network_prefetch: its H2D ran on the copy stream
+    if (consume_staged(net)) return nullptr;
+    net->resident_host = nullptr;
+    return predict_tail(net);
+  }
+  net->resident_host = nullptr;
   if (input_host != net->input_pinned) memcpy(net->input_pinned, input_host, in_bytes);
   if (cudaMemcpyAsync(net->input_dev, net->input_pinned, in_bytes, cudaMemcpyHostToDevice, net->stream) != cudaSuccess) {
     set_error("yc_network_predict: H2D failed: %s", cudaGetErrorString(cudaGetLastError()));
     return nullptr;
   }
   return predict_tail(net);
+}
+
+// Input double buffering for a stream of batches: call yc_network_prefetch(next) right BEFORE yc_network_predict(current).
+// The H2D copy of `next` runs on a separate stream (copy engine) into a device staging buffer while the forward of
+// `current` computes; a later yc_network_predict(net, next) finds it on the device.  input_host should be yc_network_input_buffer_slot(net, 0|1)
+// (pinned); any other pointer is first copied into slot 1.
+static int ensure_prefetch(yc_network* net) {
+  const size_t in_bytes = (size_t)net->batch * net->c * net->h * net->w * 4;
+  if (!net->input_pinned2) NET_CUDA(cudaHostAlloc(&net->input_pinned2, in_bytes, cudaHostAllocDefault));
+  if (!net->input_dev2) NET_CUDA(cudaMalloc(&net->input_dev2, in_bytes));
+  if (!net->copy_stream) NET_CUDA(cudaStreamCreateWithFlags(&net->copy_stream, cudaStreamNonBlocking));
+  if (!net->copy_done) NET_CUDA(cudaEventCreateWithFlags(&net->copy_done, cudaEventDisableTiming));
+  if (!net->stage_free) {
+    NET_CUDA(cudaEventCreateWithFlags(&net->stage_free, cudaEventDisableTiming));
+    NET_CUDA(cudaEventRecord(net->stage_free, net->stream));
+  }
+  return YC_OK;
+}
+extern "C" float* yc_network_input_buffer_slot(yc_network* net, int slot) {
+  if (!net || slot < 0 || slot > 1) return nullptr;
+  if (!net->finalized && yc_network_finalize(net)) return nullptr;
+  if (slot == 0) return net->input_pinned;
+  if (ensure_prefetch(net)) return nullptr;
+  return net->input_pinned2;
+}
+extern "C" int yc_network_prefetch(yc_network* net, const float* input_host) {
+  YC_REQUIRE(net && input_host, "yc_network_prefetch: null argument");
+  if (!net->finalized) {
+    int rc = yc_network_finalize(net);
+    if (rc) return rc;
+  }
+  int rc = ensure_prefetch(net);
+  if (rc) return rc;
+  const size_t in_bytes = (size_t)net->batch * net->c * net->h * net->w * 4;
+  const float* src = input_host;
+  if (input_host != net->input_pinned && input_host != net->input_pinned2) {
+    memcpy(net->input_pinned2, input_host, in_bytes);
+    src = net->input_pinned2;
+  }
+  // a batch staged earlier and not consumed yet moves into the graph's input first (the previous forward has finished:
+  // yc_network_predict is synchronous), so that the staging buffer is free for this copy
+  if (net->staged_host) {
+    rc = consume_staged(net);
+    if (rc) return rc;
+  }
+  NET_CUDA(cudaStreamWaitEvent(net->copy_stream, net->stage_free, 0));
+  NET_CUDA(cudaMemcpyAsync(net->input_dev2, src, in_bytes, cudaMemcpyHostToDevice, net->copy_stream));
+  NET_CUDA(cudaEventRecord(net->copy_done, net->copy_stream));
+  net->staged_host = input_host;
+  return YC_OK;
 }
 
 // Mat2Image + NetworkPredict (yolo_core.cpp:110-112, visualize.cpp:26-54) for a batch of u8 HWC images already at the

@@ -101,6 +101,13 @@ struct yc_network {
   cudaGraphExec_t graph_exec = nullptr;
   float* input_dev = nullptr;   // fp32 NCHW staging (net->input_state_gpu)
   float* input_pinned = nullptr;  // net->input_pinned_cpu
+  // input prefetch (yc_network_prefetch): second pinned slot, device staging buffer, copy stream
+  float* input_pinned2 = nullptr;
+  float* input_dev2 = nullptr;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t copy_done = nullptr, stage_free = nullptr;
+  const float* staged_host = nullptr;    // batch whose H2D into input_dev2 has been started
+  const float* resident_host = nullptr;  // batch already moved into input_dev, not yet consumed by a forward
   unsigned char* u8_pinned = nullptr;  // u8 HWC staging of yc_network_predict_u8 (allocated on first use)
   unsigned char* u8_dev = nullptr;
   void* input_nhwc = nullptr;   // bf16 NHWC, ldc 8

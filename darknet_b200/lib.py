@@ -128,6 +128,8 @@ _SIGS = {
     "yc_network_flops": (C.c_double, [_P]),
     "yc_network_predict": (_P, [_P, _P]),
     "yc_network_predict_u8": (_P, [_P, _P, C.c_int]),
+    "yc_network_prefetch": (C.c_int, [_P, _P]),
+    "yc_network_input_buffer_slot": (_P, [_P, C.c_int]),
     "yc_network_input_buffer_u8": (_P, [_P]),
     "yc_u8hwc_to_nchw": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "yc_network_input_buffer": (_P, [_P]),

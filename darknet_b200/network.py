@@ -120,6 +120,20 @@ def FreeNetwork(net: Network):
     net.close()
 
 
+def InputBufferSlot(net: Network, slot: int) -> np.ndarray:
+    """One of the two pinned fp32 NCHW staging buffers (slot 0 == InputBuffer) to alternate between when prefetching."""
+    p = L.lib().yc_network_input_buffer_slot(net.h, slot)
+    if not p:
+        raise L.YcError("yc_network_input_buffer_slot: " + L.lib().yc_last_error().decode())
+    return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=(net.batch, net.c, net.hh, net.w))
+
+
+def Prefetch(net: Network, x_next: np.ndarray):
+    """Start the H2D copy of the NEXT batch while the current one computes; NetworkPredict(net, x_next) picks it up."""
+    assert x_next.dtype == np.float32 and x_next.flags["C_CONTIGUOUS"]
+    L.check(L.lib().yc_network_prefetch(net.h, x_next.ctypes.data_as(C.c_void_p)), "yc_network_prefetch")
+
+
 def InputBufferU8(net: Network) -> np.ndarray:
     """The pinned u8 HWC staging buffer [batch,h,w,c] of NetworkPredictU8 (zero-copy producers write here)."""
     p = L.lib().yc_network_input_buffer_u8(net.h)

@@ -324,6 +324,13 @@ YC_API float* yc_network_predict(yc_network* net, const float* input_host);
  * are bit-identical to yc_network_predict on the Mat2Image output.  yc_network_input_buffer_u8: pinned staging. */
 YC_API float* yc_network_predict_u8(yc_network* net, const unsigned char* input_host_hwc, int swap_rb);
 YC_API unsigned char* yc_network_input_buffer_u8(yc_network* net);
+/* Input double buffering for a stream of batches (the reference's NetworkPredictGpu copies and computes serially,
+ * network_kernels.cu:502-522): yc_network_prefetch(next) starts the H2D copy of the NEXT batch on a separate stream
+ * while the current forward runs; the later yc_network_predict(net, next) (same pointer) skips its own H2D.
+ * yc_network_input_buffer_slot(net, 0|1): two pinned staging buffers to alternate between (slot 0 ==
+ * yc_network_input_buffer). */
+YC_API int yc_network_prefetch(yc_network* net, const float* input_host);
+YC_API float* yc_network_input_buffer_slot(yc_network* net, int slot);
 /* net->input_pinned_cpu (network_kernels.cu:505-513): the library's pinned staging buffer of batch*c*h*w floats.
  * A producer may fill it in place and pass it to yc_network_predict, which then skips its staging memcpy. */
 YC_API float* yc_network_input_buffer(yc_network* net);

@@ -36,3 +36,29 @@ def test_predict_u8_matches_mat2image(gpu, swap):
     again = np.array(N.NetworkPredictU8(net, buf, swap_rb=swap), copy=True)
     assert np.array_equal(again, got_last)
     net.close()
+
+
+def test_prefetch_gives_identical_results(gpu):
+    """yc_network_prefetch: a stream of batches fed through the double-buffered input gives the same outputs as plain
+    NetworkPredict calls, in order, including when a prefetched batch differs from the one before."""
+    from darknet_b200 import cfg as cfgmod, lib as L, network as N
+    B = 2
+    text, cpath, wpath = netutil.materialise("micro", batch=1)
+    net = N.LoadNetwork(cpath, wpath, batch=B, flags=L.NET_DEFAULT)
+    batches = [cfgmod.synth_images(B, 3, net.hh, net.w, seed=100 + k) for k in range(4)]
+    want = [np.array(N.NetworkPredict(net, b), copy=True) for b in batches]
+    slots = [N.InputBufferSlot(net, 0), N.InputBufferSlot(net, 1)]
+    slots[0][...] = batches[0]
+    for k in range(4):
+        if k + 1 < 4:                                  # announce the next batch, then compute the current one
+            slots[(k + 1) % 2][...] = batches[k + 1]
+            N.Prefetch(net, slots[(k + 1) % 2])
+        got = np.array(N.NetworkPredict(net, slots[k % 2]), copy=True)
+        assert np.array_equal(got, want[k]), f"batch {k}"
+    # a prefetched batch that is never asked for must not leak into a later call
+    N.Prefetch(net, slots[1])
+    got = np.array(N.NetworkPredict(net, batches[0]), copy=True)
+    assert np.array_equal(got, want[0])
+    got = np.array(N.NetworkPredict(net, batches[2]), copy=True)
+    assert np.array_equal(got, want[2])
+    net.close()
