@@ -291,8 +291,10 @@ def _run_train_tail(args, v):
     x, truth, xd, td = v["x"], v["truth"], v["xd"], v["td"]
     e2e = roof = cpu = None
     if not args.quick_exit_after_timed:
+        x_pin = N.InputBuffer(net)                   # pinned staging buffer (net->input_pinned_cpu): no pageable copy
+        x_pin[...] = x
         def e2e_step():
-            c = N.TrainNetworkDatum(net, x, truth)   # host fp32 NCHW + truth -> H2D -> forward/backward -> cost D2H
+            c = N.TrainNetworkDatum(net, x_pin, truth)   # pinned host fp32 NCHW + truth -> H2D -> forward/backward -> cost D2H
             N.UpdateNetwork(net)
             return c
         for _ in range(2):
