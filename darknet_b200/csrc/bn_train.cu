@@ -288,10 +288,24 @@ __global__ void __launch_bounds__(256, 3) bwd_reduce_kernel(TView dy, TView z, c
         }
       }
     }
+    // lanes l and l + groups of a warp own the same channels when groups divides 32: fold them with shuffles first,
+    // so that `groups` lanes per warp (not 32) issue the shared-memory atomics (32-way same-address conflicts before)
+    const bool fold = groups < 32 && (32 % groups) == 0 && (blockDim.x & 31) == 0;
+    if (fold) {
+      for (int off = 16; off >= groups; off >>= 1) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(&sh[tg * 8 + j], a1[j]);
-      if (MODE == 0) atomicAdd(&sh[C8 + tg * 8 + j], a2[j]);
+        for (int j = 0; j < 8; ++j) {
+          a1[j] += __shfl_xor_sync(0xffffffffu, a1[j], off);
+          if (MODE == 0) a2[j] += __shfl_xor_sync(0xffffffffu, a2[j], off);
+        }
+      }
+    }
+    if (!fold || (threadIdx.x & 31) < groups) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        atomicAdd(&sh[tg * 8 + j], a1[j]);
+        if (MODE == 0) atomicAdd(&sh[C8 + tg * 8 + j], a2[j]);
+      }
     }
   }
   __syncthreads();
