@@ -33,7 +33,8 @@ struct ConvParams {
   int M, N, n_store;
   int taps, ksize, cchunks, block_k, block_n, stages;
   int m_tiles, n_tiles;
-  int a_mode;  // 0: 2-D tiled map (1x1 s1 p0), 1: im2col map
+  int a_mode;  // 0: 2-D tiled map (1x1 s1 p0), 1: im2col map, 2: halo patch (3x3 s1 p1, see kHalo*)
+  int tiles_h, tiles_w;  // a_mode 2: output tiles of kHaloH x kHaloW pixels per image
   int Ho, Wo, stride, pad, dil;
   const float* bias;   // padded to n_tiles*block_n
   const float* scale;  // same padding, or nullptr
@@ -52,6 +53,16 @@ struct ConvParams {
   int stat_cols;       // n_tiles * block_n: floats per statistic in the CTA's shared-memory accumulator
 };
 
+// ---- halo mode (a_mode 2): 3x3 stride-1 pad-1 convolutions whose A operand is staged ONCE per (tile, 64-channel chunk)
+// as a (kHaloH+2) x kHaloPitch pixel patch (one tiled TMA box, border zero-filled by the engine) instead of nine im2col
+// tap loads.  M tile = kHaloH x kHaloW output pixels, row r = h*8 + w; the tap (kh, kw) operand is the same patch
+// read through a descriptor shifted by (kh*kHaloPitch + kw) rows of 128 B: 8-row groups (8 consecutive pixels of one
+// patch row) are kHaloPitch*128 = 2048 B apart (SBO).  Measured on B200 (tools/halo_debug.py): the tensor core applies
+// the 128B-swizzle XOR to the ABSOLUTE shared-memory address of each row, like TMA did when writing the patch, so a
+// start address shifted by whole rows needs NO base-offset in the descriptor (setting it to (addr>>7)&7 breaks kw != 0).
+constexpr int kHaloH = 16, kHaloW = 8, kHaloPitch = 16;
+constexpr int kHaloPatchBytes = (kHaloH + 2) * kHaloPitch * 128;  // 36864: 64 channels x bf16 per pixel
+constexpr int kHaloStages = 2;
 constexpr int kStageOutBytes = 2048;  // one epilogue staging buffer: 32 rows x 64 B
 constexpr int kEpiWarps = 16;         // four per TMEM lane quadrant == four per scheduler: enough to hide ALU/MUFU latency
 constexpr int kMaxAcc = 4;            // TMEM accumulator buffers
@@ -95,9 +106,21 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
     const uint32_t acc_phase = (it / p.nacc) & 1;
     const int m0 = (t / p.n_tiles) * kBlockM;
     const int n0 = (t % p.n_tiles) * p.block_n;
-    const int row0 = m0 + quad * 32;
-    const long long row = (long long)row0 + lane;
-    const bool row_ok = row < p.M;
+    int row0 = m0 + quad * 32;
+    long long row = (long long)row0 + lane;
+    bool row_ok = row < p.M;
+    int hb = 0, hw0 = 0, hh0 = 0;  // halo mode: image, first column / row of this warp's 4 x 8 pixel block
+    if (p.a_mode == 2) {
+      const int mt = t / p.n_tiles;
+      hb = mt / (p.tiles_h * p.tiles_w);
+      const int rem = mt - hb * (p.tiles_h * p.tiles_w);
+      hh0 = (rem / p.tiles_w) * kHaloH + quad * 4;
+      hw0 = (rem % p.tiles_w) * kHaloW;
+      const int h = hh0 + (lane >> 3), w = hw0 + (lane & 7);
+      row_ok = h < p.Ho && w < p.Wo;
+      row = ((long long)hb * p.Ho + h) * p.Wo + w;
+      row0 = hh0 < p.Ho ? 0 : p.M;  // only used as "this block has something to store"
+    }
     const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * p.block_n;
     int n_groups = (min(p.block_n, p.n_store - n0) + 31) >> 5;  // 32-column groups with something to store
     // this warp's groups: sub, sub+wps, ...
@@ -197,7 +220,8 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
         ptx::fence_proxy_async();  // generic-proxy smem writes -> visible to the TMA engine
         __syncwarp();
         if (lane == 0 && row0 < p.M) {
-          ptx::tma_store_2d(tmap_y, sbuf, col0, row0);
+          if (p.a_mode == 2) ptx::tma_store_4d(tmap_y, sbuf, col0, hw0, hh0, hb);
+          else ptx::tma_store_2d(tmap_y, sbuf, col0, row0);
           ptx::tma_store_commit();
         }
       } else {
@@ -214,7 +238,8 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
           ptx::fence_proxy_async();
           __syncwarp();
           if (lane == 0 && row0 < p.M && col0 + hh * 16 < p.n_store) {
-            ptx::tma_store_2d(tmap_y, sbuf, col0 + hh * 16, row0);
+            if (p.a_mode == 2) ptx::tma_store_4d(tmap_y, sbuf, col0 + hh * 16, hw0, hh0, hb);
+            else ptx::tma_store_2d(tmap_y, sbuf, col0 + hh * 16, row0);
             ptx::tma_store_commit();
           }
         }
@@ -231,11 +256,13 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment: required by the 128B swizzle atom (8 rows x 128 B)
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t a_bytes = kBlockM * p.block_k * 2;
+  const bool halo = p.a_mode == 2;
+  const uint32_t a_bytes = halo ? 0u : kBlockM * p.block_k * 2;           // halo: the ring holds weight slabs only
   const uint32_t b_bytes = ((uint32_t)(p.block_n * p.block_k * 2) + 1023u) & ~1023u;
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t tx_bytes = a_bytes + (uint32_t)(p.block_n * p.block_k * 2);
-  const uint32_t out_base = smem_base + p.stages * stage_bytes;           // 1024-aligned
+  const uint32_t patch_base = smem_base + p.stages * stage_bytes;         // 1024-aligned; halo: kHaloStages patches
+  const uint32_t out_base = patch_base + (halo ? kHaloStages * kHaloPatchBytes : 0);  // 1024-aligned
   const uint32_t bar_base = out_base + kEpiWarps * kStageOutBytes;        // 8-byte aligned
   // barrier map: full[s] @ +8s, empty[s] @ +8(kMaxStages+s), tmem_full[4], tmem_empty[4], tmem ptr
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
@@ -243,6 +270,8 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + kMaxAcc + a); };
   const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc);
+  auto pfull_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc + 1 + s); };
+  auto pempty_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc + 1 + kHaloStages + s); };
   const uint32_t stat_smem = bar_base + 512u;  // 2 x stat_cols floats, only when statistics are requested
   if (STATS) {
     for (int i = threadIdx.x; i < 2 * p.stat_cols; i += blockDim.x)
@@ -259,6 +288,10 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     for (int s = 0; s < p.stages; ++s) {
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), 1);
+    }
+    for (int s2 = 0; s2 < kHaloStages; ++s2) {
+      ptx::mbar_init(pfull_bar(s2), 1);
+      ptx::mbar_init(pempty_bar(s2), 1);
     }
     for (int a = 0; a < kMaxAcc; ++a) {
       ptx::mbar_init(tfull_bar(a), 1);
@@ -279,7 +312,66 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   const int total_tiles = p.m_tiles * p.n_tiles;
   const int k_blocks = p.taps * p.cchunks;
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 0 && lane == 0 && halo) {
+    // ===================== TMA producer, halo mode =====================
+    // per (tile, 64-channel chunk): one patch box {64 ch, kHaloPitch, kHaloH+2, 1} starting one pixel up-left of the
+    // tile (negative / past-the-end coordinates are zero-filled = the convolution's padding), then nine weight slabs
+    int stage = 0, ps = 0;
+    uint32_t phase = 0, pphase = 0;
+    const int tpi = p.tiles_h * p.tiles_w;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      const int mt = t / p.n_tiles;
+      const int n0 = (t % p.n_tiles) * p.block_n;
+      const int img = mt / tpi;
+      const int rem = mt - img * tpi;
+      const int h0 = (rem / p.tiles_w) * kHaloH, w0 = (rem % p.tiles_w) * kHaloW;
+      for (int cc = 0; cc < p.cchunks; ++cc) {
+        ptx::mbar_wait(pempty_bar(ps), pphase ^ 1u);
+        ptx::mbar_arrive_expect_tx(pfull_bar(ps), kHaloPatchBytes);
+        ptx::tma_load_4d(patch_base + ps * kHaloPatchBytes, &tmap_a, pfull_bar(ps), cc * 64, w0 - 1, h0 - 1, img);
+        if (++ps == kHaloStages) { ps = 0; pphase ^= 1u; }
+        for (int tap = 0; tap < 9; ++tap) {
+          ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
+          ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
+          ptx::tma_load_2d(smem_base + stage * stage_bytes, &tmap_b, full_bar(stage), (tap * p.cchunks + cc) * 64, n0);
+          if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0 && halo) {
+    // ===================== MMA issuer, halo mode =====================
+    const uint32_t idesc = ptx::make_idesc_bf16(kBlockM, p.block_n);
+    int stage = 0, ps = 0;
+    uint32_t phase = 0, pphase = 0;
+    int it = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      const int acc = it % p.nacc;
+      const uint32_t acc_phase = (it / p.nacc) & 1;
+      ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+      ptx::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * p.block_n;
+      for (int cc = 0; cc < p.cchunks; ++cc) {
+        ptx::mbar_wait(pfull_bar(ps), pphase);
+        ptx::tc_fence_after();
+        const uint32_t pa = patch_base + ps * kHaloPatchBytes;
+        for (int tap = 0; tap < 9; ++tap) {
+          const int kh = tap / 3, kw = tap - kh * 3;
+          ptx::mbar_wait(full_bar(stage), phase);
+          ptx::tc_fence_after();
+          const uint64_t adesc = ptx::make_smem_desc_sw128_shifted(pa + (uint32_t)(kh * kHaloPitch + kw) * 128u, kHaloPitch * 128u);
+          const uint64_t bdesc = ptx::make_smem_desc(smem_base + stage * stage_bytes, 128u);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            ptx::mma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (cc | tap | k) != 0);
+          ptx::mma_commit(empty_bar(stage));
+          if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+        }
+        ptx::mma_commit(pempty_bar(ps));  // the patch is free once the nine taps' MMAs have retired
+        if (cc == p.cchunks - 1) ptx::mma_commit(tfull_bar(acc));
+        if (++ps == kHaloStages) { ps = 0; pphase ^= 1u; }
+      }
+    }
+  } else if (warp == 0 && lane == 0) {
     // ===================== TMA producer =====================
     int stage = 0;
     uint32_t phase = 0;
@@ -541,6 +633,24 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
   p.a_mode = (d->ksize == 1 && d->stride == 1 && d->pad == 0) ? 0 : 1;
   p.Ho = Ho; p.Wo = Wo; p.stride = d->stride; p.pad = d->pad; p.dil = d->dilation;
   p.m_tiles = ceil_div(p.M, kBlockM);
+  p.tiles_h = p.tiles_w = 0;
+  {
+    // halo mode: 3x3 / stride 1 / pad 1 with whole 64-channel chunks.  It pays where the nine im2col tap loads bound the
+    // layer (few output channels per fetched row) and the 16x8 tiling wastes little: YC_CONV_HALO=0 never, 1 always
+    // (when legal), unset: cost rule.
+    const char* env = getenv("YC_CONV_HALO");
+    const int mode = env ? atoi(env) : -1;
+    const bool legal = d->ksize == 3 && d->stride == 1 && d->pad == 1 && d->dilation == 1 && x->c % 64 == 0;
+    const int th = ceil_div(Ho, kHaloH), tw = ceil_div(Wo, kHaloW);
+    const double waste = (double)x->n * th * tw * kBlockM / (double)p.M;
+    const bool want = mode == 1 || (mode < 0 && N <= 128 && waste <= 1.15);
+    if (legal && want && mode != 0) {
+      p.a_mode = 2;
+      p.tiles_h = th;
+      p.tiles_w = tw;
+      p.m_tiles = x->n * th * tw;
+    }
+  }
 
   // ---- tile width: minimise (waves x per-tile cost); per-tile cost ~ block_n + fixed overhead -----
   const int sms = sm_count();
@@ -558,10 +668,10 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
   }
   p.block_n = best_bn;
   p.n_tiles = ceil_div(N, p.block_n);
-  const uint32_t a_bytes = kBlockM * p.block_k * 2;
+  const uint32_t a_bytes = p.a_mode == 2 ? 0u : kBlockM * p.block_k * 2;
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
   const uint32_t stage_bytes = a_bytes + b_bytes;
-  const uint32_t out_stage = kEpiWarps * kStageOutBytes;
+  const uint32_t out_stage = kEpiWarps * kStageOutBytes + (p.a_mode == 2 ? kHaloStages * kHaloPatchBytes : 0);
   const uint32_t smem_budget = 227 * 1024 - 1024 /*align slack*/ - 512 /*barriers*/ - out_stage;
   // as deep as shared memory allows: the producer runs ahead across tiles, so the ring depth is the amount of
   // HBM traffic in flight per SM (what the memory-bound 1x1 layers live on)
@@ -606,7 +716,16 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
   // ---- tensor maps ---------------------------------------------------------------------------------
   const CUtensorMapSwizzle swz = swizzle_for(p.block_k);
   CUresult cr;
-  if (p.a_mode == 0) {
+  if (p.a_mode == 2) {
+    // the (kHaloH+2) x kHaloPitch pixel patch around a tile: plain tiled box over {c, w, h, n}, zero fill outside
+    cuuint64_t dims[4] = {(cuuint64_t)x->c, (cuuint64_t)x->w, (cuuint64_t)x->h, (cuuint64_t)x->n};
+    cuuint64_t strides[3] = {(cuuint64_t)x->ldc * 2, (cuuint64_t)x->ldc * 2 * x->w, (cuuint64_t)x->ldc * 2 * x->w * x->h};
+    cuuint32_t box[4] = {64, (cuuint32_t)kHaloPitch, (cuuint32_t)(kHaloH + 2), 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    cr = g_encode_tiled(&pl->tmap_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, x->ptr, dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  } else if (p.a_mode == 0) {
     cuuint64_t dims[2] = {(cuuint64_t)x->c, (cuuint64_t)p.M};
     cuuint64_t strides[1] = {(cuuint64_t)x->ldc * 2};
     cuuint32_t box[2] = {(cuuint32_t)p.block_k, (cuuint32_t)kBlockM};
@@ -651,14 +770,25 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
     // output map: [M rows][n_store columns] with the view's pixel pitch; box = 32 rows x chunk columns, swizzled
     // like the staging tile the epilogue writes.  Rows >= M and columns >= n_store are clipped by the TMA engine.
     const int elt_b = p.y_f32 ? 4 : 2;
+    const CUtensorMapSwizzle oswz = CU_TENSOR_MAP_SWIZZLE_64B;
+    const CUtensorMapDataType odt = p.y_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    if (p.a_mode == 2) {
+      // halo mode: a warp's 32 rows are a 4 x 8 pixel block of the image -> box {chunk, 8, 4, 1} over {c, w, h, n};
+      // the staging tile has the same row order (w fastest), clipping at the right / bottom edge is the engine's job
+      cuuint64_t dims[4] = {(cuuint64_t)p.n_store, (cuuint64_t)Wo, (cuuint64_t)Ho, (cuuint64_t)x->n};
+      cuuint64_t strides[3] = {(cuuint64_t)y->ldc * elt_b, (cuuint64_t)y->ldc * elt_b * Wo, (cuuint64_t)y->ldc * elt_b * Wo * Ho};
+      cuuint32_t box[4] = {(cuuint32_t)p.chunk, (cuuint32_t)kHaloW, 4, 1};
+      cuuint32_t estr[4] = {1, 1, 1, 1};
+      cr = g_encode_tiled(&pl->tmap_y, odt, 4, y->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, oswz,
+                          CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    } else {
     cuuint64_t dims[2] = {(cuuint64_t)p.n_store, (cuuint64_t)p.M};
     cuuint64_t strides[1] = {(cuuint64_t)y->ldc * elt_b};
     cuuint32_t box[2] = {(cuuint32_t)p.chunk, 32};
     cuuint32_t estr[2] = {1, 1};
-    const CUtensorMapSwizzle oswz = CU_TENSOR_MAP_SWIZZLE_64B;
-    cr = g_encode_tiled(&pl->tmap_y, p.y_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
-                        y->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, oswz,
+    cr = g_encode_tiled(&pl->tmap_y, odt, 2, y->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, oswz,
                         CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
     if (cr != CUDA_SUCCESS) {
       set_error("yc_conv_plan_create: output tensor map encode failed (CUresult %d, c=%d ldc=%d)", (int)cr, p.n_store, y->ldc);
       yc_conv_plan_destroy(pl);
@@ -742,10 +872,10 @@ extern "C" int yc_conv_dgrad_plan_create(yc_conv_plan** plan, const yc_conv_desc
 extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq) {
   YC_REQUIRE(pl && ((sum && sumsq) || (!sum && !sumsq)), "yc_conv_plan_set_stats: bad arguments");
   ConvParams& p = pl->p;
-  const uint32_t a_bytes = kBlockM * p.block_k * 2;
+  const uint32_t a_bytes = p.a_mode == 2 ? 0u : kBlockM * p.block_k * 2;
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
   const uint32_t stage_bytes = a_bytes + b_bytes;
-  const uint32_t out_stage = kEpiWarps * kStageOutBytes;
+  const uint32_t out_stage = kEpiWarps * kStageOutBytes + (p.a_mode == 2 ? kHaloStages * kHaloPatchBytes : 0);
   p.stat_cols = sum ? p.n_tiles * p.block_n : 0;
   const uint32_t stat_bytes = 2u * 4u * (uint32_t)p.stat_cols;
   const uint32_t smem_budget = 227 * 1024 - 1024 - 512 - out_stage - stat_bytes;

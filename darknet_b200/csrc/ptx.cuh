@@ -84,6 +84,20 @@ __device__ __forceinline__ void tma_load_im2col_4d(uint32_t dst, const void* tma
       : "memory");
 }
 
+// tiled-mode load of a rank-4 NHWC box {c, w, h, n}; coordinates may be negative / past the end: those elements
+// are zero-filled (the halo of a 3x3 convolution)
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const void* tmap, uint32_t bar, int c, int w, int h, int n) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c), "r"(w), "r"(h), "r"(n)
+      : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const void* tmap, uint32_t src, int c, int w, int h, int n) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(src), "r"(c), "r"(w), "r"(h), "r"(n)
+               : "memory");
+}
+
 // smem (swizzled tile) -> global through a tiled tensor map; bulk-group completion.
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
@@ -172,6 +186,18 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t row_
   d |= (uint64_t)((8u * row_bytes) >> 4) << 32;    // SBO: pitch between 8-row core-matrix groups
   d |= (uint64_t)1 << 46;                          // descriptor version (Blackwell)
   d |= (uint64_t)layout << 61;
+  return d;
+}
+// K-major 128B-swizzled operand whose 8-row groups are `sbo_bytes` apart and whose start address may be shifted by
+// whole 128-byte rows inside a 1024-byte-aligned tile written by TMA.  The base-offset field stays 0: the hardware
+// swizzles on absolute shared-memory address bits (verified on B200), which is already consistent with TMA's pattern.
+__device__ __forceinline__ uint64_t make_smem_desc_sw128_shifted(uint32_t saddr, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(sbo_bytes >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
   return d;
 }
 // Instruction descriptor for kind::f16 with bf16 A/B (K-major both), fp32 accumulate, M x N tile.
