@@ -35,6 +35,7 @@ struct ConvParams {
   int m_tiles, n_tiles;
   int a_mode;  // 0: 2-D tiled map (1x1 s1 p0), 1: im2col map, 2: halo patch (3x3 s1 p1, see kHalo*)
   int tiles_h, tiles_w;  // a_mode 2: output tiles of kHaloH x kHaloW pixels per image
+  int w_resident;        // a_mode 2: all 9*cchunks weight slabs stay in shared memory for the whole (persistent) CTA
   int Ho, Wo, stride, pad, dil;
   const float* bias;   // padded to n_tiles*block_n
   const float* scale;  // same padding, or nullptr
@@ -330,6 +331,16 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         ptx::mbar_arrive_expect_tx(pfull_bar(ps), kHaloPatchBytes);
         ptx::tma_load_4d(patch_base + ps * kHaloPatchBytes, &tmap_a, pfull_bar(ps), cc * 64, w0 - 1, h0 - 1, img);
         if (++ps == kHaloStages) { ps = 0; pphase ^= 1u; }
+        if (p.w_resident) {
+          // weights stationary: slab (tap, cc) lives in ring slot tap*cchunks + cc, loaded with this CTA's first tile
+          if (t == (int)blockIdx.x)
+            for (int tap = 0; tap < 9; ++tap) {
+              const int slot = tap * p.cchunks + cc;
+              ptx::mbar_arrive_expect_tx(full_bar(slot), tx_bytes);
+              ptx::tma_load_2d(smem_base + slot * stage_bytes, &tmap_b, full_bar(slot), slot * 64, n0);
+            }
+          continue;
+        }
         for (int tap = 0; tap < 9; ++tap) {
           ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
           ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
@@ -356,6 +367,10 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const uint32_t pa = patch_base + ps * kHaloPatchBytes;
         for (int tap = 0; tap < 9; ++tap) {
           const int kh = tap / 3, kw = tap - kh * 3;
+          if (p.w_resident) {  // slot of this slab; its barrier completed phase 0 once and is never re-armed
+            stage = tap * p.cchunks + cc;
+            phase = 0;
+          }
           ptx::mbar_wait(full_bar(stage), phase);
           ptx::tc_fence_after();
           const uint64_t adesc = ptx::make_smem_desc_sw128_shifted(pa + (uint32_t)(kh * kHaloPitch + kw) * 128u, kHaloPitch * 128u);
@@ -363,8 +378,10 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
           for (int k = 0; k < 4; ++k)
             ptx::mma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (cc | tap | k) != 0);
-          ptx::mma_commit(empty_bar(stage));
-          if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+          if (!p.w_resident) {
+            ptx::mma_commit(empty_bar(stage));
+            if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+          }
         }
         ptx::mma_commit(pempty_bar(ps));  // the patch is free once the nine taps' MMAs have retired
         if (cc == p.cchunks - 1) ptx::mma_commit(tfull_bar(acc));
@@ -643,7 +660,7 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
     const bool legal = d->ksize == 3 && d->stride == 1 && d->pad == 1 && d->dilation == 1 && x->c % 64 == 0;
     const int th = ceil_div(Ho, kHaloH), tw = ceil_div(Wo, kHaloW);
     const double waste = (double)x->n * th * tw * kBlockM / (double)p.M;
-    const bool want = mode == 1 || (mode < 0 && N <= 128 && waste <= 1.15);
+    const bool want = mode == 1 || (mode < 0 && N <= 128 && waste <= 1.12);
     if (legal && want && mode != 0) {
       p.a_mode = 2;
       p.tiles_h = th;
@@ -677,6 +694,11 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
   // HBM traffic in flight per SM (what the memory-bound 1x1 layers live on)
   p.stages = std::min<int>(kMaxStages, smem_budget / stage_bytes);
   YC_REQUIRE(p.stages >= 2, "tile does not fit shared memory");
+  p.w_resident = 0;
+  if (p.a_mode == 2 && p.n_tiles == 1 && 9 * p.cchunks <= p.stages) {
+    p.w_resident = 1;  // every weight slab fits: load them once per CTA instead of once per tile
+    p.stages = 9 * p.cchunks;
+  }
   pl->smem = (size_t)p.stages * stage_bytes + out_stage + 1024 + 512;
   const int groups = p.block_n / 32;
   p.epi_sets = groups >= 4 ? 1 : (groups >= 2 ? 2 : 4);
@@ -881,6 +903,10 @@ extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq
   const uint32_t smem_budget = 227 * 1024 - 1024 - 512 - out_stage - stat_bytes;
   p.stages = std::min<int>(kMaxStages, smem_budget / stage_bytes);
   YC_REQUIRE(p.stages >= 2, "tile does not fit shared memory");
+  if (p.w_resident) {
+    if (9 * p.cchunks <= p.stages) p.stages = 9 * p.cchunks;
+    else p.w_resident = 0;
+  }
   pl->smem = (size_t)p.stages * stage_bytes + out_stage + 1024 + 512 + stat_bytes;
   YC_REQUIRE(!sum || p.act == YC_LINEAR, "yc_conv_plan_set_stats: statistics are taken on the linear (pre-batchnorm) output");
   p.stat_sum = sum;

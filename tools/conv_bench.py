@@ -14,6 +14,9 @@ SHAPES = {  # name: (C, N, HW, k, stride, act)
     "c3_32_64_304": (32, 64, 304, 3, 1, "mish"),
     "c1_128_64_304": (128, 64, 304, 1, 1, "mish"),
     "c3_64_64_152": (64, 64, 152, 3, 1, "mish"),
+    "c3_64_32_152": (64, 32, 152, 3, 1, "mish"),
+    "c3_64_96_152": (64, 96, 152, 3, 1, "mish"),
+    "c3_64_128_152": (64, 128, 152, 3, 1, "mish"),
     "c1_128_128_76": (128, 128, 76, 1, 1, "mish"),
     "c3_128_128_76": (128, 128, 76, 3, 1, "mish"),
     "c3_256_256_38": (256, 256, 38, 3, 1, "mish"),
