@@ -36,6 +36,8 @@ struct ConvParams {
   int a_mode;  // 0: 2-D tiled map (1x1 s1 p0), 1: im2col map, 2: halo patch (3x3 s1 p1, see kHalo*)
   int tiles_h, tiles_w;  // a_mode 2: output tiles of kHaloH x kHaloW pixels per image
   int w_resident;        // a_mode 2: all 9*cchunks weight slabs stay in shared memory for the whole (persistent) CTA
+  int halo_stages;       // a_mode 2: patch ring depth (2..kHaloMaxStages)
+  int halo_pair;         // a_mode 2 + w_resident + one chunk: two tiles' MMAs interleaved into two accumulators
   int Ho, Wo, stride, pad, dil;
   const float* bias;   // padded to n_tiles*block_n
   const float* scale;  // same padding, or nullptr
@@ -58,12 +60,13 @@ struct ConvParams {
 // as a (kHaloH+2) x kHaloPitch pixel patch (one tiled TMA box, border zero-filled by the engine) instead of nine im2col
 // tap loads.  M tile = kHaloH x kHaloW output pixels, row r = h*8 + w; the tap (kh, kw) operand is the same patch
 // read through a descriptor shifted by (kh*kHaloPitch + kw) rows of 128 B: 8-row groups (8 consecutive pixels of one
-// patch row) are kHaloPitch*128 = 2048 B apart (SBO).  Measured on B200 (tools/halo_debug.py): the tensor core applies
+// patch row) are kHaloPitch*128 B apart (SBO).  Measured on B200 (tools/halo_debug.py): the tensor core applies
 // the 128B-swizzle XOR to the ABSOLUTE shared-memory address of each row, like TMA did when writing the patch, so a
 // start address shifted by whole rows needs NO base-offset in the descriptor (setting it to (addr>>7)&7 breaks kw != 0).
-constexpr int kHaloH = 16, kHaloW = 8, kHaloPitch = 16;
+constexpr int kHaloH = 16, kHaloW = 8, kHaloPitch = 16;  // pitch 10 (exact halo) works but runs 1.5x slower: 8-row groups then straddle 1024-byte swizzle atoms
 constexpr int kHaloPatchBytes = (kHaloH + 2) * kHaloPitch * 128;  // 36864: 64 channels x bf16 per pixel
-constexpr int kHaloStages = 2;
+constexpr int kHaloPatchStride = (kHaloPatchBytes + 1023) / 1024 * 1024;  // ring slots stay 1024-byte aligned
+constexpr int kHaloMaxStages = 4;
 constexpr int kStageOutBytes = 2048;  // one epilogue staging buffer: 32 rows x 64 B
 constexpr int kEpiWarps = 16;         // four per TMEM lane quadrant == four per scheduler: enough to hide ALU/MUFU latency
 constexpr int kMaxAcc = 4;            // TMEM accumulator buffers
@@ -263,7 +266,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t tx_bytes = a_bytes + (uint32_t)(p.block_n * p.block_k * 2);
   const uint32_t patch_base = smem_base + p.stages * stage_bytes;         // 1024-aligned; halo: kHaloStages patches
-  const uint32_t out_base = patch_base + (halo ? kHaloStages * kHaloPatchBytes : 0);  // 1024-aligned
+  const uint32_t out_base = patch_base + (halo ? p.halo_stages * kHaloPatchStride : 0);  // 1024-aligned
   const uint32_t bar_base = out_base + kEpiWarps * kStageOutBytes;        // 8-byte aligned
   // barrier map: full[s] @ +8s, empty[s] @ +8(kMaxStages+s), tmem_full[4], tmem_empty[4], tmem ptr
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
@@ -272,7 +275,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + kMaxAcc + a); };
   const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc);
   auto pfull_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc + 1 + s); };
-  auto pempty_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc + 1 + kHaloStages + s); };
+  auto pempty_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc + 1 + kHaloMaxStages + s); };
   const uint32_t stat_smem = bar_base + 512u;  // 2 x stat_cols floats, only when statistics are requested
   if (STATS) {
     for (int i = threadIdx.x; i < 2 * p.stat_cols; i += blockDim.x)
@@ -290,7 +293,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), 1);
     }
-    for (int s2 = 0; s2 < kHaloStages; ++s2) {
+    for (int s2 = 0; s2 < kHaloMaxStages; ++s2) {
       ptx::mbar_init(pfull_bar(s2), 1);
       ptx::mbar_init(pempty_bar(s2), 1);
     }
@@ -315,25 +318,32 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 
   if (warp == 0 && lane == 0 && halo) {
     // ===================== TMA producer, halo mode =====================
-    // per (tile, 64-channel chunk): one patch box {64 ch, kHaloPitch, kHaloH+2, 1} starting one pixel up-left of the
-    // tile (negative / past-the-end coordinates are zero-filled = the convolution's padding), then nine weight slabs
+    // Tiles are processed in PAIRS (two consecutive tiles of this CTA, same N tile): per 64-channel chunk the two patches
+    // {64 ch, kHaloPitch, kHaloH+2, 1} are fetched (box starts one pixel up-left of the tile; coordinates outside the
+    // image are zero-filled = the convolution's padding), then the nine weight slabs ONCE for both tiles — or never
+    // again when the weights are resident.
     int stage = 0, ps = 0;
     uint32_t phase = 0, pphase = 0;
     const int tpi = p.tiles_h * p.tiles_w;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-      const int mt = t / p.n_tiles;
-      const int n0 = (t % p.n_tiles) * p.block_n;
-      const int img = mt / tpi;
-      const int rem = mt - img * tpi;
-      const int h0 = (rem / p.tiles_w) * kHaloH, w0 = (rem % p.tiles_w) * kHaloW;
+    const int G = p.halo_pair ? 2 : 1;
+    bool first = true;
+    for (int tb = blockIdx.x; tb < total_tiles; tb += G * gridDim.x) {
+      const int nt = (G == 2 && tb + (int)gridDim.x < total_tiles) ? 2 : 1;
+      const int n0 = (tb % p.n_tiles) * p.block_n;  // halo_pair requires n_tiles == 1, so both tiles share it
       for (int cc = 0; cc < p.cchunks; ++cc) {
-        ptx::mbar_wait(pempty_bar(ps), pphase ^ 1u);
-        ptx::mbar_arrive_expect_tx(pfull_bar(ps), kHaloPatchBytes);
-        ptx::tma_load_4d(patch_base + ps * kHaloPatchBytes, &tmap_a, pfull_bar(ps), cc * 64, w0 - 1, h0 - 1, img);
-        if (++ps == kHaloStages) { ps = 0; pphase ^= 1u; }
+        for (int j = 0; j < nt; ++j) {
+          const int mt = (tb + j * (int)gridDim.x) / p.n_tiles;
+          const int img = mt / tpi;
+          const int rem = mt - img * tpi;
+          const int h0 = (rem / p.tiles_w) * kHaloH, w0 = (rem % p.tiles_w) * kHaloW;
+          ptx::mbar_wait(pempty_bar(ps), pphase ^ 1u);
+          ptx::mbar_arrive_expect_tx(pfull_bar(ps), kHaloPatchBytes);
+          ptx::tma_load_4d(patch_base + ps * kHaloPatchStride, &tmap_a, pfull_bar(ps), cc * 64, w0 - 1, h0 - 1, img);
+          if (++ps == p.halo_stages) { ps = 0; pphase ^= 1u; }
+        }
         if (p.w_resident) {
-          // weights stationary: slab (tap, cc) lives in ring slot tap*cchunks + cc, loaded with this CTA's first tile
-          if (t == (int)blockIdx.x)
+          // weights stationary: slab (tap, cc) lives in ring slot tap*cchunks + cc, loaded with this CTA's first tiles
+          if (first)
             for (int tap = 0; tap < 9; ++tap) {
               const int slot = tap * p.cchunks + cc;
               ptx::mbar_arrive_expect_tx(full_bar(slot), tx_bytes);
@@ -348,23 +358,40 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
       }
+      first = false;
     }
-  } else if (warp == 1 && lane == 0 && halo) {
+  } else if (warp == 1 && halo) {
     // ===================== MMA issuer, halo mode =====================
+    // The WHOLE warp runs this loop converged and one elected lane issues: addresses and descriptors then stay
+    // warp-uniform, i.e. in uniform registers where UTCHMMA wants them (a single-lane branch computes them in vector
+    // registers and pays an R2UR chain per instruction — the per-MMA issue cost that bounded narrow tiles).
+    const bool leader = ptx::elect_one();
+    // The two tiles of a pair accumulate into two different TMEM buffers and their MMAs alternate: back-to-back MMAs
+    // into ONE accumulator cost ~170 cycles each for tiles this narrow whatever their width (measured), independent
+    // accumulators pipeline (64->32 @152: 246 -> 178 us).  Both tiles read the same weight slab.
     const uint32_t idesc = ptx::make_idesc_bf16(kBlockM, p.block_n);
     int stage = 0, ps = 0;
     uint32_t phase = 0, pphase = 0;
     int it = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-      const int acc = it % p.nacc;
-      const uint32_t acc_phase = (it / p.nacc) & 1;
-      ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+    const int G = p.halo_pair ? 2 : 1;
+    for (int tb = blockIdx.x; tb < total_tiles; tb += G * gridDim.x) {
+      const bool two = G == 2 && tb + (int)gridDim.x < total_tiles;
+      const int acc0 = it % p.nacc, acc1 = (it + 1) % p.nacc;
+      ptx::mbar_wait(tempty_bar(acc0), ((it / p.nacc) & 1) ^ 1u);
+      if (two) ptx::mbar_wait(tempty_bar(acc1), (((it + 1) / p.nacc) & 1) ^ 1u);
       ptx::tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * p.block_n;
+      const uint32_t d0 = tmem_base + acc0 * p.block_n, d1 = tmem_base + acc1 * p.block_n;
       for (int cc = 0; cc < p.cchunks; ++cc) {
+        const int ps0 = ps;
         ptx::mbar_wait(pfull_bar(ps), pphase);
+        if (++ps == p.halo_stages) { ps = 0; pphase ^= 1u; }
+        const int ps1 = ps;
+        if (two) {
+          ptx::mbar_wait(pfull_bar(ps), pphase);
+          if (++ps == p.halo_stages) { ps = 0; pphase ^= 1u; }
+        }
         ptx::tc_fence_after();
-        const uint32_t pa = patch_base + ps * kHaloPatchBytes;
+        const uint32_t pa0 = patch_base + ps0 * kHaloPatchStride, pa1 = patch_base + ps1 * kHaloPatchStride;
         for (int tap = 0; tap < 9; ++tap) {
           const int kh = tap / 3, kw = tap - kh * 3;
           if (p.w_resident) {  // slot of this slab; its barrier completed phase 0 once and is never re-armed
@@ -373,20 +400,27 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           }
           ptx::mbar_wait(full_bar(stage), phase);
           ptx::tc_fence_after();
-          const uint64_t adesc = ptx::make_smem_desc_sw128_shifted(pa + (uint32_t)(kh * kHaloPitch + kw) * 128u, kHaloPitch * 128u);
+          const uint32_t sh = (uint32_t)(kh * kHaloPitch + kw) * 128u;
+          const uint64_t a0 = ptx::make_smem_desc_sw128_shifted(pa0 + sh, kHaloPitch * 128u);
+          const uint64_t a1 = ptx::make_smem_desc_sw128_shifted(pa1 + sh, kHaloPitch * 128u);
           const uint64_t bdesc = ptx::make_smem_desc(smem_base + stage * stage_bytes, 128u);
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            ptx::mma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (cc | tap | k) != 0);
+          for (int k = 0; k < 4; ++k) {
+            if (leader) ptx::mma_bf16_ss(d0, a0 + 2u * k, bdesc + 2u * k, idesc, (cc | tap | k) != 0);
+            if (leader && two) ptx::mma_bf16_ss(d1, a1 + 2u * k, bdesc + 2u * k, idesc, (cc | tap | k) != 0);
+          }
           if (!p.w_resident) {
-            ptx::mma_commit(empty_bar(stage));
+            if (leader) ptx::mma_commit(empty_bar(stage));
             if (++stage == p.stages) { stage = 0; phase ^= 1u; }
           }
         }
-        ptx::mma_commit(pempty_bar(ps));  // the patch is free once the nine taps' MMAs have retired
-        if (cc == p.cchunks - 1) ptx::mma_commit(tfull_bar(acc));
-        if (++ps == kHaloStages) { ps = 0; pphase ^= 1u; }
+        if (leader) ptx::mma_commit(pempty_bar(ps0));  // the patches are free once the nine taps' MMAs have retired
+        if (leader && two) ptx::mma_commit(pempty_bar(ps1));
       }
+      if (leader) ptx::mma_commit(tfull_bar(acc0));
+      if (leader && two) ptx::mma_commit(tfull_bar(acc1));
+      __syncwarp();
+      it += two ? 2 : 1;
     }
   } else if (warp == 0 && lane == 0) {
     // ===================== TMA producer =====================
@@ -688,7 +722,18 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
   const uint32_t a_bytes = p.a_mode == 2 ? 0u : kBlockM * p.block_k * 2;
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
   const uint32_t stage_bytes = a_bytes + b_bytes;
-  const uint32_t out_stage = kEpiWarps * kStageOutBytes + (p.a_mode == 2 ? kHaloStages * kHaloPatchBytes : 0);
+  // halo mode: tiles go in pairs (two accumulators, one weight slab for both) when the N tile is shared (n_tiles == 1)
+  // and four patches fit next to at least three weight slabs; YC_HALO_PAIR=0 switches the pairing off
+  p.halo_stages = 2;
+  p.halo_pair = 0;
+  if (p.a_mode == 2 && p.n_tiles == 1 && !(getenv("YC_HALO_PAIR") && atoi(getenv("YC_HALO_PAIR")) == 0)) {
+    const uint32_t need = kEpiWarps * kStageOutBytes + 4 * kHaloPatchStride + 3 * stage_bytes + 1024 + 512;
+    if (need <= 227 * 1024) {
+      p.halo_stages = 4;
+      p.halo_pair = 1;
+    }
+  }
+  const uint32_t out_stage = kEpiWarps * kStageOutBytes + (p.a_mode == 2 ? p.halo_stages * kHaloPatchStride : 0);
   const uint32_t smem_budget = 227 * 1024 - 1024 /*align slack*/ - 512 /*barriers*/ - out_stage;
   // as deep as shared memory allows: the producer runs ahead across tiles, so the ring depth is the amount of
   // HBM traffic in flight per SM (what the memory-bound 1x1 layers live on)
@@ -897,7 +942,7 @@ extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq
   const uint32_t a_bytes = p.a_mode == 2 ? 0u : kBlockM * p.block_k * 2;
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
   const uint32_t stage_bytes = a_bytes + b_bytes;
-  const uint32_t out_stage = kEpiWarps * kStageOutBytes + (p.a_mode == 2 ? kHaloStages * kHaloPatchBytes : 0);
+  const uint32_t out_stage = kEpiWarps * kStageOutBytes + (p.a_mode == 2 ? p.halo_stages * kHaloPatchStride : 0);
   p.stat_cols = sum ? p.n_tiles * p.block_n : 0;
   const uint32_t stat_bytes = 2u * 4u * (uint32_t)p.stat_cols;
   const uint32_t smem_budget = 227 * 1024 - 1024 - 512 - out_stage - stat_bytes;
