@@ -456,8 +456,10 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
       }
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1) {
     // ===================== MMA issuer =====================
+    // whole warp converged, one elected lane issues (see the halo branch): descriptors stay in uniform registers
+    const bool leader = ptx::elect_one();
     const uint32_t idesc = ptx::make_idesc_bf16(kBlockM, p.block_n);
     const uint32_t row_bytes = p.block_k * 2;
     const int k_steps = p.block_k / 16;
@@ -476,12 +478,15 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const uint32_t sa = smem_base + stage * stage_bytes;
         const uint64_t adesc = ptx::make_smem_desc(sa, row_bytes);
         const uint64_t bdesc = ptx::make_smem_desc(sa + a_bytes, row_bytes);
-        for (int k = 0; k < k_steps; ++k) {
-          // advancing K by 16 bf16 = 32 bytes inside the swizzle atom: +2 in the (addr>>4) field
-          ptx::mma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+        if (leader) {
+          for (int k = 0; k < k_steps; ++k) {
+            // advancing K by 16 bf16 = 32 bytes inside the swizzle atom: +2 in the (addr>>4) field
+            ptx::mma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+          }
+          ptx::mma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
+          if (kb == k_blocks - 1) ptx::mma_commit(tfull_bar(acc));
         }
-        ptx::mma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
-        if (kb == k_blocks - 1) ptx::mma_commit(tfull_bar(acc));
+        __syncwarp();
         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }
     }
