@@ -316,8 +316,10 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   const int total_tiles = p.m_tiles * p.n_tiles;
   const int k_blocks = p.taps * p.cchunks;
 
-  if (warp == 0 && lane == 0 && halo) {
+  if (warp == 0 && halo) {
     // ===================== TMA producer, halo mode =====================
+    // (whole warp converged, one elected lane issues the TMA instructions: coordinates stay in uniform registers)
+    const bool leader = ptx::elect_one();
     // Tiles are processed in PAIRS (two consecutive tiles of this CTA, same N tile): per 64-channel chunk the two patches
     // {64 ch, kHaloPitch, kHaloH+2, 1} are fetched (box starts one pixel up-left of the tile; coordinates outside the
     // image are zero-filled = the convolution's padding), then the nine weight slabs ONCE for both tiles — or never
@@ -337,8 +339,10 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           const int rem = mt - img * tpi;
           const int h0 = (rem / p.tiles_w) * kHaloH, w0 = (rem % p.tiles_w) * kHaloW;
           ptx::mbar_wait(pempty_bar(ps), pphase ^ 1u);
-          ptx::mbar_arrive_expect_tx(pfull_bar(ps), kHaloPatchBytes);
-          ptx::tma_load_4d(patch_base + ps * kHaloPatchStride, &tmap_a, pfull_bar(ps), cc * 64, w0 - 1, h0 - 1, img);
+          if (leader) {
+            ptx::mbar_arrive_expect_tx(pfull_bar(ps), kHaloPatchBytes);
+            ptx::tma_load_4d(patch_base + ps * kHaloPatchStride, &tmap_a, pfull_bar(ps), cc * 64, w0 - 1, h0 - 1, img);
+          }
           if (++ps == p.halo_stages) { ps = 0; pphase ^= 1u; }
         }
         if (p.w_resident) {
@@ -346,15 +350,19 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           if (first)
             for (int tap = 0; tap < 9; ++tap) {
               const int slot = tap * p.cchunks + cc;
-              ptx::mbar_arrive_expect_tx(full_bar(slot), tx_bytes);
-              ptx::tma_load_2d(smem_base + slot * stage_bytes, &tmap_b, full_bar(slot), slot * 64, n0);
+              if (leader) {
+                ptx::mbar_arrive_expect_tx(full_bar(slot), tx_bytes);
+                ptx::tma_load_2d(smem_base + slot * stage_bytes, &tmap_b, full_bar(slot), slot * 64, n0);
+              }
             }
           continue;
         }
         for (int tap = 0; tap < 9; ++tap) {
           ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
-          ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
-          ptx::tma_load_2d(smem_base + stage * stage_bytes, &tmap_b, full_bar(stage), (tap * p.cchunks + cc) * 64, n0);
+          if (leader) {
+            ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
+            ptx::tma_load_2d(smem_base + stage * stage_bytes, &tmap_b, full_bar(stage), (tap * p.cchunks + cc) * 64, n0);
+          }
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
       }
@@ -422,8 +430,9 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       __syncwarp();
       it += two ? 2 : 1;
     }
-  } else if (warp == 0 && lane == 0) {
+  } else if (warp == 0) {
     // ===================== TMA producer =====================
+    const bool leader = ptx::elect_one();  // whole warp converged, one lane issues
     int stage = 0;
     uint32_t phase = 0;
     const int hw = p.Ho * p.Wo;
@@ -445,13 +454,15 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * stage_bytes;
           const uint32_t sb = sa + a_bytes;
-          ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
-          if (p.a_mode == 1)
-            ptx::tma_load_im2col_4d(sa, &tmap_a, full_bar(stage), cc * p.block_k, base_w, base_h, img,
-                                    (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
-          else
-            ptx::tma_load_2d(sa, &tmap_a, full_bar(stage), cc * p.block_k, m0);
-          ptx::tma_load_2d(sb, &tmap_b, full_bar(stage), kb * p.block_k, n0);
+          if (leader) {
+            ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
+            if (p.a_mode == 1)
+              ptx::tma_load_im2col_4d(sa, &tmap_a, full_bar(stage), cc * p.block_k, base_w, base_h, img,
+                                      (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
+            else
+              ptx::tma_load_2d(sa, &tmap_a, full_bar(stage), cc * p.block_k, m0);
+            ptx::tma_load_2d(sb, &tmap_b, full_bar(stage), kb * p.block_k, n0);
+          }
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
       }
