@@ -108,8 +108,11 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
 
   const int units = p.tiles * p.splits;
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 0) {
     // ===================== TMA producer =====================
+    // whole warp converged, one elected lane issues: coordinates / descriptors stay in uniform registers (the
+    // single-lane form pays an R2UR chain per TMA / MMA instruction; see conv_fprop_sm100.cu)
+    const bool leader = ptx::elect_one();
     int stage = 0;
     uint32_t phase = 0;
     const int hw = p.Ho * p.Wo;
@@ -131,17 +134,20 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
         const int base_w = (rem - ho * p.Wo) * p.stride - p.pad;
         ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
         const uint32_t sa = smem_base + stage * stage_bytes;
-        ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
-        for (int j = 0; j < p.a_boxes; ++j)
-          ptx::tma_load_2d(sa + j * kBoxBytes, &tmap_dy, full_bar(stage), nt * 128 + j * 64, m0);
-        for (int j = 0; j < p.b_boxes; ++j)
-          ptx::tma_load_im2col_4d(sa + a_bytes + j * kBoxBytes, &tmap_x, full_bar(stage), ct * p.block_n + j * 64,
-                                  base_w, base_h, img, (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
+        if (leader) {
+          ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
+          for (int j = 0; j < p.a_boxes; ++j)
+            ptx::tma_load_2d(sa + j * kBoxBytes, &tmap_dy, full_bar(stage), nt * 128 + j * 64, m0);
+          for (int j = 0; j < p.b_boxes; ++j)
+            ptx::tma_load_im2col_4d(sa + a_bytes + j * kBoxBytes, &tmap_x, full_bar(stage), ct * p.block_n + j * 64,
+                                    base_w, base_h, img, (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
+        }
         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1) {
     // ===================== MMA issuer =====================
+    const bool leader = ptx::elect_one();
     // both operands MN-major: instruction-descriptor bits 15 (A) and 16 (B)
     const uint32_t idesc = ptx::make_idesc_bf16(128, p.mma_n) | (1u << 15) | (1u << 16);
     int stage = 0;
@@ -162,13 +168,16 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
         const uint32_t sa = smem_base + stage * stage_bytes;
         const uint64_t adesc = make_desc_mn_sw128(sa, kBoxBytes, 1024);
         const uint64_t bdesc = make_desc_mn_sw128(sa + a_bytes, kBoxBytes, 1024);
+        if (leader) {
 #pragma unroll
-        for (int k = 0; k < kWgKBlk / 16; ++k) {
-          // advancing K by 16 pixels = 16 rows of 128 B = 2048 B -> +128 in the (addr >> 4) field
-          ptx::mma_bf16_ss(d_tmem, adesc + 128u * k, bdesc + 128u * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          for (int k = 0; k < kWgKBlk / 16; ++k) {
+            // advancing K by 16 pixels = 16 rows of 128 B = 2048 B -> +128 in the (addr >> 4) field
+            ptx::mma_bf16_ss(d_tmem, adesc + 128u * k, bdesc + 128u * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          ptx::mma_commit(empty_bar(stage));
+          if (kb == kb1 - 1) ptx::mma_commit(tfull_bar(acc));
         }
-        ptx::mma_commit(empty_bar(stage));
-        if (kb == kb1 - 1) ptx::mma_commit(tfull_bar(acc));
+        __syncwarp();
         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }
     }
