@@ -64,8 +64,8 @@ struct ConvParams {
 // the 128B-swizzle XOR to the ABSOLUTE shared-memory address of each row, like TMA did when writing the patch, so a
 // start address shifted by whole rows needs NO base-offset in the descriptor (setting it to (addr>>7)&7 breaks kw != 0).
 constexpr int kHaloH = 16, kHaloW = 8, kHaloPitch = 16;  // pitch 10 (exact halo) works but runs 1.5x slower: 8-row groups then straddle 1024-byte swizzle atoms
-constexpr int kHaloPatchBytes = (kHaloH + 2) * kHaloPitch * 128;  // 36864: 64 channels x bf16 per pixel
-constexpr int kHaloPatchStride = (kHaloPatchBytes + 1023) / 1024 * 1024;  // ring slots stay 1024-byte aligned
+constexpr int kHaloPatchRows = (kHaloH + 2) * kHaloPitch;  // 288 pixel rows of block_k*2 bytes (128 B, or 64 B when Cin % 64 != 0)
+constexpr int kHaloPatchStride = kHaloPatchRows * 128;     // ring slot pitch (36864, 1024-byte aligned), sized for 128-byte rows
 constexpr int kHaloMaxStages = 4;
 constexpr int kStageOutBytes = 2048;  // one epilogue staging buffer: 32 rows x 64 B
 constexpr int kEpiWarps = 16;         // four per TMEM lane quadrant == four per scheduler: enough to hide ALU/MUFU latency
@@ -340,8 +340,8 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           const int h0 = (rem / p.tiles_w) * kHaloH, w0 = (rem % p.tiles_w) * kHaloW;
           ptx::mbar_wait(pempty_bar(ps), pphase ^ 1u);
           if (leader) {
-            ptx::mbar_arrive_expect_tx(pfull_bar(ps), kHaloPatchBytes);
-            ptx::tma_load_4d(patch_base + ps * kHaloPatchStride, &tmap_a, pfull_bar(ps), cc * 64, w0 - 1, h0 - 1, img);
+            ptx::mbar_arrive_expect_tx(pfull_bar(ps), (uint32_t)(kHaloPatchRows * p.block_k * 2));
+            ptx::tma_load_4d(patch_base + ps * kHaloPatchStride, &tmap_a, pfull_bar(ps), cc * p.block_k, w0 - 1, h0 - 1, img);
           }
           if (++ps == p.halo_stages) { ps = 0; pphase ^= 1u; }
         }
@@ -352,7 +352,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
               const int slot = tap * p.cchunks + cc;
               if (leader) {
                 ptx::mbar_arrive_expect_tx(full_bar(slot), tx_bytes);
-                ptx::tma_load_2d(smem_base + slot * stage_bytes, &tmap_b, full_bar(slot), slot * 64, n0);
+                ptx::tma_load_2d(smem_base + slot * stage_bytes, &tmap_b, full_bar(slot), slot * p.block_k, n0);
               }
             }
           continue;
@@ -361,7 +361,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
           if (leader) {
             ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
-            ptx::tma_load_2d(smem_base + stage * stage_bytes, &tmap_b, full_bar(stage), (tap * p.cchunks + cc) * 64, n0);
+            ptx::tma_load_2d(smem_base + stage * stage_bytes, &tmap_b, full_bar(stage), (tap * p.cchunks + cc) * p.block_k, n0);
           }
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
@@ -378,6 +378,8 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     // into ONE accumulator cost ~170 cycles each for tiles this narrow whatever their width (measured), independent
     // accumulators pipeline (64->32 @152: 246 -> 178 us).  Both tiles read the same weight slab.
     const uint32_t idesc = ptx::make_idesc_bf16(kBlockM, p.block_n);
+    const uint32_t hrow = (uint32_t)p.block_k * 2u;  // bytes per pixel row of a patch: 128 (64-channel chunks) or 64 (32)
+    const int hsteps = p.block_k / 16;
     int stage = 0, ps = 0;
     uint32_t phase = 0, pphase = 0;
     int it = 0;
@@ -408,14 +410,22 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           }
           ptx::mbar_wait(full_bar(stage), phase);
           ptx::tc_fence_after();
-          const uint32_t sh = (uint32_t)(kh * kHaloPitch + kw) * 128u;
-          const uint64_t a0 = ptx::make_smem_desc_sw128_shifted(pa0 + sh, kHaloPitch * 128u);
-          const uint64_t a1 = ptx::make_smem_desc_sw128_shifted(pa1 + sh, kHaloPitch * 128u);
-          const uint64_t bdesc = ptx::make_smem_desc(smem_base + stage * stage_bytes, 128u);
+          const uint32_t sh = (uint32_t)(kh * kHaloPitch + kw) * hrow;
+          const uint64_t a0 = ptx::make_smem_desc_shifted(pa0 + sh, kHaloPitch * hrow, hrow);
+          const uint64_t a1 = ptx::make_smem_desc_shifted(pa1 + sh, kHaloPitch * hrow, hrow);
+          const uint64_t bdesc = ptx::make_smem_desc(smem_base + stage * stage_bytes, hrow);
+          if (hsteps == 4) {  // constant trip counts: the unrolled form keeps the descriptors in uniform registers
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            if (leader) ptx::mma_bf16_ss(d0, a0 + 2u * k, bdesc + 2u * k, idesc, (cc | tap | k) != 0);
-            if (leader && two) ptx::mma_bf16_ss(d1, a1 + 2u * k, bdesc + 2u * k, idesc, (cc | tap | k) != 0);
+            for (int k = 0; k < 4; ++k) {
+              if (leader) ptx::mma_bf16_ss(d0, a0 + 2u * k, bdesc + 2u * k, idesc, (cc | tap | k) != 0);
+              if (leader && two) ptx::mma_bf16_ss(d1, a1 + 2u * k, bdesc + 2u * k, idesc, (cc | tap | k) != 0);
+            }
+          } else {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+              if (leader) ptx::mma_bf16_ss(d0, a0 + 2u * k, bdesc + 2u * k, idesc, (cc | tap | k) != 0);
+              if (leader && two) ptx::mma_bf16_ss(d1, a1 + 2u * k, bdesc + 2u * k, idesc, (cc | tap | k) != 0);
+            }
           }
           if (!p.w_resident) {
             if (leader) ptx::mma_commit(empty_bar(stage));
@@ -702,12 +712,12 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
   p.m_tiles = ceil_div(p.M, kBlockM);
   p.tiles_h = p.tiles_w = 0;
   {
-    // halo mode: 3x3 / stride 1 / pad 1 with whole 64-channel chunks.  It pays where the nine im2col tap loads bound the
+    // halo mode: 3x3 / stride 1 / pad 1 with whole 64- (or 32-) channel chunks.  It pays where the nine im2col tap loads bound the
     // layer (few output channels per fetched row) and the 16x8 tiling wastes little: YC_CONV_HALO=0 never, 1 always
     // (when legal), unset: cost rule.
     const char* env = getenv("YC_CONV_HALO");
     const int mode = env ? atoi(env) : -1;
-    const bool legal = d->ksize == 3 && d->stride == 1 && d->pad == 1 && d->dilation == 1 && x->c % 64 == 0;
+    const bool legal = d->ksize == 3 && d->stride == 1 && d->pad == 1 && d->dilation == 1 && x->c % 32 == 0;
     const int th = ceil_div(Ho, kHaloH), tw = ceil_div(Wo, kHaloW);
     const double waste = (double)x->n * th * tw * kBlockM / (double)p.M;
     const bool want = mode == 1 || (mode < 0 && N <= 128 && waste <= 1.12);
@@ -803,10 +813,10 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
     // the (kHaloH+2) x kHaloPitch pixel patch around a tile: plain tiled box over {c, w, h, n}, zero fill outside
     cuuint64_t dims[4] = {(cuuint64_t)x->c, (cuuint64_t)x->w, (cuuint64_t)x->h, (cuuint64_t)x->n};
     cuuint64_t strides[3] = {(cuuint64_t)x->ldc * 2, (cuuint64_t)x->ldc * 2 * x->w, (cuuint64_t)x->ldc * 2 * x->w * x->h};
-    cuuint32_t box[4] = {64, (cuuint32_t)kHaloPitch, (cuuint32_t)(kHaloH + 2), 1};
+    cuuint32_t box[4] = {(cuuint32_t)p.block_k, (cuuint32_t)kHaloPitch, (cuuint32_t)(kHaloH + 2), 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     cr = g_encode_tiled(&pl->tmap_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, x->ptr, dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   } else if (p.a_mode == 0) {
     cuuint64_t dims[2] = {(cuuint64_t)x->c, (cuuint64_t)p.M};

@@ -200,6 +200,17 @@ __device__ __forceinline__ uint64_t make_smem_desc_sw128_shifted(uint32_t saddr,
   d |= (uint64_t)2 << 61;
   return d;
 }
+// The same for rows of 128 / 64 / 32 bytes (swizzle 128B / 64B / 32B).
+__device__ __forceinline__ uint64_t make_smem_desc_shifted(uint32_t saddr, uint32_t sbo_bytes, uint32_t row_bytes) {
+  const uint32_t layout = row_bytes == 128 ? 2u : (row_bytes == 64 ? 4u : 6u);
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(sbo_bytes >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)layout << 61;
+  return d;
+}
 // Instruction descriptor for kind::f16 with bf16 A/B (K-major both), fp32 accumulate, M x N tile.
 //   [4,6) D fmt: 1=f32 | [7,10) A fmt: 1=bf16 | [10,13) B fmt: 1=bf16 | 15/16 A/B major: 0=K
 //   [17,23) N>>3 | [24,29) M>>4

@@ -16,7 +16,8 @@ def halo(monkeypatch):
 
 @pytest.mark.parametrize("C,N,H,W,act", [(64, 64, 16, 8, "linear"), (64, 64, 32, 32, "leaky"), (128, 128, 19, 19, "mish"),
                                          (64, 96, 7, 9, "mish"), (256, 256, 13, 13, "leaky"), (128, 64, 38, 38, "mish"),
-                                         (64, 32, 20, 76, "leaky")])
+                                         (64, 32, 20, 76, "leaky"), (32, 64, 32, 24, "mish"), (32, 32, 19, 19, "leaky"),
+                                         (96, 64, 16, 16, "leaky")])
 def test_conv3x3_halo(gpu, halo, C, N, H, W, act):
     from darknet_b200 import ops
     _run(gpu, 2, C, H, W, N, 3, 1, act)
