@@ -241,6 +241,7 @@ int free_device_state(yc_network* net) {
   if (net->input_dev2) { cudaFree(net->input_dev2); net->input_dev2 = nullptr; }
   net->staged_host = net->resident_host = nullptr;
   if (net->u8_dev) { cudaFree(net->u8_dev); net->u8_dev = nullptr; }
+  if (net->sgd_items) { cudaFree(net->sgd_items); net->sgd_items = nullptr; }
   if (net->input_nhwc) { cudaFree(net->input_nhwc); net->input_nhwc = nullptr; }
   if (net->det_regions) { cudaFree(net->det_regions); net->det_regions = nullptr; }
   if (net->det_counts) { cudaFree(net->det_counts); net->det_counts = nullptr; }

@@ -135,6 +135,56 @@ __global__ void maxpool_bwd_kernel(BV dy, const uint8_t* __restrict__ idx, BV dx
   }
 }
 
+// The same for the 2x2 / stride-2 windows of the tiny nets (size == stride, windows start at 0): every input pixel
+// lies in exactly one window, so one thread owns a window and its four input pixels; all loads are issued before
+// the first use (the general kernel chains idx -> dy -> dx).
+__global__ void __launch_bounds__(256) maxpool_bwd_2x2_kernel(BV dy, const uint8_t* __restrict__ idx, BV dx) {
+  const int groups = dx.c >> 3;  // launcher guarantees c % 8 == 0
+  const long long total = (long long)dy.n * dy.h * dy.w * groups;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % groups);
+    const long long opix = i / groups;
+    const int ow = (int)(opix % dy.w);
+    const int oh = (int)((opix / dy.w) % dy.h);
+    const long long b = opix / ((long long)dy.w * dy.h);
+    const uint2 q = *reinterpret_cast<const uint2*>(idx + opix * (long long)dx.c + g * 8);
+    const uint4 dq = *reinterpret_cast<const uint4*>(dy.ptr + opix * dy.ldc + g * 8);
+    uint4 xq[4];
+    __nv_bfloat16* xp[4];
+    bool ok[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int ih = oh * 2 + (t >> 1), iw = ow * 2 + (t & 1);
+      ok[t] = ih < dx.h && iw < dx.w;
+      xp[t] = dx.ptr + ((b * dx.h + ih) * dx.w + iw) * dx.ldc + g * 8;
+      xq[t] = ok[t] ? *reinterpret_cast<const uint4*>(xp[t]) : make_uint4(0, 0, 0, 0);
+    }
+    const __nv_bfloat162* dh = reinterpret_cast<const __nv_bfloat162*>(&dq);
+    float d[8];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(dh[e]);
+      d[2 * e] = f.x;
+      d[2 * e + 1] = f.y;
+    }
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      if (!ok[t]) continue;
+      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&xq[t]);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float2 f = __bfloat1622float2(h[e]);
+        const uint32_t w32 = e < 2 ? q.x : q.y;
+        const int t0 = (w32 >> (16 * (e & 1))) & 255, t1 = (w32 >> (16 * (e & 1) + 8)) & 255;
+        if (t0 == t) f.x += d[2 * e];
+        if (t1 == t) f.y += d[2 * e + 1];
+        h[e] = __floats2bfloat162_rn(f.x, f.y);
+      }
+      *reinterpret_cast<uint4*>(xp[t]) = xq[t];
+    }
+  }
+}
+
 // BackwardUpsampleLayer (upsample_layer.c:92-103 -> upsample_cpu forward=0, blas.c:382-406):
 // state.delta[in] += scale * sum of the stride^2 children of l->delta
 __global__ void upsample_bwd_kernel(BV dy, BV dx, int stride, float scale) {
@@ -254,7 +304,58 @@ __global__ void sgd_vector_kernel(float* __restrict__ p, float* __restrict__ dp,
   p[i] += lr_over_batch * g;
   dp[i] = g * momentum;
 }
-// all-reduce staging helpers are not needed: gradients are fp32 and contiguous per layer.
+// The whole network's update in ONE launch (yc_network_update): a table of items, 1024 elements per block, the block
+// finds its item by bisection of the block prefix.  Items with taps == 0 are plain vectors (biases, scales).
+__global__ void __launch_bounds__(256) sgd_multi_kernel(const SgdItem* __restrict__ items, int n_items, float lr_over_batch,
+                                                        float decay_batch, float momentum) {
+  int lo = 0, hi = n_items - 1;
+  while (lo < hi) {  // last item whose first_block <= blockIdx.x
+    const int mid = (lo + hi + 1) >> 1;
+    if (items[mid].first_block <= (int)blockIdx.x) lo = mid; else hi = mid - 1;
+  }
+  const SgdItem it = items[lo];
+  const long long base = (long long)((int)blockIdx.x - it.first_block) * 1024;
+  if (it.taps == 0) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const long long i = base + k * 256 + threadIdx.x;
+      if (i >= it.out_c) break;
+      const float g = it.dw[i];
+      it.w[i] += lr_over_batch * g;
+      it.dw[i] = g * momentum;
+    }
+    return;
+  }
+  const long long total = (long long)it.out_c * it.taps * it.in_c;
+  float w[4], g[4];
+  long long gi[4], wi[4];
+  int cc[4], tt[4], nn[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {  // loads of the four elements first
+    const long long i = base + k * 256 + threadIdx.x;
+    const bool ok = i < total;
+    const long long ii = ok ? i : 0;
+    cc[k] = (int)(ii % it.in_c);
+    tt[k] = (int)((ii / it.in_c) % it.taps);
+    nn[k] = ok ? (int)(ii / ((long long)it.in_c * it.taps)) : -1;
+    gi[k] = ((long long)max(nn[k], 0) * it.taps + tt[k]) * it.ldw + cc[k];
+    wi[k] = ((long long)max(nn[k], 0) * it.in_c + cc[k]) * it.taps + tt[k];
+    w[k] = it.w[wi[k]];
+    g[k] = it.dw[gi[k]];
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (nn[k] < 0) continue;
+    float gg = g[k] - decay_batch * w[k];
+    const float ww = w[k] + lr_over_batch * gg;
+    gg *= momentum;
+    it.w[wi[k]] = ww;
+    it.dw[gi[k]] = gg;
+    const __nv_bfloat16 wb = __float2bfloat16_rn(ww);
+    if (it.wp_f) it.wp_f[((long long)nn[k] * it.taps + tt[k]) * it.in_c_p + cc[k]] = wb;
+    if (it.wp_d) it.wp_d[((long long)cc[k] * it.taps + (it.taps - 1 - tt[k])) * it.out_c_p + nn[k]] = wb;
+  }
+}
 
 }  // namespace yc
 
@@ -285,6 +386,12 @@ extern "C" int yc_maxpool_bwd(const yc_tensor* dy, const unsigned char* idx, con
   YC_REQUIRE(dy->n == dx->n && dy->c == dx->c && dy->h == (dx->h + pad - size) / stride + 1 &&
                  dy->w == (dx->w + pad - size) / stride + 1,
              "yc_maxpool_bwd: shape mismatch");
+  if (size == 2 && stride == 2 && pad / 2 == 0 && dx->c % 8 == 0 && dx->ldc % 8 == 0 && dy->ldc % 8 == 0) {
+    const long long w2 = (long long)dy->n * dy->h * dy->w * (dx->c / 8);
+    maxpool_bwd_2x2_kernel<<<tl_grid(w2), 256, 0, (cudaStream_t)stream>>>(bv(dy), idx, bv(dx));
+    YC_LAUNCH_CHECK();
+    return YC_OK;
+  }
   const long long work = (long long)dx->n * dx->h * dx->w * ((dx->c + 7) / 8);
   maxpool_bwd_kernel<<<tl_grid(work), 256, 0, (cudaStream_t)stream>>>(bv(dy), idx, bv(dx), size, stride, pad);
   YC_LAUNCH_CHECK();
@@ -318,6 +425,13 @@ extern "C" int yc_shortcut_bwd(const yc_tensor* dy, const yc_tensor* y, int acti
   shortcut_bwd_kernel<<<tl_grid(work), 256, 0, (cudaStream_t)stream>>>(bv(dy), activation == YC_LINEAR ? bv(dy) : bv(y),
                                                                        activation, dprev ? bv(dprev) : none,
                                                                        dfrom ? bv(dfrom) : none);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+int yc::sgd_update_multi(const SgdItem* items_dev, int n_items, int total_blocks, float lr, int batch, float momentum,
+                         float decay, cudaStream_t st) {
+  if (n_items <= 0 || total_blocks <= 0) return YC_OK;
+  sgd_multi_kernel<<<total_blocks, 256, 0, st>>>(items_dev, n_items, lr / batch, decay * batch, momentum);
   YC_LAUNCH_CHECK();
   return YC_OK;
 }

@@ -46,6 +46,18 @@ static inline int round_up(int a, int b) { return ceil_div(a, b) * b; }
 
 int sm_count();
 
+// one entry of the whole-network SGD update (train_layers.cu: sgd_multi_kernel; built by yc_network_update)
+struct SgdItem {
+  float* w;               // fp32 master: OIHW weights, or the bias / scale vector
+  float* dw;              // gradient accumulator (packed [n][tap][ldw] for weights)
+  __nv_bfloat16* wp_f;    // bf16 forward packing [n][tap][in_c_p] (or null)
+  __nv_bfloat16* wp_d;    // bf16 data-gradient packing [c][flipped tap][out_c_p] (or null)
+  int out_c, in_c, taps, ldw, in_c_p, out_c_p;  // taps == 0: plain vector of out_c elements
+  int first_block, blocks;
+};
+int sgd_update_multi(const SgdItem* items_dev, int n_items, int total_blocks, float lr, int batch, float momentum,
+                     float decay, cudaStream_t st);
+
 // ---- device-side activation math shared by the conv epilogue and the elementwise kernels ------
 // Formulas follow the reference (activations.h:80-121, activation_kernels.cu:56-79), fp32.
 // MUFU wrappers with flush-to-zero: one SASS instruction each (the non-ftz intrinsics add range-scaling code).
