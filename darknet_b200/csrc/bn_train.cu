@@ -13,6 +13,9 @@
 
 #include "yc_common.cuh"
 
+#ifndef YC_BN_MINB
+#define YC_BN_MINB 2  // resident blocks per SM the three row kernels are compiled for (3 caps them at 80 registers: spills)
+#endif
 namespace yc {
 
 struct TView {
@@ -208,7 +211,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ sum, const float* _
 // thread = (row slot, 8-channel group): the per-channel constants live in registers, the thread walks rows with a
 // stride of gridDim*slots, two rows per iteration so that both 16-byte loads are in flight before the math.
 template <int ACT>
-__global__ void __launch_bounds__(256, 3) bn_act_fwd_kernel(TView z, const float* __restrict__ mean, const float* __restrict__ var,
+__global__ void __launch_bounds__(256, YC_BN_MINB) bn_act_fwd_kernel(TView z, const float* __restrict__ mean, const float* __restrict__ var,
                                   const float* __restrict__ gamma, const float* __restrict__ beta, TView y,
                                   int y_own_pad) {
   constexpr int act = ACT;  // compile-time: with a runtime switch unrolled 32x the kernel was 64 KB of code
@@ -225,7 +228,31 @@ __global__ void __launch_bounds__(256, 3) bn_act_fwd_kernel(TView z, const float
     Bc[j] = ok ? beta[c] - mean[c] * A[j] : 0.f;
   }
   const long long step = (long long)gridDim.x * slots;
-  for (long long row = (long long)blockIdx.x * slots + slot; row < z.rows; row += 4 * step) {
+  long long row = (long long)blockIdx.x * slots + slot;
+  if (fast_view(z, tg * 8)) {
+    // software pipeline: the next four rows are requested before the current four are converted and stored
+    uint4 q[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) q[k] = ldq(z, row + k * step, tg * 8, row + k * step < z.rows);
+    for (; row < z.rows; row += 4 * step) {
+      uint4 nq[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) nq[k] = ldq(z, row + (4 + k) * step, tg * 8, row + (4 + k) * step < z.rows);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const long long r = row + k * step;
+        if (r < z.rows) {
+          float v[8];
+          cvt8(q[k], tg * 8, z.c, v);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = act_fwd_exact(fmaf(A[j], v[j], Bc[j]), act);
+          st8(y, r, tg * 8, v, y_own_pad != 0);
+        }
+        q[k] = nq[k];
+      }
+    }
+  }
+  for (; row < z.rows; row += 4 * step) {
     const long long r[4] = {row, row + step, row + 2 * step, row + 3 * step};
     const bool ok[4] = {true, r[1] < z.rows, r[2] < z.rows, r[3] < z.rows};
     float v[4][8];
@@ -245,7 +272,7 @@ __global__ void __launch_bounds__(256, 3) bn_act_fwd_kernel(TView z, const float
 // MODE 1 (bias only):  g = dy * act'(y) evaluated on the layer OUTPUT y (leaky/relu/logistic/linear): S1 only
 // thread = (row slot, 8-channel group); registers -> shared atomics -> global atomics.
 template <int MODE, int ACT>
-__global__ void __launch_bounds__(256, 3) bwd_reduce_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
+__global__ void __launch_bounds__(256, YC_BN_MINB) bwd_reduce_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
                                   const float* __restrict__ gamma, const float* __restrict__ beta,
                                   float* __restrict__ S1, float* __restrict__ S2) {
   constexpr int act = ACT;
@@ -270,7 +297,46 @@ __global__ void __launch_bounds__(256, 3) bwd_reduce_kernel(TView dy, TView z, c
   }
   if (slot < slots) {
     const long long step = (long long)gridDim.x * slots;
-    for (long long row = (long long)blockIdx.x * slots + slot; row < dy.rows; row += 2 * step) {
+    long long row = (long long)blockIdx.x * slots + slot;
+    if (fast_view(dy, tg * 8) && fast_view(z, tg * 8)) {
+      // software pipeline: the loads of the NEXT two rows are issued before the math of the current two, so a
+      // thread always has four 16-byte loads in flight (load latency and math overlap instead of alternating)
+      uint4 qd[2], qz[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const long long r = row + k * step;
+        qd[k] = ldq(dy, r, tg * 8, r < dy.rows);
+        qz[k] = ldq(z, r, tg * 8, r < dy.rows);
+      }
+      for (; row < dy.rows; row += 2 * step) {
+        uint4 nd[2], nz[2];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          const long long r = row + (2 + k) * step;
+          nd[k] = ldq(dy, r, tg * 8, r < dy.rows);
+          nz[k] = ldq(z, r, tg * 8, r < dy.rows);
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+          float d[8], x[8];
+          cvt8(qd[k], tg * 8, dy.c, d);  // absent rows: d = 0, so they add nothing
+          cvt8(qz[k], tg * 8, z.c, x);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            if (MODE == 0) {
+              const float g = d[j] * act_grad(fmaf(A[j], x[j], Bc[j]), act);
+              a1[j] += g;
+              a2[j] = fmaf(g, x[j] - mu[j], a2[j]);
+            } else {
+              a1[j] = fmaf(d[j], act_grad_out(x[j], act), a1[j]);
+            }
+          }
+          qd[k] = nd[k];
+          qz[k] = nz[k];
+        }
+      }
+    }
+    for (; row < dy.rows; row += 2 * step) {
       const long long row2 = row + step;
       const bool two = row2 < dy.rows;
       float d[8], x[8], d2[8], x2[8];
@@ -338,7 +404,7 @@ __global__ void bn_bwd_coef_kernel(const float* __restrict__ S1, const float* __
 }
 
 template <int ACT>
-__global__ void __launch_bounds__(256, 3) bn_bwd_apply_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
+__global__ void __launch_bounds__(256, YC_BN_MINB) bn_bwd_apply_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
                                     const float* __restrict__ gamma, const float* __restrict__ beta,
                                     const float* __restrict__ coef, TView dz, int groups) {
   constexpr int act = ACT;
@@ -362,7 +428,44 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_apply_kernel(TView dy, TView z,
     c2[j] = ok ? coef[2 * n + c] - c1[j] * mu : 0.f;
   }
   const long long step = (long long)gridDim.x * slots;
-  for (long long row = (long long)blockIdx.x * slots + slot; row < dy.rows; row += 2 * step) {
+  long long row = (long long)blockIdx.x * slots + slot;
+  if (live && fast_view(dy, tg * 8) && fast_view(z, tg * 8)) {
+    // software pipeline (see bwd_reduce_kernel): next two rows' loads before the current rows' math and stores
+    uint4 qd[2], qz[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+      const long long r = row + k * step;
+      qd[k] = ldq(dy, r, tg * 8, r < dy.rows);
+      qz[k] = ldq(z, r, tg * 8, r < dy.rows);
+    }
+    for (; row < dy.rows; row += 2 * step) {
+      uint4 nd[2], nz[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const long long r = row + (2 + k) * step;
+        nd[k] = ldq(dy, r, tg * 8, r < dy.rows);
+        nz[k] = ldq(z, r, tg * 8, r < dy.rows);
+      }
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const long long r = row + k * step;
+        if (r < dy.rows) {
+          float d[8], x[8];
+          cvt8(qd[k], tg * 8, dy.c, d);
+          cvt8(qz[k], tg * 8, z.c, x);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float gg = d[j] * act_grad(fmaf(A[j], x[j], Bc[j]), act);
+            d[j] = fmaf(gg, c0[j], fmaf(c1[j], x[j], c2[j]));
+          }
+          st8(dz, r, tg * 8, d, true);
+        }
+        qd[k] = nd[k];
+        qz[k] = nz[k];
+      }
+    }
+  }
+  for (; row < dy.rows; row += 2 * step) {
     const long long row2 = row + step;
     const bool two = row2 < dy.rows;
     float d[8] = {0, 0, 0, 0, 0, 0, 0, 0}, x[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -404,10 +507,12 @@ __global__ void act_bwd_apply_kernel(TView dy, TView u, TView dz, int groups) {
   }
 }
 
-// grid for the row-walking kernels: every thread handles >= 2 rows per iteration; 8 blocks per SM keep ~2k threads x
-// two 16-byte loads per tensor in flight per SM
+// grid for the row-walking kernels: at most ONE wave of resident blocks (YC_BN_MINB per SM).  Every block pays a
+// dependent chain of per-channel constant loads before its first row; with 8 blocks per SM the mid-size layers ran
+// 2-4 waves of that chain (26^2 x 256 x 64 images: 42 us for 44 MB), with one wave the software-pipelined row loop
+// amortises it.
 static int row_grid(long long rows, int slots, int per_iter = 2) {
-  return (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(rows, (long long)slots * per_iter), (long long)sm_count() * 8));
+  return (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(rows, (long long)slots * per_iter), (long long)sm_count() * YC_BN_MINB));
 }
 // instantiate a launch for the activation id (compile-time in the kernels)
 #define YC_ACT_DISPATCH(act_id, ...)                                                  \
@@ -483,7 +588,7 @@ extern "C" int yc_bn_bwd(const yc_tensor* dy, const yc_tensor* z, const float* m
   const int groups = (n + 7) / 8;
   const int threads = reduce_threads(groups);
   const int slots = threads / groups;
-  const int grid = (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(dv.rows, (long long)slots * 4), (long long)sm_count() * 8));
+  const int grid = row_grid(dv.rows, slots, 2);
   YC_ACT_DISPATCH(activation, (bwd_reduce_kernel<0, A><<<grid, threads, sizeof(float) * 2 * groups * 8, st>>>(dv, zv, mean, var, gamma,
                                                                                                              beta, S1, S2)));
   YC_LAUNCH_CHECK();
@@ -515,7 +620,7 @@ extern "C" int yc_bias_act_bwd(const yc_tensor* dy, const yc_tensor* y, int acti
   if (bias_updates) {
     const int threads = reduce_threads(groups);
     const int slots = threads / groups;
-    const int grid = (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(dv.rows, (long long)slots * 4), (long long)sm_count() * 8));
+    const int grid = row_grid(dv.rows, slots, 2);
     YC_ACT_DISPATCH(activation, (bwd_reduce_kernel<1, A><<<grid, threads, sizeof(float) * 2 * groups * 8, st>>>(
                                     dv, uv, nullptr, nullptr, nullptr, nullptr, bias_updates, nullptr)));
     YC_LAUNCH_CHECK();
