@@ -69,6 +69,32 @@ def emit(obj):
         os.write(_REAL_STDOUT, line)
 
 
+def _ncu_traffic(n_conv):
+    """DRAM bytes per conv launch from the committed ncu launch list of this same command (profiles/; ncu cannot run
+    inside a timed bench).  None when the file is absent or does not hold a whole step."""
+    import csv
+    path = os.path.join(ROOT, "profiles", "r01_launches_yolov4_608_b64.csv")
+    if not os.path.exists(path):
+        return None
+    try:
+        with open(path, newline="") as f:
+            lines = [l for l in f if l.startswith('"')]
+        per = {}
+        for r in csv.DictReader(lines):
+            if "conv_fprop" not in r["Kernel Name"] or not r["Metric Name"].startswith("dram__bytes"):
+                continue
+            sc = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(r["Metric Unit"], 1.0)
+            per[int(r["ID"])] = per.get(int(r["ID"]), 0.0) + float(r["Metric Value"].replace(",", "")) * sc
+        ids = sorted(per)
+        if len(ids) < n_conv:
+            return None
+        last = ids[-n_conv:]
+        return {"bytes_per_launch": sum(per[i] for i in last) / n_conv,
+                "source": "profiles/r01_launches_yolov4_608_b64.csv (ncu launch list of bench.py --steps 1 --warmup 3, last step)"}
+    except Exception:
+        return None
+
+
 def _peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -565,6 +591,20 @@ def main():
                     "whole_step_frac": (flops_img * B / (ms_per_step / 1e3) / 1e12) / peaks["sustained"],
                     "how": "sum of algorithmic FLOPs of the conv launches of one step / sum of their durations; each launch "
                            "bracketed by CUDA events on the launch stream (yc_network_profile, 3 passes averaged)"}
+            tr = _ncu_traffic(n_conv)
+            if tr is not None:
+                # compulsory bytes of one step: every conv reads its input and writes its output once (bf16), weights once
+                alg = 0.0
+                for i in range(nl):
+                    if net.layer_info(i, 0) == 0:
+                        hw_out = net.layer_info(i, 2) * net.layer_info(i, 3)
+                        st_ = max(1, net.layer_info(i, 7))
+                        alg += 2.0 * B * hw_out * (net.layer_info(i, 1) + net.layer_info(i, 5) * st_ * st_)
+                        alg += 2.0 * net.layer_info(i, 1) * net.layer_info(i, 5) * net.layer_info(i, 6) ** 2
+                roof["traffic"] = tr["bytes_per_launch"]
+                roof["traffic_unit"] = "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum, mean of the step's conv launches)"
+                roof["traffic_source"] = tr["source"]
+                roof["algorithmic_bytes_per_launch"] = alg / n_conv
             if args.layers:
                 for i in range(nl):
                     if ms_layer[i] > 0:

@@ -573,6 +573,75 @@ __global__ void yolo_loss_finish_kernel(LossParams p, __nv_bfloat16* __restrict_
   }
 }
 
+// The same, tiled: one block per (image, 32 cells) stages all n*E delta entries of those cells in shared memory, so the
+// fp32 NCHW planes are read and written 128 bytes per warp and the NHWC bf16 head delta is updated row by row
+// (n*E consecutive channels per cell) instead of one 2-byte access per thread at a pitch of prev_ld.
+__global__ void __launch_bounds__(256) yolo_loss_finish_tiled_kernel(LossParams p, __nv_bfloat16* __restrict__ prev,
+                                                                     long long prev_ld) {
+  extern __shared__ float tile[];  // [n*E][33] then int cnt[n][32]
+  const int wh = p.W * p.H;
+  const int BE = box_entries(p);
+  const int E = BE + 1 + p.classes;
+  const int CH = p.n * E;
+  int* cnt = reinterpret_cast<int*>(tile + CH * 33);
+  const int tiles = (wh + 31) / 32;
+  const int b = blockIdx.x / tiles, loc0 = (blockIdx.x % tiles) * 32;
+  float* dl = p.delta + (long long)b * CH * wh;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const bool loc_ok = loc0 + lane < wh;
+  for (int ch = warp; ch < CH; ch += 8) tile[ch * 33 + lane] = loc_ok ? dl[(long long)ch * wh + loc0 + lane] : 0.f;
+  __syncthreads();
+  for (int t = threadIdx.x; t < p.n * 32; t += 256) {
+    const int a = t >> 5, l = t & 31;
+    int in_box = 0;
+    for (int c = 0; c < p.classes; ++c)
+      if (tile[(a * E + BE + 1 + c) * 33 + l] > 0) ++in_box;
+    cnt[t] = in_box;
+  }
+  __syncthreads();
+  float s_all = 0, s_nobox = 0;
+  for (int ch = warp; ch < CH; ch += 8) {
+    const int a = ch / E, e = ch - a * E;
+    float d = tile[ch * 33 + lane];
+    const int in_box = cnt[a * 32 + lane];
+    if (e < BE && in_box > 0 && loc_ok) {
+      d /= in_box;
+      dl[(long long)ch * wh + loc0 + lane] = d;
+      tile[ch * 33 + lane] = d;
+    }
+    s_all += d * d;  // cells past wh hold zeros
+    if (e >= BE) s_nobox += d * d;
+  }
+  __syncthreads();
+  if (prev) {
+    for (int l = warp; l < 32 && loc0 + l < wh; l += 8) {
+      __nv_bfloat16* pv = prev + ((long long)b * wh + loc0 + l) * prev_ld;
+      for (int c2 = lane * 2; c2 < CH; c2 += 64) {
+        if (c2 + 1 < CH) {
+          __nv_bfloat162* q = reinterpret_cast<__nv_bfloat162*>(pv + c2);
+          const float2 f = __bfloat1622float2(*q);
+          *q = __floats2bfloat162_rn(f.x + tile[c2 * 33 + l], f.y + tile[(c2 + 1) * 33 + l]);
+        } else {
+          pv[c2] = __float2bfloat16_rn(__bfloat162float(pv[c2]) + tile[c2 * 33 + l]);
+        }
+      }
+    }
+  }
+  __shared__ float sh[2][8];
+  for (int off = 16; off; off >>= 1) {
+    s_all += __shfl_xor_sync(0xffffffffu, s_all, off);
+    s_nobox += __shfl_xor_sync(0xffffffffu, s_nobox, off);
+  }
+  if (lane == 0) { sh[0][warp] = s_all; sh[1][warp] = s_nobox; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0, q = 0;
+    for (int w = 0; w < 8; ++w) { a += sh[0][w]; q += sh[1][w]; }
+    atomicAdd(&p.stats[4], a);
+    atomicAdd(&p.stats[5], q);
+  }
+}
+
 // *(l->cost) (yolo_layer.cpp:735-754)
 __global__ void yolo_loss_cost_kernel(LossParams p) {
   float count = p.stats[1];
@@ -620,8 +689,14 @@ extern "C" int yc_yolo_loss(const yc_yolo_loss_desc* d, const float* out_nchw, c
   YC_LAUNCH_CHECK();
   yolo_loss_truths_kernel<<<n, 32, 0, st>>>(p);
   YC_LAUNCH_CHECK();
-  yolo_loss_finish_kernel<<<grid, 128, 0, st>>>(p, prev_delta ? (__nv_bfloat16*)prev_delta->ptr : nullptr,
-                                                prev_delta ? prev_delta->ldc : 0);
+  const size_t tile_bytes = (size_t)d->anchors * E * 33 * 4 + (size_t)d->anchors * 32 * 4;
+  if (tile_bytes <= 48 * 1024 && (!prev_delta || prev_delta->ldc % 2 == 0)) {
+    yolo_loss_finish_tiled_kernel<<<n * ((h * w + 31) / 32), 256, tile_bytes, st>>>(
+        p, prev_delta ? (__nv_bfloat16*)prev_delta->ptr : nullptr, prev_delta ? prev_delta->ldc : 0);
+  } else {
+    yolo_loss_finish_kernel<<<grid, 128, 0, st>>>(p, prev_delta ? (__nv_bfloat16*)prev_delta->ptr : nullptr,
+                                                  prev_delta ? prev_delta->ldc : 0);
+  }
   YC_LAUNCH_CHECK();
   yolo_loss_cost_kernel<<<1, 1, 0, st>>>(p);
   YC_LAUNCH_CHECK();
