@@ -100,6 +100,56 @@ __device__ __forceinline__ float act_ct(float x) {
   return x;
 }
 
+// Packed fp32x2 arithmetic (sm_100 FFMA2 / FMUL2 / FADD2: one issue slot for two lanes of work).  The mish epilogue is
+// issue-bound (ncu: 66 % of the issue slots, XU pipe 53 %), so two outputs per instruction is what counts.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float a, float b) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+// act(x) for two values; same formulas as act_ct (mish: yc_common.cuh act_mish)
+template <int ACT>
+__device__ __forceinline__ void act_ct2(f32x2 x, float& y0, float& y1) {
+  float x0, x1;
+  unpack2(x, x0, x1);
+  if (ACT == YC_MISH) {
+    const f32x2 two = pack2(2.f, 2.f);
+    const f32x2 a = mul2(pack2(fminf(x0, 20.f), fminf(x1, 20.f)), pack2(1.4426950408889634f, 1.4426950408889634f));
+    float a0, a1;
+    unpack2(a, a0, a1);
+    const f32x2 n = pack2(ex2_ftz(a0), ex2_ftz(a1));
+    const f32x2 t = mul2(n, add2(n, two));
+    float q0, q1;
+    unpack2(add2(t, two), q0, q1);
+    unpack2(mul2(x, mul2(t, pack2(rcp_ftz(q0), rcp_ftz(q1)))), y0, y1);
+  } else if (ACT == YC_LEAKY) {
+    float m0, m1;
+    unpack2(mul2(x, pack2(0.1f, 0.1f)), m0, m1);
+    y0 = fmaxf(x0, m0);
+    y1 = fmaxf(x1, m1);
+  } else {
+    y0 = act_ct<ACT>(x0);
+    y1 = act_ct<ACT>(x1);
+  }
+}
+
 // Epilogue of one warp over all tiles of this CTA.  The warp owns TMEM lane quadrant `quad` (rows) and every
 // second 32-column group (`half`):
 //   tcgen05.ld 32 columns -> *scale + bias -> act -> (+residual -> act2) -> bf16/fp32 -> swizzled smem ->
@@ -180,10 +230,10 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
         const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
         float4 s4 = make_float4(1.f, 1.f, 1.f, 1.f);
         if (p.scale) s4 = __ldg(reinterpret_cast<const float4*>(p.scale + col0 + j));
-        v[j + 0] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 0]), s4.x, b4.x));
-        v[j + 1] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 1]), s4.y, b4.y));
-        v[j + 2] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 2]), s4.z, b4.z));
-        v[j + 3] = act_ct<ACT>(fmaf(__uint_as_float(r[j + 3]), s4.w, b4.w));
+        act_ct2<ACT>(fma2(pack2(__uint_as_float(r[j + 0]), __uint_as_float(r[j + 1])), pack2(s4.x, s4.y), pack2(b4.x, b4.y)),
+                     v[j + 0], v[j + 1]);
+        act_ct2<ACT>(fma2(pack2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])), pack2(s4.z, s4.w), pack2(b4.z, b4.w)),
+                     v[j + 2], v[j + 3]);
       }
       if (STATS) {
         // column sums over this warp's 32 rows by a transposing butterfly: 31 shuffles per statistic, after
