@@ -372,6 +372,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
   const bool stem = (flags & YC_NET_STEM_IM2COL) && nl > 0 && Ls[0].type == L_CONV && Ls[0].size > 1 &&
                     Ls[0].dilation == 1 && Ls[0].c * Ls[0].size * Ls[0].size <= 32;
   net->stem = stem;
+  net->stem_pair = false;  // decided once the buffers are placed (needs layer 0's output pitch)
   const int in_ldc = stem ? 32 : round_up(net->c, 8);
   const int in_h = stem ? Ls[0].out_h : net->h, in_w = stem ? Ls[0].out_w : net->w, in_c = stem ? 32 : net->c;
   NET_CUDA(cudaMalloc(&net->input_nhwc, (size_t)net->batch * in_h * in_w * in_ldc * 2));
@@ -383,6 +384,10 @@ extern "C" int yc_network_finalize(yc_network* net) {
     net->finalized = true;
     return YC_OK;
   }
+  if (stem && Ls[0].n % 8 == 0 && 2 * Ls[0].n <= 256 && Ls[0].out_w % 2 == 0 && Ls[0].fused_into < 0 &&
+      view_of(net, 0).ldc == Ls[0].n && view_of(net, 0).dtype == YC_BF16 &&
+      !(getenv("YC_STEM_PAIR") && atoi(getenv("YC_STEM_PAIR")) == 0))
+    net->stem_pair = true;
   // ---- parameters: fuse BN (FuseConvBatchNorm network.cpp:647-682), pack, upload ----------------------
   for (int i = 0; i < nl; ++i) {
     NLayer& L = Ls[i];
@@ -416,21 +421,42 @@ extern "C" int yc_network_finalize(yc_network* net) {
       w.swap(w2);
       pc = 32; ps = 1;
     }
+    int pn = L.n;  // output channels of the packed operand
+    if (stem && i == 0 && net->stem_pair) {
+      // Pixel pairs: the stem operand is read as [N][H][W/2][64] (two pixels' im2col rows = one 128-byte row) and
+      // multiplied by the block-diagonal [2n][64] filter; an output row is then the 2n channels of the same two
+      // pixels, which is exactly their NHWC layout.  Half the tiles, full-width TMA rows (64-byte rows are
+      // request-rate bound), at the price of MMAs on the zero blocks (the layer is nowhere near tensor-bound).
+      std::vector<float> w3((size_t)2 * L.n * 64, 0.f);
+      for (int f = 0; f < L.n; ++f)
+        for (int k = 0; k < 32; ++k) {
+          w3[(size_t)f * 64 + k] = w[(size_t)f * 32 + k];
+          w3[(size_t)(L.n + f) * 64 + 32 + k] = w[(size_t)f * 32 + k];
+        }
+      w.swap(w3);
+      pc = 64; pn = 2 * L.n;
+      b.resize(pn);
+      for (int f = 0; f < L.n; ++f) b[L.n + f] = b[f];
+      if (!sc.empty()) {
+        sc.resize(pn);
+        for (int f = 0; f < L.n; ++f) sc[L.n + f] = sc[f];
+      }
+    }
     float* w_dev = nullptr;
     NET_CUDA(cudaMalloc(&w_dev, w.size() * 4));
     NET_CUDA(cudaMemcpy(w_dev, w.data(), w.size() * 4, cudaMemcpyHostToDevice));
     NET_CUDA(h2d_done());
-    NET_CUDA(cudaMalloc(&L.w_packed, yc_conv_packed_bytes(L.n, pc, ps)));
-    int rc = yc_conv_pack(w_dev, L.n, pc, ps, L.w_packed, net->stream);
+    NET_CUDA(cudaMalloc(&L.w_packed, yc_conv_packed_bytes(pn, pc, ps)));
+    int rc = yc_conv_pack(w_dev, pn, pc, ps, L.w_packed, net->stream);
     if (rc) { cudaFree(w_dev); return rc; }
     NET_CUDA(cudaStreamSynchronize(net->stream));
     NET_CUDA(cudaFree(w_dev));
-    NET_CUDA(cudaMalloc(&L.bias_dev, L.n * 4));
-    NET_CUDA(cudaMemcpy(L.bias_dev, b.data(), L.n * 4, cudaMemcpyHostToDevice));
+    NET_CUDA(cudaMalloc(&L.bias_dev, pn * 4));
+    NET_CUDA(cudaMemcpy(L.bias_dev, b.data(), pn * 4, cudaMemcpyHostToDevice));
     NET_CUDA(h2d_done());
     if (!sc.empty()) {
-      NET_CUDA(cudaMalloc(&L.scale_dev, L.n * 4));
-      NET_CUDA(cudaMemcpy(L.scale_dev, sc.data(), L.n * 4, cudaMemcpyHostToDevice));
+      NET_CUDA(cudaMalloc(&L.scale_dev, pn * 4));
+      NET_CUDA(cudaMemcpy(L.scale_dev, sc.data(), pn * 4, cudaMemcpyHostToDevice));
     NET_CUDA(h2d_done());
     }
   }
@@ -457,6 +483,9 @@ extern "C" int yc_network_finalize(yc_network* net) {
         if (stem && i == 0) { d.ksize = 1; d.stride = 1; d.pad = 0; }
         yc_tensor x = input_view(i);
         yc_tensor y, res;
+        if (stem && i == 0 && net->stem_pair) {  // pixel pairs: [N][H][W/2][64] -> [N][H][W/2][2n]
+          x.w /= 2; x.c = 64; x.ldc = 64;
+        }
         const yc_tensor* resp = nullptr;
         if (L.fused_into >= 0) {
           const NLayer& S = Ls[L.fused_into];
@@ -467,6 +496,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
         } else {
           y = view_of(net, i);
         }
+        if (stem && i == 0 && net->stem_pair) { y.w /= 2; y.c *= 2; y.ldc *= 2; }
         int rc = yc_conv_plan_create(&L.plan, &d, &x, L.w_packed, L.bias_dev, L.scale_dev, resp, &y);
         if (rc) return rc;
         op.kind = 0;

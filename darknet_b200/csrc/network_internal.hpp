@@ -130,6 +130,7 @@ struct yc_network {
   int subdivisions = 1;
   int train_flags = 0;
   bool stem = false;  // layer 0 runs as a 1x1 conv over the 32-column im2col operand built by yc_stem_im2col
+  bool stem_pair = false;  // inference: the stem conv runs on pixel pairs (network.cu)
   void* delta_slab = nullptr;
   size_t delta_slab_bytes = 0;
   float* truth_dev = nullptr;     // [batch][max_boxes*5] (*net->truth_gpu)
