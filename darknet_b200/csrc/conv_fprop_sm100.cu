@@ -39,6 +39,7 @@ struct ConvParams {
   int halo_stages;       // a_mode 2: patch ring depth (2..kHaloMaxStages)
   int halo_pair;         // a_mode 2 + w_resident + one chunk: two tiles' MMAs interleaved into two accumulators
   int Ho, Wo, stride, pad, dil;
+  int kw, stride_w, pad_w;  // kernel width / stride / left padding along W (== ksize / stride / pad unless rectangular)
   const float* bias;   // padded to n_tiles*block_n
   const float* scale;  // same padding, or nullptr
   int y_f32;
@@ -527,11 +528,11 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const int rem = m0 - img * hw;
         const int ho = rem / p.Wo;
         base_h = ho * p.stride - p.pad;
-        base_w = (rem - ho * p.Wo) * p.stride - p.pad;
+        base_w = (rem - ho * p.Wo) * p.stride_w - p.pad_w;
       }
       int kb = 0;
       for (int tap = 0; tap < p.taps; ++tap) {
-        const int r = tap / p.ksize, s = tap - r * p.ksize;
+        const int r = tap / p.kw, s = tap - r * p.kw;
         for (int cc = 0; cc < p.cchunks; ++cc, ++kb) {
           ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * stage_bytes;
@@ -744,16 +745,35 @@ extern "C" int yc_conv_pack(const float* w, int out_c, int in_c, int ksize, void
   return YC_OK;
 }
 
+// kw / stride_w / pad_l / pad_r: kernel width, stride and left / right padding along W when they differ from the
+// square geometry of the descriptor (used by the network for the pixel-pair view of a 3x3 stride-2 layer, see
+// network.cu); the filter is packed [n][ksize*kw][c].
+static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int kw, int stride_w, int pad_l, int pad_r,
+                            const yc_tensor* x, const void* w_packed, const float* bias, const float* scale,
+                            const yc_tensor* residual, const yc_tensor* y);
 extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* d, const yc_tensor* x,
                                    const void* w_packed, const float* bias, const float* scale,
                                    const yc_tensor* residual, const yc_tensor* y) {
+  YC_REQUIRE(d, "yc_conv_plan_create: null argument");
+  return plan_create_impl(out_plan, d, d->ksize, d->stride, d->pad, d->pad, x, w_packed, bias, scale, residual, y);
+}
+extern "C" int yc_conv_plan_create_rect(yc_conv_plan** out_plan, const yc_conv_desc* d, int kw, int stride_w, int pad_l,
+                                        int pad_r, const yc_tensor* x, const void* w_packed, const float* bias,
+                                        const float* scale, const yc_tensor* residual, const yc_tensor* y) {
+  YC_REQUIRE(d && kw >= 1 && stride_w >= 1 && pad_l >= 0 && pad_r >= 0, "yc_conv_plan_create_rect: bad arguments");
+  return plan_create_impl(out_plan, d, kw, stride_w, pad_l, pad_r, x, w_packed, bias, scale, residual, y);
+}
+static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int kw, int stride_w, int pad_l, int pad_r,
+                            const yc_tensor* x, const void* w_packed, const float* bias, const float* scale,
+                            const yc_tensor* residual, const yc_tensor* y) {
   YC_REQUIRE(out_plan && d && x && w_packed && y, "yc_conv_plan_create: null argument");  // bias == NULL: zeros
+  const bool rect = kw != d->ksize || stride_w != d->stride || pad_l != d->pad || pad_r != d->pad;
   YC_REQUIRE(x->dtype == YC_BF16, "conv input must be bf16 NHWC");
   YC_REQUIRE(x->ldc % 8 == 0 && ((uintptr_t)x->ptr & 15) == 0, "conv input view must be 16-byte aligned (ldc%%8)");
   YC_REQUIRE(d->ksize >= 1 && d->stride >= 1 && d->dilation >= 1 && d->pad >= 0, "bad conv geometry");
   const int eff = d->dilation * (d->ksize - 1) + 1;
   const int Ho = (x->h + 2 * d->pad - eff) / d->stride + 1;
-  const int Wo = (x->w + 2 * d->pad - eff) / d->stride + 1;
+  const int Wo = (x->w + pad_l + pad_r - (d->dilation * (kw - 1) + 1)) / stride_w + 1;
   YC_REQUIRE(y->n == x->n && y->h == Ho && y->w == Wo, "conv output shape mismatch: want %dx%d got %dx%d", Ho, Wo,
              y->h, y->w);
   const int elt = y->dtype == YC_F32 ? 4 : 8;  // store granularity in elements (16 bytes)
@@ -775,12 +795,13 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
   // columns we may write: up to the padded pitch when the tensor owns its pitch, else exactly c
   p.n_store = std::min(round_up(N, elt), (int)y->ldc);
   YC_REQUIRE(p.n_store % elt == 0, "output channel count must be a multiple of %d for this view", elt);
-  p.taps = d->ksize * d->ksize;
+  p.taps = d->ksize * kw;
   p.ksize = d->ksize;
+  p.kw = kw; p.stride_w = stride_w; p.pad_w = pad_l;
   p.block_k = pick_block_k(x->c);
   const int in_c_p = round_up(x->c, p.block_k);
   p.cchunks = in_c_p / p.block_k;
-  p.a_mode = (d->ksize == 1 && d->stride == 1 && d->pad == 0) ? 0 : 1;
+  p.a_mode = (!rect && d->ksize == 1 && d->stride == 1 && d->pad == 0) ? 0 : 1;
   p.Ho = Ho; p.Wo = Wo; p.stride = d->stride; p.pad = d->pad; p.dil = d->dilation;
   p.m_tiles = ceil_div(p.M, kBlockM);
   p.tiles_h = p.tiles_w = 0;
@@ -790,7 +811,7 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
     // (when legal), unset: cost rule.
     const char* env = getenv("YC_CONV_HALO");
     const int mode = env ? atoi(env) : -1;
-    const bool legal = d->ksize == 3 && d->stride == 1 && d->pad == 1 && d->dilation == 1 && x->c % 32 == 0;
+    const bool legal = !rect && d->ksize == 3 && d->stride == 1 && d->pad == 1 && d->dilation == 1 && x->c % 32 == 0;
     const int th = ceil_div(Ho, kHaloH), tw = ceil_div(Wo, kHaloW);
     const double waste = (double)x->n * th * tw * kBlockM / (double)p.M;
     const bool want = mode == 1 || (mode < 0 && N <= 128 && waste <= 1.12);
@@ -904,9 +925,9 @@ extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* 
     cuuint64_t strides[3] = {(cuuint64_t)x->ldc * 2, (cuuint64_t)x->ldc * 2 * x->w,
                              (cuuint64_t)x->ldc * 2 * x->w * x->h};
     // base-pixel bounding box (fprop): lower = -pad, upper = pad - (k-1)*dilation  (relative to W-1/H-1)
-    int lower[2] = {-d->pad, -d->pad};
-    int upper[2] = {d->pad - (d->ksize - 1) * d->dilation, d->pad - (d->ksize - 1) * d->dilation};
-    cuuint32_t estr[4] = {1, (cuuint32_t)d->stride, (cuuint32_t)d->stride, 1};
+    int lower[2] = {-pad_l, -d->pad};
+    int upper[2] = {pad_r - (kw - 1) * d->dilation, d->pad - (d->ksize - 1) * d->dilation};
+    cuuint32_t estr[4] = {1, (cuuint32_t)stride_w, (cuuint32_t)d->stride, 1};
     cr = g_encode_im2col(&pl->tmap_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, x->ptr, dims, strides, lower, upper,
                          (cuuint32_t)p.block_k, (cuuint32_t)kBlockM, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

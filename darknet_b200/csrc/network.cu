@@ -421,6 +421,28 @@ extern "C" int yc_network_finalize(yc_network* net) {
       w.swap(w2);
       pc = 32; ps = 1;
     }
+    // 3x3 stride-2 pad-1 conv of 32 dense channels (layer 1 of the YOLO backbones): read the input as pixel pairs
+    // [N][H][W/2][64].  Output column wo needs input columns 2wo-1, 2wo, 2wo+1 = the second half of pair wo-1 and both
+    // halves of pair wo: a 3x2 kernel over pairs, stride 1 / left pad 1 along W, with zero weights for the unused
+    // half.  6 TMA loads of 128-byte rows per tile instead of 9 of 64-byte rows (the request rate bounds this layer).
+    L.pair_s2 = false;
+    if (i > 0 && !(stem && i == 0) && L.size == 3 && L.stride == 2 && L.pad == 1 && L.dilation == 1 && L.c == 32 &&
+        L.w % 2 == 0 && view_of(net, i - 1).ldc == 32 && view_of(net, i - 1).dtype == YC_BF16 &&
+        !(getenv("YC_PAIR_S2") && atoi(getenv("YC_PAIR_S2")) == 0)) {
+      L.pair_s2 = true;
+      std::vector<float> w2((size_t)L.n * 6 * 64, 0.f);  // [n][kh][pw][64]
+      for (int f = 0; f < L.n; ++f)
+        for (int ci = 0; ci < 32; ++ci)
+          for (int kh = 0; kh < 3; ++kh) {
+            const float* src = &w[((size_t)f * 32 + ci) * 9 + kh * 3];
+            float* dst = &w2[((size_t)f * 6 + kh * 2) * 64];
+            dst[32 + ci] = src[0];       // pair wo-1, second pixel  <- kw = 0
+            dst[64 + ci] = src[1];       // pair wo,   first pixel   <- kw = 1
+            dst[64 + 32 + ci] = src[2];  // pair wo,   second pixel  <- kw = 2
+          }
+      w.swap(w2);
+      pc = 6 * 64; ps = 1;  // packs as [n][1][384] == [n][6 taps][64]
+    }
     int pn = L.n;  // output channels of the packed operand
     if (stem && i == 0 && net->stem_pair) {
       // Pixel pairs: the stem operand is read as [N][H][W/2][64] (two pixels' im2col rows = one 128-byte row) and
@@ -497,7 +519,13 @@ extern "C" int yc_network_finalize(yc_network* net) {
           y = view_of(net, i);
         }
         if (stem && i == 0 && net->stem_pair) { y.w /= 2; y.c *= 2; y.ldc *= 2; }
-        int rc = yc_conv_plan_create(&L.plan, &d, &x, L.w_packed, L.bias_dev, L.scale_dev, resp, &y);
+        int rc;
+        if (L.pair_s2) {
+          x.w /= 2; x.c = 64; x.ldc = 64;
+          rc = yc_conv_plan_create_rect(&L.plan, &d, 2, 1, 1, 0, &x, L.w_packed, L.bias_dev, L.scale_dev, resp, &y);
+        } else {
+          rc = yc_conv_plan_create(&L.plan, &d, &x, L.w_packed, L.bias_dev, L.scale_dev, resp, &y);
+        }
         if (rc) return rc;
         op.kind = 0;
         net->ops.push_back(op);

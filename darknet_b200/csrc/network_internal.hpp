@@ -29,6 +29,7 @@ struct NLayer {
   float* bias_dev = nullptr;
   float* scale_dev = nullptr;
   yc_conv_plan* plan = nullptr;
+  bool pair_s2 = false;  // inference: 3x3 stride-2 conv of 32 channels read through the pixel-pair view (network.cu)
   // route / shortcut
   std::vector<int> inputs;
   int groups = 1, group_id = 0;
@@ -155,6 +156,10 @@ inline cudaError_t h2d_done() { return cudaStreamSynchronize(cudaStreamLegacy); 
 int yc_dp_layer_ready(yc_network* net, int layer, cudaStream_t compute);
 int yc_dp_backward_done(yc_network* net, cudaStream_t compute);
 int yc_dp_reduce_pending(yc_network* net, cudaStream_t compute);
+// conv_fprop_sm100.cu: yc_conv_plan_create with a rectangular kernel / stride / padding along W
+extern "C" int yc_conv_plan_create_rect(yc_conv_plan** out_plan, const yc_conv_desc* d, int kw, int stride_w, int pad_l,
+                                        int pad_r, const yc_tensor* x, const void* w_packed, const float* bias,
+                                        const float* scale, const yc_tensor* residual, const yc_tensor* y);
 void yc_dp_free(yc_network* net);
 
 
