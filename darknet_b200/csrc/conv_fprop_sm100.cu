@@ -90,6 +90,8 @@ __device__ __forceinline__ void tile_mn(const ConvParams& p, int t, int& mt, int
   }
 }
 
+constexpr int kActMishSharedRcp = 100;  // internal: mish with one reciprocal per output pair (YC_MISH_RCP2=1)
+
 template <int ACT>
 __device__ __forceinline__ float act_ct(float x) {
   if (ACT == YC_LINEAR) return x;
@@ -130,7 +132,20 @@ template <int ACT>
 __device__ __forceinline__ void act_ct2(f32x2 x, float& y0, float& y1) {
   float x0, x1;
   unpack2(x, x0, x1);
-  if (ACT == YC_MISH) {
+  if (ACT == kActMishSharedRcp) {
+    // mish for two outputs with ONE reciprocal: 1/q0 = q1 * r, 1/q1 = q0 * r, r = 1/(q0 q1).  x is clamped to 20, so
+    // q <= 2.4e17 and q0 q1 <= 5.6e34 stays finite (and r normal) in fp32.  3 MUFU per pair instead of 4.
+    const f32x2 two = pack2(2.f, 2.f);
+    const f32x2 a = mul2(pack2(fminf(x0, 20.f), fminf(x1, 20.f)), pack2(1.4426950408889634f, 1.4426950408889634f));
+    float a0, a1;
+    unpack2(a, a0, a1);
+    const f32x2 n = pack2(ex2_ftz(a0), ex2_ftz(a1));
+    const f32x2 t = mul2(n, add2(n, two));
+    float q0, q1;
+    unpack2(add2(t, two), q0, q1);
+    const float r = rcp_ftz(q0 * q1);
+    unpack2(mul2(mul2(x, t), mul2(pack2(q1, q0), pack2(r, r))), y0, y1);
+  } else if (ACT == YC_MISH) {
     const f32x2 two = pack2(2.f, 2.f);
     const f32x2 a = mul2(pack2(fminf(x0, 20.f), fminf(x1, 20.f)), pack2(1.4426950408889634f, 1.4426950408889634f));
     float a0, a1;
@@ -596,6 +611,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     switch (p.act) {
       case YC_LEAKY: epilogue_role<YC_LEAKY>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
       case YC_MISH: epilogue_role<YC_MISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      case kActMishSharedRcp: epilogue_role<kActMishSharedRcp>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
       case YC_LINEAR: epilogue_role<YC_LINEAR>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
       case YC_LOGISTIC: epilogue_role<YC_LOGISTIC>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
       case YC_SWISH: epilogue_role<YC_SWISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
@@ -873,6 +889,7 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   while (cols < (uint32_t)(p.nacc * p.block_n)) cols <<= 1;
   p.tmem_cols = cols;
   p.act = d->activation;
+  if (p.act == YC_MISH && getenv("YC_MISH_RCP2") && atoi(getenv("YC_MISH_RCP2")) == 1) p.act = kActMishSharedRcp;
   p.act2 = d->residual_activation;
   p.y_f32 = (y->dtype == YC_F32);
   p.chunk = p.y_f32 ? 16 : 32;  // columns per TMA store box: 64-byte rows

@@ -140,6 +140,55 @@ __global__ void stem_im2col_kernel(const float* __restrict__ src, __nv_bfloat16*
   }
 }
 
+// Strip variant for the 3-channel 3x3 stem (every detector cfg), stride 1 or 2: one block = 128 output pixels of one
+// output row.  The three input rows of the three planes are staged in shared memory with coalesced loads (each input
+// element read from global once per output row instead of once per tap), then FOUR lanes build one operand row, 16 bytes
+// each, so that a warp store covers 512 contiguous bytes (the per-pixel kernel above writes 16 bytes at a 64-byte
+// stride per lane: four partial-sector requests per row).  Same values, same rounding: bit-identical operand.
+constexpr int kStemTW = 128, kStemPitch = 260;  // (kStemTW - 1) * 2 + 3 = 257 input columns at stride 2
+__global__ void __launch_bounds__(256) stem_im2col_strip_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                                                                int H, int W, int OH, int OW, int stride, int pad, int strips) {
+  __shared__ float in_s[9 * kStemPitch];  // [ci][kh][iw - iw0]
+  __shared__ int off_s[32];
+  const int strip = blockIdx.x % strips;
+  const int oh = (blockIdx.x / strips) % OH;
+  const long long b = blockIdx.x / ((long long)strips * OH);
+  const int ow0 = strip * kStemTW;
+  const int npix = min(kStemTW, OW - ow0);
+  const int iw0 = ow0 * stride - pad, ih0 = oh * stride - pad;
+  const int ncol = (npix - 1) * stride + 3;
+  const long long plane = (long long)H * W;
+  const float* img = src + b * 3 * plane;
+  if (threadIdx.x < 32) {
+    const int k = threadIdx.x, tap = k / 3, ci = k - tap * 3, kh = tap / 3, kw = tap - kh * 3;
+    off_s[k] = k < 27 ? (ci * 3 + kh) * kStemPitch + kw : -1;
+  }
+  for (int r = 0; r < 9; ++r) {
+    const int ci = r / 3, kh = r - ci * 3, ih = ih0 + kh;
+    const bool row_in = (unsigned)ih < (unsigned)H;
+    const float* rp = img + ci * plane + (long long)ih * W;
+    for (int j = threadIdx.x; j < ncol; j += 256) {
+      const int iw = iw0 + j;
+      in_s[r * kStemPitch + j] = (row_in && (unsigned)iw < (unsigned)W) ? __ldg(rp + iw) : 0.f;
+    }
+  }
+  __syncthreads();
+  __nv_bfloat16* drow = dst + ((b * OH + oh) * OW + ow0) * 32;
+#pragma unroll
+  for (int it = 0; it < kStemTW * 4 / 256; ++it) {
+    const int j = threadIdx.x + it * 256, pix = j >> 2, q = j & 3;
+    if (pix >= npix) break;
+    uint4 o4;
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(&o4);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int off = off_s[q * 8 + e];
+      o[e] = __float2bfloat16(off >= 0 ? in_s[off + pix * stride] : 0.f);
+    }
+    *reinterpret_cast<uint4*>(drow + (long long)pix * 32 + q * 8) = o4;
+  }
+}
+
 // ---- Mat2Image on the device (visualize.cpp:26-54): u8 HWC -> fp32 NCHW in [0,1] ----------------------------------
 // image->data[k*w*h + y*w + x] = data[y*step + x*c + k] / 255.0f; swap_rb folds the preceding cvtColor(RGB2BGR)
 // (yolo_core.cpp:110) by reading channel c-1-k.  thread = pixel: 3 contiguous bytes in, one coalesced store per plane.
@@ -381,7 +430,13 @@ extern "C" int yc_stem_im2col(const float* src, int c, int h, int w, int size, i
   YC_REQUIRE(dst->h == (h + 2 * pad - size) / stride + 1 && dst->w == (w + 2 * pad - size) / stride + 1,
              "yc_stem_im2col: output shape mismatch");
   const long long work = (long long)dst->n * dst->h * dst->w;
-  if (c == 3 && size == 3)
+  if (c == 3 && size == 3 && stride <= 2) {
+    const int strips = ceil_div(dst->w, kStemTW);
+    const long long blocks = (long long)dst->n * dst->h * strips;
+    YC_REQUIRE(blocks < (1ll << 31), "yc_stem_im2col: too many strips");
+    stem_im2col_strip_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst->ptr, h, w, dst->h, dst->w,
+                                                                                 stride, pad, strips);
+  } else if (c == 3 && size == 3)
     stem_im2col_kernel<3, 3><<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst->ptr, dst->n, c, h, w,
                                                                                     dst->h, dst->w, size, stride, pad);
   else

@@ -25,37 +25,58 @@ __device__ __forceinline__ float head_ld(const HeadView& t, long long pix, int c
 // accurate logistic for the head (few elements; feeds thresholds): expf, not __expf
 __device__ __forceinline__ float logistic_acc(float x) { return 1.f / (1.f + expf(-x)); }
 
-// 32 pixels x 32 channels tile through shared memory: coalesced along channels on the NHWC read,
-// coalesced along pixels on the NCHW write.
-__global__ void yolo_decode_kernel(HeadView x, float* __restrict__ out, int S, int C, int E, float sxy,
-                                   int gaussian) {
-  __shared__ float tile[32][33];
+// 32 pixels x (up to) 256 channels per block through shared memory: the NHWC read is coalesced along channels (one
+// 128-byte request per warp, eight independent requests per pixel in flight per thread), the NCHW write along
+// pixels.  The tile pitch of 257 words makes both the row-wise stores and the column-wise loads conflict-free.
+// Algorithmic bytes: 4 B read + 4 B written per output (fp32 head); the exact expf and division are kept because
+// the decoded objectness feeds the detection threshold (parity of the detection set with the reference).
+constexpr int kDecPix = 32, kDecCh = 256, kDecPitch = kDecCh + 1;
+__global__ void __launch_bounds__(256) yolo_decode_kernel(HeadView x, float* __restrict__ out, int S, int C, int E,
+                                                          float sxy, int gaussian) {
+  extern __shared__ float tile[];  // [kDecPix][kDecPitch]
   const int b = blockIdx.z;
-  const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int p0 = blockIdx.x * kDecPix, c0 = blockIdx.y * kDecCh;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const float bias = -0.5f * (sxy - 1.f);
-  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-    const int p = p0 + i, c = c0 + threadIdx.x;
-    float v = 0.f;
-    if (p < S && c < C) {
-      v = head_ld(x, (long long)b * S + p, c);
-      const int e = c % E;
-      bool sig, aff;
-      if (gaussian) {  // gaussian_yolo_layer.cpp:497-516: x,sx,y,sy,_,sw,_,sh, obj, classes
-        sig = (e <= 3) || e == 5 || e == 7 || e >= 8;
-        aff = (e == 0) || (e == 2);
-      } else {         // yolo_layer.cpp:399-404
-        sig = (e < 2) || (e >= 4);
-        aff = (e < 2);
-      }
-      if (sig) v = logistic_acc(v);
-      if (aff) v = v * sxy + bias;
+  const int nch = min(kDecCh, C - c0);
+  // which of this lane's eight channels (c0 + lane + 32 k) take the logistic / the scale_x_y affine
+  unsigned sig_mask = 0, aff_mask = 0;
+#pragma unroll
+  for (int k = 0; k < kDecCh / 32; ++k) {
+    const int e = (c0 + lane + 32 * k) % E;
+    bool sig, aff;
+    if (gaussian) {  // gaussian_yolo_layer.cpp:497-516: x,sx,y,sy,_,sw,_,sh, obj, classes
+      sig = (e <= 3) || e == 5 || e == 7 || e >= 8;
+      aff = (e == 0) || (e == 2);
+    } else {         // yolo_layer.cpp:399-404
+      sig = (e < 2) || (e >= 4);
+      aff = (e < 2);
     }
-    tile[i][threadIdx.x] = v;
+    sig_mask |= (unsigned)sig << k;
+    aff_mask |= (unsigned)aff << k;
+  }
+  for (int i = warp; i < kDecPix; i += 8) {
+    const int p = p0 + i;
+    if (p >= S) break;
+    float v[kDecCh / 32];
+#pragma unroll
+    for (int k = 0; k < kDecCh / 32; ++k) {
+      const int c = lane + 32 * k;
+      v[k] = c < nch ? head_ld(x, (long long)b * S + p, c0 + c) : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < kDecCh / 32; ++k) {
+      float y = v[k];
+      if ((sig_mask >> k) & 1u) y = logistic_acc(y);
+      if ((aff_mask >> k) & 1u) y = y * sxy + bias;
+      tile[i * kDecPitch + lane + 32 * k] = y;
+    }
   }
   __syncthreads();
-  for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-    const int c = c0 + i, p = p0 + threadIdx.x;
-    if (c < C && p < S) out[((long long)b * C + c) * S + p] = tile[threadIdx.x][i];
+  const int p = p0 + lane;
+  if (p < S) {
+    float* o = out + ((long long)b * C + c0) * S + p;
+    for (int c = warp; c < nch; c += 8) o[(long long)c * S] = tile[lane * kDecPitch + c];
   }
 }
 
@@ -185,9 +206,10 @@ extern "C" int yc_yolo_decode(const yc_tensor* x, float* out, int anchors, int c
   YC_REQUIRE(x->c == anchors * E, "yc_yolo_decode: channels %d != anchors*(%d+classes)=%d (parser.cpp:323-330)", x->c,
              gaussian ? 9 : 5, anchors * E);
   const int S = x->h * x->w;
-  dim3 grid(ceil_div(S, 32), ceil_div(x->c, 32), x->n), block(32, 8);
+  dim3 grid(ceil_div(S, kDecPix), ceil_div(x->c, kDecCh), x->n), block(256);
   HeadView hv{x->ptr, x->ldc, x->dtype == YC_F32};
-  yolo_decode_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(hv, out, S, x->c, E, sxy, gaussian);
+  yolo_decode_kernel<<<grid, block, kDecPix * kDecPitch * sizeof(float), (cudaStream_t)stream>>>(hv, out, S, x->c, E, sxy,
+                                                                                               gaussian);
   YC_LAUNCH_CHECK();
   return YC_OK;
 }
