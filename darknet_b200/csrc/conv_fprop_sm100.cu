@@ -90,8 +90,6 @@ __device__ __forceinline__ void tile_mn(const ConvParams& p, int t, int& mt, int
   }
 }
 
-constexpr int kActMishSharedRcp = 100;  // internal: mish with one reciprocal per output pair (YC_MISH_RCP2=1)
-
 template <int ACT>
 __device__ __forceinline__ float act_ct(float x) {
   if (ACT == YC_LINEAR) return x;
@@ -132,20 +130,7 @@ template <int ACT>
 __device__ __forceinline__ void act_ct2(f32x2 x, float& y0, float& y1) {
   float x0, x1;
   unpack2(x, x0, x1);
-  if (ACT == kActMishSharedRcp) {
-    // mish for two outputs with ONE reciprocal: 1/q0 = q1 * r, 1/q1 = q0 * r, r = 1/(q0 q1).  x is clamped to 20, so
-    // q <= 2.4e17 and q0 q1 <= 5.6e34 stays finite (and r normal) in fp32.  3 MUFU per pair instead of 4.
-    const f32x2 two = pack2(2.f, 2.f);
-    const f32x2 a = mul2(pack2(fminf(x0, 20.f), fminf(x1, 20.f)), pack2(1.4426950408889634f, 1.4426950408889634f));
-    float a0, a1;
-    unpack2(a, a0, a1);
-    const f32x2 n = pack2(ex2_ftz(a0), ex2_ftz(a1));
-    const f32x2 t = mul2(n, add2(n, two));
-    float q0, q1;
-    unpack2(add2(t, two), q0, q1);
-    const float r = rcp_ftz(q0 * q1);
-    unpack2(mul2(mul2(x, t), mul2(pack2(q1, q0), pack2(r, r))), y0, y1);
-  } else if (ACT == YC_MISH) {
+  if (ACT == YC_MISH) {
     const f32x2 two = pack2(2.f, 2.f);
     const f32x2 a = mul2(pack2(fminf(x0, 20.f), fminf(x1, 20.f)), pack2(1.4426950408889634f, 1.4426950408889634f));
     float a0, a1;
@@ -184,6 +169,7 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
   const uint32_t rowoff = (uint32_t)lane * 64u;
   const uint32_t swz = ((rowoff >> 7) & 3u) << 4;  // 64B swizzle: 16-byte chunk index ^= (row / 2) % 4
   const bool has_res = p.res != nullptr;
+  const bool res_coal = has_res && !p.y_f32;
   for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
     if ((it & (p.epi_sets - 1)) != set) continue;
     const int acc = it & (p.nacc - 1);
@@ -224,14 +210,37 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
       const int col0 = n0 + g * 32;
       uint32_t r[32];
       ptx::tmem_ld_32x32b_x32(t_row + g * 32, r);
-      // residual rows are fetched while the TMEM load is in flight
+      // residual rows are fetched while the TMEM load is in flight.  bf16 output: COALESCED — request j covers the
+      // 16-byte chunk (lane & 3) of rows (lane >> 2) + 8 j, i.e. 8 rows x 64 B per instruction instead of 32 different
+      // lines (row-per-lane cost 32 L1 wavefronts per request: +270 us on the 32->64 @304^2 layer with shortcut);
+      // the chunks reach their owner lanes through this warp's staging buffer just before they are added.
       uint4 rq[4];
       if (has_res) {
-        const __nv_bfloat16* rp = p.res + row * p.ldres + col0;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          rq[j] = make_uint4(0, 0, 0, 0);
-          if (row_ok && col0 + j * 8 + 8 <= p.n_store) rq[j] = __ldg(reinterpret_cast<const uint4*>(rp + j * 8));
+        for (int j = 0; j < 4; ++j) rq[j] = make_uint4(0, 0, 0, 0);
+        if (res_coal) {
+          const int rr = lane >> 2, q = lane & 3;
+          if (col0 + q * 8 + 8 <= p.n_store) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              long long grow;
+              bool ok;
+              if (p.a_mode == 2) {
+                const int h = hh0 + j, w = hw0 + rr;
+                ok = h < p.Ho && w < p.Wo;
+                grow = ((long long)hb * p.Ho + h) * p.Wo + w;
+              } else {
+                grow = (long long)row0 + rr + 8 * j;
+                ok = grow < p.M;
+              }
+              if (ok) rq[j] = __ldg(reinterpret_cast<const uint4*>(p.res + grow * p.ldres + col0 + q * 8));
+            }
+          }
+        } else {
+          const __nv_bfloat16* rp = p.res + row * p.ldres + col0;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (row_ok && col0 + j * 8 + 8 <= p.n_store) rq[j] = __ldg(reinterpret_cast<const uint4*>(rp + j * 8));
         }
       }
       ptx::tmem_ld_wait();
@@ -280,6 +289,20 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
         asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(so + 4u * (uint32_t)p.stat_cols), "f"(red[1]) : "memory");
       }
       if (has_res) {
+        if (res_coal) {  // chunk (row r, q) -> lane r, slot q, through the (64B-swizzled) staging buffer
+          if (lane == 0) ptx::tma_store_wait_read<0>();  // this warp's previous store has finished reading `sbuf`
+          __syncwarp();
+          const int rr = lane >> 2, q = lane & 3;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t r = (uint32_t)(rr + 8 * j);
+            ptx::st_shared_v4(sbuf + r * 64u + (((uint32_t)q ^ ((r >> 1) & 3u)) << 4), rq[j].x, rq[j].y, rq[j].z, rq[j].w);
+          }
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 4; ++j) rq[j] = ptx::ld_shared_v4(sbuf + rowoff + (((uint32_t)j * 16u) ^ swz));
+          __syncwarp();  // all lanes have read their rows before the results are staged in the same buffer
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rq[j]);
@@ -611,7 +634,6 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     switch (p.act) {
       case YC_LEAKY: epilogue_role<YC_LEAKY>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
       case YC_MISH: epilogue_role<YC_MISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
-      case kActMishSharedRcp: epilogue_role<kActMishSharedRcp>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
       case YC_LINEAR: epilogue_role<YC_LINEAR>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
       case YC_LOGISTIC: epilogue_role<YC_LOGISTIC>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
       case YC_SWISH: epilogue_role<YC_SWISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
@@ -889,7 +911,6 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   while (cols < (uint32_t)(p.nacc * p.block_n)) cols <<= 1;
   p.tmem_cols = cols;
   p.act = d->activation;
-  if (p.act == YC_MISH && getenv("YC_MISH_RCP2") && atoi(getenv("YC_MISH_RCP2")) == 1) p.act = kActMishSharedRcp;
   p.act2 = d->residual_activation;
   p.y_f32 = (y->dtype == YC_F32);
   p.chunk = p.y_f32 ? 16 : 32;  // columns per TMA store box: 64-byte rows

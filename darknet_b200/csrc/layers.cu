@@ -109,83 +109,51 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, View dst, int
 // CT/ST > 0: channel count and kernel size known at compile time (3, 3 for every detector cfg), so the column -> (tap,
 // channel) split costs nothing; CT = 0: generic.
 template <int CT, int ST>
-__global__ void stem_im2col_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int B, int C_, int H, int W,
-                                   int OH, int OW, int size_, int stride, int pad) {
+__global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int B,
+                                                          int C_, int H, int W, int OH, int OW, int size_, int stride, int pad) {
+  // Each lane builds one 64-byte operand row; written directly that is four 16-byte stores at a 64-byte lane stride
+  // (two partial-sector requests per 32-byte sector at the L2).  The warp's 2 KB go through shared memory instead
+  // (16-byte chunks XOR-swizzled so that both sides are conflict-free) and leave as four 512-byte contiguous stores.
+  __shared__ uint4 tr[256 * 4];
   const int C = CT > 0 ? CT : C_, size = ST > 0 ? ST : size_;
   const long long total = (long long)B * OH * OW;
   const int kk = C * size * size;
   const long long plane = (long long)H * W;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int ow = (int)(i % OW);
-    const int oh = (int)((i / OW) % OH);
-    const long long b = i / ((long long)OW * OH);
-    const float* img = src + b * C * plane;
-    const int ih0 = oh * stride - pad, iw0 = ow * stride - pad;
+  const int lane = threadIdx.x & 31;
+  uint4* wbuf = tr + (threadIdx.x >> 5) * 128;
+  for (long long base = blockIdx.x * (long long)blockDim.x + (threadIdx.x - lane); base < total;
+       base += (long long)gridDim.x * blockDim.x) {
+    const long long i = base + lane;
     uint4 out[4];
     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+    if (i < total) {
+      const int ow = (int)(i % OW);
+      const int oh = (int)((i / OW) % OH);
+      const long long b = i / ((long long)OW * OH);
+      const float* img = src + b * C * plane;
+      const int ih0 = oh * stride - pad, iw0 = ow * stride - pad;
 #pragma unroll
-    for (int k = 0; k < 32; ++k) {
-      float v = 0.f;
-      if (k < kk) {
-        const int tap = k / C, ci = k - tap * C;
-        const int kh = tap / size, kw = tap - kh * size;
-        const int ih = ih0 + kh, iw = iw0 + kw;
-        if ((unsigned)ih < (unsigned)H && (unsigned)iw < (unsigned)W) v = __ldg(img + ci * plane + (long long)ih * W + iw);
+      for (int k = 0; k < 32; ++k) {
+        float v = 0.f;
+        if (k < kk) {
+          const int tap = k / C, ci = k - tap * C;
+          const int kh = tap / size, kw = tap - kh * size;
+          const int ih = ih0 + kh, iw = iw0 + kw;
+          if ((unsigned)ih < (unsigned)H && (unsigned)iw < (unsigned)W) v = __ldg(img + ci * plane + (long long)ih * W + iw);
+        }
+        o[k] = __float2bfloat16(v);
       }
-      o[k] = __float2bfloat16(v);
     }
-    uint4* d = reinterpret_cast<uint4*>(dst + i * 32);
 #pragma unroll
-    for (int q = 0; q < 4; ++q) d[q] = out[q];
-  }
-}
-
-// Strip variant for the 3-channel 3x3 stem (every detector cfg), stride 1 or 2: one block = 128 output pixels of one
-// output row.  The three input rows of the three planes are staged in shared memory with coalesced loads (each input
-// element read from global once per output row instead of once per tap), then FOUR lanes build one operand row, 16 bytes
-// each, so that a warp store covers 512 contiguous bytes (the per-pixel kernel above writes 16 bytes at a 64-byte
-// stride per lane: four partial-sector requests per row).  Same values, same rounding: bit-identical operand.
-constexpr int kStemTW = 128, kStemPitch = 260;  // (kStemTW - 1) * 2 + 3 = 257 input columns at stride 2
-__global__ void __launch_bounds__(256) stem_im2col_strip_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
-                                                                int H, int W, int OH, int OW, int stride, int pad, int strips) {
-  __shared__ float in_s[9 * kStemPitch];  // [ci][kh][iw - iw0]
-  __shared__ int off_s[32];
-  const int strip = blockIdx.x % strips;
-  const int oh = (blockIdx.x / strips) % OH;
-  const long long b = blockIdx.x / ((long long)strips * OH);
-  const int ow0 = strip * kStemTW;
-  const int npix = min(kStemTW, OW - ow0);
-  const int iw0 = ow0 * stride - pad, ih0 = oh * stride - pad;
-  const int ncol = (npix - 1) * stride + 3;
-  const long long plane = (long long)H * W;
-  const float* img = src + b * 3 * plane;
-  if (threadIdx.x < 32) {
-    const int k = threadIdx.x, tap = k / 3, ci = k - tap * 3, kh = tap / 3, kw = tap - kh * 3;
-    off_s[k] = k < 27 ? (ci * 3 + kh) * kStemPitch + kw : -1;
-  }
-  for (int r = 0; r < 9; ++r) {
-    const int ci = r / 3, kh = r - ci * 3, ih = ih0 + kh;
-    const bool row_in = (unsigned)ih < (unsigned)H;
-    const float* rp = img + ci * plane + (long long)ih * W;
-    for (int j = threadIdx.x; j < ncol; j += 256) {
-      const int iw = iw0 + j;
-      in_s[r * kStemPitch + j] = (row_in && (unsigned)iw < (unsigned)W) ? __ldg(rp + iw) : 0.f;
+    for (int q = 0; q < 4; ++q) wbuf[4 * lane + (q ^ ((lane >> 1) & 3))] = out[q];
+    __syncwarp();
+    uint4* d = reinterpret_cast<uint4*>(dst + base * 32);
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int c = lane + 32 * r, pl = c >> 2, q = c & 3;
+      if (base + pl < total) d[c] = wbuf[4 * pl + (q ^ ((pl >> 1) & 3))];
     }
-  }
-  __syncthreads();
-  __nv_bfloat16* drow = dst + ((b * OH + oh) * OW + ow0) * 32;
-#pragma unroll
-  for (int it = 0; it < kStemTW * 4 / 256; ++it) {
-    const int j = threadIdx.x + it * 256, pix = j >> 2, q = j & 3;
-    if (pix >= npix) break;
-    uint4 o4;
-    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(&o4);
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int off = off_s[q * 8 + e];
-      o[e] = __float2bfloat16(off >= 0 ? in_s[off + pix * stride] : 0.f);
-    }
-    *reinterpret_cast<uint4*>(drow + (long long)pix * 32 + q * 8) = o4;
+    __syncwarp();
   }
 }
 
@@ -430,13 +398,7 @@ extern "C" int yc_stem_im2col(const float* src, int c, int h, int w, int size, i
   YC_REQUIRE(dst->h == (h + 2 * pad - size) / stride + 1 && dst->w == (w + 2 * pad - size) / stride + 1,
              "yc_stem_im2col: output shape mismatch");
   const long long work = (long long)dst->n * dst->h * dst->w;
-  if (c == 3 && size == 3 && stride <= 2) {
-    const int strips = ceil_div(dst->w, kStemTW);
-    const long long blocks = (long long)dst->n * dst->h * strips;
-    YC_REQUIRE(blocks < (1ll << 31), "yc_stem_im2col: too many strips");
-    stem_im2col_strip_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst->ptr, h, w, dst->h, dst->w,
-                                                                                 stride, pad, strips);
-  } else if (c == 3 && size == 3)
+  if (c == 3 && size == 3)
     stem_im2col_kernel<3, 3><<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst->ptr, dst->n, c, h, w,
                                                                                     dst->h, dst->w, size, stride, pad);
   else
