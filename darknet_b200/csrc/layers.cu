@@ -157,6 +157,67 @@ __global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restric
   }
 }
 
+// Four output pixels per thread for the usual stem (3 channels, 3x3, stride 1, pad 1, W % 4 == 0): per (channel, kernel
+// row) one aligned float4 plus the two neighbours instead of twelve scalar loads, bounds tests once per row, and the
+// warp's 8 KB of operand rows leave through shared memory as sixteen 512-byte contiguous stores.  Same values and
+// rounding as stem_im2col_kernel: bit-identical operand.
+__global__ void __launch_bounds__(128) stem_im2col_s1x4_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                                                               int B, int H, int W) {
+  __shared__ uint4 tr[4 * 512];  // per warp: 128 pixels x 4 chunks of 16 B, XOR-swizzled within groups of 8 chunks
+  const int lane = threadIdx.x & 31;
+  uint4* wbuf = tr + (threadIdx.x >> 5) * 512;
+  const int wq = W >> 2;
+  const long long total = (long long)B * H * wq, plane = (long long)H * W;
+  for (long long base = blockIdx.x * (long long)blockDim.x + (threadIdx.x - lane); base < total;
+       base += (long long)gridDim.x * blockDim.x) {
+    const long long i = base + lane;
+    if (i < total) {
+      const int ow0 = (int)(i % wq) * 4;
+      const int oh = (int)((i / wq) % H);
+      const long long b = i / ((long long)wq * H);
+      const float* img = src + b * 3 * plane;
+      float v[3][3][6];  // [ci][kh][iw - (ow0 - 1)]
+#pragma unroll
+      for (int ci = 0; ci < 3; ++ci)
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+          const int ih = oh + kh - 1;
+          float4 m = make_float4(0.f, 0.f, 0.f, 0.f);
+          float l = 0.f, r = 0.f;
+          if ((unsigned)ih < (unsigned)H) {
+            const float* rp = img + ci * plane + (long long)ih * W + ow0;
+            m = __ldg(reinterpret_cast<const float4*>(rp));
+            if (ow0 > 0) l = __ldg(rp - 1);
+            if (ow0 + 4 < W) r = __ldg(rp + 4);
+          }
+          v[ci][kh][0] = l; v[ci][kh][1] = m.x; v[ci][kh][2] = m.y; v[ci][kh][3] = m.z; v[ci][kh][4] = m.w; v[ci][kh][5] = r;
+        }
+#pragma unroll
+      for (int px = 0; px < 4; ++px) {
+        uint4 out[4];
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+          const int tap = k / 3, ci = k - tap * 3, kh = tap / 3, kw = tap - kh * 3;
+          o[k] = __float2bfloat16(k < 27 ? v[ci][kh < 3 ? kh : 0][px + kw] : 0.f);
+        }
+        const int P = lane * 4 + px;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) wbuf[8 * (P >> 1) + ((4 * (P & 1) + q) ^ (lane & 7))] = out[q];
+      }
+    }
+    __syncwarp();
+    uint4* d = reinterpret_cast<uint4*>(dst + base * 4 * 32);
+    const long long left = (total - base) * 4;  // pixels this warp may write
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      const int c = lane + 32 * r, P = c >> 2, q = c & 3;
+      if (P < left) d[c] = wbuf[8 * (P >> 1) + ((4 * (P & 1) + q) ^ ((P >> 2) & 7))];
+    }
+    __syncwarp();
+  }
+}
+
 // ---- Mat2Image on the device (visualize.cpp:26-54): u8 HWC -> fp32 NCHW in [0,1] ----------------------------------
 // image->data[k*w*h + y*w + x] = data[y*step + x*c + k] / 255.0f; swap_rb folds the preceding cvtColor(RGB2BGR)
 // (yolo_core.cpp:110) by reading channel c-1-k.  thread = pixel: 3 contiguous bytes in, one coalesced store per plane.
@@ -398,7 +459,9 @@ extern "C" int yc_stem_im2col(const float* src, int c, int h, int w, int size, i
   YC_REQUIRE(dst->h == (h + 2 * pad - size) / stride + 1 && dst->w == (w + 2 * pad - size) / stride + 1,
              "yc_stem_im2col: output shape mismatch");
   const long long work = (long long)dst->n * dst->h * dst->w;
-  if (c == 3 && size == 3)
+  if (c == 3 && size == 3 && stride == 1 && pad == 1 && w % 4 == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0)
+    stem_im2col_s1x4_kernel<<<grid_for((work + 3) / 4, 128), 128, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst->ptr, dst->n, h, w);
+  else if (c == 3 && size == 3)
     stem_im2col_kernel<3, 3><<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst->ptr, dst->n, c, h, w,
                                                                                     dst->h, dst->w, size, stride, pad);
   else

@@ -4,6 +4,8 @@ maxpool is a selection, so the bf16 result must be bit-identical to the oracle's
 (maxpool_layer.cpp:258-288 == maxpool_layer_kernels.cu:58-101).  The stride-1 SPP windows take the
 shared-memory slab kernel (separable row/column maxima); every other geometry the direct kernel.
 """
+import ctypes as C
+
 import numpy as np
 import pytest
 import torch
@@ -79,3 +81,28 @@ def test_yolo_decode_op(gpu, gaussian, H, W, classes, dtype):
     xd = ops.to_nhwc(torch.from_numpy(x).to(gpu), dtype=dtype)
     got = ops.yolo_decode(xd, C, n, classes, 1.2, gaussian=gaussian).cpu().numpy()
     assert np.abs(got - ref).max() <= 1e-6
+
+
+@pytest.mark.parametrize("B,H,W,stride", [(2, 16, 20, 1), (3, 13, 12, 1), (1, 7, 44, 1), (2, 9, 10, 1), (2, 16, 16, 2), (1, 13, 11, 2)])
+def test_stem_im2col_operand_bit_exact(gpu, B, H, W, stride):
+    """yc_stem_im2col builds the first conv's GEMM operand from the fp32 NCHW image: row = output pixel, column
+    (kh*3 + kw)*3 + ci, zero padding, columns 27..31 zero, bf16 round-to-nearest.  Stride 1 with W % 4 == 0 takes the
+    four-pixels-per-thread kernel, everything else the per-pixel kernel; both must equal the numpy statement bit for bit
+    (warp tails included: B*H*W is not a multiple of 32 / 128 in most cases)."""
+    from darknet_b200 import lib as L
+    rng = np.random.default_rng(B * 1000 + H * 10 + W)
+    x = rng.standard_normal((B, 3, H, W)).astype(np.float32)
+    OH, OW = (H + 2 - 3) // stride + 1, (W + 2 - 3) // stride + 1
+    xp = np.pad(x, ((0, 0), (0, 0), (1, 1), (1, 1)))
+    ref = np.zeros((B, OH, OW, 32), np.float32)
+    for kh in range(3):
+        for kw in range(3):
+            for ci in range(3):
+                ref[..., (kh * 3 + kw) * 3 + ci] = xp[:, ci, kh:kh + (OH - 1) * stride + 1:stride, kw:kw + (OW - 1) * stride + 1:stride]
+    ref = _bf16_round(ref)
+    xd = torch.from_numpy(x).to(gpu)
+    out = torch.full((B, OH, OW, 32), 7.0, device=gpu, dtype=torch.bfloat16)
+    t = L.view(out, B, OH, OW, 32)
+    L.check(L.lib().yc_stem_im2col(xd.data_ptr(), 3, H, W, 3, stride, 1, C.byref(t), L.stream_ptr()), "yc_stem_im2col")
+    torch.cuda.synchronize()
+    assert np.array_equal(out.float().cpu().numpy(), ref)
