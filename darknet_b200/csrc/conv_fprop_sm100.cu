@@ -198,6 +198,36 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
     // this warp's groups: sub, sub+wps, ...
     int last_g = -1;
     for (int g = sub; g < n_groups; g += wps) last_g = g;
+    // Shortcut operand (bf16 output): this warp's 32 rows x 64 B go straight from global into its staging buffer with
+    // 16-byte asynchronous copies, COALESCED (copy j of a lane = chunk (lane & 3) of row (lane >> 2) + 8 j: 8 rows x 64 B
+    // per instruction; a row-per-lane fetch costs 32 L1 wavefronts per request), 64B-swizzled like the output staging,
+    // no registers held.  The first block of a tile is requested BEFORE waiting for the accumulator.
+    auto issue_res = [&](int g) {
+      if (lane == 0) ptx::tma_store_wait_read<0>();  // this warp's previous store has finished reading `sbuf`
+      __syncwarp();
+      const int c0 = n0 + g * 32;
+      const int rr = lane >> 2, q = lane & 3;
+      const bool col_ok = c0 + q * 8 + 8 <= p.n_store;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        long long grow;
+        bool ok;
+        if (p.a_mode == 2) {
+          const int h = hh0 + j, w = hw0 + rr;
+          ok = h < p.Ho && w < p.Wo;
+          grow = ((long long)hb * p.Ho + h) * p.Wo + w;
+        } else {
+          grow = (long long)row0 + rr + 8 * j;
+          ok = grow < p.M;
+        }
+        ok = ok && col_ok;
+        const uint32_t r = (uint32_t)(rr + 8 * j);
+        ptx::cp_async_16(sbuf + r * 64u + (((uint32_t)q ^ ((r >> 1) & 3u)) << 4),
+                         ok ? (const void*)(p.res + grow * p.ldres + c0 + q * 8) : (const void*)p.res, ok ? 16u : 0u);
+      }
+      ptx::cp_async_commit();
+    };
+    if (res_coal && last_g >= 0) issue_res(sub);
     ptx::mbar_wait(tfull0 + 8u * acc, acc_phase);
     ptx::tc_fence_after();
     if (last_g < 0) {  // nothing to do in this tile: still hand the accumulator back
@@ -208,39 +238,18 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
     }
     for (int g = sub; g < n_groups; g += wps) {
       const int col0 = n0 + g * 32;
+      if (res_coal && g != sub) issue_res(g);
       uint32_t r[32];
       ptx::tmem_ld_32x32b_x32(t_row + g * 32, r);
-      // residual rows are fetched while the TMEM load is in flight.  bf16 output: COALESCED — request j covers the
-      // 16-byte chunk (lane & 3) of rows (lane >> 2) + 8 j, i.e. 8 rows x 64 B per instruction instead of 32 different
-      // lines (row-per-lane cost 32 L1 wavefronts per request: +270 us on the 32->64 @304^2 layer with shortcut);
-      // the chunks reach their owner lanes through this warp's staging buffer just before they are added.
+      // residual rows: bf16 output -> already on their way into this warp's staging buffer (issue_res); fp32 output ->
+      // fetched row-per-lane while the TMEM load is in flight
       uint4 rq[4];
-      if (has_res) {
+      if (has_res && !res_coal) {
+        const __nv_bfloat16* rp = p.res + row * p.ldres + col0;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) rq[j] = make_uint4(0, 0, 0, 0);
-        if (res_coal) {
-          const int rr = lane >> 2, q = lane & 3;
-          if (col0 + q * 8 + 8 <= p.n_store) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              long long grow;
-              bool ok;
-              if (p.a_mode == 2) {
-                const int h = hh0 + j, w = hw0 + rr;
-                ok = h < p.Ho && w < p.Wo;
-                grow = ((long long)hb * p.Ho + h) * p.Wo + w;
-              } else {
-                grow = (long long)row0 + rr + 8 * j;
-                ok = grow < p.M;
-              }
-              if (ok) rq[j] = __ldg(reinterpret_cast<const uint4*>(p.res + grow * p.ldres + col0 + q * 8));
-            }
-          }
-        } else {
-          const __nv_bfloat16* rp = p.res + row * p.ldres + col0;
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (row_ok && col0 + j * 8 + 8 <= p.n_store) rq[j] = __ldg(reinterpret_cast<const uint4*>(rp + j * 8));
+        for (int j = 0; j < 4; ++j) {
+          rq[j] = make_uint4(0, 0, 0, 0);
+          if (row_ok && col0 + j * 8 + 8 <= p.n_store) rq[j] = __ldg(reinterpret_cast<const uint4*>(rp + j * 8));
         }
       }
       ptx::tmem_ld_wait();
@@ -289,15 +298,8 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
         asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(so + 4u * (uint32_t)p.stat_cols), "f"(red[1]) : "memory");
       }
       if (has_res) {
-        if (res_coal) {  // chunk (row r, q) -> lane r, slot q, through the (64B-swizzled) staging buffer
-          if (lane == 0) ptx::tma_store_wait_read<0>();  // this warp's previous store has finished reading `sbuf`
-          __syncwarp();
-          const int rr = lane >> 2, q = lane & 3;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const uint32_t r = (uint32_t)(rr + 8 * j);
-            ptx::st_shared_v4(sbuf + r * 64u + (((uint32_t)q ^ ((r >> 1) & 3u)) << 4), rq[j].x, rq[j].y, rq[j].z, rq[j].w);
-          }
+        if (res_coal) {  // the block staged by issue_res has landed: every lane reads its own row
+          ptx::cp_async_wait_all();
           __syncwarp();
 #pragma unroll
           for (int j = 0; j < 4; ++j) rq[j] = ptx::ld_shared_v4(sbuf + rowoff + (((uint32_t)j * 16u) ^ swz));
