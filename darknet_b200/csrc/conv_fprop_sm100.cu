@@ -130,14 +130,13 @@ template <int ACT>
 __device__ __forceinline__ void act_ct2(f32x2 x, float& y0, float& y1) {
   float x0, x1;
   unpack2(x, x0, x1);
-  if (ACT == YC_MISH) {  // x - 2x/q, q = n(n+2) + 2, n = e^x: 5 packed instructions + 4 MUFU per pair, no clamp
-    const f32x2 two = pack2(2.f, 2.f);
+  if (ACT == YC_MISH) {  // x + x*r, r = 1/(-q/2) (yc_common.cuh act_mish): 4 packed fma + 4 MUFU per pair
     float a0, a1;
-    unpack2(mul2(x, pack2(1.4426950408889634f, 1.4426950408889634f)), a0, a1);
-    const f32x2 n = pack2(ex2_ftz(a0), ex2_ftz(a1));
+    unpack2(fma2(x, pack2(1.4426950408889634f, 1.4426950408889634f), pack2(-1.f, -1.f)), a0, a1);
+    const f32x2 h = pack2(ex2_ftz(a0), ex2_ftz(a1));
     float q0, q1;
-    unpack2(fma2(n, add2(n, two), two), q0, q1);
-    unpack2(fma2(mul2(x, pack2(rcp_ftz(q0), rcp_ftz(q1))), pack2(-2.f, -2.f), x), y0, y1);
+    unpack2(fma2(h, fma2(h, pack2(-2.f, -2.f), pack2(-2.f, -2.f)), pack2(-1.f, -1.f)), q0, q1);
+    unpack2(fma2(x, pack2(rcp_ftz(q0), rcp_ftz(q1)), x), y0, y1);
   } else if (ACT == YC_LEAKY) {
     float m0, m1;
     unpack2(mul2(x, pack2(0.1f, 0.1f)), m0, m1);
@@ -305,12 +304,12 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
         }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rq[j]);
+          const uint32_t w4[4] = {rq[j].x, rq[j].y, rq[j].z, rq[j].w};
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float2 f = __bfloat1622float2(h[e]);
-            v[j * 8 + 2 * e] += f.x;
-            v[j * 8 + 2 * e + 1] += f.y;
+          for (int e = 0; e < 4; ++e) {  // bf16 pair -> fp32 pair (shift / mask), one packed add
+            const int k = j * 8 + 2 * e;
+            unpack2(add2(pack2(v[k], v[k + 1]), pack2(__uint_as_float(w4[e] << 16), __uint_as_float(w4[e] & 0xffff0000u))),
+                    v[k], v[k + 1]);
           }
         }
         if (p.act2 != YC_LINEAR) {

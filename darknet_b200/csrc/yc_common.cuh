@@ -77,12 +77,14 @@ __device__ __forceinline__ float act_logistic(float x) {
 }
 __device__ __forceinline__ float act_mish(float x) {
   // x * tanh(softplus(x)); with n = e^x: tanh(log(1+n)) = n(n+2) / (n(n+2) + 2) = 1 - 2/q, q = n(n+2) + 2, so
-  // mish(x) = x - 2x/q.  No clamp is needed: when n (or q) overflows, 1/q = 0 and the result is x, which is what the
-  // reference's softplus threshold at +20 gives (activations.h:106-113); for x -> -inf, q -> 2 and the result -> 0
-  // (absolute error <= |x| * 2^-24 where the reference has x*e^x: far below one bf16 ulp of any stored value).
-  const float n = ex2_ftz(x * 1.4426950408889634f);
-  const float q = fmaf(n, n + 2.f, 2.f);
-  return fmaf(x * rcp_ftz(q), -2.f, x);
+  // mish(x) = x - 2x/q = x + x*r with r = 1/(-q/2).  Written on h = n/2 = 2^(x*log2e - 1) every step is one fma:
+  // -(n+2) = -2h - 2, -q/2 = h*(-(n+2)) - 1.  No clamp is needed: when h (or q) overflows, r = -0 and the result is
+  // x, which is what the reference's softplus threshold at +20 gives (activations.h:106-113); for x -> -inf, r -> -1
+  // and the result -> 0 (absolute error <= |x| * 2^-23 where the reference has x*e^x: far below one bf16 ulp of any
+  // stored value).
+  const float h = ex2_ftz(fmaf(x, 1.4426950408889634f, -1.f));
+  const float m = fmaf(h, -2.f, -2.f);
+  return fmaf(x, rcp_ftz(fmaf(h, m, -1.f)), x);
 }
 __device__ __forceinline__ float apply_act(float x, int act) {
   switch (act) {
