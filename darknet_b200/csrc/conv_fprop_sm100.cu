@@ -35,6 +35,8 @@ struct ConvParams {
   int m_tiles, n_tiles;
   int a_mode;  // 0: 2-D tiled map (1x1 s1 p0), 1: im2col map, 2: halo patch (3x3 s1 p1, see kHalo*)
   int tiles_h, tiles_w;  // a_mode 2: output tiles of kHaloH x kHaloW pixels per image
+  // exact division of a tile index (< 2^20) by tiles_h*tiles_w and by tiles_w: q = (n * magic) >> shift
+  uint32_t tpi_magic, tpi_shift, tw_magic, tw_shift;
   int w_resident;        // a_mode 2: all 9*cchunks weight slabs stay in shared memory for the whole (persistent) CTA
   int halo_stages;       // a_mode 2: patch ring depth (2..kHaloMaxStages)
   int halo_pair;         // a_mode 2 + w_resident + one chunk: two tiles' MMAs interleaved into two accumulators
@@ -88,6 +90,12 @@ __device__ __forceinline__ void tile_mn(const ConvParams& p, int t, int& mt, int
     mt = t / p.n_tiles;
     nt = t - mt * p.n_tiles;
   }
+}
+
+// n / d for n < 2^20 through the multiplier the host derived from d (set_fastdiv): one wide multiply and a shift
+// instead of the ~20-instruction runtime division (two MUFU among them, on the pipe the mish epilogue lives on).
+__device__ __forceinline__ int fastdiv(int n, uint32_t magic, uint32_t shift) {
+  return (int)(((unsigned long long)(uint32_t)n * magic) >> shift);
 }
 
 template <int ACT>
@@ -181,10 +189,11 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
     int hb = 0, hw0 = 0, hh0 = 0;  // halo mode: image, first column / row of this warp's 4 x 8 pixel block
     if (p.a_mode == 2) {
       const int mt = mt_;
-      hb = mt / (p.tiles_h * p.tiles_w);
+      hb = fastdiv(mt, p.tpi_magic, p.tpi_shift);
       const int rem = mt - hb * (p.tiles_h * p.tiles_w);
-      hh0 = (rem / p.tiles_w) * kHaloH + quad * 4;
-      hw0 = (rem % p.tiles_w) * kHaloW;
+      const int th = fastdiv(rem, p.tw_magic, p.tw_shift);
+      hh0 = th * kHaloH + quad * 4;
+      hw0 = (rem - th * p.tiles_w) * kHaloW;
       const int h = hh0 + (lane >> 3), w = hw0 + (lane & 7);
       row_ok = h < p.Ho && w < p.Wo;
       row = ((long long)hb * p.Ho + h) * p.Wo + w;
@@ -256,15 +265,23 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
         if (lane == 0) ptx::mbar_arrive(tempty0 + 8u * acc);
       }
       float v[32];
+      if (p.scale) {
 #pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-        float4 s4 = make_float4(1.f, 1.f, 1.f, 1.f);
-        if (p.scale) s4 = __ldg(reinterpret_cast<const float4*>(p.scale + col0 + j));
-        act_ct2<ACT>(fma2(pack2(__uint_as_float(r[j + 0]), __uint_as_float(r[j + 1])), pack2(s4.x, s4.y), pack2(b4.x, b4.y)),
-                     v[j + 0], v[j + 1]);
-        act_ct2<ACT>(fma2(pack2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])), pack2(s4.z, s4.w), pack2(b4.z, b4.w)),
-                     v[j + 2], v[j + 3]);
+        for (int j = 0; j < 32; j += 4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+          const float4 s4 = __ldg(reinterpret_cast<const float4*>(p.scale + col0 + j));
+          act_ct2<ACT>(fma2(pack2(__uint_as_float(r[j + 0]), __uint_as_float(r[j + 1])), pack2(s4.x, s4.y), pack2(b4.x, b4.y)),
+                       v[j + 0], v[j + 1]);
+          act_ct2<ACT>(fma2(pack2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])), pack2(s4.z, s4.w), pack2(b4.z, b4.w)),
+                       v[j + 2], v[j + 3]);
+        }
+      } else {  // batchnorm folded into the weights (inference): bias only, no unit scale to materialise
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+          act_ct2<ACT>(add2(pack2(__uint_as_float(r[j + 0]), __uint_as_float(r[j + 1])), pack2(b4.x, b4.y)), v[j + 0], v[j + 1]);
+          act_ct2<ACT>(add2(pack2(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3])), pack2(b4.z, b4.w)), v[j + 2], v[j + 3]);
+        }
       }
       if (STATS) {
         // column sums over this warp's 32 rows by a transposing butterfly: 31 shuffles per statistic, after
@@ -442,9 +459,10 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         for (int j = 0; j < nt; ++j) {
           int mt, ntj_;
           tile_mn(p, tb + j * (int)gridDim.x, mt, ntj_);
-          const int img = mt / tpi;
+          const int img = fastdiv(mt, p.tpi_magic, p.tpi_shift);
           const int rem = mt - img * tpi;
-          const int h0 = (rem / p.tiles_w) * kHaloH, w0 = (rem % p.tiles_w) * kHaloW;
+          const int th = fastdiv(rem, p.tw_magic, p.tw_shift);
+          const int h0 = th * kHaloH, w0 = (rem - th * p.tiles_w) * kHaloW;
           ptx::mbar_wait(pempty_bar(ps), pphase ^ 1u);
           if (leader) {
             ptx::mbar_arrive_expect_tx(pfull_bar(ps), (uint32_t)(kHaloPatchRows * p.block_k * 2));
@@ -852,11 +870,20 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
     const int th = ceil_div(Ho, kHaloH), tw = ceil_div(Wo, kHaloW);
     const double waste = (double)x->n * th * tw * kBlockM / (double)p.M;
     const bool want = mode == 1 || (mode < 0 && N <= 128 && waste <= 1.12);
-    if (legal && want && mode != 0) {
+    if (legal && want && mode != 0 && (long long)x->n * th * tw < (1ll << 20)) {
       p.a_mode = 2;
       p.tiles_h = th;
       p.tiles_w = tw;
       p.m_tiles = x->n * th * tw;
+      // q = (n * magic) >> shift == n / d for every n < 2^20: shift = 20 + ceil(log2 d), magic = ceil(2^shift / d)
+      auto set_fastdiv = [](uint32_t dd, uint32_t& magic, uint32_t& shift) {
+        uint32_t l = 0;
+        while ((1u << l) < dd) ++l;
+        shift = 20 + l;
+        magic = (uint32_t)(((1ull << shift) + dd - 1) / dd);
+      };
+      set_fastdiv((uint32_t)(th * tw), p.tpi_magic, p.tpi_shift);
+      set_fastdiv((uint32_t)tw, p.tw_magic, p.tw_shift);
     }
   }
 
