@@ -170,13 +170,14 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
   const int wps = 4 / p.epi_sets;        // warps of one quadrant working on the same tile
   const int nacc_shift = 31 - __clz(p.nacc);
   const int set = slot / wps, sub = slot - set * wps;
-  int it = 0;
   const uint32_t rowoff = (uint32_t)lane * 64u;
   const uint32_t swz = ((rowoff >> 7) & 3u) << 4;  // 64B swizzle: 16-byte chunk index ^= (row / 2) % 4
   const bool has_res = p.res != nullptr;
   const bool res_coal = has_res && !p.y_f32;
-  for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-    if ((it & (p.epi_sets - 1)) != set) continue;
+  // this warp's set takes every epi_sets-th tile of the CTA: it = set, set + epi_sets, ... (it = index of the tile in
+  // the CTA's sequence, which is what the MMA warp's accumulator rotation counts)
+  const int t_step = (int)gridDim.x * p.epi_sets;
+  for (int t = blockIdx.x + set * (int)gridDim.x, it = set; t < total_tiles; t += t_step, it += p.epi_sets) {
     const int acc = it & (p.nacc - 1);
     const uint32_t acc_phase = (it >> nacc_shift) & 1;
     int mt_, nt_;
