@@ -385,10 +385,14 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   const bool halo = p.a_mode == 2;
   const uint32_t a_bytes = halo ? 0u : kBlockM * p.block_k * 2;           // halo: the ring holds weight slabs only
   const uint32_t b_bytes = ((uint32_t)(p.block_n * p.block_k * 2) + 1023u) & ~1023u;
-  const uint32_t stage_bytes = a_bytes + b_bytes;
-  const uint32_t tx_bytes = a_bytes + (uint32_t)(p.block_n * p.block_k * 2);
+  // tiled / im2col path with resident weights (w_resident, one N tile): the taps*cchunks weight slabs sit behind the
+  // ring (where halo mode keeps its patches), loaded once per CTA; the ring then carries A slabs only
+  const bool wres_t = !halo && p.w_resident;
+  const uint32_t stage_bytes = a_bytes + (wres_t ? 0u : b_bytes);
+  const uint32_t tx_bytes = a_bytes + (wres_t ? 0u : (uint32_t)(p.block_n * p.block_k * 2));
   const uint32_t patch_base = smem_base + p.stages * stage_bytes;         // 1024-aligned; halo: kHaloStages patches
-  const uint32_t out_base = patch_base + (halo ? p.halo_stages * kHaloPatchStride : 0);  // 1024-aligned
+  const uint32_t out_base = patch_base + (halo ? p.halo_stages * kHaloPatchStride
+                                               : (wres_t ? (uint32_t)(p.taps * p.cchunks) * b_bytes : 0u));  // 1024-aligned
   const uint32_t bar_base = out_base + kEpiWarps * kStageOutBytes;        // 8-byte aligned
   // barrier map: full[s] @ +8s, empty[s] @ +8(kMaxStages+s), tmem_full[4], tmem_empty[4], tmem ptr
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
@@ -573,6 +577,12 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     int stage = 0;
     uint32_t phase = 0;
     const int hw = p.Ho * p.Wo;
+    if (wres_t && leader) {  // all weight slabs once (n_tiles == 1): one barrier, never re-armed
+      ptx::mbar_arrive_expect_tx(pfull_bar(0), (uint32_t)k_blocks * (uint32_t)(p.block_n * p.block_k * 2));
+      for (int kb = 0; kb < k_blocks; ++kb)
+        ptx::tma_load_2d(patch_base + kb * b_bytes, &tmap_b, pfull_bar(0), kb * p.block_k, 0);
+    }
+    __syncwarp();
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
       int mt_, nt_;
       tile_mn(p, t, mt_, nt_);
@@ -600,7 +610,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
                                       (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
             else
               ptx::tma_load_2d(sa, &tmap_a, full_bar(stage), cc * p.block_k, m0);
-            ptx::tma_load_2d(sb, &tmap_b, full_bar(stage), kb * p.block_k, n0);
+            if (!wres_t) ptx::tma_load_2d(sb, &tmap_b, full_bar(stage), kb * p.block_k, n0);
           }
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
@@ -617,6 +627,10 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
+    if (wres_t) {
+      ptx::mbar_wait(pfull_bar(0), 0);
+      ptx::tc_fence_after();
+    }
     for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
       const int acc = it & (p.nacc - 1);
       const uint32_t acc_phase = (it >> nacc_shift) & 1;
@@ -628,7 +642,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         ptx::tc_fence_after();
         const uint32_t sa = smem_base + stage * stage_bytes;
         const uint64_t adesc = ptx::make_smem_desc(sa, row_bytes);
-        const uint64_t bdesc = ptx::make_smem_desc(sa + a_bytes, row_bytes);
+        const uint64_t bdesc = ptx::make_smem_desc(wres_t ? patch_base + kb * b_bytes : sa + a_bytes, row_bytes);
         if (leader) {
           for (int k = 0; k < k_steps; ++k) {
             // advancing K by 16 bf16 = 32 bytes inside the swizzle atom: +2 in the (addr>>4) field
@@ -930,6 +944,18 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
     p.stages = 9 * p.cchunks;
   }
   pl->smem = (size_t)p.stages * stage_bytes + out_stage + 1024 + 512;
+  // tiled / im2col path, one N tile, many tiles per CTA, small filter: the weight slabs stay resident behind the ring
+  // (the per-tile reload is a third of the L2 -> SM traffic of the 64-channel layers; YC_W_RES=0 switches it off)
+  const int wres_env = getenv("YC_W_RES") ? atoi(getenv("YC_W_RES")) : 1;  // 0 never, 1 multi-tap layers, 2 also 1x1
+  if (p.a_mode != 2 && p.n_tiles == 1 && (wres_env == 2 || (wres_env == 1 && p.taps > 1))) {
+    const uint32_t wres_bytes = (uint32_t)(p.taps * p.cchunks) * b_bytes;
+    const long long tiles_per_cta = (long long)p.m_tiles / std::max(1, sms);
+    if (wres_bytes <= 64 * 1024 && tiles_per_cta >= 8 && smem_budget >= wres_bytes + 4 * a_bytes) {
+      p.w_resident = 1;
+      p.stages = std::min<int>(kMaxStages, (smem_budget - wres_bytes) / a_bytes);
+      pl->smem = (size_t)p.stages * a_bytes + wres_bytes + out_stage + 1024 + 512;
+    }
+  }
   const int groups = p.block_n / 32;
   p.epi_sets = groups >= 4 ? 1 : (groups >= 2 ? 2 : 4);
   p.nacc = std::max(2, p.epi_sets);
@@ -1124,6 +1150,7 @@ extern "C" int yc_conv_dgrad_plan_create(yc_conv_plan** plan, const yc_conv_desc
 extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq) {
   YC_REQUIRE(pl && ((sum && sumsq) || (!sum && !sumsq)), "yc_conv_plan_set_stats: bad arguments");
   ConvParams& p = pl->p;
+  if (p.a_mode != 2) p.w_resident = 0;  // the ring is re-planned below with weights in every stage
   const uint32_t a_bytes = p.a_mode == 2 ? 0u : kBlockM * p.block_k * 2;
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
   const uint32_t stage_bytes = a_bytes + b_bytes;
