@@ -1,9 +1,12 @@
-# same-box A/B of plan variants selected by environment variables (per-layer tables under gpurun_out/)
 set -u
 mkdir -p gpurun_out
+cp darknet_b200/libyc_b200.so /tmp/new.so
 for i in 1 2; do
-for v in 1 0 2; do
-YC_W_RES=$v timeout 200 python bench.py --layers > gpurun_out/bench_w$v.json 2> gpurun_out/bench_layers_w$v.txt; python -c "import json;d=json.load(open('gpurun_out/bench_w$v.json'));print('W_RES=$v',d['value'],d['ms_per_step'],d['clocks']['sm_mhz'])"
+cp /tmp/new.so darknet_b200/libyc_b200.so
+timeout 200 python bench.py > gpurun_out/bench_new$i.json 2>/dev/null; python -c "import json;d=json.load(open('gpurun_out/bench_new$i.json'));print('new',d['value'],d['ms_per_step'],d['clocks']['sm_mhz'])"
+cp darknet_b200/libyc_b200_prev.so darknet_b200/libyc_b200.so
+timeout 200 python bench.py > gpurun_out/bench_prev$i.json 2>/dev/null; python -c "import json;d=json.load(open('gpurun_out/bench_prev$i.json'));print('prev',d['value'],d['ms_per_step'],d['clocks']['sm_mhz'])"
 done
-done
+cp /tmp/new.so darknet_b200/libyc_b200.so
 timeout 400 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
+timeout 200 python bench.py --mode train > gpurun_out/bench_train_new.json 2>/dev/null; cut -c1-160 gpurun_out/bench_train_new.json
