@@ -375,10 +375,11 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
   if (lane == 0) ptx::tma_store_wait<0>();  // smem must stay valid until the last store has read it
 }
 
-// 576 threads x 112 registers = 64512 of the 65536 in the file (allocation is per warp in units of 8 registers per
-// thread); __launch_bounds__(576, 1) alone makes ptxas stop at 96 and spill the tile-loop state.
+// 96 registers is the ceiling for 576 threads: the register file is allocated to warps in groups of four, so the CTA
+// counts as 640 threads (65536 / 640 = 102 -> 96); a build with __maxnreg__(112) (64512 registers by the per-warp
+// count) fails to launch on B200 ("too many resources requested").
 template <bool STATS>
-__global__ void __maxnreg__(112)
+__global__ void __launch_bounds__(kThreads, 1)
 conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                   const __grid_constant__ CUtensorMap tmap_y, const ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
