@@ -413,6 +413,7 @@ def main():
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     ap.add_argument("--layers", action="store_true", help="print the per-layer time table to stderr")
     ap.add_argument("--quick-exit-after-timed", action="store_true", help="(profiling) skip e2e / roofline / cpu legs")
+    ap.add_argument("--net-flags", default="0", help="(A/B) extra yc_network_load flags in hex, OR'ed onto the default plan")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_train(args) if args.mode == "train" else run_reference(args)
@@ -441,7 +442,7 @@ def main():
     weights = cfgmod.synth_weights(text)
     # sparse-detection regime like a trained detector: spread head logits, objectness bias -6
     cfgmod.shift_head_objectness(text, weights, -6.0, 40.0)
-    flags = L.NET_DEFAULT & ~L.NET_PULL_HEADS
+    flags = (L.NET_DEFAULT & ~L.NET_PULL_HEADS) | int(args.net_flags, 16)
     net = N.LoadSynthetic(text, weights, batch=B, flags=flags)
     del weights
     flops_img = net.flops_per_image()

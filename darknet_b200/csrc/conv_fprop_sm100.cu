@@ -57,6 +57,10 @@ struct ConvParams {
   float* stat_sum;
   float* stat_sq;
   int stat_cols;       // n_tiles * block_n: floats per statistic in the CTA's shared-memory accumulator
+  int out_bufs;        // epilogue staging buffers per warp (1 or 2): with 2 a warp stages block k+1 while the TMA
+                       // engine still reads block k
+  int split_col;       // > 0: output columns >= split_col go to a second tensor (tmap_y2) at column - split_col: two
+                       // 1x1 convolutions that read the same input (the CSP branch pairs) run as ONE GEMM
 };
 
 // ---- halo mode (a_mode 2): 3x3 stride-1 pad-1 convolutions whose A operand is staged ONCE per (tile, 64-channel chunk)
@@ -70,7 +74,7 @@ constexpr int kHaloH = 16, kHaloW = 8, kHaloPitch = 16;  // pitch 10 (exact halo
 constexpr int kHaloPatchRows = (kHaloH + 2) * kHaloPitch;  // 288 pixel rows of block_k*2 bytes (128 B, or 64 B when Cin % 64 != 0)
 constexpr int kHaloPatchStride = kHaloPatchRows * 128;     // ring slot pitch (36864, 1024-byte aligned), sized for 128-byte rows
 constexpr int kHaloMaxStages = 4;
-constexpr int kStageOutBytes = 2048;  // one epilogue staging buffer: 32 rows x 64 B
+constexpr int kStageOutBytes = 2048;  // one epilogue staging buffer: 32 rows x 64 B (a warp owns out_bufs of them, contiguous)
 constexpr int kEpiWarps = 16;         // four per TMEM lane quadrant == four per scheduler: enough to hide ALU/MUFU latency
 constexpr int kMaxAcc = 4;            // TMEM accumulator buffers
 
@@ -162,8 +166,8 @@ __device__ __forceinline__ void act_ct2(f32x2 x, float& y0, float& y1) {
 //   TMA store of a 32-row x 64-byte box (bf16: 32 columns, fp32: 16 columns); M / channel tails are clipped by
 //   the tensor map.  No inter-warp synchronisation: each warp has its own two staging buffers.
 template <int ACT, bool STATS = false>
-__device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtensorMap* tmap_y, uint32_t tmem_base,
-                                              uint32_t tfull0, uint32_t tempty0, uint32_t sbuf, int quad,
+__device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtensorMap* tmap_y, const CUtensorMap* tmap_y2,
+                                              uint32_t tmem_base, uint32_t tfull0, uint32_t tempty0, uint32_t sbuf0, int quad,
                                               int slot, int lane, int total_tiles, uint32_t stat_smem) {
   // Narrow tiles (block_n 32 / 64) have fewer 32-column groups than the four warps of a quadrant: the warps then
   // split into `epi_sets` sets that take alternate tiles, so all sixteen stay busy.
@@ -174,6 +178,19 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
   const uint32_t swz = ((rowoff >> 7) & 3u) << 4;  // 64B swizzle: 16-byte chunk index ^= (row / 2) % 4
   const bool has_res = p.res != nullptr;
   const bool res_coal = has_res && !p.y_f32;
+  // staging buffers: store number `nst` of this warp goes through buffer nst & (out_bufs - 1); before a buffer is
+  // written again at most out_bufs - 1 younger stores may still be reading theirs
+  const bool two_bufs = p.out_bufs == 2;
+  uint32_t nst = 0;
+  uint32_t sbuf = sbuf0;
+  auto wait_buf = [&]() {
+    if (lane == 0) {
+      if (two_bufs) ptx::tma_store_wait_read<1>();
+      else ptx::tma_store_wait_read<0>();
+    }
+    __syncwarp();
+    sbuf = sbuf0 + (two_bufs ? (nst & 1u) * (uint32_t)kStageOutBytes : 0u);
+  };
   // this warp's set takes every epi_sets-th tile of the CTA: it = set, set + epi_sets, ... (it = index of the tile in
   // the CTA's sequence, which is what the MMA warp's accumulator rotation counts)
   const int t_step = (int)gridDim.x * p.epi_sets;
@@ -210,8 +227,7 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
     // per instruction; a row-per-lane fetch costs 32 L1 wavefronts per request), 64B-swizzled like the output staging,
     // no registers held.  The first block of a tile is requested BEFORE waiting for the accumulator.
     auto issue_res = [&](int g) {
-      if (lane == 0) ptx::tma_store_wait_read<0>();  // this warp's previous store has finished reading `sbuf`
-      __syncwarp();
+      wait_buf();  // the store that used this buffer last has finished reading it
       const int c0 = n0 + g * 32;
       const int rr = lane >> 2, q = lane & 3;
       const bool col_ok = c0 + q * 8 + 8 <= p.n_store;
@@ -335,9 +351,12 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
           for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], p.act2);
         }
       }
+      // second output tensor of a fused pair: same rows, columns counted from split_col
+      const bool second = p.split_col > 0 && col0 >= p.split_col;
+      const CUtensorMap* ty = second ? tmap_y2 : tmap_y;
+      const int scol = second ? col0 - p.split_col : col0;
       if (!p.y_f32) {
-        if (lane == 0) ptx::tma_store_wait_read<0>();  // this warp's previous store has finished reading `sbuf`
-        __syncwarp();
+        if (!res_coal) wait_buf();  // (with a staged shortcut operand the buffer is already this block's)
 #pragma unroll
         for (int j = 0; j < 4; ++j)
           ptx::st_shared_v4(sbuf + rowoff + (((uint32_t)j * 16u) ^ swz), pack_bf16x2(v[8 * j], v[8 * j + 1]),
@@ -345,16 +364,18 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
                             pack_bf16x2(v[8 * j + 6], v[8 * j + 7]));
         ptx::fence_proxy_async();  // generic-proxy smem writes -> visible to the TMA engine
         __syncwarp();
-        if (lane == 0 && row0 < p.M) {
-          if (p.a_mode == 2) ptx::tma_store_4d(tmap_y, sbuf, col0, hw0, hh0, hb);
-          else ptx::tma_store_2d(tmap_y, sbuf, col0, row0);
+        if (lane == 0) {  // always commit (possibly an empty group): the buffer rotation counts groups
+          if (row0 < p.M) {
+            if (p.a_mode == 2) ptx::tma_store_4d(ty, sbuf, scol, hw0, hh0, hb);
+            else ptx::tma_store_2d(ty, sbuf, scol, row0);
+          }
           ptx::tma_store_commit();
         }
+        ++nst;
       } else {
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {  // fp32: two boxes of 16 columns
-          if (lane == 0) ptx::tma_store_wait_read<0>();
-          __syncwarp();
+          wait_buf();
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const int e = hh * 16 + j * 4;
@@ -363,11 +384,14 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
           }
           ptx::fence_proxy_async();
           __syncwarp();
-          if (lane == 0 && row0 < p.M && col0 + hh * 16 < p.n_store) {
-            if (p.a_mode == 2) ptx::tma_store_4d(tmap_y, sbuf, col0 + hh * 16, hw0, hh0, hb);
-            else ptx::tma_store_2d(tmap_y, sbuf, col0 + hh * 16, row0);
+          if (lane == 0) {
+            if (row0 < p.M && col0 + hh * 16 < p.n_store) {
+              if (p.a_mode == 2) ptx::tma_store_4d(ty, sbuf, scol + hh * 16, hw0, hh0, hb);
+              else ptx::tma_store_2d(ty, sbuf, scol + hh * 16, row0);
+            }
             ptx::tma_store_commit();
           }
+          ++nst;
         }
       }
     }
@@ -381,7 +405,8 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
 template <bool STATS>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                  const __grid_constant__ CUtensorMap tmap_y, const ConvParams p) {
+                  const __grid_constant__ CUtensorMap tmap_y, const __grid_constant__ CUtensorMap tmap_y2,
+                  const ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment: required by the 128B swizzle atom (8 rows x 128 B)
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -396,7 +421,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   const uint32_t patch_base = smem_base + p.stages * stage_bytes;         // 1024-aligned; halo: kHaloStages patches
   const uint32_t out_base = patch_base + (halo ? p.halo_stages * kHaloPatchStride
                                                : (wres_t ? (uint32_t)(p.taps * p.cchunks) * b_bytes : 0u));  // 1024-aligned
-  const uint32_t bar_base = out_base + kEpiWarps * kStageOutBytes;        // 8-byte aligned
+  const uint32_t bar_base = out_base + kEpiWarps * kStageOutBytes * p.out_bufs;  // 8-byte aligned
   // barrier map: full[s] @ +8s, empty[s] @ +8(kMaxStages+s), tmem_full[4], tmem_empty[4], tmem ptr
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
@@ -418,6 +443,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     ptx::prefetch_tmap(&tmap_a);
     ptx::prefetch_tmap(&tmap_b);
     ptx::prefetch_tmap(&tmap_y);
+    if (p.split_col > 0) ptx::prefetch_tmap(&tmap_y2);
     for (int s = 0; s < p.stages; ++s) {
       ptx::mbar_init(full_bar(s), 1);
       ptx::mbar_init(empty_bar(s), 1);
@@ -661,18 +687,18 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   } else if (warp >= 2) {
     // ===================== epilogue =====================
     const int quad = warp & 3;  // TMEM lane quadrant this warp may access
-    const uint32_t stage_base = out_base + (uint32_t)(warp - 2) * kStageOutBytes;
+    const uint32_t stage_base = out_base + (uint32_t)(warp - 2) * kStageOutBytes * p.out_bufs;
     const int half = (warp - 2) >> 2;  // slot 0..3 within the quadrant
     if (STATS) {
-      epilogue_role<YC_LINEAR, true>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem);
+      epilogue_role<YC_LINEAR, true>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem);
     } else
     switch (p.act) {
-      case YC_LEAKY: epilogue_role<YC_LEAKY>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
-      case YC_MISH: epilogue_role<YC_MISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
-      case YC_LINEAR: epilogue_role<YC_LINEAR>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
-      case YC_LOGISTIC: epilogue_role<YC_LOGISTIC>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
-      case YC_SWISH: epilogue_role<YC_SWISH>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
-      default: epilogue_role<YC_RELU>(p, &tmap_y, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      case YC_LEAKY: epilogue_role<YC_LEAKY>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      case YC_MISH: epilogue_role<YC_MISH>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      case YC_LINEAR: epilogue_role<YC_LINEAR>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      case YC_LOGISTIC: epilogue_role<YC_LOGISTIC>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      case YC_SWISH: epilogue_role<YC_SWISH>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
+      default: epilogue_role<YC_RELU>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
     }
   }
 
@@ -755,7 +781,8 @@ __global__ void dgrad_dilate_kernel(const __nv_bfloat16* __restrict__ dy, int B,
 using namespace yc;
 
 struct yc_conv_plan {
-  CUtensorMap tmap_a, tmap_b, tmap_y;
+  CUtensorMap tmap_a, tmap_b, tmap_y, tmap_y2;
+  bool rect = false;
   ConvParams p;
   float* bias_pad = nullptr;
   float* scale_pad = nullptr;
@@ -820,26 +847,42 @@ extern "C" int yc_conv_pack(const float* w, int out_c, int in_c, int ksize, void
 
 // kw / stride_w / pad_l / pad_r: kernel width, stride and left / right padding along W when they differ from the
 // square geometry of the descriptor (used by the network for the pixel-pair view of a 3x3 stride-2 layer, see
-// network.cu); the filter is packed [n][ksize*kw][c].
+// network.cu); the filter is packed [n][ksize*kw][c].  y2 (optional): second output tensor of a fused pair of
+// convolutions reading the same input — GEMM columns [0, y->c) go to y, [y->c, y->c + y2->c) to y2.
 static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int kw, int stride_w, int pad_l, int pad_r,
                             const yc_tensor* x, const void* w_packed, const float* bias, const float* scale,
-                            const yc_tensor* residual, const yc_tensor* y);
+                            const yc_tensor* residual, const yc_tensor* y, const yc_tensor* y2, unsigned flags);
 extern "C" int yc_conv_plan_create(yc_conv_plan** out_plan, const yc_conv_desc* d, const yc_tensor* x,
                                    const void* w_packed, const float* bias, const float* scale,
                                    const yc_tensor* residual, const yc_tensor* y) {
   YC_REQUIRE(d, "yc_conv_plan_create: null argument");
-  return plan_create_impl(out_plan, d, d->ksize, d->stride, d->pad, d->pad, x, w_packed, bias, scale, residual, y);
+  return plan_create_impl(out_plan, d, d->ksize, d->stride, d->pad, d->pad, x, w_packed, bias, scale, residual, y, nullptr, 0);
+}
+extern "C" int yc_conv_plan_create_ex(yc_conv_plan** out_plan, const yc_conv_desc* d, const yc_tensor* x,
+                                      const void* w_packed, const float* bias, const float* scale,
+                                      const yc_tensor* residual, const yc_tensor* y, const yc_tensor* y2,
+                                      unsigned plan_flags) {
+  YC_REQUIRE(d, "yc_conv_plan_create_ex: null argument");
+  return plan_create_impl(out_plan, d, d->ksize, d->stride, d->pad, d->pad, x, w_packed, bias, scale, residual, y, y2,
+                          plan_flags);
 }
 extern "C" int yc_conv_plan_create_rect(yc_conv_plan** out_plan, const yc_conv_desc* d, int kw, int stride_w, int pad_l,
                                         int pad_r, const yc_tensor* x, const void* w_packed, const float* bias,
-                                        const float* scale, const yc_tensor* residual, const yc_tensor* y) {
+                                        const float* scale, const yc_tensor* residual, const yc_tensor* y,
+                                        unsigned plan_flags) {
   YC_REQUIRE(d && kw >= 1 && stride_w >= 1 && pad_l >= 0 && pad_r >= 0, "yc_conv_plan_create_rect: bad arguments");
-  return plan_create_impl(out_plan, d, kw, stride_w, pad_l, pad_r, x, w_packed, bias, scale, residual, y);
+  return plan_create_impl(out_plan, d, kw, stride_w, pad_l, pad_r, x, w_packed, bias, scale, residual, y, nullptr,
+                          plan_flags);
 }
 static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int kw, int stride_w, int pad_l, int pad_r,
                             const yc_tensor* x, const void* w_packed, const float* bias, const float* scale,
-                            const yc_tensor* residual, const yc_tensor* y) {
+                            const yc_tensor* residual, const yc_tensor* y, const yc_tensor* y2, unsigned flags) {
   YC_REQUIRE(out_plan && d && x && w_packed && y, "yc_conv_plan_create: null argument");  // bias == NULL: zeros
+  if (y2) {
+    YC_REQUIRE(!residual && y2->dtype == y->dtype && y2->n == y->n && y2->h == y->h && y2->w == y->w && y->c % 32 == 0 &&
+                   y2->ldc % (y->dtype == YC_F32 ? 4 : 8) == 0 && ((uintptr_t)y2->ptr & 15) == 0,
+               "fused pair: the second output must have the first one's shape and type, the first a multiple of 32 channels");
+  }
   const bool rect = kw != d->ksize || stride_w != d->stride || pad_l != d->pad || pad_r != d->pad;
   YC_REQUIRE(x->dtype == YC_BF16, "conv input must be bf16 NHWC");
   YC_REQUIRE(x->ldc % 8 == 0 && ((uintptr_t)x->ptr & 15) == 0, "conv input view must be 16-byte aligned (ldc%%8)");
@@ -862,11 +905,13 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
 
   yc_conv_plan* pl = new yc_conv_plan();
   ConvParams& p = pl->p;
-  const int N = y->c;
+  const int N = y->c + (y2 ? y2->c : 0);
   p.M = x->n * Ho * Wo;
   p.N = N;
+  p.split_col = y2 ? y->c : 0;
   // columns we may write: up to the padded pitch when the tensor owns its pitch, else exactly c
-  p.n_store = std::min(round_up(N, elt), (int)y->ldc);
+  const int n_store2 = y2 ? std::min(round_up(y2->c, elt), (int)y2->ldc) : 0;
+  p.n_store = y2 ? y->c + n_store2 : std::min(round_up(N, elt), (int)y->ldc);
   YC_REQUIRE(p.n_store % elt == 0, "output channel count must be a multiple of %d for this view", elt);
   p.taps = d->ksize * kw;
   p.ksize = d->ksize;
@@ -880,11 +925,10 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   p.tiles_h = p.tiles_w = 0;
   {
     // halo mode: 3x3 / stride 1 / pad 1 with whole 64- (or 32-) channel chunks.  It pays where the nine im2col tap loads bound the
-    // layer (few output channels per fetched row) and the 16x8 tiling wastes little: YC_CONV_HALO=0 never, 1 always
-    // (when legal), unset: cost rule.
-    const char* env = getenv("YC_CONV_HALO");
-    const int mode = env ? atoi(env) : -1;
-    const bool legal = !rect && d->ksize == 3 && d->stride == 1 && d->pad == 1 && d->dilation == 1 && x->c % 32 == 0;
+    // layer (few output channels per fetched row) and the 16x8 tiling wastes little: YC_PLAN_NO_HALO never,
+    // YC_PLAN_FORCE_HALO always (when legal), neither: cost rule.
+    const int mode = (flags & YC_PLAN_NO_HALO) ? 0 : ((flags & YC_PLAN_FORCE_HALO) ? 1 : -1);
+    const bool legal = !y2 && !rect && d->ksize == 3 && d->stride == 1 && d->pad == 1 && d->dilation == 1 && x->c % 32 == 0;
     const int th = ceil_div(Ho, kHaloH), tw = ceil_div(Wo, kHaloW);
     const double waste = (double)x->n * th * tw * kBlockM / (double)p.M;
     const bool want = mode == 1 || (mode < 0 && N <= 128 && waste <= 1.12);
@@ -914,8 +958,10 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
     const int nt = ceil_div(N, bn);
     const long long tiles = (long long)p.m_tiles * nt;
     const double waves = (double)ceil_div_ll(tiles, sms);
-    // MMA time ~ bn (cycles per K=16 step: 128*bn/256) ; A-operand smem reads put a floor near bn=128
-    const double per_tile = std::max(bn, 96) + 24.0;
+    // Per-tile cost in units of one K step.  Measured on B200 (profiles/r01_layer_times.txt): a K=16 step of a 128 x 256
+    // tile takes only 1.14x the time of a 128 x 128 one (both are bound by the shared-memory operand reads of the MMA,
+    // 4 KB of A either way), and a 128 x 64 one is no faster than 128 x 128.  COST_V1 is the round-1 model.
+    const double per_tile = (flags & YC_PLAN_COST_V1) ? std::max(bn, 96) + 24.0 : std::max(bn, 192) + 32.0;
     const double cost = waves * per_tile;
     if (cost < best_cost - 1e-9) { best_cost = cost; best_bn = bn; }
   }
@@ -925,17 +971,19 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
   const uint32_t stage_bytes = a_bytes + b_bytes;
   // halo mode: tiles go in pairs (two accumulators, one weight slab for both) when the N tile is shared (n_tiles == 1)
-  // and four patches fit next to at least three weight slabs; YC_HALO_PAIR=0 switches the pairing off
+  // and four patches fit next to at least three weight slabs; YC_PLAN_NO_HALO_PAIR switches the pairing off
   p.halo_stages = 2;
   p.halo_pair = 0;
-  if (p.a_mode == 2 && p.n_tiles == 1 && !(getenv("YC_HALO_PAIR") && atoi(getenv("YC_HALO_PAIR")) == 0)) {
-    const uint32_t need = kEpiWarps * kStageOutBytes + 4 * kHaloPatchStride + 3 * stage_bytes + 1024 + 512;
+  p.out_bufs = (flags & YC_PLAN_ONE_OUT_BUF) ? 1 : 2;
+  const uint32_t out_bytes = kEpiWarps * kStageOutBytes * p.out_bufs;
+  if (p.a_mode == 2 && p.n_tiles == 1 && !(flags & YC_PLAN_NO_HALO_PAIR)) {
+    const uint32_t need = out_bytes + 4 * kHaloPatchStride + 3 * stage_bytes + 1024 + 512;
     if (need <= 227 * 1024) {
       p.halo_stages = 4;
       p.halo_pair = 1;
     }
   }
-  const uint32_t out_stage = kEpiWarps * kStageOutBytes + (p.a_mode == 2 ? p.halo_stages * kHaloPatchStride : 0);
+  const uint32_t out_stage = out_bytes + (p.a_mode == 2 ? p.halo_stages * kHaloPatchStride : 0);
   const uint32_t smem_budget = 227 * 1024 - 1024 /*align slack*/ - 512 /*barriers*/ - out_stage;
   // as deep as shared memory allows: the producer runs ahead across tiles, so the ring depth is the amount of
   // HBM traffic in flight per SM (what the memory-bound 1x1 layers live on)
@@ -948,8 +996,8 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   }
   pl->smem = (size_t)p.stages * stage_bytes + out_stage + 1024 + 512;
   // tiled / im2col path, one N tile, many tiles per CTA, small filter: the weight slabs stay resident behind the ring
-  // (the per-tile reload is a third of the L2 -> SM traffic of the 64-channel layers; YC_W_RES=0 switches it off)
-  const int wres_env = getenv("YC_W_RES") ? atoi(getenv("YC_W_RES")) : 1;  // 0 never, 1 multi-tap layers, 2 also 1x1
+  // (the per-tile reload is a third of the L2 -> SM traffic of the 64-channel layers; YC_PLAN_NO_W_RES switches it off)
+  const int wres_env = (flags & YC_PLAN_NO_W_RES) ? 0 : ((flags & YC_PLAN_W_RES_1X1) ? 2 : 1);  // 0 never, 1 multi-tap layers, 2 also 1x1
   if (p.a_mode != 2 && p.n_tiles == 1 && (wres_env == 2 || (wres_env == 1 && p.taps > 1))) {
     const uint32_t wres_bytes = (uint32_t)(p.taps * p.cchunks) * b_bytes;
     const long long tiles_per_cta = (long long)p.m_tiles / std::max(1, sms);
@@ -1053,29 +1101,33 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
     const int elt_b = p.y_f32 ? 4 : 2;
     const CUtensorMapSwizzle oswz = CU_TENSOR_MAP_SWIZZLE_64B;
     const CUtensorMapDataType odt = p.y_f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-    if (p.a_mode == 2) {
-      // halo mode: a warp's 32 rows are a 4 x 8 pixel block of the image -> box {chunk, 8, 4, 1} over {c, w, h, n};
-      // the staging tile has the same row order (w fastest), clipping at the right / bottom edge is the engine's job
-      cuuint64_t dims[4] = {(cuuint64_t)p.n_store, (cuuint64_t)Wo, (cuuint64_t)Ho, (cuuint64_t)x->n};
-      cuuint64_t strides[3] = {(cuuint64_t)y->ldc * elt_b, (cuuint64_t)y->ldc * elt_b * Wo, (cuuint64_t)y->ldc * elt_b * Wo * Ho};
-      cuuint32_t box[4] = {(cuuint32_t)p.chunk, (cuuint32_t)kHaloW, 4, 1};
-      cuuint32_t estr[4] = {1, 1, 1, 1};
-      cr = g_encode_tiled(&pl->tmap_y, odt, 4, y->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, oswz,
-                          CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    } else {
-    cuuint64_t dims[2] = {(cuuint64_t)p.n_store, (cuuint64_t)p.M};
-    cuuint64_t strides[1] = {(cuuint64_t)y->ldc * elt_b};
-    cuuint32_t box[2] = {(cuuint32_t)p.chunk, 32};
-    cuuint32_t estr[2] = {1, 1};
-    cr = g_encode_tiled(&pl->tmap_y, odt, 2, y->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, oswz,
-                        CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    }
+    auto encode_out = [&](CUtensorMap* tm, const yc_tensor* t, int cols) -> CUresult {
+      if (p.a_mode == 2) {
+        // halo mode: a warp's 32 rows are a 4 x 8 pixel block of the image -> box {chunk, 8, 4, 1} over {c, w, h, n};
+        // the staging tile has the same row order (w fastest), clipping at the right / bottom edge is the engine's job
+        cuuint64_t dims[4] = {(cuuint64_t)cols, (cuuint64_t)Wo, (cuuint64_t)Ho, (cuuint64_t)x->n};
+        cuuint64_t strides[3] = {(cuuint64_t)t->ldc * elt_b, (cuuint64_t)t->ldc * elt_b * Wo, (cuuint64_t)t->ldc * elt_b * Wo * Ho};
+        cuuint32_t box[4] = {(cuuint32_t)p.chunk, (cuuint32_t)kHaloW, 4, 1};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        return g_encode_tiled(tm, odt, 4, t->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, oswz,
+                              CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      }
+      cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)p.M};
+      cuuint64_t strides[1] = {(cuuint64_t)t->ldc * elt_b};
+      cuuint32_t box[2] = {(cuuint32_t)p.chunk, 32};
+      cuuint32_t estr[2] = {1, 1};
+      return g_encode_tiled(tm, odt, 2, t->ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, oswz,
+                            CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    };
+    cr = encode_out(&pl->tmap_y, y, y2 ? y->c : p.n_store);
+    if (cr == CUDA_SUCCESS) cr = y2 ? encode_out(&pl->tmap_y2, y2, n_store2) : (pl->tmap_y2 = pl->tmap_y, CUDA_SUCCESS);
     if (cr != CUDA_SUCCESS) {
       set_error("yc_conv_plan_create: output tensor map encode failed (CUresult %d, c=%d ldc=%d)", (int)cr, p.n_store, y->ldc);
       yc_conv_plan_destroy(pl);
       return YC_ERR_CUDA;
     }
   }
+  pl->rect = rect;
 
   pl->grid = (int)std::min<long long>((long long)p.m_tiles * p.n_tiles, sms);
   static bool attr_set = false;
@@ -1157,7 +1209,7 @@ extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq
   const uint32_t a_bytes = p.a_mode == 2 ? 0u : kBlockM * p.block_k * 2;
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
   const uint32_t stage_bytes = a_bytes + b_bytes;
-  const uint32_t out_stage = kEpiWarps * kStageOutBytes + (p.a_mode == 2 ? p.halo_stages * kHaloPatchStride : 0);
+  const uint32_t out_stage = kEpiWarps * kStageOutBytes * p.out_bufs + (p.a_mode == 2 ? p.halo_stages * kHaloPatchStride : 0);
   p.stat_cols = sum ? p.n_tiles * p.block_n : 0;
   const uint32_t stat_bytes = 2u * 4u * (uint32_t)p.stat_cols;
   const uint32_t smem_budget = 227 * 1024 - 1024 - 512 - out_stage - stat_bytes;
@@ -1185,9 +1237,9 @@ extern "C" int yc_conv_plan_destroy(yc_conv_plan* pl) {
 extern "C" int yc_conv_fprop(const yc_conv_plan* pl, void* stream) {
   YC_REQUIRE(pl, "yc_conv_fprop: null plan");
   if (pl->p.stat_sum)
-    conv_fprop_kernel_t<true><<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->p);
+    conv_fprop_kernel_t<true><<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->tmap_y2, pl->p);
   else
-    conv_fprop_kernel_t<false><<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->p);
+    conv_fprop_kernel_t<false><<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->tmap_y2, pl->p);
   YC_LAUNCH_CHECK();
   return YC_OK;
 }
@@ -1202,6 +1254,9 @@ extern "C" int yc_conv_plan_info(const yc_conv_plan* pl, int what) {
     case 4: return pl->grid;
     case 5: return pl->p.a_mode;
     case 6: return (int)pl->smem;
+    case 7:  // kernel variant: [0,2) a_mode, 4 halo tile pairs, 8 resident weights, 16 two outputs, 32 two staging buffers, 64 rectangular
+      return pl->p.a_mode | (pl->p.halo_pair ? 4 : 0) | (pl->p.w_resident ? 8 : 0) | (pl->p.split_col ? 16 : 0) |
+             (pl->p.out_bufs == 2 ? 32 : 0) | (pl->rect ? 64 : 0);
   }
   return -1;
 }

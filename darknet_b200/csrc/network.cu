@@ -230,6 +230,7 @@ int free_device_state(yc_network* net) {
     if (L.mask_dev) { cudaFree(L.mask_dev); L.mask_dev = nullptr; }
     L.alias = false; L.alias_src = -1; L.alias_coff = 0; L.parent = -1; L.parent_coff = 0;
     L.fused_into = -1; L.fused_conv = -1; L.copies.clear(); L.consumers = 0;
+    L.pair_first = -1; L.pair_second = -1;
   }
   if (net->input_dev) { cudaFree(net->input_dev); net->input_dev = nullptr; }
   if (net->input_pinned) { cudaFreeHost(net->input_pinned); net->input_pinned = nullptr; }
@@ -384,10 +385,34 @@ extern "C" int yc_network_finalize(yc_network* net) {
     net->finalized = true;
     return YC_OK;
   }
+  const unsigned plan_flags = ((unsigned)flags >> YC_NET_PLAN_SHIFT) & 0xffu;
   if (stem && Ls[0].n % 8 == 0 && 2 * Ls[0].n <= 256 && Ls[0].out_w % 2 == 0 && Ls[0].fused_into < 0 &&
-      view_of(net, 0).ldc == Ls[0].n && view_of(net, 0).dtype == YC_BF16 &&
-      !(getenv("YC_STEM_PAIR") && atoi(getenv("YC_STEM_PAIR")) == 0))
+      view_of(net, 0).ldc == Ls[0].n && view_of(net, 0).dtype == YC_BF16 && !(flags & YC_NET_NO_STEM_PAIR))
     net->stem_pair = true;
+  // ---- pairs of 1x1 convolutions that read the same tensor (the two branches of a CSP block: conv, route back,
+  // conv) become ONE GEMM with both filters stacked along out_c: the input is read once and the tile is twice as wide.
+  // The second layer's output is produced when the first one runs (its buffer has no other writer).
+  if (!(flags & YC_NET_NO_PAIR_FUSE)) {
+    auto in_view = [&](int i) { return i == 0 ? yc_tensor{nullptr, 0, 0, 0, 0, 0, 0} : view_of(net, i - 1); };
+    auto eligible = [&](int i) {
+      const NLayer& L = Ls[i];
+      return i > 0 && L.type == L_CONV && L.size == 1 && L.stride == 1 && L.pad == 0 && L.fused_into < 0 &&
+             L.pair_first < 0 && L.pair_second < 0 && view_of(net, i).dtype == YC_BF16;
+    };
+    for (int a = 1; a < nl; ++a) {
+      if (!eligible(a) || Ls[a].n % 32 != 0) continue;
+      const yc_tensor va = in_view(a);
+      for (int b = a + 1; b < std::min(nl, a + 4); ++b) {
+        if (!eligible(b)) continue;
+        const yc_tensor vb = in_view(b);
+        if (vb.ptr != va.ptr || vb.c != va.c || vb.ldc != va.ldc || vb.dtype != va.dtype) continue;
+        if (Ls[b].act != Ls[a].act || Ls[b].bn != Ls[a].bn) continue;
+        Ls[a].pair_second = b;
+        Ls[b].pair_first = a;
+        break;
+      }
+    }
+  }
   // ---- parameters: fuse BN (FuseConvBatchNorm network.cpp:647-682), pack, upload ----------------------
   for (int i = 0; i < nl; ++i) {
     NLayer& L = Ls[i];
@@ -428,7 +453,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
     L.pair_s2 = false;
     if (i > 0 && !(stem && i == 0) && L.size == 3 && L.stride == 2 && L.pad == 1 && L.dilation == 1 && L.c == 32 &&
         L.w % 2 == 0 && view_of(net, i - 1).ldc == 32 && view_of(net, i - 1).dtype == YC_BF16 &&
-        !(getenv("YC_PAIR_S2") && atoi(getenv("YC_PAIR_S2")) == 0)) {
+        !(flags & YC_NET_NO_PAIR_S2)) {
       L.pair_s2 = true;
       std::vector<float> w2((size_t)L.n * 6 * 64, 0.f);  // [n][kh][pw][64]
       for (int f = 0; f < L.n; ++f)
@@ -468,18 +493,30 @@ extern "C" int yc_network_finalize(yc_network* net) {
     NET_CUDA(cudaMalloc(&w_dev, w.size() * 4));
     NET_CUDA(cudaMemcpy(w_dev, w.data(), w.size() * 4, cudaMemcpyHostToDevice));
     NET_CUDA(h2d_done());
-    NET_CUDA(cudaMalloc(&L.w_packed, yc_conv_packed_bytes(pn, pc, ps)));
-    int rc = yc_conv_pack(w_dev, pn, pc, ps, L.w_packed, net->stream);
+    // a fused pair shares the first layer's buffers: [first's rows | second's rows]
+    const int pall = L.pair_second >= 0 ? pn + Ls[L.pair_second].n : pn;
+    void* w_dst;
+    float *b_dst, *s_dst = nullptr;
+    if (L.pair_first >= 0) {
+      NLayer& A = Ls[L.pair_first];
+      w_dst = (char*)A.w_packed + yc_conv_packed_bytes(A.n, pc, ps);
+      b_dst = A.bias_dev + A.n;
+      if (!sc.empty()) s_dst = A.scale_dev + A.n;
+    } else {
+      NET_CUDA(cudaMalloc(&L.w_packed, yc_conv_packed_bytes(pall, pc, ps)));
+      NET_CUDA(cudaMalloc(&L.bias_dev, pall * 4));
+      if (!sc.empty()) NET_CUDA(cudaMalloc(&L.scale_dev, pall * 4));
+      w_dst = L.w_packed; b_dst = L.bias_dev; s_dst = L.scale_dev;
+    }
+    int rc = yc_conv_pack(w_dev, pn, pc, ps, w_dst, net->stream);
     if (rc) { cudaFree(w_dev); return rc; }
     NET_CUDA(cudaStreamSynchronize(net->stream));
     NET_CUDA(cudaFree(w_dev));
-    NET_CUDA(cudaMalloc(&L.bias_dev, pn * 4));
-    NET_CUDA(cudaMemcpy(L.bias_dev, b.data(), pn * 4, cudaMemcpyHostToDevice));
+    NET_CUDA(cudaMemcpy(b_dst, b.data(), pn * 4, cudaMemcpyHostToDevice));
     NET_CUDA(h2d_done());
     if (!sc.empty()) {
-      NET_CUDA(cudaMalloc(&L.scale_dev, pn * 4));
-      NET_CUDA(cudaMemcpy(L.scale_dev, sc.data(), pn * 4, cudaMemcpyHostToDevice));
-    NET_CUDA(h2d_done());
+      NET_CUDA(cudaMemcpy(s_dst, sc.data(), pn * 4, cudaMemcpyHostToDevice));
+      NET_CUDA(h2d_done());
     }
   }
 
@@ -501,6 +538,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
     op.layer = i;
     switch (L.type) {
       case L_CONV: {
+        if (L.pair_first >= 0) break;  // computed by layer pair_first's kernel (second output tensor)
         yc_conv_desc d{L.size, L.stride, L.pad, L.dilation, L.act, YC_LINEAR};
         if (stem && i == 0) { d.ksize = 1; d.stride = 1; d.pad = 0; }
         yc_tensor x = input_view(i);
@@ -522,9 +560,13 @@ extern "C" int yc_network_finalize(yc_network* net) {
         int rc;
         if (L.pair_s2) {
           x.w /= 2; x.c = 64; x.ldc = 64;
-          rc = yc_conv_plan_create_rect(&L.plan, &d, 2, 1, 1, 0, &x, L.w_packed, L.bias_dev, L.scale_dev, resp, &y);
+          rc = yc_conv_plan_create_rect(&L.plan, &d, 2, 1, 1, 0, &x, L.w_packed, L.bias_dev, L.scale_dev, resp, &y,
+                                        plan_flags);
+        } else if (L.pair_second >= 0) {
+          const yc_tensor y2 = view_of(net, L.pair_second);
+          rc = yc_conv_plan_create_ex(&L.plan, &d, &x, L.w_packed, L.bias_dev, L.scale_dev, nullptr, &y, &y2, plan_flags);
         } else {
-          rc = yc_conv_plan_create(&L.plan, &d, &x, L.w_packed, L.bias_dev, L.scale_dev, resp, &y);
+          rc = yc_conv_plan_create_ex(&L.plan, &d, &x, L.w_packed, L.bias_dev, L.scale_dev, resp, &y, nullptr, plan_flags);
         }
         if (rc) return rc;
         op.kind = 0;
@@ -676,6 +718,9 @@ extern "C" int yc_network_layer_info(const yc_network* net, int layer, int what)
     case 10: return L.plan ? yc_conv_plan_info(L.plan, 0) : -1;
     case 11: return L.plan ? yc_conv_plan_info(L.plan, 2) : -1;
     case 12: return L.plan ? yc_conv_plan_info(L.plan, 3) : -1;
+    case 13: return L.plan ? yc_conv_plan_info(L.plan, 7) : (L.pair_first >= 0 ? yc_conv_plan_info(net->layers[L.pair_first].plan, 7) : -1);
+    case 14: return L.pair_first;   // >= 0: this conv is computed by that layer's kernel (fused 1x1 pair)
+    case 15: return L.pair_second;
   }
   return -1;
 }

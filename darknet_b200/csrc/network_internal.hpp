@@ -30,6 +30,8 @@ struct NLayer {
   float* scale_dev = nullptr;
   yc_conv_plan* plan = nullptr;
   bool pair_s2 = false;  // inference: 3x3 stride-2 conv of 32 channels read through the pixel-pair view (network.cu)
+  int pair_first = -1;   // inference: this 1x1 conv is computed by layer pair_first's kernel as its second output
+  int pair_second = -1;  // ... and this one also computes layer pair_second
   // route / shortcut
   std::vector<int> inputs;
   int groups = 1, group_id = 0;
@@ -159,7 +161,8 @@ int yc_dp_reduce_pending(yc_network* net, cudaStream_t compute);
 // conv_fprop_sm100.cu: yc_conv_plan_create with a rectangular kernel / stride / padding along W
 extern "C" int yc_conv_plan_create_rect(yc_conv_plan** out_plan, const yc_conv_desc* d, int kw, int stride_w, int pad_l,
                                         int pad_r, const yc_tensor* x, const void* w_packed, const float* bias,
-                                        const float* scale, const yc_tensor* residual, const yc_tensor* y);
+                                        const float* scale, const yc_tensor* residual, const yc_tensor* y,
+                                        unsigned plan_flags);
 void yc_dp_free(yc_network* net);
 
 

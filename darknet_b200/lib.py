@@ -49,6 +49,10 @@ class Detection(C.Structure):
 
 NET_FUSE_BN, NET_FUSE_SHORTCUT, NET_ELIDE_ROUTE, NET_CUDA_GRAPH, NET_PULL_HEADS, NET_REF_CPU_MAXPOOL = 1, 2, 4, 8, 16, 32
 NET_STEM_IM2COL = 512
+NET_NO_STEM_PAIR, NET_NO_PAIR_S2, NET_NO_PAIR_FUSE, NET_PLAN_SHIFT = 1024, 2048, 4096, 16
+PLAN_NO_HALO, PLAN_FORCE_HALO, PLAN_NO_HALO_PAIR, PLAN_NO_W_RES, PLAN_W_RES_1X1, PLAN_ONE_OUT_BUF, PLAN_COST_V1 = 1, 2, 4, 8, 16, 32, 64
+# every plan switch off: the plainest kernel variant of each layer (parity coverage of the non-default paths)
+NET_PLAIN_PLANS = NET_NO_STEM_PAIR | NET_NO_PAIR_S2 | NET_NO_PAIR_FUSE | ((PLAN_NO_HALO | PLAN_NO_W_RES | PLAN_ONE_OUT_BUF) << NET_PLAN_SHIFT)
 NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
 NET_TRAIN, NET_DGRAD_ACCUMULATE, NET_BN_BIAS_GRAD = 64, 128, 256
 
@@ -80,6 +84,7 @@ _SIGS = {
     "yc_conv_packed_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "yc_conv_pack": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
     "yc_conv_plan_create": (C.c_int, [C.POINTER(_P), C.POINTER(ConvDesc), _TP, _P, _P, _P, _TP, _TP]),
+    "yc_conv_plan_create_ex": (C.c_int, [C.POINTER(_P), C.POINTER(ConvDesc), _TP, _P, _P, _P, _TP, _TP, _TP, C.c_uint]),
     "yc_conv_plan_destroy": (C.c_int, [_P]),
     "yc_conv_fprop": (C.c_int, [_P, _P]),
     "yc_conv_plan_info": (C.c_int, [_P, C.c_int]),

@@ -40,7 +40,9 @@ class Conv:
 
     def __init__(self, x_buf, x_shape, w_oihw, bias, k, stride, pad, act, dil=1, scale=None,
                  out_dtype=torch.bfloat16, residual=None, residual_act="linear", x_ldc=None, x_coff=0,
-                 y_buf=None, y_ldc=None, y_coff=0):
+                 y_buf=None, y_ldc=None, y_coff=0, plan_flags=0, split=None):
+        """split=n1: the filter bank is two layers stacked along out_c ([:n1] and [n1:]) that read the same input; the
+        kernel writes them to two separate tensors (self.y, self.y2) — yc_conv_plan_create_ex's fused pair."""
         lib = L.lib()
         n, h, w, c = x_shape
         out_c = w_oihw.shape[0]
@@ -53,14 +55,20 @@ class Conv:
         self.scale = None if scale is None else scale.contiguous().float().to(dev)
         eff = dil * (k - 1) + 1
         ho, wo = (h + 2 * pad - eff) // stride + 1, (w + 2 * pad - eff) // stride + 1
+        c1 = out_c if split is None else split
         if y_buf is None:
-            y_ldc = _chan_pad(out_c, out_dtype)
+            y_ldc = _chan_pad(c1, out_dtype)
             y_buf = torch.zeros((n, ho, wo, y_ldc), dtype=out_dtype, device=dev)
         self.y = y_buf
         self.out_shape = (n, ho, wo, out_c)
+        y2v = None
+        if split is not None:
+            ld2 = _chan_pad(out_c - split, out_dtype)
+            self.y2 = torch.zeros((n, ho, wo, ld2), dtype=out_dtype, device=dev)
+            y2v = C.byref(L.view(self.y2, n, ho, wo, out_c - split, ld2))
         x_ldc = x_ldc if x_ldc is not None else x_buf.shape[-1]
         xv = L.view(x_buf, n, h, w, c, x_ldc, x_coff)
-        yv = L.view(y_buf, n, ho, wo, out_c, y_ldc, y_coff)
+        yv = L.view(y_buf, n, ho, wo, c1, y_ldc, y_coff)
         rv = None
         if residual is not None:
             self.residual = residual
@@ -68,13 +76,13 @@ class Conv:
         desc = L.ConvDesc(k, stride, pad, dil, L.ACT[act] if isinstance(act, str) else act,
                           L.ACT[residual_act] if isinstance(residual_act, str) else residual_act)
         self.plan = C.c_void_p()
-        L.check(lib.yc_conv_plan_create(C.byref(self.plan), C.byref(desc), C.byref(xv), self.packed.data_ptr(),
-                                        self.bias.data_ptr(), None if self.scale is None else self.scale.data_ptr(),
-                                        rv, C.byref(yv)), "yc_conv_plan_create")
+        L.check(lib.yc_conv_plan_create_ex(C.byref(self.plan), C.byref(desc), C.byref(xv), self.packed.data_ptr(),
+                                           self.bias.data_ptr(), None if self.scale is None else self.scale.data_ptr(),
+                                           rv, C.byref(yv), y2v, plan_flags), "yc_conv_plan_create_ex")
 
     def info(self):
         lib = L.lib()
-        keys = ["block_n", "block_k", "stages", "tiles", "grid", "a_mode", "smem"]
+        keys = ["block_n", "block_k", "stages", "tiles", "grid", "a_mode", "smem", "variant"]
         return {k: lib.yc_conv_plan_info(self.plan, i) for i, k in enumerate(keys)}
 
     def __call__(self):

@@ -115,10 +115,31 @@ YC_API int yc_conv_pack(const float* w_oihw_dev, int out_c, int in_c, int ksize,
 YC_API int yc_conv_plan_create(yc_conv_plan** plan, const yc_conv_desc* desc, const yc_tensor* x,
                         const void* w_packed, const float* bias, const float* scale,
                         const yc_tensor* residual, const yc_tensor* y);
+/* Plan-time switches (yc_conv_plan_create_ex; yc_network_load takes them shifted left by YC_NET_PLAN_SHIFT): 0 = the
+ * measured-best defaults.  They exist for A/B measurements and so that a parity run can cover every kernel variant;
+ * yc_conv_plan_info(plan, 7) reports the variant a plan actually uses. */
+enum {
+  YC_PLAN_NO_HALO = 1,       /* never stage 3x3/s1/p1 inputs as halo patches (nine im2col tap loads instead) */
+  YC_PLAN_FORCE_HALO = 2,    /* halo patches whenever legal, whatever the cost rule says */
+  YC_PLAN_NO_HALO_PAIR = 4,  /* halo mode: one tile at a time instead of tile pairs */
+  YC_PLAN_NO_W_RES = 8,      /* never keep the weight slabs resident in shared memory */
+  YC_PLAN_W_RES_1X1 = 16,    /* keep them resident for 1x1 layers as well */
+  YC_PLAN_ONE_OUT_BUF = 32,  /* one epilogue staging buffer per warp instead of two */
+  YC_PLAN_COST_V1 = 64       /* round-1 tile-width cost model */
+};
+/* [setup] yc_conv_plan_create with plan switches and, optionally, a SECOND output tensor y2: the GEMM then has
+ * y->c + y2->c output channels (weights / bias / scale of both layers concatenated along out_c, y->c a multiple of
+ * 32) and columns >= y->c are stored to y2.  Two 1x1 convolutions that read the same tensor (the two branches of a
+ * CSP block, e.g. yolov4 layers 2 and 4) run as one kernel and read their input once.  residual must be NULL then. */
+YC_API int yc_conv_plan_create_ex(yc_conv_plan** plan, const yc_conv_desc* desc, const yc_tensor* x,
+                           const void* w_packed, const float* bias, const float* scale,
+                           const yc_tensor* residual, const yc_tensor* y, const yc_tensor* y2, unsigned plan_flags);
 YC_API int yc_conv_plan_destroy(yc_conv_plan* plan);
 /* launch (1 kernel). */
 YC_API int yc_conv_fprop(const yc_conv_plan* plan, void* stream);
-/* plan introspection for tests/bench: what=0 block_n, 1 block_k, 2 stages, 3 tiles, 4 grid */
+/* plan introspection for tests/bench: what=0 block_n, 1 block_k, 2 stages, 3 tiles, 4 grid, 5 A-operand mode (0 tiled,
+ * 1 im2col, 2 halo patch), 6 dynamic shared memory bytes, 7 variant bits: [0,2) A mode | 4 halo tile pairs | 8 resident
+ * weights | 16 two outputs | 32 two staging buffers | 64 rectangular (pixel-pair) geometry */
 YC_API int yc_conv_plan_info(const yc_conv_plan* plan, int what);
 
 /* ---- convolution training path: replaces ForwardConvolutionalLayerGpu(train) / BackwardConvolutionalLayerGpu --- */
@@ -292,6 +313,10 @@ enum {
                                 its CPU path leaves it at zero) */
   YC_NET_STEM_IM2COL = 512,  /* inference: a first conv with c*size*size <= 32 reads an im2col operand built by the input
                                 conversion (yc_stem_im2col) and runs as a 1x1 layer */
+  YC_NET_NO_STEM_PAIR = 1024, /* stem conv on single pixels instead of pixel pairs (A/B + parity coverage) */
+  YC_NET_NO_PAIR_S2 = 2048,  /* 3x3 stride-2 32-channel layer on the plain im2col path instead of the pixel-pair view */
+  YC_NET_NO_PAIR_FUSE = 4096, /* do not merge two 1x1 convs that read the same tensor into one GEMM */
+  YC_NET_PLAN_SHIFT = 16,    /* bits [16,24): YC_PLAN_* switches handed to every conv plan */
   YC_NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
 };
 
@@ -311,7 +336,9 @@ YC_API int yc_network_finalize(yc_network* net);
 /* what: 0 n_layers, 1 batch, 2 w, 3 h, 4 c, 5 n_conv, 6 kernels launched per forward, 7 n_yolo */
 YC_API int yc_network_info(const yc_network* net, int what);
 /* per-layer: what: 0 type(0 conv,1 maxpool,2 upsample,3 route,4 shortcut,5 yolo,6 gaussian_yolo) 1 out_c 2 out_h
- * 3 out_w 4 has_output(0 if fused away) 5 in_c 6 size 7 stride 8 activation 9 batch_normalize */
+ * 3 out_w 4 has_output(0 if fused away) 5 in_c 6 size 7 stride 8 activation 9 batch_normalize 10 block_n 11 stages
+ * 12 tiles 13 kernel variant bits (yc_conv_plan_info what=7) 14 layer whose kernel computes this conv (fused 1x1 pair;
+ * -1 = its own) 15 layer this conv's kernel also computes (-1 = none) */
 YC_API int yc_network_layer_info(const yc_network* net, int layer, int what);
 YC_API double yc_network_flops(const yc_network* net);               /* sum 2*nweights*out_h*out_w per image
                                                                         (convolutional_layer.cpp:714) */

@@ -1,0 +1,182 @@
+"""Parity of the BASELINE configs at their OWN shapes against the unmodified reference CPU path (oracle/_ref).
+
+  configs[2] yolov4 608x608 (the headline): every layer at batch 4 (default plan = what bench.py runs, and once with
+             every plan switch off), detections of a 64-image batch through yc_network_detect, sparse and dense heads;
+  configs[1] yolov3 416x416: every layer at batch 4, detections at batch 64;
+  configs[4] Gaussian-yolov3 608x608: every layer at batch 2 + its detections; one training step at 320x320 batch 2
+             (teacher-forced backward against the bf16-emulating walker, which is pinned to the reference in fp32).
+
+Tolerances (north_star): per-layer rel-L2 <= 1e-2 and max-abs <= 2e-2 of the layer's max, free-running through the whole
+network; detections: tests/detutil.py (index identity outside a stated margin band, interval NMS).
+The reference runs one image at a time (its inference path forces batch 1, parser.cpp:1114-1115)."""
+import numpy as np
+import pytest
+
+from darknet_b200 import cfg as cfgmod
+from oracle import pyoracle
+from tests import detutil
+from tests.netutil import materialise, rel_l2, rel_to_max
+
+pytestmark = pytest.mark.gpu
+
+VARIANT_NAMES = {0: "tiled", 1: "im2col", 2: "halo"}
+
+
+def _variants(net):
+    """kernel variant per conv layer, for the record: {variant bits: count}"""
+    out = {}
+    for i in range(net.n):
+        if net.layer_info(i, 0) == 0:
+            v = net.layer_info(i, 13)
+            out[v] = out.get(v, 0) + 1
+    return out
+
+
+def _all_layers(name, B, hw, flags, tol_l2=1e-2, tol_max=2e-2, want=None, **kw):
+    from darknet_b200 import network as N
+    text, cpath, wpath = materialise(name, head_bias=-3.0, head_gain=40.0, w=hw, h=hw, **kw)
+    x = cfgmod.synth_images(B, 3, hw, hw, seed=4321)
+    ref = pyoracle.RefNet(cpath, wpath, train=False, fuse=True)
+    refs = []
+    for b in range(B):
+        ref.predict(x[b:b + 1])
+        refs.append([ref.layer_output(i)[0] for i in range(ref.n)])
+    net = N.LoadNetwork(cpath, wpath, batch=B, flags=flags)
+    N.NetworkPredict(net, x)
+    N.NetworkPredict(net, x)  # the second call replays the CUDA graph
+    variants = _variants(net)
+    if want is not None:
+        want(net, variants)
+    worst, compared = (0, 0.0, 0.0), 0
+    for i in range(net.n):
+        if not net.has_output(i):
+            continue
+        g = net.layer_output(i)
+        for b in range(B):
+            r = refs[b][i]
+            assert g[b].shape == r.shape, (i, g[b].shape, r.shape)
+            e2, em = rel_l2(g[b], r), rel_to_max(g[b], r)
+            if e2 > worst[1]:
+                worst = (i, e2, em)
+            assert e2 < tol_l2 and em < tol_max, f"{name} layer {i} ({net.layer_type(i)}) image {b}: rel-L2 {e2:.3e} rel-max {em:.3e}"
+        compared += 1
+    print(f"{name} {hw}x{hw} batch {B} flags {flags:#x}: {compared} layer outputs compared, worst layer {worst[0]} "
+          f"rel-L2 {worst[1]:.2e} rel-max {worst[2]:.2e}; kernel variants {variants}")
+    ref.close()
+    net.close()
+    return worst
+
+
+def _heads_of(net_or_ref, yolo_layers, outs, classes, gaussian):
+    return [(li, outs[li], 3, classes, gaussian) for li in yolo_layers]
+
+
+def _detections(name, B, hw, thresh, head_bias, head_gain, nms=0.45, dense_images=None, max_undecided=0.25, **kw):
+    """Every image of a batch through yc_network_predict + yc_network_detect against GetNetworkBoxes + NmsSort of the
+    reference run on the same image.  Index identity by tests/detutil.py."""
+    from darknet_b200 import network as N
+    text, cpath, wpath = materialise(name, head_bias=head_bias, head_gain=head_gain, w=hw, h=hw, **kw)
+    x = cfgmod.synth_images(B, 3, hw, hw, seed=99)
+    net = N.LoadNetwork(cpath, wpath, batch=B)
+    N.NetworkPredict(net, x)
+    yl = net.yolo_layers()
+    gaussian = net.layer_info(yl[0], 0) == 6
+    classes = N._classes(net)
+    pre_rows, counts = N.DetectBatch(net, thresh, 0.0)
+    post_rows, counts2 = N.DetectBatch(net, thresh, nms)
+    assert np.array_equal(counts, counts2)
+    ours_heads = {li: N.yolo_output(net, li).copy() for li in yl}
+    ref = pyoracle.RefNet(cpath, wpath, train=False, fuse=True)
+    tot = dict(ref=0, ours=0, common=0, in_band=0, kept=0, undecided=0, suppressed=0)
+    mx = dict(max_dscore=0.0, max_dobj=0.0, max_dxy=0.0, max_dwh_rel=0.0)
+    off = 0
+    images = range(B) if dense_images is None else range(min(B, dense_images))
+    for b in range(B):
+        mine_pre, mine_post = pre_rows[off:off + counts[b]], post_rows[off:off + counts[b]]
+        off += counts[b]
+        if b not in images:
+            continue
+        ref.predict(x[b:b + 1])
+        r7, rprobs = ref.boxes(thresh, 0.0)
+        rheads = [(li, ref.layer_output(li)[0], 3, classes, gaussian) for li in yl]
+        rids, robj = detutil.candidate_ids(rheads, thresh)
+        assert rids.shape[0] == r7.shape[0] and np.array_equal(robj, r7[:, 4]), "reference scan order mismatch"
+        oheads = [(li, ours_heads[li][b], 3, classes, gaussian) for li in yl]
+        oids, oobj = detutil.candidate_ids(oheads, thresh)
+        assert oids.shape[0] == mine_pre.shape[0], (oids.shape, mine_pre.shape)
+        assert np.array_equal(oobj, mine_pre[:, 5]) and np.all(mine_pre[:, 0] == b) and np.array_equal(oids[:, 0], mine_pre[:, 6].astype(np.int32))
+        st = detutil.compare_image(rids, r7[:, :5], rprobs, oids, mine_pre[:, 1:6], mine_pre[:, 7:], mine_post[:, 7:],
+                                   thresh, nms)
+        for k in tot:
+            tot[k] += st.get(k, 0)
+        for k in mx:
+            mx[k] = max(mx[k], st.get(k, 0.0))
+    decided = tot["kept"] + tot["suppressed"] + tot["undecided"]
+    print(f"{name} {hw} batch {B} thresh {thresh} (head bias {head_bias} gain {head_gain}): {len(list(images))} images, "
+          f"{tot}, {({k: round(v, 5) for k, v in mx.items()})}")
+    assert tot["ref"] > 0 and decided > 0, "vacuous: the reference found no detections"
+    assert tot["undecided"] <= max_undecided * decided, f"too many undecided NMS outcomes: {tot}"
+    ref.close()
+    net.close()
+    return tot
+
+
+# ---------------------------------------------------------------- configs[2]: yolov4 608 (the headline) -----------
+def test_yolov4_608_all_layers_default_plan(gpu):
+    from darknet_b200 import lib as L
+
+    def want(net, variants):
+        # the plan bench.py times: stem on pixel pairs, stride-2 pixel-pair layer, halo patches with tile pairs and resident
+        # weights, the five CSP 1x1 pairs fused, 23 shortcuts fused, two staging buffers
+        assert net.layer_info(0, 13) & 3 == 0 and net.layer_info(1, 13) & 64, "stem / pair-s2 variants not selected"
+        assert sum(1 for i in range(net.n) if net.layer_info(i, 14) >= 0) == 5, "the five CSP pairs are not fused"
+        assert any(v & 3 == 2 and v & 4 for v in variants), "no halo tile-pair layer"
+        assert sum(1 for i in range(net.n) if not net.has_output(i)) == 23, "shortcut fusion"
+    _all_layers("yolov4", 4, 608, L.NET_DEFAULT, want=want)
+
+
+def test_yolov4_608_all_layers_plain_plan(gpu):
+    """every plan switch off: plain im2col / tiled kernels, separate shortcut and route-copy kernels, no graph"""
+    from darknet_b200 import lib as L
+    flags = (L.NET_FUSE_BN | L.NET_PULL_HEADS) | L.NET_PLAIN_PLANS
+
+    def want(net, variants):
+        assert all(v & (3 | 4 | 8 | 16 | 32 | 64) in (0, 1) for v in variants), variants
+        assert all(net.has_output(i) for i in range(net.n))
+    _all_layers("yolov4", 2, 608, flags, want=want)
+
+
+def test_yolov4_608_b64_detections_sparse(gpu):
+    _detections("yolov4", 64, 608, 0.25, head_bias=-6.0, head_gain=40.0, max_undecided=0.1)
+
+
+def test_yolov4_608_b64_detections_dense(gpu):
+    """thresh 0.25 on spread heads: hundreds of candidates per image; index identity on every image, interval NMS on 8."""
+    _detections("yolov4", 64, 608, 0.25, head_bias=-3.0, head_gain=40.0, dense_images=8)
+
+
+# ---------------------------------------------------------------- configs[1]: yolov3 416 ---------------------------
+def test_yolov3_416_all_layers(gpu):
+    from darknet_b200 import lib as L
+    _all_layers("yolov3", 4, 416, L.NET_DEFAULT)
+
+
+def test_yolov3_416_b64_detections(gpu):
+    _detections("yolov3", 64, 416, 0.25, head_bias=-5.0, head_gain=40.0, max_undecided=0.1)
+    _detections("yolov3", 64, 416, 0.25, head_bias=-3.0, head_gain=40.0, dense_images=6)
+
+
+# ---------------------------------------------------------------- configs[4]: Gaussian-yolov3 608 ------------------
+def test_gaussian_yolov3_608_all_layers(gpu):
+    from darknet_b200 import lib as L
+    _all_layers("gaussian-yolov3", 2, 608, L.NET_DEFAULT)
+
+
+def test_gaussian_yolov3_608_detections(gpu):
+    _detections("gaussian-yolov3", 4, 608, 0.25, head_bias=-4.0, head_gain=40.0)
+
+
+def test_gaussian_yolov3_320_train_step(gpu):
+    """configs[4] at a size the CPU walker affords: forward free-running, backward teacher-forced (tests/test_train_emul_gpu.py)."""
+    from tests.test_train_emul_gpu import _run
+    _run("gaussian-yolov3", 2, 320, 80, steps=1, w=320, h=320)

@@ -17,7 +17,8 @@ def _bf16_round(a):
     return torch.from_numpy(a).to(torch.bfloat16).float().numpy()
 
 
-def _run(gpu, B, C, H, W, N, k, stride, act, out_f32=False, residual=False, seed=0, scale=False):
+def _run(gpu, B, C, H, W, N, k, stride, act, out_f32=False, residual=False, seed=0, scale=False, plan_flags=0, split=None,
+         want_variant=None):
     from darknet_b200 import ops
     rng = np.random.default_rng(seed)
     pad = k // 2
@@ -35,10 +36,15 @@ def _run(gpu, B, C, H, W, N, k, stride, act, out_f32=False, residual=False, seed
         res_t = ops.to_nhwc(torch.from_numpy(r).to(gpu))
     conv = ops.Conv(xd, (B, H, W, C), torch.from_numpy(w), torch.from_numpy(b), k, stride, pad, act,
                     scale=None if sc is None else torch.from_numpy(sc),
-                    out_dtype=torch.float32 if out_f32 else torch.bfloat16, residual=res_t)
+                    out_dtype=torch.float32 if out_f32 else torch.bfloat16, residual=res_t, plan_flags=plan_flags, split=split)
+    if want_variant is not None:  # (mask, value) on yc_conv_plan_info(plan, 7): the case must cover the path it names
+        assert conv.info()["variant"] & want_variant[0] == want_variant[1], conv.info()
     y = conv()
     torch.cuda.synchronize()
-    got = ops.to_nchw(y, N).cpu().numpy()
+    if split is None:
+        got = ops.to_nchw(y, N).cpu().numpy()
+    else:
+        got = np.concatenate([ops.to_nchw(y, split).cpu().numpy(), ops.to_nchw(conv.y2, N - split).cpu().numpy()], axis=1)
     assert got.shape == ref.shape
     denom = np.abs(ref).max() + 1e-12
     err = np.abs(got - ref).max() / denom
@@ -89,3 +95,26 @@ def test_conv_ragged_rect(gpu):
     _run(gpu, 3, 64, 5, 11, 72, 3, 1, "logistic")
     _run(gpu, 1, 64, 1, 1, 64, 1, 1, "swish")
     _run(gpu, 1, 64, 3, 2, 64, 3, 2, "relu")
+
+
+def test_conv_fused_pair_two_outputs(gpu):
+    """Two 1x1 layers reading the same tensor as one GEMM with two output tensors (yolov4's CSP branch pairs)."""
+    for C, n1, n2, HW in [(64, 64, 64, 24), (128, 64, 64, 19), (256, 128, 128, 19), (512, 256, 256, 13), (64, 32, 40, 9)]:
+        _run(gpu, 2, C, HW, HW, n1 + n2, 1, 1, "mish", split=n1, want_variant=(16, 16))
+    _run(gpu, 2, 128, 10, 10, 64 + 24, 1, 1, "linear", out_f32=True, split=64, want_variant=(16, 16))
+
+
+def test_conv_plan_switches(gpu):
+    """Every plan switch selects the variant it names and stays parity-green (the defaults are covered by the tests above)."""
+    from darknet_b200 import lib as L
+    # halo patches on / off, tile pairs off, weights never resident, one staging buffer, round-1 tile widths
+    _run(gpu, 4, 64, 38, 38, 64, 3, 1, "mish", plan_flags=L.PLAN_FORCE_HALO, want_variant=(3, 2))
+    _run(gpu, 4, 64, 38, 38, 64, 3, 1, "mish", plan_flags=L.PLAN_NO_HALO, want_variant=(3, 1))
+    _run(gpu, 4, 64, 38, 38, 64, 3, 1, "mish", plan_flags=L.PLAN_FORCE_HALO | L.PLAN_NO_HALO_PAIR, want_variant=(7, 2))
+    _run(gpu, 4, 64, 38, 38, 64, 3, 1, "mish", residual=True, plan_flags=L.PLAN_FORCE_HALO, want_variant=(3, 2))
+    _run(gpu, 4, 32, 38, 38, 64, 3, 2, "leaky", plan_flags=L.PLAN_NO_W_RES, want_variant=(8, 0))
+    _run(gpu, 2, 128, 19, 19, 128, 1, 1, "mish", plan_flags=L.PLAN_ONE_OUT_BUF, want_variant=(32, 0))
+    _run(gpu, 2, 128, 19, 19, 128, 1, 1, "mish", residual=True, plan_flags=L.PLAN_ONE_OUT_BUF, want_variant=(32, 0))
+    _run(gpu, 2, 128, 19, 19, 128, 1, 1, "mish", residual=True, want_variant=(32, 32))
+    _run(gpu, 8, 512, 19, 19, 512, 3, 1, "leaky", plan_flags=L.PLAN_COST_V1)
+    _run(gpu, 8, 512, 19, 19, 512, 3, 1, "leaky")
