@@ -61,6 +61,8 @@ struct ConvParams {
                        // engine still reads block k
   int split_col;       // > 0: output columns >= split_col go to a second tensor (tmap_y2) at column - split_col: two
                        // 1x1 convolutions that read the same input (the CSP branch pairs) run as ONE GEMM
+  int fast_epi;        // the specialised epilogue (epilogue_fast) applies: bf16 output, bias only, mish / leaky / linear
+  int bias_cols;       // n_tiles * block_n floats of bias staged in shared memory at kernel start
 };
 
 // ---- halo mode (a_mode 2): 3x3 stride-1 pad-1 convolutions whose A operand is staged ONCE per (tile, 64-channel chunk)
@@ -399,6 +401,213 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
   if (lane == 0) ptx::tma_store_wait<0>();  // smem must stay valid until the last store has read it
 }
 
+
+// ---- specialised epilogue: bf16 output, batchnorm folded (bias only), mish / leaky / linear, optional shortcut ----
+// ncu on the 64-channel layers at 304^2 (round 2, profiles/r02_*): the generic epilogue executes ~405 warp instructions
+// per 32 x 32 output block of which 129 are the activation math; the rest is per-tile / per-block control (runtime
+// switches on the A mode, output type, shortcut, statistics; 64-bit row arithmetic; tile index math) issued as one long
+// dependent chain, during which the warp does not feed the XU pipe (MUFU) that bounds these layers: XU 60 % busy.
+// Here everything that does not change inside the kernel is a template parameter or hoisted, the bias comes from shared
+// memory (one broadcast LDS.128 per four columns instead of an LDG), one warp works through a whole 32-row strip of a
+// tile (the per-tile work is paid once per 2-8 blocks, not once per block), and the mish math runs in phases of eight
+// independent pairs (16 MUFU.EX2, then 16 MUFU.RCP back to back) so a single warp keeps the XU pipe busy.
+template <int ACT, bool HALO, bool RES>
+__device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtensorMap* tmap_y, const CUtensorMap* tmap_y2,
+                                              uint32_t tmem_base, uint32_t tfull0, uint32_t tempty0, uint32_t sbuf0,
+                                              uint32_t bias_smem, int quad, int slot, int lane, int total_tiles) {
+  const int sets = p.epi_sets, wps = 4 / sets;
+  const int set = slot / wps, sub = slot - set * wps;
+  const int nacc_mask = p.nacc - 1, nacc_shift = 31 - __clz(p.nacc);
+  const uint32_t rowoff = (uint32_t)lane * 64u;
+  const uint32_t swz = ((rowoff >> 7) & 3u) << 4;
+  const bool two_bufs = p.out_bufs == 2;
+  const int M = p.M, n_store = p.n_store, block_n = p.block_n, n_tiles = p.n_tiles, split = p.split_col;
+  const int Ho = p.Ho, Wo = p.Wo;
+  const int tpi = p.tiles_h * p.tiles_w;
+  const __nv_bfloat16* res = p.res;
+  const long long ldres = p.ldres;
+  uint32_t nst = 0, sbuf = sbuf0;
+  auto wait_buf = [&]() {
+    if (lane == 0) {
+      if (two_bufs) ptx::tma_store_wait_read<1>();
+      else ptx::tma_store_wait_read<0>();
+    }
+    __syncwarp();
+    sbuf = sbuf0 + (two_bufs ? (nst & 1u) * (uint32_t)kStageOutBytes : 0u);
+  };
+  const int t_step = (int)gridDim.x * sets;
+  for (int t = blockIdx.x + set * (int)gridDim.x, it = set; t < total_tiles; t += t_step, it += sets) {
+    const int acc = it & nacc_mask;
+    const uint32_t acc_phase = (uint32_t)(it >> nacc_shift) & 1u;
+    int mt = t, nt = 0;
+    if (n_tiles != 1) {
+      mt = t / n_tiles;
+      nt = t - mt * n_tiles;
+    }
+    const int n0 = nt * block_n;
+    int row0 = mt * kBlockM + quad * 32;   // first GEMM row of this warp's strip (tiled / im2col)
+    int hb = 0, hw0 = 0, hh0 = 0;          // halo: image, first column / row of this warp's 4 x 8 pixel block
+    bool any_rows;
+    if (HALO) {
+      hb = fastdiv(mt, p.tpi_magic, p.tpi_shift);
+      const int rem = mt - hb * tpi;
+      const int th = fastdiv(rem, p.tw_magic, p.tw_shift);
+      hh0 = th * kHaloH + quad * 4;
+      hw0 = (rem - th * p.tiles_w) * kHaloW;
+      any_rows = hh0 < Ho;
+    } else {
+      any_rows = row0 < M;
+    }
+    const int n_groups = (min(block_n, n_store - n0) + 31) >> 5;
+    const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(acc * block_n);
+    // shortcut operand of group g: 32 rows x 64 B straight from global into this warp's staging buffer, coalesced
+    // 16-byte cp.async copies (copy j of a lane = chunk (lane & 3) of row (lane >> 2) + 8 j), 64B-swizzled
+    auto issue_res = [&](int g) {
+      wait_buf();
+      const int c0 = n0 + g * 32;
+      const int rr = lane >> 2, q = lane & 3;
+      const bool col_ok = c0 + q * 8 + 8 <= n_store;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        long long grow;
+        bool ok;
+        if (HALO) {
+          const int h = hh0 + j, w = hw0 + rr;
+          ok = h < Ho && w < Wo;
+          grow = ((long long)hb * Ho + h) * Wo + w;
+        } else {
+          grow = (long long)row0 + rr + 8 * j;
+          ok = grow < M;
+        }
+        ok = ok && col_ok;
+        const uint32_t r = (uint32_t)(rr + 8 * j);
+        ptx::cp_async_16(sbuf + r * 64u + (((uint32_t)q ^ ((r >> 1) & 3u)) << 4),
+                         ok ? (const void*)(res + grow * ldres + c0 + q * 8) : (const void*)res, ok ? 16u : 0u);
+      }
+      ptx::cp_async_commit();
+    };
+    if (RES && sub < n_groups) issue_res(sub);
+    ptx::mbar_wait(tfull0 + 8u * acc, acc_phase);
+    ptx::tc_fence_after();
+    if (sub >= n_groups) {  // nothing of this tile is this warp's: still hand the accumulator back
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(tempty0 + 8u * acc);
+      continue;
+    }
+    for (int g = sub; g < n_groups; g += wps) {
+      const int col0 = n0 + g * 32;
+      uint32_t r[32];
+      ptx::tmem_ld_32x32b_x32(t_row + g * 32, r);
+      ptx::tmem_ld_wait();
+      if (g + wps >= n_groups) {  // this warp's last read of the accumulator
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(tempty0 + 8u * acc);
+      }
+      uint4 rq[4];
+      if (RES) {  // the block staged by issue_res has landed: every lane reads its own row, then the buffer is reused
+        ptx::cp_async_wait_all();
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) rq[j] = ptx::ld_shared_v4(sbuf + rowoff + (((uint32_t)j * 16u) ^ swz));
+        __syncwarp();
+      } else {
+        wait_buf();
+      }
+      const uint32_t bsm = bias_smem + 4u * (uint32_t)col0;
+#pragma unroll
+      for (int hf = 0; hf < 2; ++hf) {  // two halves of 16 columns = 8 packed pairs each
+        f32x2 x[8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint4 b4 = ptx::ld_shared_v4(bsm + (uint32_t)(hf * 64 + j * 16));
+          x[2 * j] = add2(pack2(__uint_as_float(r[hf * 16 + 4 * j]), __uint_as_float(r[hf * 16 + 4 * j + 1])),
+                          pack2(__uint_as_float(b4.x), __uint_as_float(b4.y)));
+          x[2 * j + 1] = add2(pack2(__uint_as_float(r[hf * 16 + 4 * j + 2]), __uint_as_float(r[hf * 16 + 4 * j + 3])),
+                              pack2(__uint_as_float(b4.z), __uint_as_float(b4.w)));
+        }
+        if (ACT == YC_MISH) {  // x + x*r, r = 1/(-q/2), q = n(n+2)+2 on h = n/2 = 2^(x*log2e - 1)   (yc_common.cuh act_mish)
+          float h[16];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float a0, a1;
+            unpack2(fma2(x[j], pack2(1.4426950408889634f, 1.4426950408889634f), pack2(-1.f, -1.f)), a0, a1);
+            h[2 * j] = ex2_ftz(a0);
+            h[2 * j + 1] = ex2_ftz(a1);
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const f32x2 hh = pack2(h[2 * j], h[2 * j + 1]);
+            float q0, q1;
+            unpack2(fma2(hh, fma2(hh, pack2(-2.f, -2.f), pack2(-2.f, -2.f)), pack2(-1.f, -1.f)), q0, q1);
+            h[2 * j] = rcp_ftz(q0);
+            h[2 * j + 1] = rcp_ftz(q1);
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) x[j] = fma2(x[j], pack2(h[2 * j], h[2 * j + 1]), x[j]);
+        } else if (ACT == YC_LEAKY) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float x0, x1, m0, m1;
+            unpack2(x[j], x0, x1);
+            unpack2(mul2(x[j], pack2(0.1f, 0.1f)), m0, m1);
+            x[j] = pack2(fmaxf(x0, m0), fmaxf(x1, m1));
+          }
+        }
+        if (RES) {
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const uint4 q4 = rq[hf * 2 + j];
+            const uint32_t w4[4] = {q4.x, q4.y, q4.z, q4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e)  // bf16 pair -> fp32 pair (shift / mask), one packed add
+              x[j * 4 + e] = add2(x[j * 4 + e], pack2(__uint_as_float(w4[e] << 16), __uint_as_float(w4[e] & 0xffff0000u)));
+          }
+        }
+        uint32_t o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float y0, y1;
+          unpack2(x[j], y0, y1);
+          o[j] = pack_bf16x2(y0, y1);
+        }
+        ptx::st_shared_v4(sbuf + rowoff + (((uint32_t)(hf * 2) * 16u) ^ swz), o[0], o[1], o[2], o[3]);
+        ptx::st_shared_v4(sbuf + rowoff + (((uint32_t)(hf * 2 + 1) * 16u) ^ swz), o[4], o[5], o[6], o[7]);
+      }
+      ptx::fence_proxy_async();  // generic-proxy smem writes -> visible to the TMA engine
+      __syncwarp();
+      if (lane == 0) {  // always commit (possibly an empty group): the buffer rotation counts groups
+        if (any_rows) {
+          const bool second = split > 0 && col0 >= split;
+          const CUtensorMap* ty = second ? tmap_y2 : tmap_y;
+          const int scol = second ? col0 - split : col0;
+          if (HALO) ptx::tma_store_4d(ty, sbuf, scol, hw0, hh0, hb);
+          else ptx::tma_store_2d(ty, sbuf, scol, row0);
+        }
+        ptx::tma_store_commit();
+      }
+      ++nst;
+      if (RES && g + wps < n_groups) issue_res(g + wps);
+    }
+  }
+  if (lane == 0) ptx::tma_store_wait<0>();  // smem must stay valid until the last store has read it
+}
+
+template <int ACT>
+__device__ __forceinline__ void epilogue_fast_dispatch(const ConvParams& p, const CUtensorMap* tmap_y, const CUtensorMap* tmap_y2,
+                                                       uint32_t tmem_base, uint32_t tfull0, uint32_t tempty0, uint32_t sbuf0,
+                                                       uint32_t bias_smem, int quad, int slot, int lane, int total_tiles) {
+  const bool halo = p.a_mode == 2, has_res = p.res != nullptr;
+  if (halo) {
+    if (has_res) epilogue_fast<ACT, true, true>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles);
+    else epilogue_fast<ACT, true, false>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles);
+  } else {
+    if (has_res) epilogue_fast<ACT, false, true>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles);
+    else epilogue_fast<ACT, false, false>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles);
+  }
+}
+
 // 96 registers is the ceiling for 576 threads: the register file is allocated to warps in groups of four, so the CTA
 // counts as 640 threads (65536 / 640 = 102 -> 96); a build with __maxnreg__(112) (64512 registers by the per-warp
 // count) fails to launch on B200 ("too many resources requested").
@@ -434,6 +643,11 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   if (STATS) {
     for (int i = threadIdx.x; i < 2 * p.stat_cols; i += blockDim.x)
       asm volatile("st.shared.f32 [%0], %1;" ::"r"(stat_smem + 4u * i), "f"(0.f) : "memory");
+  }
+  const uint32_t bias_smem = stat_smem + (STATS ? 8u * (uint32_t)p.stat_cols : 0u);  // bias_cols floats (fast epilogue)
+  if (!STATS && p.fast_epi) {
+    for (int i = threadIdx.x; i < p.bias_cols; i += blockDim.x)
+      asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_smem + 4u * i), "f"(__ldg(p.bias + i)) : "memory");
   }
 
   const int warp = threadIdx.x >> 5;
@@ -691,6 +905,10 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const int half = (warp - 2) >> 2;  // slot 0..3 within the quadrant
     if (STATS) {
       epilogue_role<YC_LINEAR, true>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem);
+    } else if (p.fast_epi) {
+      if (p.act == YC_MISH) epilogue_fast_dispatch<YC_MISH>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, bias_smem, quad, half, lane, total_tiles);
+      else if (p.act == YC_LEAKY) epilogue_fast_dispatch<YC_LEAKY>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, bias_smem, quad, half, lane, total_tiles);
+      else epilogue_fast_dispatch<YC_LINEAR>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, bias_smem, quad, half, lane, total_tiles);
     } else
     switch (p.act) {
       case YC_LEAKY: epilogue_role<YC_LEAKY>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem); break;
@@ -970,53 +1188,90 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   const uint32_t a_bytes = p.a_mode == 2 ? 0u : kBlockM * p.block_k * 2;
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
   const uint32_t stage_bytes = a_bytes + b_bytes;
-  // halo mode: tiles go in pairs (two accumulators, one weight slab for both) when the N tile is shared (n_tiles == 1)
-  // and four patches fit next to at least three weight slabs; YC_PLAN_NO_HALO_PAIR switches the pairing off
-  p.halo_stages = 2;
-  p.halo_pair = 0;
-  p.out_bufs = (flags & YC_PLAN_ONE_OUT_BUF) ? 1 : 2;
-  const uint32_t out_bytes = kEpiWarps * kStageOutBytes * p.out_bufs;
-  if (p.a_mode == 2 && p.n_tiles == 1 && !(flags & YC_PLAN_NO_HALO_PAIR)) {
-    const uint32_t need = out_bytes + 4 * kHaloPatchStride + 3 * stage_bytes + 1024 + 512;
-    if (need <= 227 * 1024) {
-      p.halo_stages = 4;
-      p.halo_pair = 1;
-    }
-  }
-  const uint32_t out_stage = out_bytes + (p.a_mode == 2 ? p.halo_stages * kHaloPatchStride : 0);
-  const uint32_t smem_budget = 227 * 1024 - 1024 /*align slack*/ - 512 /*barriers*/ - out_stage;
-  // as deep as shared memory allows: the producer runs ahead across tiles, so the ring depth is the amount of
-  // HBM traffic in flight per SM (what the memory-bound 1x1 layers live on)
-  p.stages = std::min<int>(kMaxStages, smem_budget / stage_bytes);
-  YC_REQUIRE(p.stages >= 2, "tile does not fit shared memory");
-  p.w_resident = 0;
-  if (p.a_mode == 2 && p.n_tiles == 1 && 9 * p.cchunks <= p.stages) {
-    p.w_resident = 1;  // every weight slab fits: load them once per CTA instead of once per tile
-    p.stages = 9 * p.cchunks;
-  }
-  pl->smem = (size_t)p.stages * stage_bytes + out_stage + 1024 + 512;
-  // tiled / im2col path, one N tile, many tiles per CTA, small filter: the weight slabs stay resident behind the ring
-  // (the per-tile reload is a third of the L2 -> SM traffic of the 64-channel layers; YC_PLAN_NO_W_RES switches it off)
-  const int wres_env = (flags & YC_PLAN_NO_W_RES) ? 0 : ((flags & YC_PLAN_W_RES_1X1) ? 2 : 1);  // 0 never, 1 multi-tap layers, 2 also 1x1
-  if (p.a_mode != 2 && p.n_tiles == 1 && (wres_env == 2 || (wres_env == 1 && p.taps > 1))) {
-    const uint32_t wres_bytes = (uint32_t)(p.taps * p.cchunks) * b_bytes;
-    const long long tiles_per_cta = (long long)p.m_tiles / std::max(1, sms);
-    if (wres_bytes <= 64 * 1024 && tiles_per_cta >= 8 && smem_budget >= wres_bytes + 4 * a_bytes) {
-      p.w_resident = 1;
-      p.stages = std::min<int>(kMaxStages, (smem_budget - wres_bytes) / a_bytes);
-      pl->smem = (size_t)p.stages * a_bytes + wres_bytes + out_stage + 1024 + 512;
-    }
-  }
-  const int groups = p.block_n / 32;
-  p.epi_sets = groups >= 4 ? 1 : (groups >= 2 ? 2 : 4);
-  p.nacc = std::max(2, p.epi_sets);
-  if (p.block_n <= 128) p.nacc = 4;  // 4 x 128 columns fit: deeper MMA/epilogue decoupling for free
-  uint32_t cols = 32;
-  while (cols < (uint32_t)(p.nacc * p.block_n)) cols <<= 1;
-  p.tmem_cols = cols;
   p.act = d->activation;
   p.act2 = d->residual_activation;
   p.y_f32 = (y->dtype == YC_F32);
+  // the specialised epilogue covers what inference runs: bf16 output, batchnorm folded into the weights, mish / leaky /
+  // linear, optional fused shortcut with a linear second activation (YC_PLAN_GENERIC_EPI keeps the generic one)
+  p.fast_epi = !(flags & YC_PLAN_GENERIC_EPI) && !p.y_f32 && !scale && p.act2 == YC_LINEAR &&
+               (p.act == YC_MISH || p.act == YC_LEAKY || p.act == YC_LINEAR);
+  p.bias_cols = p.n_tiles * p.block_n;
+  const uint32_t bias_bytes = p.fast_epi ? 4u * (uint32_t)p.bias_cols : 0u;
+  const int k_blocks = p.taps * p.cchunks;
+  const int wres_env = (flags & YC_PLAN_NO_W_RES) ? 0 : ((flags & YC_PLAN_W_RES_1X1) ? 2 : 1);  // 0 never, 1 multi-tap layers, 2 also 1x1
+  // Shared-memory layout for a given number of epilogue staging buffers per warp:
+  //  * halo mode: tiles go in pairs (two accumulators, one weight slab for both) when the N tile is shared (n_tiles == 1)
+  //    and four patches fit next to at least three weight slabs (YC_PLAN_NO_HALO_PAIR switches the pairing off); when
+  //    all 9 * cchunks weight slabs fit they stay resident;
+  //  * tiled / im2col path, one N tile, many tiles per CTA, small filter: the weight slabs stay resident behind the ring
+  //    (the per-tile reload is a third of the L2 -> SM traffic of the 64-channel layers; YC_PLAN_NO_W_RES switches it off);
+  //  * otherwise the ring is as deep as shared memory allows: the producer runs ahead across tiles, so the ring depth is
+  //    the amount of HBM traffic in flight per SM (what the memory-bound 1x1 layers live on).
+  auto layout = [&](int out_bufs) -> bool {
+    p.out_bufs = out_bufs;
+    p.halo_stages = 2;
+    p.halo_pair = 0;
+    const uint32_t out_bytes = kEpiWarps * kStageOutBytes * out_bufs;
+    const uint32_t fixed = 1024 /*align slack*/ + 512 /*barriers*/ + bias_bytes;
+    if (p.a_mode == 2 && p.n_tiles == 1 && !(flags & YC_PLAN_NO_HALO_PAIR)) {
+      const uint32_t need = out_bytes + 4 * kHaloPatchStride + 3 * stage_bytes + fixed;
+      if (need <= 227 * 1024) {
+        p.halo_stages = 4;
+        p.halo_pair = 1;
+      }
+    }
+    const uint32_t out_stage = out_bytes + (p.a_mode == 2 ? p.halo_stages * kHaloPatchStride : 0);
+    if (out_stage + fixed + 2 * stage_bytes > 227 * 1024) return false;
+    const uint32_t smem_budget = 227 * 1024 - fixed - out_stage;
+    p.stages = std::min<int>(kMaxStages, smem_budget / stage_bytes);
+    p.w_resident = 0;
+    if (p.a_mode == 2 && p.n_tiles == 1 && 9 * p.cchunks <= p.stages) {
+      p.w_resident = 1;  // every weight slab fits: load them once per CTA instead of once per tile
+      p.stages = 9 * p.cchunks;
+    }
+    pl->smem = (size_t)p.stages * stage_bytes + out_stage + fixed;
+    if (p.a_mode != 2 && p.n_tiles == 1 && (wres_env == 2 || (wres_env == 1 && p.taps > 1))) {
+      const uint32_t wres_bytes = (uint32_t)k_blocks * b_bytes;
+      const long long tiles_per_cta = (long long)p.m_tiles / std::max(1, sms);
+      if (wres_bytes <= 64 * 1024 && tiles_per_cta >= 8 && smem_budget >= wres_bytes + 4 * a_bytes) {
+        p.w_resident = 1;
+        p.stages = std::min<int>(kMaxStages, (smem_budget - wres_bytes) / a_bytes);
+        pl->smem = (size_t)p.stages * a_bytes + wres_bytes + out_stage + fixed;
+      }
+    }
+    return p.stages >= 2;
+  };
+  // Two staging buffers let a warp stage block k+1 while the TMA engine still reads block k; they cost 32 KB of ring.
+  // Measured (tools/ab_layers.py, yolov4-608 x 64): +3..6 % on the epilogue-bound layers (few K blocks per tile), -3..6 %
+  // where the ring depth matters (>= 8 K blocks with 128 x 256 tiles) and -30 % in halo mode (tile pairs / resident
+  // weights no longer fit).  YC_PLAN_ONE_OUT_BUF / YC_PLAN_TWO_OUT_BUFS force either.
+  bool ok_layout;
+  if (flags & YC_PLAN_ONE_OUT_BUF) ok_layout = layout(1);
+  else if (flags & YC_PLAN_TWO_OUT_BUFS) ok_layout = layout(2) || layout(1);
+  else {
+    ok_layout = p.a_mode != 2 && layout(2) && (k_blocks <= 4 || p.stages >= 5 || p.w_resident);
+    if (!ok_layout) ok_layout = layout(1);
+  }
+  if (!ok_layout) {
+    set_error("yc_conv_plan_create: tile does not fit shared memory");
+    yc_conv_plan_destroy(pl);
+    return YC_ERR_ARG;
+  }
+  // Epilogue warp sets: set s takes tiles s, s + sets, ... of the CTA, each with its own TMEM accumulator.  The fast
+  // epilogue gives every warp a whole 32-row strip of its tile (sets = accumulators that fit: 4 up to 128 columns, else 2),
+  // so the per-tile work is paid once per strip; the generic one keeps four warps per quadrant on a wide tile.
+  const int groups = p.block_n / 32;
+  if (p.fast_epi && !(flags & YC_PLAN_EPI_SETS_V1)) {
+    p.epi_sets = p.block_n <= 128 ? 4 : 2;
+    p.nacc = p.epi_sets;
+  } else {
+    p.epi_sets = groups >= 4 ? 1 : (groups >= 2 ? 2 : 4);
+    p.nacc = std::max(2, p.epi_sets);
+    if (p.block_n <= 128) p.nacc = 4;  // 4 x 128 columns fit: deeper MMA/epilogue decoupling for free
+  }
+  uint32_t cols = 32;
+  while (cols < (uint32_t)(p.nacc * p.block_n)) cols <<= 1;
+  p.tmem_cols = cols;
   p.chunk = p.y_f32 ? 16 : 32;  // columns per TMA store box: 64-byte rows
   p.res = residual ? (const __nv_bfloat16*)residual->ptr : nullptr;
   p.ldres = residual ? residual->ldc : 0;
@@ -1205,6 +1460,7 @@ extern "C" int yc_conv_dgrad_plan_create(yc_conv_plan** plan, const yc_conv_desc
 extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq) {
   YC_REQUIRE(pl && ((sum && sumsq) || (!sum && !sumsq)), "yc_conv_plan_set_stats: bad arguments");
   ConvParams& p = pl->p;
+  p.fast_epi = 0;                       // statistics are reduced by the generic epilogue
   if (p.a_mode != 2) p.w_resident = 0;  // the ring is re-planned below with weights in every stage
   const uint32_t a_bytes = p.a_mode == 2 ? 0u : kBlockM * p.block_k * 2;
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
@@ -1254,9 +1510,10 @@ extern "C" int yc_conv_plan_info(const yc_conv_plan* pl, int what) {
     case 4: return pl->grid;
     case 5: return pl->p.a_mode;
     case 6: return (int)pl->smem;
-    case 7:  // kernel variant: [0,2) a_mode, 4 halo tile pairs, 8 resident weights, 16 two outputs, 32 two staging buffers, 64 rectangular
+    case 7:  // kernel variant: [0,2) a_mode, 4 halo tile pairs, 8 resident weights, 16 two outputs, 32 two staging buffers, 64 rectangular, 128 fast epilogue
       return pl->p.a_mode | (pl->p.halo_pair ? 4 : 0) | (pl->p.w_resident ? 8 : 0) | (pl->p.split_col ? 16 : 0) |
-             (pl->p.out_bufs == 2 ? 32 : 0) | (pl->rect ? 64 : 0);
+             (pl->p.out_bufs == 2 ? 32 : 0) | (pl->rect ? 64 : 0) | (pl->p.fast_epi ? 128 : 0);
+    case 8: return pl->p.epi_sets;
   }
   return -1;
 }

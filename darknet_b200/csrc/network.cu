@@ -385,7 +385,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
     net->finalized = true;
     return YC_OK;
   }
-  const unsigned plan_flags = ((unsigned)flags >> YC_NET_PLAN_SHIFT) & 0xffu;
+  const unsigned plan_flags = ((unsigned)flags >> YC_NET_PLAN_SHIFT) & 0xfffu;
   if (stem && Ls[0].n % 8 == 0 && 2 * Ls[0].n <= 256 && Ls[0].out_w % 2 == 0 && Ls[0].fused_into < 0 &&
       view_of(net, 0).ldc == Ls[0].n && view_of(net, 0).dtype == YC_BF16 && !(flags & YC_NET_NO_STEM_PAIR))
     net->stem_pair = true;
@@ -721,8 +721,61 @@ extern "C" int yc_network_layer_info(const yc_network* net, int layer, int what)
     case 13: return L.plan ? yc_conv_plan_info(L.plan, 7) : (L.pair_first >= 0 ? yc_conv_plan_info(net->layers[L.pair_first].plan, 7) : -1);
     case 14: return L.pair_first;   // >= 0: this conv is computed by that layer's kernel (fused 1x1 pair)
     case 15: return L.pair_second;
+    case 16: return L.classes;
+    case 17: return L.total;
+    case 18: return L.nms_kind;
+    case 19: return L.pad;
+    case 20: return L.dilation;
+    case 21: return L.groups;
+    case 22: return L.group_id;
+    case 23: return L.from;
+    case 24: return L.n;
+    case 25: return (int)L.inputs.size();
+    case 26: return L.max_boxes;
   }
   return -1;
+}
+
+extern "C" int yc_network_layer_input(const yc_network* net, int layer, int k) {
+  if (!net || layer < 0 || layer >= (int)net->layers.size()) return -1;
+  const NLayer& L = net->layers[layer];
+  return (k >= 0 && k < (int)L.inputs.size()) ? L.inputs[k] : -1;
+}
+
+extern "C" float yc_network_layer_float(const yc_network* net, int layer, int what) {
+  if (!net || layer < 0 || layer >= (int)net->layers.size()) return 0.f;
+  const NLayer& L = net->layers[layer];
+  switch (what) {
+    case 0: return L.scale_x_y;
+    case 1: return L.beta_nms;
+    case 2: return L.ignore_thresh;
+    case 3: return L.truth_thresh;
+    case 4: return L.iou_thresh;
+    case 5: return L.iou_normalizer;
+    case 6: return L.cls_normalizer;
+    case 7: return L.label_smooth_eps;
+    case 8: return L.max_delta;
+    case 9: return L.uc_normalizer;
+  }
+  return 0.f;
+}
+
+extern "C" int yc_network_layer_array(const yc_network* net, int layer, int what, float* dst, int capacity) {
+  YC_REQUIRE(net && dst && layer >= 0 && layer < (int)net->layers.size(), "yc_network_layer_array: bad argument");
+  const NLayer& L = net->layers[layer];
+  int n = 0;
+  if (what == 0) {
+    n = (int)L.anchors.size();
+    YC_REQUIRE(n <= capacity, "yc_network_layer_array: capacity %d < %d", capacity, n);
+    for (int i = 0; i < n; ++i) dst[i] = L.anchors[i];
+  } else if (what == 1) {
+    n = (int)L.mask.size();
+    YC_REQUIRE(n <= capacity, "yc_network_layer_array: capacity %d < %d", capacity, n);
+    for (int i = 0; i < n; ++i) dst[i] = (float)L.mask[i];
+  } else {
+    YC_REQUIRE(false, "yc_network_layer_array: unknown array %d", what);
+  }
+  return n;
 }
 
 extern "C" double yc_network_flops(const yc_network* net) {

@@ -124,8 +124,11 @@ enum {
   YC_PLAN_NO_HALO_PAIR = 4,  /* halo mode: one tile at a time instead of tile pairs */
   YC_PLAN_NO_W_RES = 8,      /* never keep the weight slabs resident in shared memory */
   YC_PLAN_W_RES_1X1 = 16,    /* keep them resident for 1x1 layers as well */
-  YC_PLAN_ONE_OUT_BUF = 32,  /* one epilogue staging buffer per warp instead of two */
-  YC_PLAN_COST_V1 = 64       /* round-1 tile-width cost model */
+  YC_PLAN_ONE_OUT_BUF = 32,  /* one epilogue staging buffer per warp (default: two where the ring depth allows) */
+  YC_PLAN_COST_V1 = 64,      /* round-1 tile-width cost model */
+  YC_PLAN_TWO_OUT_BUFS = 128, /* two staging buffers wherever they fit */
+  YC_PLAN_GENERIC_EPI = 256, /* never use the specialised (bf16 / bias-only / mish-leaky-linear) epilogue */
+  YC_PLAN_EPI_SETS_V1 = 512  /* specialised epilogue with the generic one's warp-to-tile assignment */
 };
 /* [setup] yc_conv_plan_create with plan switches and, optionally, a SECOND output tensor y2: the GEMM then has
  * y->c + y2->c output channels (weights / bias / scale of both layers concatenated along out_c, y->c a multiple of
@@ -139,7 +142,8 @@ YC_API int yc_conv_plan_destroy(yc_conv_plan* plan);
 YC_API int yc_conv_fprop(const yc_conv_plan* plan, void* stream);
 /* plan introspection for tests/bench: what=0 block_n, 1 block_k, 2 stages, 3 tiles, 4 grid, 5 A-operand mode (0 tiled,
  * 1 im2col, 2 halo patch), 6 dynamic shared memory bytes, 7 variant bits: [0,2) A mode | 4 halo tile pairs | 8 resident
- * weights | 16 two outputs | 32 two staging buffers | 64 rectangular (pixel-pair) geometry */
+ * weights | 16 two outputs | 32 two staging buffers | 64 rectangular (pixel-pair) geometry | 128 specialised epilogue;
+ * 8 epilogue warp sets */
 YC_API int yc_conv_plan_info(const yc_conv_plan* plan, int what);
 
 /* ---- convolution training path: replaces ForwardConvolutionalLayerGpu(train) / BackwardConvolutionalLayerGpu --- */
@@ -316,7 +320,7 @@ enum {
   YC_NET_NO_STEM_PAIR = 1024, /* stem conv on single pixels instead of pixel pairs (A/B + parity coverage) */
   YC_NET_NO_PAIR_S2 = 2048,  /* 3x3 stride-2 32-channel layer on the plain im2col path instead of the pixel-pair view */
   YC_NET_NO_PAIR_FUSE = 4096, /* do not merge two 1x1 convs that read the same tensor into one GEMM */
-  YC_NET_PLAN_SHIFT = 16,    /* bits [16,24): YC_PLAN_* switches handed to every conv plan */
+  YC_NET_PLAN_SHIFT = 16,    /* bits [16,28): YC_PLAN_* switches handed to every conv plan */
   YC_NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
 };
 
@@ -338,8 +342,17 @@ YC_API int yc_network_info(const yc_network* net, int what);
 /* per-layer: what: 0 type(0 conv,1 maxpool,2 upsample,3 route,4 shortcut,5 yolo,6 gaussian_yolo) 1 out_c 2 out_h
  * 3 out_w 4 has_output(0 if fused away) 5 in_c 6 size 7 stride 8 activation 9 batch_normalize 10 block_n 11 stages
  * 12 tiles 13 kernel variant bits (yc_conv_plan_info what=7) 14 layer whose kernel computes this conv (fused 1x1 pair;
- * -1 = its own) 15 layer this conv's kernel also computes (-1 = none) */
+ * -1 = its own) 15 layer this conv's kernel also computes (-1 = none)
+ * 16 classes 17 num (total anchors) 18 nms_kind 19 pad 20 dilation 21 groups 22 group_id 23 shortcut `from`
+ * 24 filters / anchors of this head 25 number of inputs 26 max boxes */
 YC_API int yc_network_layer_info(const yc_network* net, int layer, int what);
+/* k-th input layer index of a layer (route: its `layers=` list resolved; others: the previous layer), -1 past the end */
+YC_API int yc_network_layer_input(const yc_network* net, int layer, int k);
+/* what: 0 scale_x_y (upsample: scale) 1 beta_nms 2 ignore_thresh 3 truth_thresh 4 iou_thresh 5 iou_normalizer
+ * 6 cls_normalizer 7 label_smooth_eps 8 max_delta 9 uc_normalizer */
+YC_API float yc_network_layer_float(const yc_network* net, int layer, int what);
+/* what: 0 anchors (l->biases, 2*num floats) 1 mask (as floats).  Returns the number of floats written (<0: error). */
+YC_API int yc_network_layer_array(const yc_network* net, int layer, int what, float* dst, int capacity);
 YC_API double yc_network_flops(const yc_network* net);               /* sum 2*nweights*out_h*out_w per image
                                                                         (convolutional_layer.cpp:714) */
 /* NetworkPredict (network.cpp:412-430 -> NetworkPredictGpu network_kernels.cu:502-522): input = host fp32 NCHW
