@@ -59,5 +59,31 @@ def build(verbose: bool = False, force: bool = False) -> str:
     return OUT
 
 
+SHIM_SRC = os.path.join(HERE, "shim", "yolo_core_b200.cpp")
+SHIM_OUT = os.path.join(HERE, "libyolo_core_b200.so")
+REF = "/root/reference"
+
+
+def build_shim(force: bool = False):
+    """libyolo_core_b200.so: the reference's own entry points (LoadNetwork, NetworkPredict, GetNetworkBoxes, NmsSort,
+    Forward*LayerGpu(layer*, NetworkState)) on top of libyc_b200.so, compiled against the reference's public header
+    where it lies (<reference>/src/yolo_core.h; nothing of the reference is copied or linked).  Only possible where the
+    reference tree exists (this container); the built .so travels to the GPU box with the snapshot.  Returns the path,
+    or None when the header is not available and no prebuilt library exists."""
+    hdr = os.path.join(REF, "src", "yolo_core.h")
+    if not os.path.exists(hdr):
+        return SHIM_OUT if os.path.exists(SHIM_OUT) else None
+    deps = [SHIM_SRC, os.path.join(HERE, "..", "include", "yc_b200.h"), OUT]
+    if not force and os.path.exists(SHIM_OUT) and all(os.path.getmtime(d) <= os.path.getmtime(SHIM_OUT) for d in deps):
+        return SHIM_OUT
+    cmd = ["/usr/bin/g++", "-std=c++14", "-O2", "-fPIC", "-shared", "-fvisibility=hidden", "-w", "-fpermissive",
+           "-I", os.path.join(REF, "src"), "-I", os.path.join(REF, "3rdparty", "stb", "include"),
+           SHIM_SRC, "-o", SHIM_OUT, "-L", HERE, "-l:libyc_b200.so", "-Wl,-rpath,$ORIGIN", "-ldl", "-lpthread"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("shim build failed:\n" + " ".join(cmd) + "\n" + r.stdout + r.stderr)
+    return SHIM_OUT
+
+
 if __name__ == "__main__":
     print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))

@@ -151,9 +151,11 @@ def synth_weights(text: str, seed: int = 42):
     return out
 
 
-def shift_head_objectness(text, weights, bias, gain=None):
-    """Sparse-detection regime: head weights scaled by `gain` so the logits spread like a trained
-    net's, objectness bias shifted so only a few cells pass."""
+def shift_head_objectness(text, weights, bias, gain=None, box_gain=None):
+    """Sparse-detection regime: the objectness / class filters of every head are scaled by `gain` so the
+    logits spread like a trained net's, the objectness bias is set to `bias` so only a few cells pass.  box_gain (default:
+    gain) scales the box-coordinate filters separately: a trained net's tw/th stay within a few units, while gain 40+
+    on them gives boxes of e^10 image widths."""
     _, layers = walk_shapes(text)
     for L in layers:
         if L.kind in ("yolo", "Gaussian_yolo"):
@@ -161,8 +163,14 @@ def shift_head_objectness(text, weights, bias, gain=None):
             gaussian = L.kind == "Gaussian_yolo"
             classes = int(L.opts.get("classes", 20))
             E = classes + (9 if gaussian else 5)
+            nbox = 8 if gaussian else 4
             if gain is not None:
-                weights[conv.index]["weights"] *= np.float32(gain)
+                w = weights[conv.index]["weights"].reshape(conv.n, -1)
+                bg = np.float32(gain if box_gain is None else box_gain)
+                for a in range(conv.n // E):
+                    w[a * E:a * E + nbox] *= bg
+                    w[a * E + nbox:(a + 1) * E] *= np.float32(gain)
+                weights[conv.index]["weights"] = w.reshape(-1)
             b = weights[conv.index]["biases"]
             for a in range(conv.n // E):
                 if bias is not None:

@@ -62,7 +62,7 @@ struct ConvParams {
   int split_col;       // > 0: output columns >= split_col go to a second tensor (tmap_y2) at column - split_col: two
                        // 1x1 convolutions that read the same input (the CSP branch pairs) run as ONE GEMM
   int fast_epi;        // the specialised epilogue (epilogue_fast) applies: bf16 output, bias only, mish / leaky / linear
-  int bias_cols;       // n_tiles * block_n floats of bias staged in shared memory at kernel start
+  int bias_cols;       // > 0: that many floats of bias (n_tiles * block_n) are staged in shared memory at kernel start
 };
 
 // ---- halo mode (a_mode 2): 3x3 stride-1 pad-1 convolutions whose A operand is staged ONCE per (tile, 64-channel chunk)
@@ -426,6 +426,7 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtenso
   const int tpi = p.tiles_h * p.tiles_w;
   const __nv_bfloat16* res = p.res;
   const long long ldres = p.ldres;
+  const bool bias_in_smem = p.bias_cols > 0;
   uint32_t nst = 0, sbuf = sbuf0;
   auto wait_buf = [&]() {
     if (lane == 0) {
@@ -516,12 +517,17 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtenso
         wait_buf();
       }
       const uint32_t bsm = bias_smem + 4u * (uint32_t)col0;
+      const float* bgl = p.bias + col0;
 #pragma unroll
       for (int hf = 0; hf < 2; ++hf) {  // two halves of 16 columns = 8 packed pairs each
         f32x2 x[8];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const uint4 b4 = ptx::ld_shared_v4(bsm + (uint32_t)(hf * 64 + j * 16));
+          // bias: broadcast LDS.128 from the copy staged at kernel start, or (where that copy would have cost a ring
+          // stage: wide K-heavy tiles, whose epilogue is hidden anyway) straight from global / L1
+          uint4 b4;
+          if (bias_in_smem) b4 = ptx::ld_shared_v4(bsm + (uint32_t)(hf * 64 + j * 16));
+          else b4 = __ldg(reinterpret_cast<const uint4*>(bgl + hf * 16 + j * 4));
           x[2 * j] = add2(pack2(__uint_as_float(r[hf * 16 + 4 * j]), __uint_as_float(r[hf * 16 + 4 * j + 1])),
                           pack2(__uint_as_float(b4.x), __uint_as_float(b4.y)));
           x[2 * j + 1] = add2(pack2(__uint_as_float(r[hf * 16 + 4 * j + 2]), __uint_as_float(r[hf * 16 + 4 * j + 3])),
@@ -645,7 +651,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       asm volatile("st.shared.f32 [%0], %1;" ::"r"(stat_smem + 4u * i), "f"(0.f) : "memory");
   }
   const uint32_t bias_smem = stat_smem + (STATS ? 8u * (uint32_t)p.stat_cols : 0u);  // bias_cols floats (fast epilogue)
-  if (!STATS && p.fast_epi) {
+  if (!STATS && p.fast_epi) {  // (bias_cols == 0: the epilogue reads the bias from global memory)
     for (int i = threadIdx.x; i < p.bias_cols; i += blockDim.x)
       asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_smem + 4u * i), "f"(__ldg(p.bias + i)) : "memory");
   }
@@ -1195,8 +1201,7 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   // linear, optional fused shortcut with a linear second activation (YC_PLAN_GENERIC_EPI keeps the generic one)
   p.fast_epi = !(flags & YC_PLAN_GENERIC_EPI) && !p.y_f32 && !scale && p.act2 == YC_LINEAR &&
                (p.act == YC_MISH || p.act == YC_LEAKY || p.act == YC_LINEAR);
-  p.bias_cols = p.n_tiles * p.block_n;
-  const uint32_t bias_bytes = p.fast_epi ? 4u * (uint32_t)p.bias_cols : 0u;
+  uint32_t bias_bytes = 0;  // set per layout attempt below
   const int k_blocks = p.taps * p.cchunks;
   const int wres_env = (flags & YC_PLAN_NO_W_RES) ? 0 : ((flags & YC_PLAN_W_RES_1X1) ? 2 : 1);  // 0 never, 1 multi-tap layers, 2 also 1x1
   // Shared-memory layout for a given number of epilogue staging buffers per warp:
@@ -1241,17 +1246,31 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
     }
     return p.stages >= 2;
   };
-  // Two staging buffers let a warp stage block k+1 while the TMA engine still reads block k; they cost 32 KB of ring.
-  // Measured (tools/ab_layers.py, yolov4-608 x 64): +3..6 % on the epilogue-bound layers (few K blocks per tile), -3..6 %
-  // where the ring depth matters (>= 8 K blocks with 128 x 256 tiles) and -30 % in halo mode (tile pairs / resident
-  // weights no longer fit).  YC_PLAN_ONE_OUT_BUF / YC_PLAN_TWO_OUT_BUFS force either.
+  // Staging buffers per epilogue warp: two would let a warp stage block k+1 while the TMA engine still reads block k, at
+  // 32 KB of ring.  Measured with the specialised epilogue (tools/ab_layers.py, yolov4-608 x 64, round 2): one buffer is
+  // as fast or faster on every layer (11.32 vs 11.40 ms of conv per step; halo mode loses its tile pairs / resident
+  // weights with two: 3x3 64->64 @152 209 -> 323 us).  YC_PLAN_TWO_OUT_BUFS forces two where they fit.
+  // The bias copy in shared memory is taken only where it does not cost a ring stage (a 128 x 256 tile has four 48 KB
+  // stages in 227 KB with 2.5 KB to spare: 512+ columns of bias would make that three; measured -5..-14 % on those layers).
+  auto layout_bias = [&](int out_bufs) -> bool {
+    bias_bytes = 0;
+    p.bias_cols = 0;
+    if (!layout(out_bufs)) return false;
+    if (p.fast_epi) {
+      const int stages0 = p.stages, pair0 = p.halo_pair, wres0 = p.w_resident, hst0 = p.halo_stages;
+      bias_bytes = 4u * (uint32_t)(p.n_tiles * p.block_n);
+      if (layout(out_bufs) && p.stages == stages0 && p.halo_pair == pair0 && p.w_resident == wres0 && p.halo_stages == hst0) {
+        p.bias_cols = p.n_tiles * p.block_n;
+      } else {
+        bias_bytes = 0;
+        layout(out_bufs);
+      }
+    }
+    return true;
+  };
   bool ok_layout;
-  if (flags & YC_PLAN_ONE_OUT_BUF) ok_layout = layout(1);
-  else if (flags & YC_PLAN_TWO_OUT_BUFS) ok_layout = layout(2) || layout(1);
-  else {
-    ok_layout = p.a_mode != 2 && layout(2) && (k_blocks <= 4 || p.stages >= 5 || p.w_resident);
-    if (!ok_layout) ok_layout = layout(1);
-  }
+  if (flags & YC_PLAN_TWO_OUT_BUFS) ok_layout = layout_bias(2) || layout_bias(1);
+  else ok_layout = layout_bias(1);
   if (!ok_layout) {
     set_error("yc_conv_plan_create: tile does not fit shared memory");
     yc_conv_plan_destroy(pl);

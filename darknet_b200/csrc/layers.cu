@@ -396,6 +396,70 @@ __global__ void scale_channels_kernel(View x, View s, View y, int act) {
   }
 }
 
+
+// ---- scale_channels backward: backward_scale_channels_kernel (blas_kernels.cu:1348-1420) ------------------------------
+// BackwardScaleChannelsLayer (scale_channels_layer.c:99-131): dy *= act'(y) in place; ds[n,c] += sum_hw dy * x;
+// dx += s[n,c] * dy.  One block per (image, 8-channel group): every thread walks the pixels with stride blockDim,
+// 16-byte accesses along C, the per-channel sums are reduced with warp shuffles (the reference's warp-shuffle channel
+// sum) and then across the eight warps through shared memory; the block owns its eight ds entries, so no atomics and a
+// fixed summation order.
+__device__ __forceinline__ float sc_act_grad_out(float y, int act) {  // gradient_array on the output (activations.h:152-178)
+  switch (act) {
+    case YC_LEAKY: return y > 0.f ? 1.f : .1f;
+    case YC_RELU: return y > 0.f ? 1.f : 0.f;
+    case YC_LOGISTIC: return (1.f - y) * y;
+  }
+  return 1.f;
+}
+__global__ void scale_channels_bwd_kernel(View dy, View y, int act, View x, View s, View ds, View dx) {
+  const int groups = (dy.c + 7) / 8;
+  const int g = blockIdx.x % groups;
+  const long long n = blockIdx.x / groups;
+  const long long hw = (long long)dy.h * dy.w;
+  const V8 sc = load8(s, n, g * 8);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  for (long long pp = threadIdx.x; pp < hw; pp += blockDim.x) {
+    const long long pix = n * hw + pp;
+    V8 d = load8(dy, pix, g * 8);
+    if (act != YC_LINEAR) {
+      const V8 yo = load8(y, pix, g * 8);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) d.v[j] *= sc_act_grad_out(yo.v[j], act);
+      store8(dy, pix, g * 8, d);
+    }
+    const V8 xv = load8(x, pix, g * 8);
+    V8 dxv = load8(dx, pix, g * 8);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      acc[j] = fmaf(d.v[j], xv.v[j], acc[j]);
+      dxv.v[j] = fmaf(sc.v[j], d.v[j], dxv.v[j]);
+    }
+    store8(dx, pix, g * 8, dxv);
+  }
+  __shared__ float part[8][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    float v = acc[j];
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if (lane == 0) part[warp][j] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    V8 dsv = load8(ds, n, g * 8);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float v = 0.f;
+      for (int w = 0; w < (int)(blockDim.x >> 5); ++w) v += part[w][j];
+      dsv.v[j] += v;
+    }
+    store8(ds, n, g * 8, dsv);
+  }
+}
+
 // ---- reorg: reorg_kernel (blas_kernels.cu:368-402), index math of reorg_cpu (blas.c:12-46) ----------
 // forward==0 (what [reorg] forward uses): y[b,k,j,i] = x[b, k%in_c, j*s + (k/in_c)/s, i*s + (k/in_c)%s]
 // forward==1: the inverse scatter.  Scalar: not used by any of the five configs.
@@ -560,6 +624,36 @@ extern "C" int yc_scale_channels_fwd(const yc_tensor* x, const yc_tensor* s, con
   scale_channels_kernel<<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(mk(x), mk(s), mk(y), act);
   YC_LAUNCH_CHECK();
   return YC_OK;
+}
+
+extern "C" int yc_scale_channels_bwd(const yc_tensor* dy, const yc_tensor* y, int act, const yc_tensor* x, const yc_tensor* s,
+                                     const yc_tensor* ds, const yc_tensor* dx, void* stream) {
+  YC_CHECK_T(dy, "yc_scale_channels_bwd dy");
+  YC_CHECK_T(x, "yc_scale_channels_bwd x");
+  YC_CHECK_T(s, "yc_scale_channels_bwd s");
+  YC_CHECK_T(ds, "yc_scale_channels_bwd ds");
+  YC_CHECK_T(dx, "yc_scale_channels_bwd dx");
+  YC_REQUIRE(act == YC_LINEAR || act == YC_LEAKY || act == YC_RELU || act == YC_LOGISTIC,
+             "yc_scale_channels_bwd: activation outside the hot path");
+  if (act != YC_LINEAR) {
+    YC_CHECK_T(y, "yc_scale_channels_bwd y");
+    YC_REQUIRE(same_shape(dy, y) && aligned16(y), "yc_scale_channels_bwd: y must have dy's shape");
+  }
+  YC_REQUIRE(same_shape(dy, x) && same_shape(dy, dx) && s->n == dy->n && s->c == dy->c && s->h == 1 && s->w == 1 &&
+                 same_shape(s, ds),
+             "yc_scale_channels_bwd: x / dx must have dy's shape, s / ds must be [n,1,1,c]");
+  YC_REQUIRE(aligned16(dy) && aligned16(x) && aligned16(s) && aligned16(ds) && aligned16(dx), "yc_scale_channels_bwd: alignment");
+  const int groups = (dy->c + 7) / 8;
+  scale_channels_bwd_kernel<<<dy->n * groups, 256, 0, (cudaStream_t)stream>>>(mk(dy), act == YC_LINEAR ? mk(dy) : mk(y), act, mk(x),
+                                                                              mk(s), mk(ds), mk(dx));
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+// BackwardReorgLayerGpu (reorg_layer.c:129-143): the inverse rearrangement of l->delta into state.delta, OVERWRITING it
+// like reorg_cpu does.  `reverse` = l->reverse of the forward layer.
+extern "C" int yc_reorg_bwd(const yc_tensor* dy, const yc_tensor* dx, int stride, int reverse, void* stream) {
+  return yc_reorg_fwd(dy, dx, stride, reverse ? 0 : 1, stream);
 }
 
 extern "C" int yc_reorg_fwd(const yc_tensor* x, const yc_tensor* y, int stride, int forward, void* stream) {

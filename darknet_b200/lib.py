@@ -120,6 +120,8 @@ _SIGS = {
     "yc_route_copy": (C.c_int, [_TP, _TP, _P]),
     "yc_scale_channels_fwd": (C.c_int, [_TP, _TP, _TP, C.c_int, _P]),
     "yc_reorg_fwd": (C.c_int, [_TP, _TP, C.c_int, C.c_int, _P]),
+    "yc_scale_channels_bwd": (C.c_int, [_TP, _TP, C.c_int, _TP, _TP, _TP, _TP, _P]),
+    "yc_reorg_bwd": (C.c_int, [_TP, _TP, C.c_int, C.c_int, _P]),
     "yc_yolo_decode": (C.c_int, [_TP, _P, C.c_int, C.c_int, C.c_float, C.c_int, _P]),
     "yc_yolo_loss": (C.c_int, [C.POINTER(YoloLossDesc), _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _TP, _P, _P]),
     "yc_yolo_extract": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, C.c_int,

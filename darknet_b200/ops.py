@@ -278,6 +278,30 @@ def reorg(x, c, stride, forward=0):
     return y, oc
 
 
+def scale_channels_bwd(dy, y, x, s, ds, dx, c, act="linear"):
+    """BackwardScaleChannelsLayerGpu on NHWC tensors: dy is updated in place by the activation gradient, ds ([n,1,1,ldc]) and
+    dx accumulate."""
+    n, h, w, ldc = dy.shape
+    yv = None if y is None else C.byref(L.view(y, n, h, w, c, y.shape[-1]))
+    L.check(L.lib().yc_scale_channels_bwd(L.view(dy, n, h, w, c, ldc), yv, L.ACT[act], L.view(x, n, h, w, c, x.shape[-1]),
+                                          L.view(s, n, 1, 1, c, s.shape[-1]), L.view(ds, n, 1, 1, c, ds.shape[-1]),
+                                          L.view(dx, n, h, w, c, dx.shape[-1]), L.stream_ptr()), "yc_scale_channels_bwd")
+
+
+def reorg_bwd(dy, c, stride, reverse=0):
+    """BackwardReorgLayerGpu: dy has the forward layer's OUTPUT shape; returns (dx, channels of dx)."""
+    n, h, w, ldc = dy.shape
+    if reverse:   # forward scattered small -> big, backward gathers big -> small
+        oc, oh, ow = c * stride * stride, h // stride, w // stride
+    else:
+        oc, oh, ow = c // (stride * stride), h * stride, w * stride
+    oldc = _chan_pad(oc, dy.dtype)
+    dx = torch.zeros((n, oh, ow, oldc), dtype=dy.dtype, device=dy.device)
+    L.check(L.lib().yc_reorg_bwd(L.view(dy, n, h, w, c, ldc), L.view(dx, n, oh, ow, oc, oldc), stride, reverse,
+                                 L.stream_ptr()), "yc_reorg_bwd")
+    return dx, oc
+
+
 def yolo_decode(x, c, anchors, classes, scale_x_y, gaussian=False):
     n, h, w, ldc = x.shape
     out = torch.empty((n, c, h, w), dtype=torch.float32, device=x.device)

@@ -124,7 +124,7 @@ enum {
   YC_PLAN_NO_HALO_PAIR = 4,  /* halo mode: one tile at a time instead of tile pairs */
   YC_PLAN_NO_W_RES = 8,      /* never keep the weight slabs resident in shared memory */
   YC_PLAN_W_RES_1X1 = 16,    /* keep them resident for 1x1 layers as well */
-  YC_PLAN_ONE_OUT_BUF = 32,  /* one epilogue staging buffer per warp (default: two where the ring depth allows) */
+  YC_PLAN_ONE_OUT_BUF = 32,  /* one epilogue staging buffer per warp (the default since the specialised epilogue) */
   YC_PLAN_COST_V1 = 64,      /* round-1 tile-width cost model */
   YC_PLAN_TWO_OUT_BUFS = 128, /* two staging buffers wherever they fit */
   YC_PLAN_GENERIC_EPI = 256, /* never use the specialised (bf16 / bias-only / mish-leaky-linear) epilogue */
@@ -225,6 +225,15 @@ YC_API int yc_scale_channels_fwd(const yc_tensor* x, const yc_tensor* s, const y
 /* ForwardReorgLayerGpu (reorg_layer.c:113-127, blas_kernels.cu:368-402) on the reference's NCHW
  * index math, expressed over NHWC views. forward as in reorg_cpu (blas.c:12-46). */
 YC_API int yc_reorg_fwd(const yc_tensor* x, const yc_tensor* y, int stride, int forward, void* stream);
+
+/* BackwardScaleChannelsLayerGpu (scale_channels_layer.c:146-160, blas_kernels.cu:1348-1420; CPU twin :99-131),
+ * scale_wh = 0: dy *= act'(y) in place (y may be NULL for LINEAR); ds[n,c] += sum over h,w of dy * x; dx += s * dy,
+ * where x = the `from` layer's output, s = this layer's input ([n,1,1,c]), ds / dx their deltas. */
+YC_API int yc_scale_channels_bwd(const yc_tensor* dy, const yc_tensor* y, int activation, const yc_tensor* x,
+                          const yc_tensor* s, const yc_tensor* ds, const yc_tensor* dx, void* stream);
+/* BackwardReorgLayerGpu (reorg_layer.c:129-143): dx = the inverse rearrangement of dy (overwrites dx like reorg_cpu);
+ * reverse = l->reverse of the forward layer (0 for a plain [reorg]). */
+YC_API int yc_reorg_bwd(const yc_tensor* dy, const yc_tensor* dx, int stride, int reverse, void* stream);
 
 /* ---- backward of the memory-bound layers + update ---------------------------------------------- */
 /* ForwardMaxpoolLayerGpu in training: also records the winning tap (one byte per output element, [n,h,w,ceil8(c)]),

@@ -47,6 +47,11 @@ def ref_lib():
         L.ref_load_nofuse.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         L.ref_free.argtypes = [C.c_void_p]
         L.ref_num_layers.argtypes = [C.c_void_p]
+        L.ref_network_ptr.restype = C.c_void_p
+        L.ref_network_ptr.argtypes = [C.c_void_p]
+        L.ref_layer_ptr.restype = C.c_void_p
+        L.ref_layer_ptr.argtypes = [C.c_void_p, C.c_int]
+        L.ref_sizeof.argtypes = [C.c_int]
         L.ref_net_dim.argtypes = [C.c_void_p, C.c_int]
         L.ref_layer_int.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
         L.ref_layer_buf.restype = C.POINTER(C.c_float)
@@ -70,6 +75,11 @@ def ref_lib():
         L.ref_im2col.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
         L.ref_activate.argtypes = [_f32p, C.c_int, C.c_int, _f32p, _f32p]
         L.ref_activation_id.argtypes = [C.c_char_p]
+        L.ref_scale_channels.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_void_p,
+                                         C.c_void_p, C.c_void_p]
+        L.ref_reorg.argtypes = [_f32p] + [C.c_int] * 6 + [_f32p]
+        L.ref_layer_forward_train.restype = C.c_float
+        L.ref_layer_forward_train.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p, _f32p]
         L.ref_nms.argtypes = [_f32p, _f32p, _f32p, C.c_int, C.c_int, C.c_float, C.c_int, C.c_float, _i32p]
         _ref = L
     return _ref
@@ -135,6 +145,15 @@ class RefNet:
             t = self._truth.ctypes.data_as(C.c_void_p)
         self.L.ref_forward(self.h, x, t, train)
 
+    def layer_forward_train(self, i, inp, truth):
+        """Layer i's own CPU forward (train) on `inp`: returns (output, delta, cost) — the loss half of a YOLO head."""
+        shape = (self.layer_int(i, "batch"), self.layer_int(i, "out_c"), self.layer_int(i, "out_h"), self.layer_int(i, "out_w"))
+        out, delta = np.zeros(shape, np.float32), np.zeros(shape, np.float32)
+        cost = self.L.ref_layer_forward_train(self.h, i, np.ascontiguousarray(inp, np.float32).reshape(-1),
+                                              np.ascontiguousarray(truth, np.float32).reshape(-1), out.reshape(-1),
+                                              delta.reshape(-1))
+        return out, delta, float(cost)
+
     def forward_backward(self, x, truth):
         x = np.ascontiguousarray(x, np.float32).reshape(-1)
         t = np.ascontiguousarray(truth, np.float32).reshape(-1)
@@ -186,6 +205,8 @@ def oracle_lib():
         L.yo_shortcut.argtypes = [_f32p, _f32p, C.c_longlong, C.c_int, _f32p]
         L.yo_reorg.argtypes = [_f32p] + [C.c_int] * 6 + [_f32p]
         L.yo_scale_channels.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int, _f32p]
+        L.yo_scale_channels_forward.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
+        L.yo_scale_channels_backward.argtypes = [_f32p, _f32p, C.c_int, _f32p, _f32p, C.c_int, C.c_int, C.c_int, _f32p, _f32p]
         L.yo_yolo_decode.argtypes = [_f32p] + [C.c_int] * 5 + [C.c_float, _f32p]
         L.yo_gaussian_yolo_decode.argtypes = [_f32p] + [C.c_int] * 5 + [C.c_float, _f32p]
         L.yo_yolo_detections.argtypes = [_f32p] + [C.c_int] * 5 + [_f32p, _i32p, C.c_int, C.c_int, C.c_float, _f32p, C.c_int]
@@ -306,6 +327,45 @@ class O:
         out = np.zeros_like(a, dtype=np.float32)
         oracle_lib().yo_shortcut(np.ascontiguousarray(a, np.float32).reshape(-1), np.ascontiguousarray(b, np.float32).reshape(-1),
                                  a.size, ACT[act], out.reshape(-1))
+        return out
+
+    @staticmethod
+    def scale_channels(from_out, scale_in, act="linear"):
+        """ForwardScaleChannelsLayer: from_out [B,C,H,W], scale_in [B,C] -> act(scale * from_out)."""
+        B, Cc, H, W = from_out.shape
+        out = np.zeros_like(from_out, dtype=np.float32)
+        oracle_lib().yo_scale_channels_forward(np.ascontiguousarray(from_out, np.float32).reshape(-1),
+                                               np.ascontiguousarray(scale_in, np.float32).reshape(-1), B, Cc, H * W, ACT[act],
+                                               out.reshape(-1))
+        return out
+
+    @staticmethod
+    def scale_channels_backward(delta, out, from_out, scale_in, act="linear", d_scale_in=None, d_from=None):
+        """BackwardScaleChannelsLayer: returns (delta after gradient_array, d_scale_in [B,C], d_from [B,C,H,W]); the two
+        gradients ACCUMULATE onto the arrays passed in."""
+        B, Cc, H, W = from_out.shape
+        d = np.ascontiguousarray(delta, np.float32).copy()
+        ds = np.zeros((B, Cc), np.float32) if d_scale_in is None else np.ascontiguousarray(d_scale_in, np.float32).copy()
+        df = np.zeros(from_out.shape, np.float32) if d_from is None else np.ascontiguousarray(d_from, np.float32).copy()
+        oracle_lib().yo_scale_channels_backward(d.reshape(-1), np.ascontiguousarray(out, np.float32).reshape(-1), ACT[act],
+                                                np.ascontiguousarray(from_out, np.float32).reshape(-1),
+                                                np.ascontiguousarray(scale_in, np.float32).reshape(-1), B, Cc, H * W,
+                                                ds.reshape(-1), df.reshape(-1))
+        return d, ds, df
+
+    @staticmethod
+    def reorg(x, stride, forward=0):
+        """reorg_cpu on [B,C,H,W]: forward=0 (what a [reorg] layer's forward uses) -> [B, C*s*s, H/s, W/s]; forward=1 is the
+        inverse scatter."""
+        B, Cc, H, W = x.shape
+        s2 = stride * stride
+        if forward:
+            oc, oh, ow = Cc, H, W                       # reorg_cpu is told the SMALL tensor's dims
+            out = np.zeros((B, Cc // s2, H * stride, W * stride), np.float32)
+        else:
+            oc, oh, ow = Cc * s2, H // stride, W // stride
+            out = np.zeros((B, oc, oh, ow), np.float32)
+        oracle_lib().yo_reorg(np.ascontiguousarray(x, np.float32).reshape(-1), ow, oh, oc, B, stride, forward, out.reshape(-1))
         return out
 
     @staticmethod

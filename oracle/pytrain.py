@@ -67,6 +67,18 @@ def yolo_loss(out, truth, anchors, mask, opts, net_w, net_h):
 class Step:
     """State of one network across training steps (weights, momentum accumulators)."""
 
+    def _ref_net(self):
+        """the compiled reference's network of the same cfg in training mode (only its loss layers are used)"""
+        if getattr(self, "_ref", None) is None:
+            import os
+            import tempfile
+            from oracle import pyoracle
+            fd, path = tempfile.mkstemp(suffix=".cfg", prefix="yc_walker_")
+            with os.fdopen(fd, "w") as f:
+                f.write(self.text)
+            self._ref = pyoracle.RefNet(path, None, train=True)
+        return self._ref
+
     def __init__(self, text, weights, emulate_bf16=False, dgrad_accumulate=False):
         self.text = text
         self.net, self.layers = cfgmod.walk_shapes(text)
@@ -163,10 +175,10 @@ class Step:
                     [out[j][:, (out[j].shape[1] // g) * gid:(out[j].shape[1] // g) * (gid + 1)] for j in L.inputs], axis=1))
             elif L.kind == "shortcut":
                 cur = self.r(O.shortcut(out[i - 1], out[L.inputs[1]], L.activation))
-            elif L.kind == "yolo":
+            elif L.kind in ("yolo", "Gaussian_yolo"):
                 mask = [int(v) for v in L.opts["mask"].split(",")]
-                anchors = [float(v) for v in L.opts["anchors"].split(",")]
-                dec = O.yolo_decode(out[i - 1], len(mask), int(L.opts["classes"]), float(L.opts.get("scale_x_y", 1)))
+                dec = O.yolo_decode(out[i - 1], len(mask), int(L.opts["classes"]), float(L.opts.get("scale_x_y", 1)),
+                                    gaussian=L.kind == "Gaussian_yolo")
                 cur = dec
             else:
                 raise ValueError(L.kind)
@@ -185,13 +197,18 @@ class Step:
                 anchors = [float(v) for v in L.opts["anchors"].split(",")]
                 delta[L.index], cost = yolo_loss(out[L.index], truth, anchors, mask, L.opts, self.net_w, self.net_h)
                 costs.append(cost)
+            elif L.kind == "Gaussian_yolo":
+                # no restatement of the Gaussian loss exists: the UNMODIFIED reference's own layer runs on the head
+                # logits this walker holds (ForwardGaussianYoloLayer(train), gaussian_yolo_layer.cpp:486-857)
+                _, delta[L.index], cost = self._ref_net().layer_forward_train(L.index, out[L.index - 1], truth)
+                costs.append(cost)
         for L in Ls:  # network.cpp:108-109: every layer's delta starts at zero
             if delta[L.index] is None:
                 delta[L.index] = np.zeros_like(out[L.index], dtype=np.float32)
         # ---- BackwardNetwork (network.cpp:162-186) ----
         for L in reversed(Ls):
             i = L.index
-            if L.kind == "yolo":      # BackwardYoloLayer: prev.delta += delta
+            if L.kind in ("yolo", "Gaussian_yolo"):      # BackwardYoloLayer: prev.delta += delta
                 delta[i - 1] = self.r(delta[i - 1] + delta[i])
             elif L.kind in ("convolutional", "conv"):
                 p, s = self.P[i], saved[i]

@@ -76,6 +76,19 @@ void ref_free(void* h) {
 }
 
 int ref_num_layers(void* h) { return ((RefNet*)h)->net.n; }
+// raw pointers to the reference's own structs (tests of the drop-in boundary hand them to libyolo_core_b200.so's
+// trampolines: `layer*` parsed by the reference, `forward_gpu` installed by the shim) and their sizes as compiled here
+void* ref_network_ptr(void* h) { return &((RefNet*)h)->net; }
+void* ref_layer_ptr(void* h, int i) { return &((RefNet*)h)->net.layers[i]; }
+int ref_sizeof(int what) {
+  switch (what) {
+    case 0: return (int)sizeof(layer);
+    case 1: return (int)sizeof(Network);
+    case 2: return (int)sizeof(NetworkState);
+    case 3: return (int)sizeof(Detection);
+  }
+  return -1;
+}
 int ref_net_dim(void* h, int which) {
   Network* n = &((RefNet*)h)->net;
   switch (which) { case 0: return n->w; case 1: return n->h; case 2: return n->c; case 3: return n->batch;
@@ -191,6 +204,68 @@ int ref_get_boxes(void* h, float thresh, float nms_thresh, int nms_kind, float b
   }
   FreeDetections(dets, n);
   return n;
+}
+
+// ForwardScaleChannelsLayer / BackwardScaleChannelsLayer (scale_channels_layer.c:72-131) and reorg_cpu (blas.c:12-46)
+// on caller-provided arrays: a two-layer Network is put together by hand (layers[0] = the `from` layer, layers[1] =
+// the [scale_channels] layer) and the reference's own functions run on it.
+}
+#include "scale_channels_layer.h"
+extern "C" {
+void ref_scale_channels(const float* from_out, const float* scale_in, int B, int C, int H, int W, int act, float* out,
+                        float* delta /* in: l->delta, out: after gradient_array; NULL = forward only */,
+                        float* d_scale_in, float* d_from) {
+  Network net;
+  memset(&net, 0, sizeof(net));
+  layer ls[2];
+  memset(ls, 0, sizeof(ls));
+  net.n = 2;
+  net.layers = ls;
+  ls[0].output = (float*)from_out;
+  ls[0].delta = d_from;
+  ls[0].out_w = W; ls[0].out_h = H; ls[0].out_c = C;
+  layer* l = &ls[1];
+  l->type = SCALE_CHANNELS;
+  l->batch = B; l->out_c = C; l->out_h = H; l->out_w = W;
+  l->outputs = C * H * W;
+  l->index = 0;
+  l->scale_wh = 0;
+  l->activation = (ACTIVATION)act;
+  l->output = out;
+  l->delta = delta;
+  NetworkState st;
+  memset(&st, 0, sizeof(st));
+  st.net = &net;
+  st.index = 1;
+  st.input = (float*)scale_in;
+  st.delta = d_scale_in;
+  ForwardScaleChannelsLayer(l, st);
+  if (delta) BackwardScaleChannelsLayer(l, st);
+}
+void ref_reorg(const float* x, int ow, int oh, int oc, int batch, int stride, int forward, float* out) {
+  reorg_cpu((float*)x, ow, oh, oc, batch, stride, forward, out);
+}
+
+// One layer's own CPU forward in training mode on a caller-provided input (used for the loss half of
+// ForwardYoloLayer / ForwardGaussianYoloLayer, yolo_layer.cpp:388-772, gaussian_yolo_layer.cpp:486-857, on a head tensor
+// that another implementation produced): l->forward(l, state) with state.input = input, state.truth = truth,
+// state.train = 1; copies l->output and l->delta out and returns *l->cost.
+float ref_layer_forward_train(void* h, int i, const float* input, const float* truth, float* out, float* delta) {
+  RefNet* r = (RefNet*)h;
+  layer* l = &r->net.layers[i];
+  NetworkState st;
+  memset(&st, 0, sizeof(st));
+  st.net = &r->net;
+  st.index = i;
+  st.input = (float*)input;
+  st.truth = (float*)truth;
+  st.train = 1;
+  if (l->delta) memset(l->delta, 0, sizeof(float) * (size_t)l->outputs * l->batch);  // network.cpp:108-109
+  l->forward(l, st);
+  const size_t n = (size_t)l->outputs * l->batch;
+  if (out) memcpy(out, l->output, n * sizeof(float));
+  if (delta && l->delta) memcpy(delta, l->delta, n * sizeof(float));
+  return l->cost ? *l->cost : 0.f;
 }
 
 // NmsSort — reference box.cpp:393-419 on caller-provided detections.  boxes: [n][4] (x y w h), obj: [n],

@@ -241,6 +241,25 @@ void yo_scale_channels(const float* in, const float* scale, int B, int C, int HW
   for (long long i = 0; i < n; ++i) out[i] = scale[i / HW] * in[i];
 }
 
+/* ForwardScaleChannelsLayer incl. the activation (scale_channels_layer.c:72-97, scale_wh = 0):
+ * out = act(scale_in[b,c] * from_out[b,c,h,w]) */
+void yo_scale_channels_forward(const float* from_out, const float* scale_in, int B, int C, int HW, int act, float* out) {
+  yo_scale_channels(from_out, scale_in, B, C, HW, out);
+  yo_activate(out, (long long)B * C * HW, act);
+}
+
+/* BackwardScaleChannelsLayer (scale_channels_layer.c:99-131, scale_wh = 0): gradient_array on the OUTPUT modifies
+ * delta in place; d_scale_in[b,c] += sum_hw delta * from_out; d_from += scale_in[b,c] * delta. */
+void yo_scale_channels_backward(float* delta, const float* out, int act, const float* from_out, const float* scale_in,
+                                int B, int C, int HW, float* d_scale_in, float* d_from) {
+  long long n = (long long)B * C * HW;
+  yo_gradient(out, n, act, delta);
+  for (long long i = 0; i < n; ++i) {
+    d_scale_in[i / HW] += delta[i] * from_out[i];
+    d_from[i] += scale_in[i / HW] * delta[i];
+  }
+}
+
 /* ---- YOLO head -------------------------------------------------------------------------------- */
 static float logistic1(float x) { return 1.f / (1.f + expf(-x)); }
 

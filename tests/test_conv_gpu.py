@@ -115,6 +115,14 @@ def test_conv_plan_switches(gpu):
     _run(gpu, 4, 32, 38, 38, 64, 3, 2, "leaky", plan_flags=L.PLAN_NO_W_RES, want_variant=(8, 0))
     _run(gpu, 2, 128, 19, 19, 128, 1, 1, "mish", plan_flags=L.PLAN_ONE_OUT_BUF, want_variant=(32, 0))
     _run(gpu, 2, 128, 19, 19, 128, 1, 1, "mish", residual=True, plan_flags=L.PLAN_ONE_OUT_BUF, want_variant=(32, 0))
-    _run(gpu, 2, 128, 19, 19, 128, 1, 1, "mish", residual=True, want_variant=(32, 32))
+    _run(gpu, 2, 128, 19, 19, 128, 1, 1, "mish", residual=True, plan_flags=L.PLAN_TWO_OUT_BUFS, want_variant=(32, 32))
+    _run(gpu, 2, 128, 19, 19, 128, 1, 1, "mish", plan_flags=L.PLAN_TWO_OUT_BUFS, want_variant=(32, 32))
+    # the generic epilogue (what fp32 heads, unfused batchnorm and training statistics use) on a layer the specialised one
+    # would take, and the specialised one with the generic warp-to-tile assignment
+    _run(gpu, 2, 128, 19, 19, 128, 1, 1, "mish", residual=True, plan_flags=L.PLAN_GENERIC_EPI, want_variant=(128, 0))
+    _run(gpu, 4, 64, 38, 38, 64, 3, 1, "leaky", plan_flags=L.PLAN_GENERIC_EPI | L.PLAN_FORCE_HALO, want_variant=(128 | 3, 2))
+    _run(gpu, 2, 128, 19, 19, 256, 1, 1, "leaky", plan_flags=L.PLAN_EPI_SETS_V1, want_variant=(128, 128))
+    _run(gpu, 2, 128, 19, 19, 256, 1, 1, "leaky", want_variant=(128, 128))
+    _run(gpu, 8, 1024, 19, 19, 512, 1, 1, "leaky", want_variant=(128, 128))   # bias from global memory (no free shared memory)
     _run(gpu, 8, 512, 19, 19, 512, 3, 1, "leaky", plan_flags=L.PLAN_COST_V1)
     _run(gpu, 8, 512, 19, 19, 512, 3, 1, "leaky")

@@ -106,3 +106,65 @@ def test_stem_im2col_operand_bit_exact(gpu, B, H, W, stride):
     L.check(L.lib().yc_stem_im2col(xd.data_ptr(), 3, H, W, 3, stride, 1, C.byref(t), L.stream_ptr()), "yc_stem_im2col")
     torch.cuda.synchronize()
     assert np.array_equal(out.float().cpu().numpy(), ref)
+
+
+@pytest.mark.parametrize("act", ["linear", "leaky", "logistic"])
+@pytest.mark.parametrize("B,C,H,W", [(2, 64, 13, 13), (3, 24, 5, 7), (1, 256, 19, 19)])
+def test_scale_channels_fwd_bwd(gpu, act, B, C, H, W):
+    """ForwardScaleChannelsLayerGpu / BackwardScaleChannelsLayerGpu (scale_channels_layer.c:134-160) vs the restatement
+    (pinned to the reference by tests/test_oracle_pin.py).  Inputs are bf16-representable, so what is left is the bf16
+    rounding of the stored results: 1e-2 relative; the channel sums are fp32 in a fixed order."""
+    from darknet_b200 import ops
+    rng = np.random.default_rng(C + H)
+    r16 = lambda a: torch.from_numpy(a).to(torch.bfloat16).float().numpy()
+    x = r16(rng.standard_normal((B, C, H, W)).astype(np.float32))
+    s = r16(rng.uniform(0.1, 2.0, (B, C)).astype(np.float32))
+    dy = r16(rng.standard_normal((B, C, H, W)).astype(np.float32))
+    ds0 = r16(rng.standard_normal((B, C)).astype(np.float32))
+    dx0 = r16(rng.standard_normal((B, C, H, W)).astype(np.float32))
+    y_ref = O.scale_channels(x, s, act)
+    xd = ops.to_nhwc(torch.from_numpy(x).to(gpu))
+    sd = ops.to_nhwc(torch.from_numpy(s.reshape(B, C, 1, 1)).to(gpu))
+    yd = ops.scale_channels(xd, sd, C, act)
+    y = ops.to_nchw(yd, C).cpu().numpy()
+    assert np.abs(y - y_ref).max() <= 1e-2 * np.abs(y_ref).max()
+    # backward on the GPU's own (bf16) output, like the layer does
+    d_ref, ds_ref, dx_ref = O.scale_channels_backward(dy, y, x, s, act, ds0, dx0)
+    dyd = ops.to_nhwc(torch.from_numpy(dy).to(gpu))
+    dsd = ops.to_nhwc(torch.from_numpy(ds0.reshape(B, C, 1, 1)).to(gpu))
+    dxd = ops.to_nhwc(torch.from_numpy(dx0).to(gpu))
+    ops.scale_channels_bwd(dyd, yd, xd, sd, dsd, dxd, C, act)
+    torch.cuda.synchronize()
+    d = ops.to_nchw(dyd, C).cpu().numpy()
+    ds = ops.to_nchw(dsd, C).cpu().numpy().reshape(B, C)
+    dx = ops.to_nchw(dxd, C).cpu().numpy()
+    assert np.abs(d - d_ref).max() <= 1e-2 * np.abs(d_ref).max()
+    assert np.abs(dx - dx_ref).max() <= 1e-2 * np.abs(dx_ref).max()
+    # ds: the kernel sums the bf16-rounded dy*act' in fp32 and stores bf16
+    assert np.abs(ds - ds_ref).max() <= 1.5e-2 * np.abs(ds_ref).max()
+
+
+@pytest.mark.parametrize("stride", [2, 4])
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
+def test_reorg_fwd_bwd_bit_exact(gpu, stride, dtype):
+    """ForwardReorgLayerGpu / BackwardReorgLayerGpu (reorg_layer.c:113-143): pure data movement, bit-exact against
+    reorg_cpu's index math (fp32 tensors: exact; bf16 tensors: exact on bf16-representable inputs)."""
+    from darknet_b200 import ops
+    rng = np.random.default_rng(stride)
+    B, C, H, W = 2, 6, 8 * stride, 4 * stride
+    x = rng.standard_normal((B, C, H, W)).astype(np.float32)
+    td = torch.float32 if dtype == "f32" else torch.bfloat16
+    if dtype == "bf16":
+        x = torch.from_numpy(x).to(torch.bfloat16).float().numpy()
+    want = O.reorg(x, stride, 0)
+    xd = ops.to_nhwc(torch.from_numpy(x).to(gpu), dtype=td)
+    yd, oc = ops.reorg(xd, C, stride, 0)
+    got = ops.to_nchw(yd, oc).cpu().numpy()
+    assert got.shape == want.shape and np.array_equal(got, want)
+    dy = rng.standard_normal(want.shape).astype(np.float32)
+    if dtype == "bf16":
+        dy = torch.from_numpy(dy).to(torch.bfloat16).float().numpy()
+    dyd = ops.to_nhwc(torch.from_numpy(dy).to(gpu), dtype=td)
+    dxd, ic = ops.reorg_bwd(dyd, oc, stride, 0)
+    dx = ops.to_nchw(dxd, ic).cpu().numpy()
+    assert ic == C and np.array_equal(dx, O.reorg(dy, stride, 1))

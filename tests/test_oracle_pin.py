@@ -97,3 +97,49 @@ def test_detections_and_nms_match_reference(built):
     b = sorted((tuple(np.round(r7n[i, :4], 3)), int(c)) for i in range(r7n.shape[0]) for c in np.nonzero(rprobsn[i] > 0)[0])
     assert a == b
     ref.close()
+
+
+
+@pytest.mark.parametrize("act", ["linear", "leaky", "logistic"])
+def test_scale_channels_restatement_vs_reference(act):
+    """ForwardScaleChannelsLayer / BackwardScaleChannelsLayer (scale_channels_layer.c:72-131) — the reference's own
+    functions on a hand-built two-layer network vs oracle/yc_oracle.c (bit for bit where no libm call is involved)."""
+    import ctypes as C
+    rng = np.random.default_rng(3)
+    B, Cc, H, W = 2, 24, 5, 7
+    from_out = rng.standard_normal((B, Cc, H, W)).astype(np.float32)
+    scale_in = rng.uniform(0.1, 2.0, (B, Cc)).astype(np.float32)
+    delta = rng.standard_normal((B, Cc, H, W)).astype(np.float32)
+    ds0 = rng.standard_normal((B, Cc)).astype(np.float32)     # the gradients ACCUMULATE onto what is there
+    df0 = rng.standard_normal((B, Cc, H, W)).astype(np.float32)
+    out = O.scale_channels(from_out, scale_in, act)
+    d, ds, df = O.scale_channels_backward(delta, out, from_out, scale_in, act, ds0, df0)
+    r_out = np.zeros_like(out)
+    r_d, r_ds, r_df = delta.copy(), ds0.copy(), df0.copy()
+    vp = lambda a: a.ctypes.data_as(C.c_void_p)
+    pyoracle.ref_lib().ref_scale_channels(from_out.reshape(-1), scale_in.reshape(-1), B, Cc, H, W, pyoracle.ACT[act],
+                                          r_out.reshape(-1), vp(r_d), vp(r_ds), vp(r_df))
+    if act == "logistic":   # the reference is built with -Ofast: its expf differs from libm's in the last bits
+        np.testing.assert_allclose(out, r_out, rtol=2e-6, atol=1e-6)
+        np.testing.assert_allclose(d, r_d, rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(df, r_df, rtol=1e-5, atol=1e-6)
+    else:
+        assert np.array_equal(out, r_out)
+        assert np.array_equal(d, r_d) and np.array_equal(df, r_df)
+    np.testing.assert_allclose(ds, r_ds, rtol=1e-5, atol=1e-5)   # -Ofast may reassociate the channel sums
+
+
+
+@pytest.mark.parametrize("stride,forward", [(2, 0), (2, 1), (4, 0)])
+def test_reorg_restatement_vs_reference(stride, forward):
+    rng = np.random.default_rng(4)
+    B, Cc, H, W = 2, 3 * (stride * stride if forward else 1), 8, 8
+    x = rng.standard_normal((B, Cc, H, W)).astype(np.float32)
+    got = O.reorg(x, stride, forward)
+    s2 = stride * stride
+    oc, oh, ow = (Cc, H, W) if forward else (Cc * s2, H // stride, W // stride)
+    want = np.zeros_like(got)
+    pyoracle.ref_lib().ref_reorg(x.reshape(-1), ow, oh, oc, B, stride, forward, want.reshape(-1))
+    assert np.array_equal(got, want)
+    if not forward:  # BackwardReorgLayer = the inverse rearrangement: round trip is the identity
+        assert np.array_equal(O.reorg(got, stride, 1), x)

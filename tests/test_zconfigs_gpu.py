@@ -77,13 +77,22 @@ def _heads_of(net_or_ref, yolo_layers, outs, classes, gaussian):
     return [(li, outs[li], 3, classes, gaussian) for li in yolo_layers]
 
 
-def _detections(name, B, hw, thresh, head_bias, head_gain, nms=0.45, dense_images=None, max_undecided=0.25, **kw):
+def _detections(name, B, hw, thresh, head_bias, head_gain, nms=0.45, box_gain=8.0, identity_images=None, interval_images=None,
+                max_undecided=0.25, max_mismatch=0.02, **kw):
     """Every image of a batch through yc_network_predict + yc_network_detect against GetNetworkBoxes + NmsSort of the
-    reference run on the same image.  Index identity by tests/detutil.py."""
-    from darknet_b200 import network as N
-    text, cpath, wpath = materialise(name, head_bias=head_bias, head_gain=head_gain, w=hw, h=hw, **kw)
+    reference run on the same image (the reference reads batch element 0 only, so it runs image by image).
+
+    Per image, by INDEX (image, yolo layer, anchor, cell, class) — tests/detutil.py:
+      * candidates / classes / boxes: identical outside the margin band (margin 0.01 on scores: 1.6x the largest score
+        deviation measured on these nets, 6e-3);
+      * post-NMS, direct: the reference's NmsSort runs on the reference's candidates, ours ran inside yc_network_detect;
+        the two survivor sets are compared entry by entry, at most `max_mismatch` of them may differ (a flipped
+        in-band score cascades through greedy suppression);
+      * post-NMS, interval: every entry the reference keeps / suppresses whatever the rounding must be kept / suppressed by
+        us (no tolerance), and the undecided share is bounded where the regime has confident scores."""
+    from darknet_b200 import lib as L, network as N
+    text, cpath, wpath = materialise(name, head_bias=head_bias, head_gain=head_gain, box_gain=box_gain, w=hw, h=hw, **kw)
     x = cfgmod.synth_images(B, 3, hw, hw, seed=99)
-    from darknet_b200 import lib as L
     net = N.LoadNetwork(cpath, wpath, batch=B, flags=L.NET_DEFAULT | L.NET_REF_CPU_MAXPOOL)
     N.NetworkPredict(net, x)
     yl = net.yolo_layers()
@@ -94,14 +103,15 @@ def _detections(name, B, hw, thresh, head_bias, head_gain, nms=0.45, dense_image
     assert np.array_equal(counts, counts2)
     ours_heads = {li: N.yolo_output(net, li).copy() for li in yl}
     ref = pyoracle.RefNet(cpath, wpath, train=False, fuse=True)
-    tot = dict(ref=0, ours=0, common=0, in_band=0, kept=0, undecided=0, suppressed=0)
+    tot = dict(ref=0, ours=0, common=0, in_band=0, kept=0, undecided=0, suppressed=0, survivors=0, mismatched=0)
     mx = dict(max_dscore=0.0, max_dobj=0.0, max_dxy=0.0, max_dwh_rel=0.0)
     off = 0
-    images = range(B) if dense_images is None else range(min(B, dense_images))
+    n_id = B if identity_images is None else min(B, identity_images)
+    n_iv = n_id if interval_images is None else min(n_id, interval_images)
     for b in range(B):
         mine_pre, mine_post = pre_rows[off:off + counts[b]], post_rows[off:off + counts[b]]
         off += counts[b]
-        if b not in images:
+        if b >= n_id:
             continue
         ref.predict(x[b:b + 1])
         r7, rprobs = ref.boxes(thresh, 0.0)
@@ -113,16 +123,24 @@ def _detections(name, B, hw, thresh, head_bias, head_gain, nms=0.45, dense_image
         assert oids.shape[0] == mine_pre.shape[0], (oids.shape, mine_pre.shape)
         assert np.array_equal(oobj, mine_pre[:, 5]) and np.all(mine_pre[:, 0] == b) and np.array_equal(oids[:, 0], mine_pre[:, 6].astype(np.int32))
         st = detutil.compare_image(rids, r7[:, :5], rprobs, oids, mine_pre[:, 1:6], mine_pre[:, 7:], mine_post[:, 7:],
-                                   thresh, nms)
+                                   thresh, nms if b < n_iv else 0.0, margin=0.01, iou_margin=0.03)
+        # direct identity of the post-NMS sets
+        rafter, _ = pyoracle.ref_nms(r7[:, :4], r7[:, 4], rprobs, nms)
+        rset = {(int(rids[i, 0]), int(rids[i, 1]), int(rids[i, 2]), int(c)) for i, c in np.argwhere(rafter > 0)}
+        oset = {(int(oids[i, 0]), int(oids[i, 1]), int(oids[i, 2]), int(c)) for i, c in np.argwhere(mine_post[:, 7:] > 0)}
+        st["survivors"] = len(rset)
+        st["mismatched"] = len(rset ^ oset)
         for k in tot:
             tot[k] += st.get(k, 0)
         for k in mx:
             mx[k] = max(mx[k], st.get(k, 0.0))
     decided = tot["kept"] + tot["suppressed"] + tot["undecided"]
-    print(f"{name} {hw} batch {B} thresh {thresh} (head bias {head_bias} gain {head_gain}): {len(list(images))} images, "
-          f"{tot}, {({k: round(v, 5) for k, v in mx.items()})}")
-    assert tot["ref"] > 0 and decided > 0, "vacuous: the reference found no detections"
-    assert tot["undecided"] <= max_undecided * decided, f"too many undecided NMS outcomes: {tot}"
+    print(f"{name} {hw} batch {B} thresh {thresh} (head bias {head_bias} gain {head_gain}): identity on {n_id} images, interval NMS on "
+          f"{n_iv}: {tot}, {({k: round(v, 5) for k, v in mx.items()})}")
+    assert tot["ref"] > 0 and tot["survivors"] > 0, "vacuous: the reference found no detections"
+    assert tot["mismatched"] <= max_mismatch * tot["survivors"], f"post-NMS sets differ: {tot}"
+    if max_undecided is not None:
+        assert decided > 0 and tot["undecided"] <= max_undecided * decided, f"too many undecided NMS outcomes: {tot}"
     ref.close()
     net.close()
     return tot
@@ -155,13 +173,22 @@ def test_yolov4_608_all_layers_plain_plan(gpu):
     _all_layers("yolov4", 2, 608, flags, want=want)
 
 
+def test_yolov4_608_b64_detections(gpu):
+    """Heads spread like a trained net's (gain 200 on objectness / classes, bias -20: a few hundred candidates per image,
+    three quarters of them with objectness > 0.5), all 64 images."""
+    _detections("yolov4", 64, 608, 0.25, head_bias=-20.0, head_gain=200.0, interval_images=16)
+
+
 def test_yolov4_608_b64_detections_sparse(gpu):
-    _detections("yolov4", 64, 608, 0.25, head_bias=-6.0, head_gain=40.0, max_undecided=0.1)
+    """The regime bench.py times (objectness bias -6, gain 40): one candidate per image, scores just above the threshold."""
+    _detections("yolov4", 64, 608, 0.25, head_bias=-6.0, head_gain=40.0, box_gain=None, max_undecided=None)
 
 
 def test_yolov4_608_b64_detections_dense(gpu):
-    """thresh 0.25 on spread heads: hundreds of candidates per image; index identity on every image, interval NMS on 8."""
-    _detections("yolov4", 64, 608, 0.25, head_bias=-3.0, head_gain=40.0, dense_images=8)
+    """thresh 0.25 with every cell of an anchor above it: ~6000 candidates and ~260000 class scores per image, boxes of
+    neighbouring cells overlapping heavily (the NMS stress case of SURVEY 8d)."""
+    _detections("yolov4", 64, 608, 0.25, head_bias=-3.0, head_gain=40.0, identity_images=4, interval_images=1,
+                max_undecided=None)
 
 
 # ---------------------------------------------------------------- configs[1]: yolov3 416 ---------------------------
@@ -171,8 +198,8 @@ def test_yolov3_416_all_layers(gpu):
 
 
 def test_yolov3_416_b64_detections(gpu):
-    _detections("yolov3", 64, 416, 0.25, head_bias=-5.0, head_gain=40.0, max_undecided=0.1)
-    _detections("yolov3", 64, 416, 0.25, head_bias=-3.0, head_gain=40.0, dense_images=6)
+    _detections("yolov3", 64, 416, 0.25, head_bias=-22.0, head_gain=200.0, interval_images=16)
+    _detections("yolov3", 64, 416, 0.25, head_bias=-3.0, head_gain=40.0, identity_images=4, interval_images=1, max_undecided=None)
 
 
 # ---------------------------------------------------------------- configs[4]: Gaussian-yolov3 608 ------------------
@@ -182,7 +209,7 @@ def test_gaussian_yolov3_608_all_layers(gpu):
 
 
 def test_gaussian_yolov3_608_detections(gpu):
-    _detections("gaussian-yolov3", 4, 608, 0.25, head_bias=-4.0, head_gain=40.0)
+    _detections("gaussian-yolov3", 4, 608, 0.25, head_bias=-21.0, head_gain=200.0, interval_images=2)
 
 
 def test_gaussian_yolov3_320_train_step(gpu):
