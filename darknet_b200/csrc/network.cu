@@ -48,7 +48,10 @@ int build_layers(yc_network* net, const std::string& text, int batch) {
   std::string err;
   if (!parse_cfg_text(text, secs, err)) NET_FAIL(YC_ERR_PARSE, "%s", err.c_str());
   const Section& n0 = secs[0];
-  net->batch = batch > 0 ? batch : n0.get_int("batch", 1);
+  net->subdivisions = std::max(1, n0.get_int("subdivisions", 1));
+  // ParseNetOptions (parser.cpp:926-928): the network's batch is the MINI-batch, [net] batch / subdivisions; an explicit
+  // `batch` argument is the mini-batch itself (the reference's inference path forces it to 1, parser.cpp:1114-1115)
+  net->batch = batch > 0 ? batch : std::max(1, n0.get_int("batch", 1) / net->subdivisions);
   net->w = n0.get_int("width", 0);
   net->h = n0.get_int("height", 0);
   net->c = n0.get_int("channels", 0);
@@ -56,7 +59,26 @@ int build_layers(yc_network* net, const std::string& text, int batch) {
   net->lr = n0.get_float("learning_rate", .001f);   // ParseNetOptions parser.cpp:1116-1140
   net->momentum = n0.get_float("momentum", .9f);
   net->decay = n0.get_float("decay", .0001f);
-  net->subdivisions = n0.get_int("subdivisions", 1);
+  {  // learning-rate schedule (parser.cpp:944-995, 1028)
+    const std::string pol = n0.get_str("policy", "constant");
+    const char* names[] = {"constant", "step", "exp", "poly", "steps", "sigmoid", "random", "sgdr"};
+    net->policy = 0;
+    for (int k = 0; k < 8; ++k)
+      if (pol == names[k]) net->policy = k;
+    net->lr_min = n0.get_float("learning_rate_min", .00001f);
+    net->burn_in = n0.get_int("burn_in", 0);
+    net->power = n0.get_float("power", 4.f);
+    net->step = n0.get_int("step", 1);
+    net->scale = n0.get_float("scale", 1.f);
+    net->gamma = n0.get_float("gamma", 1.f);
+    net->sgdr_cycle = n0.get_int("sgdr_cycle", 0);
+    net->sgdr_mult = n0.get_int("sgdr_mult", 2);
+    net->steps = parse_float_list(n0.get_str("steps", ""));
+    net->scales = parse_float_list(n0.get_str("scales", ""));
+    if (net->policy == 4 && (net->steps.empty() || net->scales.size() < net->steps.size()))
+      NET_FAIL(YC_ERR_PARSE, "STEPS policy must have steps and scales in cfg file");  // parser.cpp:963-964
+    net->max_iter = n0.get_int("max_batches", 0);  // the reference's driver derives max_iter from max_epoch; see yc_network_set_schedule
+  }
   int c = net->c, h = net->h, w = net->w;
   for (size_t si = 1; si < secs.size(); ++si) {
     const Section& s = secs[si];
@@ -179,12 +201,27 @@ int build_layers(yc_network* net, const std::string& text, int batch) {
     } else {
       NET_FAIL(YC_ERR_ARG, "layer %d: [%s] is outside the conv/YOLO hot path this library replaces", idx, s.name.c_str());
     }
+    // training gates, parsed for every layer type (parser.cpp:1362-1366)
+    L.onlyforward = s.get_int("onlyforward", 0);
+    L.dont_update = s.get_int("dont_update", 0);
+    L.burnin_update = s.get_int("burnin_update", 0);
+    L.stopbackward = s.get_int("stopbackward", 0);
+    L.train_only_bn = s.get_int("train_only_bn", 0);
     if (idx == 0 && L.type != L_CONV) NET_FAIL(YC_ERR_ARG, "the first layer must be convolutional");
     if (L.out_h <= 0 || L.out_w <= 0) NET_FAIL(YC_ERR_ARG, "layer %d: empty output", idx);
     net->layers.push_back(std::move(L));
     c = net->layers.back().out_c; h = net->layers.back().out_h; w = net->layers.back().out_w;
   }
   if (net->layers.empty()) NET_FAIL(YC_ERR_PARSE, "cfg has no layers");
+  {  // SetTrainOnlyBn (parser.cpp:1062-1074): a train_only_bn mark applies to every EARLIER layer as well
+    int mark = 0;
+    for (int i = (int)net->layers.size() - 1; i >= 0; --i) {
+      if (net->layers[i].train_only_bn) mark = net->layers[i].train_only_bn;
+      if (mark) net->layers[i].train_only_bn = mark;
+    }
+  }
+  for (const NLayer& L : net->layers)
+    if (L.dont_update || L.burnin_update || L.train_only_bn) net->any_gate = true;
   return YC_OK;
 }
 
@@ -194,11 +231,20 @@ int load_weights_file(yc_network* net, const char* path) {
   if (!fp) NET_FAIL(YC_ERR_IO, "cannot open weights file %s", path);
   int hdr[3];
   uint64_t seen = 0;
-  bool ok = fread(hdr, sizeof(int), 3, fp) == 3 && fread(&seen, sizeof(uint64_t), 1, fp) == 1;
-  for (size_t i = 0; ok && i < net->layers.size(); ++i) {
+  if (!(fread(hdr, sizeof(int), 3, fp) == 3 && fread(&seen, sizeof(uint64_t), 1, fp) == 1)) {
+    fclose(fp);
+    NET_FAIL(YC_ERR_IO, "weights file %s: bad header", path);
+  }
+  net->seen = (long long)seen;  // *net->seen (parser.cpp:1797-1806); curr_iter = seen / (batch * subdivisions)
+  net->curr_iter = (long long)(seen / (uint64_t)std::max(1, net->batch * net->subdivisions));
+  // LoadWeightsUpTo stops quietly at the end of the file (parser.cpp:1837): a backbone file such as yolov4.conv.137
+  // fills the first layers and leaves the rest at their initial values.  A file that ends INSIDE a layer is an error.
+  for (size_t i = 0; i < net->layers.size(); ++i) {
     NLayer& L = net->layers[i];
     if (L.type != L_CONV) continue;
-    ok = fread(L.biases.data(), 4, L.n, fp) == (size_t)L.n;
+    const size_t got = fread(L.biases.data(), 4, L.n, fp);
+    if (got == 0 && feof(fp)) break;  // clean end at a layer boundary
+    bool ok = got == (size_t)L.n;
     if (ok && L.bn) {
       ok = fread(L.scales.data(), 4, L.n, fp) == (size_t)L.n && fread(L.rmean.data(), 4, L.n, fp) == (size_t)L.n &&
            fread(L.rvar.data(), 4, L.n, fp) == (size_t)L.n;
@@ -206,11 +252,11 @@ int load_weights_file(yc_network* net, const char* path) {
     if (ok) ok = fread(L.weights.data(), 4, L.weights.size(), fp) == L.weights.size();
     if (!ok) {
       fclose(fp);
-      NET_FAIL(YC_ERR_IO, "weights file %s is truncated at layer %zu", path, i);
+      NET_FAIL(YC_ERR_IO, "weights file %s is truncated inside layer %zu", path, i);
     }
+    net->layers_loaded = (int)i + 1;
   }
   fclose(fp);
-  if (!ok) NET_FAIL(YC_ERR_IO, "weights file %s: bad header", path);
   return YC_OK;
 }
 
@@ -289,8 +335,16 @@ extern "C" int yc_network_finalize(yc_network* net) {
   }
   free_device_state(net);
   const int nl = (int)net->layers.size();
-  if (net->flags & YC_NET_TRAIN)  // training keeps batchnorm live and every layer's own output; ops run un-graphed
+  if (net->flags & YC_NET_TRAIN) {  // training keeps batchnorm live and every layer's own output; ops run un-graphed
     net->flags &= ~(YC_NET_FUSE_BN | YC_NET_FUSE_SHORTCUT | YC_NET_CUDA_GRAPH | YC_NET_PULL_HEADS);
+    // Default training semantics = the reference's GPU path, which this library replaces: the data gradient ADDS to the
+    // previous layer's delta (cudnnConvolutionBackwardData beta = 1, convolutional_kernels.cu:735-738) and the batchnorm
+    // shift is trained (backward_bias_gpu, batchnorm_layer.cpp:330).  YC_NET_TRAIN_REF_CPU selects the CPU path's
+    // behaviour instead (col2im overwrites, no gradient for the shift) — the mode the CPU oracle is
+    // compared in.
+    if (net->flags & YC_NET_TRAIN_REF_CPU) net->flags &= ~(YC_NET_DGRAD_ACCUMULATE | YC_NET_BN_BIAS_GRAD);
+    else net->flags |= YC_NET_DGRAD_ACCUMULATE | YC_NET_BN_BIAS_GRAD;
+  }
   const int flags = net->flags;
   auto& Ls = net->layers;
   if (!net->stream) NET_CUDA(cudaStreamCreateWithFlags(&net->stream, cudaStreamNonBlocking));
@@ -686,6 +740,119 @@ extern "C" int yc_network_set_conv_weights(yc_network* net, int layer, const flo
   return YC_OK;
 }
 
+
+// ---- weights on disk / initialisation / learning-rate schedule ---------------------------------------------------
+// In a training network the current values live on the device (master weights in fp32): bring them back into the
+// host-side copies the loader / saver / finalize work from (PullConvolutionalLayer, convolutional_kernels.cu:817-836).
+int yc_train_pull_params(yc_network* net);  // network_train.cu
+
+// LoadWeights (parser.cpp:1846-1850) on an already parsed network; call yc_network_finalize after.
+extern "C" int yc_network_load_weights(yc_network* net, const char* path) {
+  YC_REQUIRE(net && path, "yc_network_load_weights: null argument");
+  int rc = load_weights_file(net, path);
+  net->finalized = false;
+  return rc;
+}
+
+// SaveWeightsUpto (parser.cpp:1590-1643) + SaveConvolutionalWeights (:1545-1560): header major, minor, revision (int32)
+// and seen (uint64), then per conv layer biases, [scales, rolling_mean, rolling_variance], weights (OIHW fp32).
+extern "C" int yc_network_save_weights(yc_network* net, const char* path, int cutoff) {
+  YC_REQUIRE(net && path, "yc_network_save_weights: null argument");
+  if ((net->flags & YC_NET_TRAIN) && net->finalized) {
+    int rc = yc_train_pull_params(net);
+    if (rc) return rc;
+  }
+  FILE* fp = fopen(path, "wb");
+  if (!fp) NET_FAIL(YC_ERR_IO, "cannot open %s for writing", path);
+  const int hdr[3] = {0, 2, 5};  // MAJOR_VERSION, MINOR_VERSION, PATCH_VERSION (parser.cpp:1603-1609)
+  const uint64_t seen = (uint64_t)net->seen;
+  bool ok = fwrite(hdr, sizeof(int), 3, fp) == 3 && fwrite(&seen, sizeof(uint64_t), 1, fp) == 1;
+  const int n = cutoff > 0 ? std::min<int>(cutoff, (int)net->layers.size()) : (int)net->layers.size();
+  for (int i = 0; ok && i < n; ++i) {
+    const NLayer& L = net->layers[i];
+    if (L.type != L_CONV) continue;
+    ok = fwrite(L.biases.data(), 4, L.n, fp) == (size_t)L.n;
+    if (ok && L.bn)
+      ok = fwrite(L.scales.data(), 4, L.n, fp) == (size_t)L.n && fwrite(L.rmean.data(), 4, L.n, fp) == (size_t)L.n &&
+           fwrite(L.rvar.data(), 4, L.n, fp) == (size_t)L.n;
+    if (ok) ok = fwrite(L.weights.data(), 4, L.weights.size(), fp) == L.weights.size();
+  }
+  ok = (fclose(fp) == 0) && ok;
+  if (!ok) NET_FAIL(YC_ERR_IO, "short write to %s", path);
+  return YC_OK;
+}
+
+// FillConvLayer's initialisation (convolutional_layer.cpp:478-493): W = sqrt(2 / (k*k*c)) * RandUniform(-1, 1) with
+// RandUniform = (float)rand() / RAND_MAX * 2 - 1 (utils.cpp:368-383), biases 0, scales 1, rolling statistics 0.  With
+// srand(seed) and the same layer order the values are the reference's own, bit for bit, for every conv layer parsed
+// before the first [yolo] section (FillYoloLayer re-seeds from the clock, yolo_layer.cpp:86).  first_layer: layers
+// below it keep their values (what loading a backbone file and training the rest does).
+extern "C" int yc_network_init_weights(yc_network* net, unsigned seed, int first_layer) {
+  YC_REQUIRE(net, "yc_network_init_weights: null network");
+  srand(seed);
+  for (size_t i = 0; i < net->layers.size(); ++i) {
+    NLayer& L = net->layers[i];
+    if (L.type != L_CONV) continue;
+    const float scale = (float)sqrt(2. / (L.size * L.size * L.c));
+    if ((int)i < first_layer) {
+      for (size_t k = 0; k < L.weights.size(); ++k) (void)rand();  // keep the sequence aligned with a full initialisation
+      continue;
+    }
+    for (size_t k = 0; k < L.weights.size(); ++k) L.weights[k] = scale * (((float)rand() / RAND_MAX * 2.f) + -1.f);
+    std::fill(L.biases.begin(), L.biases.end(), 0.f);
+    if (L.bn) {
+      std::fill(L.scales.begin(), L.scales.end(), 1.f);
+      std::fill(L.rmean.begin(), L.rmean.end(), 0.f);
+      std::fill(L.rvar.begin(), L.rvar.end(), 0.f);
+    }
+  }
+  net->finalized = false;
+  return YC_OK;
+}
+
+// GetCurrLr (network.cpp:32-84).  max_iter <= 0 takes the value set by yc_network_set_schedule / [net] max_batches.
+extern "C" float yc_network_current_rate(const yc_network* net, long long iter, int max_iter) {
+  if (!net) return 0.f;
+  if (max_iter <= 0) max_iter = net->max_iter;
+  if (iter < net->burn_in) return net->lr * (float)pow((float)iter / net->burn_in, net->power);
+  switch (net->policy) {
+    case 0: return net->lr;
+    case 1: return net->lr * (float)pow(net->scale, iter / net->step);
+    case 4: {  // STEPS: the step positions are FRACTIONS of max_iter in this reference (network.cpp:49-58)
+      float lr = net->lr;
+      for (size_t i = 0; i < net->steps.size(); ++i) {
+        if (max_iter * net->steps[i] > iter) return lr;
+        lr *= net->scales[i];
+      }
+      return lr;
+    }
+    case 2: return net->lr * (float)pow(net->gamma, iter);
+    case 3: return net->lr * (float)pow(1 - (float)iter / max_iter, net->power);
+    case 6: return net->lr;  // RANDOM draws from rand(): not reproducible; the base rate is returned
+    case 5: return (float)(net->lr * (1. / (1. + exp(net->gamma * (iter - net->step)))));
+    case 7: {
+      int last_iter = 0;
+      int cycle = net->sgdr_cycle > 0 ? net->sgdr_cycle : max_iter;  // parser.cpp:957 (a zero cycle would never end)
+      if (cycle <= 0) return net->lr;
+      while (last_iter + cycle < iter) {
+        last_iter += cycle;
+        cycle *= net->sgdr_mult;
+      }
+      return net->lr_min + 0.5f * (net->lr - net->lr_min) * (1.0f + (float)cos((float)(iter - last_iter) * M_PI / cycle));
+    }
+  }
+  return net->lr;
+}
+
+// net->max_iter and net->curr_iter of the reference are owned by its training driver (detector.cpp); here the caller
+// sets them.  iter < 0 keeps the current iteration count (it advances by one per yc_network_update).
+extern "C" int yc_network_set_schedule(yc_network* net, int max_iter, long long iter) {
+  YC_REQUIRE(net, "yc_network_set_schedule: null network");
+  if (max_iter > 0) net->max_iter = max_iter;
+  if (iter >= 0) net->curr_iter = iter;
+  return YC_OK;
+}
+
 extern "C" int yc_network_info(const yc_network* net, int what) {
   if (!net) return -1;
   switch (what) {
@@ -697,6 +864,11 @@ extern "C" int yc_network_info(const yc_network* net, int what) {
     case 5: return net->n_conv;
     case 6: return (int)net->ops.size();
     case 7: return (int)net->yolo_layers.size();
+    case 8: return net->subdivisions;
+    case 9: return (int)std::min<long long>(net->curr_iter, 0x7fffffff);
+    case 10: return (int)std::min<long long>(net->seen, 0x7fffffff);
+    case 11: return net->layers_loaded;
+    case 12: return net->flags;
   }
   return -1;
 }

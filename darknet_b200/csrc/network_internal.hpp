@@ -56,6 +56,9 @@ struct NLayer {
   int dtype = YC_BF16;
   std::vector<std::pair<int, int>> copies;  // route fallback: (input layer, dst channel offset)
   int consumers = 0;
+  // per-layer training gates (parser.cpp:1362-1366; honoured by the backward / update loops, network_kernels.cu:140-143,
+  // 231-241)
+  int onlyforward = 0, dont_update = 0, burnin_update = 0, stopbackward = 0, train_only_bn = 0;
   // ---- training state (network_train.cu; allocated only with YC_NET_TRAIN) ----
   // yolo hyper-parameters (ParseYolo parser.cpp:312-415)
   int max_boxes = 90, iou_loss = 2 /*MSE*/, iou_thresh_kind = 0, focal_loss = 0;
@@ -131,6 +134,13 @@ struct yc_network {
   // ---- training (network_train.cu) ----
   float lr = .001f, momentum = .9f, decay = .0001f;  // [net] learning_rate / momentum / decay (parser.cpp:1116-1140)
   int subdivisions = 1;
+  // learning-rate schedule (ParseNetOptions parser.cpp:944-995, GetCurrLr network.cpp:32-84)
+  int policy = 0;  // 0 constant 1 step 2 exp 3 poly 4 steps 5 sigmoid 6 random 7 sgdr
+  int burn_in = 0, step = 1, max_iter = 0, sgdr_cycle = 0, sgdr_mult = 2;
+  float lr_min = .00001f, scale = 1.f, gamma = 1.f, power = 4.f;
+  std::vector<float> steps, scales;
+  long long curr_iter = 0;  // net->curr_iter: completed updates
+  bool any_gate = false;    // some layer has dont_update / burnin_update / train_only_bn: the update table is per call
   int train_flags = 0;
   bool stem = false;  // layer 0 runs as a 1x1 conv over the 32-column im2col operand built by yc_stem_im2col
   bool stem_pair = false;  // inference: the stem conv runs on pixel pairs (network.cu)
@@ -142,6 +152,7 @@ struct yc_network {
   float* cost_host = nullptr;     // pinned: 8 floats per yolo layer
   std::vector<Op> bwd_ops;
   long long seen = 0;
+  int layers_loaded = 0;          // layers [0, layers_loaded) got their parameters from the weights file
   void* dp = nullptr;             // data-parallel context (NCCL), network_dp.cu
 };
 

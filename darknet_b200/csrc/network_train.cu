@@ -343,6 +343,10 @@ int train_backward(yc_network* net, cudaStream_t st) {
   auto& Ls = net->layers;
   for (int i = nl - 1; i >= 0; --i) {
     NLayer& L = Ls[i];
+    // network_kernels.cu:140-143: stopbackward = 1 ends the backward pass at this layer for good, stopbackward = k > 1
+    // until iteration k; :158 onlyforward layers are skipped
+    if (L.stopbackward == 1 || L.stopbackward > net->curr_iter) break;
+    if (L.onlyforward) continue;
     int rc = YC_OK;
     switch (L.type) {
       case L_CONV: {
@@ -468,7 +472,8 @@ extern "C" int yc_network_train_datum(yc_network* net, const float* x_host, cons
 // the cfg's [net] values; batch = net->batch * subdivisions (network.cpp:118).
 extern "C" int yc_network_update(yc_network* net, float lr, float momentum, float decay, void* stream) {
   YC_REQUIRE(net && (net->flags & YC_NET_TRAIN) && net->finalized, "yc_network_update: not a finalized training network");
-  if (lr < 0) lr = net->lr;
+  const long long iter = net->curr_iter;
+  if (lr < 0) lr = yc_network_current_rate(net, iter, 0);  // UpdateNetworkGpu: lr = GetCurrLr(net)
   if (momentum < 0) momentum = net->momentum;
   if (decay < 0) decay = net->decay;
   const int world = std::max(1, net->train_flags);  // data-parallel world size (network_dp.cu)
@@ -483,8 +488,9 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
     if (rc) return rc;
   }
   // one launch for every layer's weights, biases and scales (the same arithmetic as yc_sgd_update_conv per layer:
-  // 61 launches of a few microseconds each on yolov4-tiny otherwise)
-  if (!net->sgd_items) {
+  // 61 launches of a few microseconds each on yolov4-tiny otherwise).  The table is built once — or, when some layer
+  // carries an update gate, per call from the layers that update at this iteration (network_kernels.cu:231-241).
+  if (!net->sgd_items || net->any_gate) {
     std::vector<yc::SgdItem> items;
     int blocks = 0;
     auto push = [&](yc::SgdItem it, long long elements) {
@@ -495,6 +501,9 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
     };
     for (NLayer& L : net->layers) {
       if (L.type != L_CONV) continue;
+      if (L.burnin_update && (long long)L.burnin_update * net->burn_in > iter) continue;
+      if (L.train_only_bn) continue;
+      if (!(L.dont_update < iter) && L.dont_update) continue;  // the reference updates when l->dont_update < iter
       const Geo G = geo(net, (int)(&L - net->layers.data()));
       const int taps = G.size * G.size;
       yc::SgdItem w{L.w_master, L.dw_packed, (__nv_bfloat16*)L.w_packed, (__nv_bfloat16*)L.w_packed_d, L.n, G.c, taps,
@@ -504,6 +513,11 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
       if (L.bn && L.scale_dev && L.scale_upd)
         push(yc::SgdItem{L.scale_dev, L.scale_upd, nullptr, nullptr, L.n, 0, 0, 0, 0, 0, 0, 0}, L.n);
     }
+    if (net->sgd_items) {  // gated networks only: the previous update may still be reading the table
+      YC_CUDA(cudaStreamSynchronize(st));
+      cudaFree(net->sgd_items);
+      net->sgd_items = nullptr;
+    }
     if (!items.empty()) {
       YC_CUDA(cudaMalloc(&net->sgd_items, items.size() * sizeof(yc::SgdItem)));
       YC_CUDA(cudaMemcpy(net->sgd_items, items.data(), items.size() * sizeof(yc::SgdItem), cudaMemcpyHostToDevice));
@@ -512,7 +526,34 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
     net->sgd_n = (int)items.size();
     net->sgd_blocks = blocks;
   }
+  net->curr_iter = iter + 1;
   return yc::sgd_update_multi(net->sgd_items, net->sgd_n, net->sgd_blocks, lr, batch, carry, decay, st);
+}
+
+// PullConvolutionalLayer for every conv layer (convolutional_kernels.cu:817-836): device master copies -> the host-side
+// parameter vectors that yc_network_save_weights / yc_network_finalize read.
+int yc_train_pull_params(yc_network* net) {
+  cudaStream_t st = net->stream;
+  for (size_t i = 0; i < net->layers.size(); ++i) {
+    NLayer& L = net->layers[i];
+    if (L.type != L_CONV || !L.w_master) continue;
+    if (i == 0 && net->stem) {
+      std::vector<float> h((size_t)L.n * 32);
+      NET_CUDA(cudaMemcpyAsync(h.data(), L.w_master, h.size() * 4, cudaMemcpyDeviceToHost, st));
+      NET_CUDA(cudaStreamSynchronize(st));
+      stem_permute(L, h.data(), L.weights.data(), false);
+    } else {
+      NET_CUDA(cudaMemcpyAsync(L.weights.data(), L.w_master, L.weights.size() * 4, cudaMemcpyDeviceToHost, st));
+    }
+    NET_CUDA(cudaMemcpyAsync(L.biases.data(), L.bias_dev, (size_t)L.n * 4, cudaMemcpyDeviceToHost, st));
+    if (L.bn) {
+      NET_CUDA(cudaMemcpyAsync(L.scales.data(), L.scale_dev, (size_t)L.n * 4, cudaMemcpyDeviceToHost, st));
+      NET_CUDA(cudaMemcpyAsync(L.rmean.data(), L.rmean_dev, (size_t)L.n * 4, cudaMemcpyDeviceToHost, st));
+      NET_CUDA(cudaMemcpyAsync(L.rvar.data(), L.rvar_dev, (size_t)L.n * 4, cudaMemcpyDeviceToHost, st));
+    }
+  }
+  NET_CUDA(cudaStreamSynchronize(st));
+  return YC_OK;
 }
 
 // Device time of one forward+backward(+update) by operator category, averaged over iters:
@@ -525,6 +566,7 @@ extern "C" int yc_network_train_profile(yc_network* net, const float* input_dev_
   for (int i = 0; i < 7; ++i) ms[i] = 0.f;
   cudaStream_t st = net->stream;
   int rc = YC_OK;
+  const long long iter0 = net->curr_iter, seen0 = net->seen;  // a timing pass is not a training iteration
   for (int it = 0; it < iters && !rc; ++it) {
     Prof prof;
     g_prof = &prof;
@@ -546,6 +588,8 @@ extern "C" int yc_network_train_profile(yc_network* net, const float* input_dev_
     for (cudaEvent_t e : prof.ev) cudaEventDestroy(e);
   }
   g_prof = nullptr;
+  net->curr_iter = iter0;
+  net->seen = seen0;
   return rc;
 }
 

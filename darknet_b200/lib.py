@@ -55,7 +55,7 @@ PLAN_TWO_OUT_BUFS, PLAN_GENERIC_EPI, PLAN_EPI_SETS_V1 = 128, 256, 512
 # every plan switch off: the plainest kernel variant of each layer (parity coverage of the non-default paths)
 NET_PLAIN_PLANS = NET_NO_STEM_PAIR | NET_NO_PAIR_S2 | NET_NO_PAIR_FUSE | ((PLAN_NO_HALO | PLAN_NO_W_RES | PLAN_ONE_OUT_BUF | PLAN_GENERIC_EPI) << NET_PLAN_SHIFT)
 NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
-NET_TRAIN, NET_DGRAD_ACCUMULATE, NET_BN_BIAS_GRAD = 64, 128, 256
+NET_TRAIN, NET_DGRAD_ACCUMULATE, NET_BN_BIAS_GRAD, NET_TRAIN_REF_CPU = 64, 128, 256, 8192
 
 _lib = None
 
@@ -137,6 +137,11 @@ _SIGS = {
     "yc_network_layer_float": (C.c_float, [_P, C.c_int, C.c_int]),
     "yc_network_layer_array": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_int]),
     "yc_network_flops": (C.c_double, [_P]),
+    "yc_network_load_weights": (C.c_int, [_P, C.c_char_p]),
+    "yc_network_save_weights": (C.c_int, [_P, C.c_char_p, C.c_int]),
+    "yc_network_init_weights": (C.c_int, [_P, C.c_uint, C.c_int]),
+    "yc_network_current_rate": (C.c_float, [_P, C.c_longlong, C.c_int]),
+    "yc_network_set_schedule": (C.c_int, [_P, C.c_int, C.c_longlong]),
     "yc_network_predict": (_P, [_P, _P]),
     "yc_network_predict_u8": (_P, [_P, _P, C.c_int]),
     "yc_network_prefetch": (C.c_int, [_P, _P]),

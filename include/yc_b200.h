@@ -320,12 +320,16 @@ enum {
   YC_NET_TRAIN = 64,         /* LoadNetwork(train=true): batchnorm uses batch statistics, every layer keeps delta
                                 buffers, conv layers keep fp32 master weights + gradient accumulators */
   YC_NET_DGRAD_ACCUMULATE = 128, /* data gradient ADDS to the previous layer's delta (cuDNN beta=1,
-                                convolutional_kernels.cu:735-738) instead of overwriting it like col2im (col2im.c:70, the
-                                reference CPU path's behaviour and this library's parity default) */
+                                convolutional_kernels.cu:735-738) instead of overwriting it like col2im (col2im.c:70;
+                                SURVEY B6).  Implied by YC_NET_TRAIN unless YC_NET_TRAIN_REF_CPU. */
   YC_NET_BN_BIAS_GRAD = 256, /* also accumulate the batchnorm shift's gradient into bias_updates (the reference GPU path;
-                                its CPU path leaves it at zero) */
+                                its CPU path leaves it at zero).  Implied likewise. */
   YC_NET_STEM_IM2COL = 512,  /* inference: a first conv with c*size*size <= 32 reads an im2col operand built by the input
                                 conversion (yc_stem_im2col) and runs as a 1x1 layer */
+  YC_NET_TRAIN_REF_CPU = 8192, /* with YC_NET_TRAIN: the reference CPU path's semantics instead of its GPU path's — the data
+                                gradient OVERWRITES the previous layer's delta (col2im.c:70) and the batchnorm shift gets no
+                                gradient.  The mode the CPU oracle is compared in.  Without it YC_NET_TRAIN
+                                implies YC_NET_DGRAD_ACCUMULATE | YC_NET_BN_BIAS_GRAD. */
   YC_NET_NO_STEM_PAIR = 1024, /* stem conv on single pixels instead of pixel pairs (A/B + parity coverage) */
   YC_NET_NO_PAIR_S2 = 2048,  /* 3x3 stride-2 32-channel layer on the plain im2col path instead of the pixel-pair view */
   YC_NET_NO_PAIR_FUSE = 4096, /* do not merge two 1x1 convs that read the same tensor into one GEMM */
@@ -346,7 +350,28 @@ YC_API int yc_network_set_conv_weights(yc_network* net, int layer, const float* 
 /* [setup] fuse BN, pack weights, plan buffers and conv kernels.  Called by yc_network_load when weights_path
  * is given; idempotent. */
 YC_API int yc_network_finalize(yc_network* net);
-/* what: 0 n_layers, 1 batch, 2 w, 3 h, 4 c, 5 n_conv, 6 kernels launched per forward, 7 n_yolo */
+/* [setup] LoadWeights (parser.cpp:1846-1850, LoadWeightsUpTo :1778-1844) on a parsed network.  A file that ends at a layer
+ * boundary fills the first layers only (a backbone such as yolov4.conv.137; yc_network_info(net, 11) = layers filled) and
+ * leaves the others as they are; a file that ends inside a layer is YC_ERR_IO.  The header's `seen` becomes the
+ * network's image / iteration count.  Call yc_network_finalize after. */
+YC_API int yc_network_load_weights(yc_network* net, const char* path);
+/* SaveWeights (parser.cpp:1545-1560, 1590-1643): darknet .weights format — int32 major, minor, revision, uint64 seen, then
+ * per conv layer biases, [scales, rolling_mean, rolling_variance], weights (OIHW fp32).  A training network's current
+ * device values are pulled first.  cutoff > 0 saves the first `cutoff` layers only (SaveWeightsUpto). */
+YC_API int yc_network_save_weights(yc_network* net, const char* path, int cutoff);
+/* [setup] FillConvLayer's initialisation law (convolutional_layer.cpp:478-493) through libc rand() after srand(seed): the
+ * reference's own values for every conv parsed before the first [yolo] section (which re-seeds from the clock).  Layers
+ * below first_layer keep their values (a loaded backbone).  Call yc_network_finalize after. */
+YC_API int yc_network_init_weights(yc_network* net, unsigned seed, int first_layer);
+/* GetCurrLr (network.cpp:32-84): learning rate at iteration `iter` under the [net] policy (constant, step, steps — whose
+ * positions are fractions of max_iter in this reference —, exp, poly, sigmoid, sgdr; random returns the base rate) with
+ * burn-in lr * (iter / burn_in)^power.  max_iter <= 0: the value of yc_network_set_schedule / [net] max_batches. */
+YC_API float yc_network_current_rate(const yc_network* net, long long iter, int max_iter);
+/* net->max_iter / net->curr_iter (owned by the reference's training driver): max_iter <= 0 and iter < 0 keep the
+ * current values.  The iteration count advances by one per yc_network_update. */
+YC_API int yc_network_set_schedule(yc_network* net, int max_iter, long long iter);
+/* what: 0 n_layers, 1 batch, 2 w, 3 h, 4 c, 5 n_conv, 6 kernels launched per forward, 7 n_yolo, 8 subdivisions,
+ * 9 current iteration, 10 images seen, 11 layers filled from the weights file, 12 effective flags */
 YC_API int yc_network_info(const yc_network* net, int what);
 /* per-layer: what: 0 type(0 conv,1 maxpool,2 upsample,3 route,4 shortcut,5 yolo,6 gaussian_yolo) 1 out_c 2 out_h
  * 3 out_w 4 has_output(0 if fused away) 5 in_c 6 size 7 stride 8 activation 9 batch_normalize 10 block_n 11 stages
@@ -401,8 +426,11 @@ YC_API int yc_network_profile(yc_network* net, const float* input_dev_nchw, int 
 YC_API int yc_network_train_datum(yc_network* net, const float* x_host, const float* truth_host, float* cost);
 /* ForwardBackwardNetworkGpu on device-resident fp32 NCHW input and truth; asynchronous on `stream`. */
 YC_API int yc_network_forward_backward(yc_network* net, const float* input_dev_nchw, const float* truth_dev, void* stream);
-/* UpdateNetworkGpu: SGD step on every conv layer; negative lr/momentum/decay take the cfg's [net] values;
- * batch = net batch * subdivisions (x data-parallel world size).  stream NULL = the network's own stream. */
+/* UpdateNetworkGpu (network_kernels.cu:214-243): SGD step on every conv layer.  lr < 0 = GetCurrLr at the current iteration
+ * (yc_network_current_rate; with the default constant policy and no burn-in that is [net] learning_rate), negative
+ * momentum / decay = the cfg's [net] values; batch = net batch * subdivisions (x data-parallel world size).  Layers are
+ * skipped as the reference does: burnin_update * burn_in > iter, train_only_bn, dont_update >= iter.  Advances the
+ * iteration count.  stream NULL = the network's own stream. */
 YC_API int yc_network_update(yc_network* net, float lr, float momentum, float decay, void* stream);
 /* net->benchmark_layers for the training step: device time by operator category (CUDA events after every operator),
  * averaged over iters.  ms[7]: conv fprop, wgrad, dgrad, batchnorm/activation passes, other layers + loss, SGD update,

@@ -78,6 +78,8 @@ def ref_lib():
         L.ref_scale_channels.argtypes = [_f32p, _f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p, C.c_void_p,
                                          C.c_void_p, C.c_void_p]
         L.ref_reorg.argtypes = [_f32p] + [C.c_int] * 6 + [_f32p]
+        L.ref_curr_lr.restype = C.c_float
+        L.ref_curr_lr.argtypes = [C.c_void_p, C.c_longlong, C.c_int]
         L.ref_layer_forward_train.restype = C.c_float
         L.ref_layer_forward_train.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p, _f32p]
         L.ref_nms.argtypes = [_f32p, _f32p, _f32p, C.c_int, C.c_int, C.c_float, C.c_int, C.c_float, _i32p]

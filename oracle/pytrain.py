@@ -79,11 +79,12 @@ class Step:
             self._ref = pyoracle.RefNet(path, None, train=True)
         return self._ref
 
-    def __init__(self, text, weights, emulate_bf16=False, dgrad_accumulate=False):
+    def __init__(self, text, weights, emulate_bf16=False, dgrad_accumulate=False, bn_bias_grad=False):
         self.text = text
         self.net, self.layers = cfgmod.walk_shapes(text)
         self.emul = emulate_bf16
-        self.accum = dgrad_accumulate
+        self.accum = dgrad_accumulate      # cuDNN beta = 1 (convolutional_kernels.cu:735-738) instead of col2im's overwrite
+        self.bn_bias = bn_bias_grad        # backward_bias_gpu in BackwardBatchnormLayerGpu (batchnorm_layer.cpp:330)
         self.P = {}
         for L in self.layers:
             if L.kind in ("convolutional", "conv"):
@@ -221,6 +222,8 @@ class Step:
                     S1 = g.sum(axis=(0, 2, 3), dtype=np.float64)
                     S2 = (g * s["xc"]).sum(axis=(0, 2, 3), dtype=np.float64)
                     p["scale_updates"] += (S2 / np.sqrt(var + np.float32(.000001))).astype(np.float32)
+                    if self.bn_bias:
+                        p["bias_updates"] += S1.astype(np.float32)
                     ga = p["scales"].astype(np.float64)
                     md = ga * S1 * (-1. / np.sqrt((var + np.float32(.00001)).astype(np.float64)))
                     vd = ga * S2 * (-.5 * np.power((var + np.float32(.00001)).astype(np.float64), -1.5))

@@ -268,6 +268,14 @@ float ref_layer_forward_train(void* h, int i, const float* input, const float* t
   return l->cost ? *l->cost : 0.f;
 }
 
+// GetCurrLr (network.cpp:32-84) at a given iteration / max_iter (both are owned by the reference's training driver)
+float ref_curr_lr(void* h, long long iter, int max_iter) {
+  Network* n = &((RefNet*)h)->net;
+  n->curr_iter = (int)iter;
+  n->max_iter = max_iter;
+  return GetCurrLr(n);
+}
+
 // NmsSort — reference box.cpp:393-419 on caller-provided detections.  boxes: [n][4] (x y w h), obj: [n],
 // probs: [n][classes] (zeroed in place); order_out[i] = original index of the detection that ends at
 // position i of the reference's array after its qsorts.

@@ -30,7 +30,7 @@ from tests.netutil import rel_l2
 pytestmark = pytest.mark.gpu
 
 
-def _compare(net, st, tol, tag, what):
+def _compare(net, st, tol, tag, what, gpu_semantics=False):
     """what = 'forward': outputs + statistics; 'backward': deltas + parameter gradients."""
     from darknet_b200 import network as N
     worst = dict(out=0.0, delta=0.0, wu=0.0, su=0.0, bu=0.0, stat=0.0)
@@ -60,7 +60,10 @@ def _compare(net, st, tol, tag, what):
                 if L.bn:
                     e = rel_l2(N.layer_param(net, i, "scale_updates"), p["scale_updates"])
                     chk("su", i, L.kind, "scale_updates", e, tol); row.append(f"su {e:.2e}")
-                    if np.abs(N.layer_param(net, i, "bias_updates")).max() != 0.0:
+                    if gpu_semantics:   # the reference GPU path trains the batchnorm shift (batchnorm_layer.cpp:330)
+                        e = rel_l2(N.layer_param(net, i, "bias_updates"), p["bias_updates"])
+                        chk("bu", i, L.kind, "bias_updates", e, tol); row.append(f"bu {e:.2e}")
+                    elif np.abs(N.layer_param(net, i, "bias_updates")).max() != 0.0:
                         bad.append(f"layer {i}: bias_updates of a batch-normalised layer must stay 0 (B8)")
                 else:
                     e = rel_l2(N.layer_param(net, i, "bias_updates"), p["bias_updates"])
@@ -85,12 +88,15 @@ def _adopt(net, st):
     st.adopt_forward(outs, zs, means, variances)
 
 
-def _run(name, B, hw, classes, tol=1.5e-2, tol_fwd=(5e-2, 1e-1), steps=2, **kw):
+def _run(name, B, hw, classes, tol=1.5e-2, tol_fwd=(5e-2, 1e-1), steps=2, gpu_semantics=False, **kw):
     from darknet_b200 import lib as L, network as N
     text, cpath, wpath = netutil.materialise(name, batch=B, subdivisions=1, **kw)
     W, _ = cfgmod.read_weights(wpath, text)
-    st = pytrain.Step(text, W, emulate_bf16=True)
-    net = N.LoadNetwork(cpath, wpath, batch=B, flags=L.NET_DEFAULT | L.NET_TRAIN)
+    # gpu_semantics: the library's default training mode = the reference GPU path (data gradients accumulate, the
+    # batchnorm shift is trained); otherwise the reference CPU path's quirks, the mode the compiled reference runs in
+    st = pytrain.Step(text, W, emulate_bf16=True, dgrad_accumulate=gpu_semantics, bn_bias_grad=gpu_semantics)
+    net = N.LoadNetwork(cpath, wpath, batch=B, flags=L.NET_DEFAULT | L.NET_TRAIN | (0 if gpu_semantics else L.NET_TRAIN_REF_CPU))
+    assert bool(net.info(12) & L.NET_DGRAD_ACCUMULATE) == gpu_semantics and bool(net.info(12) & L.NET_BN_BIAS_GRAD) == gpu_semantics
     for step in range(steps):
         x = cfgmod.synth_images(B, 3, hw, hw, seed=5 + 10 * step)
         truth = cfgmod.synth_truth(B, 90, classes=classes, seed=6 + 10 * step)
@@ -100,7 +106,7 @@ def _run(name, B, hw, classes, tol=1.5e-2, tol_fwd=(5e-2, 1e-1), steps=2, **kw):
         _adopt(net, st)
         cw = st.backward()
         assert abs(cg - cw) <= 2e-3 * abs(cw), f"step {step}: cost {cg} vs walker on the same heads {cw}"
-        wb = _compare(net, st, tol, f"{name} step {step}", "backward")
+        wb = _compare(net, st, tol, f"{name} step {step}", "backward", gpu_semantics)
         print(name, kw, "step", step, "cost", cg, cw, {k: f"{v:.2e}" for k, v in {**wf, **wb}.items()})
         st.update()
         N.UpdateNetwork(net)
@@ -121,3 +127,15 @@ def test_micro_leaky_vs_bf16_walker(gpu):
 def test_yolov4_tiny_vs_bf16_walker(gpu):
     """BASELINE config 4 at batch 2."""
     _run("yolov4-tiny", 2, 416, 80, steps=1, w=416, h=416)
+
+
+def test_micro_gpu_semantics_vs_bf16_walker(gpu):
+    """The library's DEFAULT training mode (YC_NET_TRAIN alone): cuDNN-style accumulating data gradients and a trained
+    batchnorm shift.  In micro, route 7 sends gradient into layer 4's delta before conv 5 ... 6 run their dgrad into it,
+    and shortcut 4 feeds layers 3 and 1: with the CPU path's overwrite those contributions are erased."""
+    _run("micro", 4, 64, 3, act="mish", gpu_semantics=True)
+    _run("micro", 4, 64, 3, act="leaky", gpu_semantics=True)
+
+
+def test_yolov4_tiny_gpu_semantics_vs_bf16_walker(gpu):
+    _run("yolov4-tiny", 2, 416, 80, steps=1, gpu_semantics=True, w=416, h=416)

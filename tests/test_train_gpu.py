@@ -31,7 +31,7 @@ def _setup(name, B, **kw):
         pytest.skip("oracle/_ref not built")
     text, cpath, wpath = netutil.materialise(name, batch=B, subdivisions=1, **kw)
     ref = pyoracle.RefNet(cpath, wpath, train=True)
-    net = N.LoadNetwork(cpath, wpath, batch=B, flags=L.NET_DEFAULT | L.NET_TRAIN)
+    net = N.LoadNetwork(cpath, wpath, batch=B, flags=L.NET_DEFAULT | L.NET_TRAIN | L.NET_TRAIN_REF_CPU)
     sh = cfgmod.walk_shapes(text)
     return text, ref, net, sh
 

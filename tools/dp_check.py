@@ -29,7 +29,7 @@ def main():
     kw = {} if name == "micro" else dict(w=hw, h=hw)
     text = cfgs.CONFIGS[name](batch=B, subdivisions=1, **kw)
     weights = cfgmod.synth_weights(text)
-    flags = L.NET_DEFAULT | L.NET_TRAIN
+    flags = L.NET_DEFAULT | L.NET_TRAIN | L.NET_TRAIN_REF_CPU
 
     def fresh():
         return N.LoadSynthetic(text, weights, batch=B, flags=flags)

@@ -21,7 +21,7 @@ def main():
     t = cfgmod.synth_truth(B, 90, classes=classes, seed=6)
     runs = []
     for r in range(3):
-        net = N.LoadSynthetic(text, weights, batch=B, flags=L.NET_DEFAULT | L.NET_TRAIN)
+        net = N.LoadSynthetic(text, weights, batch=B, flags=L.NET_DEFAULT | L.NET_TRAIN | L.NET_TRAIN_REF_CPU)
         cost = N.TrainNetworkDatum(net, x, t)
         convs = [i for i in range(net.n) if net.layer_type(i) == "convolutional"]
         runs.append((cost, {i: N.layer_param(net, i, "weight_updates") for i in convs},

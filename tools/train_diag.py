@@ -9,7 +9,7 @@ from tests.netutil import rel_l2
 
 name = sys.argv[1] if len(sys.argv) > 1 else "micro"
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 4
-flags = L.NET_DEFAULT | L.NET_TRAIN
+flags = L.NET_DEFAULT | L.NET_TRAIN | L.NET_TRAIN_REF_CPU
 kw = dict(w=416, h=416) if name != "micro" else {}
 text, cpath, wpath = netutil.materialise(name, batch=B, subdivisions=1, **kw)
 ref = pyoracle.RefNet(cpath, wpath, train=True)
