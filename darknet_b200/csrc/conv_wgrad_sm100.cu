@@ -12,8 +12,9 @@
 // (128-byte rows, 128B swizzle) into shared memory — dY through a tiled map, X through an im2col-mode map that
 // applies the tap offset, stride, dilation and zero padding — and tcgen05.mma reads them through MN-major
 // descriptors (instruction-descriptor bits 15/16 = 1).  K is split across CTAs (split-K over pixel ranges) so that
-// small filters still fill 148 SMs; partial sums are added to the fp32 gradient with vector reductions
-// (red.global.add.v4.f32), which is also the reference's `+=` accumulation semantics.
+// small filters still fill 148 SMs.  The partial sums of the splits go through a scratch buffer and are added to the
+// fp32 gradient in split order by the last unit to finish (no float atomics: the step is reproducible bit for bit);
+// `+=` into dw is the reference's accumulation semantics.
 //
 // CTA = 320 threads, persistent over work units (tile x K-split):
 //   warp 0 / lane 0 : TMA producer, warp 1 / lane 0 : tcgen05.mma issuer, warps 2..9 : epilogue (TMEM -> red.global)
@@ -46,6 +47,12 @@ struct WgradParams {
   uint32_t tmem_cols;
   float* dw;        // [N_out][taps][ldw] fp32
   int ldw;
+  // split-K without atomics (splits > 1): every (tile, split) unit stores its partial sums to partial[split], and the
+  // epilogue warp that arrives LAST at its (tile, warp slot) ticket adds the partials in split order into dw.  The sum
+  // order is fixed whatever the scheduling, so two runs of a training step give bit-identical gradients.
+  float* partial;             // [splits][N_out * taps * ldw] or nullptr (splits == 1: a single writer per element)
+  long long partial_stride;   // floats per split
+  unsigned* tickets;          // [tiles][8]
 };
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -187,7 +194,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
     const int half = (warp - 2) >> 2;  // 0/1: alternate 32-column groups
     int it = 0;
     for (int u = blockIdx.x; u < units; u += gridDim.x, ++it) {
-      const int tile = u % p.tiles;
+      const int tile = u % p.tiles, split = u / p.tiles;
       const int ct = tile % p.c_tiles;
       const int tap = (tile / p.c_tiles) % p.taps;
       const int nt = tile / (p.c_tiles * p.taps);
@@ -218,17 +225,53 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
         if (row_ok) {
           const int cbase = ct * p.block_n + g * 32;
           const int lim = is_tail ? 16 : 32;
+          float* dst = p.partial ? p.partial + (long long)split * p.partial_stride + (rowp - p.dw) : rowp;
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
-            if (j < lim && cbase + j < p.ldw)
-              red_add_v4(rowp + g * 32 + j, __uint_as_float(rr[j]), __uint_as_float(rr[j + 1]), __uint_as_float(rr[j + 2]),
-                         __uint_as_float(rr[j + 3]));
+            if (j < lim && cbase + j < p.ldw) {
+              if (p.partial)
+                *reinterpret_cast<float4*>(dst + g * 32 + j) = make_float4(__uint_as_float(rr[j]), __uint_as_float(rr[j + 1]),
+                                                                           __uint_as_float(rr[j + 2]), __uint_as_float(rr[j + 3]));
+              else  // one split: this unit is the only writer of these elements in this launch
+                red_add_v4(dst + g * 32 + j, __uint_as_float(rr[j]), __uint_as_float(rr[j + 1]), __uint_as_float(rr[j + 2]),
+                           __uint_as_float(rr[j + 3]));
+            }
           }
         }
       }
+      // the accumulator has been read: hand it back before the (possibly long) ordered reduction
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(tempty_bar(acc));
+      if (p.partial) {
+        __threadfence();  // this warp's partial sums are visible before its ticket
+        __syncwarp();
+        unsigned t = 0;
+        if (lane == 0) t = atomicAdd(p.tickets + tile * 8 + (warp - 2), 1u);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t == (unsigned)p.splits - 1) {  // last split to finish this warp slot of the tile: add all splits in order
+          __threadfence();
+          if (row_ok) {
+            for (int g = half; g < groups + tail16; g += 2) {
+              const int cbase = ct * p.block_n + g * 32;
+              const int lim = (g == groups) ? 16 : 32;
+#pragma unroll 1
+              for (int j = 0; j < lim; j += 4) {
+                if (cbase + j >= p.ldw) break;
+                float4 a = *reinterpret_cast<const float4*>(rowp + g * 32 + j);
+                for (int sp = 0; sp < p.splits; ++sp) {
+                  const float4 v = __ldcg(reinterpret_cast<const float4*>(p.partial + (long long)sp * p.partial_stride +
+                                                                        (rowp - p.dw) + g * 32 + j));
+                  a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+                }
+                *reinterpret_cast<float4*>(rowp + g * 32 + j) = a;
+              }
+            }
+          }
+          __syncwarp();
+          if (lane == 0) p.tickets[tile * 8 + (warp - 2)] = 0u;  // ready for the next launch
+        }
+      }
     }
   }
 
@@ -272,6 +315,8 @@ struct yc_wgrad_plan {
   WgradParams p;
   int grid = 0;
   size_t smem = 0;
+  float* partial = nullptr;      // plan-owned split-K scratch (splits > 1)
+  unsigned* tickets = nullptr;
 };
 
 namespace {
@@ -354,6 +399,25 @@ extern "C" int yc_conv_wgrad_plan_create(yc_wgrad_plan** out_plan, const yc_conv
   p.tmem_cols = cols;
   p.dw = dw_packed;
   p.ldw = yc_conv_wgrad_ld(C);
+  p.partial = nullptr;
+  p.partial_stride = (long long)out_c * p.taps * p.ldw;
+  p.tickets = nullptr;
+  if (p.splits > 1) {
+    // zero-filled once: the epilogue rewrites the same elements at every launch, the padding columns it never writes
+    // stay zero
+    cudaError_t e = cudaMalloc(&pl->partial, (size_t)p.splits * p.partial_stride * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemset(pl->partial, 0, (size_t)p.splits * p.partial_stride * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&pl->tickets, (size_t)p.tiles * 8 * sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMemset(pl->tickets, 0, (size_t)p.tiles * 8 * sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaStreamSynchronize(cudaStreamLegacy);
+    if (e != cudaSuccess) {
+      set_error("yc_conv_wgrad_plan_create: split-K scratch: %s", cudaGetErrorString(e));
+      yc_conv_wgrad_plan_destroy(pl);
+      return YC_ERR_ALLOC;
+    }
+    p.partial = pl->partial;
+    p.tickets = pl->tickets;
+  }
 
   CUresult cr;
   {
@@ -401,6 +465,9 @@ extern "C" int yc_conv_wgrad_plan_create(yc_wgrad_plan** out_plan, const yc_conv
 }
 
 extern "C" int yc_conv_wgrad_plan_destroy(yc_wgrad_plan* pl) {
+  if (!pl) return YC_OK;
+  if (pl->partial) cudaFree(pl->partial);
+  if (pl->tickets) cudaFree(pl->tickets);
   delete pl;
   return YC_OK;
 }
