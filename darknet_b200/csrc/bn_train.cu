@@ -274,13 +274,15 @@ __global__ void __launch_bounds__(256, YC_BN_MINB) bn_act_fwd_kernel(TView z, co
 template <int MODE, int ACT>
 __global__ void __launch_bounds__(256, YC_BN_MINB) bwd_reduce_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
                                   const float* __restrict__ gamma, const float* __restrict__ beta,
-                                  float* __restrict__ S1, float* __restrict__ S2) {
+                                  float* __restrict__ S1, float* __restrict__ S2, float* __restrict__ P,
+                                  unsigned* __restrict__ ticket) {
   constexpr int act = ACT;
-  extern __shared__ float sh[];  // [2][groups*8]
+  // Reproducible sums (no float atomics): thread sums -> one shared-memory entry per (warp | row slot, channel) -> the
+  // block's partial = entries added in index order -> P[block][2][C8] -> the block that draws the last ticket adds the
+  // partials in block order.  MODE 0 overwrites S1 / S2, MODE 1 adds the total to S1 (bias_updates accumulate, B7).
+  extern __shared__ float sh[];  // [entries][2][groups*8]
   const int groups = (dy.c + 7) / 8;
   const int C8 = groups * 8;
-  for (int i = threadIdx.x; i < 2 * C8; i += blockDim.x) sh[i] = 0.f;
-  __syncthreads();
   const int tg = threadIdx.x % groups;  // blockDim.x is a multiple of groups (host)
   const int slots = blockDim.x / groups;
   const int slot = threadIdx.x / groups;
@@ -366,18 +368,51 @@ __global__ void __launch_bounds__(256, YC_BN_MINB) bwd_reduce_kernel(TView dy, T
         }
       }
     }
+    const int e = fold ? (threadIdx.x >> 5) : slot;
     if (!fold || (threadIdx.x & 31) < groups) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        atomicAdd(&sh[tg * 8 + j], a1[j]);
-        if (MODE == 0) atomicAdd(&sh[C8 + tg * 8 + j], a2[j]);
+        sh[(e * 2) * C8 + tg * 8 + j] = a1[j];
+        if (MODE == 0) sh[(e * 2 + 1) * C8 + tg * 8 + j] = a2[j];
       }
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < dy.c; i += blockDim.x) {
-    atomicAdd(&S1[i], sh[i]);
-    if (MODE == 0) atomicAdd(&S2[i], sh[C8 + i]);
+  {
+    const bool fold = groups < 32 && (32 % groups) == 0 && (blockDim.x & 31) == 0;
+    const int entries = fold ? (int)(blockDim.x >> 5) : slots;
+    float* mine = P + (size_t)blockIdx.x * 2 * C8;
+    for (int i = threadIdx.x; i < C8; i += blockDim.x) {
+      float s1 = 0.f, s2 = 0.f;
+      for (int e = 0; e < entries; ++e) {
+        s1 += sh[(e * 2) * C8 + i];
+        if (MODE == 0) s2 += sh[(e * 2 + 1) * C8 + i];
+      }
+      mine[i] = s1;
+      if (MODE == 0) mine[C8 + i] = s2;
+    }
+  }
+  __threadfence();
+  __syncthreads();
+  __shared__ unsigned is_last;
+  if (threadIdx.x == 0) is_last = atomicAdd(ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    for (int i = threadIdx.x; i < dy.c; i += blockDim.x) {
+      float s1 = 0.f, s2 = 0.f;
+      for (unsigned b = 0; b < gridDim.x; ++b) {
+        s1 += __ldcg(P + (size_t)b * 2 * C8 + i);
+        if (MODE == 0) s2 += __ldcg(P + (size_t)b * 2 * C8 + C8 + i);
+      }
+      if (MODE == 0) {
+        S1[i] = s1;
+        S2[i] = s2;
+      } else {
+        S1[i] += s1;
+      }
+    }
+    if (threadIdx.x == 0) *ticket = 0u;  // ready for the next launch
   }
 }
 
@@ -525,6 +560,13 @@ static int row_grid(long long rows, int slots, int per_iter = 2) {
     case YC_MISH: { constexpr int A = YC_MISH; __VA_ARGS__; } break;                  \
     default: set_error("unsupported activation %d", (int)(act_id)); return YC_ERR_ARG; \
   }
+// dynamic shared memory of bwd_reduce_kernel: one entry per warp when the channel groups fold inside a warp, else one
+// per row slot; each entry is [2][groups*8] floats
+static size_t reduce_smem(int groups, int threads) {
+  const bool fold = groups < 32 && (32 % groups) == 0 && (threads & 31) == 0;
+  const int entries = fold ? threads / 32 : threads / groups;
+  return sizeof(float) * 2 * (size_t)groups * 8 * entries;
+}
 static int reduce_threads(int groups) {
   int t = (256 / groups) * groups;
   if (t < groups) t = groups;  // more than 256 groups (c > 2048): refused by the callers (launch bounds are 256)
@@ -542,6 +584,13 @@ static bool ok_view(const yc_tensor* t) {
 static int ew_grid(long long work) {
   long long blocks = ceil_div_ll(work, 256);
   return (int)std::max<long long>(1, std::min<long long>(blocks, (long long)sm_count() * 16));
+}
+
+// floats of the workspace yc_bn_bwd / yc_bias_act_bwd need for c channels: S1, S2, three coefficient vectors, the
+// ticket, and one [2][ceil8(c)] partial per block of the reduction grid (at most one wave of resident blocks)
+extern "C" size_t yc_bn_bwd_workspace_floats(int c) {
+  const size_t c8 = (size_t)round_up(c, 8);
+  return 5 * (size_t)c + 4 + (size_t)sm_count() * YC_BN_MINB * 2 * c8;
 }
 
 extern "C" int yc_bn_finalize(const float* sum, const float* sumsq, long long count, float* mean, float* var,
@@ -584,13 +633,14 @@ extern "C" int yc_bn_bwd(const yc_tensor* dy, const yc_tensor* z, const float* m
   float* S1 = workspace;          // [n]
   float* S2 = workspace + n;      // [n]
   float* coef = workspace + 2 * n;  // [3n]
-  YC_CUDA(cudaMemsetAsync(workspace, 0, sizeof(float) * 2 * n, st));
+  unsigned* ticket = reinterpret_cast<unsigned*>(workspace + 5 * n);  // zero between launches (the kernel resets it)
+  float* P = workspace + 5 * n + 4;  // [grid][2][C8] block partials
   const int groups = (n + 7) / 8;
   const int threads = reduce_threads(groups);
   const int slots = threads / groups;
   const int grid = row_grid(dv.rows, slots, 2);
-  YC_ACT_DISPATCH(activation, (bwd_reduce_kernel<0, A><<<grid, threads, sizeof(float) * 2 * groups * 8, st>>>(dv, zv, mean, var, gamma,
-                                                                                                             beta, S1, S2)));
+  YC_ACT_DISPATCH(activation, (bwd_reduce_kernel<0, A><<<grid, threads, reduce_smem(groups, threads), st>>>(dv, zv, mean, var, gamma,
+                                                                                                            beta, S1, S2, P, ticket)));
   YC_LAUNCH_CHECK();
   bn_bwd_coef_kernel<<<ceil_div(n, 128), 128, 0, st>>>(S1, S2, var, gamma, (float)dv.rows, scale_updates, bias_updates, coef, n);
   YC_LAUNCH_CHECK();
@@ -604,8 +654,9 @@ extern "C" int yc_bn_bwd(const yc_tensor* dy, const yc_tensor* z, const float* m
 }
 
 extern "C" int yc_bias_act_bwd(const yc_tensor* dy, const yc_tensor* y, int activation, float* bias_updates,
-                               const yc_tensor* dz, void* stream) {
-  YC_REQUIRE(ok_view(dy) && ok_view(dz) && (activation == YC_LINEAR || ok_view(y)), "yc_bias_act_bwd: bad arguments");
+                               float* workspace, const yc_tensor* dz, void* stream) {
+  YC_REQUIRE(ok_view(dy) && ok_view(dz) && (activation == YC_LINEAR || ok_view(y)) && (!bias_updates || workspace),
+             "yc_bias_act_bwd: bad arguments (bias_updates needs a workspace of yc_bn_bwd_workspace_floats(c) floats)");
   YC_REQUIRE(activation == YC_LINEAR || activation == YC_LEAKY || activation == YC_RELU || activation == YC_LOGISTIC,
              "yc_bias_act_bwd: mish/swish need the saved pre-activation, which only batch-normalised layers keep");
   YC_REQUIRE(dz->n == dy->n && dz->h == dy->h && dz->w == dy->w && dz->c >= dy->c && dz->dtype == YC_BF16,
@@ -621,8 +672,10 @@ extern "C" int yc_bias_act_bwd(const yc_tensor* dy, const yc_tensor* y, int acti
     const int threads = reduce_threads(groups);
     const int slots = threads / groups;
     const int grid = row_grid(dv.rows, slots, 2);
-    YC_ACT_DISPATCH(activation, (bwd_reduce_kernel<1, A><<<grid, threads, sizeof(float) * 2 * groups * 8, st>>>(
-                                    dv, uv, nullptr, nullptr, nullptr, nullptr, bias_updates, nullptr)));
+    unsigned* ticket = reinterpret_cast<unsigned*>(workspace + 5 * n);  // same layout as yc_bn_bwd's workspace
+    float* P = workspace + 5 * n + 4;
+    YC_ACT_DISPATCH(activation, (bwd_reduce_kernel<1, A><<<grid, threads, reduce_smem(groups, threads), st>>>(
+                                    dv, uv, nullptr, nullptr, nullptr, nullptr, bias_updates, nullptr, P, ticket)));
     YC_LAUNCH_CHECK();
   }
   const int agroups = (dz->ldc >= (long long)groups * 8) ? dz->ldc / 8 : groups;

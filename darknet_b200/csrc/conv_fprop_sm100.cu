@@ -57,6 +57,13 @@ struct ConvParams {
   float* stat_sum;
   float* stat_sq;
   int stat_cols;       // n_tiles * block_n: floats per statistic in the CTA's shared-memory accumulator
+  // Reproducible statistics (no float atomics anywhere): inside a CTA every (TMEM quadrant, epilogue set) pair of warps
+  // accumulates into its OWN shared-memory region (the warps of a pair own disjoint columns), the regions are added in
+  // index order into the CTA's partial, partials go to stat_partial[cta][2][stat_cols], and the CTA that draws the last
+  // ticket adds the partials in CTA order into stat_sum / stat_sq (overwriting them).
+  int stat_regions;    // 4 * epi_sets
+  float* stat_partial;
+  unsigned* stat_ticket;
   int out_bufs;        // epilogue staging buffers per warp (1 or 2): with 2 a warp stages block k+1 while the TMA
                        // engine still reads block k
   int split_col;       // > 0: output columns >= split_col go to a second tensor (tmap_y2) at column - split_col: two
@@ -326,7 +333,7 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
           }
           red[pass] = a[0];
         }
-        const uint32_t so = stat_smem + 4u * (uint32_t)(col0 + lane);
+        const uint32_t so = stat_smem + 4u * (uint32_t)((quad * p.epi_sets + set) * 2 * p.stat_cols + col0 + lane);
         asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(so), "f"(red[0]) : "memory");
         asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(so + 4u * (uint32_t)p.stat_cols), "f"(red[1]) : "memory");
       }
@@ -426,7 +433,8 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtenso
   const int tpi = p.tiles_h * p.tiles_w;
   const __nv_bfloat16* res = p.res;
   const long long ldres = p.ldres;
-  const bool bias_in_smem = p.bias_cols > 0;
+  // one GENERIC pointer for both cases (a single load path in the block loop): the shared-memory copy or global memory
+  const float* bias_ptr = p.bias_cols > 0 ? ptx::smem_generic<float>(bias_smem) : p.bias;
   uint32_t nst = 0, sbuf = sbuf0;
   auto wait_buf = [&]() {
     if (lane == 0) {
@@ -516,18 +524,15 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtenso
       } else {
         wait_buf();
       }
-      const uint32_t bsm = bias_smem + 4u * (uint32_t)col0;
-      const float* bgl = p.bias + col0;
+      const float* bcol = bias_ptr + col0;
 #pragma unroll
       for (int hf = 0; hf < 2; ++hf) {  // two halves of 16 columns = 8 packed pairs each
         f32x2 x[8];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          // bias: broadcast LDS.128 from the copy staged at kernel start, or (where that copy would have cost a ring
-          // stage: wide K-heavy tiles, whose epilogue is hidden anyway) straight from global / L1
-          uint4 b4;
-          if (bias_in_smem) b4 = ptx::ld_shared_v4(bsm + (uint32_t)(hf * 64 + j * 16));
-          else b4 = __ldg(reinterpret_cast<const uint4*>(bgl + hf * 16 + j * 4));
+          // bias: broadcast 16-byte load from the copy staged in shared memory at kernel start, or (where that copy would
+          // have cost a ring stage: wide K-heavy tiles, whose epilogue is hidden anyway) from global memory / L1
+          const uint4 b4 = *reinterpret_cast<const uint4*>(bcol + hf * 16 + j * 4);
           x[2 * j] = add2(pack2(__uint_as_float(r[hf * 16 + 4 * j]), __uint_as_float(r[hf * 16 + 4 * j + 1])),
                           pack2(__uint_as_float(b4.x), __uint_as_float(b4.y)));
           x[2 * j + 1] = add2(pack2(__uint_as_float(r[hf * 16 + 4 * j + 2]), __uint_as_float(r[hf * 16 + 4 * j + 3])),
@@ -647,10 +652,10 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   auto pempty_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc + 1 + kHaloMaxStages + s); };
   const uint32_t stat_smem = bar_base + 512u;  // 2 x stat_cols floats, only when statistics are requested
   if (STATS) {
-    for (int i = threadIdx.x; i < 2 * p.stat_cols; i += blockDim.x)
+    for (int i = threadIdx.x; i < 2 * p.stat_cols * p.stat_regions; i += blockDim.x)
       asm volatile("st.shared.f32 [%0], %1;" ::"r"(stat_smem + 4u * i), "f"(0.f) : "memory");
   }
-  const uint32_t bias_smem = stat_smem + (STATS ? 8u * (uint32_t)p.stat_cols : 0u);  // bias_cols floats (fast epilogue)
+  const uint32_t bias_smem = stat_smem + (STATS ? 8u * (uint32_t)(p.stat_cols * p.stat_regions) : 0u);  // bias_cols floats (fast epilogue)
   if (!STATS && p.fast_epi) {  // (bias_cols == 0: the epilogue reads the bias from global memory)
     for (int i = threadIdx.x; i < p.bias_cols; i += blockDim.x)
       asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_smem + 4u * i), "f"(__ldg(p.bias + i)) : "memory");
@@ -929,13 +934,39 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   ptx::tc_fence_before();
   __syncthreads();
   if (STATS) {
-    for (int i = threadIdx.x; i < p.stat_cols; i += blockDim.x) {
-      if (i >= p.N) break;
-      float a, q;
-      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(a) : "r"(stat_smem + 4u * i));
-      asm volatile("ld.shared.f32 %0, [%1];" : "=f"(q) : "r"(stat_smem + 4u * (i + p.stat_cols)));
-      atomicAdd(p.stat_sum + i, a);
-      atomicAdd(p.stat_sq + i, q);
+    // CTA partial = regions added in index order
+    float* mine = p.stat_partial + (size_t)blockIdx.x * 2 * p.stat_cols;
+    for (int i = threadIdx.x; i < 2 * p.stat_cols; i += blockDim.x) {
+      float a = 0.f;
+      for (int r = 0; r < p.stat_regions; ++r) {
+        float v;
+        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(stat_smem + 4u * (uint32_t)(r * 2 * p.stat_cols + i)));
+        a += v;
+      }
+      mine[i] = a;
+    }
+    __threadfence();
+    __syncthreads();
+    const uint32_t flag_slot = bar_base + 504u;  // last word pair of the 512-byte barrier block (unused by the barrier map)
+    if (threadIdx.x == 0) {
+      const unsigned last = atomicAdd(p.stat_ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
+      asm volatile("st.shared.u32 [%0], %1;" ::"r"(flag_slot), "r"(last) : "memory");
+    }
+    __syncthreads();
+    unsigned last_flag;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(last_flag) : "r"(flag_slot));
+    if (last_flag) {  // every partial is visible: add them in CTA order
+      __threadfence();
+      for (int i = threadIdx.x; i < p.N; i += blockDim.x) {
+        float a = 0.f, q = 0.f;
+        for (unsigned b = 0; b < gridDim.x; ++b) {
+          a += __ldcg(p.stat_partial + (size_t)b * 2 * p.stat_cols + i);
+          q += __ldcg(p.stat_partial + (size_t)b * 2 * p.stat_cols + p.stat_cols + i);
+        }
+        p.stat_sum[i] = a;
+        p.stat_sq[i] = q;
+      }
+      if (threadIdx.x == 0) *p.stat_ticket = 0u;  // ready for the next launch
     }
   }
   if (warp == 1) {
@@ -1010,6 +1041,8 @@ struct yc_conv_plan {
   ConvParams p;
   float* bias_pad = nullptr;
   float* scale_pad = nullptr;
+  float* stat_partial = nullptr;   // [grid][2][stat_cols] (training statistics)
+  unsigned* stat_ticket = nullptr;
   int grid = 0;
   size_t smem = 0;
 };
@@ -1479,23 +1512,42 @@ extern "C" int yc_conv_dgrad_plan_create(yc_conv_plan** plan, const yc_conv_desc
 extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq) {
   YC_REQUIRE(pl && ((sum && sumsq) || (!sum && !sumsq)), "yc_conv_plan_set_stats: bad arguments");
   ConvParams& p = pl->p;
+  YC_REQUIRE(!sum || p.act == YC_LINEAR, "yc_conv_plan_set_stats: statistics are taken on the linear (pre-batchnorm) output");
   p.fast_epi = 0;                       // statistics are reduced by the generic epilogue
+  p.bias_cols = 0;
   if (p.a_mode != 2) p.w_resident = 0;  // the ring is re-planned below with weights in every stage
+  // the generic epilogue's warp-to-tile assignment: four warps per quadrant on a wide tile (fewer statistics regions)
+  const int groups = p.block_n / 32;
+  p.epi_sets = groups >= 4 ? 1 : (groups >= 2 ? 2 : 4);
   const uint32_t a_bytes = p.a_mode == 2 ? 0u : kBlockM * p.block_k * 2;
   const uint32_t b_bytes = (uint32_t)round_up(p.block_n * p.block_k * 2, 1024);
   const uint32_t stage_bytes = a_bytes + b_bytes;
   const uint32_t out_stage = kEpiWarps * kStageOutBytes * p.out_bufs + (p.a_mode == 2 ? p.halo_stages * kHaloPatchStride : 0);
   p.stat_cols = sum ? p.n_tiles * p.block_n : 0;
-  const uint32_t stat_bytes = 2u * 4u * (uint32_t)p.stat_cols;
+  p.stat_regions = 4 * p.epi_sets;
+  const uint32_t stat_bytes = 2u * 4u * (uint32_t)(p.stat_cols * p.stat_regions);
+  YC_REQUIRE(1024 + 512 + out_stage + stat_bytes + 2 * stage_bytes <= 227 * 1024, "tile does not fit shared memory");
   const uint32_t smem_budget = 227 * 1024 - 1024 - 512 - out_stage - stat_bytes;
   p.stages = std::min<int>(kMaxStages, smem_budget / stage_bytes);
-  YC_REQUIRE(p.stages >= 2, "tile does not fit shared memory");
   if (p.w_resident) {
     if (9 * p.cchunks <= p.stages) p.stages = 9 * p.cchunks;
     else p.w_resident = 0;
   }
   pl->smem = (size_t)p.stages * stage_bytes + out_stage + 1024 + 512 + stat_bytes;
-  YC_REQUIRE(!sum || p.act == YC_LINEAR, "yc_conv_plan_set_stats: statistics are taken on the linear (pre-batchnorm) output");
+  if (pl->stat_partial) { cudaFree(pl->stat_partial); pl->stat_partial = nullptr; }
+  if (pl->stat_ticket) { cudaFree(pl->stat_ticket); pl->stat_ticket = nullptr; }
+  if (sum) {
+    cudaError_t e = cudaMalloc(&pl->stat_partial, (size_t)pl->grid * 2 * p.stat_cols * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&pl->stat_ticket, sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMemset(pl->stat_ticket, 0, sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaStreamSynchronize(cudaStreamLegacy);
+    if (e != cudaSuccess) {
+      set_error("yc_conv_plan_set_stats: %s", cudaGetErrorString(e));
+      return YC_ERR_ALLOC;
+    }
+  }
+  p.stat_partial = pl->stat_partial;
+  p.stat_ticket = pl->stat_ticket;
   p.stat_sum = sum;
   p.stat_sq = sumsq;
   return YC_OK;
@@ -1505,6 +1557,8 @@ extern "C" int yc_conv_plan_destroy(yc_conv_plan* pl) {
   if (!pl) return YC_OK;
   if (pl->bias_pad) cudaFree(pl->bias_pad);
   if (pl->scale_pad) cudaFree(pl->scale_pad);
+  if (pl->stat_partial) cudaFree(pl->stat_partial);
+  if (pl->stat_ticket) cudaFree(pl->stat_ticket);
   delete pl;
   return YC_OK;
 }

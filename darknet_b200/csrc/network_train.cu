@@ -139,7 +139,7 @@ int yc_train_finalize(yc_network* net) {
         if (!rc && L.bn) rc = dev_alloc(&L.mean_dev, L.n);
         if (!rc && L.bn) rc = dev_alloc(&L.var_dev, L.n);
         if (!rc && L.bn) rc = dev_alloc(&L.stats_dev, 2 * (size_t)L.n);
-        if (!rc && L.bn) rc = dev_alloc(&L.ws_dev, 5 * (size_t)L.n);
+        if (!rc) rc = dev_alloc(&L.ws_dev, yc_bn_bwd_workspace_floats(L.n));  // zero-filled: holds the reduction ticket
         if (!rc) {
           // one contiguous gradient bucket per layer: [weight_updates | bias_updates | scale_updates] — what the
           // data-parallel all-reduce sends in a single call (network_dp.cu)
@@ -212,7 +212,7 @@ int yc_train_finalize(yc_network* net) {
         NET_CUDA(cudaMemcpy(L.mask_dev, L.mask.data(), L.mask.size() * 4, cudaMemcpyHostToDevice));
     NET_CUDA(h2d_done());
         int rc = dev_alloc(&L.ydelta, elems);
-        if (!rc) rc = dev_alloc(&L.ystats, 8);
+        if (!rc) rc = dev_alloc(&L.ystats, yc_yolo_loss_stats_floats(B, L.out_h, L.out_w));
         if (rc) return rc;
         net->truth_floats = std::max(net->truth_floats, L.max_boxes * 5);
         if (i == 0 || Ls[i - 1].type != L_CONV) NET_FAIL(YC_ERR_ARG, "layer %d: a [yolo] layer must follow its head conv", i);
@@ -359,7 +359,7 @@ int train_backward(yc_network* net, cudaStream_t st) {
                          (net->flags & YC_NET_BN_BIAS_GRAD) ? L.bias_upd : nullptr, L.ws_dev, &dz, st);
         } else {
           const yc_tensor y = view_of(net, i);
-          rc = yc_bias_act_bwd(&dy, L.act == YC_LINEAR ? nullptr : &y, L.act, L.bias_upd, &dz, st);
+          rc = yc_bias_act_bwd(&dy, L.act == YC_LINEAR ? nullptr : &y, L.act, L.bias_upd, L.ws_dev, &dz, st);
         }
         tick(CAT_BN, st);
         if (!rc) rc = yc_conv_wgrad(L.wplan, st);

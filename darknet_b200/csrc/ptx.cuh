@@ -11,6 +11,13 @@ namespace ptx {
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
+// generic address of a shared-memory location given as a 32-bit shared-window address
+template <typename T>
+__device__ __forceinline__ T* smem_generic(uint32_t saddr) {
+  uint64_t g;
+  asm("cvta.shared.u64 %0, %1;" : "=l"(g) : "l"((uint64_t)saddr));
+  return reinterpret_cast<T*>(g);
+}
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred = 0;
   asm volatile(

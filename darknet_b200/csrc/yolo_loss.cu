@@ -1,17 +1,30 @@
-// YOLO-layer loss and deltas on the device.
+// YOLO / Gaussian-YOLO loss and deltas on the device.
 //
-// Replaces the training half of ForwardYoloLayer (yolo_layer.cpp:409-772: delta_yolo_box, delta_yolo_class,
-// averages_yolo_deltas, compare_yolo_class; IoU math box.cpp:36-351) and BackwardYoloLayerGpu (:884-888).  In the
-// reference this runs on ONE host thread between a device->host copy of the head and a host->device copy of the
-// deltas (yolo_layer.cpp:856-880); here the head never leaves HBM:
-//   1. yolo_loss_cells   : thread per (image, anchor, cell)   — best IoU over the truths, objectness delta
-//   2. yolo_loss_truths  : one warp per image, truths in order — box / objectness / class deltas of the
-//                          responsible anchors (order-dependent in the reference, so kept sequential per image;
-//                          the class loop runs across the lanes)
-//   3. yolo_loss_finish  : thread per (image, anchor, cell)   — averages_yolo_deltas, sum of squares for the cost,
-//                          and prev.delta += delta written straight into the head conv's NHWC bf16 delta
-// Layouts: `out` / `delta` are fp32 NCHW [B][n*(5+classes)][H][W] exactly like l->output / l->delta
-// (EntryIndex, yolo_layer.cpp:380-386); truth is [B][max_boxes][5] = (x, y, w, h, class id).
+// Replaces the training half of ForwardYoloLayer (yolo_layer.cpp:409-772) / ForwardGaussianYoloLayer
+// (gaussian_yolo_layer.cpp:486-857) and BackwardYoloLayerGpu (:884-888).  In the reference this is ONE host thread between
+// a device->host copy of the head and a host->device copy of the deltas; here the head never leaves HBM and the work is
+// spread as follows:
+//
+//   objectness pass : thread per (image, anchor, cell), one image per blockIdx.y so that the image's truth list sits in
+//                     shared memory: best IoU over the truths -> objectness delta (ignore_thresh / truth_thresh)
+//   assignment pass : block per image.  Every (truth, candidate anchor) pair becomes a RECORD in shared memory, computed
+//                     in parallel (thread per truth).  The reference walks the truths in order and several truths may
+//                     land on the same (anchor, cell): box deltas then accumulate, class deltas depend on what an
+//                     earlier truth left.  That order is restored by a resolve step: the first record of every
+//                     location owns it and applies all records of that location in record order.  Different locations
+//                     proceed in parallel; nothing depends on thread scheduling.
+//   finish pass     : block per (image, 32 cells): box deltas / number of positive classes (averages_yolo_deltas), the
+//                     sums of squares of the cost, and prev.delta += delta straight into the head conv's NHWC bf16 delta
+//   cost pass       : one block adds the per-image and per-block partial sums IN INDEX ORDER (no float atomics: two runs
+//                     give the same bits) and forms *(l->cost)
+//
+// The arithmetic of every formula follows the reference's CPU code operation by operation (its float / double mix
+// included), because the deltas are compared with it at 2e-5; what is this file's own is how the formulas are organised:
+// one edge representation per box pair, the IoU-family gradient as a template over the loss kind with every shared
+// sub-expression formed once, and per-edge derivative tables instead of sixteen named scalars.
+//
+// Layouts: `out` / `delta` are fp32 NCHW [B][n*(E)][H][W] like l->output / l->delta (EntryIndex, yolo_layer.cpp:380-386);
+// truth is [B][max_boxes][5] = (x, y, w, h, class id), ended by the first entry with a valid class and x == 0.
 #include <float.h>
 #include <math.h>
 #include <algorithm>
@@ -20,602 +33,468 @@
 
 namespace yc {
 
-enum { IOU_IOU = 0, IOU_GIOU = 1, IOU_MSE = 2, IOU_DIOU = 3, IOU_CIOU = 4 };  // IOU_LOSS, box.h:6-13
+enum LossKind { K_IOU = 0, K_GIOU = 1, K_MSE = 2, K_DIOU = 3, K_CIOU = 4 };  // IOU_LOSS, box.h:6-13
 
-struct BoxF { float x, y, w, h; };
-struct DxRep { float dt, db, dl, dr; };
-struct IousF { float iou, giou, diou, ciou; };
+struct Box4 { float x, y, w, h; };
+struct Edges { float l, r, t, b; };
+__device__ __forceinline__ Edges edges_of(const Box4& q) {
+  return Edges{q.x - q.w / 2.0f, q.x + q.w / 2.0f, q.y - q.h / 2.0f, q.y + q.h / 2.0f};
+}
+__device__ __forceinline__ float sq(float a) { return a * a; }
 
-#define YSQ(a) ((a) * (a))
-
-__device__ __forceinline__ float b_overlap(float x1, float w1, float x2, float w2) {  // Box::Overlap box.cpp:36-46
-  const float l1 = x1 - w1 / 2, l2 = x2 - w2 / 2;
-  const float left = l1 > l2 ? l1 : l2;
-  const float r1 = x1 + w1 / 2, r2 = x2 + w2 / 2;
-  const float right = r1 < r2 ? r1 : r2;
-  return right - left;
+// ---- overlap measures of a box pair (box.cpp:36-128), all from one evaluation of intersection and union ------------
+struct Overlap {
+  float inter, uni, iou;
+  float enc_w, enc_h;  // smallest enclosing box
+};
+__device__ __forceinline__ float span_overlap(float c1, float e1, float c2, float e2) {  // Box::Overlap
+  const float lo = fmaxf(c1 - e1 / 2, c2 - e2 / 2), hi = fminf(c1 + e1 / 2, c2 + e2 / 2);
+  return hi - lo;
 }
-__device__ __forceinline__ float b_intersect(const BoxF& a, const BoxF& b) {  // box.cpp:48-57
-  const float w = b_overlap(a.x, a.w, b.x, b.w), h = b_overlap(a.y, a.h, b.y, b.h);
-  if (w < 0 || h < 0) return 0;
-  return w * h;
+__device__ __forceinline__ Overlap overlap_of(const Box4& a, const Box4& b) {
+  Overlap o;
+  const float w = span_overlap(a.x, a.w, b.x, b.w), h = span_overlap(a.y, a.h, b.y, b.h);
+  o.inter = (w < 0 || h < 0) ? 0.f : w * h;
+  o.uni = a.w * a.h + b.w * b.h - o.inter;
+  o.iou = (fabsf(o.inter) < FLT_EPSILON || fabsf(o.uni) < FLT_EPSILON) ? 0.f : o.inter / o.uni;
+  const Edges ea = edges_of(a), eb = edges_of(b);
+  o.enc_w = fmaxf(ea.r, eb.r) - fminf(ea.l, eb.l);
+  o.enc_h = fmaxf(ea.b, eb.b) - fminf(ea.t, eb.t);
+  return o;
 }
-__device__ __forceinline__ float b_union(const BoxF& a, const BoxF& b) { return a.w * a.h + b.w * b.h - b_intersect(a, b); }
-__device__ __forceinline__ float b_iou(const BoxF& a, const BoxF& b) {  // box.cpp:64-72
-  const float I = b_intersect(a, b), U = b_union(a, b);
-  if (fabsf(I) < FLT_EPSILON || fabsf(U) < FLT_EPSILON) return 0;
-  return I / U;
+__device__ __forceinline__ float iou_of(const Box4& a, const Box4& b) { return overlap_of(a, b).iou; }
+__device__ __forceinline__ float giou_of(const Overlap& o) {  // Box::Giou
+  const float c = o.enc_w * o.enc_h;
+  return fabsf(c) < FLT_EPSILON ? o.iou : o.iou - (c - o.uni) / c;
 }
-struct AbsF { float left, right, top, bottom; };
-__device__ __forceinline__ AbsF b_abs(const BoxF& b) {  // box.cpp:353-359
-  return AbsF{b.x - b.w / 2.0f, b.x + b.w / 2.0f, b.y - b.h / 2.0f, b.y + b.h / 2.0f};
+__device__ __forceinline__ float diou_of(const Overlap& o, const Box4& a, const Box4& b, float beta) {  // Box::Diou
+  const float c = sq(o.enc_w) + sq(o.enc_h);
+  if (fabsf(c) < FLT_EPSILON) return o.iou;
+  const float d = sq(a.x - b.x) + sq(a.y - b.y);
+  return o.iou - (float)pow((double)(d / c), (double)beta);
 }
-__device__ __forceinline__ AbsF b_abs2(const BoxF& a, const BoxF& b) {  // box.cpp:361-370
-  const AbsF p = b_abs(a), q = b_abs(b);
-  return AbsF{fminf(p.left, q.left), fmaxf(p.right, q.right), fminf(p.top, q.top), fmaxf(p.bottom, q.bottom)};
-}
-__device__ float b_giou(const BoxF& a, const BoxF& b) {  // box.cpp:113-128
-  const AbsF ab = b_abs2(a, b);
-  const float w = ab.right - ab.left, h = ab.bottom - ab.top;
-  const float c = w * h;
-  const float iou = b_iou(a, b);
-  if (fabsf(c) < FLT_EPSILON) return iou;
-  const float u = b_union(a, b);
-  return iou - (c - u) / c;
-}
-__device__ float b_diou(const BoxF& a, const BoxF& b, float beta) {  // box.cpp:96-111
-  const AbsF ab = b_abs2(a, b);
-  const float w = ab.right - ab.left, h = ab.bottom - ab.top;
-  const float c = w * w + h * h;
-  const float iou = b_iou(a, b);
-  if (fabsf(c) < FLT_EPSILON) return iou;
-  const float d = YSQ(a.x - b.x) + YSQ(a.y - b.y);
-  return iou - (float)pow((double)(d / c), (double)beta);
-}
-__device__ float b_ciou(const BoxF& a, const BoxF& b) {  // box.cpp:74-94
-  const AbsF ab = b_abs2(a, b);
-  const float w = ab.right - ab.left, h = ab.bottom - ab.top;
-  const float c = w * w + h * h;
-  const float iou = b_iou(a, b);
-  if (fabsf(c) < FLT_EPSILON) return iou;
-  const float u = YSQ(a.x - b.x) + YSQ(a.y - b.y);
-  const float d = u / c;
+__device__ __forceinline__ float ciou_of(const Overlap& o, const Box4& a, const Box4& b) {  // Box::Ciou
+  const float c = sq(o.enc_w) + sq(o.enc_h);
+  if (fabsf(c) < FLT_EPSILON) return o.iou;
+  const float d = (sq(a.x - b.x) + sq(a.y - b.y)) / c;
   const float ar_gt = b.w / b.h, ar_pred = a.w / a.h;
-  const float ar_loss = (float)(4 / YSQ(M_PI) * YSQ(atan((double)ar_gt) - atan((double)ar_pred)));
-  const float alpha = (float)(ar_loss / (1 - iou + ar_loss + 0.000001));
-  return iou - (d + alpha * ar_loss);
+  const float ar_loss = (float)(4 / (M_PI * M_PI) * sq(atan((double)ar_gt) - atan((double)ar_pred)));
+  const float alpha = (float)(ar_loss / (1 - o.iou + ar_loss + 0.000001));
+  return o.iou - (d + alpha * ar_loss);
 }
-__device__ float b_rmse(const BoxF& a, const BoxF& b) {
-  return sqrtf(YSQ(a.x - b.x) + YSQ(a.y - b.y) + YSQ(a.w - b.w) + YSQ(a.h - b.h));
-}
-__device__ float b_iou_kind(const BoxF& a, const BoxF& b, int kind) {  // box.cpp:136-151
+__device__ float measure_of(const Box4& a, const Box4& b, int kind) {  // Box::Iou(b1, b2, iou_type), box.cpp:136-151
+  if (kind == K_MSE) return sqrtf(sq(a.x - b.x) + sq(a.y - b.y) + sq(a.w - b.w) + sq(a.h - b.h));
+  const Overlap o = overlap_of(a, b);
   switch (kind) {
-    case IOU_GIOU: return b_giou(a, b);
-    case IOU_MSE: return b_rmse(a, b);
-    case IOU_DIOU: return b_diou(a, b, 0.6f);
-    case IOU_CIOU: return b_ciou(a, b);
+    case K_GIOU: return giou_of(o);
+    case K_DIOU: return diou_of(o, a, b, 0.6f);
+    case K_CIOU: return ciou_of(o, a, b);
   }
-  return b_iou(a, b);
+  return o.iou;
 }
 
-// Box::DxIou (box.cpp:153-351): gradient of IoU / GIoU / DIoU / CIoU w.r.t. (x, y, w, h) of the prediction
-__device__ DxRep b_dx_iou(const BoxF& pred, const BoxF& gt, int iou_type) {
-  const AbsF ap = b_abs(pred);
-  const float pred_t = fminf(ap.top, ap.bottom), pred_b = fmaxf(ap.top, ap.bottom);
-  const float pred_l = fminf(ap.left, ap.right), pred_r = fmaxf(ap.left, ap.right);
-  const AbsF ag = b_abs(gt);
-  const float X = (pred_b - pred_t) * (pred_r - pred_l);
-  const float Xhat = (ag.bottom - ag.top) * (ag.right - ag.left);
-  const float Ih = fminf(pred_b, ag.bottom) - fmaxf(pred_t, ag.top);
-  const float Iw = fminf(pred_r, ag.right) - fmaxf(pred_l, ag.left);
-  const float I = Iw * Ih;
-  const float U = X + Xhat - I;
-  const float S = YSQ(pred.x - gt.x) + YSQ(pred.y - gt.y);
-  const float giou_Cw = fmaxf(pred_r, ag.right) - fminf(pred_l, ag.left);
-  const float giou_Ch = fmaxf(pred_b, ag.bottom) - fminf(pred_t, ag.top);
-  const float giou_C = giou_Cw * giou_Ch;
-  const float dX_wrt_t = -1 * (pred_r - pred_l), dX_wrt_b = pred_r - pred_l;
-  const float dX_wrt_l = -1 * (pred_b - pred_t), dX_wrt_r = pred_b - pred_t;
-  const float dI_wrt_t = pred_t > ag.top ? (-1 * Iw) : 0, dI_wrt_b = pred_b < ag.bottom ? Iw : 0;
-  const float dI_wrt_l = pred_l > ag.left ? (-1 * Ih) : 0, dI_wrt_r = pred_r < ag.right ? Ih : 0;
-  const float dU_wrt_t = dX_wrt_t - dI_wrt_t, dU_wrt_b = dX_wrt_b - dI_wrt_b;
-  const float dU_wrt_l = dX_wrt_l - dI_wrt_l, dU_wrt_r = dX_wrt_r - dI_wrt_r;
-  const float dC_wrt_t = pred_t < ag.top ? (-1 * giou_Cw) : 0, dC_wrt_b = pred_b > ag.bottom ? giou_Cw : 0;
-  const float dC_wrt_l = pred_l < ag.left ? (-1 * giou_Ch) : 0, dC_wrt_r = pred_r > ag.right ? giou_Ch : 0;
-  float p_dt = 0, p_db = 0, p_dl = 0, p_dr = 0;
-  if (U > 0) {
-    p_dt = ((U * dI_wrt_t) - (I * dU_wrt_t)) / (U * U);
-    p_db = ((U * dI_wrt_b) - (I * dU_wrt_b)) / (U * U);
-    p_dl = ((U * dI_wrt_l) - (I * dU_wrt_l)) / (U * U);
-    p_dr = ((U * dI_wrt_r) - (I * dU_wrt_r)) / (U * U);
+// ---- gradient of IoU / GIoU / DIoU / CIoU with respect to (x, y, w, h) of the prediction (Box::DxIou, box.cpp:153-351) --
+// Edge order of the tables: 0 top, 1 bottom, 2 left, 3 right.
+template <int KIND>
+__device__ float4 iou_family_grad(const Box4& pred, const Box4& gt) {
+  const Edges pe = edges_of(pred), ge = edges_of(gt);
+  // a prediction with negative width / height has its edges swapped: the gradient is taken on the sorted edges
+  const float pt = fminf(pe.t, pe.b), pb = fmaxf(pe.t, pe.b), pl = fminf(pe.l, pe.r), pr = fmaxf(pe.l, pe.r);
+  const float pw = pr - pl, ph = pb - pt;
+  const float area_p = ph * pw, area_g = (ge.b - ge.t) * (ge.r - ge.l);
+  const float ih = fminf(pb, ge.b) - fmaxf(pt, ge.t), iw = fminf(pr, ge.r) - fmaxf(pl, ge.l);
+  const float inter = iw * ih, uni = area_p + area_g - inter;
+  const bool disjoint = iw <= 0 || ih <= 0;
+  // d(area_p), d(inter) per edge; d(uni) = their difference
+  const float d_area[4] = {-1 * pw, pw, -1 * ph, ph};
+  const float d_inter[4] = {pt > ge.t ? (-1 * iw) : 0, pb < ge.b ? iw : 0, pl > ge.l ? (-1 * ih) : 0, pr < ge.r ? ih : 0};
+  float d_uni[4], g[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    d_uni[e] = d_area[e] - d_inter[e];
+    g[e] = uni > 0 ? ((uni * d_inter[e]) - (inter * d_uni[e])) / (uni * uni) : 0.f;
   }
-  // sequential re-assignments exactly as in the reference (box.cpp:215-218)
-  p_dt = ap.top < ap.bottom ? p_dt : p_db;
-  p_db = ap.top < ap.bottom ? p_db : p_dt;
-  p_dl = ap.left < ap.right ? p_dl : p_dr;
-  p_dr = ap.left < ap.right ? p_dr : p_dl;
-  if (iou_type == IOU_GIOU) {
-    if (giou_C > 0) {
-      p_dt += ((giou_C * dU_wrt_t) - (U * dC_wrt_t)) / (giou_C * giou_C);
-      p_db += ((giou_C * dU_wrt_b) - (U * dC_wrt_b)) / (giou_C * giou_C);
-      p_dl += ((giou_C * dU_wrt_l) - (U * dC_wrt_l)) / (giou_C * giou_C);
-      p_dr += ((giou_C * dU_wrt_r) - (U * dC_wrt_r)) / (giou_C * giou_C);
-    }
-    if (Iw <= 0 || Ih <= 0) {
-      p_dt = ((giou_C * dU_wrt_t) - (U * dC_wrt_t)) / (giou_C * giou_C);
-      p_db = ((giou_C * dU_wrt_b) - (U * dC_wrt_b)) / (giou_C * giou_C);
-      p_dl = ((giou_C * dU_wrt_l) - (U * dC_wrt_l)) / (giou_C * giou_C);
-      p_dr = ((giou_C * dU_wrt_r) - (U * dC_wrt_r)) / (giou_C * giou_C);
+  // the reference re-assigns the pairs one after the other (box.cpp:215-218): for swapped edges BOTH end up with the
+  // second one's value
+  g[0] = pe.t < pe.b ? g[0] : g[1];
+  g[1] = pe.t < pe.b ? g[1] : g[0];
+  g[2] = pe.l < pe.r ? g[2] : g[3];
+  g[3] = pe.l < pe.r ? g[3] : g[2];
+  if (KIND == K_GIOU) {
+    const float cw = fmaxf(pr, ge.r) - fminf(pl, ge.l), ch = fmaxf(pb, ge.b) - fminf(pt, ge.t), c = cw * ch;
+    const float d_enc[4] = {pt < ge.t ? (-1 * cw) : 0, pb > ge.b ? cw : 0, pl < ge.l ? (-1 * ch) : 0, pr > ge.r ? ch : 0};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float term = ((c * d_uni[e]) - (uni * d_enc[e])) / (c * c);  // formed once: added when c > 0, alone when disjoint
+      if (c > 0) g[e] += term;
+      if (disjoint) g[e] = term;
     }
   }
-  const float Ct = fminf(pred.y - pred.h / 2, gt.y - gt.h / 2), Cb = fmaxf(pred.y + pred.h / 2, gt.y + gt.h / 2);
-  const float Cl = fminf(pred.x - pred.w / 2, gt.x - gt.w / 2), Cr = fmaxf(pred.x + pred.w / 2, gt.x + gt.w / 2);
-  const float Cw = Cr - Cl, Ch = Cb - Ct;
-  const float C = YSQ(Cw) + YSQ(Ch);
-  const float dCt_dy = pred_t < ag.top ? 1 : 0, dCt_dh = pred_t < ag.top ? -0.5f : 0;
-  const float dCb_dy = pred_b > ag.bottom ? 1 : 0, dCb_dh = pred_b > ag.bottom ? 0.5f : 0;
-  const float dCl_dx = pred_l < ag.left ? 1 : 0, dCl_dw = pred_l < ag.left ? -0.5f : 0;
-  const float dCr_dx = pred_r > ag.right ? 1 : 0, dCr_dw = pred_r > ag.right ? 0.5f : 0;
-  const float dCw_dx = dCr_dx - dCl_dx, dCw_dy = 0, dCw_dw = dCr_dw - dCl_dw, dCw_dh = 0;
-  const float dCh_dx = 0, dCh_dy = dCb_dy - dCt_dy, dCh_dw = 0, dCh_dh = dCb_dh - dCt_dh;
-  float p_dx = p_dl + p_dr;
-  float p_dy = p_dt + p_db;
-  float p_dw = (p_dr - p_dl);
-  float p_dh = (p_db - p_dt);
-  if (iou_type == IOU_DIOU) {
-    if (C > 0) {
-      p_dx += (2 * (gt.x - pred.x) * C - (2 * Cw * dCw_dx + 2 * Ch * dCh_dx) * S) / YSQ(C);
-      p_dy += (2 * (gt.y - pred.y) * C - (2 * Cw * dCw_dy + 2 * Ch * dCh_dy) * S) / YSQ(C);
-      p_dw += (2 * Cw * dCw_dw + 2 * Ch * dCh_dw) * S / YSQ(C);
-      p_dh += (2 * Cw * dCw_dh + 2 * Ch * dCh_dh) * S / YSQ(C);
+  float dx = g[2] + g[3], dy = g[0] + g[1], dw = g[3] - g[2], dh = g[1] - g[0];
+  if (KIND == K_DIOU || KIND == K_CIOU) {
+    // centre-distance penalty S / C with C the squared diagonal of the enclosing box (of the UNSORTED prediction edges)
+    const float cw = fmaxf(pe.r, ge.r) - fminf(pe.l, ge.l), ch = fmaxf(pe.b, ge.b) - fminf(pe.t, ge.t);
+    const float c = sq(cw) + sq(ch);
+    const float s = sq(pred.x - gt.x) + sq(pred.y - gt.y);
+    const float dcw_dx = (pr > ge.r ? 1.f : 0.f) - (pl < ge.l ? 1.f : 0.f);
+    const float dcw_dw = (pr > ge.r ? 0.5f : 0.f) - (pl < ge.l ? -0.5f : 0.f);
+    const float dch_dy = (pb > ge.b ? 1.f : 0.f) - (pt < ge.t ? 1.f : 0.f);
+    const float dch_dh = (pb > ge.b ? 0.5f : 0.f) - (pt < ge.t ? -0.5f : 0.f);
+    const float zero = 0.f;  // the reference's dCh_dx, dCw_dy, dCh_dw, dCw_dh: kept in the sums (inf * 0 must stay NaN)
+    float tx = (2 * (gt.x - pred.x) * c - (2 * cw * dcw_dx + 2 * ch * zero) * s) / sq(c);
+    float ty = (2 * (gt.y - pred.y) * c - (2 * cw * zero + 2 * ch * dch_dy) * s) / sq(c);
+    float tw = (2 * cw * dcw_dw + 2 * ch * zero) * s / sq(c);
+    float th = (2 * cw * zero + 2 * ch * dch_dh) * s / sq(c);
+    if (KIND == K_CIOU) {  // aspect-ratio term
+      const float ar_gt = gt.w / gt.h, ar_pred = pred.w / pred.h;
+      const double dat = atan((double)ar_gt) - atan((double)ar_pred);
+      const float ar_loss = (float)(4 / (M_PI * M_PI) * (dat * dat));
+      const float alpha = (float)(ar_loss / (1 - inter / uni + ar_loss + 0.000001));
+      tw = tw + alpha * (float)(8 / (M_PI * M_PI) * dat * pred.h);
+      th = th + alpha * (float)(-8 / (M_PI * M_PI) * dat * pred.w);
     }
-    if (Iw <= 0 || Ih <= 0) {
-      p_dx = (2 * (gt.x - pred.x) * C - (2 * Cw * dCw_dx + 2 * Ch * dCh_dx) * S) / YSQ(C);
-      p_dy = (2 * (gt.y - pred.y) * C - (2 * Cw * dCw_dy + 2 * Ch * dCh_dy) * S) / YSQ(C);
-      p_dw = (2 * Cw * dCw_dw + 2 * Ch * dCh_dw) * S / YSQ(C);
-      p_dh = (2 * Cw * dCw_dh + 2 * Ch * dCh_dh) * S / YSQ(C);
-    }
+    if (c > 0) { dx += tx; dy += ty; dw += tw; dh += th; }
+    if (disjoint) { dx = tx; dy = ty; dw = tw; dh = th; }
   }
-  if (iou_type == IOU_CIOU) {
-    const float ar_gt = gt.w / gt.h, ar_pred = pred.w / pred.h;
-    const double dat = atan((double)ar_gt) - atan((double)ar_pred);
-    const float ar_loss = (float)(4 / YSQ(M_PI) * YSQ(dat));
-    const float alpha = (float)(ar_loss / (1 - I / U + ar_loss + 0.000001));
-    const float ar_dw = (float)(8 / YSQ(M_PI) * dat * pred.h);
-    const float ar_dh = (float)(-8 / YSQ(M_PI) * dat * pred.w);
-    if (C > 0) {
-      p_dx += (2 * (gt.x - pred.x) * C - (2 * Cw * dCw_dx + 2 * Ch * dCh_dx) * S) / YSQ(C);
-      p_dy += (2 * (gt.y - pred.y) * C - (2 * Cw * dCw_dy + 2 * Ch * dCh_dy) * S) / YSQ(C);
-      p_dw += (2 * Cw * dCw_dw + 2 * Ch * dCh_dw) * S / YSQ(C) + alpha * ar_dw;
-      p_dh += (2 * Cw * dCw_dh + 2 * Ch * dCh_dh) * S / YSQ(C) + alpha * ar_dh;
-    }
-    if (Iw <= 0 || Ih <= 0) {
-      p_dx = (2 * (gt.x - pred.x) * C - (2 * Cw * dCw_dx + 2 * Ch * dCh_dx) * S) / YSQ(C);
-      p_dy = (2 * (gt.y - pred.y) * C - (2 * Cw * dCw_dy + 2 * Ch * dCh_dy) * S) / YSQ(C);
-      p_dw = (2 * Cw * dCw_dw + 2 * Ch * dCh_dw) * S / YSQ(C) + alpha * ar_dw;
-      p_dh = (2 * Cw * dCw_dh + 2 * Ch * dCh_dh) * S / YSQ(C) + alpha * ar_dh;
-    }
+  return make_float4(dx, dy, dw, dh);
+}
+__device__ float4 iou_family_grad_rt(const Box4& pred, const Box4& gt, int kind) {
+  switch (kind) {
+    case K_GIOU: return iou_family_grad<K_GIOU>(pred, gt);
+    case K_DIOU: return iou_family_grad<K_DIOU>(pred, gt);
+    case K_CIOU: return iou_family_grad<K_CIOU>(pred, gt);
   }
-  return DxRep{p_dx, p_dy, p_dw, p_dh};
+  return iou_family_grad<K_IOU>(pred, gt);
 }
 
-struct LossParams {
+// ---- the head tensor ---------------------------------------------------------------------------------------------------
+struct Head {
   int B, H, W, n, total, classes, max_boxes, net_w, net_h;
   int iou_loss, iou_thresh_kind, focal_loss;
   float ignore_thresh, truth_thresh, iou_thresh, iou_normalizer, cls_normalizer, label_smooth_eps, max_delta;
-  int gaussian;         // 1: [Gaussian_yolo] entry layout mu_x,s_x,mu_y,s_y,mu_w,s_w,mu_h,s_h,obj,classes (gaussian_yolo_layer.cpp)
+  int gaussian;  // 1: entries mu_x, s_x, mu_y, s_y, mu_w, s_w, mu_h, s_h, objectness, classes (gaussian_yolo_layer.cpp)
   float uc_normalizer;
   const float* out;     // decoded head, fp32 NCHW
   const float* truth;   // [B][max_boxes*5]
-  const float* biases;  // anchors, 2*total
+  const float* anchors; // l->biases, 2*total
   const int* mask;      // n
-  float* delta;         // fp32 NCHW, same shape as out
-  float* stats;         // [0] cost [1] count [2] tot_iou_loss [3] tot_giou_loss [4] sum delta^2 [5] sum delta^2 w/o box
-                        // [6] tot_iou [7] class_count
+  float* delta;         // fp32 NCHW, shape of out
+  float* stats;         // [0..8) public: cost, count, sum(1-iou), sum(1-giou), |delta|^2, |delta w/o box|^2, sum iou, class
+                        // count; then per-image partials [B][4] and per-block partials of the finish pass [blocks][2]
+  int finish_blocks;
+
+  __device__ __forceinline__ int wh() const { return W * H; }
+  __device__ __forceinline__ int box_entries() const { return gaussian ? 8 : 4; }
+  __device__ __forceinline__ int entries() const { return box_entries() + 1 + classes; }
+  // element (image b, anchor slot a, entry e, cell) — EntryIndex yolo_layer.cpp:380-386
+  __device__ __forceinline__ long long at(int b, int a, int e, int cell) const {
+    return ((long long)(b * n + a) * entries() + e) * wh() + cell;
+  }
+  __device__ __forceinline__ float* img_partial(int b) const { return stats + 8 + 4 * b; }
+  __device__ __forceinline__ float* blk_partial(int k) const { return stats + 8 + 4 * B + 2 * k; }
 };
 
-__device__ __forceinline__ int box_entries(const LossParams& p) { return p.gaussian ? 8 : 4; }  // obj follows, then classes
-// yolo_layer.cpp:380-386 / EntryGaussianIndex gaussian_yolo_layer.cpp:476-484
-__device__ __forceinline__ int entry_index(const LossParams& p, int b, int location, int entry) {
-  const int wh = p.W * p.H;
-  const int E = box_entries(p) + 1 + p.classes;
-  const int n = location / wh, loc = location % wh;
-  return b * (p.n * E * wh) + n * wh * E + entry * wh + loc;
+// GetYoloBox (yolo_layer.cpp:139-148) / GetGaussianYoloBox (gaussian_yolo_layer.cpp:151-160, yolo_point = center) for
+// anchor `anchor` (absolute index) at cell (col, row); `base` = index of the cell's first entry
+__device__ __forceinline__ Box4 predicted_box(const Head& p, long long base, int anchor, int col, int row) {
+  const int s = p.wh();
+  const int ex = 0, ey = p.gaussian ? 2 : 1, ew = p.gaussian ? 4 : 2, eh = p.gaussian ? 6 : 3;
+  Box4 q;
+  q.x = (col + p.out[base + ex * s]) / p.W;
+  q.y = (row + p.out[base + ey * s]) / p.H;
+  q.w = expf(p.out[base + ew * s]) * p.anchors[2 * anchor] / p.net_w;
+  q.h = expf(p.out[base + eh * s]) * p.anchors[2 * anchor + 1] / p.net_h;
+  return q;
 }
-__device__ __forceinline__ BoxF get_yolo_box(const float* x, const float* biases, int n, int index, int i, int j, int lw,
-                                             int lh, int w, int h, int stride) {  // yolo_layer.cpp:139-148
-  BoxF b;
-  b.x = (i + x[index + 0 * stride]) / lw;
-  b.y = (j + x[index + 1 * stride]) / lh;
-  b.w = expf(x[index + 2 * stride]) * biases[2 * n] / w;
-  b.h = expf(x[index + 3 * stride]) * biases[2 * n + 1] / h;
-  return b;
-}
-__device__ __forceinline__ float fix_nan_inf(float v) { return (isnan(v) || isinf(v)) ? 0.f : v; }
-__device__ __forceinline__ float clip_value(float v, float m) { return v > m ? m : (v < -m ? -m : v); }
+__device__ __forceinline__ float sanitize(float v) { return (isnan(v) || isinf(v)) ? 0.f : v; }       // fix_nan_inf
+__device__ __forceinline__ float clamp_abs(float v, float m) { return v > m ? m : (v < -m ? -m : v); }  // clip_value
 
-// delta_yolo_box (yolo_layer.cpp:172-262), accumulate = 1; executed by ONE thread
-__device__ IousF delta_yolo_box(const LossParams& p, const BoxF& truth, int n, int index, int i, int j, float scale,
-                                float iou_normalizer) {
-  const int stride = p.W * p.H;
-  const float* x = p.out;
-  float* delta = p.delta;
-  IousF all;
-  BoxF pred = get_yolo_box(x, p.biases, n, index, i, j, p.W, p.H, p.net_w, p.net_h, stride);
-  all.iou = b_iou(pred, truth);
-  all.giou = b_giou(pred, truth);
-  all.diou = b_diou(pred, truth, 0.6f);
-  all.ciou = b_ciou(pred, truth);
+// Box delta of one (truth, location) pair, ACCUMULATED into delta (delta_yolo_box yolo_layer.cpp:172-262,
+// delta_gaussian_yolo_box gaussian_yolo_layer.cpp:198-402 with yolo_point = center).  Returns (iou, giou) for the layer
+// statistics.  Executed by one thread.
+__device__ float2 box_delta(const Head& p, const Box4& truth, long long base, int anchor, int col, int row) {
+  const int s = p.wh();
+  const float scale = 2 - truth.w * truth.h;
+  Box4 pred = predicted_box(p, base, anchor, col, row);
+  const Overlap o = overlap_of(pred, truth);
+  float2 r = make_float2(o.iou, giou_of(o));
   if (pred.w == 0) pred.w = 1.0f;
   if (pred.h == 0) pred.h = 1.0f;
-  if (p.iou_loss == IOU_MSE) {
-    const float tx = (truth.x * p.W - i);
-    const float ty = (truth.y * p.H - j);
-    const float tw = logf(truth.w * p.net_w / p.biases[2 * n]);
-    const float th = logf(truth.h * p.net_h / p.biases[2 * n + 1]);
-    delta[index + 0 * stride] += scale * (tx - x[index + 0 * stride]) * iou_normalizer;
-    delta[index + 1 * stride] += scale * (ty - x[index + 1 * stride]) * iou_normalizer;
-    delta[index + 2 * stride] += scale * (tw - x[index + 2 * stride]) * iou_normalizer;
-    delta[index + 3 * stride] += scale * (th - x[index + 3 * stride]) * iou_normalizer;
-  } else {
-    const DxRep g = b_dx_iou(pred, truth, p.iou_loss);
-    float dx = g.dt, dy = g.db, dw = g.dl, dh = g.dr;  // "dt, db, dl, dr are already dx, dy, dw, dh" (:229-232)
-    dw *= expf(x[index + 2 * stride]);
-    dh *= expf(x[index + 3 * stride]);
-    dx *= iou_normalizer; dy *= iou_normalizer; dw *= iou_normalizer; dh *= iou_normalizer;
-    dx = fix_nan_inf(dx); dy = fix_nan_inf(dy); dw = fix_nan_inf(dw); dh = fix_nan_inf(dh);
-    if (p.max_delta != FLT_MAX) {
-      dx = clip_value(dx, p.max_delta); dy = clip_value(dy, p.max_delta);
-      dw = clip_value(dw, p.max_delta); dh = clip_value(dh, p.max_delta);
+  // regression targets in the head's own parametrisation
+  const float target[4] = {truth.x * p.W - col, truth.y * p.H - row, logf(truth.w * p.net_w / p.anchors[2 * anchor]),
+                           logf(truth.h * p.net_h / p.anchors[2 * anchor + 1])};
+  if (!p.gaussian) {
+    float d[4];
+    if (p.iou_loss == K_MSE) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) d[k] = scale * (target[k] - p.out[base + k * s]) * p.iou_normalizer;
+    } else {
+      const float4 g = iou_family_grad_rt(pred, truth, p.iou_loss);
+      d[0] = g.x; d[1] = g.y;
+      d[2] = g.z * expf(p.out[base + 2 * s]);
+      d[3] = g.w * expf(p.out[base + 3 * s]);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        d[k] = sanitize(d[k] * p.iou_normalizer);
+        if (p.max_delta != FLT_MAX) d[k] = clamp_abs(d[k], p.max_delta);
+      }
     }
-    delta[index + 0 * stride] += dx;
-    delta[index + 1 * stride] += dy;
-    delta[index + 2 * stride] += dw;
-    delta[index + 3 * stride] += dh;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) p.delta[base + k * s] += d[k];
+    return r;
   }
-  return all;
-}
-
-// GetGaussianYoloBox (gaussian_yolo_layer.cpp:151-178), yolo_point = center
-__device__ __forceinline__ BoxF get_gaussian_box(const float* x, const float* biases, int n, int index, int i, int j, int lw,
-                                                 int lh, int w, int h, int stride) {
-  BoxF b;
-  b.w = expf(x[index + 4 * stride]) * biases[2 * n] / w;
-  b.h = expf(x[index + 6 * stride]) * biases[2 * n + 1] / h;
-  b.x = (i + x[index + 0 * stride]) / lw;
-  b.y = (j + x[index + 2 * stride]) / lh;
-  return b;
-}
-__device__ __forceinline__ BoxF get_box(const LossParams& p, int n, int index, int i, int j) {
-  const int wh = p.W * p.H;
-  return p.gaussian ? get_gaussian_box(p.out, p.biases, n, index, i, j, p.W, p.H, p.net_w, p.net_h, wh)
-                    : get_yolo_box(p.out, p.biases, n, index, i, j, p.W, p.H, p.net_w, p.net_h, wh);
-}
-
-// delta_gaussian_yolo_box (gaussian_yolo_layer.cpp:198-402), accumulate = 1, yolo_point = center; ONE thread.
-// The reference mixes float and double (the literals 1./2., M_PI, pow): the same promotions are kept.
-__device__ float delta_gaussian_box(const LossParams& p, const BoxF& truth, int n, int index, int i, int j, float scale,
-                                    float iou_normalizer) {
-  const int stride = p.W * p.H;
-  const float* x = p.out;
-  float* delta = p.delta;
-  BoxF pred = get_gaussian_box(x, p.biases, n, index, i, j, p.W, p.H, p.net_w, p.net_h, stride);
-  float iou = b_iou(pred, truth);
-  const float giou = b_giou(pred, truth);
-  if (pred.w == 0) pred.w = 1.0f;
-  if (pred.h == 0) pred.h = 1.0f;
+  // Gaussian head: negative log-likelihood of the target under N(mu, sigma) per coordinate (sigma_const 0.3, eps 1e-9);
+  // the reference evaluates it in a float / double mix that is kept here
   const float sigma_const = 0.3f;
   const float epsi = (float)pow(10.0, -9.0);
-  const float t4[4] = {truth.x * p.W - i, truth.y * p.H - j, logf(truth.w * p.net_w / p.biases[2 * n]),
-                       logf(truth.h * p.net_h / p.biases[2 * n + 1])};
-  float dl[4], du[4];
+  float dmu[4], dsg[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    const float mu = x[index + (2 * k) * stride], sg = x[index + (2 * k + 1) * stride];
-    const float d = t4[k] - mu;
-    const float in_exp = d / sg;
-    const float in_exp_2 = (float)pow((double)in_exp, 2.0);
-    const float normal = (float)(exp((double)in_exp_2 * (-1. / 2.)) / (sqrt(M_PI * 2.0) * (double)(sg + sigma_const)));
-    const float temp = (float)((1. / 2.) * 1. / (double)(normal + epsi) * (double)normal * (double)scale);
-    dl[k] = (float)((double)(temp * in_exp) * (1. / (double)sg));
-    du[k] = (float)((double)temp * ((double)(in_exp_2 / sg) - 1. / (double)(sg + sigma_const)));
+    const float mu = p.out[base + (2 * k) * s], sg = p.out[base + (2 * k + 1) * s];
+    const float z = (target[k] - mu) / sg;
+    const float z2 = (float)pow((double)z, 2.0);
+    const float normal = (float)(exp((double)z2 * (-1. / 2.)) / (sqrt(M_PI * 2.0) * (double)(sg + sigma_const)));
+    const float t = (float)((1. / 2.) * 1. / (double)(normal + epsi) * (double)normal * (double)scale);
+    dmu[k] = (float)((double)(t * z) * (1. / (double)sg));
+    dsg[k] = (float)((double)t * ((double)(z2 / sg) - 1. / (double)(sg + sigma_const)));
   }
-  if (p.iou_loss != IOU_MSE) {
-    iou = giou;
-    const DxRep g = b_dx_iou(pred, truth, p.iou_loss);
-    dl[0] = g.dt; dl[1] = g.db;
-    dl[2] = g.dl * expf(x[index + 4 * stride]);
-    dl[3] = g.dr * expf(x[index + 6 * stride]);
+  if (p.iou_loss == K_MSE) {
+    r.y = r.x;                // the Gaussian layer keeps ONE overlap figure for its statistics: IoU with mse ...
+  } else {                    // ... GIoU otherwise (gaussian_yolo_layer.cpp:352); IoU-family gradient for the means
+    r.x = r.y;
+    const float4 g = iou_family_grad_rt(pred, truth, p.iou_loss);
+    dmu[0] = g.x; dmu[1] = g.y;
+    dmu[2] = g.z * expf(p.out[base + 4 * s]);
+    dmu[3] = g.w * expf(p.out[base + 6 * s]);
   }
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    dl[k] = fix_nan_inf(dl[k] * iou_normalizer);
-    du[k] = fix_nan_inf(du[k] * p.uc_normalizer);
+    dmu[k] = sanitize(dmu[k] * p.iou_normalizer);
+    dsg[k] = sanitize(dsg[k] * p.uc_normalizer);
     if (p.max_delta != FLT_MAX) {
-      dl[k] = clip_value(dl[k], p.max_delta);
-      du[k] = clip_value(du[k], p.max_delta);
+      dmu[k] = clamp_abs(dmu[k], p.max_delta);
+      dsg[k] = clamp_abs(dsg[k], p.max_delta);
     }
-    delta[index + (2 * k) * stride] += dl[k];
-    delta[index + (2 * k + 1) * stride] += du[k];
+    p.delta[base + (2 * k) * s] += dmu[k];
+    p.delta[base + (2 * k + 1) * s] += dsg[k];
   }
-  return iou;
+  return r;
 }
 
-// DeltaGaussianYoloClass (gaussian_yolo_layer.cpp:429-461): the "already marked" test looks at the FIRST class entry
-// (delta[index]), no focal loss, no NaN filter.  Lanes split the class loop like delta_yolo_class.
-__device__ float delta_gaussian_class(const LossParams& p, int index, int class_id, int lane, int nl) {
-  const int stride = p.W * p.H;
-  const float* output = p.out;
-  float* delta = p.delta;
-  const bool marked = delta[index] != 0.f;
-  if (nl > 1) __syncwarp();
+// Class deltas of one (truth, location) pair (delta_yolo_class yolo_layer.cpp:285-357, DeltaGaussianYoloClass
+// gaussian_yolo_layer.cpp:429-461); cls0 = index of the cell's first class entry.  One thread.
+__device__ void class_delta(const Head& p, long long cls0, int class_id) {
+  const int s = p.wh();
+  const float smooth = p.label_smooth_eps;
+  const float on = smooth ? 1 * (1 - smooth) + 0.5f * smooth : 1.f;
+  const float off = smooth ? 0 * (1 - smooth) + 0.5f * smooth : 0.f;
+  // a location an earlier truth has already marked only gets this truth's class refreshed.  [yolo] looks at this class'
+  // delta, [Gaussian_yolo] at the first class' delta.
+  const bool marked = p.gaussian ? (p.delta[cls0] != 0.f) : (p.delta[cls0 + (long long)s * class_id] != 0.f);
   if (marked) {
-    float y_true = 1;
-    if (p.label_smooth_eps) y_true = y_true * (1 - p.label_smooth_eps) + 0.5f * p.label_smooth_eps;
-    if (lane == 0) delta[index + stride * class_id] = y_true - output[index + stride * class_id];
-    if (nl > 1) __syncwarp();
-    return output[index + stride * class_id];
+    const float r = on - p.out[cls0 + (long long)s * class_id];
+    if (p.gaussian || (!isnan(r) && !isinf(r))) p.delta[cls0 + (long long)s * class_id] = r;
+    return;
   }
-  for (int n = lane; n < p.classes; n += nl) {
-    float y_true = ((n == class_id) ? 1 : 0);
-    if (p.label_smooth_eps) y_true = y_true * (1 - p.label_smooth_eps) + 0.5f * p.label_smooth_eps;
-    delta[index + stride * n] = y_true - output[index + stride * n];
-  }
-  if (nl > 1) __syncwarp();
-  return output[index + stride * class_id];
-}
-
-// delta_yolo_class (yolo_layer.cpp:285-357); the class loop is strided over `nl` cooperating lanes (lane, nl) =
-// (0, 1) for a single thread.  Returns the avg_cat contribution.
-__device__ float delta_yolo_class(const LossParams& p, int index, int class_id, int lane, int nl) {
-  const int stride = p.W * p.H;
-  const float* output = p.out;
-  float* delta = p.delta;
-  if (delta[index + stride * class_id]) {  // this class was already marked by an earlier truth
-    float y_true = 1;
-    if (p.label_smooth_eps) y_true = y_true * (1 - p.label_smooth_eps) + 0.5f * p.label_smooth_eps;
-    const float r = y_true - output[index + stride * class_id];
-    if (nl > 1) __syncwarp();
-    if (lane == 0 && !isnan(r) && !isinf(r)) delta[index + stride * class_id] = r;
-    if (nl > 1) __syncwarp();
-    return output[index + stride * class_id];
-  }
-  if (nl > 1) __syncwarp();
-  if (p.focal_loss) {
-    const float alpha = 0.5f;
-    const int ti = index + stride * class_id;
-    const float pt = output[ti] + 0.000000000000001F;
+  if (p.focal_loss && !p.gaussian) {
+    const float pt = p.out[cls0 + (long long)s * class_id] + 0.000000000000001F;
     const float grad = -(1 - pt) * (2 * pt * logf(pt) + pt - 1);
-    for (int n = lane; n < p.classes; n += nl) {
-      float d = (((n == class_id) ? 1 : 0) - output[index + stride * n]);
-      d *= alpha * grad;
-      delta[index + stride * n] = d;
+    for (int c = 0; c < p.classes; ++c) {
+      float d = ((c == class_id) ? 1 : 0) - p.out[cls0 + (long long)s * c];
+      d *= 0.5f * grad;
+      p.delta[cls0 + (long long)s * c] = d;
     }
-  } else {
-    for (int n = lane; n < p.classes; n += nl) {
-      float y_true = ((n == class_id) ? 1 : 0);
-      if (p.label_smooth_eps) y_true = y_true * (1 - p.label_smooth_eps) + 0.5f * p.label_smooth_eps;
-      const float r = y_true - output[index + stride * n];
-      if (!isnan(r) && !isinf(r)) delta[index + stride * n] = r;
-    }
+    return;
   }
-  if (nl > 1) __syncwarp();
-  return output[index + stride * class_id];
+  for (int c = 0; c < p.classes; ++c) {
+    const float r = (c == class_id ? on : off) - p.out[cls0 + (long long)s * c];
+    if (p.gaussian || (!isnan(r) && !isinf(r))) p.delta[cls0 + (long long)s * c] = r;
+  }
 }
 
-// ---- 1. per (image, anchor, cell): objectness delta from the best IoU over the truths (yolo_layer.cpp:431-522) ----
-__global__ void yolo_loss_cells_kernel(LossParams p) {
-  const int wh = p.W * p.H;
-  const long long total = (long long)p.B * p.n * wh;
-  for (long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; t0 < total; t0 += (long long)gridDim.x * blockDim.x) {
-    const int loc = (int)(t0 % wh);
-    const int n = (int)((t0 / wh) % p.n);
-    const int b = (int)(t0 / ((long long)wh * p.n));
-    const int i = loc % p.W, j = loc / p.W;
-    const int box_index = entry_index(p, b, n * wh + loc, 0);
-    const int obj_index = entry_index(p, b, n * wh + loc, box_entries(p));
-    const int class_index = entry_index(p, b, n * wh + loc, box_entries(p) + 1);
-    const BoxF pred = get_box(p, p.mask[n], box_index, i, j);
-    float best_match_iou = 0, best_iou = 0;
+constexpr int kMaxTruthSmem = 256;  // truth boxes staged per image (the cfgs use max = 90 .. 200)
+
+// the truth list of image b into shared memory; returns the number of entries before the terminator
+__device__ int stage_truths(const Head& p, int b, float* sh /* [max_boxes*5] */, int* sh_end) {
+  const float* tr = p.truth + (long long)b * p.max_boxes * 5;
+  if (threadIdx.x == 0) *sh_end = p.max_boxes;
+  for (int i = threadIdx.x; i < p.max_boxes * 5; i += blockDim.x) sh[i] = tr[i];
+  __syncthreads();
+  for (int t = threadIdx.x; t < p.max_boxes; t += blockDim.x) {
+    const int cls = (int)sh[t * 5 + 4];
+    if (cls < p.classes && cls >= 0 && !sh[t * 5]) atomicMin(sh_end, t);  // first valid-class entry with x == 0 ends the list
+  }
+  __syncthreads();
+  return *sh_end;
+}
+__device__ __forceinline__ bool truth_valid(const Head& p, const float* sh, int t) {
+  const int cls = (int)sh[t * 5 + 4];
+  return cls < p.classes && cls >= 0;
+}
+
+// ---- objectness pass (yolo_layer.cpp:431-522) ----------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) yolo_objectness_kernel(Head p) {
+  __shared__ float tr[kMaxTruthSmem * 5];
+  __shared__ int end_s;
+  const int b = blockIdx.y;
+  const int n_truth = stage_truths(p, b, tr, &end_s);
+  const int s = p.wh();
+  const int be = p.box_entries();
+  for (int t0 = blockIdx.x * blockDim.x + threadIdx.x; t0 < p.n * s; t0 += gridDim.x * blockDim.x) {
+    const int a = t0 / s, cell = t0 - a * s;
+    const int col = cell % p.W, row = cell / p.W;
+    const long long base = p.at(b, a, 0, cell);
+    const Box4 pred = predicted_box(p, base, p.mask[a], col, row);
+    float best_iou = 0, best_match = 0;
     int best_t = 0;
-    int class_match = -1;  // compare_yolo_class(..., 0.25f) does not depend on the truth: evaluated once, on demand
-    const float* tr = p.truth + (long long)b * p.max_boxes * 5;
-    for (int t = 0; t < p.max_boxes; ++t) {
-      const BoxF truth{tr[t * 5 + 0], tr[t * 5 + 1], tr[t * 5 + 2], tr[t * 5 + 3]};
-      const int class_id = (int)tr[t * 5 + 4];
-      if (class_id >= p.classes || class_id < 0) continue;
-      if (!truth.x) break;
-      if (class_match < 0) {
-        class_match = 0;
+    int confident = -1;  // compare_yolo_class(..., 0.25): some class score above 0.25; evaluated once, on demand
+    for (int t = 0; t < n_truth; ++t) {
+      if (!truth_valid(p, tr, t)) continue;
+      const Box4 g{tr[t * 5], tr[t * 5 + 1], tr[t * 5 + 2], tr[t * 5 + 3]};
+      if (confident < 0) {
+        confident = 0;
         for (int c = 0; c < p.classes; ++c)
-          if (p.out[class_index + wh * c] > 0.25f) { class_match = 1; break; }
+          if (p.out[base + (long long)(be + 1 + c) * s] > 0.25f) { confident = 1; break; }
       }
-      const float iou = b_iou(pred, truth);
-      if (iou > best_match_iou && class_match == 1) best_match_iou = iou;
+      const float iou = iou_of(pred, g);
+      if (iou > best_match && confident == 1) best_match = iou;
       if (iou > best_iou) { best_iou = iou; best_t = t; }
     }
-    const float o = p.out[obj_index];
-    float d = p.cls_normalizer * (0 - o);
-    if (best_match_iou > p.ignore_thresh) d = 0;
-    p.delta[obj_index] = d;
-    if (best_iou > p.truth_thresh) {
-      p.delta[obj_index] = p.cls_normalizer * (1 - o);
-      const int class_id = (int)tr[best_t * 5 + 4];
-      const BoxF truth{tr[best_t * 5 + 0], tr[best_t * 5 + 1], tr[best_t * 5 + 2], tr[best_t * 5 + 3]};
-      if (p.gaussian) {
-        delta_gaussian_class(p, class_index, class_id, 0, 1);
-        delta_gaussian_box(p, truth, p.mask[n], box_index, i, j, (2 - truth.w * truth.h), p.iou_normalizer);
-      } else {
-        delta_yolo_class(p, class_index, class_id, 0, 1);
-        delta_yolo_box(p, truth, p.mask[n], box_index, i, j, (2 - truth.w * truth.h), p.iou_normalizer);
-      }
+    const float obj = p.out[base + (long long)be * s];
+    p.delta[base + (long long)be * s] = best_match > p.ignore_thresh ? 0.f : p.cls_normalizer * (0 - obj);
+    if (best_iou > p.truth_thresh) {  // (truth_thresh = 1 in every cfg of the path: this never fires there)
+      p.delta[base + (long long)be * s] = p.cls_normalizer * (1 - obj);
+      const Box4 g{tr[best_t * 5], tr[best_t * 5 + 1], tr[best_t * 5 + 2], tr[best_t * 5 + 3]};
+      class_delta(p, base + (long long)(be + 1) * s, (int)tr[best_t * 5 + 4]);
+      box_delta(p, g, base, p.mask[a], col, row);
     }
   }
 }
 
-// ---- 2. one warp per image: the truths in order (yolo_layer.cpp:524-676) -------------------------------------------
-__global__ void yolo_loss_truths_kernel(LossParams p) {
+// ---- assignment pass (yolo_layer.cpp:524-676) -----------------------------------------------------------------------------
+// record (t, k): truth t with its best anchor (k = 0) or with anchor k - 1 when that one passes iou_thresh (k >= 1)
+struct Rec {
+  int loc;     // slot * wh + cell inside the image, -1: not applicable
+  short t, anchor;
+};
+__global__ void __launch_bounds__(128) yolo_assign_kernel(Head p) {
+  extern __shared__ unsigned char smem_[];
+  float* tr = reinterpret_cast<float*>(smem_);                       // [max_boxes*5]
+  Rec* recs = reinterpret_cast<Rec*>(tr + p.max_boxes * 5);            // [max_boxes*(total+1)]
+  float* rstat = reinterpret_cast<float*>(recs + p.max_boxes * (p.total + 1));     // (iou, giou) per applied record
+  __shared__ int end_s;
   const int b = blockIdx.x;
-  const int lane = threadIdx.x;
-  const int wh = p.W * p.H;
-  const float* tr = p.truth + (long long)b * p.max_boxes * 5;
-  float tot_iou = 0, tot_iou_loss = 0, tot_giou_loss = 0;
-  int count = 0;
-  for (int t = 0; t < p.max_boxes; ++t) {
-    const BoxF truth{tr[t * 5 + 0], tr[t * 5 + 1], tr[t * 5 + 2], tr[t * 5 + 3]};
-    const int class_id = (int)tr[t * 5 + 4];
-    if (class_id >= p.classes || class_id < 0) continue;
-    if (!truth.x) break;
-    float best_iou = 0;
-    int best_n = 0;
-    const int i = (int)(truth.x * p.W);
-    const int j = (int)(truth.y * p.H);
-    BoxF truth_shift = truth;
-    truth_shift.x = truth_shift.y = 0;
-    for (int n = 0; n < p.total; ++n) {
-      BoxF pred{0, 0, p.biases[2 * n] / p.net_w, p.biases[2 * n + 1] / p.net_h};
-      const float iou = b_iou(pred, truth_shift);
-      if (iou > best_iou) { best_iou = iou; best_n = n; }
+  const int n_truth = stage_truths(p, b, tr, &end_s);
+  const int s = p.wh();
+  const int per = p.total + 1;
+  const int n_rec = n_truth * per;
+  // records: thread per truth
+  for (int t = threadIdx.x; t < n_truth; t += blockDim.x) {
+    for (int k = 0; k < per; ++k) recs[t * per + k].loc = -1;
+    if (!truth_valid(p, tr, t)) continue;
+    const Box4 g{tr[t * 5], tr[t * 5 + 1], tr[t * 5 + 2], tr[t * 5 + 3]};
+    const int col = (int)(g.x * p.W), row = (int)(g.y * p.H);
+    const Box4 shape{0, 0, g.w, g.h};
+    float best = 0;
+    int best_a = 0;
+    for (int a = 0; a < p.total; ++a) {  // best anchor by shape IoU
+      const Box4 an{0, 0, p.anchors[2 * a] / p.net_w, p.anchors[2 * a + 1] / p.net_h};
+      const float iou = iou_of(an, shape);
+      if (iou > best) { best = iou; best_a = a; }
     }
-    for (int pass = 0; pass <= p.total; ++pass) {
-      // pass 0: the best anchor (:563-605); passes 1..total: the other anchors over iou_thresh (:607-676)
-      int n_abs, mask_n = -1;
-      if (pass == 0) {
-        n_abs = best_n;
-      } else {
-        n_abs = pass - 1;
-        if (n_abs == best_n || !(p.iou_thresh < 1.0f)) continue;
+    for (int k = 0; k < per; ++k) {
+      const int a = k == 0 ? best_a : k - 1;
+      if (k > 0) {
+        if (a == best_a || !(p.iou_thresh < 1.0f)) continue;
+        const Box4 an{0, 0, p.anchors[2 * a] / p.net_w, p.anchors[2 * a + 1] / p.net_h};
+        if (!(measure_of(an, shape, p.iou_thresh_kind) > p.iou_thresh)) continue;
       }
+      int slot = -1;
       for (int m = 0; m < p.n; ++m)
-        if (p.mask[m] == n_abs) { mask_n = m; break; }  // int_index
-      if (mask_n < 0) continue;
-      if (pass > 0) {
-        BoxF pred{0, 0, p.biases[2 * n_abs] / p.net_w, p.biases[2 * n_abs + 1] / p.net_h};
-        const float iou = b_iou_kind(pred, truth_shift, p.iou_thresh_kind);
-        if (!(iou > p.iou_thresh)) continue;
-      }
-      const int loc = mask_n * wh + j * p.W + i;
-      const int box_index = entry_index(p, b, loc, 0);
-      const int obj_index = entry_index(p, b, loc, box_entries(p));
-      const int class_index = entry_index(p, b, loc, box_entries(p) + 1);
-      __syncwarp();
-      IousF all{0, 0, 0, 0};
-      if (lane == 0) {
-        if (p.gaussian) all.iou = all.giou = delta_gaussian_box(p, truth, n_abs, box_index, i, j, (2 - truth.w * truth.h), p.iou_normalizer);
-        else all = delta_yolo_box(p, truth, n_abs, box_index, i, j, (2 - truth.w * truth.h), p.iou_normalizer);
-        p.delta[obj_index] = p.cls_normalizer * (1 - p.out[obj_index]);
-        tot_iou += all.iou;
-        tot_iou_loss += 1 - all.iou;
-        tot_giou_loss += 1 - all.giou;
-        ++count;
-      }
-      __syncwarp();
-      if (p.gaussian) delta_gaussian_class(p, class_index, class_id, lane, 32);
-      else delta_yolo_class(p, class_index, class_id, lane, 32);
+        if (p.mask[m] == a) { slot = m; break; }  // int_index: is this anchor one of this head's?
+      if (slot < 0) continue;
+      recs[t * per + k] = Rec{slot * s + row * p.W + col, (short)t, (short)a};
     }
   }
-  if (lane == 0 && count > 0) {
-    atomicAdd(&p.stats[1], (float)count);
-    atomicAdd(&p.stats[2], tot_iou_loss);
-    atomicAdd(&p.stats[3], tot_giou_loss);
-    atomicAdd(&p.stats[6], tot_iou);
-    atomicAdd(&p.stats[7], (float)count);
-  }
-}
-
-// ---- 3. per (image, anchor, cell): averages_yolo_deltas (:264-283, :679-696), the two sums of squares of the cost
-// (:708-733), and BackwardYoloLayer's prev.delta += delta (:774-777) into the head conv's NHWC bf16 delta -----------
-__global__ void yolo_loss_finish_kernel(LossParams p, __nv_bfloat16* __restrict__ prev, long long prev_ld) {
-  const int wh = p.W * p.H;
-  const int BE = box_entries(p);
-  const int E = BE + 1 + p.classes;
-  const long long total = (long long)p.B * p.n * wh;
-  float s_all = 0, s_nobox = 0;
-  for (long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; t0 < total; t0 += (long long)gridDim.x * blockDim.x) {
-    const int loc = (int)(t0 % wh);
-    const int n = (int)((t0 / wh) % p.n);
-    const int b = (int)(t0 / ((long long)wh * p.n));
-    const int base = entry_index(p, b, n * wh + loc, 0);
-    int in_box = 0;
-    for (int c = 0; c < p.classes; ++c)
-      if (p.delta[base + (BE + 1 + c) * wh] > 0) ++in_box;
-    __nv_bfloat16* pv = prev ? prev + ((long long)b * wh + loc) * prev_ld + n * E : nullptr;
-    for (int e = 0; e < E; ++e) {
-      float d = p.delta[base + e * wh];
-      if (e < BE && in_box > 0) {
-        d /= in_box;
-        p.delta[base + e * wh] = d;
-      }
-      s_all += d * d;
-      if (e >= BE) s_nobox += d * d;
-      if (pv) pv[e] = __float2bfloat16_rn(__bfloat162float(pv[e]) + d);
-    }
-  }
-  __shared__ float sh[2][32];
-  for (int off = 16; off; off >>= 1) {
-    s_all += __shfl_xor_sync(0xffffffffu, s_all, off);
-    s_nobox += __shfl_xor_sync(0xffffffffu, s_nobox, off);
-  }
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (lane == 0) { sh[0][warp] = s_all; sh[1][warp] = s_nobox; }
   __syncthreads();
-  if (warp == 0) {
-    const int nw = blockDim.x >> 5;
-    float a = lane < nw ? sh[0][lane] : 0.f, q = lane < nw ? sh[1][lane] : 0.f;
-    for (int off = 16; off; off >>= 1) {
-      a += __shfl_xor_sync(0xffffffffu, a, off);
-      q += __shfl_xor_sync(0xffffffffu, q, off);
+  // resolve: the first record of a location applies every record of that location, in record order
+  for (int r = threadIdx.x; r < n_rec; r += blockDim.x) {
+    rstat[2 * r] = rstat[2 * r + 1] = 0.f;
+    const int loc = recs[r].loc;
+    if (loc < 0) continue;
+    bool owner = true;
+    for (int q = 0; q < r && owner; ++q) owner = recs[q].loc != loc;
+    if (!owner) continue;
+    const int slot = loc / s, cell = loc - slot * s;
+    const int col = cell % p.W, row = cell / p.W;
+    const long long base = p.at(b, slot, 0, cell);
+    const int be = p.box_entries();
+    for (int q = r; q < n_rec; ++q) {
+      if (recs[q].loc != loc) continue;
+      const int t = recs[q].t;
+      const Box4 g{tr[t * 5], tr[t * 5 + 1], tr[t * 5 + 2], tr[t * 5 + 3]};
+      const float2 m = box_delta(p, g, base, recs[q].anchor, col, row);
+      rstat[2 * q] = m.x;
+      rstat[2 * q + 1] = m.y;
+      p.delta[base + (long long)be * s] = p.cls_normalizer * (1 - p.out[base + (long long)be * s]);
+      class_delta(p, base + (long long)(be + 1) * s, (int)tr[t * 5 + 4]);
     }
-    if (lane == 0) {
-      atomicAdd(&p.stats[4], a);
-      atomicAdd(&p.stats[5], q);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {  // this image's statistics, summed in record order
+    float count = 0, iou_loss = 0, giou_loss = 0, iou_sum = 0;
+    for (int r = 0; r < n_rec; ++r) {
+      if (recs[r].loc < 0) continue;
+      count += 1;
+      iou_sum += rstat[2 * r];
+      iou_loss += 1 - rstat[2 * r];
+      giou_loss += 1 - rstat[2 * r + 1];
     }
+    float* o = p.img_partial(b);
+    o[0] = count; o[1] = iou_loss; o[2] = giou_loss; o[3] = iou_sum;
   }
 }
 
-// The same, tiled: one block per (image, 32 cells) stages all n*E delta entries of those cells in shared memory, so the
-// fp32 NCHW planes are read and written 128 bytes per warp and the NHWC bf16 head delta is updated row by row
-// (n*E consecutive channels per cell) instead of one 2-byte access per thread at a pitch of prev_ld.
-__global__ void __launch_bounds__(256) yolo_loss_finish_tiled_kernel(LossParams p, __nv_bfloat16* __restrict__ prev,
-                                                                     long long prev_ld) {
-  extern __shared__ float tile[];  // [n*E][33] then int cnt[n][32]
-  const int wh = p.W * p.H;
-  const int BE = box_entries(p);
-  const int E = BE + 1 + p.classes;
-  const int CH = p.n * E;
-  int* cnt = reinterpret_cast<int*>(tile + CH * 33);
-  const int tiles = (wh + 31) / 32;
-  const int b = blockIdx.x / tiles, loc0 = (blockIdx.x % tiles) * 32;
-  float* dl = p.delta + (long long)b * CH * wh;
+// ---- finish pass: averages_yolo_deltas (:264-283, :679-696), sums of squares of the cost (:708-733), BackwardYoloLayer's
+// prev.delta += delta (:774-777) into the head conv's NHWC bf16 delta.  Block per (image, 32 cells): all n*E entries of the
+// cells staged in shared memory, so the fp32 NCHW planes move 128 bytes per warp and the NHWC delta is updated row by row.
+__global__ void __launch_bounds__(256) yolo_finish_tiled_kernel(Head p, __nv_bfloat16* __restrict__ prev, long long prev_ld) {
+  extern __shared__ float tile[];  // [n*E][33] then int positives[n][32]
+  const int s = p.wh();
+  const int be = p.box_entries(), E = p.entries(), CH = p.n * E;
+  int* positives = reinterpret_cast<int*>(tile + CH * 33);
+  const int tiles = (s + 31) / 32;
+  const int b = blockIdx.x / tiles, cell0 = (blockIdx.x % tiles) * 32;
+  float* dl = p.delta + (long long)b * CH * s;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const bool loc_ok = loc0 + lane < wh;
-  for (int ch = warp; ch < CH; ch += 8) tile[ch * 33 + lane] = loc_ok ? dl[(long long)ch * wh + loc0 + lane] : 0.f;
+  const bool in_range = cell0 + lane < s;
+  for (int ch = warp; ch < CH; ch += 8) tile[ch * 33 + lane] = in_range ? dl[(long long)ch * s + cell0 + lane] : 0.f;
   __syncthreads();
   for (int t = threadIdx.x; t < p.n * 32; t += 256) {
     const int a = t >> 5, l = t & 31;
-    int in_box = 0;
+    int k = 0;
     for (int c = 0; c < p.classes; ++c)
-      if (tile[(a * E + BE + 1 + c) * 33 + l] > 0) ++in_box;
-    cnt[t] = in_box;
+      if (tile[(a * E + be + 1 + c) * 33 + l] > 0) ++k;
+    positives[t] = k;
   }
   __syncthreads();
-  float s_all = 0, s_nobox = 0;
+  float sum_all = 0, sum_rest = 0;
   for (int ch = warp; ch < CH; ch += 8) {
     const int a = ch / E, e = ch - a * E;
     float d = tile[ch * 33 + lane];
-    const int in_box = cnt[a * 32 + lane];
-    if (e < BE && in_box > 0 && loc_ok) {
-      d /= in_box;
-      dl[(long long)ch * wh + loc0 + lane] = d;
+    const int k = positives[a * 32 + lane];
+    if (e < be && k > 0 && in_range) {
+      d /= k;
+      dl[(long long)ch * s + cell0 + lane] = d;
       tile[ch * 33 + lane] = d;
     }
-    s_all += d * d;  // cells past wh hold zeros
-    if (e >= BE) s_nobox += d * d;
+    sum_all += d * d;  // cells past the image hold zeros
+    if (e >= be) sum_rest += d * d;
   }
   __syncthreads();
   if (prev) {
-    for (int l = warp; l < 32 && loc0 + l < wh; l += 8) {
-      __nv_bfloat16* pv = prev + ((long long)b * wh + loc0 + l) * prev_ld;
+    for (int l = warp; l < 32 && cell0 + l < s; l += 8) {
+      __nv_bfloat16* pv = prev + ((long long)b * s + cell0 + l) * prev_ld;
       for (int c2 = lane * 2; c2 < CH; c2 += 64) {
         if (c2 + 1 < CH) {
           __nv_bfloat162* q = reinterpret_cast<__nv_bfloat162*>(pv + c2);
@@ -627,31 +506,88 @@ __global__ void __launch_bounds__(256) yolo_loss_finish_tiled_kernel(LossParams 
       }
     }
   }
-  __shared__ float sh[2][8];
+  __shared__ float part[2][8];
   for (int off = 16; off; off >>= 1) {
-    s_all += __shfl_xor_sync(0xffffffffu, s_all, off);
-    s_nobox += __shfl_xor_sync(0xffffffffu, s_nobox, off);
+    sum_all += __shfl_xor_sync(0xffffffffu, sum_all, off);
+    sum_rest += __shfl_xor_sync(0xffffffffu, sum_rest, off);
   }
-  if (lane == 0) { sh[0][warp] = s_all; sh[1][warp] = s_nobox; }
+  if (lane == 0) { part[0][warp] = sum_all; part[1][warp] = sum_rest; }
   __syncthreads();
   if (threadIdx.x == 0) {
     float a = 0, q = 0;
-    for (int w = 0; w < 8; ++w) { a += sh[0][w]; q += sh[1][w]; }
-    atomicAdd(&p.stats[4], a);
-    atomicAdd(&p.stats[5], q);
+    for (int w = 0; w < 8; ++w) { a += part[0][w]; q += part[1][w]; }
+    float* o = p.blk_partial(blockIdx.x);
+    o[0] = a; o[1] = q;
+  }
+}
+// the same without the shared-memory tile, for heads whose n*E entries do not fit it: thread per (image, anchor, cell)
+__global__ void __launch_bounds__(128) yolo_finish_kernel(Head p, __nv_bfloat16* __restrict__ prev, long long prev_ld) {
+  const int s = p.wh();
+  const int be = p.box_entries(), E = p.entries();
+  const long long total = (long long)p.B * p.n * s;
+  float sum_all = 0, sum_rest = 0;
+  for (long long t0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; t0 < total; t0 += (long long)gridDim.x * blockDim.x) {
+    const int cell = (int)(t0 % s);
+    const int a = (int)((t0 / s) % p.n);
+    const int b = (int)(t0 / ((long long)s * p.n));
+    const long long base = p.at(b, a, 0, cell);
+    int k = 0;
+    for (int c = 0; c < p.classes; ++c)
+      if (p.delta[base + (long long)(be + 1 + c) * s] > 0) ++k;
+    __nv_bfloat16* pv = prev ? prev + ((long long)b * s + cell) * prev_ld + a * E : nullptr;
+    for (int e = 0; e < E; ++e) {
+      float d = p.delta[base + (long long)e * s];
+      if (e < be && k > 0) {
+        d /= k;
+        p.delta[base + (long long)e * s] = d;
+      }
+      sum_all += d * d;
+      if (e >= be) sum_rest += d * d;
+      if (pv) pv[e] = __float2bfloat16_rn(__bfloat162float(pv[e]) + d);
+    }
+  }
+  __shared__ float part[2][4];
+  for (int off = 16; off; off >>= 1) {
+    sum_all += __shfl_xor_sync(0xffffffffu, sum_all, off);
+    sum_rest += __shfl_xor_sync(0xffffffffu, sum_rest, off);
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) { part[0][warp] = sum_all; part[1][warp] = sum_rest; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0, q = 0;
+    for (int w = 0; w < 4; ++w) { a += part[0][w]; q += part[1][w]; }
+    float* o = p.blk_partial(blockIdx.x);
+    o[0] = a; o[1] = q;
   }
 }
 
-// *(l->cost) (yolo_layer.cpp:735-754)
-__global__ void yolo_loss_cost_kernel(LossParams p) {
-  float count = p.stats[1];
-  if (count == 0) count = 1;
-  const float classification_loss = p.cls_normalizer * p.stats[5];
-  if (p.iou_loss == IOU_MSE || p.gaussian) {  // Gaussian: *(l->cost) = |delta|^2 always (gaussian_yolo_layer.cpp:835)
-    p.stats[0] = p.stats[4];
+// ---- cost pass: partial sums in index order, then *(l->cost) (yolo_layer.cpp:735-754, gaussian_yolo_layer.cpp:835) --------
+__global__ void __launch_bounds__(256) yolo_cost_kernel(Head p) {
+  __shared__ float acc[256][2];
+  float a = 0, q = 0;
+  for (int k = threadIdx.x; k < p.finish_blocks; k += 256) {
+    a += p.blk_partial(k)[0];
+    q += p.blk_partial(k)[1];
+  }
+  acc[threadIdx.x][0] = a;
+  acc[threadIdx.x][1] = q;
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  float sum_all = 0, sum_rest = 0;
+  for (int k = 0; k < 256; ++k) { sum_all += acc[k][0]; sum_rest += acc[k][1]; }
+  float count = 0, iou_loss = 0, giou_loss = 0, iou_sum = 0;
+  for (int b = 0; b < p.B; ++b) {
+    const float* o = p.img_partial(b);
+    count += o[0]; iou_loss += o[1]; giou_loss += o[2]; iou_sum += o[3];
+  }
+  float* st = p.stats;
+  st[1] = count; st[2] = iou_loss; st[3] = giou_loss; st[4] = sum_all; st[5] = sum_rest; st[6] = iou_sum; st[7] = count;
+  if (p.iou_loss == K_MSE || p.gaussian) {
+    st[0] = sum_all;
   } else {
-    const float tot = p.iou_loss == IOU_GIOU ? p.stats[3] : p.stats[2];
-    p.stats[0] = p.iou_normalizer * (tot / count) + classification_loss;
+    const float n = count == 0 ? 1 : count;
+    st[0] = p.iou_normalizer * ((p.iou_loss == K_GIOU ? giou_loss : iou_loss) / n) + p.cls_normalizer * sum_rest;
   }
 }
 
@@ -659,46 +595,57 @@ __global__ void yolo_loss_cost_kernel(LossParams p) {
 
 using namespace yc;
 
+// floats of the `stats` buffer yc_yolo_loss needs for a head of n images and h x w cells: the 8 public values, one
+// 4-float partial per image and one 2-float partial per block of the finish pass
+extern "C" size_t yc_yolo_loss_stats_floats(int n, int h, int w) {
+  const size_t tiles = (size_t)n * (((size_t)h * w + 31) / 32);
+  return 8 + 4 * (size_t)n + 2 * std::max<size_t>(tiles, (size_t)148 * 16);
+}
+
 extern "C" int yc_yolo_loss(const yc_yolo_loss_desc* d, const float* out_nchw, const float* truth, const float* anchor_wh,
                             const int* mask, int n, int h, int w, float* delta_nchw, const yc_tensor* prev_delta,
                             float* stats, void* stream) {
   YC_REQUIRE(d && out_nchw && truth && anchor_wh && mask && delta_nchw && stats && n > 0 && h > 0 && w > 0,
              "yc_yolo_loss: bad arguments");
   YC_REQUIRE(d->anchors > 0 && d->total >= d->anchors && d->classes > 0 && d->max_boxes > 0, "yc_yolo_loss: bad descriptor");
+  YC_REQUIRE(d->max_boxes <= kMaxTruthSmem, "yc_yolo_loss: more than %d truth boxes per image", kMaxTruthSmem);
   const int E = (d->gaussian ? 9 : 5) + d->classes;
   if (prev_delta)
     YC_REQUIRE(prev_delta->dtype == YC_BF16 && prev_delta->n == n && prev_delta->h == h && prev_delta->w == w &&
                    prev_delta->ldc >= d->anchors * E,
                "yc_yolo_loss: prev_delta must be the head conv's NHWC bf16 delta");
+  YC_REQUIRE(!(d->gaussian && d->focal_loss), "yc_yolo_loss: [Gaussian_yolo] has no focal loss");
   cudaStream_t st = (cudaStream_t)stream;
-  LossParams p;
+  Head p;
   p.B = n; p.H = h; p.W = w; p.n = d->anchors; p.total = d->total; p.classes = d->classes; p.max_boxes = d->max_boxes;
   p.net_w = d->net_w; p.net_h = d->net_h; p.iou_loss = d->iou_loss; p.iou_thresh_kind = d->iou_thresh_kind;
   p.focal_loss = d->focal_loss; p.ignore_thresh = d->ignore_thresh; p.truth_thresh = d->truth_thresh;
   p.iou_thresh = d->iou_thresh; p.iou_normalizer = d->iou_normalizer; p.cls_normalizer = d->cls_normalizer;
   p.label_smooth_eps = d->label_smooth_eps; p.max_delta = d->max_delta;
   p.gaussian = d->gaussian ? 1 : 0; p.uc_normalizer = d->uc_normalizer;
-  YC_REQUIRE(!(p.gaussian && p.focal_loss), "yc_yolo_loss: [Gaussian_yolo] has no focal loss");
-  p.out = out_nchw; p.truth = truth; p.biases = anchor_wh; p.mask = mask; p.delta = delta_nchw; p.stats = stats;
+  p.out = out_nchw; p.truth = truth; p.anchors = anchor_wh; p.mask = mask; p.delta = delta_nchw; p.stats = stats;
   const size_t elems = (size_t)n * d->anchors * E * h * w;
   YC_CUDA(cudaMemsetAsync(delta_nchw, 0, elems * 4, st));
-  YC_CUDA(cudaMemsetAsync(stats, 0, 8 * sizeof(float), st));
-  const long long cells = (long long)n * d->anchors * h * w;
-  const int grid = (int)std::max<long long>(1, std::min<long long>(ceil_div_ll(cells, 128), (long long)sm_count() * 16));
-  yolo_loss_cells_kernel<<<grid, 128, 0, st>>>(p);
+  const int cells = d->anchors * h * w;
+  const dim3 grid_obj((unsigned)std::max(1, std::min(ceil_div(cells, 128), std::max(1, sm_count() * 16 / n))), (unsigned)n);
+  yolo_objectness_kernel<<<grid_obj, 128, 0, st>>>(p);
   YC_LAUNCH_CHECK();
-  yolo_loss_truths_kernel<<<n, 32, 0, st>>>(p);
+  const size_t assign_smem = (size_t)d->max_boxes * 5 * 4 + (size_t)d->max_boxes * (d->total + 1) * (sizeof(Rec) + sizeof(float2));
+  YC_REQUIRE(assign_smem <= 48 * 1024, "yc_yolo_loss: max_boxes * (num + 1) too large for the assignment pass");
+  yolo_assign_kernel<<<n, 128, assign_smem, st>>>(p);
   YC_LAUNCH_CHECK();
   const size_t tile_bytes = (size_t)d->anchors * E * 33 * 4 + (size_t)d->anchors * 32 * 4;
+  __nv_bfloat16* pv = prev_delta ? (__nv_bfloat16*)prev_delta->ptr : nullptr;
+  const long long pld = prev_delta ? prev_delta->ldc : 0;
   if (tile_bytes <= 48 * 1024 && (!prev_delta || prev_delta->ldc % 2 == 0)) {
-    yolo_loss_finish_tiled_kernel<<<n * ((h * w + 31) / 32), 256, tile_bytes, st>>>(
-        p, prev_delta ? (__nv_bfloat16*)prev_delta->ptr : nullptr, prev_delta ? prev_delta->ldc : 0);
+    p.finish_blocks = n * ((h * w + 31) / 32);
+    yolo_finish_tiled_kernel<<<p.finish_blocks, 256, tile_bytes, st>>>(p, pv, pld);
   } else {
-    yolo_loss_finish_kernel<<<grid, 128, 0, st>>>(p, prev_delta ? (__nv_bfloat16*)prev_delta->ptr : nullptr,
-                                                  prev_delta ? prev_delta->ldc : 0);
+    p.finish_blocks = (int)std::max<long long>(1, std::min<long long>(ceil_div_ll((long long)n * cells, 128), (long long)148 * 16));
+    yolo_finish_kernel<<<p.finish_blocks, 128, 0, st>>>(p, pv, pld);
   }
   YC_LAUNCH_CHECK();
-  yolo_loss_cost_kernel<<<1, 1, 0, st>>>(p);
+  yolo_cost_kernel<<<1, 256, 0, st>>>(p);
   YC_LAUNCH_CHECK();
   return YC_OK;
 }

@@ -93,7 +93,8 @@ _SIGS = {
     "yc_bn_finalize": (C.c_int, [_P, _P, C.c_longlong, _P, _P, _P, _P, C.c_int, _P]),
     "yc_bn_act_fwd": (C.c_int, [_TP, _P, _P, _P, _P, C.c_int, _TP, _P]),
     "yc_bn_bwd": (C.c_int, [_TP, _TP, _P, _P, _P, _P, C.c_int, _P, _P, _P, _TP, _P]),
-    "yc_bias_act_bwd": (C.c_int, [_TP, _TP, C.c_int, _P, _TP, _P]),
+    "yc_bias_act_bwd": (C.c_int, [_TP, _TP, C.c_int, _P, _P, _TP, _P]),
+    "yc_bn_bwd_workspace_floats": (C.c_size_t, [C.c_int]),
     "yc_conv_dgrad_channels": (C.c_int, [C.c_int]),
     "yc_conv_dgrad_packed_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "yc_conv_pack_dgrad": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
@@ -123,6 +124,7 @@ _SIGS = {
     "yc_scale_channels_bwd": (C.c_int, [_TP, _TP, C.c_int, _TP, _TP, _TP, _TP, _P]),
     "yc_reorg_bwd": (C.c_int, [_TP, _TP, C.c_int, C.c_int, _P]),
     "yc_yolo_decode": (C.c_int, [_TP, _P, C.c_int, C.c_int, C.c_float, C.c_int, _P]),
+    "yc_yolo_loss_stats_floats": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "yc_yolo_loss": (C.c_int, [C.POINTER(YoloLossDesc), _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _TP, _P, _P]),
     "yc_yolo_extract": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, C.c_int,
                                   C.c_float, C.c_int, _P, C.c_int, _P, _P]),

@@ -140,7 +140,7 @@ class ConvTrain:
         # backward buffers
         self.cd = lib.yc_conv_dgrad_channels(N)
         self.dz = torch.zeros((n, ho, wo, self.cd), dtype=torch.bfloat16, device=dev)
-        self.ws = torch.zeros(5 * N, dtype=torch.float32, device=dev)
+        self.ws = torch.zeros(lib.yc_bn_bwd_workspace_floats(N), dtype=torch.float32, device=dev)
         self.scale_updates = torch.zeros(N, dtype=torch.float32, device=dev)
         self.bias_updates = torch.zeros(N, dtype=torch.float32, device=dev)
         self.dw_packed = torch.zeros(lib.yc_conv_wgrad_bytes(N, c, k) // 4, dtype=torch.float32, device=dev)
@@ -193,7 +193,7 @@ class ConvTrain:
                                   None, self.ws.data_ptr(), dzv, st), "yc_bn_bwd")
         else:
             L.check(lib.yc_bias_act_bwd(dyv, L.view(self.y, n, ho, wo, N, ldy), self.act, self.bias_updates.data_ptr(),
-                                        dzv, st), "yc_bias_act_bwd")
+                                        self.ws.data_ptr(), dzv, st), "yc_bias_act_bwd")
         L.check(lib.yc_conv_wgrad(self.wplan, st), "yc_conv_wgrad")
         if not want_dx:
             return None
@@ -340,10 +340,10 @@ def yolo_loss(out_nchw, truth, anchors_wh, mask, classes, net_w, net_h, max_boxe
                        focal_loss, ignore_thresh, truth_thresh, iou_thresh, iou_normalizer, cls_normalizer,
                        label_smooth_eps, max_delta, 1 if gaussian else 0, uc_normalizer)
     delta = torch.empty_like(out_nchw)
-    stats = torch.zeros(8, dtype=torch.float32, device=dev)
+    stats = torch.zeros(L.lib().yc_yolo_loss_stats_floats(n, h, w), dtype=torch.float32, device=dev)
     pv = None
     if prev_delta is not None:
         pv = C.byref(L.view(prev_delta, n, h, w, c, prev_delta.shape[-1]))
     L.check(L.lib().yc_yolo_loss(C.byref(d), out_nchw.data_ptr(), t.data_ptr(), a.data_ptr(), m.data_ptr(), n, h, w,
                                  delta.data_ptr(), pv, stats.data_ptr(), L.stream_ptr()), "yc_yolo_loss")
-    return delta, stats
+    return delta, stats[:8]

@@ -153,8 +153,9 @@ YC_API int yc_conv_plan_info(const yc_conv_plan* plan, int what);
  * Forward of a batch-normalised layer in training:
  *   z = conv(x, w)                       yc_conv_fprop on a plan with activation LINEAR, bias NULL, and
  *   sum_c z, sum_c z^2                   yc_conv_plan_set_stats(): the statistics of fast_mean_gpu /
- *                                        fast_variance_gpu are reduced inside the conv epilogue (from the fp32
- *                                        accumulators; caller zeroes sum/sumsq before the launch)
+ *                                        fast_variance_gpu are reduced inside the conv epilogue and WRITTEN to
+ *                                        sum / sumsq by the launch (fixed summation order, no float atomics: two
+ *                                        launches on the same input give the same bits)
  *   mean, var, rolling update            yc_bn_finalize (unbiased variance, rolling = .9 roll + .1 batch)
  *   y = act(gamma*(z-mean)/sqrt(var+1e-6)+beta)   yc_bn_act_fwd */
 YC_API int yc_conv_plan_set_stats(yc_conv_plan* plan, float* sum, float* sumsq);
@@ -167,14 +168,18 @@ YC_API int yc_bn_act_fwd(const yc_tensor* z, const float* mean, const float* var
  * dy = l->delta (NHWC bf16), z = saved pre-batchnorm conv output; dz (bf16, channels >= dy.c, pad lanes zeroed)
  * receives the gradient the dgrad / wgrad GEMMs read.  scale_updates is accumulated into; bias_updates may be NULL
  * (the reference CPU path leaves the batchnorm shift without gradient) or receives sum(dy*act').
- * workspace: 5*c floats. */
+ * workspace: yc_bn_bwd_workspace_floats(c) floats, ZERO-FILLED once when allocated (it holds the two sums, three
+ * coefficient vectors, a ticket and one partial per block: the sums are formed in a fixed order, without float atomics,
+ * so the backward pass is reproducible bit for bit). */
+YC_API size_t yc_bn_bwd_workspace_floats(int c);
 YC_API int yc_bn_bwd(const yc_tensor* dy, const yc_tensor* z, const float* mean, const float* var,
                      const float* gamma, const float* beta, int activation, float* scale_updates,
                      float* bias_updates, float* workspace, const yc_tensor* dz, void* stream);
 /* Layers without batchnorm: dz = dy * act'(y) on the layer output y (leaky/relu/logistic/linear), bias_updates +=
- * per-channel sums (gradient_array + backward_bias, convolutional_layer.cpp:1327-1336).  y may be NULL for LINEAR. */
+ * per-channel sums (gradient_array + backward_bias, convolutional_layer.cpp:1327-1336).  y may be NULL for LINEAR.
+ * workspace: as for yc_bn_bwd (needed when bias_updates is given). */
 YC_API int yc_bias_act_bwd(const yc_tensor* dy, const yc_tensor* y, int activation, float* bias_updates,
-                           const yc_tensor* dz, void* stream);
+                           float* workspace, const yc_tensor* dz, void* stream);
 
 /* Data gradient (gemm(1,0,...) + col2im_gpu_ext, convolutional_kernels.cu:765-802): runs through the forward
  * implicit-GEMM kernel on the flipped, channel-transposed filter.  yc_conv_dgrad_channels(out_c) is the channel
@@ -271,8 +276,10 @@ YC_API int yc_yolo_decode(const yc_tensor* x, float* out_nchw, int anchors, int 
  * host thread in the reference) and BackwardYoloLayerGpu (:884-888).  out_nchw = decoded head (yc_yolo_decode),
  * truth = [n][max_boxes][5] (x, y, w, h, class id; the list ends at the first x == 0), anchor_wh = l->biases
  * (2*total floats), delta_nchw = l->delta (fp32, same shape as the head, overwritten).  prev_delta (optional) is the
- * head conv's NHWC bf16 delta, which receives += delta.  stats (device, 8 floats): [0] *(l->cost), [1] count,
- * [2] sum(1-iou), [3] sum(1-giou), [4] |delta|^2, [5] |delta without box entries|^2, [6] sum iou, [7] class_count. */
+ * head conv's NHWC bf16 delta, which receives += delta.  stats (device, yc_yolo_loss_stats_floats(n, h, w) floats; the
+ * first 8 are the results): [0] *(l->cost), [1] count, [2] sum(1-iou), [3] sum(1-giou), [4] |delta|^2, [5] |delta without
+ * box entries|^2, [6] sum iou, [7] class_count; the rest holds per-image and per-block partial sums, which the last
+ * kernel adds in index order (no float atomics: the loss and its deltas are reproducible bit for bit). */
 typedef struct yc_yolo_loss_desc {
   int anchors;  /* l->n: anchors of this head (mask length) */
   int total;    /* l->total */
@@ -287,6 +294,7 @@ typedef struct yc_yolo_loss_desc {
                           yolo_point = center); cost = sum delta^2 */
   float uc_normalizer; /* l->uc_normalizer (parser.cpp:471) */
 } yc_yolo_loss_desc;
+YC_API size_t yc_yolo_loss_stats_floats(int n, int h, int w);
 YC_API int yc_yolo_loss(const yc_yolo_loss_desc* desc, const float* out_nchw, const float* truth, const float* anchor_wh,
                         const int* mask, int n, int h, int w, float* delta_nchw, const yc_tensor* prev_delta,
                         float* stats, void* stream);

@@ -25,7 +25,7 @@ for hw, c in shapes:
     dz = torch.empty(n, hw, hw, cd, device=dev, dtype=torch.bfloat16)
     mean = torch.zeros(c, device=dev); var = torch.ones(c, device=dev)
     gamma = torch.ones(c, device=dev); beta = torch.zeros(c, device=dev)
-    su = torch.zeros(c, device=dev); ws = torch.zeros(5 * c, device=dev)
+    su = torch.zeros(c, device=dev); ws = torch.zeros(lib.yc_bn_bwd_workspace_floats(c), device=dev)
     zv, yv, dyv, dzv = (L.view(t, n, hw, hw, t.shape[-1] if t is dz else c, t.shape[-1]) for t in (z, y, dy, dz))
     def fwd():
         L.check(lib.yc_bn_act_fwd(zv, mean.data_ptr(), var.data_ptr(), gamma.data_ptr(), beta.data_ptr(), act, yv, st), "fwd")
