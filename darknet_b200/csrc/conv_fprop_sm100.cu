@@ -69,6 +69,7 @@ struct ConvParams {
   int split_col;       // > 0: output columns >= split_col go to a second tensor (tmap_y2) at column - split_col: two
                        // 1x1 convolutions that read the same input (the CSP branch pairs) run as ONE GEMM
   int fast_epi;        // the specialised epilogue (epilogue_fast) applies: bf16 output, bias only, mish / leaky / linear
+  int mish_nr;         // specialised epilogue: mish with a Newton reciprocal (one MUFU per output instead of two)
   int bias_cols;       // > 0: that many floats of bias (n_tiles * block_n) are staged in shared memory at kernel start
 };
 
@@ -418,6 +419,8 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
 // memory (one broadcast LDS.128 per four columns instead of an LDG), one warp works through a whole 32-row strip of a
 // tile (the per-tile work is paid once per 2-8 blocks, not once per block), and the mish math runs in phases of eight
 // independent pairs (16 MUFU.EX2, then 16 MUFU.RCP back to back) so a single warp keeps the XU pipe busy.
+constexpr int kMishNR = 117;  // epilogue_fast only: mish with the reciprocal on the FMA pipe (Newton) instead of MUFU.RCP
+
 template <int ACT, bool HALO, bool RES>
 __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtensorMap* tmap_y, const CUtensorMap* tmap_y2,
                                               uint32_t tmem_base, uint32_t tfull0, uint32_t tempty0, uint32_t sbuf0,
@@ -557,6 +560,33 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtenso
           }
 #pragma unroll
           for (int j = 0; j < 8; ++j) x[j] = fma2(x[j], pack2(h[2 * j], h[2 * j + 1]), x[j]);
+        } else if (ACT == kMishNR) {
+          // mish(x) = x * t / (t + 1) with t = n(n+2)/2, n = e^x — the same function without the second MUFU: the
+          // reciprocal of d = t + 1 >= 1 comes from the exponent trick (seed, 5 % error) and two Newton steps on the FMA
+          // pipe (6.6e-6 relative; as a PRODUCT x*y*t there is no cancellation, the result is accurate to 9e-6 relative
+          // everywhere = 1/450 of a bf16 half-ulp).  The XU pipe (MUFU) bounded the mish layers at 80-85 % busy with two
+          // MUFU per output; with one, the issue slots do (16 instructions per pair, 10 of them packed).
+          // h = 2^min(x*log2e - 1, 30): beyond that mish(x) == x in fp32, and d stays finite.
+          f32x2 hh[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float a0, a1;
+            unpack2(fma2(x[j], pack2(1.4426950408889634f, 1.4426950408889634f), pack2(-1.f, -1.f)), a0, a1);
+            hh[j] = pack2(ex2_ftz(fminf(a0, 30.f)), ex2_ftz(fminf(a1, 30.f)));
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const f32x2 t = mul2(hh[j], fma2(hh[j], pack2(2.f, 2.f), pack2(2.f, 2.f)));  // n(n+2)/2
+            const f32x2 nd = fma2(t, pack2(-1.f, -1.f), pack2(-1.f, -1.f));             // -(t + 1)
+            float nd0, nd1;
+            unpack2(nd, nd0, nd1);
+            // 1/d seed: magic - bits(d), with bits(d) = bits(-d) ^ sign folded into the constant
+            f32x2 y = pack2(__int_as_float((int)(0xFEF311C7u - (unsigned)__float_as_int(nd0))),
+                            __int_as_float((int)(0xFEF311C7u - (unsigned)__float_as_int(nd1))));
+            y = mul2(y, fma2(nd, y, pack2(2.f, 2.f)));
+            y = mul2(y, fma2(nd, y, pack2(2.f, 2.f)));
+            x[j] = mul2(mul2(x[j], y), t);
+          }
         } else if (ACT == YC_LEAKY) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -917,7 +947,8 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     if (STATS) {
       epilogue_role<YC_LINEAR, true>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, quad, half, lane, total_tiles, stat_smem);
     } else if (p.fast_epi) {
-      if (p.act == YC_MISH) epilogue_fast_dispatch<YC_MISH>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, bias_smem, quad, half, lane, total_tiles);
+      if (p.act == YC_MISH && p.mish_nr) epilogue_fast_dispatch<kMishNR>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, bias_smem, quad, half, lane, total_tiles);
+      else if (p.act == YC_MISH) epilogue_fast_dispatch<YC_MISH>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, bias_smem, quad, half, lane, total_tiles);
       else if (p.act == YC_LEAKY) epilogue_fast_dispatch<YC_LEAKY>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, bias_smem, quad, half, lane, total_tiles);
       else epilogue_fast_dispatch<YC_LINEAR>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty_bar(0), stage_base, bias_smem, quad, half, lane, total_tiles);
     } else
@@ -1234,6 +1265,7 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   // linear, optional fused shortcut with a linear second activation (YC_PLAN_GENERIC_EPI keeps the generic one)
   p.fast_epi = !(flags & YC_PLAN_GENERIC_EPI) && !p.y_f32 && !scale && p.act2 == YC_LINEAR &&
                (p.act == YC_MISH || p.act == YC_LEAKY || p.act == YC_LINEAR);
+  p.mish_nr = (flags & YC_PLAN_MISH_MUFU) ? 0 : 1;
   uint32_t bias_bytes = 0;  // set per layout attempt below
   const int k_blocks = p.taps * p.cchunks;
   const int wres_env = (flags & YC_PLAN_NO_W_RES) ? 0 : ((flags & YC_PLAN_W_RES_1X1) ? 2 : 1);  // 0 never, 1 multi-tap layers, 2 also 1x1

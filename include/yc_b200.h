@@ -128,7 +128,8 @@ enum {
   YC_PLAN_COST_V1 = 64,      /* round-1 tile-width cost model */
   YC_PLAN_TWO_OUT_BUFS = 128, /* two staging buffers wherever they fit */
   YC_PLAN_GENERIC_EPI = 256, /* never use the specialised (bf16 / bias-only / mish-leaky-linear) epilogue */
-  YC_PLAN_EPI_SETS_V1 = 512  /* specialised epilogue with the generic one's warp-to-tile assignment */
+  YC_PLAN_EPI_SETS_V1 = 512, /* specialised epilogue with the generic one's warp-to-tile assignment */
+  YC_PLAN_MISH_MUFU = 1024   /* specialised epilogue: mish with MUFU.RCP (two MUFU per output) instead of the Newton reciprocal */
 };
 /* [setup] yc_conv_plan_create with plan switches and, optionally, a SECOND output tensor y2: the GEMM then has
  * y->c + y2->c output channels (weights / bias / scale of both layers concatenated along out_c, y->c a multiple of

@@ -69,24 +69,30 @@ def box_iou(a, b):
     return iou.astype(np.float32)
 
 
-def interval_nms(boxes, p, certain, nms_thresh, margin, iou_margin):
+def interval_nms(boxes, p, certain, nms_thresh, margin, iou_margin, boxes2=None):
     """Three-valued greedy NMS of ONE class.  boxes [n,4], p [n] scores (> 0), certain [n] bool (the candidate exists
-    on both sides whatever the rounding).  Returns state [n]: 1 KEPT, 0 SUPPRESSED, 2 UNDECIDED."""
+    on both sides whatever the rounding); boxes2: the other side's boxes of the same candidates (an overlap then counts
+    as certain only if BOTH sides' boxes say so, as possible if EITHER does).  Returns state [n]: 1 KEPT, 0 SUPPRESSED,
+    2 UNDECIDED."""
     n = p.shape[0]
     order = np.argsort(-p, kind="stable")
     b, ps, cert = boxes[order], p[order], certain[order]
     iou = box_iou(b, b)
-    hi = iou > nms_thresh + iou_margin       # suppresses whatever the rounding
-    lo = iou > nms_thresh - iou_margin       # may suppress
+    iou_lo = iou_hi = iou
+    if boxes2 is not None:
+        iou2 = box_iou(boxes2[order], boxes2[order])
+        iou_lo, iou_hi = np.minimum(iou, iou2), np.maximum(iou, iou2)
+    hi = iou_lo > nms_thresh + iou_margin       # suppresses whatever the rounding
+    lo = iou_hi > nms_thresh - iou_margin       # may suppress
     state = np.zeros(n, np.int8)
     for k in range(n):
         before = np.arange(n) < k
-        sure_order = before & (ps - ps[k] > margin)
+        sure_order = before & (ps - ps[k] > 2 * margin)   # both scores may move by up to `margin`
         if np.any(sure_order & hi[:, k] & (state == 1)):
             state[k] = 0
             continue
         # anything that may come first and may be alive and may overlap enough
-        maybe_first = (before | (ps > ps[k] - margin)) & (np.arange(n) != k)
+        maybe_first = (before | (ps > ps[k] - 2 * margin)) & (np.arange(n) != k)
         alive = np.where(before, state != 0, True)
         if np.any(maybe_first & alive & lo[:, k]) or not cert[k]:
             state[k] = 2
@@ -134,6 +140,10 @@ def compare_image(ref_ids, ref_rows, ref_probs, our_ids, our_rows, our_probs_pre
         classes = ref_probs.shape[1]
         only_ours = np.array([i for i, k in enumerate(ok) if int(k) not in r_of], np.int64)
         boxes = np.concatenate([ref_rows[:, :4], our_rows[only_ours, :4]], axis=0)
+        boxes_other = boxes.copy()   # the B200 side's box of every candidate it has
+        for i, k in enumerate(rk):
+            if int(k) in o_of:
+                boxes_other[i] = our_rows[o_of[int(k)], :4]
         probs = np.concatenate([ref_probs, our_probs_pre[only_ours]], axis=0)
         keys = np.concatenate([rk, ok[only_ours]])
         exists_other = np.array([int(k) in o_of for k in rk] + [False] * len(only_ours))
@@ -144,7 +154,7 @@ def compare_image(ref_ids, ref_rows, ref_probs, our_ids, our_rows, our_probs_pre
                 continue
             p = probs[sel, c]
             cert = exists_other[sel] & (p > thr + margin)
-            st = interval_nms(boxes[sel], p, cert, nms_thresh, margin, iou_margin)
+            st = interval_nms(boxes[sel], p, cert, nms_thresh, margin, iou_margin, boxes_other[sel])
             kept += int((st == 1).sum()); undecided += int((st == 2).sum()); suppressed += int((st == 0).sum())
             for j, s in zip(sel, st):
                 k = int(keys[j])

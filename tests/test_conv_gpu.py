@@ -126,3 +126,31 @@ def test_conv_plan_switches(gpu):
     _run(gpu, 8, 1024, 19, 19, 512, 1, 1, "leaky", want_variant=(128, 128))   # bias from global memory (no free shared memory)
     _run(gpu, 8, 512, 19, 19, 512, 3, 1, "leaky", plan_flags=L.PLAN_COST_V1)
     _run(gpu, 8, 512, 19, 19, 512, 3, 1, "leaky")
+
+
+def test_mish_newton_reciprocal_equals_mufu_variant(gpu):
+    """The specialised epilogue's default mish (one MUFU.EX2 + a Newton reciprocal on the FMA pipe, 9e-6 relative) against
+    its two-MUFU variant on the same accumulators: the bf16 outputs may differ by one ulp on a handful of elements that sit
+    on a rounding boundary, nowhere by more."""
+    from darknet_b200 import lib as L, ops
+    rng = np.random.default_rng(7)
+    B, C, HW, N = 4, 64, 38, 128
+    x = _bf16_round((3.0 * rng.standard_normal((B, C, HW, HW))).astype(np.float32))   # pre-activations spread over [-25, 25]
+    w = _bf16_round((rng.standard_normal((N, C, 1, 1)) * 0.3).astype(np.float32))
+    b = rng.uniform(-2, 2, N).astype(np.float32)
+    xd = ops.to_nhwc(torch.from_numpy(x).to(gpu))
+    outs = []
+    for flags in (0, L.PLAN_MISH_MUFU):
+        conv = ops.Conv(xd, (B, HW, HW, C), torch.from_numpy(w), torch.from_numpy(b), 1, 1, 0, "mish", plan_flags=flags)
+        assert conv.info()["variant"] & 128
+        outs.append(ops.to_nchw(conv(), N).cpu().numpy())
+        torch.cuda.synchronize()
+    a, m = outs
+    ref = O.conv_forward(x, w, b, 1, 1, 0, "mish")
+    assert np.abs(a - ref).max() <= 1e-2 * np.abs(ref).max() and np.abs(m - ref).max() <= 1e-2 * np.abs(ref).max()
+    diff = a != m
+    ulp = np.maximum(np.abs(m), 1e-30) * 2.0 ** -7      # one bf16 ulp is at most 2^-7 relative
+    assert np.all(np.abs(a - m)[diff] <= ulp[diff] * 1.001), "more than one bf16 ulp apart"
+    assert diff.mean() < 0.02, f"{diff.mean():.4f} of the outputs differ"
+    # and the error against the fp32 reference is no worse than the MUFU variant's
+    assert np.abs(a - ref).mean() <= 1.02 * np.abs(m - ref).mean()
