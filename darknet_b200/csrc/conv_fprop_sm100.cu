@@ -40,6 +40,7 @@ struct ConvParams {
   int w_resident;        // a_mode 2: all 9*cchunks weight slabs stay in shared memory for the whole (persistent) CTA
   int halo_stages;       // a_mode 2: patch ring depth (2..kHaloMaxStages)
   int halo_pair;         // a_mode 2 + w_resident + one chunk: two tiles' MMAs interleaved into two accumulators
+  int tile_pair;         // a_mode 0 / 1, one N tile, block_n <= 128: the same on the tiled / im2col path
   int Ho, Wo, stride, pad, dil;
   int kw, stride_w, pad_w;  // kernel width / stride / left padding along W (== ksize / stride / pad unless rectangular)
   const float* bias;   // padded to n_tiles*block_n
@@ -564,8 +565,10 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtenso
           // mish(x) = x * t / (t + 1) with t = n(n+2)/2, n = e^x — the same function without the second MUFU: the
           // reciprocal of d = t + 1 >= 1 comes from the exponent trick (seed, 5 % error) and two Newton steps on the FMA
           // pipe (6.6e-6 relative; as a PRODUCT x*y*t there is no cancellation, the result is accurate to 9e-6 relative
-          // everywhere = 1/450 of a bf16 half-ulp).  The XU pipe (MUFU) bounded the mish layers at 80-85 % busy with two
-          // MUFU per output; with one, the issue slots do (16 instructions per pair, 10 of them packed).
+          // everywhere = 1/450 of a bf16 half-ulp).  OPT-IN (YC_PLAN_MISH_NEWTON): measured on yolov4-608 x 64 it is 5-8 %
+          // SLOWER than the two-MUFU form on every mish layer (stem 564 vs 524 us, 1x1 64->64 @304 289 vs 269 us): with the XU
+          // pipe at 80-85 % the epilogue is as much issue-bound as MUFU-bound, and this form issues 16 instructions per
+          // pair instead of 9.
           // h = 2^min(x*log2e - 1, 30): beyond that mish(x) == x in fp32, and d stays finite.
           f32x2 hh[8];
 #pragma unroll
@@ -666,7 +669,9 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   // tiled / im2col path with resident weights (w_resident, one N tile): the taps*cchunks weight slabs sit behind the
   // ring (where halo mode keeps its patches), loaded once per CTA; the ring then carries A slabs only
   const bool wres_t = !halo && p.w_resident;
-  const uint32_t stage_bytes = a_bytes + (wres_t ? 0u : b_bytes);
+  // tile pairs on the tiled / im2col path (p.tile_pair): a stage holds the A slabs of TWO tiles and one weight slab
+  const uint32_t a_slabs = (!halo && p.tile_pair) ? 2u : 1u;
+  const uint32_t stage_bytes = a_slabs * a_bytes + (wres_t ? 0u : b_bytes);
   const uint32_t tx_bytes = a_bytes + (wres_t ? 0u : (uint32_t)(p.block_n * p.block_k * 2));
   const uint32_t patch_base = smem_base + p.stages * stage_bytes;         // 1024-aligned; halo: kHaloStages patches
   const uint32_t out_base = patch_base + (halo ? p.halo_stages * kHaloPatchStride
@@ -867,18 +872,28 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         ptx::tma_load_2d(patch_base + kb * b_bytes, &tmap_b, pfull_bar(0), kb * p.block_k, 0);
     }
     __syncwarp();
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    // Tile pairs (p.tile_pair, one N tile): two consecutive tiles of this CTA go through the ring together — per K block
+    // one stage with both A slabs and ONE weight slab — so that the MMA warp can alternate between two accumulators
+    // (see the MMA branch).
+    const int G = p.tile_pair ? 2 : 1;
+    for (int t = blockIdx.x; t < total_tiles; t += G * gridDim.x) {
+      const int nt2 = (G == 2 && t + (int)gridDim.x < total_tiles) ? 2 : 1;
       int mt_, nt_;
       tile_mn(p, t, mt_, nt_);
-      const int m0 = mt_ * kBlockM;
       const int n0 = nt_ * p.block_n;
-      int img = 0, base_w = 0, base_h = 0;
-      if (p.a_mode == 1) {
-        img = m0 / hw;
-        const int rem = m0 - img * hw;
-        const int ho = rem / p.Wo;
-        base_h = ho * p.stride - p.pad;
-        base_w = (rem - ho * p.Wo) * p.stride_w - p.pad_w;
+      int m0[2], img[2] = {0, 0}, base_w[2] = {0, 0}, base_h[2] = {0, 0};
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        int mtj = mt_, ntj;
+        if (j == 1) tile_mn(p, t + (int)gridDim.x, mtj, ntj);
+        m0[j] = mtj * kBlockM;
+        if (p.a_mode == 1) {
+          img[j] = m0[j] / hw;
+          const int rem = m0[j] - img[j] * hw;
+          const int ho = rem / p.Wo;
+          base_h[j] = ho * p.stride - p.pad;
+          base_w[j] = (rem - ho * p.Wo) * p.stride_w - p.pad_w;
+        }
       }
       int kb = 0;
       for (int tap = 0; tap < p.taps; ++tap) {
@@ -886,14 +901,16 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         for (int cc = 0; cc < p.cchunks; ++cc, ++kb) {
           ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * stage_bytes;
-          const uint32_t sb = sa + a_bytes;
+          const uint32_t sb = sa + a_slabs * a_bytes;
           if (leader) {
-            ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
-            if (p.a_mode == 1)
-              ptx::tma_load_im2col_4d(sa, &tmap_a, full_bar(stage), cc * p.block_k, base_w, base_h, img,
-                                      (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
-            else
-              ptx::tma_load_2d(sa, &tmap_a, full_bar(stage), cc * p.block_k, m0);
+            ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes + (nt2 == 2 ? a_bytes : 0u));
+            for (int j = 0; j < nt2; ++j) {
+              if (p.a_mode == 1)
+                ptx::tma_load_im2col_4d(sa + j * a_bytes, &tmap_a, full_bar(stage), cc * p.block_k, base_w[j], base_h[j], img[j],
+                                        (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
+              else
+                ptx::tma_load_2d(sa + j * a_bytes, &tmap_a, full_bar(stage), cc * p.block_k, m0[j]);
+            }
             if (!wres_t) ptx::tma_load_2d(sb, &tmap_b, full_bar(stage), kb * p.block_k, n0);
           }
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
@@ -915,29 +932,40 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       ptx::mbar_wait(pfull_bar(0), 0);
       ptx::tc_fence_after();
     }
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-      const int acc = it & (p.nacc - 1);
-      const uint32_t acc_phase = (it >> nacc_shift) & 1;
-      ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+    // Back-to-back MMAs into ONE accumulator are serialised by the accumulator dependency: measured ~175 cycles per MMA
+    // whatever its width up to N = 128 (3x3 s2 32->64 and 64->128: tensor pipe 19 % / 36 % busy with the whole tile time
+    // = MMAs x 175 cycles).  With tile pairs the MMAs of two tiles alternate between two accumulators and pipeline.
+    const int G = p.tile_pair ? 2 : 1;
+    for (int t = blockIdx.x; t < total_tiles; t += G * gridDim.x) {
+      const bool two = G == 2 && t + (int)gridDim.x < total_tiles;
+      const int acc0 = it & (p.nacc - 1), acc1 = (it + 1) & (p.nacc - 1);
+      ptx::mbar_wait(tempty_bar(acc0), ((it >> nacc_shift) & 1) ^ 1u);
+      if (two) ptx::mbar_wait(tempty_bar(acc1), (((it + 1) >> nacc_shift) & 1) ^ 1u);
       ptx::tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * p.block_n;
+      const uint32_t d0 = tmem_base + acc0 * p.block_n, d1 = tmem_base + acc1 * p.block_n;
       for (int kb = 0; kb < k_blocks; ++kb) {
         ptx::mbar_wait(full_bar(stage), phase);
         ptx::tc_fence_after();
         const uint32_t sa = smem_base + stage * stage_bytes;
-        const uint64_t adesc = ptx::make_smem_desc(sa, row_bytes);
-        const uint64_t bdesc = ptx::make_smem_desc(wres_t ? patch_base + kb * b_bytes : sa + a_bytes, row_bytes);
+        const uint64_t adesc0 = ptx::make_smem_desc(sa, row_bytes);
+        const uint64_t adesc1 = ptx::make_smem_desc(sa + a_bytes, row_bytes);
+        const uint64_t bdesc = ptx::make_smem_desc(wres_t ? patch_base + kb * b_bytes : sa + a_slabs * a_bytes, row_bytes);
         if (leader) {
           for (int k = 0; k < k_steps; ++k) {
             // advancing K by 16 bf16 = 32 bytes inside the swizzle atom: +2 in the (addr>>4) field
-            ptx::mma_bf16_ss(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+            ptx::mma_bf16_ss(d0, adesc0 + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+            if (two) ptx::mma_bf16_ss(d1, adesc1 + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
           }
           ptx::mma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
-          if (kb == k_blocks - 1) ptx::mma_commit(tfull_bar(acc));
+          if (kb == k_blocks - 1) {
+            ptx::mma_commit(tfull_bar(acc0));
+            if (two) ptx::mma_commit(tfull_bar(acc1));
+          }
         }
         __syncwarp();
         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }
+      it += two ? 2 : 1;
     }
   } else if (warp >= 2) {
     // ===================== epilogue =====================
@@ -1265,7 +1293,7 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   // linear, optional fused shortcut with a linear second activation (YC_PLAN_GENERIC_EPI keeps the generic one)
   p.fast_epi = !(flags & YC_PLAN_GENERIC_EPI) && !p.y_f32 && !scale && p.act2 == YC_LINEAR &&
                (p.act == YC_MISH || p.act == YC_LEAKY || p.act == YC_LINEAR);
-  p.mish_nr = (flags & YC_PLAN_MISH_MUFU) ? 0 : 1;
+  p.mish_nr = (flags & YC_PLAN_MISH_NEWTON) ? 1 : 0;
   uint32_t bias_bytes = 0;  // set per layout attempt below
   const int k_blocks = p.taps * p.cchunks;
   const int wres_env = (flags & YC_PLAN_NO_W_RES) ? 0 : ((flags & YC_PLAN_W_RES_1X1) ? 2 : 1);  // 0 never, 1 multi-tap layers, 2 also 1x1
@@ -1277,10 +1305,17 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   //    (the per-tile reload is a third of the L2 -> SM traffic of the 64-channel layers; YC_PLAN_NO_W_RES switches it off);
   //  * otherwise the ring is as deep as shared memory allows: the producer runs ahead across tiles, so the ring depth is
   //    the amount of HBM traffic in flight per SM (what the memory-bound 1x1 layers live on).
+  // tile pairs on the tiled / im2col path: worth it where a tile issues enough dependent MMAs for their ~175-cycle
+  // accumulator latency to show (>= 8 per tile) and the CTA has at least two tiles
+  p.tile_pair = (p.a_mode != 2 && p.n_tiles == 1 && p.block_n <= 128 && !(flags & YC_PLAN_NO_TILE_PAIR) &&
+                 k_blocks * (p.block_k / 16) >= 8 && p.m_tiles >= 2 * sms) ? 1 : 0;
+  const uint32_t stage_bytes_g = (p.tile_pair ? 2u : 1u) * a_bytes + b_bytes;  // tiled / im2col ring stage
   auto layout = [&](int out_bufs) -> bool {
     p.out_bufs = out_bufs;
     p.halo_stages = 2;
     p.halo_pair = 0;
+    const uint32_t stage_bytes = p.a_mode == 2 ? b_bytes : stage_bytes_g;
+    const uint32_t a_ring = (p.tile_pair ? 2u : 1u) * a_bytes;
     const uint32_t out_bytes = kEpiWarps * kStageOutBytes * out_bufs;
     const uint32_t fixed = 1024 /*align slack*/ + 512 /*barriers*/ + bias_bytes;
     if (p.a_mode == 2 && p.n_tiles == 1 && !(flags & YC_PLAN_NO_HALO_PAIR)) {
@@ -1303,10 +1338,10 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
     if (p.a_mode != 2 && p.n_tiles == 1 && (wres_env == 2 || (wres_env == 1 && p.taps > 1))) {
       const uint32_t wres_bytes = (uint32_t)k_blocks * b_bytes;
       const long long tiles_per_cta = (long long)p.m_tiles / std::max(1, sms);
-      if (wres_bytes <= 64 * 1024 && tiles_per_cta >= 8 && smem_budget >= wres_bytes + 4 * a_bytes) {
+      if (wres_bytes <= 64 * 1024 && tiles_per_cta >= 8 && smem_budget >= wres_bytes + 4 * a_ring) {
         p.w_resident = 1;
-        p.stages = std::min<int>(kMaxStages, (smem_budget - wres_bytes) / a_bytes);
-        pl->smem = (size_t)p.stages * a_bytes + wres_bytes + out_stage + fixed;
+        p.stages = std::min<int>(kMaxStages, (smem_budget - wres_bytes) / a_ring);
+        pl->smem = (size_t)p.stages * a_ring + wres_bytes + out_stage + fixed;
       }
     }
     return p.stages >= 2;
@@ -1547,6 +1582,7 @@ extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq
   YC_REQUIRE(!sum || p.act == YC_LINEAR, "yc_conv_plan_set_stats: statistics are taken on the linear (pre-batchnorm) output");
   p.fast_epi = 0;                       // statistics are reduced by the generic epilogue
   p.bias_cols = 0;
+  p.tile_pair = 0;
   if (p.a_mode != 2) p.w_resident = 0;  // the ring is re-planned below with weights in every stage
   // the generic epilogue's warp-to-tile assignment: four warps per quadrant on a wide tile (fewer statistics regions)
   const int groups = p.block_n / 32;
@@ -1617,7 +1653,7 @@ extern "C" int yc_conv_plan_info(const yc_conv_plan* pl, int what) {
     case 6: return (int)pl->smem;
     case 7:  // kernel variant: [0,2) a_mode, 4 halo tile pairs, 8 resident weights, 16 two outputs, 32 two staging buffers, 64 rectangular, 128 fast epilogue
       return pl->p.a_mode | (pl->p.halo_pair ? 4 : 0) | (pl->p.w_resident ? 8 : 0) | (pl->p.split_col ? 16 : 0) |
-             (pl->p.out_bufs == 2 ? 32 : 0) | (pl->rect ? 64 : 0) | (pl->p.fast_epi ? 128 : 0);
+             (pl->p.out_bufs == 2 ? 32 : 0) | (pl->rect ? 64 : 0) | (pl->p.fast_epi ? 128 : 0) | (pl->p.tile_pair ? 256 : 0);
     case 8: return pl->p.epi_sets;
   }
   return -1;

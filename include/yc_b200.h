@@ -129,7 +129,8 @@ enum {
   YC_PLAN_TWO_OUT_BUFS = 128, /* two staging buffers wherever they fit */
   YC_PLAN_GENERIC_EPI = 256, /* never use the specialised (bf16 / bias-only / mish-leaky-linear) epilogue */
   YC_PLAN_EPI_SETS_V1 = 512, /* specialised epilogue with the generic one's warp-to-tile assignment */
-  YC_PLAN_MISH_MUFU = 1024   /* specialised epilogue: mish with MUFU.RCP (two MUFU per output) instead of the Newton reciprocal */
+  YC_PLAN_NO_TILE_PAIR = 2048, /* tiled / im2col path: one tile at a time instead of tile pairs (two accumulators) */
+  YC_PLAN_MISH_NEWTON = 1024 /* specialised epilogue: mish with one MUFU + a Newton reciprocal on the FMA pipe (measured slower) */
 };
 /* [setup] yc_conv_plan_create with plan switches and, optionally, a SECOND output tensor y2: the GEMM then has
  * y->c + y2->c output channels (weights / bias / scale of both layers concatenated along out_c, y->c a multiple of
@@ -143,7 +144,7 @@ YC_API int yc_conv_plan_destroy(yc_conv_plan* plan);
 YC_API int yc_conv_fprop(const yc_conv_plan* plan, void* stream);
 /* plan introspection for tests/bench: what=0 block_n, 1 block_k, 2 stages, 3 tiles, 4 grid, 5 A-operand mode (0 tiled,
  * 1 im2col, 2 halo patch), 6 dynamic shared memory bytes, 7 variant bits: [0,2) A mode | 4 halo tile pairs | 8 resident
- * weights | 16 two outputs | 32 two staging buffers | 64 rectangular (pixel-pair) geometry | 128 specialised epilogue;
+ * weights | 16 two outputs | 32 two staging buffers | 64 rectangular (pixel-pair) geometry  | 128 specialised epilogue | 256 tile pairs on the tiled / im2col path;
  * 8 epilogue warp sets */
 YC_API int yc_conv_plan_info(const yc_conv_plan* plan, int what);
 
