@@ -1306,9 +1306,11 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   //  * otherwise the ring is as deep as shared memory allows: the producer runs ahead across tiles, so the ring depth is
   //    the amount of HBM traffic in flight per SM (what the memory-bound 1x1 layers live on).
   // tile pairs on the tiled / im2col path: worth it where a tile issues enough dependent MMAs for their ~175-cycle
-  // accumulator latency to show (>= 8 per tile) and the CTA has at least two tiles
+  // accumulator latency to show and the CTA has at least two tiles.  Measured (profiles/r02_ab_tile_pair.txt): 3x3 s2
+  // 32->64 (18 MMAs per tile) 863 -> 509 us, 3x3 s2 64->128 (36) 365 -> 238 us; the 1x1 layers with 8 MMAs per tile lose
+  // 5-10 % (they are bound by the activation stream, and a pair halves the number of ring stages) -> threshold 12
   p.tile_pair = (p.a_mode != 2 && p.n_tiles == 1 && p.block_n <= 128 && !(flags & YC_PLAN_NO_TILE_PAIR) &&
-                 k_blocks * (p.block_k / 16) >= 8 && p.m_tiles >= 2 * sms) ? 1 : 0;
+                 k_blocks * (p.block_k / 16) >= 12 && p.m_tiles >= 2 * sms) ? 1 : 0;
   const uint32_t stage_bytes_g = (p.tile_pair ? 2u : 1u) * a_bytes + b_bytes;  // tiled / im2col ring stage
   auto layout = [&](int out_bufs) -> bool {
     p.out_bufs = out_bufs;

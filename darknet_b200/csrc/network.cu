@@ -43,7 +43,8 @@ using namespace yc;
 namespace {
 
 // ---- cfg -> layers (ParseNetworkCfg, parser.cpp:1076-1519; shape rules cited per layer) --------------------
-int build_layers(yc_network* net, const std::string& text, int batch) {
+// w_over / h_over > 0 replace [net] width / height (yc_network_resize).
+int build_layers(yc_network* net, const std::string& text, int batch, int w_over = 0, int h_over = 0) {
   std::vector<Section> secs;
   std::string err;
   if (!parse_cfg_text(text, secs, err)) NET_FAIL(YC_ERR_PARSE, "%s", err.c_str());
@@ -52,8 +53,8 @@ int build_layers(yc_network* net, const std::string& text, int batch) {
   // ParseNetOptions (parser.cpp:926-928): the network's batch is the MINI-batch, [net] batch / subdivisions; an explicit
   // `batch` argument is the mini-batch itself (the reference's inference path forces it to 1, parser.cpp:1114-1115)
   net->batch = batch > 0 ? batch : std::max(1, n0.get_int("batch", 1) / net->subdivisions);
-  net->w = n0.get_int("width", 0);
-  net->h = n0.get_int("height", 0);
+  net->w = w_over > 0 ? w_over : n0.get_int("width", 0);
+  net->h = h_over > 0 ? h_over : n0.get_int("height", 0);
   net->c = n0.get_int("channels", 0);
   if (!(net->w > 0 && net->h > 0 && net->c > 0)) NET_FAIL(YC_ERR_PARSE, "[net] needs width/height/channels");
   net->lr = n0.get_float("learning_rate", .001f);   // ParseNetOptions parser.cpp:1116-1140
@@ -685,6 +686,7 @@ static int load_common(yc_network** out, const std::string& text, const char* we
   YC_REQUIRE(out, "yc_network_load: null output");
   yc_network* net = new yc_network();
   net->flags = flags;
+  net->cfg_text = text;
   int rc = build_layers(net, text, batch);
   if (!rc && weights_path && weights_path[0]) {
     rc = load_weights_file(net, weights_path);
@@ -721,6 +723,82 @@ extern "C" int yc_network_free(yc_network* net) {
   free_device_state(net);
   if (net->stream) cudaStreamDestroy(net->stream);
   delete net;
+  return YC_OK;
+}
+
+int yc_train_pull_params(yc_network* net);  // network_train.cu
+
+// ResizeNetwork (network.cpp:255-383; detector.cpp:150-182 calls it every ten iterations when a yolo layer has
+// random=1): every layer's shape is re-derived for a new input size, the parameters stay.  The reference resizes layer
+// by layer and reallocates each output; here the shapes are re-derived from the cfg text with the new size, the
+// spatially independent state (parameters, rolling statistics, the momentum-carrying gradient buckets) takes a round
+// trip through host memory, and plans / activation buffers / graph are rebuilt by yc_network_finalize.  A data-parallel
+// context survives (it holds the communicator and per-layer events, no buffer pointers); every rank must resize alike.
+extern "C" int yc_network_resize(yc_network* net, int w, int h) {
+  YC_REQUIRE(net && w > 0 && h > 0, "yc_network_resize: bad argument");
+  YC_REQUIRE(!net->cfg_text.empty(), "yc_network_resize: the network was not built from a cfg");
+  if (w == net->w && h == net->h) return YC_OK;
+  const bool was_final = net->finalized, train = (net->flags & YC_NET_TRAIN) != 0;
+  const size_t nl = net->layers.size();
+  std::vector<std::vector<float>> buckets(nl);
+  if (was_final && train) {
+    int rc = yc_train_pull_params(net);
+    if (rc) return rc;
+    for (size_t i = 0; i < nl; ++i) {
+      const NLayer& L = net->layers[i];
+      if (L.type != L_CONV || !L.dw_packed || !L.bucket_floats) continue;
+      buckets[i].resize(L.bucket_floats);
+      NET_CUDA(cudaMemcpyAsync(buckets[i].data(), L.dw_packed, L.bucket_floats * 4, cudaMemcpyDeviceToHost, net->stream));
+    }
+    NET_CUDA(cudaStreamSynchronize(net->stream));
+  }
+  void* dp = net->dp;
+  net->dp = nullptr;  // yc_train_free would drop the communicator
+  free_device_state(net);
+  // scalars that the host may have changed since the cfg was parsed
+  const float lr = net->lr, momentum = net->momentum, decay = net->decay;
+  const int max_iter = net->max_iter, batch = net->batch, old_w = net->w, old_h = net->h;
+  std::vector<NLayer> old = std::move(net->layers);
+  const std::vector<int> old_yolo = net->yolo_layers;
+  net->layers.clear();
+  net->yolo_layers.clear();
+  net->n_conv = 0;
+  int rc = build_layers(net, net->cfg_text, batch, w, h);
+  if (!rc && net->layers.size() != nl) { set_error("yc_network_resize: layer count changed"); rc = YC_ERR_ARG; }
+  if (rc) {  // e.g. a size at which some layer's output is empty: the network keeps its old shape (not finalized)
+    net->layers = std::move(old);
+    net->yolo_layers = old_yolo;
+    net->n_conv = 0;
+    for (const NLayer& L : net->layers) net->n_conv += L.type == L_CONV;
+    net->w = old_w; net->h = old_h;
+    net->dp = dp;
+    net->lr = lr; net->momentum = momentum; net->decay = decay; net->max_iter = max_iter;
+    return rc;
+  }
+  net->lr = lr; net->momentum = momentum; net->decay = decay; net->max_iter = max_iter;
+  for (size_t i = 0; i < nl; ++i) {
+    NLayer& L = net->layers[i];
+    NLayer& O = old[i];
+    if (L.type != L_CONV) continue;
+    L.weights.swap(O.weights); L.biases.swap(O.biases); L.scales.swap(O.scales);
+    L.rmean.swap(O.rmean); L.rvar.swap(O.rvar);
+  }
+  net->dp = dp;
+  if (!was_final) return YC_OK;
+  rc = yc_network_finalize(net);
+  if (rc) return rc;
+  if (train) {
+    for (size_t i = 0; i < nl; ++i) {
+      NLayer& L = net->layers[i];
+      if (buckets[i].empty()) continue;
+      if (!L.dw_packed || L.bucket_floats != buckets[i].size()) {
+        set_error("yc_network_resize: layer %zu changed its gradient bucket", i);
+        return YC_ERR_ARG;
+      }
+      NET_CUDA(cudaMemcpyAsync(L.dw_packed, buckets[i].data(), L.bucket_floats * 4, cudaMemcpyHostToDevice, net->stream));
+    }
+    NET_CUDA(cudaStreamSynchronize(net->stream));
+  }
   return YC_OK;
 }
 

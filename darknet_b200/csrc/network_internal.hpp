@@ -100,6 +100,7 @@ struct Op {
 struct yc_network {
   int batch = 1, w = 0, h = 0, c = 0, flags = YC_NET_DEFAULT;
   std::vector<NLayer> layers;
+  std::string cfg_text;  // what the layers were built from (yc_network_resize re-derives the shapes from it)
   std::vector<Op> ops;
   bool finalized = false;
   cudaStream_t stream = nullptr;

@@ -144,6 +144,7 @@ _SIGS = {
     "yc_network_init_weights": (C.c_int, [_P, C.c_uint, C.c_int]),
     "yc_network_current_rate": (C.c_float, [_P, C.c_longlong, C.c_int]),
     "yc_network_set_schedule": (C.c_int, [_P, C.c_int, C.c_longlong]),
+    "yc_network_resize": (C.c_int, [_P, C.c_int, C.c_int]),
     "yc_network_predict": (_P, [_P, _P]),
     "yc_network_predict_u8": (_P, [_P, _P, C.c_int]),
     "yc_network_prefetch": (C.c_int, [_P, _P]),

@@ -98,6 +98,13 @@ def Finalize(net: Network):
     L.check(L.lib().yc_network_finalize(net.h), "yc_network_finalize")
 
 
+def ResizeNetwork(net: Network, w: int, h: int):
+    """ResizeNetwork (network.cpp:255-383): new input size, parameters / momentum / counters kept."""
+    L.check(L.lib().yc_network_resize(net.h, w, h), "ResizeNetwork")
+    net.w = L.lib().yc_network_info(net.h, 2)
+    net.hh = L.lib().yc_network_info(net.h, 3)
+
+
 def LoadSynthetic(cfg_text, weights: dict, batch=0, flags=L.NET_DEFAULT) -> Network:
     """LoadNetwork from a cfg string and a {layer: {weights,biases,scales,rolling_mean,rolling_variance}} dict
     (darknet_b200.cfg.synth_weights) without going through a .weights file."""

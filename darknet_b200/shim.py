@@ -14,6 +14,7 @@ SO = os.path.join(HERE, "libyolo_core_b200.so")
 # every symbol a yolo-core build would bind (yolo_core.h:625-663, network.h:8-18, box.h:93-94, layer function pointers)
 REFERENCE_SYMBOLS = ["LoadNetwork", "FreeNetwork", "NetworkPredict", "NetworkPredictGpu", "ForwardNetworkGpu",
                      "GetNetworkBoxes", "FreeDetections", "FuseConvBatchNorm", "_Z7NmsSortP9Detectioniif8NMS_KINDf",
+                     "_Z13ResizeNetworkP7Networkii",
                      "ForwardConvolutionalLayerGpu", "ForwardMaxpoolLayerGpu", "ForwardUpsampleLayerGpu",
                      "ForwardShortcutLayerGpu", "ForwardRouteLayerGpu", "ForwardYoloLayerGpu",
                      "ForwardGaussianYoloLayerGpu", "CudaGetDeviceCount", "cuda_set_device"]
@@ -49,6 +50,7 @@ def lib():
         L.GetNetworkBoxes.argtypes = [C.c_void_p, C.c_float, C.POINTER(C.c_int)]
         L.FreeDetections.argtypes = [C.POINTER(RefDetection), C.c_int]
         L.yc_shim_nms_sort.argtypes = [C.POINTER(RefDetection), C.c_int, C.c_int, C.c_float, C.c_int, C.c_float]
+        L.yc_shim_resize_network.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.yc_shim_sizeof.argtypes = [C.c_int]
         L.yc_shim_install.argtypes = [C.c_void_p]
         L.yc_shim_release.argtypes = [C.c_void_p]
@@ -90,6 +92,9 @@ class ShimNetwork:
             probs[i] = np.ctypeslib.as_array(d[i].prob, shape=(classes,))
         L.FreeDetections(d, n.value)
         return rows, probs
+
+    def resize(self, w, h):
+        lib().yc_shim_resize_network(self.ptr, w, h)
 
     def close(self):
         if self.ptr:

@@ -14,6 +14,7 @@
 //   void FreeDetections(Detection*, int)                   (network.cpp:505-516)
 //   void NmsSort(Detection*, total, classes, thresh, ...)  yc_nms_sort                (box.cpp:393-419)
 //   void FuseConvBatchNorm(Network*)                       no-op: folded at load      (network.cpp:647-682)
+//   void ResizeNetwork(Network*, w, h)  [C++ linkage]      yc_network_resize          (network.cpp:255-383)
 //
 //   per-layer operator seam (yolo_core.h:157-159: void (*forward_gpu)(layer*, NetworkState))
 //   ----------------------------------------------------  -----------------------------------------------------------
@@ -467,6 +468,38 @@ SHIM_API void FreeNetwork(Network* net) {
     net->layers = nullptr;
   }
 }
+
+// ResizeNetwork (network.h:34, network.cpp:255-383) — C++ linkage like the original; yc_shim_resize_network is the same
+// entry for C callers.  The library re-derives every shape (yc_network_resize); the mirror's spatial fields follow, and
+// per-layer trampoline state of the old shapes is dropped.
+__attribute__((visibility("default"))) void ResizeNetwork(Network* net, int w, int h) {
+  yc_network* hn = handle_of(net);
+  if (!hn) {
+    fprintf(stderr, "yolo_core_b200: ResizeNetwork: not a network of this library\n");
+    exit(EXIT_FAILURE);
+  }
+  YC_OR_DIE(yc_network_resize(hn, w, h), "yc_network_resize");
+  net->w = yc_network_info(hn, 2);
+  net->h = yc_network_info(hn, 3);
+  net->inputs = net->w * net->h * net->c;
+  for (int i = 0; i < net->n; ++i) {
+    layer* l = &net->layers[i];
+    yc_shim_release(l);
+    l->out_h = yc_network_layer_info(hn, i, 2);
+    l->out_w = yc_network_layer_info(hn, i, 3);
+    l->outputs = l->out_c * l->out_h * l->out_w;
+    const int in0 = yc_network_layer_input(hn, i, 0);
+    if (in0 >= 0) { l->h = net->layers[in0].out_h; l->w = net->layers[in0].out_w; }
+    else { l->h = net->h; l->w = net->w; }
+    l->inputs = l->h * l->w * l->c;
+    if (l->type == ROUTE || l->type == SHORTCUT)
+      for (int k = 0; k < l->n; ++k) l->input_sizes[k] = net->layers[l->input_layers[k]].outputs;
+    if ((l->type == YOLO || l->type == GAUSSIAN_YOLO) && !net->train)
+      l->output = (float*)yc_network_yolo_output(hn, i);  // the pinned head buffers were reallocated
+  }
+  net->outputs = net->layers[net->n - 1].outputs;
+}
+SHIM_API void yc_shim_resize_network(Network* net, int w, int h) { ResizeNetwork(net, w, h); }
 
 SHIM_API void FuseConvBatchNorm(Network* net) { (void)net; /* folded when the network was planned (csrc/network.cu) */ }
 

@@ -380,6 +380,13 @@ YC_API float yc_network_current_rate(const yc_network* net, long long iter, int 
 /* net->max_iter / net->curr_iter (owned by the reference's training driver): max_iter <= 0 and iter < 0 keep the
  * current values.  The iteration count advances by one per yc_network_update. */
 YC_API int yc_network_set_schedule(yc_network* net, int max_iter, long long iter);
+
+/* ResizeNetwork (network.cpp:255-383): a new input size for an existing network.  Every layer's shape is re-derived, the
+ * parameters, rolling statistics, momentum-carrying gradient buffers, seen / iteration counters and a data-parallel
+ * context are kept; plans, activation buffers and the captured graph are rebuilt (the network is finalized again if it
+ * was).  Pointers obtained before the call (input buffers, yolo outputs) are invalid afterwards.  A size at which some
+ * layer would have an empty output fails and leaves the old shape in place (call yc_network_finalize to go on). */
+YC_API int yc_network_resize(yc_network* net, int w, int h);
 /* what: 0 n_layers, 1 batch, 2 w, 3 h, 4 c, 5 n_conv, 6 kernels launched per forward, 7 n_yolo, 8 subdivisions,
  * 9 current iteration, 10 images seen, 11 layers filled from the weights file, 12 effective flags */
 YC_API int yc_network_info(const yc_network* net, int what);

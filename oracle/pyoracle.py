@@ -80,6 +80,7 @@ def ref_lib():
         L.ref_reorg.argtypes = [_f32p] + [C.c_int] * 6 + [_f32p]
         L.ref_curr_lr.restype = C.c_float
         L.ref_curr_lr.argtypes = [C.c_void_p, C.c_longlong, C.c_int]
+        L.ref_resize.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.ref_layer_forward_train.restype = C.c_float
         L.ref_layer_forward_train.argtypes = [C.c_void_p, C.c_int, _f32p, _f32p, _f32p, _f32p]
         L.ref_nms.argtypes = [_f32p, _f32p, _f32p, C.c_int, C.c_int, C.c_float, C.c_int, C.c_float, _i32p]
@@ -118,6 +119,11 @@ class RefNet:
         if self.h:
             self.L.ref_free(self.h)
             self.h = None
+
+    def resize(self, w, h):
+        """ResizeNetwork (network.cpp:255-383)."""
+        self.L.ref_resize(self.h, w, h)
+        self.w, self.hh = (self.L.ref_net_dim(self.h, i) for i in range(2))
 
     def layer_int(self, i, key):
         return self.L.ref_layer_int(self.h, i, key.encode())

@@ -276,6 +276,9 @@ float ref_curr_lr(void* h, long long iter, int max_iter) {
   return GetCurrLr(n);
 }
 
+// ResizeNetwork (network.cpp:255-383) of the loaded reference network
+void ref_resize(void* h, int w, int hh) { ResizeNetwork(&((RefNet*)h)->net, w, hh); }
+
 // NmsSort — reference box.cpp:393-419 on caller-provided detections.  boxes: [n][4] (x y w h), obj: [n],
 // probs: [n][classes] (zeroed in place); order_out[i] = original index of the detection that ends at
 // position i of the reference's array after its qsorts.

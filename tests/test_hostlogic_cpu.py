@@ -180,3 +180,33 @@ def test_init_weights_is_the_reference_law(built):
     assert checked >= 9
     ref.close()
     lib.yc_network_free(h)
+
+
+@needs_ref
+@pytest.mark.parametrize("gen,size0,sizes", [("yolov4_tiny", 416, [(320, 320), (608, 352)]), ("yolov4", 608, [(416, 416), (320, 512)]),
+                                             ("gaussian_yolov3", 608, [(352, 352)])])
+def test_resize_rederives_every_shape_like_ResizeNetwork(built, gen, size0, sizes):
+    """yc_network_resize on a parsed (not finalized: no device needed) network against ResizeNetwork of the compiled
+    reference (network.cpp:255-383): input / output shape of every layer, for square and non-square sizes, and back."""
+    lib = L.lib()
+    text = getattr(cfgs, gen)(w=size0, h=size0)
+    h = _load_text(text)
+    ref = pyoracle.RefNet(_write(f"rs_{gen}.cfg", text), None, train=True, fuse=False)
+    n = lib.yc_network_info(h, 0)
+    assert n == ref.n
+    for (w, hh) in sizes + [(size0, size0)]:
+        L.check(lib.yc_network_resize(h, w, hh), "resize")
+        ref.resize(w, hh)
+        assert (lib.yc_network_info(h, 2), lib.yc_network_info(h, 3)) == (ref.w, ref.hh) == (w, hh)
+        for i in range(n):
+            mine = tuple(lib.yc_network_layer_info(h, i, k) for k in (1, 2, 3))
+            # (ResizeYoloLayer updates l->h / l->w and leaves out_h / out_w stale, yolo_layer.cpp:89-95)
+            yolo = lib.yc_network_layer_info(h, i, 0) >= 5
+            theirs = tuple(ref.layer_int(i, k) for k in (("out_c", "h", "w") if yolo else ("out_c", "out_h", "out_w")))
+            assert mine == theirs, (gen, w, hh, i, mine, theirs)
+    # a size at which a layer would be empty is refused and the old shape stays
+    assert lib.yc_network_resize(h, 8, 8) != 0
+    assert (lib.yc_network_info(h, 2), lib.yc_network_info(h, 3)) == (size0, size0)
+    assert lib.yc_network_layer_info(h, n - 1, 2) == ref.layer_int(n - 1, "h")
+    lib.yc_network_free(h)
+    ref.close()
