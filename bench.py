@@ -73,9 +73,11 @@ def _ncu_traffic(n_conv):
     """DRAM bytes per conv launch from the committed ncu launch list of this same command (profiles/; ncu cannot run
     inside a timed bench).  None when the file is absent or does not hold a whole step."""
     import csv
-    path = os.path.join(ROOT, "profiles", "r01_launches_yolov4_608_b64.csv")
-    if not os.path.exists(path):
+    import glob
+    found = sorted(glob.glob(os.path.join(ROOT, "profiles", "r[0-9][0-9]_launches_yolov4_608_b64.csv")))
+    if not found:
         return None
+    path = found[-1]  # the newest round's list
     try:
         with open(path, newline="") as f:
             lines = [l for l in f if l.startswith('"')]
@@ -90,7 +92,7 @@ def _ncu_traffic(n_conv):
             return None
         last = ids[-n_conv:]
         return {"bytes_per_launch": sum(per[i] for i in last) / n_conv,
-                "source": "profiles/r01_launches_yolov4_608_b64.csv (ncu launch list of bench.py --steps 1 --warmup 3, last step)"}
+                "source": f"profiles/{os.path.basename(path)} (ncu launch list of bench.py --steps 1 --warmup 3, last step)"}
     except Exception:
         return None
 
@@ -705,7 +707,8 @@ def main():
             other_ms = float(ms_layer.sum() - conv_ms)
             peaks = _peaks()
             ach = flops_img * B / (conv_ms / 1e3) / 1e12
-            n_conv = net.info(5)
+            # conv LAUNCHES per step: a 1x1 conv computed by its CSP sibling's kernel (fused pair) has none of its own
+            n_conv = sum(1 for i in range(nl) if net.layer_info(i, 0) == 0 and net.layer_info(i, 14) < 0)
             roof = {"bound": "tensor", "kernel": "conv_fprop_kernel", "achieved": ach, "peak": peaks["sustained"],
                     "unit": "TFLOP/s", "frac": ach / peaks["sustained"], "traffic": None,
                     "frac_of_burst_peak": ach / peaks["burst"], "peak_source": peaks["source"] + ", sustained bf16",
