@@ -1447,7 +1447,7 @@ extern "C" int yc_network_detect(yc_network* net, float thresh, float nms_thresh
   if (!net->det_regions) {
     int max_cells = 0;
     for (int li : net->yolo_layers) max_cells = std::max(max_cells, net->layers[li].n * net->layers[li].out_h * net->layers[li].out_w);
-    net->det_cap = std::min(max_cells, 16384);  // rows kept per (head, image); more is reported as an error
+    net->det_cap = std::min(max_cells, 16384);  // rows kept per (head, image); grown to max_cells when an image has more
     net->det_dense_cap = B * 256;
     net->det_R = R;
     NET_CUDA(cudaMalloc(&net->det_regions, (size_t)heads * B * net->det_cap * R * 4));
@@ -1458,28 +1458,39 @@ extern "C" int yc_network_detect(yc_network* net, float thresh, float nms_thresh
     NET_CUDA(cudaHostAlloc(&net->det_img_counts_host, (size_t)(heads + 1) * B * 4, cudaHostAllocDefault));
   }
   cudaStream_t st = net->stream;
-  for (int hd = 0; hd < heads; ++hd) {
-    const int li = net->yolo_layers[hd];
-    NLayer& L = net->layers[li];
-    int rc = launch_yolo_extract(L.dec_dev, B, L.out_h, L.out_w, L.n, L.classes, L.anchors_dev, L.mask_dev, net->w, net->h,
-                                 thresh, L.type == L_GYOLO, net->det_regions + (size_t)hd * B * net->det_cap * R,
-                                 net->det_cap, net->det_counts + (size_t)hd * B, R, (float)li, st);
-    if (rc) return rc;
-  }
-  int rc = launch_yolo_gather(net->det_regions, net->det_counts, heads, B, net->det_cap, R, net->det_dense,
-                              net->det_img_counts, net->det_dense_cap, st);
-  if (rc) return rc;
-  NET_CUDA(cudaMemcpyAsync(net->det_img_counts_host, net->det_img_counts, (size_t)B * 4, cudaMemcpyDeviceToHost, st));
-  NET_CUDA(cudaMemcpyAsync(net->det_img_counts_host + B, net->det_counts, (size_t)heads * B * 4, cudaMemcpyDeviceToHost, st));
-  NET_CUDA(cudaStreamSynchronize(st));
+  int rc = YC_OK;
   long long tot = 0;
-  for (int b = 0; b < B; ++b) tot += net->det_img_counts_host[b];
-  for (int i = 0; i < heads * B; ++i)
-    if (net->det_img_counts_host[B + i] > net->det_cap) {
-      set_error("yc_network_detect: %d candidates in one image of head %d exceed the per-head capacity %d (raise thresh)",
-                net->det_img_counts_host[B + i], i / B, net->det_cap);
-      return YC_ERR_ARG;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    for (int hd = 0; hd < heads; ++hd) {
+      const int li = net->yolo_layers[hd];
+      NLayer& L = net->layers[li];
+      rc = launch_yolo_extract(L.dec_dev, B, L.out_h, L.out_w, L.n, L.classes, L.anchors_dev, L.mask_dev, net->w, net->h,
+                               thresh, L.type == L_GYOLO, net->det_regions + (size_t)hd * B * net->det_cap * R,
+                               net->det_cap, net->det_counts + (size_t)hd * B, R, (float)li, st);
+      if (rc) return rc;
     }
+    rc = launch_yolo_gather(net->det_regions, net->det_counts, heads, B, net->det_cap, R, net->det_dense,
+                            net->det_img_counts, net->det_dense_cap, st);
+    if (rc) return rc;
+    NET_CUDA(cudaMemcpyAsync(net->det_img_counts_host, net->det_img_counts, (size_t)B * 4, cudaMemcpyDeviceToHost, st));
+    NET_CUDA(cudaMemcpyAsync(net->det_img_counts_host + B, net->det_counts, (size_t)heads * B * 4, cudaMemcpyDeviceToHost, st));
+    NET_CUDA(cudaStreamSynchronize(st));
+    tot = 0;
+    for (int b = 0; b < B; ++b) tot += net->det_img_counts_host[b];
+    int worst = 0;
+    for (int i = 0; i < heads * B; ++i) worst = std::max(worst, net->det_img_counts_host[B + i]);
+    if (worst <= net->det_cap) break;
+    // an image has more candidates in one head than the per-head regions hold (the reference has no limit: GetNetworkBoxes
+    // sizes its array from the count, network.cpp:432-470): regrow them to the number of cells, which no count can
+    // exceed, and extract again
+    int max_cells = 0;
+    for (int li : net->yolo_layers) max_cells = std::max(max_cells, net->layers[li].n * net->layers[li].out_h * net->layers[li].out_w);
+    YC_REQUIRE(attempt == 0 && max_cells > net->det_cap, "yc_network_detect: %d candidates in one head exceed its %d cells", worst, max_cells);
+    cudaFree(net->det_regions);
+    net->det_regions = nullptr;
+    net->det_cap = max_cells;
+    NET_CUDA(cudaMalloc(&net->det_regions, (size_t)heads * B * net->det_cap * R * 4));
+  }
   if (tot > net->det_dense_cap) {  // grow the dense buffers and gather again (the per-head regions are intact)
     cudaFree(net->det_dense);
     cudaFreeHost(net->det_host);

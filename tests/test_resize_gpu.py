@@ -32,7 +32,10 @@ def test_resized_inference_network_equals_one_loaded_at_that_size(gpu, name, B, 
         for u, v in zip(a, b):
             assert u.shape == v.shape and np.array_equal(u, v), f"{name} {w}x{h}: resized != loaded at that size"
         # detections through the resized network's workspace
-        da, db = N.DetectBatch(net, 0.25), N.DetectBatch(fresh, 0.25)
+        # (yolov4 with random heads: every cell of the 76x76 head is a candidate, which also takes yc_network_detect through
+        # its regrow path; the host NMS of 2 x 54k boxes would take minutes, so it is off there)
+        nms = 0.45 if name == "yolov4-tiny" else 0.0
+        da, db = N.DetectBatch(net, 0.25, nms), N.DetectBatch(fresh, 0.25, nms)
         assert np.array_equal(da[0], db[0]) and np.array_equal(da[1], db[1])
         fresh.close()
     net.close()
