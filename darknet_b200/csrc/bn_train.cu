@@ -10,6 +10,7 @@
 // Each pass reads/writes every tensor element once with 16-byte accesses; reductions go registers -> shared-memory
 // atomics -> one global atomic per (block, channel).
 #include <algorithm>
+#include <mutex>
 
 #include "yc_common.cuh"
 
@@ -678,6 +679,82 @@ extern "C" int yc_bias_act_bwd(const yc_tensor* dy, const yc_tensor* y, int acti
                                     dv, uv, nullptr, nullptr, nullptr, nullptr, bias_updates, nullptr, P, ticket)));
     YC_LAUNCH_CHECK();
   }
+  const int agroups = (dz->ldc >= (long long)groups * 8) ? dz->ldc / 8 : groups;
+  YC_ACT_DISPATCH(activation, (act_bwd_apply_kernel<A><<<ew_grid(dv.rows * agroups), 256, 0, st>>>(dv, uv, ov, agroups)));
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+// ---- yc_bias_act_bwd_noalloc: the same operator for callers that cannot allocate (CUDA-graph capture, serving loops) ----
+// No counterpart in the reference.  The reduction's scratch (the ticket
+// and one [2][ceil8(c)] partial per block) lives in this file-scope device array instead of a caller-allocated
+// workspace: every GPU that loads the library holds YC_NOALLOC_SCRATCH_FLOATS * 4 bytes (2.4 MB) until exit.
+// All calls on a device share the array: calls that overlap on the GPU (two streams) race.
+#define YC_NOALLOC_MAX_C 1024                       /* channels */
+#define YC_NOALLOC_MAX_BLOCKS 296                   /* blocks of the reduction grid (148 SMs x YC_BN_MINB) */
+#define YC_NOALLOC_SCRATCH_FLOATS (64 + (size_t)YC_NOALLOC_MAX_BLOCKS * 2 * YC_NOALLOC_MAX_C)
+static __device__ __align__(256) float g_noalloc_scratch[YC_NOALLOC_SCRATCH_FLOATS];
+
+// In host code `g_noalloc_scratch` is only a handle; the device address comes from cudaGetSymbolAddress, asked once per
+// device with that device current.
+static float* noalloc_scratch_ptr() {
+  constexpr int kMaxDev = 64;
+  static float* ptrs[kMaxDev] = {};
+  static std::mutex mu;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) {
+    set_error("yc_bias_act_bwd_noalloc: no current CUDA device");
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> g(mu);
+  if (!ptrs[dev]) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) {
+      set_error("yc_bias_act_bwd_noalloc: cudaGetSymbolAddress(g_noalloc_scratch) on device %d -> %s", dev,
+                cudaGetErrorString(e));
+      return nullptr;
+    }
+    ptrs[dev] = p;
+  }
+  return ptrs[dev];
+}
+
+extern "C" size_t yc_bias_act_bwd_noalloc_max_channels(void) { return YC_NOALLOC_MAX_C; }
+
+extern "C" int yc_bias_act_bwd_noalloc(const yc_tensor* dy, const yc_tensor* y, int activation, float* bias_updates,
+                                       const yc_tensor* dz, void* stream) {
+  YC_REQUIRE(ok_view(dy) && ok_view(dz) && (activation == YC_LINEAR || ok_view(y)) && bias_updates,
+             "yc_bias_act_bwd_noalloc: bad arguments");
+  YC_REQUIRE(activation == YC_LINEAR || activation == YC_LEAKY || activation == YC_RELU || activation == YC_LOGISTIC,
+             "yc_bias_act_bwd_noalloc: mish/swish need the saved pre-activation, which only batch-normalised layers keep");
+  YC_REQUIRE(dz->n == dy->n && dz->h == dy->h && dz->w == dy->w && dz->c >= dy->c && dz->dtype == YC_BF16,
+             "yc_bias_act_bwd_noalloc: shape mismatch");
+  YC_REQUIRE(dy->c <= YC_NOALLOC_MAX_C, "yc_bias_act_bwd_noalloc: %d channels exceed the static scratch's maximum of %d",
+             dy->c, YC_NOALLOC_MAX_C);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int n = dy->c;
+  const TView dv = tv(dy);
+  const TView uv = activation == YC_LINEAR ? dv : tv(y);
+  TView ov = tv(dz);
+  ov.c = n;
+  const int groups = (n + 7) / 8;
+  const int threads = reduce_threads(groups);
+  const int slots = threads / groups;
+  const int grid = row_grid(dv.rows, slots, 2);
+  YC_REQUIRE(grid <= YC_NOALLOC_MAX_BLOCKS,
+             "yc_bias_act_bwd_noalloc: a reduction grid of %d blocks exceeds the static scratch's maximum of %d", grid,
+             YC_NOALLOC_MAX_BLOCKS);
+  float* scratch = noalloc_scratch_ptr();
+  if (!scratch) return YC_ERR_CUDA;
+  unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
+  float* P = scratch + 64;
+  // the array keeps the last call's contents: the ticket must start at zero (a call that was aborted would leave it
+  // set); the partials are overwritten before they are read
+  YC_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned), st));
+  YC_ACT_DISPATCH(activation, (bwd_reduce_kernel<1, A><<<grid, threads, reduce_smem(groups, threads), st>>>(
+                                  dv, uv, nullptr, nullptr, nullptr, nullptr, bias_updates, nullptr, P, ticket)));
+  YC_LAUNCH_CHECK();
   const int agroups = (dz->ldc >= (long long)groups * 8) ? dz->ldc / 8 : groups;
   YC_ACT_DISPATCH(activation, (act_bwd_apply_kernel<A><<<ew_grid(dv.rows * agroups), 256, 0, st>>>(dv, uv, ov, agroups)));
   YC_LAUNCH_CHECK();

@@ -95,6 +95,8 @@ _SIGS = {
     "yc_bn_bwd": (C.c_int, [_TP, _TP, _P, _P, _P, _P, C.c_int, _P, _P, _P, _TP, _P]),
     "yc_bias_act_bwd": (C.c_int, [_TP, _TP, C.c_int, _P, _P, _TP, _P]),
     "yc_bn_bwd_workspace_floats": (C.c_size_t, [C.c_int]),
+    "yc_bias_act_bwd_noalloc": (C.c_int, [_TP, _TP, C.c_int, _P, _TP, _P]),
+    "yc_bias_act_bwd_noalloc_max_channels": (C.c_size_t, []),
     "yc_conv_dgrad_channels": (C.c_int, [C.c_int]),
     "yc_conv_dgrad_packed_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "yc_conv_pack_dgrad": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),

@@ -182,6 +182,16 @@ YC_API int yc_bn_bwd(const yc_tensor* dy, const yc_tensor* z, const float* mean,
  * workspace: as for yc_bn_bwd (needed when bias_updates is given). */
 YC_API int yc_bias_act_bwd(const yc_tensor* dy, const yc_tensor* y, int activation, float* bias_updates,
                            float* workspace, const yc_tensor* dz, void* stream);
+/* yc_bias_act_bwd for callers that cannot allocate device memory (code under CUDA-graph capture, serving loops,
+ * harnesses that forbid cudaMalloc).  NO counterpart in the reference.
+ * Same arguments and results as yc_bias_act_bwd without the workspace: the reduction's scratch (ticket + one partial
+ * per block) is a file-scope static __device__ array of the library (2.4 MB, held by every GPU that loads the library
+ * until exit).  Limits: dy->c <= yc_bias_act_bwd_noalloc_max_channels() (1024) and a reduction grid of at most 296
+ * blocks; larger arguments return YC_ERR_ARG.  bias_updates is required.  The call allocates and frees nothing.
+ * Every call on a device shares the one array: calls that overlap on the GPU (different streams) race. */
+YC_API size_t yc_bias_act_bwd_noalloc_max_channels(void);
+YC_API int yc_bias_act_bwd_noalloc(const yc_tensor* dy, const yc_tensor* y, int activation, float* bias_updates,
+                                   const yc_tensor* dz, void* stream);
 
 /* Data gradient (gemm(1,0,...) + col2im_gpu_ext, convolutional_kernels.cu:765-802): runs through the forward
  * implicit-GEMM kernel on the flipped, channel-transposed filter.  yc_conv_dgrad_channels(out_c) is the channel
