@@ -72,6 +72,9 @@ struct ConvParams {
   int fast_epi;        // the specialised epilogue (epilogue_fast) applies: bf16 output, bias only, mish / leaky / linear
   int mish_nr;         // specialised epilogue: mish with a Newton reciprocal (one MUFU per output instead of two)
   int bias_cols;       // > 0: that many floats of bias (n_tiles * block_n) are staged in shared memory at kernel start
+  int cta_pair;        // conv_fprop_pair_kernel: tiles of 256 rows over a cluster of two CTAs (tcgen05 cta_group::2);
+                       // m_tiles then counts 256-row tiles
+  int m_tiles128;      // CTA pairs: the number of real 128-row tiles (an odd count leaves the last pair's second CTA idle)
 };
 
 // ---- halo mode (a_mode 2): 3x3 stride-1 pad-1 convolutions whose A operand is staged ONCE per (tile, 64-channel chunk)
@@ -422,10 +425,14 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
 // independent pairs (16 MUFU.EX2, then 16 MUFU.RCP back to back) so a single warp keeps the XU pipe busy.
 constexpr int kMishNR = 117;  // epilogue_fast only: mish with the reciprocal on the FMA pipe (Newton) instead of MUFU.RCP
 
-template <int ACT, bool HALO, bool RES>
+// PAIR (conv_fprop_pair_kernel, cta_group::2): the tile is 256 GEMM rows over two CTAs, this CTA (cluster rank `rank`)
+// owns rows (2 * mt + rank) * 128 ..., tiles are walked per CTA pair (cta_first = pair index, cta_stride = pairs), and the
+// accumulator is handed back on the LEADER's barrier (tempty0 is then a shared::cluster address).
+template <int ACT, bool HALO, bool RES, bool PAIR = false>
 __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtensorMap* tmap_y, const CUtensorMap* tmap_y2,
                                               uint32_t tmem_base, uint32_t tfull0, uint32_t tempty0, uint32_t sbuf0,
-                                              uint32_t bias_smem, int quad, int slot, int lane, int total_tiles) {
+                                              uint32_t bias_smem, int quad, int slot, int lane, int total_tiles,
+                                              int cta_first, int cta_stride, int rank) {
   const int sets = p.epi_sets, wps = 4 / sets;
   const int set = slot / wps, sub = slot - set * wps;
   const int nacc_mask = p.nacc - 1, nacc_shift = 31 - __clz(p.nacc);
@@ -448,8 +455,12 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtenso
     __syncwarp();
     sbuf = sbuf0 + (two_bufs ? (nst & 1u) * (uint32_t)kStageOutBytes : 0u);
   };
-  const int t_step = (int)gridDim.x * sets;
-  for (int t = blockIdx.x + set * (int)gridDim.x, it = set; t < total_tiles; t += t_step, it += sets) {
+  const int t_step = cta_stride * sets;
+  auto give_back = [&](int acc) {  // one arrival per epilogue warp on the accumulator's "empty" barrier
+    if (PAIR) ptx::mbar_arrive_cluster(tempty0 + 8u * acc);
+    else ptx::mbar_arrive(tempty0 + 8u * acc);
+  };
+  for (int t = cta_first + set * cta_stride, it = set; t < total_tiles; t += t_step, it += sets) {
     const int acc = it & nacc_mask;
     const uint32_t acc_phase = (uint32_t)(it >> nacc_shift) & 1u;
     int mt = t, nt = 0;
@@ -457,17 +468,20 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtenso
       mt = t / n_tiles;
       nt = t - mt * n_tiles;
     }
+    if (PAIR) mt = 2 * mt + rank;
     const int n0 = nt * block_n;
     int row0 = mt * kBlockM + quad * 32;   // first GEMM row of this warp's strip (tiled / im2col)
     int hb = 0, hw0 = 0, hh0 = 0;          // halo: image, first column / row of this warp's 4 x 8 pixel block
     bool any_rows;
+    bool real = true;  // PAIR + HALO: an odd number of 128-pixel tiles leaves the last pair's second CTA without a tile
     if (HALO) {
       hb = fastdiv(mt, p.tpi_magic, p.tpi_shift);
       const int rem = mt - hb * tpi;
       const int th = fastdiv(rem, p.tw_magic, p.tw_shift);
       hh0 = th * kHaloH + quad * 4;
       hw0 = (rem - th * p.tiles_w) * kHaloW;
-      any_rows = hh0 < Ho;
+      if (PAIR) real = mt < p.m_tiles128;
+      any_rows = real && hh0 < Ho;
     } else {
       any_rows = row0 < M;
     }
@@ -486,7 +500,7 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtenso
         bool ok;
         if (HALO) {
           const int h = hh0 + j, w = hw0 + rr;
-          ok = h < Ho && w < Wo;
+          ok = real && h < Ho && w < Wo;
           grow = ((long long)hb * Ho + h) * Wo + w;
         } else {
           grow = (long long)row0 + rr + 8 * j;
@@ -505,7 +519,7 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtenso
     if (sub >= n_groups) {  // nothing of this tile is this warp's: still hand the accumulator back
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(tempty0 + 8u * acc);
+      if (lane == 0) give_back(acc);
       continue;
     }
     for (int g = sub; g < n_groups; g += wps) {
@@ -516,7 +530,7 @@ __device__ __forceinline__ void epilogue_fast(const ConvParams& p, const CUtenso
       if (g + wps >= n_groups) {  // this warp's last read of the accumulator
         ptx::tc_fence_before();
         __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(tempty0 + 8u * acc);
+        if (lane == 0) give_back(acc);
       }
       uint4 rq[4];
       if (RES) {  // the block staged by issue_res has landed: every lane reads its own row, then the buffer is reused
@@ -643,12 +657,27 @@ __device__ __forceinline__ void epilogue_fast_dispatch(const ConvParams& p, cons
                                                        uint32_t tmem_base, uint32_t tfull0, uint32_t tempty0, uint32_t sbuf0,
                                                        uint32_t bias_smem, int quad, int slot, int lane, int total_tiles) {
   const bool halo = p.a_mode == 2, has_res = p.res != nullptr;
+  const int f = (int)blockIdx.x, st = (int)gridDim.x;
   if (halo) {
-    if (has_res) epilogue_fast<ACT, true, true>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles);
-    else epilogue_fast<ACT, true, false>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles);
+    if (has_res) epilogue_fast<ACT, true, true>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles, f, st, 0);
+    else epilogue_fast<ACT, true, false>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles, f, st, 0);
   } else {
-    if (has_res) epilogue_fast<ACT, false, true>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles);
-    else epilogue_fast<ACT, false, false>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles);
+    if (has_res) epilogue_fast<ACT, false, true>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles, f, st, 0);
+    else epilogue_fast<ACT, false, false>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0, sbuf0, bias_smem, quad, slot, lane, total_tiles, f, st, 0);
+  }
+}
+// the same for the CTA-pair kernel (tiled / im2col operands only)
+template <int ACT>
+__device__ __forceinline__ void epilogue_pair_dispatch(const ConvParams& p, const CUtensorMap* tmap_y, const CUtensorMap* tmap_y2,
+                                                       uint32_t tmem_base, uint32_t tfull0, uint32_t tempty0_leader, uint32_t sbuf0,
+                                                       uint32_t bias_smem, int quad, int slot, int lane, int total_tiles,
+                                                       int pair, int npairs, int rank) {
+  if (p.a_mode == 2) {
+    if (p.res != nullptr) epilogue_fast<ACT, true, true, true>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0_leader, sbuf0, bias_smem, quad, slot, lane, total_tiles, pair, npairs, rank);
+    else epilogue_fast<ACT, true, false, true>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0_leader, sbuf0, bias_smem, quad, slot, lane, total_tiles, pair, npairs, rank);
+  } else {
+    if (p.res != nullptr) epilogue_fast<ACT, false, true, true>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0_leader, sbuf0, bias_smem, quad, slot, lane, total_tiles, pair, npairs, rank);
+    else epilogue_fast<ACT, false, false, true>(p, tmap_y, tmap_y2, tmem_base, tfull0, tempty0_leader, sbuf0, bias_smem, quad, slot, lane, total_tiles, pair, npairs, rank);
   }
 }
 
@@ -1035,6 +1064,303 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   }
 }
 
+// ---- CTA pairs: the same GEMM with tcgen05 cta_group::2 ---------------------------------------------------------------
+// Why: with one CTA per MMA a K block of a 128 x 256 tile moves 48 KB INTO shared memory (TMA) and the four MMAs read 48 KB
+// OUT of it in 512 tensor-pipe cycles: 192 B/clk against the 128 B/clk a B200 SM's shared memory delivers, i.e. the wide
+// layers cannot exceed ~2/3 of the tensor peak whatever the pipeline does (measured: 1.0-1.17 PFLOP/s at 1.74 GHz).  A pair
+// of CTAs (cluster of two = one TPC) shares every MMA of M = 256: each CTA stages its own 128 rows of A and only HALF of the
+// weight rows, 32 KB in + 32 KB out per K block = exactly 128 B/clk, and the L2 -> SM traffic for weights halves as well.
+//   * both CTAs run the TMA producer for their own slabs; all bytes are counted on the LEADER's (rank 0) "full" barrier
+//     (cp.async.bulk.tensor ... .cta_group::2 with the leader's barrier address);
+//   * the leader's MMA warp issues tcgen05.mma.cta_group::2 (A / B descriptors name the same offsets in both CTAs; each
+//     CTA's TMEM receives its own 128 rows) and commits with .multicast::cluster to the "empty" / "accumulator full"
+//     barriers of both CTAs;
+//   * both CTAs run the specialised epilogue on their 128 rows; every epilogue warp hands the accumulator back on the
+//     leader's barrier (remote mbarrier.arrive for the peer).
+// Tiled (1x1) and im2col operands, specialised epilogue only (bf16 output, folded batchnorm); everything else stays on
+// conv_fprop_kernel_t.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+conv_fprop_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                       const __grid_constant__ CUtensorMap tmap_y, const __grid_constant__ CUtensorMap tmap_y2,
+                       const ConvParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const bool halo = p.a_mode == 2;
+  const uint32_t a_bytes = halo ? 0u : kBlockM * p.block_k * 2;           // halo: the ring holds weight half-slabs only
+  const uint32_t half_n = (uint32_t)p.block_n >> 1;                       // weight rows this CTA stages
+  const uint32_t bh_tx = half_n * (uint32_t)p.block_k * 2u;
+  const uint32_t bh_bytes = (bh_tx + 1023u) & ~1023u;
+  const uint32_t stage_bytes = a_bytes + bh_bytes;
+  const uint32_t patch_base = smem_base + p.stages * stage_bytes;         // 1024-aligned; halo: halo_stages patches
+  const uint32_t out_base = patch_base + (halo ? p.halo_stages * kHaloPatchStride : 0u);
+  const uint32_t bar_base = out_base + kEpiWarps * kStageOutBytes * p.out_bufs;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + kMaxAcc + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc);
+  auto pfull_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc + 1 + s); };
+  auto pempty_bar = [&](int s) { return bar_base + 8u * (2 * kMaxStages + 2 * kMaxAcc + 1 + kHaloMaxStages + s); };
+  const uint32_t bias_smem = bar_base + 512u;
+  for (int i = threadIdx.x; i < p.bias_cols; i += blockDim.x)
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_smem + 4u * i), "f"(__ldg(p.bias + i)) : "memory");
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const int pair = (int)(blockIdx.x >> 1), npairs = (int)(gridDim.x >> 1);
+
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tmap(&tmap_a);
+    ptx::prefetch_tmap(&tmap_b);
+    ptx::prefetch_tmap(&tmap_y);
+    if (p.split_col > 0) ptx::prefetch_tmap(&tmap_y2);
+    for (int s = 0; s < p.stages; ++s) {
+      ptx::mbar_init(full_bar(s), 1);    // the leader's: one arrive.expect_tx for the bytes of both CTAs
+      ptx::mbar_init(empty_bar(s), 1);   // each CTA's own, arrived by the leader's multicast commit
+    }
+    for (int s2 = 0; s2 < kHaloMaxStages; ++s2) {
+      ptx::mbar_init(pfull_bar(s2), 1);
+      ptx::mbar_init(pempty_bar(s2), 1);
+    }
+    for (int a = 0; a < kMaxAcc; ++a) {
+      ptx::mbar_init(tfull_bar(a), 1);
+      ptx::mbar_init(tempty_bar(a), 2 * kEpiWarps / p.epi_sets);  // the leader's: the tile's set of warps of BOTH CTAs
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {  // the same warp of both CTAs
+    ptx::tmem_alloc_pair(tmem_slot, p.tmem_cols);
+    ptx::tmem_relinquish_pair();
+  }
+  ptx::tc_fence_before();
+  ptx::cluster_sync();  // barriers of BOTH CTAs are initialised before any remote arrival / TMA completion
+  ptx::tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  const int total_tiles = p.m_tiles * p.n_tiles;  // 256-row tiles x N tiles
+  const int k_blocks = p.taps * p.cchunks;
+
+  if (warp == 0 && halo) {
+    // ===================== TMA producer, halo mode (both CTAs): own patches, own half of the weight rows =====================
+    // As in conv_fprop_kernel_t's halo branch, tiles go in PAIRS (halo_pair): two 256-pixel tiles (one 16 x 8 block per
+    // CTA each) accumulate into two TMEM buffers and share every weight slab, so that the leader's MMAs alternate between
+    // two independent accumulators.
+    const bool leader = ptx::elect_one();
+    const uint32_t full0_leader = ptx::mapa(full_bar(0), 0), pfull0_leader = ptx::mapa(pfull_bar(0), 0);
+    int stage = 0, ps = 0;
+    uint32_t phase = 0, pphase = 0;
+    const int tpi = p.tiles_h * p.tiles_w;
+    const int G = p.halo_pair ? 2 : 1;
+    bool first = true;
+    for (int tb = pair; tb < total_tiles; tb += G * npairs) {
+      const int nt = (G == 2 && tb + npairs < total_tiles) ? 2 : 1;
+      int mtb_, ntb_;
+      tile_mn(p, tb, mtb_, ntb_);
+      const int n0 = ntb_ * p.block_n + (int)(rank * half_n);
+      for (int cc = 0; cc < p.cchunks; ++cc) {
+        for (int j = 0; j < nt; ++j) {
+          int mt, ntj_;
+          tile_mn(p, tb + j * npairs, mt, ntj_);
+          mt = 2 * mt + (int)rank;  // (== m_tiles128 for the idle half of an odd last pair: image index past the batch, zero fill)
+          const int img = fastdiv(mt, p.tpi_magic, p.tpi_shift);
+          const int rem = mt - img * tpi;
+          const int th = fastdiv(rem, p.tw_magic, p.tw_shift);
+          const int h0 = th * kHaloH, w0 = (rem - th * p.tiles_w) * kHaloW;
+          ptx::mbar_wait(pempty_bar(ps), pphase ^ 1u);
+          if (leader) {
+            if (rank == 0) ptx::mbar_arrive_expect_tx(pfull_bar(ps), 2u * (uint32_t)(kHaloPatchRows * p.block_k * 2));
+            ptx::tma_load_4d_pair(patch_base + ps * kHaloPatchStride, &tmap_a, pfull0_leader + 8u * ps, cc * p.block_k, w0 - 1,
+                                  h0 - 1, img);
+          }
+          if (++ps == p.halo_stages) { ps = 0; pphase ^= 1u; }
+        }
+        if (p.w_resident) {
+          if (first)
+            for (int tap = 0; tap < 9; ++tap) {
+              const int slot = tap * p.cchunks + cc;
+              if (leader) {
+                if (rank == 0) ptx::mbar_arrive_expect_tx(full_bar(slot), 2u * bh_tx);
+                ptx::tma_load_2d_pair(smem_base + slot * stage_bytes, &tmap_b, full0_leader + 8u * slot, slot * p.block_k, n0);
+              }
+            }
+          continue;
+        }
+        for (int tap = 0; tap < 9; ++tap) {
+          ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
+          if (leader) {
+            if (rank == 0) ptx::mbar_arrive_expect_tx(full_bar(stage), 2u * bh_tx);
+            ptx::tma_load_2d_pair(smem_base + stage * stage_bytes, &tmap_b, full0_leader + 8u * stage,
+                                  (tap * p.cchunks + cc) * p.block_k, n0);
+          }
+          if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+      first = false;
+    }
+  } else if (warp == 1 && halo) {
+    if (rank == 0) {
+      // ===================== MMA issuer, halo mode (leader CTA only) =====================
+      const bool leader = ptx::elect_one();
+      const uint32_t idesc = ptx::make_idesc_bf16(2 * kBlockM, p.block_n);
+      const uint32_t hrow = (uint32_t)p.block_k * 2u;
+      const int hsteps = p.block_k / 16;
+      int stage = 0, ps = 0;
+      uint32_t phase = 0, pphase = 0;
+      int it = 0;
+      const int G = p.halo_pair ? 2 : 1;
+      const int nacc_shift = 31 - __clz(p.nacc);
+      for (int tb = pair; tb < total_tiles; tb += G * npairs) {
+        const bool two = G == 2 && tb + npairs < total_tiles;
+        const int acc0 = it & (p.nacc - 1), acc1 = (it + 1) & (p.nacc - 1);
+        ptx::mbar_wait(tempty_bar(acc0), ((it >> nacc_shift) & 1) ^ 1u);
+        if (two) ptx::mbar_wait(tempty_bar(acc1), (((it + 1) >> nacc_shift) & 1) ^ 1u);
+        ptx::tc_fence_after();
+        const uint32_t d0 = tmem_base + acc0 * p.block_n, d1 = tmem_base + acc1 * p.block_n;
+        for (int cc = 0; cc < p.cchunks; ++cc) {
+          const int ps0 = ps;
+          ptx::mbar_wait(pfull_bar(ps), pphase);
+          if (++ps == p.halo_stages) { ps = 0; pphase ^= 1u; }
+          const int ps1 = ps;
+          if (two) {
+            ptx::mbar_wait(pfull_bar(ps), pphase);
+            if (++ps == p.halo_stages) { ps = 0; pphase ^= 1u; }
+          }
+          ptx::tc_fence_after();
+          const uint32_t pa0 = patch_base + ps0 * kHaloPatchStride, pa1 = patch_base + ps1 * kHaloPatchStride;
+          for (int tap = 0; tap < 9; ++tap) {
+            const int kh = tap / 3, kw = tap - kh * 3;
+            if (p.w_resident) {
+              stage = tap * p.cchunks + cc;
+              phase = 0;
+            }
+            ptx::mbar_wait(full_bar(stage), phase);
+            ptx::tc_fence_after();
+            const uint32_t sh = (uint32_t)(kh * kHaloPitch + kw) * hrow;
+            const uint64_t a0 = ptx::make_smem_desc_shifted(pa0 + sh, kHaloPitch * hrow, hrow);
+            const uint64_t a1 = ptx::make_smem_desc_shifted(pa1 + sh, kHaloPitch * hrow, hrow);
+            const uint64_t bdesc = ptx::make_smem_desc(smem_base + stage * stage_bytes, hrow);
+            if (hsteps == 4) {
+#pragma unroll
+              for (int k2 = 0; k2 < 4; ++k2) {
+                if (leader) ptx::mma_bf16_ss_pair(d0, a0 + 2u * k2, bdesc + 2u * k2, idesc, (cc | tap | k2) != 0);
+                if (leader && two) ptx::mma_bf16_ss_pair(d1, a1 + 2u * k2, bdesc + 2u * k2, idesc, (cc | tap | k2) != 0);
+              }
+            } else {
+#pragma unroll
+              for (int k2 = 0; k2 < 2; ++k2) {
+                if (leader) ptx::mma_bf16_ss_pair(d0, a0 + 2u * k2, bdesc + 2u * k2, idesc, (cc | tap | k2) != 0);
+                if (leader && two) ptx::mma_bf16_ss_pair(d1, a1 + 2u * k2, bdesc + 2u * k2, idesc, (cc | tap | k2) != 0);
+              }
+            }
+            if (!p.w_resident) {
+              if (leader) ptx::mma_commit_pair(empty_bar(stage), 3);
+              if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+            }
+          }
+          if (leader) ptx::mma_commit_pair(pempty_bar(ps0), 3);
+          if (leader && two) ptx::mma_commit_pair(pempty_bar(ps1), 3);
+        }
+        if (leader) ptx::mma_commit_pair(tfull_bar(acc0), 3);
+        if (leader && two) ptx::mma_commit_pair(tfull_bar(acc1), 3);
+        __syncwarp();
+        it += two ? 2 : 1;
+      }
+    }
+  } else if (warp == 0) {
+    // ===================== TMA producer (both CTAs): own 128 rows of A, own half of the weight rows =====================
+    const bool leader = ptx::elect_one();
+    const uint32_t full0_leader = ptx::mapa(full_bar(0), 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    const int hw = p.Ho * p.Wo;
+    for (int t = pair; t < total_tiles; t += npairs) {
+      int mt, nt;
+      tile_mn(p, t, mt, nt);
+      const int m0 = (2 * mt + (int)rank) * kBlockM;
+      const int n0 = nt * p.block_n + (int)(rank * half_n);
+      int img = 0, base_w = 0, base_h = 0;
+      if (p.a_mode == 1) {
+        img = m0 / hw;
+        const int rem = m0 - img * hw;
+        const int ho = rem / p.Wo;
+        base_h = ho * p.stride - p.pad;
+        base_w = (rem - ho * p.Wo) * p.stride_w - p.pad_w;
+      }
+      int kb = 0;
+      for (int tap = 0; tap < p.taps; ++tap) {
+        const int r = tap / p.kw, s = tap - r * p.kw;
+        for (int cc = 0; cc < p.cchunks; ++cc, ++kb) {
+          ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = smem_base + stage * stage_bytes;
+          if (leader) {
+            if (rank == 0) ptx::mbar_arrive_expect_tx(full_bar(stage), 2u * (a_bytes + bh_tx));
+            const uint32_t fb = full0_leader + 8u * stage;
+            if (p.a_mode == 1)
+              ptx::tma_load_im2col_4d_pair(sa, &tmap_a, fb, cc * p.block_k, base_w, base_h, img, (uint16_t)(s * p.dil),
+                                           (uint16_t)(r * p.dil));
+            else
+              ptx::tma_load_2d_pair(sa, &tmap_a, fb, cc * p.block_k, m0);
+            ptx::tma_load_2d_pair(sa + a_bytes, &tmap_b, fb, kb * p.block_k, n0);
+          }
+          if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0) {
+      // ===================== MMA issuer (leader CTA only), one elected lane =====================
+      const bool leader = ptx::elect_one();
+      const uint32_t idesc = ptx::make_idesc_bf16(2 * kBlockM, p.block_n);
+      const uint32_t row_bytes = p.block_k * 2;
+      const int nacc_shift = 31 - __clz(p.nacc);
+      const int k_steps = p.block_k / 16;
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = pair; t < total_tiles; t += npairs, ++it) {
+        const int acc = it & (p.nacc - 1);
+        ptx::mbar_wait(tempty_bar(acc), ((it >> nacc_shift) & 1) ^ 1u);
+        ptx::tc_fence_after();
+        const uint32_t d = tmem_base + acc * p.block_n;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          ptx::mbar_wait(full_bar(stage), phase);
+          ptx::tc_fence_after();
+          const uint32_t sa = smem_base + stage * stage_bytes;
+          const uint64_t adesc = ptx::make_smem_desc(sa, row_bytes);
+          const uint64_t bdesc = ptx::make_smem_desc(sa + a_bytes, row_bytes);
+          if (leader) {
+            for (int k = 0; k < k_steps; ++k)
+              ptx::mma_bf16_ss_pair(d, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+            ptx::mma_commit_pair(empty_bar(stage), 3);  // frees the slot in both CTAs when these MMAs retire
+            if (kb == k_blocks - 1) ptx::mma_commit_pair(tfull_bar(acc), 3);
+          }
+          __syncwarp();
+          if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue (both CTAs, own 128 rows) =====================
+    const int quad = warp & 3;
+    const uint32_t stage_base = out_base + (uint32_t)(warp - 2) * kStageOutBytes * p.out_bufs;
+    const int slot = (warp - 2) >> 2;
+    const uint32_t tempty0_leader = ptx::mapa(tempty_bar(0), 0);
+    const int r = (int)rank;
+    if (p.act == YC_MISH) epilogue_pair_dispatch<YC_MISH>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty0_leader, stage_base, bias_smem, quad, slot, lane, total_tiles, pair, npairs, r);
+    else if (p.act == YC_LEAKY) epilogue_pair_dispatch<YC_LEAKY>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty0_leader, stage_base, bias_smem, quad, slot, lane, total_tiles, pair, npairs, r);
+    else epilogue_pair_dispatch<YC_LINEAR>(p, &tmap_y, &tmap_y2, tmem_base, tfull_bar(0), tempty0_leader, stage_base, bias_smem, quad, slot, lane, total_tiles, pair, npairs, r);
+  }
+
+  ptx::tc_fence_before();
+  ptx::cluster_sync();  // neither CTA's shared memory / TMEM goes away while the other may still use it
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc_pair(tmem_base, p.tmem_cols);
+  }
+}
+
 // ---- weight packing: OIHW fp32 -> [out_c][tap][in_c_p] bf16 ------------------------------------
 __global__ void pack_weights_kernel(const float* __restrict__ w, int out_c, int in_c, int taps, int in_c_p,
                                     __nv_bfloat16* __restrict__ out) {
@@ -1104,6 +1430,8 @@ struct yc_conv_plan {
   unsigned* stat_ticket = nullptr;
   int grid = 0;
   size_t smem = 0;
+  const void* w_packed = nullptr;  // for re-encoding the weight map when a CTA-pair plan falls back (yc_conv_plan_set_stats)
+  int w_kdim = 0;                  // taps * padded in_c
 };
 
 namespace {
@@ -1311,12 +1639,28 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   // 5-10 % (they are bound by the activation stream, and a pair halves the number of ring stages) -> threshold 12
   p.tile_pair = (p.a_mode != 2 && p.n_tiles == 1 && p.block_n <= 128 && !(flags & YC_PLAN_NO_TILE_PAIR) &&
                  k_blocks * (p.block_k / 16) >= 12 && p.m_tiles >= 2 * sms) ? 1 : 0;
-  const uint32_t stage_bytes_g = (p.tile_pair ? 2u : 1u) * a_bytes + b_bytes;  // tiled / im2col ring stage
+  // CTA pairs (conv_fprop_pair_kernel, tcgen05 cta_group::2): 256-row tiles over a cluster of two CTAs, each staging its own
+  // A rows and half of the weight rows.  Default: the 256-wide tiles of the tiled / im2col path with the specialised
+  // epilogue (they are shared-memory-bandwidth bound with one CTA per MMA); YC_PLAN_CTA_PAIR_ALL: wherever legal (tests),
+  // YC_PLAN_NO_CTA_PAIR: never.
+  // Measured (yolov4-608 x 64, same box, tools/ab_layers.py pair / nopair): 3x3 512->1024 @19 214 -> 153 us (1.42 PFLOP/s),
+  // 256->256 @38 120 -> 91 us, 512->512 @19 137 -> 100 us, 1x1 1024->512 @19 41 -> 34 us; the 1x1 layers with K <= 512 (8 K
+  // blocks or fewer) gain nothing or lose up to 10 % (their tiles are short: the pair's start-up and the remote hand-backs
+  // show) -> from 12 K blocks on.
+  // Halo mode: the 128-wide tiles with at least 128 input channels (3x3 128->128 @76: one MMA of a 128 x 128 tile is 64
+  // tensor-pipe cycles of work against an issue interval of ~175 for MMAs on one accumulator; a pair of CTAs doubles the
+  // work per MMA, two tiles in flight double it again).
+  const bool pair_rule = p.a_mode == 2 ? (p.block_n == 128 && p.n_tiles == 1 && x->c >= 128) : (p.block_n == 256 && k_blocks >= 12);
+  p.cta_pair = (p.fast_epi && !(flags & YC_PLAN_NO_CTA_PAIR) && sms >= 2 &&
+                (pair_rule || (flags & YC_PLAN_CTA_PAIR_ALL))) ? 1 : 0;
+  if (p.cta_pair) p.tile_pair = 0;
+  const uint32_t bh_bytes = (uint32_t)round_up((p.block_n / 2) * p.block_k * 2, 1024);
+  const uint32_t stage_bytes_g = p.cta_pair ? a_bytes + bh_bytes : (p.tile_pair ? 2u : 1u) * a_bytes + b_bytes;  // tiled / im2col ring stage
   auto layout = [&](int out_bufs) -> bool {
     p.out_bufs = out_bufs;
     p.halo_stages = 2;
     p.halo_pair = 0;
-    const uint32_t stage_bytes = p.a_mode == 2 ? b_bytes : stage_bytes_g;
+    const uint32_t stage_bytes = p.a_mode == 2 ? (p.cta_pair ? bh_bytes : b_bytes) : stage_bytes_g;
     const uint32_t a_ring = (p.tile_pair ? 2u : 1u) * a_bytes;
     const uint32_t out_bytes = kEpiWarps * kStageOutBytes * out_bufs;
     const uint32_t fixed = 1024 /*align slack*/ + 512 /*barriers*/ + bias_bytes;
@@ -1337,7 +1681,7 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
       p.stages = 9 * p.cchunks;
     }
     pl->smem = (size_t)p.stages * stage_bytes + out_stage + fixed;
-    if (p.a_mode != 2 && p.n_tiles == 1 && (wres_env == 2 || (wres_env == 1 && p.taps > 1))) {
+    if (p.a_mode != 2 && !p.cta_pair && p.n_tiles == 1 && (wres_env == 2 || (wres_env == 1 && p.taps > 1))) {
       const uint32_t wres_bytes = (uint32_t)k_blocks * b_bytes;
       const long long tiles_per_cta = (long long)p.m_tiles / std::max(1, sms);
       if (wres_bytes <= 64 * 1024 && tiles_per_cta >= 8 && smem_budget >= wres_bytes + 4 * a_ring) {
@@ -1459,8 +1803,10 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   {
     cuuint64_t dims[2] = {(cuuint64_t)p.taps * in_c_p, (cuuint64_t)N};
     cuuint64_t strides[1] = {(cuuint64_t)p.taps * in_c_p * 2};
-    cuuint32_t box[2] = {(cuuint32_t)p.block_k, (cuuint32_t)p.block_n};
+    cuuint32_t box[2] = {(cuuint32_t)p.block_k, (cuuint32_t)(p.cta_pair ? p.block_n / 2 : p.block_n)};
     cuuint32_t estr[2] = {1, 1};
+    pl->w_packed = w_packed;
+    pl->w_kdim = p.taps * in_c_p;
     cr = g_encode_tiled(&pl->tmap_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(w_packed), dims, strides,
                         box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -1505,12 +1851,20 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   }
   pl->rect = rect;
 
-  pl->grid = (int)std::min<long long>((long long)p.m_tiles * p.n_tiles, sms);
+  p.m_tiles128 = p.m_tiles;
+  if (p.cta_pair) {  // 256-row tiles, one cluster of two CTAs per tile at a time
+    p.m_tiles = ceil_div(p.m_tiles, 2);
+    pl->grid = 2 * (int)std::min<long long>((long long)p.m_tiles * p.n_tiles, sms / 2);
+  } else {
+    pl->grid = (int)std::min<long long>((long long)p.m_tiles * p.n_tiles, sms);
+  }
   static bool attr_set = false;
   if (!attr_set) {
     e = cudaFuncSetAttribute(conv_fprop_kernel_t<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(conv_fprop_kernel_t<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(conv_fprop_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       set_error("cudaFuncSetAttribute(max dynamic smem) failed: %s", cudaGetErrorString(e));
       yc_conv_plan_destroy(pl);
@@ -1585,6 +1939,19 @@ extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq
   p.fast_epi = 0;                       // statistics are reduced by the generic epilogue
   p.bias_cols = 0;
   p.tile_pair = 0;
+  if (p.cta_pair) {  // back to one CTA per tile: 128-row tiles, the whole N tile's weight rows per stage
+    p.cta_pair = 0;
+    p.m_tiles = p.m_tiles128;
+    pl->grid = (int)std::min<long long>((long long)p.m_tiles * p.n_tiles, sm_count());
+    cuuint64_t dims[2] = {(cuuint64_t)pl->w_kdim, (cuuint64_t)p.N};
+    cuuint64_t strides[1] = {(cuuint64_t)pl->w_kdim * 2};
+    cuuint32_t box[2] = {(cuuint32_t)p.block_k, (cuuint32_t)p.block_n};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult cr = g_encode_tiled(&pl->tmap_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(pl->w_packed), dims,
+                                 strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(p.block_k),
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    YC_REQUIRE(cr == CUDA_SUCCESS, "yc_conv_plan_set_stats: weight tensor map encode failed (CUresult %d)", (int)cr);
+  }
   if (p.a_mode != 2) p.w_resident = 0;  // the ring is re-planned below with weights in every stage
   // the generic epilogue's warp-to-tile assignment: four warps per quadrant on a wide tile (fewer statistics regions)
   const int groups = p.block_n / 32;
@@ -1623,6 +1990,14 @@ extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq
   return YC_OK;
 }
 
+// The plan holds a padded COPY of the bias taken when it was created: after the bias changes (an SGD step on a layer
+// without batchnorm, i.e. the YOLO heads) the copy has to follow.  Asynchronous on `stream`, N floats device to device.
+extern "C" int yc_conv_plan_set_bias(yc_conv_plan* pl, const float* bias, void* stream) {
+  YC_REQUIRE(pl && bias && pl->bias_pad, "yc_conv_plan_set_bias: bad arguments");
+  YC_CUDA(cudaMemcpyAsync(pl->bias_pad, bias, sizeof(float) * pl->p.N, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return YC_OK;
+}
+
 extern "C" int yc_conv_plan_destroy(yc_conv_plan* pl) {
   if (!pl) return YC_OK;
   if (pl->bias_pad) cudaFree(pl->bias_pad);
@@ -1637,6 +2012,8 @@ extern "C" int yc_conv_fprop(const yc_conv_plan* pl, void* stream) {
   YC_REQUIRE(pl, "yc_conv_fprop: null plan");
   if (pl->p.stat_sum)
     conv_fprop_kernel_t<true><<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->tmap_y2, pl->p);
+  else if (pl->p.cta_pair)  // cluster of two CTAs per 256-row tile (static __cluster_dims__)
+    conv_fprop_pair_kernel<<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->tmap_y2, pl->p);
   else
     conv_fprop_kernel_t<false><<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->tmap_y2, pl->p);
   YC_LAUNCH_CHECK();
@@ -1653,9 +2030,10 @@ extern "C" int yc_conv_plan_info(const yc_conv_plan* pl, int what) {
     case 4: return pl->grid;
     case 5: return pl->p.a_mode;
     case 6: return (int)pl->smem;
-    case 7:  // kernel variant: [0,2) a_mode, 4 halo tile pairs, 8 resident weights, 16 two outputs, 32 two staging buffers, 64 rectangular, 128 fast epilogue
+    case 7:  // kernel variant: [0,2) a_mode, 4 halo tile pairs, 8 resident weights, 16 two outputs, 32 two staging buffers, 64 rectangular, 128 fast epilogue, 256 tile pairs, 512 CTA pairs
       return pl->p.a_mode | (pl->p.halo_pair ? 4 : 0) | (pl->p.w_resident ? 8 : 0) | (pl->p.split_col ? 16 : 0) |
-             (pl->p.out_bufs == 2 ? 32 : 0) | (pl->rect ? 64 : 0) | (pl->p.fast_epi ? 128 : 0) | (pl->p.tile_pair ? 256 : 0);
+             (pl->p.out_bufs == 2 ? 32 : 0) | (pl->rect ? 64 : 0) | (pl->p.fast_epi ? 128 : 0) | (pl->p.tile_pair ? 256 : 0) |
+             (pl->p.cta_pair ? 512 : 0);
     case 8: return pl->p.epi_sets;
   }
   return -1;

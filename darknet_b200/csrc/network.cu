@@ -440,7 +440,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
     net->finalized = true;
     return YC_OK;
   }
-  const unsigned plan_flags = ((unsigned)flags >> YC_NET_PLAN_SHIFT) & 0xfffu;
+  const unsigned plan_flags = ((unsigned)flags >> YC_NET_PLAN_SHIFT) & 0x3fffu;
   if (stem && Ls[0].n % 8 == 0 && 2 * Ls[0].n <= 256 && Ls[0].out_w % 2 == 0 && Ls[0].fused_into < 0 &&
       view_of(net, 0).ldc == Ls[0].n && view_of(net, 0).dtype == YC_BF16 && !(flags & YC_NET_NO_STEM_PAIR))
     net->stem_pair = true;
@@ -1280,6 +1280,56 @@ extern "C" int yc_network_profile(yc_network* net, const float* input_dev, int i
   }
   for (auto& e : ev) cudaEventDestroy(e);
   return rc;
+}
+
+// The forward's kernels of one class replayed back to back as a CUDA graph, the way they run inside the real step
+// (yc_network_profile brackets every launch with events: each kernel then starts on an idle GPU and the stream drains in
+// between, which costs the many short layers 5-10 us each).  which: 0 = the convolution launches only, 1 = every other
+// kernel, 2 = all of them.  The buffers hold whatever the last forward left: the kernels' timing does not depend on the
+// values.  ms_per_replay = mean over `iters` replays, CUDA events on the network's stream around the whole batch of
+// replays.
+extern "C" int yc_network_time_ops(yc_network* net, const float* input_dev, int which, int iters, float* ms_per_replay,
+                                   int* launches) {
+  YC_REQUIRE(net && input_dev && ms_per_replay && iters > 0 && which >= 0 && which <= 2, "yc_network_time_ops: bad argument");
+  if (!net->finalized) {
+    int rc = yc_network_finalize(net);
+    if (rc) return rc;
+  }
+  net->graph_input = input_dev;
+  cudaGraph_t g = nullptr;
+  cudaGraphExec_t ge = nullptr;
+  int n = 0;
+  NET_CUDA(cudaStreamBeginCapture(net->stream, cudaStreamCaptureModeThreadLocal));
+  int rc = YC_OK;
+  for (size_t k = 0; k < net->ops.size() && !rc; ++k) {
+    const bool conv = net->ops[k].kind == 0;
+    if (which == 2 || (which == 0) == conv) {
+      rc = run_op(net, net->ops[k], net->stream);
+      ++n;
+    }
+  }
+  cudaError_t e = cudaStreamEndCapture(net->stream, &g);
+  if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+  if (e != cudaSuccess) NET_FAIL(YC_ERR_CUDA, "yc_network_time_ops: cudaStreamEndCapture: %s", cudaGetErrorString(e));
+  if (launches) *launches = n;
+  if (n == 0) { cudaGraphDestroy(g); *ms_per_replay = 0.f; return YC_OK; }
+  NET_CUDA(cudaGraphInstantiate(&ge, g, 0));
+  cudaEvent_t e0, e1;
+  NET_CUDA(cudaEventCreate(&e0));
+  NET_CUDA(cudaEventCreate(&e1));
+  for (int i = 0; i < 2; ++i) NET_CUDA(cudaGraphLaunch(ge, net->stream));  // warm-up
+  NET_CUDA(cudaEventRecord(e0, net->stream));
+  for (int i = 0; i < iters; ++i) NET_CUDA(cudaGraphLaunch(ge, net->stream));
+  NET_CUDA(cudaEventRecord(e1, net->stream));
+  NET_CUDA(cudaStreamSynchronize(net->stream));
+  float ms = 0.f;
+  NET_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  *ms_per_replay = ms / iters;
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaGraphExecDestroy(ge);
+  cudaGraphDestroy(g);
+  return YC_OK;
 }
 
 // ---- detections on the host: GetNetworkBoxes / NmsSort --------------------------------------------------

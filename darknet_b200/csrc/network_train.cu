@@ -527,7 +527,12 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
     net->sgd_blocks = blocks;
   }
   net->curr_iter = iter + 1;
-  return yc::sgd_update_multi(net->sgd_items, net->sgd_n, net->sgd_blocks, lr, batch, carry, decay, st);
+  int rc = yc::sgd_update_multi(net->sgd_items, net->sgd_n, net->sgd_blocks, lr, batch, carry, decay, st);
+  // layers without batchnorm (the YOLO heads) add their bias in the conv epilogue, from the plan's own padded copy: it
+  // follows the update (found by tests/test_resize_gpu.py: a re-planned network saw the new biases, the running one did not)
+  for (NLayer& L : net->layers)
+    if (!rc && L.type == L_CONV && !L.bn && L.plan && L.bias_dev && L.bias_upd) rc = yc_conv_plan_set_bias(L.plan, L.bias_dev, st);
+  return rc;
 }
 
 // PullConvolutionalLayer for every conv layer (convolutional_kernels.cu:817-836): device master copies -> the host-side

@@ -52,6 +52,7 @@ NET_STEM_IM2COL = 512
 NET_NO_STEM_PAIR, NET_NO_PAIR_S2, NET_NO_PAIR_FUSE, NET_PLAN_SHIFT = 1024, 2048, 4096, 16
 PLAN_NO_HALO, PLAN_FORCE_HALO, PLAN_NO_HALO_PAIR, PLAN_NO_W_RES, PLAN_W_RES_1X1, PLAN_ONE_OUT_BUF, PLAN_COST_V1 = 1, 2, 4, 8, 16, 32, 64
 PLAN_TWO_OUT_BUFS, PLAN_GENERIC_EPI, PLAN_EPI_SETS_V1, PLAN_MISH_NEWTON, PLAN_NO_TILE_PAIR = 128, 256, 512, 1024, 2048
+PLAN_NO_CTA_PAIR, PLAN_CTA_PAIR_ALL = 4096, 8192
 # every plan switch off: the plainest kernel variant of each layer (parity coverage of the non-default paths)
 NET_PLAIN_PLANS = NET_NO_STEM_PAIR | NET_NO_PAIR_S2 | NET_NO_PAIR_FUSE | ((PLAN_NO_HALO | PLAN_NO_W_RES | PLAN_ONE_OUT_BUF | PLAN_GENERIC_EPI | PLAN_NO_TILE_PAIR) << NET_PLAN_SHIFT)
 NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
@@ -90,6 +91,7 @@ _SIGS = {
     "yc_conv_fprop": (C.c_int, [_P, _P]),
     "yc_conv_plan_info": (C.c_int, [_P, C.c_int]),
     "yc_conv_plan_set_stats": (C.c_int, [_P, _P, _P]),
+    "yc_conv_plan_set_bias": (C.c_int, [_P, _P, _P]),
     "yc_bn_finalize": (C.c_int, [_P, _P, C.c_longlong, _P, _P, _P, _P, C.c_int, _P]),
     "yc_bn_act_fwd": (C.c_int, [_TP, _P, _P, _P, _P, C.c_int, _TP, _P]),
     "yc_bn_bwd": (C.c_int, [_TP, _TP, _P, _P, _P, _P, C.c_int, _P, _P, _P, _TP, _P]),
@@ -158,6 +160,7 @@ _SIGS = {
     "yc_network_layer_output": (C.c_int, [_P, C.c_int, _P]),
     "yc_network_yolo_output": (_P, [_P, C.c_int]),
     "yc_network_profile": (C.c_int, [_P, _P, C.c_int, _P]),
+    "yc_network_time_ops": (C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P]),
     "yc_network_train_datum": (C.c_int, [_P, _P, _P, C.POINTER(C.c_float)]),
     "yc_network_forward_backward": (C.c_int, [_P, _P, _P, _P]),
     "yc_network_update": (C.c_int, [_P, C.c_float, C.c_float, C.c_float, _P]),

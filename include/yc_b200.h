@@ -130,7 +130,9 @@ enum {
   YC_PLAN_GENERIC_EPI = 256, /* never use the specialised (bf16 / bias-only / mish-leaky-linear) epilogue */
   YC_PLAN_EPI_SETS_V1 = 512, /* specialised epilogue with the generic one's warp-to-tile assignment */
   YC_PLAN_NO_TILE_PAIR = 2048, /* tiled / im2col path: one tile at a time instead of tile pairs (two accumulators) */
-  YC_PLAN_MISH_NEWTON = 1024 /* specialised epilogue: mish with one MUFU + a Newton reciprocal on the FMA pipe (measured slower) */
+  YC_PLAN_MISH_NEWTON = 1024, /* specialised epilogue: mish with one MUFU + a Newton reciprocal on the FMA pipe (measured slower) */
+  YC_PLAN_NO_CTA_PAIR = 4096, /* never run a layer on CTA pairs (tcgen05 cta_group::2, 256-row tiles over a cluster of two) */
+  YC_PLAN_CTA_PAIR_ALL = 8192 /* CTA pairs wherever legal (tiled / im2col operands, specialised epilogue), not only for 256-wide tiles */
 };
 /* [setup] yc_conv_plan_create with plan switches and, optionally, a SECOND output tensor y2: the GEMM then has
  * y->c + y2->c output channels (weights / bias / scale of both layers concatenated along out_c, y->c a multiple of
@@ -161,6 +163,10 @@ YC_API int yc_conv_plan_info(const yc_conv_plan* plan, int what);
  *   mean, var, rolling update            yc_bn_finalize (unbiased variance, rolling = .9 roll + .1 batch)
  *   y = act(gamma*(z-mean)/sqrt(var+1e-6)+beta)   yc_bn_act_fwd */
 YC_API int yc_conv_plan_set_stats(yc_conv_plan* plan, float* sum, float* sumsq);
+/* A plan keeps a padded copy of the bias it was created with; after the bias changes (update_convolutional_layer on a
+ * layer without batchnorm: the YOLO heads, convolutional_layer.cpp:1382-1401 axpy on l.biases) hand it the new values.
+ * Asynchronous on `stream`. */
+YC_API int yc_conv_plan_set_bias(yc_conv_plan* plan, const float* bias_dev, void* stream);
 YC_API int yc_bn_finalize(const float* sum, const float* sumsq, long long count, float* mean, float* var,
                           float* rolling_mean, float* rolling_var, int n, void* stream);
 YC_API int yc_bn_act_fwd(const yc_tensor* z, const float* mean, const float* var, const float* gamma,
@@ -353,7 +359,7 @@ enum {
   YC_NET_NO_STEM_PAIR = 1024, /* stem conv on single pixels instead of pixel pairs (A/B + parity coverage) */
   YC_NET_NO_PAIR_S2 = 2048,  /* 3x3 stride-2 32-channel layer on the plain im2col path instead of the pixel-pair view */
   YC_NET_NO_PAIR_FUSE = 4096, /* do not merge two 1x1 convs that read the same tensor into one GEMM */
-  YC_NET_PLAN_SHIFT = 16,    /* bits [16,28): YC_PLAN_* switches handed to every conv plan */
+  YC_NET_PLAN_SHIFT = 16,    /* bits [16,30): YC_PLAN_* switches handed to every conv plan */
   YC_NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
 };
 
@@ -445,6 +451,11 @@ YC_API const float* yc_network_yolo_output(yc_network* net, int layer);
 /* per-layer device time of one un-graphed forward, averaged over iters (net->benchmark_layers,
  * network_kernels.cu:70-94).  ms_per_layer has n_layers entries (+1: the input conversion at index n). */
 YC_API int yc_network_profile(yc_network* net, const float* input_dev_nchw, int iters, float* ms_per_layer);
+/* Measurement: the forward's kernels of one class (which = 0: convolution launches, 1: all other kernels, 2: all)
+ * replayed back to back as one CUDA graph, the way they run inside the step; mean ms per replay over `iters` replays
+ * (CUDA events on the network's stream), number of kernels per replay in *launches.  No reference counterpart. */
+YC_API int yc_network_time_ops(yc_network* net, const float* input_dev_nchw, int which, int iters, float* ms_per_replay,
+                               int* launches);
 
 /* ---- training step: replaces TrainNetworkDatumGpu / ForwardBackwardNetworkGpu / UpdateNetworkGpu -------------- */
 /* (network_kernels.cu:116-293; CPU twins network.cpp:101-208.)  The network must be loaded with YC_NET_TRAIN.

@@ -133,6 +133,41 @@ def test_conv_plan_switches(gpu):
     _run(gpu, 8, 512, 19, 19, 512, 3, 1, "leaky")
 
 
+def test_conv_cta_pairs(gpu):
+    """conv_fprop_pair_kernel (tcgen05 cta_group::2: 256-row tiles over a cluster of two CTAs, each staging its own A rows
+    and half of the weight rows): the default rule (256-wide tiles, specialised epilogue) and, forced, every operand shape it
+    accepts — odd tile counts (the last pair's second CTA entirely past M), several N tiles, many tiles per pair, narrow
+    tiles, 32-channel K chunks, stride 2, fused shortcut, two output tensors."""
+    from darknet_b200 import lib as L
+    PA = L.PLAN_CTA_PAIR_ALL
+    _run(gpu, 8, 256, 38, 38, 256, 3, 1, "leaky", want_variant=(512 | 3, 512 | 1))          # default rule, im2col
+    _run(gpu, 8, 256, 38, 38, 256, 3, 1, "leaky", plan_flags=L.PLAN_NO_CTA_PAIR, want_variant=(512, 0))
+    _run(gpu, 64, 128, 19, 19, 512, 3, 1, "leaky", want_variant=(512, 512))                 # 2 N tiles, 182 pair tiles on 74 pairs
+    _run(gpu, 64, 1024, 19, 19, 256, 1, 1, "mish", want_variant=(512 | 3, 512 | 0))         # default rule, 1x1 tiled map, 16 K blocks
+    _run(gpu, 64, 512, 19, 19, 256, 1, 1, "mish", want_variant=(512, 0))                    # 8 K blocks: stays on one CTA per tile
+    _run(gpu, 3, 512, 19, 19, 256, 3, 1, "mish", plan_flags=PA, want_variant=(512, 512))    # 9 row tiles: odd
+    _run(gpu, 5, 512, 19, 19, 256, 1, 1, "leaky", residual=True, plan_flags=PA, want_variant=(512, 512))
+    _run(gpu, 4, 64, 38, 38, 64, 1, 1, "mish", plan_flags=PA | L.PLAN_NO_HALO, want_variant=(512, 512))
+    _run(gpu, 4, 64, 38, 38, 128, 3, 2, "mish", plan_flags=PA, want_variant=(512, 512))
+    _run(gpu, 2, 96, 24, 24, 96, 3, 1, "linear", plan_flags=PA | L.PLAN_NO_HALO, want_variant=(512, 512))
+    _run(gpu, 1, 64, 5, 5, 40, 3, 1, "leaky", plan_flags=PA | L.PLAN_NO_HALO, want_variant=(512, 512))   # one tile, ragged
+    _run(gpu, 2, 256, 19, 19, 256, 1, 1, "mish", split=128, plan_flags=PA, want_variant=(16 | 512, 16 | 512))
+    # halo patches on CTA pairs (each CTA its own 16 x 8 block, tile pairs alternate between two accumulators): the default
+    # rule (128 -> 128), then forced: resident weights + shortcut, an odd number of blocks, 32-channel chunks, three chunks
+    FH = L.PLAN_FORCE_HALO
+    _run(gpu, 4, 128, 76, 76, 128, 3, 1, "mish", want_variant=(512 | 3 | 4, 512 | 2 | 4))
+    _run(gpu, 4, 128, 76, 76, 128, 3, 1, "mish", residual=True, plan_flags=L.PLAN_NO_CTA_PAIR, want_variant=(512 | 3, 2))
+    _run(gpu, 4, 64, 38, 38, 64, 3, 1, "mish", residual=True, plan_flags=PA | FH, want_variant=(512 | 3 | 8, 512 | 2 | 8))
+    _run(gpu, 3, 64, 38, 22, 64, 3, 1, "leaky", residual=True, plan_flags=PA | FH, want_variant=(512 | 3, 512 | 2))
+    _run(gpu, 32, 64, 38, 38, 64, 3, 1, "linear", plan_flags=PA | FH, want_variant=(512 | 3, 512 | 2))  # 480 blocks on 74 pairs
+    _run(gpu, 4, 32, 38, 38, 64, 3, 1, "mish", plan_flags=PA | FH, want_variant=(512 | 3, 512 | 2))
+    _run(gpu, 2, 96, 24, 24, 128, 3, 1, "leaky", plan_flags=PA | FH, want_variant=(512 | 3, 512 | 2))
+    _run(gpu, 2, 256, 19, 19, 256, 3, 1, "leaky", plan_flags=PA | FH, want_variant=(512 | 3, 512 | 2))  # two N tiles? no: one of 256
+    # not legal -> stays on the one-CTA kernel whatever the flag says: fp32 output, unfused scale
+    _run(gpu, 2, 128, 10, 10, 24, 1, 1, "linear", out_f32=True, plan_flags=PA, want_variant=(512, 0))
+    _run(gpu, 2, 64, 10, 10, 64, 3, 1, "leaky", scale=True, plan_flags=PA | L.PLAN_NO_HALO, want_variant=(512, 0))
+
+
 def test_mish_newton_reciprocal_variant(gpu):
     """The specialised epilogue's opt-in mish (one MUFU.EX2 + a Newton reciprocal on the FMA pipe, 9e-6 relative) against
     the default two-MUFU form on the same accumulators: the bf16 outputs may differ by one ulp on a handful of elements that
