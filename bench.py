@@ -257,6 +257,8 @@ def run_train(args):
         import torch.distributed as dist  # noqa: F811
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     cfgname, B = args.train_net, args.batch
+    if args.wgrad_single_tap:
+        L.lib().yc_conv_wgrad_set_tap_groups(0)
     hw = 416 if cfgname == "yolov4-tiny" else 608
     text = cfgs.CONFIGS[cfgname](w=hw, h=hw, batch=B, subdivisions=1)
     weights = cfgmod.synth_weights(text)
@@ -505,6 +507,7 @@ def main():
     ap.add_argument("--quick-exit-after-timed", action="store_true", help="(profiling) skip e2e / roofline / cpu legs")
     ap.add_argument("--net-flags", default="0", help="(A/B) extra yc_network_load flags in hex, OR'ed onto the default plan")
     ap.add_argument("--no-train-leg", action="store_true", help="skip the data-parallel training measurements of the default run")
+    ap.add_argument("--wgrad-single-tap", action="store_true", help="(A/B, --mode train) plan wgrad with one tap per work unit")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_train(args) if args.mode == "train" else run_reference(args)

@@ -40,7 +40,12 @@ struct WgradParams {
   int mma_n;        // N of the MMA instruction (multiple of 16, <= block_n)
   int n_tiles;      // ceil(N_out / 128)
   int c_tiles;      // ceil(C_in / block_n)
-  int tiles;        // n_tiles * taps * c_tiles
+  int tap_group;    // taps per work unit (1, 3 = one kernel row, or 9): they share the unit's dY boxes and accumulate into
+                    // tap_group independent TMEM regions, so the MMA stream alternates between accumulators
+  int tgroups;      // taps / tap_group
+  int acc_cols;     // TMEM columns per tap accumulator (mma_n rounded up to 32)
+  int nbuf;         // accumulator sets in TMEM: 2 (the epilogue of unit i overlaps the main loop of unit i + 1) or 1
+  int tiles;        // n_tiles * tgroups * c_tiles
   int splits, kb_total, kb_per_split;
   int stages;
   int a_boxes, b_boxes;
@@ -79,7 +84,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t a_bytes = p.a_boxes * kBoxBytes;
-  const uint32_t stage_bytes = (p.a_boxes + p.b_boxes) * kBoxBytes;
+  const uint32_t stage_bytes = (p.a_boxes + p.tap_group * p.b_boxes) * kBoxBytes;
   const uint32_t bar_base = smem_base + p.stages * stage_bytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kWgMaxStages + s); };
@@ -127,9 +132,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
     for (int u = blockIdx.x; u < units; u += gridDim.x) {
       const int tile = u % p.tiles, split = u / p.tiles;
       const int ct = tile % p.c_tiles;
-      const int tap = (tile / p.c_tiles) % p.taps;
-      const int nt = tile / (p.c_tiles * p.taps);
-      const int r = tap / p.ksize, s = tap - r * p.ksize;
+      const int tap0 = ((tile / p.c_tiles) % p.tgroups) * p.tap_group;
+      const int nt = tile / (p.c_tiles * p.tgroups);
       const int kb0 = split * p.kb_per_split;
       const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
       for (int kb = kb0; kb < kb1; ++kb) {
@@ -145,9 +149,13 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
           ptx::mbar_arrive_expect_tx(full_bar(stage), tx_bytes);
           for (int j = 0; j < p.a_boxes; ++j)
             ptx::tma_load_2d(sa + j * kBoxBytes, &tmap_dy, full_bar(stage), nt * 128 + j * 64, m0);
-          for (int j = 0; j < p.b_boxes; ++j)
-            ptx::tma_load_im2col_4d(sa + a_bytes + j * kBoxBytes, &tmap_x, full_bar(stage), ct * p.block_n + j * 64,
-                                    base_w, base_h, img, (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
+          for (int t = 0; t < p.tap_group; ++t) {  // the X boxes of every tap of the group (the dY boxes are shared)
+            const int tap = tap0 + t;
+            const int r = tap / p.ksize, s = tap - r * p.ksize;
+            for (int j = 0; j < p.b_boxes; ++j)
+              ptx::tma_load_im2col_4d(sa + a_bytes + (t * p.b_boxes + j) * kBoxBytes, &tmap_x, full_bar(stage),
+                                      ct * p.block_n + j * 64, base_w, base_h, img, (uint16_t)(s * p.dil), (uint16_t)(r * p.dil));
+          }
         }
         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }
@@ -164,11 +172,12 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
       const int split = u / p.tiles;
       const int kb0 = split * p.kb_per_split;
       const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
-      const int acc = it & 1;
-      const uint32_t acc_phase = (it >> 1) & 1;
+      const int acc = p.nbuf == 2 ? (it & 1) : 0;
+      const uint32_t acc_phase = (p.nbuf == 2 ? (it >> 1) : it) & 1;
       ptx::mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
       ptx::tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * p.block_n;
+      const uint32_t d_tmem = tmem_base + acc * (p.tap_group * p.acc_cols);
+      const uint32_t b_tap_bytes = p.b_boxes * kBoxBytes;
       for (int kb = kb0; kb < kb1; ++kb) {
         ptx::mbar_wait(full_bar(stage), phase);
         ptx::tc_fence_after();
@@ -178,8 +187,11 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
         if (leader) {
 #pragma unroll
           for (int k = 0; k < kWgKBlk / 16; ++k) {
-            // advancing K by 16 pixels = 16 rows of 128 B = 2048 B -> +128 in the (addr >> 4) field
-            ptx::mma_bf16_ss(d_tmem, adesc + 128u * k, bdesc + 128u * k, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            // advancing K by 16 pixels = 16 rows of 128 B = 2048 B -> +128 in the (addr >> 4) field; the taps of the group
+            // go to independent accumulators, so consecutive MMAs do not depend on each other
+            for (int t = 0; t < p.tap_group; ++t)
+              ptx::mma_bf16_ss(d_tmem + t * p.acc_cols, adesc + 128u * k, bdesc + (uint64_t)((t * b_tap_bytes) >> 4) + 128u * k,
+                               idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           ptx::mma_commit(empty_bar(stage));
           if (kb == kb1 - 1) ptx::mma_commit(tfull_bar(acc));
@@ -196,17 +208,19 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
     for (int u = blockIdx.x; u < units; u += gridDim.x, ++it) {
       const int tile = u % p.tiles, split = u / p.tiles;
       const int ct = tile % p.c_tiles;
-      const int tap = (tile / p.c_tiles) % p.taps;
-      const int nt = tile / (p.c_tiles * p.taps);
-      const int acc = it & 1;
-      const uint32_t acc_phase = (it >> 1) & 1;
+      const int tap0 = ((tile / p.c_tiles) % p.tgroups) * p.tap_group;
+      const int nt = tile / (p.c_tiles * p.tgroups);
+      const int acc = p.nbuf == 2 ? (it & 1) : 0;
+      const uint32_t acc_phase = (p.nbuf == 2 ? (it >> 1) : it) & 1;
       const int n = nt * 128 + quad * 32 + lane;
       const bool row_ok = n < p.N_out;
-      const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * p.block_n;
       const int groups = p.mma_n >> 5;  // whole 32-column groups
       const int tail16 = (p.mma_n & 31) ? 1 : 0;
       ptx::mbar_wait(tfull_bar(acc), acc_phase);
       ptx::tc_fence_after();
+      for (int tt = 0; tt < p.tap_group; ++tt) {
+      const int tap = tap0 + tt;
+      const uint32_t t_row = tmem_base + ((uint32_t)(quad * 32) << 16) + acc * (p.tap_group * p.acc_cols) + tt * p.acc_cols;
       float* rowp = p.dw + ((long long)n * p.taps + tap) * p.ldw + ct * p.block_n;
       for (int g = half; g < groups + tail16; g += 2) {
         uint32_t rr[32];
@@ -238,6 +252,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_cons
             }
           }
         }
+      }
       }
       ptx::tc_fence_before();
       __syncwarp();
@@ -325,6 +340,14 @@ int load_entry_points() {
 }
 }  // namespace
 
+// plan-time switch (A/B measurements, parity coverage of both schedules): 0 = one tap per work unit as in round 1
+static int g_wgrad_tap_groups = 1;
+extern "C" int yc_conv_wgrad_set_tap_groups(int on) {
+  const int old = g_wgrad_tap_groups;
+  g_wgrad_tap_groups = on ? 1 : 0;
+  return old;
+}
+
 extern "C" int yc_conv_wgrad_ld(int in_c) { return round_up(in_c, 32); }
 extern "C" size_t yc_conv_wgrad_bytes(int out_c, int in_c, int ksize) {
   return (size_t)out_c * ksize * ksize * yc_conv_wgrad_ld(in_c) * 4;
@@ -360,7 +383,19 @@ extern "C" int yc_conv_wgrad_plan_create(yc_wgrad_plan** out_plan, const yc_conv
   p.mma_n = C < 64 ? round_up(C, 16) : p.block_n;
   p.n_tiles = ceil_div(out_c, 128);
   p.c_tiles = ceil_div(C, p.block_n);
-  p.tiles = p.n_tiles * p.taps * p.c_tiles;
+  // taps per work unit: a whole 3x3 filter or one kernel row share the unit's dY boxes (one third / one ninth of the dY
+  // traffic and of the TMA instructions, and 3 or 9 independent accumulators for the MMA stream to alternate between) as
+  // far as the accumulators fit the 512 TMEM columns — twice (double-buffered against the epilogue) or, failing that, once
+  p.acc_cols = round_up(p.mma_n, 32);
+  p.tap_group = 1;
+  p.nbuf = 2;
+  if (p.taps == 9 && g_wgrad_tap_groups) {
+    if (2 * 9 * p.acc_cols <= 512) p.tap_group = 9;
+    else if (2 * 3 * p.acc_cols <= 512) p.tap_group = 3;
+    else if (3 * p.acc_cols <= 512) { p.tap_group = 3; p.nbuf = 1; }
+  }
+  p.tgroups = p.taps / p.tap_group;
+  p.tiles = p.n_tiles * p.tgroups * p.c_tiles;
   p.kb_total = ceil_div(p.M, kWgKBlk);
   const int sms = sm_count();
   int splits = std::max(1, ceil_div(2 * sms, p.tiles));
@@ -372,12 +407,12 @@ extern "C" int yc_conv_wgrad_plan_create(yc_wgrad_plan** out_plan, const yc_conv
   // never stores (row_ok).  Saves one third of the TMA rows of the small layers, which are TMA-row-rate bound.
   p.a_boxes = out_c > 64 ? 2 : 1;
   p.b_boxes = p.block_n / 64;
-  const uint32_t stage_bytes = (p.a_boxes + p.b_boxes) * kBoxBytes;
+  const uint32_t stage_bytes = (p.a_boxes + p.tap_group * p.b_boxes) * kBoxBytes;
   p.stages = std::min<int>(kWgMaxStages, (227 * 1024 - 1024 - 256) / stage_bytes);
   YC_REQUIRE(p.stages >= 2, "wgrad tile does not fit shared memory");
   pl->smem = (size_t)p.stages * stage_bytes + 1024 + 256;
   uint32_t cols = 32;
-  while (cols < (uint32_t)(2 * p.block_n)) cols <<= 1;
+  while (cols < (uint32_t)(p.nbuf * p.tap_group * p.acc_cols)) cols <<= 1;
   p.tmem_cols = cols;
   p.dw = dw_packed;
   p.ldw = yc_conv_wgrad_ld(C);
@@ -472,6 +507,8 @@ extern "C" int yc_conv_wgrad_plan_info(const yc_wgrad_plan* pl, int what) {
     case 3: return pl->p.tiles;
     case 4: return pl->grid;
     case 5: return pl->p.kb_per_split;
+    case 6: return pl->p.tap_group;
+    case 7: return pl->p.nbuf;
   }
   return -1;
 }

@@ -313,6 +313,7 @@ int run_op(yc_network* net, const Op& op, cudaStream_t st) {
     case 5: return yc_yolo_decode(&op.a, L->dec_dev, op.i0, op.i1, op.f0, op.i2, st);
     case 6: return yc_nchw_to_nhwc(net->graph_input, &op.y, st);
     case 7: return yc_stem_im2col(net->graph_input, net->c, net->h, net->w, op.i0, op.i1, op.i2, &op.y, st);
+    case 8: return yc_stem_conv_direct(net->graph_input, net->batch, net->h, net->w, L->w_packed, L->bias_dev, op.i0, &op.y, st);
   }
   return YC_ERR_ARG;
 }
@@ -441,7 +442,14 @@ extern "C" int yc_network_finalize(yc_network* net) {
     return YC_OK;
   }
   const unsigned plan_flags = ((unsigned)flags >> YC_NET_PLAN_SHIFT) & 0x3fffu;
-  if (stem && Ls[0].n % 8 == 0 && 2 * Ls[0].n <= 256 && Ls[0].out_w % 2 == 0 && Ls[0].fused_into < 0 &&
+  // Opt-in (YC_NET_STEM_DIRECT; measured slower, see yc_b200.h): stem computed straight from the fp32 NCHW input by
+  // yc_stem_conv_direct (no operand in global memory at all): the 3 -> 8..32 channel 3x3 / stride 1 / pad 1 first layer of
+  // the YOLO backbones with folded batchnorm.
+  net->stem_direct = stem && (flags & YC_NET_STEM_DIRECT) && Ls[0].c == 3 && Ls[0].size == 3 && Ls[0].stride == 1 &&
+                     Ls[0].pad == 1 && Ls[0].n % 8 == 0 && Ls[0].n <= 32 && Ls[0].fused_into < 0 &&
+                     (!Ls[0].bn || (flags & YC_NET_FUSE_BN)) && view_of(net, 0).dtype == YC_BF16 &&
+                     (Ls[0].act == YC_MISH || Ls[0].act == YC_LEAKY || Ls[0].act == YC_LINEAR);
+  if (!net->stem_direct && stem && Ls[0].n % 8 == 0 && 2 * Ls[0].n <= 256 && Ls[0].out_w % 2 == 0 && Ls[0].fused_into < 0 &&
       view_of(net, 0).ldc == Ls[0].n && view_of(net, 0).dtype == YC_BF16 && !(flags & YC_NET_NO_STEM_PAIR))
     net->stem_pair = true;
   // ---- pairs of 1x1 convolutions that read the same tensor (the two branches of a CSP block: conv, route back,
@@ -576,7 +584,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
   }
 
   // ---- op list -------------------------------------------------------------------------------------
-  {
+  if (!net->stem_direct) {
     Op op;
     op.layer = -1; op.kind = stem ? 7 : 6;
     op.y = yc_tensor{net->input_nhwc, net->batch, in_h, in_w, in_c, in_ldc, YC_BF16};
@@ -594,6 +602,11 @@ extern "C" int yc_network_finalize(yc_network* net) {
     switch (L.type) {
       case L_CONV: {
         if (L.pair_first >= 0) break;  // computed by layer pair_first's kernel (second output tensor)
+        if (i == 0 && net->stem_direct) {  // input conversion + conv in one kernel, no plan
+          op.kind = 8; op.i0 = L.act; op.y = view_of(net, 0);
+          net->ops.push_back(op);
+          break;
+        }
         yc_conv_desc d{L.size, L.stride, L.pad, L.dilation, L.act, YC_LINEAR};
         if (stem && i == 0) { d.ksize = 1; d.stride = 1; d.pad = 0; }
         yc_tensor x = input_view(i);
@@ -1302,7 +1315,7 @@ extern "C" int yc_network_time_ops(yc_network* net, const float* input_dev, int 
   NET_CUDA(cudaStreamBeginCapture(net->stream, cudaStreamCaptureModeThreadLocal));
   int rc = YC_OK;
   for (size_t k = 0; k < net->ops.size() && !rc; ++k) {
-    const bool conv = net->ops[k].kind == 0;
+    const bool conv = net->ops[k].kind == 0 || net->ops[k].kind == 8;
     if (which == 2 || (which == 0) == conv) {
       rc = run_op(net, net->ops[k], net->stream);
       ++n;

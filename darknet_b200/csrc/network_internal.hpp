@@ -91,7 +91,7 @@ struct NLayer {
 
 struct Op {
   int layer;
-  int kind;  // 0 conv, 1 maxpool, 2 upsample, 3 shortcut, 4 route copy, 5 yolo decode, 6 input convert
+  int kind;  // 0 conv, 1 maxpool, 2 upsample, 3 shortcut, 4 route copy, 5 yolo decode, 6 input convert, 7 stem operand, 8 direct stem conv
   yc_tensor a, b, y;
   int i0 = 0, i1 = 0, i2 = 0, i3 = 0;
   float f0 = 0.f;
@@ -145,6 +145,7 @@ struct yc_network {
   int train_flags = 0;
   bool stem = false;  // layer 0 runs as a 1x1 conv over the 32-column im2col operand built by yc_stem_im2col
   bool stem_pair = false;  // inference: the stem conv runs on pixel pairs (network.cu)
+  bool stem_direct = false;  // inference: layer 0 is computed from the fp32 NCHW input by yc_stem_conv_direct
   void* delta_slab = nullptr;
   size_t delta_slab_bytes = 0;
   float* truth_dev = nullptr;     // [batch][max_boxes*5] (*net->truth_gpu)

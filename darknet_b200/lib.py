@@ -50,11 +50,12 @@ class Detection(C.Structure):
 NET_FUSE_BN, NET_FUSE_SHORTCUT, NET_ELIDE_ROUTE, NET_CUDA_GRAPH, NET_PULL_HEADS, NET_REF_CPU_MAXPOOL = 1, 2, 4, 8, 16, 32
 NET_STEM_IM2COL = 512
 NET_NO_STEM_PAIR, NET_NO_PAIR_S2, NET_NO_PAIR_FUSE, NET_PLAN_SHIFT = 1024, 2048, 4096, 16
+NET_STEM_DIRECT = 16384
 PLAN_NO_HALO, PLAN_FORCE_HALO, PLAN_NO_HALO_PAIR, PLAN_NO_W_RES, PLAN_W_RES_1X1, PLAN_ONE_OUT_BUF, PLAN_COST_V1 = 1, 2, 4, 8, 16, 32, 64
 PLAN_TWO_OUT_BUFS, PLAN_GENERIC_EPI, PLAN_EPI_SETS_V1, PLAN_MISH_NEWTON, PLAN_NO_TILE_PAIR = 128, 256, 512, 1024, 2048
 PLAN_NO_CTA_PAIR, PLAN_CTA_PAIR_ALL = 4096, 8192
 # every plan switch off: the plainest kernel variant of each layer (parity coverage of the non-default paths)
-NET_PLAIN_PLANS = NET_NO_STEM_PAIR | NET_NO_PAIR_S2 | NET_NO_PAIR_FUSE | ((PLAN_NO_HALO | PLAN_NO_W_RES | PLAN_ONE_OUT_BUF | PLAN_GENERIC_EPI | PLAN_NO_TILE_PAIR) << NET_PLAN_SHIFT)
+NET_PLAIN_PLANS = NET_NO_STEM_PAIR | NET_NO_PAIR_S2 | NET_NO_PAIR_FUSE | ((PLAN_NO_HALO | PLAN_NO_W_RES | PLAN_ONE_OUT_BUF | PLAN_GENERIC_EPI | PLAN_NO_TILE_PAIR | PLAN_NO_CTA_PAIR) << NET_PLAN_SHIFT)
 NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
 NET_TRAIN, NET_DGRAD_ACCUMULATE, NET_BN_BIAS_GRAD, NET_TRAIN_REF_CPU = 64, 128, 256, 8192
 
@@ -82,6 +83,7 @@ _SIGS = {
     "yc_nchw_to_nhwc": (C.c_int, [_P, _TP, _P]),
     "yc_nhwc_to_nchw": (C.c_int, [_TP, _P, _P]),
     "yc_stem_im2col": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _TP, _P]),
+    "yc_stem_conv_direct": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, _TP, _P]),
     "yc_conv_padded_in_c": (C.c_int, [C.c_int]),
     "yc_conv_packed_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "yc_conv_pack": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
@@ -111,6 +113,7 @@ _SIGS = {
     "yc_conv_wgrad_plan_destroy": (C.c_int, [_P]),
     "yc_conv_wgrad": (C.c_int, [_P, _P]),
     "yc_conv_wgrad_plan_info": (C.c_int, [_P, C.c_int]),
+    "yc_conv_wgrad_set_tap_groups": (C.c_int, [C.c_int]),
     "yc_conv_wgrad_unpack": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
     "yc_conv_wgrad_pack": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),
     "yc_maxpool_fwd_train": (C.c_int, [_TP, _TP, _P, C.c_int, C.c_int, C.c_int, _P]),

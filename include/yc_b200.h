@@ -84,6 +84,14 @@ YC_API int yc_nchw_to_nhwc(const float* src, const yc_tensor* dst, void* stream)
  * convolution over 32 channels; replaces im2col_ongpu (im2col_kernels.cu) for that layer. */
 YC_API int yc_stem_im2col(const float* src, int c, int h, int w, int size, int stride, int pad, const yc_tensor* dst,
                           void* stream);
+/* The first convolution computed straight from the fp32 NCHW network input: 3 channels -> y->c (8, 16, 24 or 32)
+ * channels, 3x3 / stride 1 / pad 1, + bias + activation (mish / leaky / linear) -> NHWC bf16 view y, in one kernel that
+ * keeps no operand in global memory.  Replaces, for layer 0, the input layout step (network_kernels.cu:513),
+ * im2col_gpu_ext + gemm (convolutional_kernels.cu:252-553, im2col_kernels.cu) and add_bias / activate_array.
+ * w_packed: bf16 [out_c][32], column (kh*3+kw)*3 + ci (= yc_conv_pack of the filter re-ordered to [n][32][1][1]);
+ * inputs are rounded to bf16 like every other layer's, accumulation is fp32. */
+YC_API int yc_stem_conv_direct(const float* x_nchw, int batch, int h, int w, const void* w_packed, const float* bias,
+                               int activation, const yc_tensor* y, void* stream);
 /* Mat2Image on the device (visualize.cpp:26-54): u8 HWC [n][h][w][c] -> fp32 NCHW, value/255.0f; swap_rb reads
  * channel c-1-k (the cvtColor(RGB2BGR) of yolo_core.cpp:110). */
 YC_API int yc_u8hwc_to_nchw(const unsigned char* src, int n, int c, int h, int w, int swap_rb, float* dst, void* stream);
@@ -225,6 +233,10 @@ YC_API int yc_conv_wgrad_plan_destroy(yc_wgrad_plan* plan);
 YC_API int yc_conv_wgrad(const yc_wgrad_plan* plan, void* stream);
 /* what=0 block_n, 1 K splits, 2 stages, 3 tiles, 4 grid, 5 K blocks per split */
 YC_API int yc_conv_wgrad_plan_info(const yc_wgrad_plan* plan, int what);
+/* Plan-time switch for the plans created afterwards (A/B measurements; parity coverage of both schedules): 1 (default) = a
+ * 3x3 layer's work units cover a kernel row or the whole filter and share the dY boxes, 0 = one tap per unit.  Returns
+ * the previous setting.  yc_conv_wgrad_plan_info(plan, 6) = taps per unit, (plan, 7) = accumulator sets in TMEM. */
+YC_API int yc_conv_wgrad_set_tap_groups(int on);
 /* packed fp32 gradient <-> the reference's OIHW weight_updates layout */
 YC_API int yc_conv_wgrad_unpack(const float* dw_packed, int out_c, int in_c, int ksize, float* dw_oihw, void* stream);
 YC_API int yc_conv_wgrad_pack(const float* dw_oihw, int out_c, int in_c, int ksize, float* dw_packed, void* stream);
@@ -359,6 +371,10 @@ enum {
   YC_NET_NO_STEM_PAIR = 1024, /* stem conv on single pixels instead of pixel pairs (A/B + parity coverage) */
   YC_NET_NO_PAIR_S2 = 2048,  /* 3x3 stride-2 32-channel layer on the plain im2col path instead of the pixel-pair view */
   YC_NET_NO_PAIR_FUSE = 4096, /* do not merge two 1x1 convs that read the same tensor into one GEMM */
+  YC_NET_STEM_DIRECT = 16384, /* opt-in: compute the 3->32 3x3 stem straight from the fp32 input with yc_stem_conv_direct
+                                instead of the im2col-operand + 1x1 path.  Measured SLOWER on B200 (1.32 ms against 0.53 +
+                                0.32 ms per yolov4-608 x 64 step: the legacy mma.sync rate of sm_100 bounds it), kept as a
+                                tested alternative. */
   YC_NET_PLAN_SHIFT = 16,    /* bits [16,30): YC_PLAN_* switches handed to every conv plan */
   YC_NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
 };

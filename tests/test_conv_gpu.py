@@ -133,6 +133,41 @@ def test_conv_plan_switches(gpu):
     _run(gpu, 8, 512, 19, 19, 512, 3, 1, "leaky")
 
 
+@pytest.mark.parametrize("B,H,W,N,act", [(2, 40, 72, 32, "mish"), (1, 16, 32, 32, "leaky"), (3, 19, 33, 16, "linear"),
+                                         (2, 64, 64, 24, "mish"), (1, 5, 7, 8, "leaky")])
+def test_stem_conv_direct(gpu, B, H, W, N, act):
+    """yc_stem_conv_direct (3 -> N channels, 3x3 / stride 1 / pad 1 straight from the fp32 NCHW image; mma.sync with register
+    A fragments, no operand in global memory) against the oracle conv on the same bf16-rounded inputs; ragged sizes cover
+    partial tiles in both directions, N < 32 the channel guard, and a wider pixel pitch the concat placement."""
+    from darknet_b200 import lib as L, ops
+    lib = L.lib()
+    rng = np.random.default_rng(B * 100 + H)
+    x = _bf16_round(rng.standard_normal((B, 3, H, W)).astype(np.float32))
+    w = _bf16_round((rng.standard_normal((N, 3, 3, 3)) * np.sqrt(2.0 / 27)).astype(np.float32))
+    b = rng.uniform(-0.5, 0.5, N).astype(np.float32)
+    ref = O.conv_forward(x, w, b, 3, 1, 1, act)
+    # filter in the stem order: [n][32], column (kh*3+kw)*3 + ci
+    w2 = np.zeros((N, 32), np.float32)
+    for ci in range(3):
+        for t in range(9):
+            w2[:, t * 3 + ci] = w[:, ci, t // 3, t % 3]
+    wd = torch.from_numpy(w2).to(gpu)
+    packed = torch.zeros(N * 32, dtype=torch.bfloat16, device=gpu)
+    L.check(lib.yc_conv_pack(wd.data_ptr(), N, 32, 1, packed.data_ptr(), L.stream_ptr()), "yc_conv_pack")
+    xd = torch.from_numpy(x).to(gpu)
+    bd = torch.from_numpy(b).to(gpu)
+    ldy = 40 if N == 24 else N        # N == 24: the output is a channel slice of a wider buffer
+    y = torch.full((B, H, W, ldy), 3.0, dtype=torch.bfloat16, device=gpu)
+    L.check(lib.yc_stem_conv_direct(xd.data_ptr(), B, H, W, packed.data_ptr(), bd.data_ptr(), L.ACT[act],
+                                    L.view(y, B, H, W, N, ldy), L.stream_ptr()), "yc_stem_conv_direct")
+    torch.cuda.synchronize()
+    got = y[..., :N].float().permute(0, 3, 1, 2).cpu().numpy()
+    err = np.abs(got - ref).max() / (np.abs(ref).max() + 1e-12)
+    assert err < 1e-2, f"rel-to-max err {err:.3e}"
+    if ldy > N:
+        assert float((y[..., N:].float() - 3.0).abs().max()) == 0.0, "wrote outside its channel slice"
+
+
 def test_conv_cta_pairs(gpu):
     """conv_fprop_pair_kernel (tcgen05 cta_group::2: 256-row tiles over a cluster of two CTAs, each staging its own A rows
     and half of the weight rows): the default rule (256-wide tiles, specialised epilogue) and, forced, every operand shape it
@@ -157,7 +192,8 @@ def test_conv_cta_pairs(gpu):
     FH = L.PLAN_FORCE_HALO
     _run(gpu, 4, 128, 76, 76, 128, 3, 1, "mish", want_variant=(512 | 3 | 4, 512 | 2 | 4))
     _run(gpu, 4, 128, 76, 76, 128, 3, 1, "mish", residual=True, plan_flags=L.PLAN_NO_CTA_PAIR, want_variant=(512 | 3, 2))
-    _run(gpu, 4, 64, 38, 38, 64, 3, 1, "mish", residual=True, plan_flags=PA | FH, want_variant=(512 | 3 | 8, 512 | 2 | 8))
+    _run(gpu, 4, 64, 38, 38, 64, 3, 1, "mish", residual=True, plan_flags=PA | FH, want_variant=(512 | 3, 512 | 2))
+    _run(gpu, 64, 64, 38, 38, 64, 3, 1, "mish", residual=True, plan_flags=PA | FH, want_variant=(512 | 3 | 8, 512 | 2 | 8))  # one N tile: resident weights
     _run(gpu, 3, 64, 38, 22, 64, 3, 1, "leaky", residual=True, plan_flags=PA | FH, want_variant=(512 | 3, 512 | 2))
     _run(gpu, 32, 64, 38, 38, 64, 3, 1, "linear", plan_flags=PA | FH, want_variant=(512 | 3, 512 | 2))  # 480 blocks on 74 pairs
     _run(gpu, 4, 32, 38, 38, 64, 3, 1, "mish", plan_flags=PA | FH, want_variant=(512 | 3, 512 | 2))

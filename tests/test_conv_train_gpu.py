@@ -141,3 +141,20 @@ def test_train_accumulate_semantics(gpu):
 def test_train_many_pixels_split_k(gpu):
     _case(gpu, 8, 64, 52, 52, 64, 3, 1, "leaky")
     _case(gpu, 4, 128, 38, 38, 256, 3, 1, "leaky")
+
+
+def test_wgrad_tap_groups_and_single_tap_units(gpu):
+    """wgrad work units: a 3x3 layer's unit covers a kernel row (or the whole filter) and shares the dY boxes, with one
+    TMEM accumulator per tap; yc_conv_wgrad_set_tap_groups(0) plans one tap per unit as in round 1.  Both schedules on the
+    channel counts that select each variant: C = 32 / 64 (row groups, double-buffered), 128 (row groups, one accumulator
+    set), 256 (always one tap per unit)."""
+    from darknet_b200 import lib as L
+    lib = L.lib()
+    cases = [(2, 32, 16, 16, 64), (4, 64, 26, 26, 64), (2, 128, 13, 13, 128), (2, 256, 8, 8, 256)]
+    try:
+        for on in (1, 0):
+            lib.yc_conv_wgrad_set_tap_groups(on)
+            for (B, C, H, W, N) in cases:
+                _case(gpu, B, C, H, W, N, 3, 1, "leaky", seed=on)
+    finally:
+        lib.yc_conv_wgrad_set_tap_groups(1)

@@ -164,8 +164,10 @@ def test_yolov4_608_all_layers_default_plan(gpu):
 
     def want(net, variants):
         # the plan bench.py times: stem on pixel pairs, stride-2 pixel-pair layer, halo patches with tile pairs and resident
-        # weights, the five CSP 1x1 pairs fused, 23 shortcuts fused, two staging buffers
+        # weights, CTA pairs (tiled / im2col and halo), the five CSP 1x1 pairs fused, 23 shortcuts fused, specialised epilogue
         assert net.layer_info(0, 13) & 3 == 0 and net.layer_info(1, 13) & 64, "stem / pair-s2 variants not selected"
+        assert any(v >= 0 and v & 512 and v & 3 != 2 for v in variants) and any(v >= 0 and v & 512 and v & 3 == 2 for v in variants), \
+            "no CTA-pair layer (im2col and halo)"
         assert sum(1 for i in range(net.n) if net.layer_info(i, 14) >= 0) == 5, "the five CSP pairs are not fused"
         assert any(v & 3 == 2 and v & 4 for v in variants), "no halo tile-pair layer"
         assert all(v & 128 for i in range(net.n) if net.layer_info(i, 0) == 0 and net.layer_info(i, 14) < 0

@@ -35,6 +35,7 @@ def main():
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--act", default=None)
+    ap.add_argument("--warmup", type=int, default=3, help="untimed launches per shape (0 under ncu: one launch per shape)")
     a = ap.parse_args()
     L.check(L.lib().yc_set_device(0), "set_device")
     dev = torch.device("cuda:0")
@@ -51,7 +52,7 @@ def main():
         conv = ops.Conv(x, (B, HW, HW, C), w, b, k, s, k // 2, act,
                         out_dtype=torch.float32 if N == 255 else torch.bfloat16)
         n, ho, wo, _ = conv.out_shape
-        for _ in range(3):
+        for _ in range(a.warmup):
             conv()
         ts = []
         for _ in range(a.iters):
