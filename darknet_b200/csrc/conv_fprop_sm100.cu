@@ -756,6 +756,11 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   ptx::tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  // Programmatic dependent launch (plans with YC_PLAN_PDL): everything above — barrier init, TMEM allocation, tensor-map
+  // prefetch, the bias copy (plan-owned, constant) — ran while the previous layer's last CTAs were still finishing on
+  // other SMs; from here on this kernel reads what that layer wrote.  The next layer may be scheduled from now on.
+  ptx::pdl_wait();
+  ptx::pdl_launch_dependents();
 
   const int total_tiles = p.m_tiles * p.n_tiles;
   const int k_blocks = p.taps * p.cchunks;
@@ -1138,6 +1143,8 @@ conv_fprop_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
   ptx::tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  ptx::pdl_wait();               // (see conv_fprop_kernel_t)
+  ptx::pdl_launch_dependents();
 
   const int total_tiles = p.m_tiles * p.n_tiles;  // 256-row tiles x N tiles
   const int k_blocks = p.taps * p.cchunks;
@@ -1430,6 +1437,7 @@ struct yc_conv_plan {
   unsigned* stat_ticket = nullptr;
   int grid = 0;
   size_t smem = 0;
+  bool pdl = false;                // launch with programmatic stream serialization (YC_PLAN_PDL)
   const void* w_packed = nullptr;  // for re-encoding the weight map when a CTA-pair plan falls back (yc_conv_plan_set_stats)
   int w_kdim = 0;                  // taps * padded in_c
 };
@@ -1850,6 +1858,7 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
     }
   }
   pl->rect = rect;
+  pl->pdl = (flags & YC_PLAN_PDL) != 0;
 
   p.m_tiles128 = p.m_tiles;
   if (p.cta_pair) {  // 256-row tiles, one cluster of two CTAs per tile at a time
@@ -1936,6 +1945,7 @@ extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq
   YC_REQUIRE(pl && ((sum && sumsq) || (!sum && !sumsq)), "yc_conv_plan_set_stats: bad arguments");
   ConvParams& p = pl->p;
   YC_REQUIRE(!sum || p.act == YC_LINEAR, "yc_conv_plan_set_stats: statistics are taken on the linear (pre-batchnorm) output");
+  pl->pdl = false;
   p.fast_epi = 0;                       // statistics are reduced by the generic epilogue
   p.bias_cols = 0;
   p.tile_pair = 0;
@@ -2012,7 +2022,26 @@ extern "C" int yc_conv_fprop(const yc_conv_plan* pl, void* stream) {
   YC_REQUIRE(pl, "yc_conv_fprop: null plan");
   if (pl->p.stat_sum)
     conv_fprop_kernel_t<true><<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->tmap_y2, pl->p);
-  else if (pl->p.cta_pair)  // cluster of two CTAs per 256-row tile (static __cluster_dims__)
+  else if (pl->pdl) {
+    // programmatic dependent launch: this kernel's set-up overlaps the tail of the kernel before it in the stream
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)pl->grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = pl->smem;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    cudaError_t e = pl->p.cta_pair
+        ? cudaLaunchKernelEx(&cfg, conv_fprop_pair_kernel, pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->tmap_y2, pl->p)
+        : cudaLaunchKernelEx(&cfg, conv_fprop_kernel_t<false>, pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->tmap_y2, pl->p);
+    if (e != cudaSuccess) {
+      set_error("yc_conv_fprop: cudaLaunchKernelEx -> %s", cudaGetErrorString(e));
+      return YC_ERR_CUDA;
+    }
+  } else if (pl->p.cta_pair)  // cluster of two CTAs per 256-row tile (static __cluster_dims__)
     conv_fprop_pair_kernel<<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->tmap_y2, pl->p);
   else
     conv_fprop_kernel_t<false><<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->tmap_y2, pl->p);
@@ -2030,10 +2059,10 @@ extern "C" int yc_conv_plan_info(const yc_conv_plan* pl, int what) {
     case 4: return pl->grid;
     case 5: return pl->p.a_mode;
     case 6: return (int)pl->smem;
-    case 7:  // kernel variant: [0,2) a_mode, 4 halo tile pairs, 8 resident weights, 16 two outputs, 32 two staging buffers, 64 rectangular, 128 fast epilogue, 256 tile pairs, 512 CTA pairs
+    case 7:  // kernel variant: [0,2) a_mode, 4 halo tile pairs, 8 resident weights, 16 two outputs, 32 two staging buffers, 64 rectangular, 128 fast epilogue, 256 tile pairs, 512 CTA pairs, 1024 programmatic dependent launch
       return pl->p.a_mode | (pl->p.halo_pair ? 4 : 0) | (pl->p.w_resident ? 8 : 0) | (pl->p.split_col ? 16 : 0) |
              (pl->p.out_bufs == 2 ? 32 : 0) | (pl->rect ? 64 : 0) | (pl->p.fast_epi ? 128 : 0) | (pl->p.tile_pair ? 256 : 0) |
-             (pl->p.cta_pair ? 512 : 0);
+             (pl->p.cta_pair ? 512 : 0) | (pl->pdl ? 1024 : 0);
     case 8: return pl->p.epi_sets;
   }
   return -1;

@@ -441,7 +441,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
     net->finalized = true;
     return YC_OK;
   }
-  const unsigned plan_flags = ((unsigned)flags >> YC_NET_PLAN_SHIFT) & 0x3fffu;
+  const unsigned plan_flags = (((unsigned)flags >> YC_NET_PLAN_SHIFT) & 0x7fffu) | ((flags & YC_NET_PDL) ? (unsigned)YC_PLAN_PDL : 0u);
   // Opt-in (YC_NET_STEM_DIRECT; measured slower, see yc_b200.h): stem computed straight from the fp32 NCHW input by
   // yc_stem_conv_direct (no operand in global memory at all): the 3 -> 8..32 channel 3x3 / stride 1 / pad 1 first layer of
   // the YOLO backbones with folded batchnorm.

@@ -266,6 +266,13 @@ __device__ __forceinline__ void mma_commit_pair(uint32_t bar, uint16_t cta_mask)
                : "memory");
 }
 
+// ---- programmatic dependent launch -------------------------------------------------------------------------------
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start while its predecessor in the stream
+// still runs; griddepcontrol.wait blocks until every prerequisite grid has completed and its memory is visible (a no-op
+// in a normally launched kernel).  launch_dependents lets the NEXT kernel's CTAs be scheduled as soon as SMs free up.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---- UMMA descriptors ----------------------------------------------------------------------------
 // Shared-memory matrix descriptor for a K-major operand tile stored as rows of `row_bytes`
 // (= the swizzle span: 128 / 64 / 32 B), 8-row groups `8*row_bytes` apart (what TMA writes with

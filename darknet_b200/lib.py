@@ -50,10 +50,10 @@ class Detection(C.Structure):
 NET_FUSE_BN, NET_FUSE_SHORTCUT, NET_ELIDE_ROUTE, NET_CUDA_GRAPH, NET_PULL_HEADS, NET_REF_CPU_MAXPOOL = 1, 2, 4, 8, 16, 32
 NET_STEM_IM2COL = 512
 NET_NO_STEM_PAIR, NET_NO_PAIR_S2, NET_NO_PAIR_FUSE, NET_PLAN_SHIFT = 1024, 2048, 4096, 16
-NET_STEM_DIRECT = 16384
+NET_STEM_DIRECT, NET_PDL = 16384, 32768
 PLAN_NO_HALO, PLAN_FORCE_HALO, PLAN_NO_HALO_PAIR, PLAN_NO_W_RES, PLAN_W_RES_1X1, PLAN_ONE_OUT_BUF, PLAN_COST_V1 = 1, 2, 4, 8, 16, 32, 64
 PLAN_TWO_OUT_BUFS, PLAN_GENERIC_EPI, PLAN_EPI_SETS_V1, PLAN_MISH_NEWTON, PLAN_NO_TILE_PAIR = 128, 256, 512, 1024, 2048
-PLAN_NO_CTA_PAIR, PLAN_CTA_PAIR_ALL = 4096, 8192
+PLAN_NO_CTA_PAIR, PLAN_CTA_PAIR_ALL, PLAN_PDL = 4096, 8192, 16384
 # every plan switch off: the plainest kernel variant of each layer (parity coverage of the non-default paths)
 NET_PLAIN_PLANS = NET_NO_STEM_PAIR | NET_NO_PAIR_S2 | NET_NO_PAIR_FUSE | ((PLAN_NO_HALO | PLAN_NO_W_RES | PLAN_ONE_OUT_BUF | PLAN_GENERIC_EPI | PLAN_NO_TILE_PAIR | PLAN_NO_CTA_PAIR) << NET_PLAN_SHIFT)
 NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512

@@ -140,7 +140,11 @@ enum {
   YC_PLAN_NO_TILE_PAIR = 2048, /* tiled / im2col path: one tile at a time instead of tile pairs (two accumulators) */
   YC_PLAN_MISH_NEWTON = 1024, /* specialised epilogue: mish with one MUFU + a Newton reciprocal on the FMA pipe (measured slower) */
   YC_PLAN_NO_CTA_PAIR = 4096, /* never run a layer on CTA pairs (tcgen05 cta_group::2, 256-row tiles over a cluster of two) */
-  YC_PLAN_CTA_PAIR_ALL = 8192 /* CTA pairs wherever legal (tiled / im2col operands, specialised epilogue), not only for 256-wide tiles */
+  YC_PLAN_CTA_PAIR_ALL = 8192, /* CTA pairs wherever legal (tiled / im2col operands, specialised epilogue), not only for 256-wide tiles */
+  YC_PLAN_PDL = 16384        /* launch with programmatic stream serialization: the kernel's set-up (barriers, TMEM, tensor-map
+                                prefetch) overlaps the tail of the kernel before it in the stream; it waits
+                                (griddepcontrol.wait) before touching anything that kernel wrote.  yc_network_load sets it
+                                for inference plans under YC_NET_PDL (opt-in: no measured gain). */
 };
 /* [setup] yc_conv_plan_create with plan switches and, optionally, a SECOND output tensor y2: the GEMM then has
  * y->c + y2->c output channels (weights / bias / scale of both layers concatenated along out_c, y->c a multiple of
@@ -375,7 +379,11 @@ enum {
                                 instead of the im2col-operand + 1x1 path.  Measured SLOWER on B200 (1.32 ms against 0.53 +
                                 0.32 ms per yolov4-608 x 64 step: the legacy mma.sync rate of sm_100 bounds it), kept as a
                                 tested alternative. */
-  YC_NET_PLAN_SHIFT = 16,    /* bits [16,30): YC_PLAN_* switches handed to every conv plan */
+  YC_NET_PDL = 32768,        /* opt-in: programmatic dependent launches for the inference conv kernels (YC_PLAN_PDL).  Measured
+                                twice (round 1, round 2 with the CTA-pair build: 11.21 / 11.40 ms against 11.38 / 11.39 ms per
+                                yolov4-608 x 64 step, i.e. noise): the next kernel's CTA cannot become resident next to a
+                                226 KB one, and what it could overlap — its own set-up — is not what the short layers pay for */
+  YC_NET_PLAN_SHIFT = 16,    /* bits [16,31): YC_PLAN_* switches handed to every conv plan */
   YC_NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
 };
 

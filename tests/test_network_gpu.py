@@ -35,7 +35,7 @@ def _compare_layers(net, outs, tol_l2, tol_max, skip_fused=True):
     return worst
 
 
-@pytest.mark.parametrize("flags_extra", [0, "nofuse_shortcut", "no_elide", "no_graph", "stem_direct"])
+@pytest.mark.parametrize("flags_extra", [0, "nofuse_shortcut", "no_elide", "no_graph", "stem_direct", "pdl"])
 def test_micro_net_all_layers(gpu, flags_extra):
     from darknet_b200 import lib as L, network as N
     text, cpath, wpath = materialise("micro")
@@ -48,6 +48,8 @@ def test_micro_net_all_layers(gpu, flags_extra):
         flags &= ~L.NET_ELIDE_ROUTE
     elif flags_extra == "no_graph":
         flags &= ~L.NET_CUDA_GRAPH
+    elif flags_extra == "pdl":          # opt-in: programmatic dependent launches inside the captured graph
+        flags |= L.NET_PDL
     elif flags_extra == "stem_direct":  # opt-in: layer 0 straight from the fp32 input (yc_stem_conv_direct), no plan
         flags |= L.NET_STEM_DIRECT
     net = N.LoadNetwork(cpath, wpath, batch=1, flags=flags)
