@@ -276,7 +276,9 @@ template <int MODE, int ACT>
 __global__ void __launch_bounds__(256, YC_BN_MINB) bwd_reduce_kernel(TView dy, TView z, const float* __restrict__ mean, const float* __restrict__ var,
                                   const float* __restrict__ gamma, const float* __restrict__ beta,
                                   float* __restrict__ S1, float* __restrict__ S2, float* __restrict__ P,
-                                  unsigned* __restrict__ ticket) {
+                                  unsigned* __restrict__ ticket, float* __restrict__ scale_updates = nullptr,
+                                  float* __restrict__ bias_updates = nullptr, float* __restrict__ coef = nullptr,
+                                  float m_rows = 0.f) {
   constexpr int act = ACT;
   // Reproducible sums (no float atomics): thread sums -> one shared-memory entry per (warp | row slot, channel) -> the
   // block's partial = entries added in index order -> P[block][2][C8] -> the block that draws the last ticket adds the
@@ -409,6 +411,16 @@ __global__ void __launch_bounds__(256, YC_BN_MINB) bwd_reduce_kernel(TView dy, T
       if (MODE == 0) {
         S1[i] = s1;
         S2[i] = s2;
+        if (coef) {  // the per-channel coefficients right here (what bn_bwd_coef_kernel computes: one launch less per layer)
+          const float v = var[i], ga = gamma[i];
+          if (scale_updates) scale_updates[i] += s2 / sqrtf(v + .000001f);
+          if (bias_updates) bias_updates[i] += s1;
+          const double md = (double)(ga * s1) * (-1. / sqrt((double)(v + .00001f)));
+          const double vd = (double)(ga * s2) * (-.5 * pow((double)(v + .00001f), (double)(float)(-3. / 2.)));
+          coef[i] = (float)((double)ga / (sqrt((double)v) + .00001));
+          coef[dy.c + i] = (float)(vd * 2. / m_rows);
+          coef[2 * dy.c + i] = (float)(md / m_rows);
+        }
       } else {
         S1[i] += s1;
       }
@@ -640,10 +652,10 @@ extern "C" int yc_bn_bwd(const yc_tensor* dy, const yc_tensor* z, const float* m
   const int threads = reduce_threads(groups);
   const int slots = threads / groups;
   const int grid = row_grid(dv.rows, slots, 2);
-  YC_ACT_DISPATCH(activation, (bwd_reduce_kernel<0, A><<<grid, threads, reduce_smem(groups, threads), st>>>(dv, zv, mean, var, gamma,
-                                                                                                            beta, S1, S2, P, ticket)));
-  YC_LAUNCH_CHECK();
-  bn_bwd_coef_kernel<<<ceil_div(n, 128), 128, 0, st>>>(S1, S2, var, gamma, (float)dv.rows, scale_updates, bias_updates, coef, n);
+  // (the block that draws the last ticket also turns the two sums into the coefficients of the apply pass and adds the
+  // scale / bias gradients: bn_bwd_coef_kernel's arithmetic, without its launch)
+  YC_ACT_DISPATCH(activation, (bwd_reduce_kernel<0, A><<<grid, threads, reduce_smem(groups, threads), st>>>(
+                                  dv, zv, mean, var, gamma, beta, S1, S2, P, ticket, scale_updates, bias_updates, coef, (float)dv.rows)));
   YC_LAUNCH_CHECK();
   ov.c = dy->c;
   const int agroups = (dz->ldc >= (long long)groups * 8) ? dz->ldc / 8 : groups;

@@ -65,6 +65,10 @@ struct ConvParams {
   int stat_regions;    // 4 * epi_sets
   float* stat_partial;
   unsigned* stat_ticket;
+  // optional (yc_conv_plan_set_bn_finalize): the CTA that adds the partials also turns the sums into batch mean / unbiased
+  // variance and updates the rolling averages — yc_bn_finalize's arithmetic without its launch
+  float* bn_mean; float* bn_var; float* bn_rmean; float* bn_rvar;
+  float bn_count;
   int out_bufs;        // epilogue staging buffers per warp (1 or 2): with 2 a warp stages block k+1 while the TMA
                        // engine still reads block k
   int split_col;       // > 0: output columns >= split_col go to a second tensor (tmap_y2) at column - split_col: two
@@ -1058,6 +1062,15 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
         p.stat_sum[i] = a;
         p.stat_sq[i] = q;
+        if (p.bn_mean) {  // forward_batchnorm_layer (batchnorm_layer.cpp:186-205): mean, unbiased variance, rolling averages
+          const float m = a / p.bn_count;
+          float v = (q - p.bn_count * m * m) / (p.bn_count - 1.f);
+          v = fmaxf(v, 0.f);
+          p.bn_mean[i] = m;
+          p.bn_var[i] = v;
+          if (p.bn_rmean) p.bn_rmean[i] = .9f * p.bn_rmean[i] + .1f * m;
+          if (p.bn_rvar) p.bn_rvar[i] = .9f * p.bn_rvar[i] + .1f * v;
+        }
       }
       if (threadIdx.x == 0) *p.stat_ticket = 0u;  // ready for the next launch
     }
@@ -1997,6 +2010,17 @@ extern "C" int yc_conv_plan_set_stats(yc_conv_plan* pl, float* sum, float* sumsq
   p.stat_ticket = pl->stat_ticket;
   p.stat_sum = sum;
   p.stat_sq = sumsq;
+  return YC_OK;
+}
+
+// Fold yc_bn_finalize into a statistics plan's kernel: its last CTA writes mean / var (and updates the rolling averages,
+// either may be NULL) from the sums it has just formed.  count = pixels per channel (batch * out_h * out_w).
+extern "C" int yc_conv_plan_set_bn_finalize(yc_conv_plan* pl, long long count, float* mean, float* var, float* rolling_mean,
+                                            float* rolling_var) {
+  YC_REQUIRE(pl && pl->p.stat_sum && mean && var && count > 1,
+             "yc_conv_plan_set_bn_finalize: needs a plan with statistics (yc_conv_plan_set_stats) and mean / var buffers");
+  pl->p.bn_mean = mean; pl->p.bn_var = var; pl->p.bn_rmean = rolling_mean; pl->p.bn_rvar = rolling_var;
+  pl->p.bn_count = (float)count;
   return YC_OK;
 }
 

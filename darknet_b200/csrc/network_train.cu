@@ -166,6 +166,8 @@ int yc_train_finalize(yc_network* net) {
           const yc_tensor z = z_view(net, i);
           rc = yc_conv_plan_create(&L.plan, &d, &x, L.w_packed, nullptr, nullptr, nullptr, &z);
           if (!rc) rc = yc_conv_plan_set_stats(L.plan, L.stats_dev, L.stats_dev + L.n);
+          // mean / variance / rolling averages come out of the same kernel (its last CTA): no yc_bn_finalize launch
+          if (!rc) rc = yc_conv_plan_set_bn_finalize(L.plan, (long long)B * L.out_h * L.out_w, L.mean_dev, L.var_dev, L.rmean_dev, L.rvar_dev);
         } else {
           rc = yc_conv_plan_create(&L.plan, &d, &x, L.w_packed, L.bias_dev, nullptr, nullptr, &y);
         }
@@ -266,13 +268,10 @@ int train_forward(yc_network* net, const float* input_dev, const float* truth_de
     int rc = YC_OK;
     switch (L.type) {
       case L_CONV: {
-        if (L.bn) NET_CUDA(cudaMemsetAsync(L.stats_dev, 0, sizeof(float) * 2 * L.n, st));
-        tick(CAT_OTHER, st);
+        // (the statistics kernel OVERWRITES sum / sum of squares from its ordered partials: no memset per layer)
         rc = yc_conv_fprop(L.plan, st);
         tick(CAT_FPROP, st);
         if (!rc && L.bn) {
-          rc = yc_bn_finalize(L.stats_dev, L.stats_dev + L.n, (long long)B * L.out_h * L.out_w, L.mean_dev, L.var_dev,
-                              L.rmean_dev, L.rvar_dev, L.n, st);
           const yc_tensor z = z_view(net, i), y = view_of(net, i);
           if (!rc) rc = yc_bn_act_fwd(&z, L.mean_dev, L.var_dev, L.scale_dev, L.bias_dev, L.act, &y, st);
           tick(CAT_BN, st);

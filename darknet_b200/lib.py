@@ -94,6 +94,7 @@ _SIGS = {
     "yc_conv_plan_info": (C.c_int, [_P, C.c_int]),
     "yc_conv_plan_set_stats": (C.c_int, [_P, _P, _P]),
     "yc_conv_plan_set_bias": (C.c_int, [_P, _P, _P]),
+    "yc_conv_plan_set_bn_finalize": (C.c_int, [_P, C.c_longlong, _P, _P, _P, _P]),
     "yc_bn_finalize": (C.c_int, [_P, _P, C.c_longlong, _P, _P, _P, _P, C.c_int, _P]),
     "yc_bn_act_fwd": (C.c_int, [_TP, _P, _P, _P, _P, C.c_int, _TP, _P]),
     "yc_bn_bwd": (C.c_int, [_TP, _TP, _P, _P, _P, _P, C.c_int, _P, _P, _P, _TP, _P]),

@@ -175,6 +175,10 @@ YC_API int yc_conv_plan_info(const yc_conv_plan* plan, int what);
  *   mean, var, rolling update            yc_bn_finalize (unbiased variance, rolling = .9 roll + .1 batch)
  *   y = act(gamma*(z-mean)/sqrt(var+1e-6)+beta)   yc_bn_act_fwd */
 YC_API int yc_conv_plan_set_stats(yc_conv_plan* plan, float* sum, float* sumsq);
+/* Optional: fold yc_bn_finalize into the statistics plan's kernel (the CTA that adds the per-CTA partials also writes
+ * mean / var and updates the rolling averages; same arithmetic, one launch less per layer).  count = batch*out_h*out_w. */
+YC_API int yc_conv_plan_set_bn_finalize(yc_conv_plan* plan, long long count, float* mean, float* var, float* rolling_mean,
+                                        float* rolling_var);
 /* A plan keeps a padded copy of the bias it was created with; after the bias changes (update_convolutional_layer on a
  * layer without batchnorm: the YOLO heads, convolutional_layer.cpp:1382-1401 axpy on l.biases) hand it the new values.
  * Asynchronous on `stream`. */
