@@ -273,8 +273,11 @@ def run_train(args):
     truth = cfgmod.synth_truth(B, 90, classes=80, seed=4321 + rank)
     info_mib = L.lib().yc_network_train_info(net.h, 2)
     xd, td = torch.from_numpy(x).cuda(), torch.from_numpy(truth).cuda()
-    stream = torch.cuda.current_stream()
-    sp = L.stream_ptr()
+    # an explicit stream of our own for the whole step AND its timing events (torch's default stream is the legacy stream,
+    # handle 0, which the library's training entry points read as "the network's own stream")
+    stream = torch.cuda.Stream()
+    torch.cuda.synchronize()
+    sp = C.c_void_p(stream.cuda_stream)
 
     def step():
         N.ForwardBackwardNetworkGpu(net, xd.data_ptr(), td.data_ptr(), sp)
@@ -402,8 +405,9 @@ def train_leg(rank, world, dist, cfgname, hw, B, steps, warmup=3):
         dp.init(net, dist)
     x = torch.from_numpy(cfgmod.synth_images(B, 3, hw, hw, seed=1234 + rank)).cuda()
     t = torch.from_numpy(cfgmod.synth_truth(B, 90, classes=80, seed=4321 + rank)).cuda()
-    stream = torch.cuda.current_stream()
-    sp = L.stream_ptr()
+    stream = torch.cuda.Stream()   # explicit stream for the step and its events (see run_train)
+    torch.cuda.synchronize()
+    sp = C.c_void_p(stream.cuda_stream)
 
     def barrier():
         torch.cuda.synchronize()

@@ -440,7 +440,10 @@ extern "C" int yc_network_forward_backward(yc_network* net, const float* input_d
     int rc = yc_network_finalize(net);
     if (rc) return rc;
   }
-  cudaStream_t st = (cudaStream_t)stream;
+  // NULL = the network's own stream, as in yc_network_update (round 2: NULL used to mean the legacy default stream HERE and
+  // the network's stream THERE, so a caller passing NULL to both — bench.py did, through torch's default stream — had the
+  // update racing with the backward pass it follows; found through a NaN cost in the bench's host-fed leg)
+  cudaStream_t st = stream ? (cudaStream_t)stream : net->stream;
   int rc = train_forward(net, input_dev_nchw, truth_dev, st);
   if (!rc) rc = train_backward(net, st);
   if (!rc) net->seen += net->batch;

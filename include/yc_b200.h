@@ -490,7 +490,10 @@ YC_API int yc_network_time_ops(yc_network* net, const float* input_dev_nchw, int
  * truth = [batch][max_boxes*5] floats (x, y, w, h, class id), the reference's net->truth layout. */
 /* TrainNetworkDatum: host input + truth -> forward + backward (no update); *cost = GetNetworkCost. Synchronous. */
 YC_API int yc_network_train_datum(yc_network* net, const float* x_host, const float* truth_host, float* cost);
-/* ForwardBackwardNetworkGpu on device-resident fp32 NCHW input and truth; asynchronous on `stream`. */
+/* ForwardBackwardNetworkGpu on device-resident fp32 NCHW input and truth; asynchronous on `stream`.  In every training
+ * entry point a NULL stream means the NETWORK'S OWN stream (the one yc_network_train_datum uses; a non-blocking stream:
+ * it does not synchronise with the legacy default stream) — pass one and the same stream to yc_network_forward_backward
+ * and yc_network_update, and record timing events on that stream. */
 YC_API int yc_network_forward_backward(yc_network* net, const float* input_dev_nchw, const float* truth_dev, void* stream);
 /* UpdateNetworkGpu (network_kernels.cu:214-243): SGD step on every conv layer.  lr < 0 = GetCurrLr at the current iteration
  * (yc_network_current_rate; with the default constant policy and no burn-in that is [net] learning_rate), negative

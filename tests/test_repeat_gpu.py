@@ -64,3 +64,37 @@ def test_data_parallel_world1_equals_local_step(gpu):
     a = _one_step("yolov4-tiny", 8, 416, 80, w=416, h=416)
     b = _one_step("yolov4-tiny", 8, 416, 80, dp_world1=True, w=416, h=416)
     _assert_same(a, b, "data-parallel world 1 vs local")
+
+
+@pytest.mark.parametrize("stream_kind", ["null", "default", "own"])
+def test_steps_enqueued_back_to_back_equal_synchronised_steps(gpu, stream_kind):
+    """yc_network_forward_backward + yc_network_update enqueued with no host synchronisation in between (how a training
+    loop and bench.py run them) give the same bits as the same calls with a synchronisation after each — on a NULL stream
+    (= the network's own stream in BOTH entry points), on torch's default stream (handle 0, i.e. NULL again) and on a
+    stream of the caller's.  Round 2 regression: NULL used to mean the legacy default stream in forward_backward and the
+    network's stream in update, so the update raced with the backward pass before it."""
+    import torch
+    from darknet_b200 import lib as L, network as N
+    B, hw = 8, 416
+    text = cfgs.CONFIGS["yolov4-tiny"](batch=B, subdivisions=1, w=hw, h=hw)
+    weights = cfgmod.synth_weights(text)
+    xd = torch.from_numpy(cfgmod.synth_images(B, 3, hw, hw, seed=31)).to(gpu)
+    td = torch.from_numpy(cfgmod.synth_truth(B, 90, classes=80, seed=32)).to(gpu)
+    own = torch.cuda.Stream()
+    torch.cuda.synchronize()
+    sp = {"null": None, "default": C.c_void_p(torch.cuda.current_stream().cuda_stream), "own": C.c_void_p(own.cuda_stream)}[stream_kind]
+    res = []
+    for sync in (True, False):
+        net = N.LoadSynthetic(text, weights, batch=B, flags=L.NET_DEFAULT | L.NET_TRAIN)
+        for _ in range(6):
+            L.check(L.lib().yc_network_forward_backward(net.h, C.c_void_p(xd.data_ptr()), C.c_void_p(td.data_ptr()), sp), "fb")
+            if sync:
+                torch.cuda.synchronize()
+            L.check(L.lib().yc_network_update(net.h, -1.0, -1.0, -1.0, sp), "update")
+            if sync:
+                torch.cuda.synchronize()
+        torch.cuda.synchronize()
+        res.append({i: N.layer_param(net, i, "weights") for i in range(net.n) if net.layer_info(i, 0) == 0})
+        net.close()
+    bad = [i for i in res[0] if not np.array_equal(res[0][i], res[1][i])]
+    assert not bad, f"{stream_kind} stream: layers {bad[:6]} differ between synchronised and back-to-back steps"

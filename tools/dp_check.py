@@ -92,16 +92,19 @@ def main():
     # 4. timing: step with and without the all-reduce (device events, max over ranks)
     xd = torch.from_numpy(x).cuda()
     td = torch.from_numpy(t).cuda()
-    st = torch.cuda.current_stream()
+    st = torch.cuda.Stream()   # explicit stream for the steps and their events (NULL = the network's own stream)
+    torch.cuda.synchronize()
+    import ctypes as _C
+    sp = _C.c_void_p(st.cuda_stream)
 
     def timed(n, iters=10):
         for _ in range(3):
-            N.ForwardBackwardNetworkGpu(n, xd.data_ptr(), td.data_ptr())
+            N.ForwardBackwardNetworkGpu(n, xd.data_ptr(), td.data_ptr(), sp)
         torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(st)
         for _ in range(iters):
-            N.ForwardBackwardNetworkGpu(n, xd.data_ptr(), td.data_ptr())
+            N.ForwardBackwardNetworkGpu(n, xd.data_ptr(), td.data_ptr(), sp)
         e1.record(st)
         torch.cuda.synchronize()
         ms = torch.tensor([e0.elapsed_time(e1) / iters], device="cuda")
@@ -112,8 +115,8 @@ def main():
 
     def timed_deferred(iters=10):
         def one():
-            N.ForwardBackwardNetworkGpu(net2, xd.data_ptr(), td.data_ptr())
-            dp.reduce(net2, L.stream_ptr())
+            N.ForwardBackwardNetworkGpu(net2, xd.data_ptr(), td.data_ptr(), sp)
+            dp.reduce(net2, sp)
         for _ in range(3):
             one()
         torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
