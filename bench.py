@@ -436,7 +436,9 @@ def train_leg(rank, world, dist, cfgname, hw, B, steps, warmup=3):
         N.ForwardBackwardNetworkGpu(net, x.data_ptr(), t.data_ptr(), sp)
         N.UpdateNetwork(net, stream=sp)
 
-    def fb():
+    def fb():   # a backward pass without an update (timing only): declare the previous pass's reduced gradients discarded
+        if dist is not None:
+            dp.discard_step(net)
         N.ForwardBackwardNetworkGpu(net, x.data_ptr(), t.data_ptr(), sp)
 
     ms_step = timed(step, steps)
@@ -446,7 +448,9 @@ def train_leg(rank, world, dist, cfgname, hw, B, steps, warmup=3):
     if dist is not None:
         ms_fb = timed(fb, steps)                 # per-layer all-reduce overlapped with backward
         dp.set_overlap(net, False)
+        dp.discard_step(net)
         def fb_local():                          # buckets stay local during backward; exchanged outside the compared region
+            dp.discard_step(net)
             N.ForwardBackwardNetworkGpu(net, x.data_ptr(), t.data_ptr(), sp)
         for _ in range(warmup):
             fb_local()
@@ -463,6 +467,7 @@ def train_leg(rank, world, dist, cfgname, hw, B, steps, warmup=3):
         tt = torch.tensor([ms_local], device="cuda")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms_local = float(tt.item())
+        dp.discard_step(net)
         dp.set_overlap(net, True)
         out.update({"buckets_per_step": lib.yc_network_dp_info(net.h, 2), "allreduce_mib_per_step": lib.yc_network_dp_info(net.h, 3),
                     "forward_backward_ms_overlapped": ms_fb, "forward_backward_ms_local_only": ms_local,

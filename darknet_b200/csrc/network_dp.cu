@@ -79,6 +79,10 @@ struct DpCtx {
   int buckets = 0;
   bool overlap = true;   // all-reduce each bucket during backward; false: all buckets at once before the update
   bool pending = false;  // backward passes have run since the last reduction (overlap == false)
+  // The buckets carry the momentum term divided by the world size (yc_network_update), which is only right if every
+  // bucket is all-reduced exactly ONCE between two updates.  These two flags turn the sequences that would reduce a
+  // bucket twice into errors instead of silently scaled gradients:
+  bool reduced = false;  // the buckets hold all-reduced sums; no further backward pass may add to them before the update
 };
 
 #define NCCL_CALL(call)                                                                        \
@@ -147,6 +151,13 @@ extern "C" int yc_network_dp_init(yc_network* net, const void* unique_id128, int
 int yc_dp_layer_ready(yc_network* net, int layer, cudaStream_t compute) {
   DpCtx* ctx = (DpCtx*)net->dp;
   if (!ctx || ctx->world <= 1) return YC_OK;
+  if (ctx->reduced) {
+    set_error("data parallelism: a backward pass after the gradients of this step were already all-reduced (a second "
+              "yc_network_forward_backward before yc_network_update under per-layer overlap, or one after "
+              "yc_network_dp_reduce): the buckets would be reduced twice.  With several backward passes per update load "
+              "the network with subdivisions > 1 or call yc_network_dp_set_overlap(net, 0)");
+    return YC_ERR_ARG;
+  }
   if (!ctx->overlap) {
     ctx->pending = true;
     return YC_OK;
@@ -163,7 +174,14 @@ int yc_dp_backward_done(yc_network* net, cudaStream_t compute) {
   if (!ctx || ctx->world <= 1 || !ctx->overlap) return YC_OK;
   NET_CUDA(cudaEventRecord(ctx->done, ctx->comm_stream));
   NET_CUDA(cudaStreamWaitEvent(compute, ctx->done, 0));
+  ctx->reduced = true;  // until yc_network_update
   return YC_OK;
+}
+
+// yc_network_update has consumed the reduced gradients: the next backward pass starts a new step
+void yc_dp_update_done(yc_network* net) {
+  DpCtx* ctx = (DpCtx*)net->dp;
+  if (ctx) ctx->reduced = false;
 }
 
 // All buckets in one NCCL group, after everything enqueued on `compute`; `compute` then waits for the result.  Called by
@@ -181,6 +199,7 @@ int yc_dp_reduce_pending(yc_network* net, cudaStream_t compute) {
   NET_CUDA(cudaEventRecord(ctx->done, ctx->comm_stream));
   NET_CUDA(cudaStreamWaitEvent(compute, ctx->done, 0));
   ctx->pending = false;
+  ctx->reduced = true;  // until yc_network_update
   return YC_OK;
 }
 
@@ -192,6 +211,14 @@ extern "C" int yc_network_dp_set_overlap(yc_network* net, int on) {
   YC_REQUIRE(!on || net->subdivisions == 1, "yc_network_dp_set_overlap: per-layer overlap needs subdivisions=1");
   YC_REQUIRE(!ctx->pending, "yc_network_dp_set_overlap: un-reduced gradients pending");
   ctx->overlap = on != 0;
+  return YC_OK;
+}
+
+// The caller throws this step's gradients away (timing loops that run backward passes without updates): the next
+// backward pass may all-reduce again.  The buckets' CONTENTS are then meaningless until the caller zeroes them.
+extern "C" int yc_network_dp_discard_step(yc_network* net) {
+  YC_REQUIRE(net && net->dp, "yc_network_dp_discard_step: network has no data-parallel context");
+  ((DpCtx*)net->dp)->reduced = false;
   return YC_OK;
 }
 

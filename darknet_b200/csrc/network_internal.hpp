@@ -171,6 +171,7 @@ inline cudaError_t h2d_done() { return cudaStreamSynchronize(cudaStreamLegacy); 
 int yc_dp_layer_ready(yc_network* net, int layer, cudaStream_t compute);
 int yc_dp_backward_done(yc_network* net, cudaStream_t compute);
 int yc_dp_reduce_pending(yc_network* net, cudaStream_t compute);
+void yc_dp_update_done(yc_network* net);
 // conv_fprop_sm100.cu: yc_conv_plan_create with a rectangular kernel / stride / padding along W
 extern "C" int yc_conv_plan_create_rect(yc_conv_plan** out_plan, const yc_conv_desc* d, int kw, int stride_w, int pad_l,
                                         int pad_r, const yc_tensor* x, const void* w_packed, const float* bias,

@@ -530,6 +530,7 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
   }
   net->curr_iter = iter + 1;
   int rc = yc::sgd_update_multi(net->sgd_items, net->sgd_n, net->sgd_blocks, lr, batch, carry, decay, st);
+  if (net->dp) yc_dp_update_done(net);  // the reduced gradients are consumed: the next backward pass starts a new step
   // layers without batchnorm (the YOLO heads) add their bias in the conv epilogue, from the plan's own padded copy: it
   // follows the update (found by tests/test_resize_gpu.py: a re-planned network saw the new biases, the running one did not)
   for (NLayer& L : net->layers)
@@ -574,6 +575,22 @@ extern "C" int yc_network_train_profile(yc_network* net, const float* input_dev_
   cudaStream_t st = net->stream;
   int rc = YC_OK;
   const long long iter0 = net->curr_iter, seen0 = net->seen;  // a timing pass is not a training iteration
+  // ... nor may it leave traces in the training state: the passes below accumulate gradients, scale the accumulators by the
+  // momentum (update with lr = 0) and move the rolling batchnorm statistics — snapshot both, restore afterwards
+  std::vector<float*> snap_b(net->layers.size(), nullptr), snap_r(net->layers.size(), nullptr);
+  for (size_t i = 0; i < net->layers.size(); ++i) {
+    NLayer& L = net->layers[i];
+    if (L.type != L_CONV) continue;
+    if (L.dw_packed && L.bucket_floats) {
+      NET_CUDA(cudaMalloc(&snap_b[i], L.bucket_floats * 4));
+      NET_CUDA(cudaMemcpyAsync(snap_b[i], L.dw_packed, L.bucket_floats * 4, cudaMemcpyDeviceToDevice, st));
+    }
+    if (L.bn && L.rmean_dev && L.rvar_dev) {
+      NET_CUDA(cudaMalloc(&snap_r[i], (size_t)2 * L.n * 4));
+      NET_CUDA(cudaMemcpyAsync(snap_r[i], L.rmean_dev, (size_t)L.n * 4, cudaMemcpyDeviceToDevice, st));
+      NET_CUDA(cudaMemcpyAsync(snap_r[i] + L.n, L.rvar_dev, (size_t)L.n * 4, cudaMemcpyDeviceToDevice, st));
+    }
+  }
   for (int it = 0; it < iters && !rc; ++it) {
     Prof prof;
     g_prof = &prof;
@@ -597,6 +614,18 @@ extern "C" int yc_network_train_profile(yc_network* net, const float* input_dev_
   g_prof = nullptr;
   net->curr_iter = iter0;
   net->seen = seen0;
+  for (size_t i = 0; i < net->layers.size(); ++i) {
+    NLayer& L = net->layers[i];
+    if (snap_b[i]) cudaMemcpyAsync(L.dw_packed, snap_b[i], L.bucket_floats * 4, cudaMemcpyDeviceToDevice, st);
+    if (snap_r[i]) {
+      cudaMemcpyAsync(L.rmean_dev, snap_r[i], (size_t)L.n * 4, cudaMemcpyDeviceToDevice, st);
+      cudaMemcpyAsync(L.rvar_dev, snap_r[i] + L.n, (size_t)L.n * 4, cudaMemcpyDeviceToDevice, st);
+    }
+  }
+  cudaStreamSynchronize(st);
+  for (float* q : snap_b) if (q) cudaFree(q);
+  for (float* q : snap_r) if (q) cudaFree(q);
+  if (net->dp) yc_dp_update_done(net);
   return rc;
 }
 

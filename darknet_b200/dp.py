@@ -67,3 +67,9 @@ def set_overlap(net, on: bool):
 def reduce(net, stream=None):
     """All-reduce the gradients accumulated since the last reduction (collective; no-op if none are pending)."""
     L.check(L.lib().yc_network_dp_reduce(net.h, stream), "yc_network_dp_reduce")
+
+
+def discard_step(net):
+    """Timing loops that run backward passes without updates: declare this step's gradients discarded, so that the next
+    backward pass may all-reduce again (the library refuses to reduce a bucket twice between two updates)."""
+    L.check(L.lib().yc_network_dp_discard_step(net.h), "yc_network_dp_discard_step")

@@ -179,6 +179,7 @@ _SIGS = {
     "yc_network_dp_info": (C.c_int, [_P, C.c_int]),
     "yc_network_dp_set_overlap": (C.c_int, [_P, C.c_int]),
     "yc_network_dp_reduce": (C.c_int, [_P, _P]),
+    "yc_network_dp_discard_step": (C.c_int, [_P]),
     "yc_network_get_boxes": (C.POINTER(Detection), [_P, C.c_int, C.c_float, C.POINTER(C.c_int)]),
     "yc_free_detections": (None, [C.POINTER(Detection), C.c_int]),
     "yc_nms_sort": (None, [C.POINTER(Detection), C.c_int, C.c_int, C.c_float, C.c_int, C.c_float]),

@@ -529,6 +529,11 @@ YC_API int yc_dp_nccl_version(void);
 YC_API int yc_network_dp_init(yc_network* net, const void* unique_id128, int rank, int world);
 YC_API int yc_network_dp_set_overlap(yc_network* net, int on);
 YC_API int yc_network_dp_reduce(yc_network* net, void* stream);
+/* Every gradient bucket must be all-reduced exactly once between two updates (the momentum term is carried divided by
+ * the world size): a backward pass after this step's gradients were reduced — a second yc_network_forward_backward before
+ * yc_network_update under per-layer overlap, or one after yc_network_dp_reduce — returns YC_ERR_ARG.  A caller that runs
+ * backward passes WITHOUT updates on purpose (timing loops) declares the step's gradients discarded with this call. */
+YC_API int yc_network_dp_discard_step(yc_network* net);
 /* what: 0 world, 1 rank, 2 buckets per step, 3 MiB all-reduced per step, 4 per-layer overlap on */
 YC_API int yc_network_dp_info(const yc_network* net, int what);
 

@@ -98,3 +98,34 @@ def test_steps_enqueued_back_to_back_equal_synchronised_steps(gpu, stream_kind):
         net.close()
     bad = [i for i in res[0] if not np.array_equal(res[0][i], res[1][i])]
     assert not bad, f"{stream_kind} stream: layers {bad[:6]} differ between synchronised and back-to-back steps"
+
+
+def test_profile_pass_leaves_no_trace_in_the_training_state(gpu):
+    """yc_network_train_profile times forward + backward + an update with lr = 0: afterwards the gradient accumulators
+    (momentum history), the rolling batchnorm statistics, the weights and the counters are what they were (ADVICE round 1:
+    the timing pass used to scale the accumulators by the momentum and move the rolling statistics)."""
+    import torch
+    from darknet_b200 import lib as L, network as N
+    B, hw = 4, 64
+    text = cfgs.micro(batch=B, subdivisions=1)
+    net = N.LoadSynthetic(text, cfgmod.synth_weights(text), batch=B, flags=L.NET_DEFAULT | L.NET_TRAIN)
+    x = cfgmod.synth_images(B, 3, hw, hw, seed=41)
+    truth = cfgmod.synth_truth(B, 90, classes=3, seed=42)
+    N.TrainNetworkDatum(net, x, truth)
+    N.UpdateNetwork(net)
+
+    def state():
+        out = {"seen": np.int64(net.info(10))}
+        for i in range(net.n):
+            if net.layer_info(i, 0) == 0:
+                for key in ("weights", "weight_updates", "bias_updates", "biases") + (("scale_updates", "rolling_mean", "rolling_variance", "scales") if net.layer_info(i, 9) else ()):
+                    out[f"L{i}.{key}"] = N.layer_param(net, i, key)
+        return out
+    before = state()
+    xd, td = torch.from_numpy(x).to(gpu), torch.from_numpy(truth).to(gpu)
+    ms = np.zeros(7, np.float32)
+    L.check(L.lib().yc_network_train_profile(net.h, C.c_void_p(xd.data_ptr()), C.c_void_p(td.data_ptr()), 2, ms.ctypes.data_as(C.c_void_p)),
+            "yc_network_train_profile")
+    assert ms[6] > 0
+    _assert_same(before, state(), "training state across a profile pass")
+    net.close()
