@@ -497,7 +497,8 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
     int blocks = 0;
     auto push = [&](yc::SgdItem it, long long elements) {
       it.first_block = blocks;
-      it.blocks = (int)((elements + 1023) / 1024);
+      (void)elements;
+      it.blocks = yc::sgd_item_blocks(it);
       blocks += it.blocks;
       items.push_back(it);
     };

@@ -55,6 +55,7 @@ struct SgdItem {
   int out_c, in_c, taps, ldw, in_c_p, out_c_p;  // taps == 0: plain vector of out_c elements
   int first_block, blocks;
 };
+int sgd_item_blocks(const SgdItem& it);
 int sgd_update_multi(const SgdItem* items_dev, int n_items, int total_blocks, float lr, int batch, float momentum,
                      float decay, cudaStream_t st);
 
