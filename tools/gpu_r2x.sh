@@ -1,5 +1,5 @@
 #!/bin/bash
-# Round 2, call X: tiled SGD update, DP guards, profile restore — training tests, training benches.
+# Round 2, call X (re-used): training tests + training benches — training tests, training benches.
 set -u
 mkdir -p gpurun_out
 timeout 1500 python -m pytest tests/test_conv_train_gpu.py tests/test_train_emul_gpu.py tests/test_train_gpu.py tests/test_repeat_gpu.py tests/test_train_gates_gpu.py tests/test_resize_gpu.py tests/test_zconfigs_gpu.py -m gpu -x -q -k "not detections" > gpurun_out/pytest_x.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/pytest_x.log
