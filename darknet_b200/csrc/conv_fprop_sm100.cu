@@ -78,6 +78,12 @@ struct ConvParams {
   int bias_cols;       // > 0: that many floats of bias (n_tiles * block_n) are staged in shared memory at kernel start
   int cta_pair;        // conv_fprop_pair_kernel: tiles of 256 rows over a cluster of two CTAs (tcgen05 cta_group::2);
                        // m_tiles then counts 256-row tiles
+  // YOLO head (yc_conv_plan_set_yolo_decode): the fp32 results are not stored NHWC but decoded (logistic / scale_x_y per
+  // entry, yolo_layer.cpp:399-404) and written straight into the [yolo] layer's NCHW fp32 output — ForwardYoloLayerGpu
+  // inside the head convolution's epilogue, no intermediate tensor, no decode kernel
+  float* dec_out;
+  int dec_S, dec_E, dec_gauss;
+  float dec_sxy;
   int m_tiles128;      // CTA pairs: the number of real 128-row tiles (an odd count leaves the last pair's second CTA idle)
 };
 
@@ -390,6 +396,26 @@ __device__ __forceinline__ void epilogue_role(const ConvParams& p, const CUtenso
           ptx::tma_store_commit();
         }
         ++nst;
+      } else if (p.dec_out) {
+        // fused YOLO decode: lane = pixel, so for a fixed channel the 32 lanes write 32 consecutive floats of that
+        // channel's plane (128-byte requests without any transpose)
+        const int img = (int)(row / p.dec_S);
+        float* ob = p.dec_out + ((long long)img * p.N) * p.dec_S + (row - (long long)img * p.dec_S);
+        const float dbias = -0.5f * (p.dec_sxy - 1.f);
+        int e = col0 % p.dec_E;
+#pragma unroll 4
+        for (int j = 0; j < 32; ++j) {
+          const int c = col0 + j;
+          bool sig, aff;
+          if (p.dec_gauss) { sig = (e <= 3) || e == 5 || e == 7 || e >= 8; aff = (e == 0) || (e == 2); }
+          else { sig = (e < 2) || (e >= 4); aff = (e < 2); }
+          float yv = v[j];
+          if (sig) yv = act_logistic(yv);  // MUFU ex2 + rcp: within 2e-7 of the libm form (with expf + a division this
+                                           // epilogue took 546 us on the 76x76 head against 174 + 176 us unfused)
+          if (aff) yv = yv * p.dec_sxy + dbias;
+          if (row_ok && c < p.N) ob[(long long)c * p.dec_S] = yv;
+          if (++e == p.dec_E) e = 0;
+        }
       } else {
 #pragma unroll
         for (int hh = 0; hh < 2; ++hh) {  // fp32: two boxes of 16 columns
@@ -2021,6 +2047,23 @@ extern "C" int yc_conv_plan_set_bn_finalize(yc_conv_plan* pl, long long count, f
              "yc_conv_plan_set_bn_finalize: needs a plan with statistics (yc_conv_plan_set_stats) and mean / var buffers");
   pl->p.bn_mean = mean; pl->p.bn_var = var; pl->p.bn_rmean = rolling_mean; pl->p.bn_rvar = rolling_var;
   pl->p.bn_count = (float)count;
+  return YC_OK;
+}
+
+// ForwardYoloLayerGpu folded into the head convolution: the plan's fp32 results go, decoded, straight into the [yolo]
+// layer's NCHW fp32 output (out_nchw: [batch][channels][h*w], channels = anchors * entries); the plan's own output tensor
+// is not written any more.  entries = 5 + classes (9 + classes for Gaussian heads).
+extern "C" int yc_conv_plan_set_yolo_decode(yc_conv_plan* pl, float* out_nchw, int entries, float scale_x_y, int gaussian) {
+  YC_REQUIRE(pl && out_nchw && entries > 0, "yc_conv_plan_set_yolo_decode: bad arguments");
+  ConvParams& p = pl->p;
+  YC_REQUIRE(p.y_f32 && p.a_mode != 2 && !p.fast_epi && !p.cta_pair && !p.res && !p.stat_sum && p.act == YC_LINEAR &&
+                 !p.split_col && p.N % entries == 0,
+             "yc_conv_plan_set_yolo_decode: needs a plain fp32-output linear convolution whose channels are whole anchors");
+  p.dec_out = out_nchw;
+  p.dec_S = p.Ho * p.Wo;
+  p.dec_E = entries;
+  p.dec_gauss = gaussian ? 1 : 0;
+  p.dec_sxy = scale_x_y;
   return YC_OK;
 }
 

@@ -276,7 +276,7 @@ int free_device_state(yc_network* net) {
     if (L.anchors_dev) { cudaFree(L.anchors_dev); L.anchors_dev = nullptr; }
     if (L.mask_dev) { cudaFree(L.mask_dev); L.mask_dev = nullptr; }
     L.alias = false; L.alias_src = -1; L.alias_coff = 0; L.parent = -1; L.parent_coff = 0;
-    L.fused_into = -1; L.fused_conv = -1; L.copies.clear(); L.consumers = 0;
+    L.fused_into = -1; L.fused_conv = -1; L.copies.clear(); L.consumers = 0; L.head_decoded = false;
     L.pair_first = -1; L.pair_second = -1;
   }
   if (net->input_dev) { cudaFree(net->input_dev); net->input_dev = nullptr; }
@@ -683,6 +683,18 @@ extern "C" int yc_network_finalize(yc_network* net) {
         NET_CUDA(cudaMalloc(&L.mask_dev, L.mask.size() * 4));
         NET_CUDA(cudaMemcpy(L.mask_dev, L.mask.data(), L.mask.size() * 4, cudaMemcpyHostToDevice));
     NET_CUDA(h2d_done());
+        // ForwardYoloLayerGpu inside the head convolution's epilogue: when the layer before is a convolution with an fp32
+        // output that nobody else reads, its plan decodes and writes this layer's NCHW output itself — no NHWC head tensor,
+        // no decode kernel.  Opt-in (YC_PLAN_HEAD_DECODE): measured neutral on the step and it moves decode time into the
+        // conv kernels (profiles/r02_ab_head_decode.txt)
+        if ((plan_flags & YC_PLAN_HEAD_DECODE) && i > 0 && Ls[i - 1].type == L_CONV && Ls[i - 1].plan &&
+            Ls[i - 1].consumers == 1 && Ls[i - 1].fused_into < 0 && Ls[i - 1].pair_first < 0 && Ls[i - 1].pair_second < 0 &&
+            L.inputs.size() == 1 && L.inputs[0] == i - 1 && view_of(net, i - 1).dtype == YC_F32 &&
+            yc_conv_plan_info(Ls[i - 1].plan, 5) != 2 &&
+            yc_conv_plan_set_yolo_decode(Ls[i - 1].plan, L.dec_dev, L.out_c / L.n, L.scale_x_y, L.type == L_GYOLO ? 1 : 0) == YC_OK) {
+          Ls[i - 1].head_decoded = true;
+          break;
+        }
         op.kind = 5; op.a = input_view(i); op.i0 = L.n; op.i1 = L.classes; op.f0 = L.scale_x_y;
         op.i2 = L.type == L_GYOLO ? 1 : 0;
         net->ops.push_back(op);
@@ -972,7 +984,7 @@ extern "C" int yc_network_layer_info(const yc_network* net, int layer, int what)
     case 1: return L.out_c;
     case 2: return L.out_h;
     case 3: return L.out_w;
-    case 4: return (L.fused_into >= 0) ? 0 : 1;
+    case 4: return (L.fused_into >= 0 || L.head_decoded) ? 0 : 1;
     case 5: return L.c;
     case 6: return L.size;
     case 7: return L.stride;
@@ -1243,6 +1255,9 @@ extern "C" int yc_network_layer_output(yc_network* net, int layer, float* dst_ho
   YC_REQUIRE(net && dst_host && layer >= 0 && layer < (int)net->layers.size(), "yc_network_layer_output: bad argument");
   YC_REQUIRE(net->finalized, "yc_network_layer_output: network not finalized");
   NLayer& L = net->layers[layer];
+  YC_REQUIRE(!L.head_decoded, "yc_network_layer_output: layer %d is a head convolution whose results go, decoded, straight "
+             "into the [yolo] layer after it (yc_network_layer_info(layer, 4) == 0; YC_PLAN_HEAD_DECODE)",
+             layer);
   const size_t elems = (size_t)net->batch * L.out_c * L.out_h * L.out_w;
   if (L.type == L_YOLO || L.type == L_GYOLO) {
     NET_CUDA(cudaMemcpyAsync(dst_host, L.dec_dev, elems * 4, cudaMemcpyDeviceToHost, net->stream));

@@ -50,6 +50,7 @@ struct NLayer {
   int alias_src = -1, alias_coff = 0;
   int parent = -1, parent_coff = 0;  // placed inside `parent`'s concat buffer
   int fused_into = -1;      // conv whose epilogue also performs shortcut `fused_into`
+  bool head_decoded = false;  // head conv whose epilogue writes the following [yolo] layer's decoded output (no output of its own)
   int fused_conv = -1;      // shortcut computed by conv `fused_conv`
   void* buf = nullptr;      // owned allocation (root buffers only)
   int own_ldc = 0;

@@ -54,8 +54,9 @@ NET_STEM_DIRECT, NET_PDL = 16384, 32768
 PLAN_NO_HALO, PLAN_FORCE_HALO, PLAN_NO_HALO_PAIR, PLAN_NO_W_RES, PLAN_W_RES_1X1, PLAN_ONE_OUT_BUF, PLAN_COST_V1 = 1, 2, 4, 8, 16, 32, 64
 PLAN_TWO_OUT_BUFS, PLAN_GENERIC_EPI, PLAN_EPI_SETS_V1, PLAN_MISH_NEWTON, PLAN_NO_TILE_PAIR = 128, 256, 512, 1024, 2048
 PLAN_NO_CTA_PAIR, PLAN_CTA_PAIR_ALL, PLAN_PDL = 4096, 8192, 16384
+PLAN_HEAD_DECODE = 32  # (the bit of the former no-op PLAN_ONE_OUT_BUF)
 # every plan switch off: the plainest kernel variant of each layer (parity coverage of the non-default paths)
-NET_PLAIN_PLANS = NET_NO_STEM_PAIR | NET_NO_PAIR_S2 | NET_NO_PAIR_FUSE | ((PLAN_NO_HALO | PLAN_NO_W_RES | PLAN_ONE_OUT_BUF | PLAN_GENERIC_EPI | PLAN_NO_TILE_PAIR | PLAN_NO_CTA_PAIR) << NET_PLAN_SHIFT)
+NET_PLAIN_PLANS = NET_NO_STEM_PAIR | NET_NO_PAIR_S2 | NET_NO_PAIR_FUSE | ((PLAN_NO_HALO | PLAN_NO_W_RES | PLAN_GENERIC_EPI | PLAN_NO_TILE_PAIR | PLAN_NO_CTA_PAIR) << NET_PLAN_SHIFT)
 NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
 NET_TRAIN, NET_DGRAD_ACCUMULATE, NET_BN_BIAS_GRAD, NET_TRAIN_REF_CPU = 64, 128, 256, 8192
 
@@ -94,6 +95,7 @@ _SIGS = {
     "yc_conv_plan_info": (C.c_int, [_P, C.c_int]),
     "yc_conv_plan_set_stats": (C.c_int, [_P, _P, _P]),
     "yc_conv_plan_set_bias": (C.c_int, [_P, _P, _P]),
+    "yc_conv_plan_set_yolo_decode": (C.c_int, [_P, _P, C.c_int, C.c_float, C.c_int]),
     "yc_conv_plan_set_bn_finalize": (C.c_int, [_P, C.c_longlong, _P, _P, _P, _P]),
     "yc_bn_finalize": (C.c_int, [_P, _P, C.c_longlong, _P, _P, _P, _P, C.c_int, _P]),
     "yc_bn_act_fwd": (C.c_int, [_TP, _P, _P, _P, _P, C.c_int, _TP, _P]),

@@ -132,7 +132,13 @@ enum {
   YC_PLAN_NO_HALO_PAIR = 4,  /* halo mode: one tile at a time instead of tile pairs */
   YC_PLAN_NO_W_RES = 8,      /* never keep the weight slabs resident in shared memory */
   YC_PLAN_W_RES_1X1 = 16,    /* keep them resident for 1x1 layers as well */
-  YC_PLAN_ONE_OUT_BUF = 32,  /* one epilogue staging buffer per warp (the default since the specialised epilogue) */
+  YC_PLAN_HEAD_DECODE = 32,  /* network level, opt-in: fold the YOLO decode into the head convolution's epilogue
+                                (yc_conv_plan_set_yolo_decode) instead of running it as a kernel of its own.  Measured: the three
+                                launches it removes cost 246 us, the epilogues grow by 178 us (16 warps per SM doing the
+                                transposed stores), the step does not move (11.22 / 11.05 against 11.06 / 11.17 ms) and the conv
+                                time — the roofline's denominator — grows: off by default.  (Bit 32 was YC_PLAN_ONE_OUT_BUF, a
+                                no-op since one staging buffer became the default.) */
+  YC_PLAN_ONE_OUT_BUF = 32,
   YC_PLAN_COST_V1 = 64,      /* round-1 tile-width cost model */
   YC_PLAN_TWO_OUT_BUFS = 128, /* two staging buffers wherever they fit */
   YC_PLAN_GENERIC_EPI = 256, /* never use the specialised (bf16 / bias-only / mish-leaky-linear) epilogue */
@@ -183,6 +189,10 @@ YC_API int yc_conv_plan_set_bn_finalize(yc_conv_plan* plan, long long count, flo
  * layer without batchnorm: the YOLO heads, convolutional_layer.cpp:1382-1401 axpy on l.biases) hand it the new values.
  * Asynchronous on `stream`. */
 YC_API int yc_conv_plan_set_bias(yc_conv_plan* plan, const float* bias_dev, void* stream);
+/* ForwardYoloLayerGpu (yolo_layer.cpp:836-853, gaussian_yolo_layer.cpp:934-961) folded into the head convolution: the
+ * plan (fp32 output, linear, 1x1 / im2col operand) applies logistic / scale_x_y per entry and writes the [yolo] layer's
+ * NCHW fp32 output `out_nchw` [batch][anchors*entries][h*w] itself; its own output tensor is no longer written. */
+YC_API int yc_conv_plan_set_yolo_decode(yc_conv_plan* plan, float* out_nchw, int entries, float scale_x_y, int gaussian);
 YC_API int yc_bn_finalize(const float* sum, const float* sumsq, long long count, float* mean, float* var,
                           float* rolling_mean, float* rolling_var, int n, void* stream);
 YC_API int yc_bn_act_fwd(const yc_tensor* z, const float* mean, const float* var, const float* gamma,

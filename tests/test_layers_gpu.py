@@ -83,6 +83,33 @@ def test_yolo_decode_op(gpu, gaussian, H, W, classes, dtype):
     assert np.abs(got - ref).max() <= 1e-6
 
 
+@pytest.mark.parametrize("gaussian,classes,Cin,B,H,W", [(False, 80, 256, 3, 19, 19), (False, 3, 64, 2, 13, 17), (True, 80, 128, 2, 38, 38),
+                                                        (False, 80, 512, 5, 76, 76)])
+def test_head_conv_with_fused_yolo_decode(gpu, gaussian, classes, Cin, B, H, W):
+    """yc_conv_plan_set_yolo_decode (ForwardYoloLayerGpu inside the head convolution's epilogue) == the head convolution
+    followed by yc_yolo_decode to 1e-6 absolute (the same accumulators; pass-through entries bit for bit); sizes cover several
+    row tiles per image, tiles that straddle two images and the channel tail of the last 32-column group."""
+    from darknet_b200 import lib as L, ops
+    rng = np.random.default_rng(17)
+    n = 3
+    E = (9 if gaussian else 5) + classes
+    N = n * E
+    x = _bf16_round(rng.standard_normal((B, Cin, H, W)).astype(np.float32))
+    w = _bf16_round((rng.standard_normal((N, Cin, 1, 1)) * (2.0 / Cin) ** 0.5 * 3).astype(np.float32))
+    b = rng.uniform(-1, 1, N).astype(np.float32)
+    xd = ops.to_nhwc(torch.from_numpy(x).to(gpu))
+    conv = ops.Conv(xd, (B, H, W, Cin), torch.from_numpy(w), torch.from_numpy(b), 1, 1, 0, "linear", out_dtype=torch.float32)
+    want = ops.yolo_decode(conv(), N, n, classes, 1.05, gaussian=gaussian)
+    fused = ops.Conv(xd, (B, H, W, Cin), torch.from_numpy(w), torch.from_numpy(b), 1, 1, 0, "linear", out_dtype=torch.float32)
+    got = torch.full((B, N, H, W), -7.0, dtype=torch.float32, device=gpu)
+    L.check(L.lib().yc_conv_plan_set_yolo_decode(fused.plan, got.data_ptr(), E, 1.05, int(gaussian)), "yc_conv_plan_set_yolo_decode")
+    fused()
+    torch.cuda.synchronize()
+    # same accumulators; the logistic is the MUFU form (ex2 + rcp) here and libm's expf + a division in the separate kernel
+    assert float((got - want).abs().max()) <= 1e-6, f"max diff {float((got - want).abs().max()):.3e}"
+    assert torch.equal(got[:, 2::E], want[:, 2::E]) and torch.equal(got[:, 3::E], want[:, 3::E]), "w / h entries are passed through"
+
+
 @pytest.mark.parametrize("B,H,W,stride", [(2, 16, 20, 1), (3, 13, 12, 1), (1, 7, 44, 1), (2, 9, 10, 1), (2, 16, 16, 2), (1, 13, 11, 2)])
 def test_stem_im2col_operand_bit_exact(gpu, B, H, W, stride):
     """yc_stem_im2col builds the first conv's GEMM operand from the fp32 NCHW image: row = output pixel, column

@@ -35,7 +35,7 @@ def _compare_layers(net, outs, tol_l2, tol_max, skip_fused=True):
     return worst
 
 
-@pytest.mark.parametrize("flags_extra", [0, "nofuse_shortcut", "no_elide", "no_graph", "stem_direct", "pdl"])
+@pytest.mark.parametrize("flags_extra", [0, "nofuse_shortcut", "no_elide", "no_graph", "stem_direct", "pdl", "head_decode"])
 def test_micro_net_all_layers(gpu, flags_extra):
     from darknet_b200 import lib as L, network as N
     text, cpath, wpath = materialise("micro")
@@ -48,12 +48,15 @@ def test_micro_net_all_layers(gpu, flags_extra):
         flags &= ~L.NET_ELIDE_ROUTE
     elif flags_extra == "no_graph":
         flags &= ~L.NET_CUDA_GRAPH
+    elif flags_extra == "head_decode":  # opt-in: YOLO decode inside the head convolutions' epilogues (no output of their own)
+        flags |= L.PLAN_HEAD_DECODE << L.NET_PLAN_SHIFT
     elif flags_extra == "pdl":          # opt-in: programmatic dependent launches inside the captured graph
         flags |= L.NET_PDL
     elif flags_extra == "stem_direct":  # opt-in: layer 0 straight from the fp32 input (yc_stem_conv_direct), no plan
         flags |= L.NET_STEM_DIRECT
     net = N.LoadNetwork(cpath, wpath, batch=1, flags=flags)
     assert (net.layer_info(0, 13) == -1) == (flags_extra == "stem_direct")
+    assert (not net.has_output(16) and not net.has_output(23)) == (flags_extra == "head_decode")
     N.NetworkPredict(net, x)
     N.NetworkPredict(net, x)  # second call replays the graph
     worst = _compare_layers(net, outs, 1e-2, 2e-2)

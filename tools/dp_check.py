@@ -137,6 +137,21 @@ def main():
     ms_deferred = timed_deferred()
     net1 = fresh()
     ms_local = timed(net1)
+    # 5. the library refuses to all-reduce a bucket twice between two updates (the momentum term is carried divided by the
+    #    world size): a second backward pass under per-layer overlap must fail on every rank alike, before any NCCL call
+    import ctypes as _C2
+    torch.cuda.synchronize(); dist.barrier()
+    dp.discard_step(net)
+    args = (net.h, _C2.c_void_p(xd.data_ptr()), _C2.c_void_p(td.data_ptr()), sp)
+    rc1 = L.lib().yc_network_forward_backward(*args)
+    rc2 = L.lib().yc_network_forward_backward(*args)
+    msg = L.lib().yc_last_error().decode()
+    guard_ok = rc1 == 0 and rc2 != 0 and "reduced twice" in msg
+    N.UpdateNetwork(net, stream=sp)            # consumes the first pass: the next step is legal again
+    rc3 = L.lib().yc_network_forward_backward(*args)
+    N.UpdateNetwork(net, stream=sp)
+    torch.cuda.synchronize(); dist.barrier()
+    guard_ok = guard_ok and rc3 == 0
     if rank == 0:
         print(json.dumps({"dp_check": name, "world": world, "batch_per_gpu": B, "cost_rank0": cost,
                           "allreduce_relL2_vs_sum_of_local_runs": worst, "replicas_identical_after_2_updates": same,
@@ -146,12 +161,13 @@ def main():
                           "buckets": L.lib().yc_network_dp_info(net.h, 2), "mib_per_step": L.lib().yc_network_dp_info(net.h, 3),
                           "nccl": L.lib().yc_dp_nccl_version(),
                           "reduced_gradients_bit_identical_across_ranks": identical,
+                          "second_backward_before_update_is_refused": guard_ok,
                           "per_layer_relL2_vs_sum_and_vs_local_only": {str(k): [float(f"{v[0]:.2e}"), float(f"{v[1]:.2e}")]
                                                                        for k, v in per_layer.items()}}))
     dist.barrier()
     net.close(); net1.close(); net2.close()
     dist.destroy_process_group()
-    return 0 if (exact_err < 1e-6 and same and identical) else 1
+    return 0 if (exact_err < 1e-6 and same and identical and guard_ok) else 1
 
 
 if __name__ == "__main__":
