@@ -1693,11 +1693,16 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
   // Measured (yolov4-608 x 64, same box, tools/ab_layers.py pair / nopair): 3x3 512->1024 @19 214 -> 153 us (1.42 PFLOP/s),
   // 256->256 @38 120 -> 91 us, 512->512 @19 137 -> 100 us, 1x1 1024->512 @19 41 -> 34 us; the 1x1 layers with K <= 512 (8 K
   // blocks or fewer) gain nothing or lose up to 10 % (their tiles are short: the pair's start-up and the remote hand-backs
-  // show) -> from 12 K blocks on.
+  // show) -> from 12 K blocks on (first A/B; lowered to 8 by the second one, below).
   // Halo mode: the 128-wide tiles with at least 128 input channels (3x3 128->128 @76: one MMA of a 128 x 128 tile is 64
   // tensor-pipe cycles of work against an issue interval of ~175 for MMAs on one accumulator; a pair of CTAs doubles the
   // work per MMA, two tiles in flight double it again).
-  const bool pair_rule = p.a_mode == 2 ? (p.block_n == 128 && p.n_tiles == 1 && x->c >= 128) : (p.block_n == 256 && k_blocks >= 12);
+  // Second same-box A/B (default / pairs everywhere / default / pairs everywhere, profiles/r02_ab_cta_pair_all.txt): halo
+  // 3x3 64->64 @152 233 -> 185 us (-18 %), 1x1 with 8 K blocks (512->256 @38, 512->512 @19 / @38) -7..-15 %; 1x1 with 4 K blocks
+  // +-5 % (noise), everything at 304^2 and the stride-2 layers +13..+60 % -> halo from 64 channels on, tiled / im2col from
+  // 8 K blocks on.
+  const bool pair_rule = p.a_mode == 2 ? (p.n_tiles == 1 && ((p.block_n == 128 && x->c >= 128) || (p.block_n == 64 && x->c == 64)))
+                                       : (p.block_n == 256 && k_blocks >= 8);
   p.cta_pair = (p.fast_epi && !(flags & YC_PLAN_NO_CTA_PAIR) && sms >= 2 &&
                 (pair_rule || (flags & YC_PLAN_CTA_PAIR_ALL))) ? 1 : 0;
   if (p.cta_pair) p.tile_pair = 0;

@@ -179,7 +179,8 @@ def test_conv_cta_pairs(gpu):
     _run(gpu, 8, 256, 38, 38, 256, 3, 1, "leaky", plan_flags=L.PLAN_NO_CTA_PAIR, want_variant=(512, 0))
     _run(gpu, 64, 128, 19, 19, 512, 3, 1, "leaky", want_variant=(512, 512))                 # 2 N tiles, 182 pair tiles on 74 pairs
     _run(gpu, 64, 1024, 19, 19, 256, 1, 1, "mish", want_variant=(512 | 3, 512 | 0))         # default rule, 1x1 tiled map, 16 K blocks
-    _run(gpu, 64, 512, 19, 19, 256, 1, 1, "mish", want_variant=(512, 0))                    # 8 K blocks: stays on one CTA per tile
+    _run(gpu, 64, 512, 19, 19, 256, 1, 1, "mish", want_variant=(512, 512))                  # 8 K blocks: the threshold
+    _run(gpu, 64, 256, 19, 19, 256, 1, 1, "mish", want_variant=(512, 0))                    # 4 K blocks: stays on one CTA per tile
     _run(gpu, 3, 512, 19, 19, 256, 3, 1, "mish", plan_flags=PA, want_variant=(512, 512))    # 9 row tiles: odd
     _run(gpu, 5, 512, 19, 19, 256, 1, 1, "leaky", residual=True, plan_flags=PA, want_variant=(512, 512))
     _run(gpu, 4, 64, 38, 38, 64, 1, 1, "mish", plan_flags=PA | L.PLAN_NO_HALO, want_variant=(512, 512))
