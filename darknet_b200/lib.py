@@ -85,6 +85,7 @@ _SIGS = {
     "yc_nhwc_to_nchw": (C.c_int, [_TP, _P, _P]),
     "yc_stem_im2col": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _TP, _P]),
     "yc_stem_conv_direct": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, _TP, _P]),
+    "yc_stem_conv_tc": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, C.c_int, _TP, _P]),
     "yc_conv_padded_in_c": (C.c_int, [C.c_int]),
     "yc_conv_packed_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "yc_conv_pack": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P]),

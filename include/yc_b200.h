@@ -92,6 +92,12 @@ YC_API int yc_stem_im2col(const float* src, int c, int h, int w, int size, int s
  * inputs are rounded to bf16 like every other layer's, accumulation is fp32. */
 YC_API int yc_stem_conv_direct(const float* x_nchw, int batch, int h, int w, const void* w_packed, const float* bias,
                                int activation, const yc_tensor* y, void* stream);
+/* The same layer, same arguments, on the tensor cores of sm_100a: builder warps assemble each 128-pixel tile's [128][32]
+ * bf16 operand in shared memory (64B-swizzled K-major rows), one lane issues tcgen05.mma against the filters resident in
+ * shared memory, accumulators in TMEM, epilogue warps add bias + activation and TMA-store NHWC bf16.  No operand in global
+ * memory: 12 B read + 2*ldc B written per pixel. */
+YC_API int yc_stem_conv_tc(const float* x_nchw, int batch, int h, int w, const void* w_packed, const float* bias,
+                           int activation, const yc_tensor* y, void* stream);
 /* Mat2Image on the device (visualize.cpp:26-54): u8 HWC [n][h][w][c] -> fp32 NCHW, value/255.0f; swap_rb reads
  * channel c-1-k (the cvtColor(RGB2BGR) of yolo_core.cpp:110). */
 YC_API int yc_u8hwc_to_nchw(const unsigned char* src, int n, int c, int h, int w, int swap_rb, float* dst, void* stream);

@@ -133,12 +133,15 @@ def test_conv_plan_switches(gpu):
     _run(gpu, 8, 512, 19, 19, 512, 3, 1, "leaky")
 
 
+@pytest.mark.parametrize("entry", ["yc_stem_conv_direct", "yc_stem_conv_tc"])
 @pytest.mark.parametrize("B,H,W,N,act", [(2, 40, 72, 32, "mish"), (1, 16, 32, 32, "leaky"), (3, 19, 33, 16, "linear"),
-                                         (2, 64, 64, 24, "mish"), (1, 5, 7, 8, "leaky")])
-def test_stem_conv_direct(gpu, B, H, W, N, act):
+                                         (2, 64, 64, 24, "mish"), (1, 5, 7, 8, "leaky"), (5, 200, 328, 32, "mish")])
+def test_stem_conv_direct(gpu, B, H, W, N, act, entry):
     """yc_stem_conv_direct (3 -> N channels, 3x3 / stride 1 / pad 1 straight from the fp32 NCHW image; mma.sync with register
-    A fragments, no operand in global memory) against the oracle conv on the same bf16-rounded inputs; ragged sizes cover
-    partial tiles in both directions, N < 32 the channel guard, and a wider pixel pitch the concat placement."""
+    A fragments) and yc_stem_conv_tc (tcgen05: operand tiles built in shared memory by the kernel, accumulators in TMEM, TMA
+    stores) — neither keeps an operand in global memory — against the oracle conv on the same bf16-rounded inputs; ragged
+    sizes cover partial tiles in both directions, N < 32 the channel guard, a wider pixel pitch the concat placement, and
+    the last case gives every persistent CTA several tiles (all A slots and accumulators wrap around)."""
     from darknet_b200 import lib as L, ops
     lib = L.lib()
     rng = np.random.default_rng(B * 100 + H)
@@ -158,8 +161,8 @@ def test_stem_conv_direct(gpu, B, H, W, N, act):
     bd = torch.from_numpy(b).to(gpu)
     ldy = 40 if N == 24 else N        # N == 24: the output is a channel slice of a wider buffer
     y = torch.full((B, H, W, ldy), 3.0, dtype=torch.bfloat16, device=gpu)
-    L.check(lib.yc_stem_conv_direct(xd.data_ptr(), B, H, W, packed.data_ptr(), bd.data_ptr(), L.ACT[act],
-                                    L.view(y, B, H, W, N, ldy), L.stream_ptr()), "yc_stem_conv_direct")
+    L.check(getattr(lib, entry)(xd.data_ptr(), B, H, W, packed.data_ptr(), bd.data_ptr(), L.ACT[act],
+                                L.view(y, B, H, W, N, ldy), L.stream_ptr()), entry)
     torch.cuda.synchronize()
     got = y[..., :N].float().permute(0, 3, 1, 2).cpu().numpy()
     err = np.abs(got - ref).max() / (np.abs(ref).max() + 1e-12)
