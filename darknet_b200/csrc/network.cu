@@ -313,7 +313,7 @@ int run_op(yc_network* net, const Op& op, cudaStream_t st) {
     case 5: return yc_yolo_decode(&op.a, L->dec_dev, op.i0, op.i1, op.f0, op.i2, st);
     case 6: return yc_nchw_to_nhwc(net->graph_input, &op.y, st);
     case 7: return yc_stem_im2col(net->graph_input, net->c, net->h, net->w, op.i0, op.i1, op.i2, &op.y, st);
-    case 8: return yc_stem_conv_direct(net->graph_input, net->batch, net->h, net->w, L->w_packed, L->bias_dev, op.i0, &op.y, st);
+    case 8: return (op.i1 ? yc_stem_conv_tc : yc_stem_conv_direct)(net->graph_input, net->batch, net->h, net->w, L->w_packed, L->bias_dev, op.i0, &op.y, st);
   }
   return YC_ERR_ARG;
 }
@@ -442,13 +442,16 @@ extern "C" int yc_network_finalize(yc_network* net) {
     return YC_OK;
   }
   const unsigned plan_flags = (((unsigned)flags >> YC_NET_PLAN_SHIFT) & 0x7fffu) | ((flags & YC_NET_PDL) ? (unsigned)YC_PLAN_PDL : 0u);
-  // Opt-in (YC_NET_STEM_DIRECT; measured slower, see yc_b200.h): stem computed straight from the fp32 NCHW input by
-  // yc_stem_conv_direct (no operand in global memory at all): the 3 -> 8..32 channel 3x3 / stride 1 / pad 1 first layer of
-  // the YOLO backbones with folded batchnorm.
-  net->stem_direct = stem && (flags & YC_NET_STEM_DIRECT) && Ls[0].c == 3 && Ls[0].size == 3 && Ls[0].stride == 1 &&
-                     Ls[0].pad == 1 && Ls[0].n % 8 == 0 && Ls[0].n <= 32 && Ls[0].fused_into < 0 &&
-                     (!Ls[0].bn || (flags & YC_NET_FUSE_BN)) && view_of(net, 0).dtype == YC_BF16 &&
-                     (Ls[0].act == YC_MISH || Ls[0].act == YC_LEAKY || Ls[0].act == YC_LINEAR);
+  // The 3 -> 8..32 channel 3x3 / stride 1 / pad 1 first layer of the YOLO backbones (folded batchnorm) is computed straight
+  // from the fp32 NCHW input, no operand in global memory at all: by yc_stem_conv_tc (tcgen05; the default), by
+  // yc_stem_conv_direct under YC_NET_STEM_DIRECT (mma.sync, measured slower), or — YC_NET_STEM_OPERAND — through the round-1
+  // path (im2col operand built by the input conversion + a 1x1 layer; A/B and parity coverage).
+  const bool stem_kernel_ok = stem && Ls[0].c == 3 && Ls[0].size == 3 && Ls[0].stride == 1 && Ls[0].pad == 1 &&
+                              Ls[0].n % 8 == 0 && Ls[0].n <= 32 && Ls[0].fused_into < 0 &&
+                              (!Ls[0].bn || (flags & YC_NET_FUSE_BN)) && view_of(net, 0).dtype == YC_BF16 &&
+                              (Ls[0].act == YC_MISH || Ls[0].act == YC_LEAKY || Ls[0].act == YC_LINEAR);
+  net->stem_tc = stem_kernel_ok && !(flags & (YC_NET_STEM_DIRECT | YC_NET_STEM_OPERAND)) && net->w % 4 == 0;
+  net->stem_direct = stem_kernel_ok && ((flags & YC_NET_STEM_DIRECT) || net->stem_tc);
   if (!net->stem_direct && stem && Ls[0].n % 8 == 0 && 2 * Ls[0].n <= 256 && Ls[0].out_w % 2 == 0 && Ls[0].fused_into < 0 &&
       view_of(net, 0).ldc == Ls[0].n && view_of(net, 0).dtype == YC_BF16 && !(flags & YC_NET_NO_STEM_PAIR))
     net->stem_pair = true;
@@ -603,7 +606,7 @@ extern "C" int yc_network_finalize(yc_network* net) {
       case L_CONV: {
         if (L.pair_first >= 0) break;  // computed by layer pair_first's kernel (second output tensor)
         if (i == 0 && net->stem_direct) {  // input conversion + conv in one kernel, no plan
-          op.kind = 8; op.i0 = L.act; op.y = view_of(net, 0);
+          op.kind = 8; op.i0 = L.act; op.i1 = net->stem_tc ? 1 : 0; op.y = view_of(net, 0);
           net->ops.push_back(op);
           break;
         }

@@ -146,7 +146,8 @@ struct yc_network {
   int train_flags = 0;
   bool stem = false;  // layer 0 runs as a 1x1 conv over the 32-column im2col operand built by yc_stem_im2col
   bool stem_pair = false;  // inference: the stem conv runs on pixel pairs (network.cu)
-  bool stem_direct = false;  // inference: layer 0 is computed from the fp32 NCHW input by yc_stem_conv_direct
+  bool stem_direct = false;  // inference: layer 0 is computed from the fp32 NCHW input by one kernel (no operand, no plan)
+  bool stem_tc = false;      //   ... by yc_stem_conv_tc (tcgen05) rather than yc_stem_conv_direct (mma.sync)
   void* delta_slab = nullptr;
   size_t delta_slab_bytes = 0;
   float* truth_dev = nullptr;     // [batch][max_boxes*5] (*net->truth_gpu)

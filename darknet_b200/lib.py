@@ -51,6 +51,7 @@ NET_FUSE_BN, NET_FUSE_SHORTCUT, NET_ELIDE_ROUTE, NET_CUDA_GRAPH, NET_PULL_HEADS,
 NET_STEM_IM2COL = 512
 NET_NO_STEM_PAIR, NET_NO_PAIR_S2, NET_NO_PAIR_FUSE, NET_PLAN_SHIFT = 1024, 2048, 4096, 16
 NET_STEM_DIRECT, NET_PDL = 16384, 32768
+NET_STEM_OPERAND = -2147483648  # bit 31 of the int flags word
 PLAN_NO_HALO, PLAN_FORCE_HALO, PLAN_NO_HALO_PAIR, PLAN_NO_W_RES, PLAN_W_RES_1X1, PLAN_ONE_OUT_BUF, PLAN_COST_V1 = 1, 2, 4, 8, 16, 32, 64
 PLAN_TWO_OUT_BUFS, PLAN_GENERIC_EPI, PLAN_EPI_SETS_V1, PLAN_MISH_NEWTON, PLAN_NO_TILE_PAIR = 128, 256, 512, 1024, 2048
 PLAN_NO_CTA_PAIR, PLAN_CTA_PAIR_ALL, PLAN_PDL = 4096, 8192, 16384

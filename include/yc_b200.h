@@ -395,16 +395,17 @@ enum {
   YC_NET_NO_STEM_PAIR = 1024, /* stem conv on single pixels instead of pixel pairs (A/B + parity coverage) */
   YC_NET_NO_PAIR_S2 = 2048,  /* 3x3 stride-2 32-channel layer on the plain im2col path instead of the pixel-pair view */
   YC_NET_NO_PAIR_FUSE = 4096, /* do not merge two 1x1 convs that read the same tensor into one GEMM */
-  YC_NET_STEM_DIRECT = 16384, /* opt-in: compute the 3->32 3x3 stem straight from the fp32 input with yc_stem_conv_direct
-                                instead of the im2col-operand + 1x1 path.  Measured SLOWER on B200 (1.32 ms against 0.53 +
-                                0.32 ms per yolov4-608 x 64 step: the legacy mma.sync rate of sm_100 bounds it), kept as a
-                                tested alternative. */
+  YC_NET_STEM_DIRECT = 16384, /* the 3->32 3x3 stem by yc_stem_conv_direct (mma.sync) instead of yc_stem_conv_tc (tcgen05, the
+                                default for such a layer).  Measured slower (1.13 ms against 0.50 ms per yolov4-608 x 64 step:
+                                the legacy mma.sync rate of sm_100 bounds it), kept as a tested alternative. */
   YC_NET_PDL = 32768,        /* opt-in: programmatic dependent launches for the inference conv kernels (YC_PLAN_PDL).  Measured
                                 twice (round 1, round 2 with the CTA-pair build: 11.21 / 11.40 ms against 11.38 / 11.39 ms per
                                 yolov4-608 x 64 step, i.e. noise): the next kernel's CTA cannot become resident next to a
                                 226 KB one, and what it could overlap — its own set-up — is not what the short layers pay for */
   YC_NET_PLAN_SHIFT = 16,    /* bits [16,31): YC_PLAN_* switches handed to every conv plan */
-  YC_NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512
+  YC_NET_DEFAULT = 1 | 2 | 4 | 8 | 16 | 512,
+  YC_NET_STEM_OPERAND = (int)0x80000000u /* the stem through the round-1 path — im2col operand written by the input conversion
+                                (yc_stem_im2col) + a 1x1 layer over it — instead of the one-kernel stem (A/B, parity coverage) */
 };
 
 /* [setup] LoadNetwork (parser.cpp:1852-1875).  batch <= 0 keeps the cfg's batch (the reference forces

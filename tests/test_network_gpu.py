@@ -35,7 +35,7 @@ def _compare_layers(net, outs, tol_l2, tol_max, skip_fused=True):
     return worst
 
 
-@pytest.mark.parametrize("flags_extra", [0, "nofuse_shortcut", "no_elide", "no_graph", "stem_direct", "pdl", "head_decode"])
+@pytest.mark.parametrize("flags_extra", [0, "nofuse_shortcut", "no_elide", "no_graph", "stem_direct", "stem_operand", "pdl", "head_decode"])
 def test_micro_net_all_layers(gpu, flags_extra):
     from darknet_b200 import lib as L, network as N
     text, cpath, wpath = materialise("micro")
@@ -52,10 +52,12 @@ def test_micro_net_all_layers(gpu, flags_extra):
         flags |= L.PLAN_HEAD_DECODE << L.NET_PLAN_SHIFT
     elif flags_extra == "pdl":          # opt-in: programmatic dependent launches inside the captured graph
         flags |= L.NET_PDL
-    elif flags_extra == "stem_direct":  # opt-in: layer 0 straight from the fp32 input (yc_stem_conv_direct), no plan
+    elif flags_extra == "stem_direct":  # layer 0 by the mma.sync kernel (yc_stem_conv_direct) instead of yc_stem_conv_tc
         flags |= L.NET_STEM_DIRECT
+    elif flags_extra == "stem_operand":  # layer 0 through the im2col operand + 1x1 plan (round-1 path)
+        flags |= L.NET_STEM_OPERAND
     net = N.LoadNetwork(cpath, wpath, batch=1, flags=flags)
-    assert (net.layer_info(0, 13) == -1) == (flags_extra == "stem_direct")
+    assert (net.layer_info(0, 13) == -1) == (flags_extra != "stem_operand")   # one-kernel stem: layer 0 has no plan
     assert (not net.has_output(16) and not net.has_output(23)) == (flags_extra == "head_decode")
     N.NetworkPredict(net, x)
     N.NetworkPredict(net, x)  # second call replays the graph

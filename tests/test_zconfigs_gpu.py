@@ -66,7 +66,7 @@ def _all_layers(name, B, hw, flags, tol_l2=1e-2, tol_max=2e-2, want=None, **kw):
                 worst = (i, e2, em)
             assert e2 < tol_l2 and em < tol_max, f"{name} layer {i} ({net.layer_type(i)}) image {b}: rel-L2 {e2:.3e} rel-max {em:.3e}"
         compared += 1
-    print(f"{name} {hw}x{hw} batch {B} flags {flags:#x}: {compared} layer outputs compared, worst layer {worst[0]} "
+    print(f"{name} {hw}x{hw} batch {B} flags {flags & 0xffffffff:#x}: {compared} layer outputs compared, worst layer {worst[0]} "
           f"rel-L2 {worst[1]:.2e} rel-max {worst[2]:.2e}; kernel variants {variants}")
     ref.close()
     net.close()
@@ -163,9 +163,10 @@ def test_yolov4_608_all_layers_default_plan(gpu):
     from darknet_b200 import lib as L
 
     def want(net, variants):
-        # the plan bench.py times: stem on pixel pairs, stride-2 pixel-pair layer, halo patches with tile pairs and resident
-        # weights, CTA pairs (tiled / im2col and halo), the five CSP 1x1 pairs fused, 23 shortcuts fused, specialised epilogue
-        assert net.layer_info(0, 13) & 3 == 0 and net.layer_info(1, 13) & 64, "stem / pair-s2 variants not selected"
+        # the plan bench.py times: one-kernel tcgen05 stem (no plan), stride-2 pixel-pair layer, halo patches with tile pairs
+        # and resident weights, CTA pairs (tiled / im2col and halo), the five CSP 1x1 pairs fused, 23 shortcuts fused,
+        # specialised epilogue
+        assert net.layer_info(0, 13) == -1 and net.layer_info(1, 13) & 64, "stem kernel / pair-s2 variant not selected"
         assert any(v >= 0 and v & 512 and v & 3 != 2 for v in variants) and any(v >= 0 and v & 512 and v & 3 == 2 for v in variants), \
             "no CTA-pair layer (im2col and halo)"
         assert sum(1 for i in range(net.n) if net.layer_info(i, 14) >= 0) == 5, "the five CSP pairs are not fused"
@@ -174,6 +175,15 @@ def test_yolov4_608_all_layers_default_plan(gpu):
                    for v in [net.layer_info(i, 13)] if net.layer_info(i + 1, 0) not in (5, 6)), "specialised epilogue not selected"
         assert sum(1 for i in range(net.n) if not net.has_output(i)) == 23, "shortcut fusion"
     _all_layers("yolov4", 4, 608, L.NET_DEFAULT, want=want)
+
+
+def test_yolov4_608_all_layers_stem_operand_path(gpu):
+    """YC_NET_STEM_OPERAND: the round-1 stem (im2col operand written by the input conversion + a 1x1 layer on pixel pairs)"""
+    from darknet_b200 import lib as L
+
+    def want(net, variants):
+        assert net.layer_info(0, 13) >= 0 and net.layer_info(0, 13) & 3 == 0, "stem operand path not selected"
+    _all_layers("yolov4", 1, 608, L.NET_DEFAULT | L.NET_STEM_OPERAND, want=want)
 
 
 def test_yolov4_608_all_layers_plain_plan(gpu):
