@@ -137,30 +137,6 @@ __device__ __forceinline__ float act_ct(float x) {
   return x;
 }
 
-// Packed fp32x2 arithmetic (sm_100 FFMA2 / FMUL2 / FADD2: one issue slot for two lanes of work).  The mish epilogue is
-// issue-bound (ncu: 66 % of the issue slots, XU pipe 53 %), so two outputs per instruction is what counts.
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 pack2(float a, float b) {
-  f32x2 r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
-  return r;
-}
-__device__ __forceinline__ void unpack2(f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
-__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
-  f32x2 d;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-  return d;
-}
-__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
-  f32x2 d;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  return d;
-}
-__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
-  f32x2 d;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  return d;
-}
 // act(x) for two values; same formulas as act_ct (mish: yc_common.cuh act_mish)
 template <int ACT>
 __device__ __forceinline__ void act_ct2(f32x2 x, float& y0, float& y1) {

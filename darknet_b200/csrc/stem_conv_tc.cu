@@ -59,13 +59,6 @@ __device__ __forceinline__ uint32_t tc_pack(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
-template <int ACT>
-__device__ __forceinline__ float tc_act(float x) {
-  if (ACT == YC_MISH) return act_mish(x);
-  if (ACT == YC_LEAKY) return fmaxf(x, 0.1f * x);
-  return x;
-}
-
 // (image, tile row, tile column) of a tile index that advances by a fixed step: one division pair up front, then carries only
 // (a lone thread feeds the TMA engine; two integer divisions per tile made it the slowest stage of the pipeline)
 struct TcTileWalk {
@@ -253,13 +246,41 @@ stem_conv_tc_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
       if (lane == 0) ptx::tma_store_wait_read<1>();  // the store that used this buffer two stores ago has read it
       __syncwarp();
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        uint32_t o[4];
+      for (int j = 0; j < 4; ++j) {  // eight channels = one 16-byte chunk of the pixel's row, as four packed fp32 pairs
+        f32x2 x[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           float b0, b1;
           asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(b0), "=f"(b1) : "r"(bias_smem + 4u * (uint32_t)(8 * j + 2 * e)));
-          o[e] = tc_pack(tc_act<ACT>(__uint_as_float(r[8 * j + 2 * e]) + b0), tc_act<ACT>(__uint_as_float(r[8 * j + 2 * e + 1]) + b1));
+          x[e] = add2(pack2(__uint_as_float(r[8 * j + 2 * e]), __uint_as_float(r[8 * j + 2 * e + 1])), pack2(b0, b1));
+        }
+        uint32_t o[4];
+        if (ACT == YC_MISH) {  // act_mish (yc_common.cuh) on pairs: x + x*r, r = 1/(-q/2), q = n(n+2)+2 on h = n/2
+          float h[8];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float a0, a1;
+            unpack2(fma2(x[e], pack2(1.4426950408889634f, 1.4426950408889634f), pack2(-1.f, -1.f)), a0, a1);
+            h[2 * e] = ex2_ftz(a0);
+            h[2 * e + 1] = ex2_ftz(a1);
+          }
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const f32x2 hh = pack2(h[2 * e], h[2 * e + 1]);
+            float q0, q1;
+            unpack2(fma2(hh, fma2(hh, pack2(-2.f, -2.f), pack2(-2.f, -2.f)), pack2(-1.f, -1.f)), q0, q1);
+            h[2 * e] = rcp_ftz(q0);
+            h[2 * e + 1] = rcp_ftz(q1);
+          }
+#pragma unroll
+          for (int e = 0; e < 4; ++e) x[e] = fma2(x[e], pack2(h[2 * e], h[2 * e + 1]), x[e]);
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float y0, y1;
+          unpack2(x[e], y0, y1);
+          if (ACT == YC_LEAKY) { y0 = fmaxf(y0, 0.1f * y0); y1 = fmaxf(y1, 0.1f * y1); }
+          o[e] = tc_pack(y0, y1);
         }
         ptx::st_shared_v4(sbuf + rowoff + (((uint32_t)j ^ swz) << 4), o[0], o[1], o[2], o[3]);
       }
