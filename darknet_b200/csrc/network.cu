@@ -282,6 +282,9 @@ int free_device_state(yc_network* net) {
   if (net->input_dev) { cudaFree(net->input_dev); net->input_dev = nullptr; }
   if (net->input_pinned) { cudaFreeHost(net->input_pinned); net->input_pinned = nullptr; }
   if (net->u8_pinned) { cudaFreeHost(net->u8_pinned); net->u8_pinned = nullptr; }
+  if (net->u8_src_pinned) { cudaFreeHost(net->u8_src_pinned); net->u8_src_pinned = nullptr; }
+  if (net->u8_src_dev) { cudaFree(net->u8_src_dev); net->u8_src_dev = nullptr; }
+  net->u8_src_bytes = 0;
   if (net->copy_stream) { cudaStreamSynchronize(net->copy_stream); cudaStreamDestroy(net->copy_stream); net->copy_stream = nullptr; }
   if (net->copy_done) { cudaEventDestroy(net->copy_done); net->copy_done = nullptr; }
   if (net->stage_free) { cudaEventDestroy(net->stage_free); net->stage_free = nullptr; }
@@ -1216,6 +1219,39 @@ extern "C" float* yc_network_predict_u8(yc_network* net, const unsigned char* in
     return nullptr;
   }
   if (yc_u8hwc_to_nchw(net->u8_dev, net->batch, net->c, net->h, net->w, swap_rb, net->input_dev, net->stream)) return nullptr;
+  return predict_tail(net);
+}
+
+// ProcImage (yolo_core.cpp:104-112) from the camera frame on: cv::resize to the network's size, cvtColor(RGB2BGR),
+// Mat2Image, NetworkPredict — the H2D copy carries the frames as they are (u8, any size), the rest runs on the device.
+extern "C" float* yc_network_predict_u8_resized(yc_network* net, const unsigned char* frames_host_hwc, int src_h, int src_w,
+                                                int swap_rb) {
+  if (!net || !frames_host_hwc || src_h <= 0 || src_w <= 0) {
+    set_error("yc_network_predict_u8_resized: bad arguments");
+    return nullptr;
+  }
+  if (!net->finalized && yc_network_finalize(net)) return nullptr;
+  if (src_h == net->h && src_w == net->w) return yc_network_predict_u8(net, frames_host_hwc, swap_rb);
+  const size_t bytes = (size_t)net->batch * net->c * src_h * src_w;
+  if (bytes > net->u8_src_bytes) {  // staging for frames of this size (grown, never shrunk)
+    if (cudaStreamSynchronize(net->stream) != cudaSuccess) return nullptr;
+    if (net->u8_src_pinned) cudaFreeHost(net->u8_src_pinned);
+    if (net->u8_src_dev) cudaFree(net->u8_src_dev);
+    net->u8_src_pinned = nullptr; net->u8_src_dev = nullptr; net->u8_src_bytes = 0;
+    if (cudaHostAlloc(&net->u8_src_pinned, bytes, cudaHostAllocDefault) != cudaSuccess ||
+        cudaMalloc(&net->u8_src_dev, bytes) != cudaSuccess) {
+      set_error("yc_network_predict_u8_resized: staging allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(cudaGetLastError()));
+      return nullptr;
+    }
+    net->u8_src_bytes = bytes;
+  }
+  memcpy(net->u8_src_pinned, frames_host_hwc, bytes);
+  if (cudaMemcpyAsync(net->u8_src_dev, net->u8_src_pinned, bytes, cudaMemcpyHostToDevice, net->stream) != cudaSuccess) {
+    set_error("yc_network_predict_u8_resized: H2D failed: %s", cudaGetErrorString(cudaGetLastError()));
+    return nullptr;
+  }
+  if (yc_resize_u8_to_nchw(net->u8_src_dev, net->batch, net->c, src_h, src_w, swap_rb, net->input_dev, net->h, net->w, net->stream))
+    return nullptr;
   return predict_tail(net);
 }
 

@@ -118,6 +118,9 @@ struct yc_network {
   const float* resident_host = nullptr;  // batch already moved into input_dev, not yet consumed by a forward
   unsigned char* u8_pinned = nullptr;  // u8 HWC staging of yc_network_predict_u8 (allocated on first use)
   unsigned char* u8_dev = nullptr;
+  unsigned char* u8_src_pinned = nullptr;  // frames of another size than the network's (yc_network_predict_u8_resized),
+  unsigned char* u8_src_dev = nullptr;     //   grown on demand
+  size_t u8_src_bytes = 0;
   yc::SgdItem* sgd_items = nullptr;  // device table of the one-launch update (built on the first yc_network_update)
   int sgd_n = 0, sgd_blocks = 0;
   void* input_nhwc = nullptr;   // bf16 NHWC, ldc 8

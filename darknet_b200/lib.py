@@ -159,10 +159,13 @@ _SIGS = {
     "yc_network_resize": (C.c_int, [_P, C.c_int, C.c_int]),
     "yc_network_predict": (_P, [_P, _P]),
     "yc_network_predict_u8": (_P, [_P, _P, C.c_int]),
+    "yc_network_predict_u8_resized": (_P, [_P, _P, C.c_int, C.c_int, C.c_int]),
     "yc_network_prefetch": (C.c_int, [_P, _P]),
     "yc_network_input_buffer_slot": (_P, [_P, C.c_int]),
     "yc_network_input_buffer_u8": (_P, [_P]),
     "yc_u8hwc_to_nchw": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "yc_resize_u8": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, _P, C.c_int, C.c_int, _P]),
+    "yc_resize_u8_to_nchw": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, C.c_int, C.c_int, _P]),
     "yc_network_input_buffer": (_P, [_P]),
     "yc_network_forward": (C.c_int, [_P, _P, _P]),
     "yc_network_layer_output": (C.c_int, [_P, C.c_int, _P]),

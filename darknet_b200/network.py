@@ -164,6 +164,23 @@ def NetworkPredictU8(net: Network, img_u8: np.ndarray, swap_rb=False):
     return None
 
 
+def NetworkPredictFrames(net: Network, frames_u8: np.ndarray, swap_rb=True):
+    """ProcImage from the frame on (yolo_core.cpp:104-112): frames_u8 = host u8 HWC [batch,src_h,src_w,c] of ANY size;
+    cv::resize to the network's size, cvtColor(RGB2BGR) (swap_rb), Mat2Image and NetworkPredict, the first three in one
+    device kernel.  Bit-identical to NetworkPredictU8 on cv::resize'd frames."""
+    if not (frames_u8.dtype == np.uint8 and frames_u8.flags["C_CONTIGUOUS"]):
+        frames_u8 = np.ascontiguousarray(frames_u8, np.uint8)
+    assert frames_u8.ndim == 4 and frames_u8.shape[0] == net.batch and frames_u8.shape[3] == net.c, "frames must be [batch,h,w,c]"
+    p = L.lib().yc_network_predict_u8_resized(net.h, frames_u8.ctypes.data_as(C.c_void_p), frames_u8.shape[1],
+                                              frames_u8.shape[2], 1 if swap_rb else 0)
+    if not p:
+        raise L.YcError("NetworkPredictFrames failed: " + L.lib().yc_last_error().decode())
+    last = net.n - 1
+    if net.layer_info(last, 0) in (5, 6):
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=net.layer_shape(last))
+    return None
+
+
 def NetworkPredict(net: Network, x: np.ndarray):
     """NetworkPredict (network.cpp:412-430): x = host fp32 NCHW [batch,c,h,w]; synchronous.  Returns a numpy
     view of the last layer's host output (layer-owned, valid until the next call)."""

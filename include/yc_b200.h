@@ -101,6 +101,14 @@ YC_API int yc_stem_conv_tc(const float* x_nchw, int batch, int h, int w, const v
 /* Mat2Image on the device (visualize.cpp:26-54): u8 HWC [n][h][w][c] -> fp32 NCHW, value/255.0f; swap_rb reads
  * channel c-1-k (the cvtColor(RGB2BGR) of yolo_core.cpp:110). */
 YC_API int yc_u8hwc_to_nchw(const unsigned char* src, int n, int c, int h, int w, int swap_rb, float* dst, void* stream);
+/* cv::resize(src, dst, Size(dw, dh)) — default INTER_LINEAR — for n 8-bit interleaved images (1..4 channels) on the device,
+ * bit-identical to the library (ProcImage's two resizes, yolo_core.cpp:108-109; OpenCV imgproc/src/resize.cpp: 11-bit fixed-
+ * point coefficients, the (b*(row>>4))>>16 vertical pass, INTER_AREA for an exact 2x2 decimation; pinned against cv2 4.13 by
+ * tests/golden/cv_resize.npz).  yc_resize_u8_to_nchw fuses the cvtColor(RGB2BGR) + Mat2Image that follow (swap_rb, /255.0f,
+ * fp32 NCHW).  Device pointers. */
+YC_API int yc_resize_u8(const unsigned char* src, int n, int c, int sh, int sw, unsigned char* dst, int dh, int dw, void* stream);
+YC_API int yc_resize_u8_to_nchw(const unsigned char* src, int n, int c, int sh, int sw, int swap_rb, float* dst_nchw, int dh,
+                                int dw, void* stream);
 /* NHWC view -> fp32 NCHW (what the reference's host code and other layers read). */
 YC_API int yc_nhwc_to_nchw(const yc_tensor* src, float* dst, void* stream);
 
@@ -476,6 +484,12 @@ YC_API float* yc_network_predict(yc_network* net, const float* input_host);
  * are bit-identical to yc_network_predict on the Mat2Image output.  yc_network_input_buffer_u8: pinned staging. */
 YC_API float* yc_network_predict_u8(yc_network* net, const unsigned char* input_host_hwc, int swap_rb);
 YC_API unsigned char* yc_network_input_buffer_u8(yc_network* net);
+/* ProcImage from the frame on (yolo_core.cpp:104-112): cv::resize(frame, Size(net->w, net->h)) + cvtColor + Mat2Image +
+ * NetworkPredict for a batch of u8 HWC frames of ANY size src_h x src_w: the frames cross PCIe as bytes, resize (bit-identical
+ * to the library's INTER_LINEAR for 8-bit data, yc_resize_u8), channel swap, /255 and layout run in one device kernel.
+ * Equals yc_network_predict_u8 on host-resized frames bit for bit. */
+YC_API float* yc_network_predict_u8_resized(yc_network* net, const unsigned char* frames_host_hwc, int src_h, int src_w,
+                                            int swap_rb);
 /* Input double buffering for a stream of batches (the reference's NetworkPredictGpu copies and computes serially,
  * network_kernels.cu:502-522): yc_network_prefetch(next) starts the H2D copy of the NEXT batch on a separate stream
  * while the current forward runs; the later yc_network_predict(net, next) (same pointer) skips its own H2D.

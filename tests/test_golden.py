@@ -11,7 +11,7 @@ import pytest
 from darknet_b200 import cfg as cfgmod
 from tests.netutil import materialise, rel_l2, rel_to_max
 
-GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+GOLD = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "micro_*.npz")))  # (cv_resize.npz: test_cv_resize_cpu.py)
 
 
 def _load(path):

@@ -107,7 +107,8 @@ def test_head_conv_with_fused_yolo_decode(gpu, gaussian, classes, Cin, B, H, W):
     torch.cuda.synchronize()
     # same accumulators; the logistic is the MUFU form (ex2 + rcp) here and libm's expf + a division in the separate kernel
     assert float((got - want).abs().max()) <= 1e-6, f"max diff {float((got - want).abs().max()):.3e}"
-    assert torch.equal(got[:, 2::E], want[:, 2::E]) and torch.equal(got[:, 3::E], want[:, 3::E]), "w / h entries are passed through"
+    e_w, e_h = (4, 6) if gaussian else (2, 3)   # the entries no logistic touches (gaussian_yolo_layer.cpp:497-516: mu_w, mu_h)
+    assert torch.equal(got[:, e_w::E], want[:, e_w::E]) and torch.equal(got[:, e_h::E], want[:, e_h::E]), "w / h entries are passed through"
 
 
 @pytest.mark.parametrize("B,H,W,stride", [(2, 16, 20, 1), (3, 13, 12, 1), (1, 7, 44, 1), (2, 9, 10, 1), (2, 16, 16, 2), (1, 13, 11, 2)])
