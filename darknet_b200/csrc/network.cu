@@ -60,6 +60,12 @@ int build_layers(yc_network* net, const std::string& text, int batch, int w_over
   net->lr = n0.get_float("learning_rate", .001f);   // ParseNetOptions parser.cpp:1116-1140
   net->momentum = n0.get_float("momentum", .9f);
   net->decay = n0.get_float("decay", .0001f);
+  net->adam = n0.get_int("adam", 0);                 // parser.cpp:995-1001
+  if (net->adam) {
+    net->B1 = n0.get_float("B1", .9f);
+    net->B2 = n0.get_float("B2", .999f);
+    net->adam_eps = n0.get_float("eps", .000001f);
+  }
   {  // learning-rate schedule (parser.cpp:944-995, 1028)
     const std::string pol = n0.get_str("policy", "constant");
     const char* names[] = {"constant", "step", "exp", "poly", "steps", "sigmoid", "random", "sgdr"};
@@ -771,7 +777,7 @@ extern "C" int yc_network_resize(yc_network* net, int w, int h) {
   if (w == net->w && h == net->h) return YC_OK;
   const bool was_final = net->finalized, train = (net->flags & YC_NET_TRAIN) != 0;
   const size_t nl = net->layers.size();
-  std::vector<std::vector<float>> buckets(nl);
+  std::vector<std::vector<float>> buckets(nl), adam_m(nl), adam_v(nl);
   if (was_final && train) {
     int rc = yc_train_pull_params(net);
     if (rc) return rc;
@@ -780,6 +786,12 @@ extern "C" int yc_network_resize(yc_network* net, int w, int h) {
       if (L.type != L_CONV || !L.dw_packed || !L.bucket_floats) continue;
       buckets[i].resize(L.bucket_floats);
       NET_CUDA(cudaMemcpyAsync(buckets[i].data(), L.dw_packed, L.bucket_floats * 4, cudaMemcpyDeviceToHost, net->stream));
+      if (L.adam_m && L.adam_v) {  // Adam moments travel like the momentum carried in the bucket
+        adam_m[i].resize(L.bucket_floats);
+        adam_v[i].resize(L.bucket_floats);
+        NET_CUDA(cudaMemcpyAsync(adam_m[i].data(), L.adam_m, L.bucket_floats * 4, cudaMemcpyDeviceToHost, net->stream));
+        NET_CUDA(cudaMemcpyAsync(adam_v[i].data(), L.adam_v, L.bucket_floats * 4, cudaMemcpyDeviceToHost, net->stream));
+      }
     }
     NET_CUDA(cudaStreamSynchronize(net->stream));
   }
@@ -827,6 +839,10 @@ extern "C" int yc_network_resize(yc_network* net, int w, int h) {
         return YC_ERR_ARG;
       }
       NET_CUDA(cudaMemcpyAsync(L.dw_packed, buckets[i].data(), L.bucket_floats * 4, cudaMemcpyHostToDevice, net->stream));
+      if (!adam_m[i].empty() && L.adam_m && L.adam_v) {
+        NET_CUDA(cudaMemcpyAsync(L.adam_m, adam_m[i].data(), L.bucket_floats * 4, cudaMemcpyHostToDevice, net->stream));
+        NET_CUDA(cudaMemcpyAsync(L.adam_v, adam_v[i].data(), L.bucket_floats * 4, cudaMemcpyHostToDevice, net->stream));
+      }
     }
     NET_CUDA(cudaStreamSynchronize(net->stream));
   }

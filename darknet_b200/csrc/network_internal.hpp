@@ -76,6 +76,8 @@ struct NLayer {
   size_t bucket_floats = 0;      // dw_packed + bias_upd + scale_upd, contiguous (one all-reduce per layer)
   float* bias_upd = nullptr;     // l->bias_updates_gpu
   float* scale_upd = nullptr;    // l->scale_updates_gpu
+  float* adam_m = nullptr;       // [net] adam=1: first / second moments, laid out like the gradient bucket (l->m_gpu, l->v_gpu,
+  float* adam_v = nullptr;       //   bias_m/v, scale_m/v of convolutional_layer.cpp:589-600)
   void* w_packed_d = nullptr;    // data-gradient operand packing
   void* z_buf = nullptr;         // bf16 NHWC pre-batchnorm conv output (l->x_gpu)
   int z_ldc = 0;
@@ -138,6 +140,8 @@ struct yc_network {
   std::vector<float> det_rows_out;
   // ---- training (network_train.cu) ----
   float lr = .001f, momentum = .9f, decay = .0001f;  // [net] learning_rate / momentum / decay (parser.cpp:1116-1140)
+  int adam = 0;                                       // [net] adam / B1 / B2 / eps (parser.cpp:995-1001)
+  float B1 = .9f, B2 = .999f, adam_eps = .000001f;
   int subdivisions = 1;
   // learning-rate schedule (ParseNetOptions parser.cpp:944-995, GetCurrLr network.cpp:32-84)
   int policy = 0;  // 0 constant 1 step 2 exp 3 poly 4 steps 5 sigmoid 6 random 7 sgdr

@@ -80,7 +80,7 @@ void yc_train_free(yc_network* net) {
   for (NLayer& L : net->layers) {
     L.bias_upd = L.scale_upd = nullptr;  // inside the dw_packed bucket
     float** fp[] = {&L.w_master, &L.rmean_dev, &L.rvar_dev, &L.mean_dev, &L.var_dev, &L.stats_dev, &L.ws_dev,
-                    &L.dw_packed, &L.ydelta, &L.ystats};
+                    &L.dw_packed, &L.ydelta, &L.ystats, &L.adam_m, &L.adam_v};
     for (float** p : fp)
       if (*p) { cudaFree(*p); *p = nullptr; }
     void** vp[] = {&L.w_packed_d, &L.z_buf, &L.dil_buf};
@@ -148,6 +148,8 @@ int yc_train_finalize(yc_network* net) {
           rc = dev_alloc(&L.dw_packed, L.bucket_floats);
           L.bias_upd = L.dw_packed + nw;
           L.scale_upd = L.bias_upd + round_up(L.n, 4);
+          if (!rc && net->adam) rc = dev_alloc(&L.adam_m, L.bucket_floats);  // zero-filled like the reference's calloc
+          if (!rc && net->adam) rc = dev_alloc(&L.adam_v, L.bucket_floats);
         }
         if (rc) return rc;
         NET_CUDA(cudaMalloc(&L.w_packed, yc_conv_packed_bytes(L.n, G.c, G.size)));
@@ -474,7 +476,9 @@ extern "C" int yc_network_train_datum(yc_network* net, const float* x_host, cons
 // the cfg's [net] values; batch = net->batch * subdivisions (network.cpp:118).
 extern "C" int yc_network_update(yc_network* net, float lr, float momentum, float decay, void* stream) {
   YC_REQUIRE(net && (net->flags & YC_NET_TRAIN) && net->finalized, "yc_network_update: not a finalized training network");
-  const long long iter = net->curr_iter;
+  // TrainNetwork (network.cpp:227-231) advances curr_iter BEFORE UpdateNetworkGpu: the k-th update of a run sees iter = k
+  // in GetCurrLr, in the update gates and as Adam's t (l->t = iter, network_kernels.cu:229).
+  const long long iter = net->curr_iter + 1;
   if (lr < 0) lr = yc_network_current_rate(net, iter, 0);  // UpdateNetworkGpu: lr = GetCurrLr(net)
   if (momentum < 0) momentum = net->momentum;
   if (decay < 0) decay = net->decay;
@@ -509,12 +513,18 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
       if (!(L.dont_update < iter) && L.dont_update) continue;  // the reference updates when l->dont_update < iter
       const Geo G = geo(net, (int)(&L - net->layers.data()));
       const int taps = G.size * G.size;
+      // Adam moments mirror the gradient bucket: same offsets as dw_packed / bias_upd / scale_upd
+      auto mom = [&](float* base, const float* upd) -> float* { return base ? base + (upd - L.dw_packed) : nullptr; };
       yc::SgdItem w{L.w_master, L.dw_packed, (__nv_bfloat16*)L.w_packed, (__nv_bfloat16*)L.w_packed_d, L.n, G.c, taps,
-                    yc_conv_wgrad_ld(G.c), yc_conv_padded_in_c(G.c), yc_conv_padded_in_c(yc_conv_dgrad_channels(L.n)), 0, 0};
+                    yc_conv_wgrad_ld(G.c), yc_conv_padded_in_c(G.c), yc_conv_padded_in_c(yc_conv_dgrad_channels(L.n)), 0, 0,
+                    L.adam_m, L.adam_v};
       push(w, (long long)L.n * taps * G.c);
-      if (L.bias_dev && L.bias_upd) push(yc::SgdItem{L.bias_dev, L.bias_upd, nullptr, nullptr, L.n, 0, 0, 0, 0, 0, 0, 0}, L.n);
+      if (L.bias_dev && L.bias_upd)
+        push(yc::SgdItem{L.bias_dev, L.bias_upd, nullptr, nullptr, L.n, 0, 0, 0, 0, 0, 0, 0, mom(L.adam_m, L.bias_upd),
+                         mom(L.adam_v, L.bias_upd)}, L.n);
       if (L.bn && L.scale_dev && L.scale_upd)
-        push(yc::SgdItem{L.scale_dev, L.scale_upd, nullptr, nullptr, L.n, 0, 0, 0, 0, 0, 0, 0}, L.n);
+        push(yc::SgdItem{L.scale_dev, L.scale_upd, nullptr, nullptr, L.n, 0, 0, 0, 0, 0, 0, 0, mom(L.adam_m, L.scale_upd),
+                         mom(L.adam_v, L.scale_upd)}, L.n);
     }
     if (net->sgd_items) {  // gated networks only: the previous update may still be reading the table
       YC_CUDA(cudaStreamSynchronize(st));
@@ -529,8 +539,10 @@ extern "C" int yc_network_update(yc_network* net, float lr, float momentum, floa
     net->sgd_n = (int)items.size();
     net->sgd_blocks = blocks;
   }
-  net->curr_iter = iter + 1;
-  int rc = yc::sgd_update_multi(net->sgd_items, net->sgd_n, net->sgd_blocks, lr, batch, carry, decay, st);
+  net->curr_iter = iter;
+  const yc::UpdRule rule{lr / batch, decay * batch, carry, net->adam, (int)std::min<long long>(iter, 0x7fffffff), net->B1, net->B2,
+                         net->adam_eps, lr};
+  int rc = yc::sgd_update_multi(net->sgd_items, net->sgd_n, net->sgd_blocks, rule, st);
   if (net->dp) yc_dp_update_done(net);  // the reduced gradients are consumed: the next backward pass starts a new step
   // layers without batchnorm (the YOLO heads) add their bias in the conv epilogue, from the plan's own padded copy: it
   // follows the update (found by tests/test_resize_gpu.py: a re-planned network saw the new biases, the running one did not)

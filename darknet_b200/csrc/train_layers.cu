@@ -268,6 +268,37 @@ __global__ void shortcut_bwd_kernel(BV dy, BV y, int act, BV dprev, BV dfrom) {
 
 namespace yc {
 
+// One parameter of UpdateConvolutionalLayerGpu (convolutional_kernels.cu:865-922).  Weight arrays first get the GPU path's
+// scrub (:881-882): reset_nan_and_inf on the gradient (NaN / Inf -> 0) and fix_nan_and_inf on the weight (-> 1 / (index + 1),
+// index = the element's OIHW position; blas_kernels.cu:1157-1201).  Then SGD — dW -= decay*batch*W (weights only);
+// W += (lr/batch)*dW; dW *= momentum — or adam_update_gpu (blas_kernels.cu:99-134), which decays biases and scales too:
+//   m = B1 m; v = B2 v; d -= decay*batch*w; m += (1-B1) d; d = d*d; v += (1-B2) d;
+//   w += rate * (m / (1 - B1^t)) / (sqrt(v / (1 - B2^t)) + eps); d = 0.
+// bc1 / bc2 = 1 - B^t are evaluated by the caller once per thread (device powf like the reference's adam_kernel).
+__device__ __forceinline__ void upd_elem(const UpdRule& r, float bc1, float bc2, float& w, float& g, float* m, float* v,
+                                         bool is_weight, int oihw_index) {
+  if (is_weight) {
+    if (isnan(g) || isinf(g)) g = 0.f;
+    if (isnan(w) || isinf(w)) w = 1.0f / (fabsf((float)oihw_index) + 1);
+  }
+  if (r.adam) {
+    float mm = *m * r.B1, vv = *v * r.B2;
+    g = fmaf(-r.decay_batch, w, g);
+    mm = fmaf(1.f - r.B1, g, mm);
+    g = g * g;
+    vv = fmaf(1.f - r.B2, g, vv);
+    const float mhat = mm / bc1, vhat = vv / bc2;
+    w = w + r.rate * mhat / (sqrtf(vhat) + r.eps);
+    *m = mm;
+    *v = vv;
+    g = 0.f;
+  } else {
+    if (is_weight) g += -r.decay_batch * w;
+    w += r.lr_over_batch * g;
+    g *= r.momentum;
+  }
+}
+
 // UpdateConvolutionalLayer (convolutional_layer.cpp:1382-1400), SGD with momentum and weight decay:
 //   dW -= decay*batch*W ; W += (lr/batch)*dW ; dW *= momentum
 // in one pass over the packed gradient; also refreshes the two bf16 operand packings the GEMMs read
@@ -285,9 +316,8 @@ __global__ void sgd_weights_kernel(float* __restrict__ w_oihw, float* __restrict
     const long long wi = ((long long)n * in_c + c) * taps + tap;
     float w = w_oihw[wi];
     float g = dwp[gi];
-    g += -decay_batch * w;
-    w += lr_over_batch * g;
-    g *= momentum;
+    const UpdRule r{lr_over_batch, decay_batch, momentum, 0, 0, 0.f, 0.f, 0.f, 0.f};
+    upd_elem(r, 1.f, 1.f, w, g, nullptr, nullptr, true, (int)wi);
     w_oihw[wi] = w;
     dwp[gi] = g;
     const __nv_bfloat16 wb = __float2bfloat16_rn(w);
@@ -307,8 +337,12 @@ __global__ void sgd_vector_kernel(float* __restrict__ p, float* __restrict__ dp,
 constexpr int kSgdTN = 16, kSgdTC = 32, kSgdMaxTaps = 9;  // tile of the weights branch of sgd_multi_kernel
 // The whole network's update in ONE launch (yc_network_update): a table of items, 1024 elements per block, the block
 // finds its item by bisection of the block prefix.  Items with taps == 0 are plain vectors (biases, scales).
-__global__ void __launch_bounds__(256) sgd_multi_kernel(const SgdItem* __restrict__ items, int n_items, float lr_over_batch,
-                                                        float decay_batch, float momentum) {
+__global__ void __launch_bounds__(256) sgd_multi_kernel(const SgdItem* __restrict__ items, int n_items, const UpdRule rule) {
+  float bc1 = 1.f, bc2 = 1.f;
+  if (rule.adam) {
+    bc1 = 1.f - powf(rule.B1, (float)rule.t);
+    bc2 = 1.f - powf(rule.B2, (float)rule.t);
+  }
   int lo = 0, hi = n_items - 1;
   while (lo < hi) {  // last item whose first_block <= blockIdx.x
     const int mid = (lo + hi + 1) >> 1;
@@ -321,9 +355,10 @@ __global__ void __launch_bounds__(256) sgd_multi_kernel(const SgdItem* __restric
     for (int k = 0; k < 4; ++k) {
       const long long i = base + k * 256 + threadIdx.x;
       if (i >= it.out_c) break;
-      const float g = it.dw[i];
-      it.w[i] += lr_over_batch * g;
-      it.dw[i] = g * momentum;
+      float g = it.dw[i], w = it.w[i];
+      upd_elem(rule, bc1, bc2, w, g, it.m ? it.m + i : nullptr, it.v ? it.v + i : nullptr, false, 0);
+      it.w[i] = w;
+      it.dw[i] = g;
     }
     return;
   }
@@ -353,10 +388,11 @@ __global__ void __launch_bounds__(256) sgd_multi_kernel(const SgdItem* __restric
       if (cl >= cw) continue;
       const int n = n0 + nl, c = c0 + cl;
       float* gp = it.dw + ((long long)n * taps + t) * it.ldw + c;
-      const float wv = Ws[nl][cl * taps + t];
-      float gg = *gp - decay_batch * wv;
-      const float ww = wv + lr_over_batch * gg;
-      gg *= momentum;
+      float ww = Ws[nl][cl * taps + t];
+      float gg = *gp;
+      const long long go = gp - it.dw;
+      upd_elem(rule, bc1, bc2, ww, gg, it.m ? it.m + go : nullptr, it.v ? it.v + go : nullptr, true,
+               (int)(((long long)n * it.in_c + c) * taps + t));
       *gp = gg;
       Ws[nl][cl * taps + t] = ww;
       const __nv_bfloat16 wb = __float2bfloat16_rn(ww);
@@ -396,9 +432,8 @@ __global__ void __launch_bounds__(256) sgd_multi_kernel(const SgdItem* __restric
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
     if (nn[k] < 0) continue;
-    float gg = g[k] - decay_batch * w[k];
-    const float ww = w[k] + lr_over_batch * gg;
-    gg *= momentum;
+    float gg = g[k], ww = w[k];
+    upd_elem(rule, bc1, bc2, ww, gg, it.m ? it.m + gi[k] : nullptr, it.v ? it.v + gi[k] : nullptr, true, (int)wi[k]);
     it.w[wi[k]] = ww;
     it.dw[gi[k]] = gg;
     const __nv_bfloat16 wb = __float2bfloat16_rn(ww);
@@ -485,10 +520,9 @@ int yc::sgd_item_blocks(const SgdItem& it) {
   const long long elements = it.taps > 0 ? (long long)it.out_c * it.taps * it.in_c : it.out_c;
   return (int)((elements + 1023) / 1024);
 }
-int yc::sgd_update_multi(const SgdItem* items_dev, int n_items, int total_blocks, float lr, int batch, float momentum,
-                         float decay, cudaStream_t st) {
+int yc::sgd_update_multi(const SgdItem* items_dev, int n_items, int total_blocks, const UpdRule& rule, cudaStream_t st) {
   if (n_items <= 0 || total_blocks <= 0) return YC_OK;
-  sgd_multi_kernel<<<total_blocks, 256, 0, st>>>(items_dev, n_items, lr / batch, decay * batch, momentum);
+  sgd_multi_kernel<<<total_blocks, 256, 0, st>>>(items_dev, n_items, rule);
   YC_LAUNCH_CHECK();
   return YC_OK;
 }

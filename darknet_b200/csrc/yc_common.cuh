@@ -54,10 +54,19 @@ struct SgdItem {
   __nv_bfloat16* wp_d;    // bf16 data-gradient packing [c][flipped tap][out_c_p] (or null)
   int out_c, in_c, taps, ldw, in_c_p, out_c_p;  // taps == 0: plain vector of out_c elements
   int first_block, blocks;
+  float* m;               // Adam moments, laid out like dw (null: SGD)
+  float* v;
+};
+// UpdateConvolutionalLayerGpu's rule (convolutional_kernels.cu:865-922): SGD with momentum and decay, or Adam
+// (adam_update_gpu, blas_kernels.cu:99-134) when adam != 0: rate is the learning rate NOT divided by the batch, t the
+// iteration (l->t, network_kernels.cu:229).
+struct UpdRule {
+  float lr_over_batch, decay_batch, momentum;
+  int adam, t;
+  float B1, B2, eps, rate;
 };
 int sgd_item_blocks(const SgdItem& it);
-int sgd_update_multi(const SgdItem* items_dev, int n_items, int total_blocks, float lr, int batch, float momentum,
-                     float decay, cudaStream_t st);
+int sgd_update_multi(const SgdItem* items_dev, int n_items, int total_blocks, const UpdRule& rule, cudaStream_t st);
 
 // ---- device-side activation math shared by the conv epilogue and the elementwise kernels ------
 // Formulas follow the reference (activations.h:80-121, activation_kernels.cu:56-79), fp32.

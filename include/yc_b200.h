@@ -526,11 +526,13 @@ YC_API int yc_network_train_datum(yc_network* net, const float* x_host, const fl
  * it does not synchronise with the legacy default stream) — pass one and the same stream to yc_network_forward_backward
  * and yc_network_update, and record timing events on that stream. */
 YC_API int yc_network_forward_backward(yc_network* net, const float* input_dev_nchw, const float* truth_dev, void* stream);
-/* UpdateNetworkGpu (network_kernels.cu:214-243): SGD step on every conv layer.  lr < 0 = GetCurrLr at the current iteration
- * (yc_network_current_rate; with the default constant policy and no burn-in that is [net] learning_rate), negative
- * momentum / decay = the cfg's [net] values; batch = net batch * subdivisions (x data-parallel world size).  Layers are
- * skipped as the reference does: burnin_update * burn_in > iter, train_only_bn, dont_update >= iter.  Advances the
- * iteration count.  stream NULL = the network's own stream. */
+/* The tail of TrainNetwork (network.cpp:227-231): curr_iter++ and then UpdateNetworkGpu (network_kernels.cu:214-243) ->
+ * UpdateConvolutionalLayerGpu on every conv layer (convolutional_kernels.cu:865-922): NaN / Inf scrub of gradient and
+ * weights, then SGD with momentum and decay, or adam_update_gpu under [net] adam=1 (B1, B2, eps; t = iter), in one launch.
+ * lr < 0 = GetCurrLr at the incremented iteration (yc_network_current_rate; with the default constant policy and no burn-in
+ * that is [net] learning_rate), negative momentum / decay = the cfg's [net] values; batch = net batch * subdivisions
+ * (x data-parallel world size).  Layers are skipped as the reference does: burnin_update * burn_in > iter, train_only_bn,
+ * dont_update >= iter.  stream NULL = the network's own stream. */
 YC_API int yc_network_update(yc_network* net, float lr, float momentum, float decay, void* stream);
 /* net->benchmark_layers for the training step: device time by operator category (CUDA events after every operator),
  * averaged over iters.  ms[7]: conv fprop, wgrad, dgrad, batchnorm/activation passes, other layers + loss, SGD update,
