@@ -83,7 +83,8 @@ def _ncu_traffic(n_conv):
             lines = [l for l in f if l.startswith('"')]
         per = {}
         for r in csv.DictReader(lines):
-            if "conv_fprop" not in r["Kernel Name"] or not r["Metric Name"].startswith("dram__bytes"):
+            conv = "conv_fprop" in r["Kernel Name"] or "stem_conv" in r["Kernel Name"]  # (the stem is a conv launch of its own)
+            if not conv or not r["Metric Name"].startswith("dram__bytes"):
                 continue
             sc = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(r["Metric Unit"], 1.0)
             per[int(r["ID"])] = per.get(int(r["ID"]), 0.0) + float(r["Metric Value"].replace(",", "")) * sc
