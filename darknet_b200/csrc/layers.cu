@@ -335,6 +335,54 @@ __global__ void maxpool_s1_slab_kernel(View x, View y, int size, int off) {
   }
 }
 
+// The SPP block as ONE launch: its three stride-1 max-pools (5 / 9 / 13) read the same tensor, so the slab is staged once
+// and the separable row / column passes run once per window into the three outputs (each result identical to
+// maxpool_s1_slab_kernel's: max is a selection).  Three launches of ~25 us on 24 MB tensors were launch / ramp bound.
+struct PoolMulti {
+  View y[3];
+  int size[3], off[3];
+  int n;
+};
+__global__ void maxpool_s1_multi_kernel(View x, PoolMulti pm) {
+  extern __shared__ uint4 pool_sm[];
+  const int hw = x.h * x.w, items = hw * kPoolG;
+  uint4* in = pool_sm;
+  uint4* rows = pool_sm + items;
+  const int chunks = (x.c / 8 + kPoolG - 1) / kPoolG;
+  const int b = blockIdx.x / chunks, g0 = (blockIdx.x % chunks) * kPoolG;
+  const int gn = min(kPoolG, x.c / 8 - g0);
+  const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x.ptr) + (long long)b * hw * x.ldc + g0 * 8;
+  for (int i = threadIdx.x; i < items; i += blockDim.x) {
+    const int pix = i / kPoolG, g = i % kPoolG;
+    if (g < gn) in[i] = *reinterpret_cast<const uint4*>(xp + (long long)pix * x.ldc + g * 8);
+  }
+  for (int o = 0; o < pm.n; ++o) {
+    const int size = pm.size[o], off = pm.off[o];
+    __syncthreads();  // the slab is loaded / the previous window's column pass has read `rows`
+    for (int i = threadIdx.x; i < items; i += blockDim.x) {
+      const int pix = i / kPoolG, g = i % kPoolG;
+      if (g >= gn) continue;
+      const int ow = pix % x.w, r0 = pix - ow;
+      const int k0 = max(0, ow + off), k1 = min(x.w - 1, ow + off + size - 1);
+      uint4 m = in[(r0 + k0) * kPoolG + g];
+      for (int k = k0 + 1; k <= k1; ++k) m = max8_bf16(m, in[(r0 + k) * kPoolG + g]);
+      rows[i] = m;
+    }
+    __syncthreads();
+    __nv_bfloat16* yp = reinterpret_cast<__nv_bfloat16*>(pm.y[o].ptr) + (long long)b * hw * pm.y[o].ldc + g0 * 8;
+    const long long ldy = pm.y[o].ldc;
+    for (int i = threadIdx.x; i < items; i += blockDim.x) {
+      const int pix = i / kPoolG, g = i % kPoolG;
+      if (g >= gn) continue;
+      const int oh = pix / x.w, ow = pix - oh * x.w;
+      const int n0 = max(0, oh + off), n1 = min(x.h - 1, oh + off + size - 1);
+      uint4 m = rows[(n0 * x.w + ow) * kPoolG + g];
+      for (int n = n0 + 1; n <= n1; ++n) m = max8_bf16(m, rows[(n * x.w + ow) * kPoolG + g]);
+      *reinterpret_cast<uint4*>(yp + (long long)pix * ldy + g * 8) = m;
+    }
+  }
+}
+
 // ---- upsample: upsample_kernel (blas_kernels.cu:1121-1155), forward, nearest ----------------------
 __global__ void upsample_kernel(View x, View y, int stride, float scale) {
   const int groups = (x.c + 7) / 8;
@@ -573,6 +621,38 @@ extern "C" int yc_maxpool_fwd(const yc_tensor* x, const yc_tensor* y, int size, 
   maxpool_kernel<<<grid_for(work, 256), 256, 0, (cudaStream_t)stream>>>(mk(x), mk(y), size, stride, pad, quirk);
   YC_LAUNCH_CHECK();
   return YC_OK;
+}
+
+// true when yc_maxpool_fwd would take the shared-memory slab path for this geometry (stride 1, "same" output, bf16)
+static bool pool_slab_ok(const yc_tensor* x, const yc_tensor* y, int size, int stride, int pad) {
+  const size_t slab = (size_t)x->h * x->w * kPoolG * sizeof(uint4) * 2;
+  return stride == 1 && x->dtype == YC_BF16 && y->dtype == YC_BF16 && x->c % 8 == 0 && y->h == x->h && y->w == x->w &&
+         y->n == x->n && y->c == x->c && pad / 2 < size && size - 1 - pad / 2 >= 0 && slab <= 160 * 1024;
+}
+extern "C" int yc_maxpool_s1_multi(const yc_tensor* x, int n_out, const yc_tensor* const* ys, const int* sizes, const int* pads,
+                                   void* stream) {
+  YC_CHECK_T(x, "yc_maxpool_s1_multi x");
+  YC_REQUIRE(n_out >= 1 && n_out <= 3 && ys && sizes && pads && aligned16(x), "yc_maxpool_s1_multi: 1..3 outputs");
+  PoolMulti pm;
+  pm.n = n_out;
+  for (int o = 0; o < n_out; ++o) {
+    YC_CHECK_T(ys[o], "yc_maxpool_s1_multi y");
+    YC_REQUIRE(aligned16(ys[o]) && sizes[o] >= 1 && pads[o] >= 0 && pool_slab_ok(x, ys[o], sizes[o], 1, pads[o]),
+               "yc_maxpool_s1_multi: output %d is not a stride-1 same-size bf16 max-pool that fits the shared-memory slab", o);
+    pm.y[o] = mk(ys[o]);
+    pm.size[o] = sizes[o];
+    pm.off[o] = -pads[o] / 2;
+  }
+  const size_t slab = (size_t)x->h * x->w * kPoolG * sizeof(uint4) * 2;
+  if (slab > 48 * 1024)
+    YC_CUDA(cudaFuncSetAttribute(maxpool_s1_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+  const int chunks = (x->c / 8 + kPoolG - 1) / kPoolG;
+  maxpool_s1_multi_kernel<<<x->n * chunks, 256, slab, (cudaStream_t)stream>>>(mk(x), pm);
+  YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+extern "C" int yc_maxpool_s1_multi_eligible(const yc_tensor* x, const yc_tensor* y, int size, int stride, int pad) {
+  return (x && y && aligned16(x) && aligned16(y) && pool_slab_ok(x, y, size, stride, pad)) ? 1 : 0;
 }
 
 extern "C" int yc_upsample_fwd(const yc_tensor* x, const yc_tensor* y, int stride, float scale, void* stream) {

@@ -317,6 +317,11 @@ int run_op(yc_network* net, const Op& op, cudaStream_t st) {
     case 0: return yc_conv_fprop(L->plan, st);
     case 1: return yc_maxpool_fwd(&op.a, &op.y, op.i0, op.i1, op.i2, op.i3, st);
     case 2: return yc_upsample_fwd(&op.a, &op.y, op.i0, op.f0, st);
+    case 9: {
+      const yc_tensor* ys[3] = {&op.y, &op.b, &op.y3};
+      const int sizes[3] = {op.i0, op.i2, op.i4}, pads[3] = {op.i1, op.i3, op.i5};
+      return yc_maxpool_s1_multi(&op.a, op.n_out, ys, sizes, pads, st);
+    }
     case 3: return yc_shortcut_fwd(&op.a, &op.b, &op.y, op.i0, st);
     case 4: return yc_route_copy(&op.a, &op.y, st);
     case 5: return yc_yolo_decode(&op.a, L->dec_dev, op.i0, op.i1, op.f0, op.i2, st);
@@ -713,6 +718,38 @@ extern "C" int yc_network_finalize(yc_network* net) {
         break;
       }
     }
+  }
+  // ---- the SPP block: consecutive stride-1 max-pools that read the SAME tensor (route elision makes the route layers
+  // between them views) become one launch that stages the input once (yc_maxpool_s1_multi)
+  {
+    std::vector<Op> merged;
+    for (size_t k = 0; k < net->ops.size(); ++k) {
+      Op op = net->ops[k];
+      auto poolable = [&](const Op& o) {
+        return o.kind == 1 && o.i3 == 0 && yc_maxpool_s1_multi_eligible(&o.a, &o.y, o.i0, o.i1, o.i2);
+      };
+      auto same_input = [&](const Op& o) {
+        return o.a.ptr == op.a.ptr && o.a.n == op.a.n && o.a.h == op.a.h && o.a.w == op.a.w && o.a.c == op.a.c &&
+               o.a.ldc == op.a.ldc && o.a.dtype == op.a.dtype;
+      };
+      if (poolable(op)) {
+        size_t e = k + 1;
+        while (e < net->ops.size() && e - k < 3 && poolable(net->ops[e]) && same_input(net->ops[e])) ++e;
+        if (e - k >= 2) {
+          Op m = op;  // op.layer stays the first pool's: per-layer timing reports the block there
+          m.kind = 9;
+          m.n_out = (int)(e - k);
+          m.i0 = op.i0; m.i1 = op.i2;
+          m.b = net->ops[k + 1].y; m.i2 = net->ops[k + 1].i0; m.i3 = net->ops[k + 1].i2;
+          if (e - k == 3) { m.y3 = net->ops[k + 2].y; m.i4 = net->ops[k + 2].i0; m.i5 = net->ops[k + 2].i2; }
+          merged.push_back(m);
+          k = e - 1;
+          continue;
+        }
+      }
+      merged.push_back(op);
+    }
+    net->ops.swap(merged);
   }
   NET_CUDA(cudaDeviceSynchronize());  // memsets / uploads of the set-up ran on the legacy stream: finish them
   net->finalized = true;

@@ -94,8 +94,10 @@ struct NLayer {
 
 struct Op {
   int layer;
-  int kind;  // 0 conv, 1 maxpool, 2 upsample, 3 shortcut, 4 route copy, 5 yolo decode, 6 input convert, 7 stem operand, 8 direct stem conv
-  yc_tensor a, b, y;
+  int kind;  // 0 conv, 1 maxpool, 2 upsample, 3 shortcut, 4 route copy, 5 yolo decode, 6 input convert, 7 stem operand, 8 direct stem conv,
+             // 9 several stride-1 max-pools of one tensor (SPP): outputs y, b, y3 with (size, pad) = (i0, i1), (i2, i3), (i4, i5)
+  yc_tensor a, b, y, y3;
+  int i4 = 0, i5 = 0, n_out = 1;
   int i0 = 0, i1 = 0, i2 = 0, i3 = 0;
   float f0 = 0.f;
 };

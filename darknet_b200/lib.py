@@ -128,6 +128,8 @@ _SIGS = {
     "yc_shortcut_bwd": (C.c_int, [_TP, _TP, C.c_int, _TP, _TP, _P]),
     "yc_sgd_update_conv": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_float, C.c_float, _P, _P, _P, _P, _P, _P, _P]),
     "yc_maxpool_fwd": (C.c_int, [_TP, _TP, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+    "yc_maxpool_s1_multi": (C.c_int, [_TP, C.c_int, _P, _P, _P, _P]),
+    "yc_maxpool_s1_multi_eligible": (C.c_int, [_TP, _TP, C.c_int, C.c_int, C.c_int]),
     "yc_upsample_fwd": (C.c_int, [_TP, _TP, C.c_int, C.c_float, _P]),
     "yc_shortcut_fwd": (C.c_int, [_TP, _TP, _TP, C.c_int, _P]),
     "yc_route_copy": (C.c_int, [_TP, _TP, _P]),

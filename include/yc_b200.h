@@ -281,6 +281,13 @@ YC_API int yc_conv_wgrad_pack(const float* dw_oihw, int out_c, int in_c, int ksi
  * == the reference GPU kernel. */
 YC_API int yc_maxpool_fwd(const yc_tensor* x, const yc_tensor* y, int size, int stride, int pad,
                    int ref_cpu_quirk, void* stream);
+/* Up to three stride-1 "same" max-pools of ONE bf16 tensor in one launch (the SPP block, maxpool 5 / 9 / 13 of yolov4 /
+ * yolov3-spp: three forward_maxpool_layer_gpu calls on the same input, maxpool_layer_kernels.cu:58-101): the input slab is
+ * staged in shared memory once.  ys[o] may be channel slices of one concat buffer.  Results are identical to yc_maxpool_fwd.
+ * yc_maxpool_s1_multi_eligible: 1 when (x, y, size, stride, pad) can be one of the outputs. */
+YC_API int yc_maxpool_s1_multi(const yc_tensor* x, int n_out, const yc_tensor* const* ys, const int* sizes, const int* pads,
+                               void* stream);
+YC_API int yc_maxpool_s1_multi_eligible(const yc_tensor* x, const yc_tensor* y, int size, int stride, int pad);
 /* ForwardUpsampleLayerGpu (upsample_layer.c:106-119, blas_kernels.cu:1121-1155): nearest x stride */
 YC_API int yc_upsample_fwd(const yc_tensor* x, const yc_tensor* y, int stride, float scale, void* stream);
 /* ForwardShortcutLayerGpu (shortcut_layer.c:191-204, blas_kernels.cu:941-978): y = act(a + b) */

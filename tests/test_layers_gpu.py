@@ -196,3 +196,51 @@ def test_reorg_fwd_bwd_bit_exact(gpu, stride, dtype):
     dxd, ic = ops.reorg_bwd(dyd, oc, stride, 0)
     dx = ops.to_nchw(dxd, ic).cpu().numpy()
     assert ic == C and np.array_equal(dx, O.reorg(dy, stride, 1))
+
+
+@pytest.mark.parametrize("B,H,W,C", [(3, 19, 19, 512), (2, 13, 13, 48), (1, 20, 17, 16)])
+def test_spp_maxpools_in_one_launch(gpu, B, H, W, C):
+    """yc_maxpool_s1_multi (the SPP block's three stride-1 max-pools of one tensor, outputs = channel slices of the concat
+    buffer) == three yc_maxpool_fwd calls, bit for bit (those are checked against the oracle above)."""
+    import ctypes as C_
+    from darknet_b200 import lib as L
+    lib = L.lib()
+    g = torch.Generator(device="cpu").manual_seed(H * 100 + C)
+    cat = torch.randn((B, H, W, 4 * C), generator=g).to(torch.bfloat16).to(gpu)        # [mp13 | mp9 | mp5 | x] like route -1,-3,-5,-6
+    x = L.view(cat, B, H, W, C, 4 * C, c_off=3 * C)
+    sizes, pads = [5, 9, 13], [4, 8, 12]
+    want = cat.clone()
+    for o, (s, p) in enumerate(zip(sizes, pads)):
+        y = L.view(want, B, H, W, C, 4 * C, c_off=(2 - o) * C)
+        xw = L.view(want, B, H, W, C, 4 * C, c_off=3 * C)
+        L.check(lib.yc_maxpool_fwd(xw, y, s, 1, p, 0, L.stream_ptr()), "yc_maxpool_fwd")
+    got = cat.clone()
+    xg = L.view(got, B, H, W, C, 4 * C, c_off=3 * C)
+    ys = [L.view(got, B, H, W, C, 4 * C, c_off=(2 - o) * C) for o in range(3)]
+    arr = (C_.POINTER(L.Tensor) * 3)(*[C_.pointer(y) for y in ys])
+    assert all(lib.yc_maxpool_s1_multi_eligible(xg, y, s, 1, p) == 1 for y, s, p in zip(ys, sizes, pads))
+    L.check(lib.yc_maxpool_s1_multi(xg, 3, arr, (C_.c_int * 3)(*sizes), (C_.c_int * 3)(*pads), L.stream_ptr()), "yc_maxpool_s1_multi")
+    torch.cuda.synchronize()
+    assert torch.equal(got, want)
+    assert not torch.equal(got[..., :C], cat[..., :C])
+
+
+def test_spp_block_of_the_network_is_merged(gpu):
+    """yolov4's SPP max-pools run as one launch under route elision (default) and as three without it: same outputs"""
+    from darknet_b200 import cfg as cfgmod, cfgs, lib as L, network as N
+    text = cfgs.CONFIGS["yolov4"](w=320, h=320)
+    weights = cfgmod.synth_weights(text)
+    x = cfgmod.synth_images(2, 3, 320, 320, seed=9)
+    outs, n_ops = [], []
+    for flags in (L.NET_DEFAULT, L.NET_DEFAULT & ~L.NET_ELIDE_ROUTE):
+        net = N.LoadSynthetic(text, weights, batch=2, flags=flags)
+        pools = [i for i in range(net.n) if net.layer_type(i) == "maxpool"]
+        assert len(pools) == 3
+        N.NetworkPredict(net, x)
+        n_ops.append(L.lib().yc_network_info(net.h, 6))
+        outs.append([np.array(net.layer_output(i), copy=True) for i in pools + [pools[-1] + 1]])
+        net.close()
+    for a, b in zip(*outs):
+        assert np.array_equal(a, b)
+    routes = 21   # yolov4 has 21 [route] layers: at least one copy each without elision, and the pools stay apart
+    assert n_ops[1] - n_ops[0] >= routes + 2, f"ops {n_ops}: the three pools are not one launch"
