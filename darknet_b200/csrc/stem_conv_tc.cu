@@ -6,19 +6,20 @@
 // (convolutional_kernels.cu:252-553, im2col_kernels.cu) and add_bias / activate_array.
 //
 // Tile = 8 rows x 16 columns of output pixels = the 128 rows of one MMA.  Per CTA (persistent, one per SM, 26 warps):
-//   warp 8     one lane TMA-loads each tile's input patch — box {24 w, 10 h, 3 c} fp32 of the NCHW image starting one row
-//              above and four columns left of the tile, the engine zero-fills whatever lies outside the image (= the padding) — into an 8-deep
-//              ring of 2880-byte slots;
-//   warps 0-7  "builders", two groups of four taking tiles round robin: thread p of a group owns pixel (p / 16, p % 16): 27 shared-memory loads from the patch, rounded
-//              to bf16 and written as the pixel's 64-byte K-major row — column (kh*3+kw)*3+ci, 27 of 32 used — in the
-//              64B-swizzled layout the tensor core reads (generic-proxy stores + fence.proxy.async + an mbarrier the 128
-//              builders arrive on);
-//   warp 9     one elected lane issues two tcgen05.mma (M128 x N32 x K16 each) per tile against the 32 x 32 filter matrix
-//              resident in shared memory, accumulators in TMEM (8 buffers of 32 columns), tcgen05.commit frees the A slot
-//              and publishes the accumulator;
+//   warp 8      one lane TMA-loads each tile's input patch — box {24 w, 10 h, 3 c} fp32 of the NCHW image starting one
+//               row above and four columns left of the tile; the engine zero-fills whatever lies outside the image (=
+//               the padding) — into an 8-deep ring of 2880-byte slots;
+//   warps 0-7   "builders", two groups of four taking tiles round robin: thread p of a group owns pixel (p / 16, p % 16):
+//               27 shared-memory loads from the patch, rounded to bf16 and written as the pixel's 64-byte K-major row —
+//               column (kh*3+kw)*3+ci, 27 of 32 used — in the 64B-swizzled layout the tensor core reads (generic-proxy
+//               stores + fence.proxy.async + an mbarrier the 128 builders of the group arrive on);
+//   warp 9      one elected lane issues two tcgen05.mma (M128 x N32 x K16 each) per tile against the 32 x 32 filter
+//               matrix resident in shared memory, accumulators in TMEM (8 buffers of 32 columns), tcgen05.commit frees
+//               the A slot and publishes the accumulator;
 //   warps 10-25 epilogue, four sets of four (one warp per TMEM lane quadrant) taking tiles round robin: tcgen05.ld ->
-//              + bias -> activation -> bf16 -> swizzled staging -> TMA store of a {32 ch, 16 w, 2 h} box (clipped at the
-//              image border and at the channel count, so partial tiles and concat slices need no special case).
+//               + bias -> activation (packed fp32 pairs) -> bf16 -> swizzled staging -> TMA store of a {32 ch, 16 w, 2 h}
+//               box (clipped at the image border and at the channel count: partial tiles and concat slices need no
+//               special case).
 // HBM traffic: 12 B read + 64 B written per pixel (the operand path: 204 B).  The layer is then bound by its activation:
 // 757 M mish values x 2 MUFU on yolov4-608 x 64 = 0.37 ms of XU-pipe time at 16 per clock per SM.
 // The input map needs a row pitch that is a multiple of 16 bytes: widths that are not a multiple of 4 go to the mma.sync
