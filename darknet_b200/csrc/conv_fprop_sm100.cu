@@ -41,6 +41,7 @@ struct ConvParams {
   int halo_stages;       // a_mode 2: patch ring depth (2..kHaloMaxStages)
   int halo_pair;         // a_mode 2 + w_resident + one chunk: two tiles' MMAs interleaved into two accumulators
   int tile_pair;         // a_mode 0 / 1, one N tile, block_n <= 128: the same on the tiled / im2col path
+  int issue_v2;          // halo mode, resident weights: unrolled tap issue (halo_taps_resident); 0 = the rolled loop (A/B)
   int Ho, Wo, stride, pad, dil;
   int kw, stride_w, pad_w;  // kernel width / stride / left padding along W (== ksize / stride / pad unless rectangular)
   const float* bias;   // padded to n_tiles*block_n
@@ -687,6 +688,40 @@ __device__ __forceinline__ void epilogue_pair_dispatch(const ConvParams& p, cons
   }
 }
 
+// Halo mode with resident weights: the nine taps of one 64- / 32-channel chunk for a tile (pair), fully unrolled.
+// ncu on 3x3 32->64 @304 (the MMA warp never waits, everything else does): the rolled loop spent ~85 instructions per tap —
+// tap / 3, the patch shift, three descriptors rebuilt from addresses in vector registers and moved over with R2UR, a
+// try_wait on a barrier that completed with the CTA's first tile — i.e. ~900 instructions of ONE warp per tile pair, which
+// is what bounded the layer.  Here the descriptors are base + compile-time constant (a descriptor is linear in the
+// address: start field = addr >> 4, no carry for shared-memory addresses), and the slab barriers are polled for the first
+// tile pair only.
+template <int HSTEPS>  // K16 steps per chunk: 4 (64 channels, 128-byte rows) or 2 (32 channels, 64-byte rows)
+__device__ __forceinline__ void halo_taps_resident(bool leader, bool two, bool first, bool acc_in, uint32_t d0, uint32_t d1,
+                                                   uint32_t pa0, uint32_t pa1, uint32_t slab0, uint32_t slab_step,
+                                                   uint32_t full0, uint32_t full_step, uint32_t idesc) {
+  constexpr uint32_t hrow = 32u * HSTEPS;
+  const uint64_t abase0 = ptx::make_smem_desc_shifted(pa0, kHaloPitch * hrow, hrow);
+  const uint64_t abase1 = ptx::make_smem_desc_shifted(pa1, kHaloPitch * hrow, hrow);
+  const uint64_t bbase = ptx::make_smem_desc(slab0, hrow);
+  const uint64_t bstep = (uint64_t)(slab_step >> 4);
+#pragma unroll
+  for (int tap = 0; tap < 9; ++tap) {
+    if (first) {  // the slab of (tap, chunk) arrives with this CTA's first tiles; its barrier is never re-armed
+      ptx::mbar_wait(full0 + (uint32_t)tap * full_step, 0);
+      ptx::tc_fence_after();
+    }
+    constexpr uint32_t kp = kHaloPitch;
+    const uint64_t sh = (uint64_t)((((uint32_t)(tap / 3) * kp + (uint32_t)(tap % 3)) * hrow) >> 4);
+    const uint64_t b = bbase + bstep * (uint64_t)tap;
+#pragma unroll
+    for (int k = 0; k < HSTEPS; ++k) {
+      const uint32_t acc = (tap | k) != 0 ? 1u : (acc_in ? 1u : 0u);
+      if (leader) ptx::mma_bf16_ss(d0, abase0 + sh + 2u * k, b + 2u * k, idesc, acc);
+      if (leader && two) ptx::mma_bf16_ss(d1, abase1 + sh + 2u * k, b + 2u * k, idesc, acc);
+    }
+  }
+}
+
 // 96 registers is the ceiling for 576 threads: the register file is allocated to warps in groups of four, so the CTA
 // counts as 640 threads (65536 / 640 = 102 -> 96); a build with __maxnreg__(112) (64512 registers by the per-warp
 // count) fails to launch on B200 ("too many resources requested").
@@ -844,6 +879,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     int it = 0;
     const int G = p.halo_pair ? 2 : 1;
     const int nacc_shift = 31 - __clz(p.nacc);
+    bool first_pair = true;  // resident weight slabs arrive with the first tiles (halo_taps_resident)
     for (int tb = blockIdx.x; tb < total_tiles; tb += G * gridDim.x) {
       const bool two = G == 2 && tb + (int)gridDim.x < total_tiles;
       const int acc0 = it & (p.nacc - 1), acc1 = (it + 1) & (p.nacc - 1);
@@ -862,6 +898,13 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
         ptx::tc_fence_after();
         const uint32_t pa0 = patch_base + ps0 * kHaloPatchStride, pa1 = patch_base + ps1 * kHaloPatchStride;
+        if (p.w_resident && p.issue_v2) {  // slab (tap, cc) lives in ring slot tap*cchunks + cc
+          const uint32_t slab0 = smem_base + cc * stage_bytes, slab_step = p.cchunks * stage_bytes;
+          if (hsteps == 4)
+            halo_taps_resident<4>(leader, two, first_pair, cc != 0, d0, d1, pa0, pa1, slab0, slab_step, full_bar(cc), 8u * p.cchunks, idesc);
+          else
+            halo_taps_resident<2>(leader, two, first_pair, cc != 0, d0, d1, pa0, pa1, slab0, slab_step, full_bar(cc), 8u * p.cchunks, idesc);
+        } else
         for (int tap = 0; tap < 9; ++tap) {
           const int kh = tap / 3, kw = tap - kh * 3;
           if (p.w_resident) {  // slot of this slab; its barrier completed phase 0 once and is never re-armed
@@ -895,6 +938,7 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         if (leader) ptx::mma_commit(pempty_bar(ps0));  // the patches are free once the nine taps' MMAs have retired
         if (leader && two) ptx::mma_commit(pempty_bar(ps1));
       }
+      first_pair = false;
       if (leader) ptx::mma_commit(tfull_bar(acc0));
       if (leader && two) ptx::mma_commit(tfull_bar(acc1));
       __syncwarp();
@@ -1467,6 +1511,7 @@ typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t
                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 EncodeTiledFn g_encode_tiled = nullptr;
+int g_issue_v2 = 1;  // yc_conv_fprop_set_issue_v2 (A/B): plans created from now on use the unrolled halo tap issue
 EncodeIm2colFn g_encode_im2col = nullptr;
 
 int load_driver_entry_points() {
@@ -1762,6 +1807,7 @@ static int plan_create_impl(yc_conv_plan** out_plan, const yc_conv_desc* d, int 
     p.nacc = std::max(2, p.epi_sets);
     if (p.block_n <= 128) p.nacc = 4;  // 4 x 128 columns fit: deeper MMA/epilogue decoupling for free
   }
+  p.issue_v2 = g_issue_v2;
   uint32_t cols = 32;
   while (cols < (uint32_t)(p.nacc * p.block_n)) cols <<= 1;
   p.tmem_cols = cols;
@@ -2094,6 +2140,12 @@ extern "C" int yc_conv_fprop(const yc_conv_plan* pl, void* stream) {
   else
     conv_fprop_kernel_t<false><<<pl->grid, kThreads, pl->smem, (cudaStream_t)stream>>>(pl->tmap_a, pl->tmap_b, pl->tmap_y, pl->tmap_y2, pl->p);
   YC_LAUNCH_CHECK();
+  return YC_OK;
+}
+
+// (A/B) plans created from now on issue the halo taps unrolled (1, default) or with the rolled loop (0)
+extern "C" int yc_conv_fprop_set_issue_v2(int on) {
+  g_issue_v2 = on ? 1 : 0;
   return YC_OK;
 }
 

@@ -94,6 +94,7 @@ _SIGS = {
     "yc_conv_plan_create_ex": (C.c_int, [C.POINTER(_P), C.POINTER(ConvDesc), _TP, _P, _P, _P, _TP, _TP, _TP, C.c_uint]),
     "yc_conv_plan_destroy": (C.c_int, [_P]),
     "yc_conv_fprop": (C.c_int, [_P, _P]),
+    "yc_conv_fprop_set_issue_v2": (C.c_int, [C.c_int]),
     "yc_conv_plan_info": (C.c_int, [_P, C.c_int]),
     "yc_conv_plan_set_stats": (C.c_int, [_P, _P, _P]),
     "yc_conv_plan_set_bias": (C.c_int, [_P, _P, _P]),

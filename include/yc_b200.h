@@ -176,6 +176,9 @@ YC_API int yc_conv_plan_create_ex(yc_conv_plan** plan, const yc_conv_desc* desc,
 YC_API int yc_conv_plan_destroy(yc_conv_plan* plan);
 /* launch (1 kernel). */
 YC_API int yc_conv_fprop(const yc_conv_plan* plan, void* stream);
+/* (A/B) conv plans created from now on issue the nine taps of a halo tile unrolled with constant descriptor offsets (1, the
+ * default) or through the rolled loop (0).  Process-wide like yc_conv_wgrad_set_tap_groups. */
+YC_API int yc_conv_fprop_set_issue_v2(int on);
 /* plan introspection for tests/bench: what=0 block_n, 1 block_k, 2 stages, 3 tiles, 4 grid, 5 A-operand mode (0 tiled,
  * 1 im2col, 2 halo patch), 6 dynamic shared memory bytes, 7 variant bits: [0,2) A mode | 4 halo tile pairs | 8 resident
  * weights | 16 two outputs | 32 two staging buffers | 64 rectangular (pixel-pair) geometry  | 128 specialised epilogue | 256 tile pairs on the tiled / im2col path;

@@ -36,6 +36,7 @@ def main():
     for spec in args.sets:
         name, _, hx = spec.partition("=")
         extra = int(hx or "0", 16)
+        L.lib().yc_conv_fprop_set_issue_v2(0 if name.startswith("issue1") else 1)   # (process-wide A/B switch)
         net = N.LoadSynthetic(text, weights, batch=args.batch, flags=(L.NET_DEFAULT & ~L.NET_PULL_HEADS) | extra)
         for _ in range(3):
             L.check(L.lib().yc_network_forward(net.h, C.c_void_p(x.data_ptr()), sp), "forward")
