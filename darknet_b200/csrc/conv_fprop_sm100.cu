@@ -695,7 +695,8 @@ __device__ __forceinline__ void epilogue_pair_dispatch(const ConvParams& p, cons
 // is what bounded the layer.  Here the descriptors are base + compile-time constant (a descriptor is linear in the
 // address: start field = addr >> 4, no carry for shared-memory addresses), and the slab barriers are polled for the first
 // tile pair only.
-template <int HSTEPS>  // K16 steps per chunk: 4 (64 channels, 128-byte rows) or 2 (32 channels, 64-byte rows)
+template <int HSTEPS, bool PAIR = false>  // K16 steps per chunk: 4 (64 channels, 128-byte rows) or 2 (32 channels, 64-byte rows);
+                                          // PAIR: tcgen05 cta_group::2 (conv_fprop_pair_kernel)
 __device__ __forceinline__ void halo_taps_resident(bool leader, bool two, bool first, bool acc_in, uint32_t d0, uint32_t d1,
                                                    uint32_t pa0, uint32_t pa1, uint32_t slab0, uint32_t slab_step,
                                                    uint32_t full0, uint32_t full_step, uint32_t idesc) {
@@ -716,8 +717,13 @@ __device__ __forceinline__ void halo_taps_resident(bool leader, bool two, bool f
 #pragma unroll
     for (int k = 0; k < HSTEPS; ++k) {
       const uint32_t acc = (tap | k) != 0 ? 1u : (acc_in ? 1u : 0u);
-      if (leader) ptx::mma_bf16_ss(d0, abase0 + sh + 2u * k, b + 2u * k, idesc, acc);
-      if (leader && two) ptx::mma_bf16_ss(d1, abase1 + sh + 2u * k, b + 2u * k, idesc, acc);
+      if (PAIR) {
+        if (leader) ptx::mma_bf16_ss_pair(d0, abase0 + sh + 2u * k, b + 2u * k, idesc, acc);
+        if (leader && two) ptx::mma_bf16_ss_pair(d1, abase1 + sh + 2u * k, b + 2u * k, idesc, acc);
+      } else {
+        if (leader) ptx::mma_bf16_ss(d0, abase0 + sh + 2u * k, b + 2u * k, idesc, acc);
+        if (leader && two) ptx::mma_bf16_ss(d1, abase1 + sh + 2u * k, b + 2u * k, idesc, acc);
+      }
     }
   }
 }
@@ -1277,6 +1283,7 @@ conv_fprop_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
       int it = 0;
       const int G = p.halo_pair ? 2 : 1;
       const int nacc_shift = 31 - __clz(p.nacc);
+      bool first_pair = true;
       for (int tb = pair; tb < total_tiles; tb += G * npairs) {
         const bool two = G == 2 && tb + npairs < total_tiles;
         const int acc0 = it & (p.nacc - 1), acc1 = (it + 1) & (p.nacc - 1);
@@ -1295,6 +1302,13 @@ conv_fprop_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           }
           ptx::tc_fence_after();
           const uint32_t pa0 = patch_base + ps0 * kHaloPatchStride, pa1 = patch_base + ps1 * kHaloPatchStride;
+          if (p.w_resident && p.issue_v2) {  // unrolled taps, constant descriptor offsets (halo_taps_resident)
+            const uint32_t slab0 = smem_base + cc * stage_bytes, slab_step = p.cchunks * stage_bytes;
+            if (hsteps == 4)
+              halo_taps_resident<4, true>(leader, two, first_pair, cc != 0, d0, d1, pa0, pa1, slab0, slab_step, full_bar(cc), 8u * p.cchunks, idesc);
+            else
+              halo_taps_resident<2, true>(leader, two, first_pair, cc != 0, d0, d1, pa0, pa1, slab0, slab_step, full_bar(cc), 8u * p.cchunks, idesc);
+          } else
           for (int tap = 0; tap < 9; ++tap) {
             const int kh = tap / 3, kw = tap - kh * 3;
             if (p.w_resident) {
@@ -1328,6 +1342,7 @@ conv_fprop_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
           if (leader) ptx::mma_commit_pair(pempty_bar(ps0), 3);
           if (leader && two) ptx::mma_commit_pair(pempty_bar(ps1), 3);
         }
+        first_pair = false;
         if (leader) ptx::mma_commit_pair(tfull_bar(acc0), 3);
         if (leader && two) ptx::mma_commit_pair(tfull_bar(acc1), 3);
         __syncwarp();
