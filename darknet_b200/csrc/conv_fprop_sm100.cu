@@ -728,6 +728,21 @@ __device__ __forceinline__ void halo_taps_resident(bool leader, bool two, bool f
   }
 }
 
+// One K block of the tiled / im2col path for a tile (pair): KS steps of 16 channels, unrolled, descriptors advanced by
+// constants (ncu on the stride-2 32->64 layer: ~100 instructions of the MMA warp per K block with the rolled loop — three
+// descriptors rebuilt from addresses, a runtime trip count, R2UR chains — for eight MMAs).
+template <int KS>
+__device__ __forceinline__ void mma_kblock(bool two, uint32_t d0, uint32_t d1, uint64_t a0, uint64_t a1, uint64_t b, uint32_t idesc,
+                                           bool acc_in) {
+#pragma unroll
+  for (int k = 0; k < KS; ++k) {
+    const uint32_t acc = k != 0 ? 1u : (acc_in ? 1u : 0u);
+    // advancing K by 16 bf16 = 32 bytes inside the swizzle atom: +2 in the (addr >> 4) field
+    ptx::mma_bf16_ss(d0, a0 + 2u * k, b + 2u * k, idesc, acc);
+    if (two) ptx::mma_bf16_ss(d1, a1 + 2u * k, b + 2u * k, idesc, acc);
+  }
+}
+
 // 96 registers is the ceiling for 576 threads: the register file is allocated to warps in groups of four, so the CTA
 // counts as 640 threads (65536 / 640 = 102 -> 96); a build with __maxnreg__(112) (64512 registers by the per-warp
 // count) fails to launch on B200 ("too many resources requested").
@@ -986,8 +1001,8 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         }
       }
       int kb = 0;
-      for (int tap = 0; tap < p.taps; ++tap) {
-        const int r = tap / p.kw, s = tap - r * p.kw;
+      int r = 0, s = 0;  // filter row / column of the tap (no division per tap: a lone warp feeds the TMA engine)
+      for (int tap = 0; tap < p.taps; ++tap, r += (s + 1 == p.kw) ? 1 : 0, s = (s + 1 == p.kw) ? 0 : s + 1) {
         for (int cc = 0; cc < p.cchunks; ++cc, ++kb) {
           ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * stage_bytes;
@@ -1015,6 +1030,10 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const uint32_t row_bytes = p.block_k * 2;
     const int nacc_shift = 31 - __clz(p.nacc);
     const int k_steps = p.block_k / 16;
+    const uint64_t adesc_stage0 = ptx::make_smem_desc(smem_base, row_bytes);
+    const uint64_t desc_stage_step = (uint64_t)(stage_bytes >> 4), desc_a1_off = (uint64_t)(a_bytes >> 4);
+    const uint64_t desc_b_off = (uint64_t)((a_slabs * a_bytes) >> 4);
+    const uint64_t bdesc_res0 = ptx::make_smem_desc(patch_base, row_bytes), desc_bres_step = (uint64_t)(b_bytes >> 4);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
@@ -1036,16 +1055,19 @@ conv_fprop_kernel_t(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       for (int kb = 0; kb < k_blocks; ++kb) {
         ptx::mbar_wait(full_bar(stage), phase);
         ptx::tc_fence_after();
-        const uint32_t sa = smem_base + stage * stage_bytes;
-        const uint64_t adesc0 = ptx::make_smem_desc(sa, row_bytes);
-        const uint64_t adesc1 = ptx::make_smem_desc(sa + a_bytes, row_bytes);
-        const uint64_t bdesc = ptx::make_smem_desc(wres_t ? patch_base + kb * b_bytes : sa + a_slabs * a_bytes, row_bytes);
+        // a descriptor is linear in the address (start field = addr >> 4, no carry for shared-memory addresses)
+        const uint64_t adesc0 = adesc_stage0 + desc_stage_step * (uint64_t)stage;
+        const uint64_t adesc1 = adesc0 + desc_a1_off;
+        const uint64_t bdesc = wres_t ? bdesc_res0 + desc_bres_step * (uint64_t)kb : adesc0 + desc_b_off;
         if (leader) {
-          for (int k = 0; k < k_steps; ++k) {
-            // advancing K by 16 bf16 = 32 bytes inside the swizzle atom: +2 in the (addr>>4) field
-            ptx::mma_bf16_ss(d0, adesc0 + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
-            if (two) ptx::mma_bf16_ss(d1, adesc1 + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
-          }
+          if (!p.issue_v2) {  // (A/B) the rolled loop
+            for (int k = 0; k < k_steps; ++k) {
+              ptx::mma_bf16_ss(d0, adesc0 + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+              if (two) ptx::mma_bf16_ss(d1, adesc1 + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
+            }
+          } else if (k_steps == 4) mma_kblock<4>(two, d0, d1, adesc0, adesc1, bdesc, idesc, kb != 0);
+          else if (k_steps == 2) mma_kblock<2>(two, d0, d1, adesc0, adesc1, bdesc, idesc, kb != 0);
+          else mma_kblock<1>(two, d0, d1, adesc0, adesc1, bdesc, idesc, kb != 0);
           ptx::mma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
           if (kb == k_blocks - 1) {
             ptx::mma_commit(tfull_bar(acc0));
@@ -1370,8 +1392,8 @@ conv_fprop_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_
         base_w = (rem - ho * p.Wo) * p.stride_w - p.pad_w;
       }
       int kb = 0;
-      for (int tap = 0; tap < p.taps; ++tap) {
-        const int r = tap / p.kw, s = tap - r * p.kw;
+      int r = 0, s = 0;  // filter row / column of the tap (no division per tap: a lone warp feeds the TMA engine)
+      for (int tap = 0; tap < p.taps; ++tap, r += (s + 1 == p.kw) ? 1 : 0, s = (s + 1 == p.kw) ? 0 : s + 1) {
         for (int cc = 0; cc < p.cchunks; ++cc, ++kb) {
           ptx::mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * stage_bytes;
